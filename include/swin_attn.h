@@ -1,0 +1,125 @@
+/*
+ * swin_attn.h -- C ABI of the B200 (sm_100a) shifted-window attention library.
+ *
+ * This is the drop-in boundary for ONE hot path of
+ * pitlover/Monocular-Depth-Estimation: everything the reference computes
+ * between the q/k(/v) Linear and the output Linear of its two WindowAttention
+ * modules, together with the pad / torch.roll / window_partition /
+ * window_reverse / crop plumbing of the blocks that call them.
+ *
+ *   reference interface replaced                         (paths under /root/reference)
+ *   ---------------------------------------------------------------------------------
+ *   WindowAttention.forward (decoder, x & external v)    model/NewCRFs/newcrf_layers.py:110-149
+ *   WindowAttention.forward (encoder, fused qkv)         model/NewCRFs/swin_transformer.py:112-144
+ *   window_partition / window_reverse                    newcrf_layers.py:30-59, swin_transformer.py:32-61
+ *   F.pad / torch.roll / crop in the block forwards      newcrf_layers.py:210-249, swin_transformer.py:204-238
+ *   SW-MSA mask construction                             newcrf_layers.py:331-350, swin_transformer.py:361-380
+ *   relative_position_bias_table[index] gather           newcrf_layers.py:124-127, swin_transformer.py:126-129
+ *   autograd backward of all of the above                (implicit in the reference)
+ *
+ * The reference has no FFI; its boundary is the Python nn.Module API, which
+ * monocular-depth-estimation_b200/layers.py mirrors on top of these entry
+ * points (bound with ctypes).
+ *
+ * Conventions
+ *   - All tensors are "image order": (B, H, W, channels), un-shifted,
+ *     un-partitioned.  The cyclic shift, the window tiling, the zero padding
+ *     up to (Hp, Wp) = (ceil(H/ws)*ws, ceil(W/ws)*ws) and the final crop are
+ *     address arithmetic inside the kernels; nothing is materialised.
+ *   - q/k/v may be channel slices of a wider tensor (e.g. the (B,H,W,3C)
+ *     output of the qkv Linear): `*_pix_stride` is the distance in ELEMENTS
+ *     between consecutive pixels, the pointer already includes the channel
+ *     offset.  Rows and images are dense: row stride = W * pix_stride.
+ *   - head_dim must be 32 (every NewCRFs / Swin configuration); window 7 or 12.
+ *   - dtype: SWIN_ATTN_F32 (fp32 storage, fp32 FFMA math, for <=1e-5 parity)
+ *            SWIN_ATTN_BF16 (bf16 storage, tcgen05 bf16 MMA, fp32 accumulate/softmax)
+ *   - `*_pad` (nullable): C-element vectors giving the value of q/k/v at the
+ *     padding tokens (y >= H or x >= W).  The reference pads BEFORE the
+ *     Linear, so pad tokens carry the Linear bias; NULL means zeros (decoder
+ *     v, newcrf_layers.py:216).
+ *   - `stream` is a cudaStream_t (NULL = default stream).  Device entry points
+ *     never synchronise.
+ *   - Return value: 0 on success, non-zero on error; swin_attn_last_error()
+ *     then returns a message (thread-local).
+ */
+#ifndef SWIN_ATTN_H_
+#define SWIN_ATTN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { SWIN_ATTN_F32 = 0, SWIN_ATTN_BF16 = 1 };
+
+/* Which kernel family serves the bf16 forward/backward.  AUTO picks the
+ * tcgen05/TMEM kernel whenever the shape allows it. */
+enum { SWIN_ATTN_IMPL_AUTO = 0, SWIN_ATTN_IMPL_SIMT = 1, SWIN_ATTN_IMPL_TCGEN05 = 2 };
+
+typedef struct {
+  int32_t batch;       /* B */
+  int32_t height;      /* H: valid rows of q/k/v/o */
+  int32_t width;       /* W: valid columns */
+  int32_t num_heads;   /* nH; channels C = nH * 32 */
+  int32_t window;      /* ws: 7 or 12 */
+  int32_t shift;       /* 0 (W-MSA) or 0 < shift < ws (SW-MSA; reference uses ws/2) */
+  int32_t dtype;       /* SWIN_ATTN_F32 | SWIN_ATTN_BF16 */
+  int32_t impl;        /* SWIN_ATTN_IMPL_* */
+  float scale;         /* q scale, head_dim^-0.5 unless qk_scale was given */
+  float dropout_p;     /* attention dropout probability (0 in every NewCRFs config) */
+  uint64_t seed;       /* Philox seed for dropout */
+  int64_t q_pix_stride;
+  int64_t k_pix_stride;
+  int64_t v_pix_stride;
+  int64_t o_pix_stride; /* output (B,H,W,*) pixel stride, >= C */
+  int32_t mask_windows; /* nW of the explicit mask (0 when attn_mask is NULL) */
+  int32_t reserved;
+} swin_attn_shape_t;
+
+/* Forward.  o: (B,H,W,C) un-shifted & cropped.  lse (nullable): fp32
+ * (B,Hp,Wp,nH) log-sum-exp of every query row, kept for the backward. */
+int swin_attn_forward(const swin_attn_shape_t* shape,
+                      const void* q, const void* k, const void* v,
+                      const void* q_pad, const void* k_pad, const void* v_pad,
+                      const float* bias_table, /* ((2ws-1)^2, nH) fp32 */
+                      const float* attn_mask,  /* nullable: explicit additive mask (mask_windows, N, N) fp32,
+                                                  window w uses slice w % mask_windows, exactly as
+                                                  WindowAttention.forward(x, mask) does (newcrf_layers.py:130-133).
+                                                  NULL: the SW-MSA mask is derived analytically from `shift`. */
+                      void* o, float* lse, void* stream);
+
+/* Backward (recomputes the probabilities from q, k, lse).  Requires H, W to be
+ * multiples of ws (the caller pads explicitly when it needs gradients, so that
+ * pad-token gradients reach the Linear bias through autograd).
+ * dq/dk/dv use the q/k/v pixel strides of `shape`; d_bias_table is fp32
+ * ((2ws-1)^2, nH) and is OVERWRITTEN (zeroed, then accumulated). */
+int swin_attn_backward(const swin_attn_shape_t* shape,
+                       const void* q, const void* k, const void* v,
+                       const void* o, const void* d_o, const float* lse,
+                       const float* bias_table, const float* attn_mask,
+                       void* dq, void* dk, void* dv, float* d_bias_table,
+                       void* stream);
+
+/* Host-buffer forward: q/k/v/o are HOST pointers (pinned or pageable) laid out
+ * as dense (B,H,W,C) tensors; the call stages them through device scratch that
+ * the library owns, runs swin_attn_forward and copies o back before returning.
+ * This is the end-to-end entry a non-PyTorch caller would bind. */
+int swin_attn_forward_host(const swin_attn_shape_t* shape,
+                           const void* q, const void* k, const void* v,
+                           const void* q_pad, const void* k_pad, const void* v_pad,
+                           const float* bias_table, void* o);
+
+/* Number of kernel launches issued by this library since load (all threads). */
+uint64_t swin_attn_launch_count(void);
+
+/* 1 if the tcgen05 kernel serves this shape under IMPL_AUTO, else 0. */
+int swin_attn_uses_tcgen05(const swin_attn_shape_t* shape, int backward);
+
+const char* swin_attn_last_error(void);
+const char* swin_attn_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SWIN_ATTN_H_ */

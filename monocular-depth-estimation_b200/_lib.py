@@ -1,0 +1,78 @@
+"""ctypes binding of libswin_attn.so (C ABI in include/swin_attn.h).
+
+There is no fallback: if the library has not been built (``python -c "import
+__graft_entry__ as g; g.build()"`` or ``csrc/build.sh``) importing the ops
+raises, and every entry point raises ``RuntimeError`` with the library's own
+message on a non-zero return code.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_uint64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libswin_attn.so")
+
+F32, BF16 = 0, 1
+IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05 = 0, 1, 2
+
+EXPORTS = (
+    "swin_attn_forward",
+    "swin_attn_backward",
+    "swin_attn_forward_host",
+    "swin_attn_launch_count",
+    "swin_attn_uses_tcgen05",
+    "swin_attn_last_error",
+    "swin_attn_version",
+)
+
+
+class Shape(Structure):
+    """Mirror of ``swin_attn_shape_t``."""
+
+    _fields_ = [
+        ("batch", c_int32), ("height", c_int32), ("width", c_int32), ("num_heads", c_int32),
+        ("window", c_int32), ("shift", c_int32), ("dtype", c_int32), ("impl", c_int32),
+        ("scale", c_float), ("dropout_p", c_float), ("seed", c_uint64),
+        ("q_pix_stride", c_int64), ("k_pix_stride", c_int64), ("v_pix_stride", c_int64), ("o_pix_stride", c_int64),
+        ("mask_windows", c_int32), ("reserved", c_int32),
+    ]
+
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: the CUDA extension has not been built (run __graft_entry__.build()); "
+            "this package has no CPU or PyTorch fallback")
+    lib = ctypes.CDLL(LIB_PATH)
+    vp = c_void_p
+    lib.swin_attn_forward.argtypes = [POINTER(Shape)] + [vp] * 11
+    lib.swin_attn_forward.restype = c_int
+    lib.swin_attn_backward.argtypes = [POINTER(Shape)] + [vp] * 13
+    lib.swin_attn_backward.restype = c_int
+    lib.swin_attn_forward_host.argtypes = [POINTER(Shape)] + [vp] * 8
+    lib.swin_attn_forward_host.restype = c_int
+    lib.swin_attn_launch_count.argtypes = []
+    lib.swin_attn_launch_count.restype = c_uint64
+    lib.swin_attn_uses_tcgen05.argtypes = [POINTER(Shape), c_int]
+    lib.swin_attn_uses_tcgen05.restype = c_int
+    lib.swin_attn_last_error.restype = c_char_p
+    lib.swin_attn_version.restype = c_char_p
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise RuntimeError("swin_attn: " + load().swin_attn_last_error().decode())
+
+
+def launch_count() -> int:
+    return int(load().swin_attn_launch_count())

@@ -1,0 +1,18 @@
+#!/usr/bin/env bash
+# Build libswin_attn.so for sm_100a, in-tree (the .so travels with the repo to the GPU box).
+set -euo pipefail
+here="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+root="$(cd "$here/../.." && pwd)"
+out="$here/../libswin_attn.so"
+NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
+flags=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC
+       -I"$root/include" -I"$here" -Xptxas -v)
+mkdir -p "$here/build"
+pids=()
+for f in swin_attn_simt swin_attn_tc swin_attn_api; do
+  "$NVCC" "${flags[@]}" -c "$here/$f.cu" -o "$here/build/$f.o" > "$here/build/$f.log" 2>&1 &
+  pids+=($!)
+done
+for p in "${pids[@]}"; do wait "$p" || { cat "$here"/build/*.log; exit 1; }; done
+"$NVCC" -shared -o "$out" "$here"/build/swin_attn_simt.o "$here"/build/swin_attn_tc.o "$here"/build/swin_attn_api.o -lcudart
+echo "built $out"

@@ -1,0 +1,170 @@
+// C ABI of libswin_attn.so (see include/swin_attn.h): argument checking,
+// dispatch between the tcgen05 and the CUDA-core kernels, host-buffer entry.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+#include "swin_common.cuh"
+
+namespace swin {
+static std::atomic<uint64_t> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+static thread_local std::string g_error;
+
+static int fail(const std::string& msg) {
+  g_error = msg;
+  return 1;
+}
+static int fail_cuda(const char* what, cudaError_t e) {
+  g_error = std::string(what) + ": " + cudaGetErrorString(e);
+  return 2;
+}
+
+static size_t elem_size(int dtype) { return dtype == SWIN_ATTN_F32 ? 4 : 2; }
+
+// Validate the shape (mirrors the reference's asserts: shift in [0, ws),
+// newcrf_layers.py:180; C divisible by heads) and fill the launch description.
+static int make_problem(const swin_attn_shape_t* s, Problem& p) {
+  if (s == nullptr) return fail("shape is null");
+  if (s->dtype != SWIN_ATTN_F32 && s->dtype != SWIN_ATTN_BF16) return fail("dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
+  if (s->window != 7 && s->window != 12) return fail("window must be 7 or 12 (got " + std::to_string(s->window) + ")");
+  if (s->shift < 0 || s->shift >= s->window) return fail("shift_size must in 0-window_size");
+  if (s->batch <= 0 || s->height <= 0 || s->width <= 0 || s->num_heads <= 0) return fail("batch/height/width/num_heads must be positive");
+  if (s->dropout_p != 0.0f) return fail("attention dropout > 0 is not implemented (every NewCRFs configuration uses 0)");
+  memset(&p, 0, sizeof(p));
+  p.B = s->batch; p.H = s->height; p.W = s->width; p.nH = s->num_heads;
+  p.C = s->num_heads * kHeadDim;
+  p.ws = s->window; p.shift = s->shift;
+  p.nWy = (p.H + p.ws - 1) / p.ws; p.nWx = (p.W + p.ws - 1) / p.ws;
+  p.Hp = p.nWy * p.ws; p.Wp = p.nWx * p.ws;
+  p.q_ps = s->q_pix_stride; p.k_ps = s->k_pix_stride; p.v_ps = s->v_pix_stride; p.o_ps = s->o_pix_stride;
+  if (p.q_ps < p.C || p.k_ps < p.C || p.v_ps < p.C || p.o_ps < p.C) return fail("pixel strides must be >= num_heads*32");
+  if ((p.q_ps | p.k_ps | p.v_ps | p.o_ps) & 3) return fail("pixel strides must be multiples of 4 elements");
+  if ((int64_t)p.B * p.Hp * p.Wp * p.nH >= (1ll << 31)) return fail("problem too large for 32-bit tile indices");
+  p.scale = s->scale; p.dropout_p = s->dropout_p; p.seed = s->seed;
+  return 0;
+}
+
+static int set_mask(const swin_attn_shape_t* s, const float* mask, Problem& p) {
+  if (mask == nullptr) { p.mask = nullptr; p.mask_nw = 0; return 0; }
+  if (s->mask_windows <= 0) return fail("attn_mask given but mask_windows <= 0");
+  if ((p.B * p.nWy * p.nWx) % s->mask_windows != 0) return fail("number of windows is not a multiple of mask_windows");
+  p.mask = mask; p.mask_nw = s->mask_windows;
+  return 0;
+}
+
+static bool misaligned(const void* ptr, int dtype) {
+  return (reinterpret_cast<uintptr_t>(ptr) & (4 * elem_size(dtype) - 1)) != 0;
+}
+
+}  // namespace swin
+
+using namespace swin;
+
+extern "C" {
+
+int swin_attn_forward(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v,
+                      const void* q_pad, const void* k_pad, const void* v_pad, const float* bias_table,
+                      const float* attn_mask, void* o, float* lse, void* stream) {
+  Problem p;
+  if (int rc = make_problem(shape, p)) return rc;
+  if (!q || !k || !v || !bias_table || !o) return fail("q, k, v, bias_table and o must be non-null");
+  if (misaligned(q, shape->dtype) || misaligned(k, shape->dtype) || misaligned(v, shape->dtype) || misaligned(o, shape->dtype))
+    return fail("q/k/v/o must be aligned to 4 elements");
+  p.q = q; p.k = k; p.v = v; p.q_pad = q_pad; p.k_pad = k_pad; p.v_pad = v_pad;
+  p.table = bias_table; p.o = o; p.lse = lse;
+  if (int rc = set_mask(shape, attn_mask, p)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_forward_supported(p, shape->dtype);
+  if (shape->impl == SWIN_ATTN_IMPL_TCGEN05 && !want_tc) return fail("tcgen05 forward does not support this shape/dtype");
+  if (want_tc) {
+    const char* why = nullptr;
+    cudaError_t e = launch_tc_forward(p, st, &why);
+    if (e != cudaSuccess) return why ? fail(std::string("tcgen05 forward: ") + why) : fail_cuda("tcgen05 forward launch", e);
+    return 0;
+  }
+  cudaError_t e = launch_simt_forward(p, shape->dtype, st);
+  if (e != cudaSuccess) return fail_cuda("forward launch", e);
+  return 0;
+}
+
+int swin_attn_backward(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v,
+                       const void* o, const void* d_o, const float* lse, const float* bias_table,
+                       const float* attn_mask, void* dq, void* dk, void* dv, float* d_bias_table, void* stream) {
+  Problem p;
+  if (int rc = make_problem(shape, p)) return rc;
+  if (p.H != p.Hp || p.W != p.Wp) return fail("backward needs height and width to be multiples of the window (pad explicitly)");
+  if (!q || !k || !v || !o || !d_o || !lse || !bias_table || !dq || !dk || !dv || !d_bias_table)
+    return fail("backward: all pointers must be non-null");
+  if (p.o_ps != p.C) return fail("backward: o and d_o must be dense (pixel stride == C)");
+  if (misaligned(q, shape->dtype) || misaligned(k, shape->dtype) || misaligned(v, shape->dtype) || misaligned(o, shape->dtype) ||
+      misaligned(d_o, shape->dtype) || misaligned(dq, shape->dtype) || misaligned(dk, shape->dtype) || misaligned(dv, shape->dtype))
+    return fail("backward: tensors must be aligned to 4 elements");
+  p.q = q; p.k = k; p.v = v; p.o_in = o; p.d_o = d_o; p.lse = const_cast<float*>(lse);
+  p.table = bias_table; p.dq = dq; p.dk = dk; p.dv = dv; p.d_table = d_bias_table;
+  if (int rc = set_mask(shape, attn_mask, p)) return rc;
+  cudaError_t e = launch_simt_backward(p, shape->dtype, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail_cuda("backward launch", e);
+  return 0;
+}
+
+// Device scratch for the host-buffer entry point; grown on demand, reused.
+static std::mutex g_host_mu;
+static void* g_scratch = nullptr;
+static size_t g_scratch_bytes = 0;
+
+int swin_attn_forward_host(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v,
+                           const void* q_pad, const void* k_pad, const void* v_pad, const float* bias_table, void* o) {
+  Problem p;
+  if (int rc = make_problem(shape, p)) return rc;
+  if (!q || !k || !v || !bias_table || !o) return fail("q, k, v, bias_table and o must be non-null");
+  if (p.q_ps != p.C || p.k_ps != p.C || p.v_ps != p.C || p.o_ps != p.C) return fail("host entry takes dense (B,H,W,C) buffers");
+  std::lock_guard<std::mutex> lock(g_host_mu);
+  const size_t es = elem_size(shape->dtype);
+  const size_t tens = (size_t)p.B * p.H * p.W * p.C * es;
+  const size_t tens_al = (tens + 255) & ~size_t(255);
+  const size_t vec = ((size_t)p.C * es + 255) & ~size_t(255);
+  const size_t tab = (((size_t)(2 * p.ws - 1) * (2 * p.ws - 1) * p.nH * 4) + 255) & ~size_t(255);
+  const size_t need = 4 * tens_al + 3 * vec + tab;
+  cudaError_t e;
+  if (need > g_scratch_bytes) {
+    if (g_scratch) cudaFree(g_scratch);
+    g_scratch = nullptr; g_scratch_bytes = 0;
+    if ((e = cudaMalloc(&g_scratch, need)) != cudaSuccess) return fail_cuda("cudaMalloc scratch", e);
+    g_scratch_bytes = need;
+  }
+  char* base = static_cast<char*>(g_scratch);
+  void* dq = base; void* dk = base + tens_al; void* dv = base + 2 * tens_al; void* dout = base + 3 * tens_al;
+  char* vecs = base + 4 * tens_al;
+  void* dqp = q_pad ? vecs : nullptr; void* dkp = k_pad ? vecs + vec : nullptr; void* dvp = v_pad ? vecs + 2 * vec : nullptr;
+  float* dtab = reinterpret_cast<float*>(vecs + 3 * vec);
+  cudaStream_t st = nullptr;
+  if ((e = cudaMemcpyAsync(dq, q, tens, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D q", e);
+  if ((e = cudaMemcpyAsync(dk, k, tens, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D k", e);
+  if ((e = cudaMemcpyAsync(dv, v, tens, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D v", e);
+  if (q_pad) cudaMemcpyAsync(dqp, q_pad, p.C * es, cudaMemcpyHostToDevice, st);
+  if (k_pad) cudaMemcpyAsync(dkp, k_pad, p.C * es, cudaMemcpyHostToDevice, st);
+  if (v_pad) cudaMemcpyAsync(dvp, v_pad, p.C * es, cudaMemcpyHostToDevice, st);
+  cudaMemcpyAsync(dtab, bias_table, (size_t)(2 * p.ws - 1) * (2 * p.ws - 1) * p.nH * 4, cudaMemcpyHostToDevice, st);
+  int rc = swin_attn_forward(shape, dq, dk, dv, dqp, dkp, dvp, dtab, nullptr, dout, nullptr, st);
+  if (rc) return rc;
+  if ((e = cudaMemcpyAsync(o, dout, tens, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return fail_cuda("D2H o", e);
+  if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return fail_cuda("host forward", e);
+  return 0;
+}
+
+uint64_t swin_attn_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int swin_attn_uses_tcgen05(const swin_attn_shape_t* shape, int backward) {
+  Problem p;
+  if (make_problem(shape, p)) return 0;
+  if (backward) return 0;
+  return shape->impl != SWIN_ATTN_IMPL_SIMT && tc_forward_supported(p, shape->dtype) ? 1 : 0;
+}
+
+const char* swin_attn_last_error(void) { return g_error.c_str(); }
+const char* swin_attn_version(void) { return "swin_attn 0.1 (sm_100a)"; }
+
+}  // extern "C"

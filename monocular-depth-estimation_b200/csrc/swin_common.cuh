@@ -1,0 +1,104 @@
+// Shared definitions for the shifted-window attention kernels (sm_100a).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "swin_attn.h"
+
+namespace swin {
+
+constexpr int kHeadDim = 32;
+
+// Launch-time description of one attention call; all strides in elements.
+struct Problem {
+  const void* q;
+  const void* k;
+  const void* v;
+  const void* q_pad;   // nullable, C elements
+  const void* k_pad;
+  const void* v_pad;
+  const float* table;  // ((2ws-1)^2, nH)
+  const float* mask;   // nullable explicit additive mask (mask_nw, N, N)
+  int mask_nw;
+  void* o;             // (B,H,W,*)
+  float* lse;          // (B,Hp,Wp,nH) or null
+  // backward only
+  const void* d_o;     // (B,H,W,C) dense
+  const void* o_in;    // (B,H,W,C) dense
+  void* dq;
+  void* dk;
+  void* dv;
+  float* d_table;
+  int B, H, W, Hp, Wp, nH, C, ws, shift;
+  int nWy, nWx;        // windows per column / row of the padded image
+  int64_t q_ps, k_ps, v_ps, o_ps;
+  float scale;
+  float dropout_p;
+  uint64_t seed;
+};
+
+// Token t of window (wy, wx) -> un-shifted coordinates in the padded image.
+// Restates the composition roll(-s) . window_partition of the reference
+// (newcrf_layers.py:220-227 with :39-41): shifted[ys] = x[(ys + s) mod Hp].
+__device__ __forceinline__ void token_coord(const Problem& p, int wy, int wx, int t, int& y, int& x) {
+  int i = t / p.ws, j = t - i * p.ws;
+  y = wy * p.ws + i + p.shift;
+  x = wx * p.ws + j + p.shift;
+  if (y >= p.Hp) y -= p.Hp;
+  if (x >= p.Wp) x -= p.Wp;
+}
+
+// SW-MSA region id of a token in SHIFTED coordinates (newcrf_layers.py:335-345):
+// slices [0,Hp-ws) [Hp-ws,Hp-s) [Hp-s,Hp) along each axis, id = 3*rh + rw.
+__device__ __forceinline__ int region_id(const Problem& p, int wy, int wx, int t) {
+  int i = t / p.ws, j = t - i * p.ws;
+  int ys = wy * p.ws + i, xs = wx * p.ws + j;
+  int rh = ys < p.Hp - p.ws ? 0 : (ys < p.Hp - p.shift ? 1 : 2);
+  int rw = xs < p.Wp - p.ws ? 0 : (xs < p.Wp - p.shift ? 1 : 2);
+  return 3 * rh + rw;
+}
+
+// relative_position_index[i, j] (newcrf_layers.py:89-100).
+__device__ __forceinline__ int rel_index(int ws, int ti, int tj) {
+  int yi = ti / ws, xi = ti - yi * ws;
+  int yj = tj / ws, xj = tj - yj * ws;
+  return (yi - yj + ws - 1) * (2 * ws - 1) + (xi - xj + ws - 1);
+}
+
+template <typename T>
+struct Elem;
+template <>
+struct Elem<float> {
+  static __device__ __forceinline__ float4 load4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+  static __device__ __forceinline__ void store4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+  static __device__ __forceinline__ void store1(float* p, float v) { *p = v; }
+};
+template <>
+struct Elem<__nv_bfloat16> {
+  static __device__ __forceinline__ float4 load4(const __nv_bfloat16* p) {
+    uint2 raw = *reinterpret_cast<const uint2*>(p);
+    __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&raw.x);
+    __nv_bfloat162 b = *reinterpret_cast<__nv_bfloat162*>(&raw.y);
+    float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+    return make_float4(fa.x, fa.y, fb.x, fb.y);
+  }
+  static __device__ __forceinline__ void store4(__nv_bfloat16* p, float4 v) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 raw;
+    raw.x = *reinterpret_cast<uint32_t*>(&a);
+    raw.y = *reinterpret_cast<uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(p) = raw;
+  }
+  static __device__ __forceinline__ void store1(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+};
+
+// Launchers implemented by the kernel translation units.
+cudaError_t launch_simt_forward(const Problem& p, int dtype, cudaStream_t st);
+cudaError_t launch_simt_backward(const Problem& p, int dtype, cudaStream_t st);
+bool tc_forward_supported(const Problem& p, int dtype);
+cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** err);
+
+void count_launch(int n = 1);
+
+}  // namespace swin

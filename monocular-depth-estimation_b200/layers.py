@@ -1,0 +1,350 @@
+"""Drop-in ``nn.Module``s for the reference's window-attention stack.
+
+Constructor arguments, ``forward`` signatures, return values and
+``state_dict`` keys equal those of
+
+    model/NewCRFs/newcrf_layers.py   WindowAttention :62, CRFBlock :152,
+                                     BasicCRFLayer :260, NewCRF :366, Mlp :9
+    model/NewCRFs/swin_transformer.py WindowAttention :64 (here
+                                     ``EncoderWindowAttention``),
+                                     SwinTransformerBlock :147, PatchMerging :249,
+                                     BasicLayer :292, PatchEmbed :396
+
+so a reference checkpoint loads with ``strict=True`` and the callers
+(``NewCRFDepth``) run unchanged.  What differs is the execution: between the
+qk/qkv Linear and the proj Linear everything -- pad, cyclic shift, window
+partition, bias gather, SW-MSA mask, softmax, PV, window reverse, un-shift,
+crop -- is ONE launch of the sm_100a kernel behind ``ops.window_attention``;
+no rolled / partitioned / padded copy and no (nW, N, N) mask is materialised.
+The kernels are the only implementation: there is no PyTorch fallback.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+
+def _pair(v):
+    return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+
+
+class DropPath(nn.Module):
+    """Per-sample stochastic depth (the reference takes it from timm 0.5.4)."""
+
+    def __init__(self, drop_prob: float = 0.0):
+        super().__init__()
+        self.drop_prob = float(drop_prob)
+
+    def forward(self, x):
+        if self.drop_prob == 0.0 or not self.training:
+            return x
+        keep = 1.0 - self.drop_prob
+        gate = x.new_empty((x.shape[0],) + (1,) * (x.ndim - 1)).bernoulli_(keep)
+        return x * gate / keep
+
+
+class Mlp(nn.Module):
+    """fc1 -> act -> drop -> fc2 -> drop (newcrf_layers.py:9-27)."""
+
+    def __init__(self, in_features, hidden_features=None, out_features=None, act_layer=nn.GELU, drop=0.0):
+        super().__init__()
+        self.fc1 = nn.Linear(in_features, hidden_features or in_features)
+        self.act = act_layer()
+        self.fc2 = nn.Linear(hidden_features or in_features, out_features or in_features)
+        self.drop = nn.Dropout(drop)
+
+    def forward(self, x):
+        return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
+
+
+def _relative_position_index(wh: int, ww: int) -> torch.Tensor:
+    ys, xs = torch.meshgrid(torch.arange(wh), torch.arange(ww), indexing="ij")
+    ys, xs = ys.flatten(), xs.flatten()
+    return (ys[:, None] - ys[None, :] + wh - 1) * (2 * ww - 1) + (xs[:, None] - xs[None, :] + ww - 1)
+
+
+class _WindowAttentionBase(nn.Module):
+    """Parameters and buffers shared by both reference flavours."""
+
+    def __init__(self, dim, window_size, num_heads, out_dim, qk_scale, attn_drop, proj_drop):
+        super().__init__()
+        self.dim = dim
+        self.window_size = _pair(window_size)
+        if self.window_size[0] != self.window_size[1]:
+            raise ValueError("only square windows are supported (the reference only builds square ones)")
+        self.num_heads = num_heads
+        head_dim = dim // num_heads
+        if head_dim * num_heads != dim or head_dim != 32:
+            raise ValueError(f"the sm_100a kernels need head_dim == 32 (dim={dim}, num_heads={num_heads})")
+        self.scale = qk_scale or head_dim ** -0.5
+        wh, ww = self.window_size
+        self.relative_position_bias_table = nn.Parameter(torch.zeros((2 * wh - 1) * (2 * ww - 1), num_heads))
+        self.register_buffer("relative_position_index", _relative_position_index(wh, ww))
+        if attn_drop != 0.0:
+            raise NotImplementedError("attn_drop > 0 is not implemented in the fused kernel "
+                                      "(every NewCRFs configuration uses 0, SURVEY.md F7)")
+        self.attn_drop = nn.Dropout(attn_drop)
+        self.proj = nn.Linear(out_dim, out_dim)
+        self.proj_drop = nn.Dropout(proj_drop)
+        nn.init.trunc_normal_(self.relative_position_bias_table, std=0.02)
+        self.softmax = nn.Softmax(dim=-1)  # kept for module-tree parity; the kernel does the softmax
+
+    def _windows_as_images(self, t):
+        ws = self.window_size[0]
+        return t.reshape(t.shape[0], ws, ws, t.shape[-1])
+
+
+class WindowAttention(_WindowAttentionBase):
+    """NeWCRF decoder attention: q, k from ``x``; ``v`` external (newcrf_layers.py:62-149)."""
+
+    def __init__(self, dim, window_size, num_heads, v_dim, qkv_bias=True, qk_scale=None, attn_drop=0., proj_drop=0.):
+        super().__init__(dim, window_size, num_heads, v_dim, qk_scale, attn_drop, proj_drop)
+        self.qk = nn.Linear(dim, dim * 2, bias=qkv_bias)
+
+    def forward(self, x, v, mask=None):
+        """x, v: (num_windows*B, N, C) window-order tokens; mask: (nW, N, N) or None."""
+        b_, n, c = x.shape
+        assert self.dim == v.shape[-1], "self.dim != v.shape[-1]"
+        qk = self._windows_as_images(self.qk(x))
+        o = ops.window_attention(qk, self._windows_as_images(v), self.relative_position_bias_table,
+                                 self.window_size[0], 0, self.num_heads, self.scale, attn_mask=mask)
+        return self.proj_drop(self.proj(o.reshape(b_, n, c)))
+
+    def forward_image(self, x_img, v_img, shift):
+        """x_img, v_img: (B, H, W, C) image-order (x already normalised).  Pad
+        tokens take the Linear bias for q/k and zero for v, as in the reference
+        where ``F.pad`` precedes the Linear (newcrf_layers.py:212-216)."""
+        ws = self.window_size[0]
+        if torch.is_grad_enabled() and (x_img.requires_grad or v_img.requires_grad or
+                                        self.relative_position_bias_table.requires_grad):
+            h, w = x_img.shape[1:3]
+            pb, pr = (-h) % ws, (-w) % ws
+            if pb or pr:
+                x_img = F.pad(x_img, (0, 0, 0, pr, 0, pb))
+                v_img = F.pad(v_img, (0, 0, 0, pr, 0, pb))
+            o = ops.window_attention(self.qk(x_img), v_img, self.relative_position_bias_table, ws, shift,
+                                     self.num_heads, self.scale)
+            o = o[:, :h, :w, :]
+        else:
+            o = ops.window_attention(self.qk(x_img), v_img, self.relative_position_bias_table, ws, shift,
+                                     self.num_heads, self.scale, packed_pad=self.qk.bias, v_pad=None)
+        return self.proj_drop(self.proj(o))
+
+
+class EncoderWindowAttention(_WindowAttentionBase):
+    """Swin encoder attention with fused qkv (swin_transformer.py:64-144)."""
+
+    def __init__(self, dim, window_size, num_heads, qkv_bias=True, qk_scale=None, attn_drop=0., proj_drop=0.):
+        super().__init__(dim, window_size, num_heads, dim, qk_scale, attn_drop, proj_drop)
+        self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
+
+    def forward(self, x, mask=None):
+        b_, n, c = x.shape
+        qkv = self._windows_as_images(self.qkv(x))
+        o = ops.window_attention(qkv, None, self.relative_position_bias_table, self.window_size[0], 0,
+                                 self.num_heads, self.scale, attn_mask=mask)
+        return self.proj_drop(self.proj(o.reshape(b_, n, c)))
+
+    def forward_image(self, x_img, shift):
+        ws = self.window_size[0]
+        if torch.is_grad_enabled() and (x_img.requires_grad or self.relative_position_bias_table.requires_grad):
+            h, w = x_img.shape[1:3]
+            pb, pr = (-h) % ws, (-w) % ws
+            if pb or pr:
+                x_img = F.pad(x_img, (0, 0, 0, pr, 0, pb))
+            o = ops.window_attention(self.qkv(x_img), None, self.relative_position_bias_table, ws, shift,
+                                     self.num_heads, self.scale)
+            o = o[:, :h, :w, :]
+        else:
+            o = ops.window_attention(self.qkv(x_img), None, self.relative_position_bias_table, ws, shift,
+                                     self.num_heads, self.scale, packed_pad=self.qkv.bias)
+        return self.proj_drop(self.proj(o))
+
+
+class CRFBlock(nn.Module):
+    """norm1 -> (S)W-MSA(x, v) -> +shortcut -> norm2 -> MLP -> + (newcrf_layers.py:152-257).
+
+    ``mask_matrix`` is accepted for signature parity; the kernel derives the
+    identical SW-MSA mask from ``shift_size`` analytically.
+    """
+
+    def __init__(self, dim, num_heads, v_dim, window_size=7, shift_size=0, mlp_ratio=4., qkv_bias=True,
+                 qk_scale=None, drop=0., attn_drop=0., drop_path=0., act_layer=nn.GELU, norm_layer=nn.LayerNorm):
+        super().__init__()
+        self.dim, self.num_heads, self.v_dim = dim, num_heads, v_dim
+        self.window_size, self.shift_size, self.mlp_ratio = window_size, shift_size, mlp_ratio
+        assert 0 <= self.shift_size < self.window_size, "shift_size must in 0-window_size"
+        self.norm1 = norm_layer(dim)
+        self.attn = WindowAttention(dim, window_size=_pair(window_size), num_heads=num_heads, v_dim=v_dim,
+                                    qkv_bias=qkv_bias, qk_scale=qk_scale, attn_drop=attn_drop, proj_drop=drop)
+        self.drop_path = DropPath(drop_path) if drop_path > 0. else nn.Identity()
+        self.norm2 = norm_layer(v_dim)
+        self.mlp = Mlp(in_features=v_dim, hidden_features=int(v_dim * mlp_ratio), act_layer=act_layer, drop=drop)
+        self.H = None
+        self.W = None
+
+    def forward(self, x, v, mask_matrix=None):
+        b, l, c = x.shape
+        h, w = self.H, self.W
+        assert l == h * w, "input feature has wrong size"
+        a = self.attn.forward_image(self.norm1(x).view(b, h, w, c), v, self.shift_size)
+        x = x + self.drop_path(a.reshape(b, h * w, self.v_dim))
+        return x + self.drop_path(self.mlp(self.norm2(x)))
+
+
+class BasicCRFLayer(nn.Module):
+    """One NeWCRF stage: blocks alternating shift 0 / ws//2 (newcrf_layers.py:260-363)."""
+
+    def __init__(self, dim, depth, num_heads, v_dim, window_size=7, mlp_ratio=4., qkv_bias=True, qk_scale=None,
+                 drop=0., attn_drop=0., drop_path=0., norm_layer=nn.LayerNorm, downsample=None,
+                 use_checkpoint=False):
+        super().__init__()
+        self.window_size, self.shift_size = window_size, window_size // 2
+        self.depth, self.use_checkpoint = depth, use_checkpoint
+        self.blocks = nn.ModuleList([
+            CRFBlock(dim=dim, num_heads=num_heads, v_dim=v_dim, window_size=window_size,
+                     shift_size=0 if i % 2 == 0 else window_size // 2, mlp_ratio=mlp_ratio, qkv_bias=qkv_bias,
+                     qk_scale=qk_scale, drop=drop, attn_drop=attn_drop,
+                     drop_path=drop_path[i] if isinstance(drop_path, list) else drop_path, norm_layer=norm_layer)
+            for i in range(depth)])
+        self.downsample = downsample(dim=dim, norm_layer=norm_layer) if downsample is not None else None
+
+    def forward(self, x, v, H, W):
+        for blk in self.blocks:
+            blk.H, blk.W = H, W
+            x = blk(x, v, None)
+        if self.downsample is not None:
+            return x, H, W, self.downsample(x, H, W), (H + 1) // 2, (W + 1) // 2
+        return x, H, W, x, H, W
+
+
+class NewCRF(nn.Module):
+    """3x3 conv projections -> BasicCRFLayer -> LayerNorm -> NCHW (newcrf_layers.py:366-432)."""
+
+    def __init__(self, input_dim=96, embed_dim=96, v_dim=64, window_size=7, num_heads=4, depth=2, patch_size=4,
+                 in_chans=3, norm_layer=nn.LayerNorm, patch_norm=True):
+        super().__init__()
+        self.embed_dim, self.patch_norm = embed_dim, patch_norm
+        self.proj_x = nn.Conv2d(input_dim, embed_dim, 3, padding=1) if input_dim != embed_dim else None
+        self.proj_v = nn.Conv2d(v_dim, embed_dim, 3, padding=1) if v_dim != embed_dim else None
+        self.crf_layer = BasicCRFLayer(dim=embed_dim, depth=depth, num_heads=num_heads, v_dim=embed_dim,
+                                       window_size=window_size, mlp_ratio=4., qkv_bias=True, qk_scale=None,
+                                       drop=0., attn_drop=0., drop_path=0., norm_layer=norm_layer,
+                                       downsample=None, use_checkpoint=False)
+        self.norm_crf = norm_layer(embed_dim)
+
+    def forward(self, x, v):
+        if self.proj_x is not None:
+            x = self.proj_x(x)
+        if self.proj_v is not None:
+            v = self.proj_v(v)
+        h, w = x.shape[2], x.shape[3]
+        x = x.flatten(2).transpose(1, 2)
+        v = v.permute(0, 2, 3, 1)
+        x_out, h, w, _, _, _ = self.crf_layer(x, v, h, w)
+        x_out = self.norm_crf(x_out)
+        return x_out.view(-1, h, w, self.embed_dim).permute(0, 3, 1, 2).contiguous()
+
+
+class SwinTransformerBlock(nn.Module):
+    """Swin block (swin_transformer.py:147-246); see CRFBlock about ``mask_matrix``."""
+
+    def __init__(self, dim, num_heads, window_size=7, shift_size=0, mlp_ratio=4., qkv_bias=True, qk_scale=None,
+                 drop=0., attn_drop=0., drop_path=0., act_layer=nn.GELU, norm_layer=nn.LayerNorm):
+        super().__init__()
+        self.dim, self.num_heads = dim, num_heads
+        self.window_size, self.shift_size, self.mlp_ratio = window_size, shift_size, mlp_ratio
+        assert 0 <= self.shift_size < self.window_size, "shift_size must in 0-window_size"
+        self.norm1 = norm_layer(dim)
+        self.attn = EncoderWindowAttention(dim, window_size=_pair(window_size), num_heads=num_heads,
+                                           qkv_bias=qkv_bias, qk_scale=qk_scale, attn_drop=attn_drop, proj_drop=drop)
+        self.drop_path = DropPath(drop_path) if drop_path > 0. else nn.Identity()
+        self.norm2 = norm_layer(dim)
+        self.mlp = Mlp(in_features=dim, hidden_features=int(dim * mlp_ratio), act_layer=act_layer, drop=drop)
+        self.H = None
+        self.W = None
+
+    def forward(self, x, mask_matrix=None):
+        b, l, c = x.shape
+        h, w = self.H, self.W
+        assert l == h * w, "input feature has wrong size"
+        a = self.attn.forward_image(self.norm1(x).view(b, h, w, c), self.shift_size)
+        x = x + self.drop_path(a.reshape(b, h * w, c))
+        return x + self.drop_path(self.mlp(self.norm2(x)))
+
+
+class PatchMerging(nn.Module):
+    """2x2 neighbourhood concat -> LN -> Linear(4C, 2C) (swin_transformer.py:249-289)."""
+
+    def __init__(self, dim, norm_layer=nn.LayerNorm):
+        super().__init__()
+        self.dim = dim
+        self.reduction = nn.Linear(4 * dim, 2 * dim, bias=False)
+        self.norm = norm_layer(4 * dim)
+
+    def forward(self, x, H, W):
+        b, l, c = x.shape
+        assert l == H * W, "input feature has wrong size"
+        x = x.view(b, H, W, c)
+        if H % 2 or W % 2:
+            x = F.pad(x, (0, 0, 0, W % 2, 0, H % 2))
+        x = torch.cat([x[:, 0::2, 0::2], x[:, 1::2, 0::2], x[:, 0::2, 1::2], x[:, 1::2, 1::2]], -1)
+        return self.reduction(self.norm(x.view(b, -1, 4 * c)))
+
+
+class BasicLayer(nn.Module):
+    """One Swin stage (swin_transformer.py:292-393)."""
+
+    def __init__(self, dim, depth, num_heads, window_size=7, mlp_ratio=4., qkv_bias=True, qk_scale=None, drop=0.,
+                 attn_drop=0., drop_path=0., norm_layer=nn.LayerNorm, downsample=None, use_checkpoint=False):
+        super().__init__()
+        self.window_size, self.shift_size = window_size, window_size // 2
+        self.depth, self.use_checkpoint = depth, use_checkpoint
+        self.blocks = nn.ModuleList([
+            SwinTransformerBlock(dim=dim, num_heads=num_heads, window_size=window_size,
+                                 shift_size=0 if i % 2 == 0 else window_size // 2, mlp_ratio=mlp_ratio,
+                                 qkv_bias=qkv_bias, qk_scale=qk_scale, drop=drop, attn_drop=attn_drop,
+                                 drop_path=drop_path[i] if isinstance(drop_path, list) else drop_path,
+                                 norm_layer=norm_layer)
+            for i in range(depth)])
+        self.downsample = downsample(dim=dim, norm_layer=norm_layer) if downsample is not None else None
+
+    def forward(self, x, H, W):
+        for blk in self.blocks:
+            blk.H, blk.W = H, W
+            if self.use_checkpoint and torch.is_grad_enabled():
+                x = torch.utils.checkpoint.checkpoint(blk, x, None, use_reentrant=False)
+            else:
+                x = blk(x, None)
+        if self.downsample is not None:
+            return x, H, W, self.downsample(x, H, W), (H + 1) // 2, (W + 1) // 2
+        return x, H, W, x, H, W
+
+
+class PatchEmbed(nn.Module):
+    """4x4/4 conv patchify (+LN) (swin_transformer.py:396-436)."""
+
+    def __init__(self, patch_size=4, in_chans=3, embed_dim=96, norm_layer=None):
+        super().__init__()
+        self.patch_size = _pair(patch_size)
+        self.in_chans, self.embed_dim = in_chans, embed_dim
+        self.proj = nn.Conv2d(in_chans, embed_dim, kernel_size=self.patch_size, stride=self.patch_size)
+        self.norm = norm_layer(embed_dim) if norm_layer is not None else None
+
+    def forward(self, x):
+        _, _, h, w = x.shape
+        ph, pw = self.patch_size
+        if w % pw:
+            x = F.pad(x, (0, pw - w % pw))
+        if h % ph:
+            x = F.pad(x, (0, 0, 0, ph - h % ph))
+        x = self.proj(x)
+        if self.norm is not None:
+            hh, ww = x.shape[2], x.shape[3]
+            x = self.norm(x.flatten(2).transpose(1, 2)).transpose(1, 2).view(-1, self.embed_dim, hh, ww)
+        return x

@@ -1,0 +1,240 @@
+"""``torch.library`` custom ops over the C ABI of ``libswin_attn.so``.
+
+``swin_attn::fwd`` / ``swin_attn::bwd`` take the *packed* output of the
+reference's projection Linear -- ``qkv`` (B,H,W,3C) for the encoder
+(swin_transformer.py:120) or ``qk`` (B,H,W,2C) plus an external ``v``
+(B,H,W,C) for the NeWCRF decoder (newcrf_layers.py:118,143-144) -- in image
+order, and return the attention output in image order, cropped to (H, W).
+Everything in between (pad, roll, partition, bias gather, mask, softmax, PV,
+reverse, un-roll, crop) happens inside one kernel launch.
+
+CUDA only.  There is deliberately no CPU implementation registered: calling
+the ops with CPU tensors raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+
+_DTYPES = {torch.float32: _lib.F32, torch.bfloat16: _lib.BF16}
+
+
+def _ptr(t: Optional[Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _image_layout(t: Tensor) -> Tensor:
+    """Dense rows/images with unit channel stride (pixel stride may exceed C)."""
+    b, h, w, c = t.shape
+    s = t.stride()
+    if s[3] == 1 and s[1] == w * s[2] and s[0] == h * s[1] and s[2] % 4 == 0 and s[2] >= c:
+        return t
+    return t.contiguous()
+
+
+def _shape(batch, height, width, num_heads, window, shift, dtype, impl, scale, q_ps, k_ps, v_ps, o_ps,
+           mask_windows=0) -> _lib.Shape:
+    if dtype not in _DTYPES:
+        raise RuntimeError(f"swin_attn: dtype {dtype} is not supported (float32 or bfloat16)")
+    return _lib.Shape(batch, height, width, num_heads, window, shift, _DTYPES[dtype], impl,
+                      float(scale), 0.0, 0, q_ps, k_ps, v_ps, o_ps, mask_windows, 0)
+
+
+def _mask_arg(attn_mask: Optional[Tensor], window: int):
+    if attn_mask is None:
+        return None, 0
+    n = window * window
+    if attn_mask.dim() != 3 or attn_mask.shape[1:] != (n, n):
+        raise RuntimeError(f"swin_attn: attn_mask must be (nW, {n}, {n}), got {tuple(attn_mask.shape)}")
+    return attn_mask.detach().to(torch.float32).contiguous(), attn_mask.shape[0]
+
+
+def _split(packed: Tensor, v: Optional[Tensor], num_heads: int):
+    c = num_heads * 32
+    want = 3 * c if v is None else 2 * c
+    if packed.dim() != 4 or packed.shape[-1] != want:
+        raise RuntimeError(f"swin_attn: packed projection must be (B,H,W,{want}) for {num_heads} heads of dim 32, "
+                           f"got {tuple(packed.shape)}")
+    if v is not None and (v.shape[:3] != packed.shape[:3] or v.shape[-1] != c):
+        raise RuntimeError("self.dim != v.shape[-1]")  # reference assert, newcrf_layers.py:143
+    return c
+
+
+@torch.library.custom_op("swin_attn::fwd", mutates_args=(), device_types="cuda")
+def _fwd(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, packed_pad: Optional[Tensor],
+         v_pad: Optional[Tensor], window: int, shift: int, num_heads: int, scale: float,
+         need_lse: bool, impl: int, attn_mask: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
+    c = _split(packed, v, num_heads)
+    mask, mask_nw = _mask_arg(attn_mask, window)
+    lib = _lib.load()
+    packed = _image_layout(packed)
+    b, h, w, _ = packed.shape
+    dt = packed.dtype
+    ps = packed.stride(2)
+    es = packed.element_size()
+    base = packed.data_ptr()
+    if v is None:
+        v_ptr, v_ps = base + 2 * c * es, ps
+        vpad_ptr = None if packed_pad is None else packed_pad.data_ptr() + 2 * c * es
+    else:
+        v = _image_layout(v.to(dt))
+        v_ptr, v_ps = v.data_ptr(), v.stride(2)
+        if v_pad is not None:
+            v_pad = v_pad.to(dt).contiguous()
+        vpad_ptr = None if v_pad is None else v_pad.data_ptr()
+    if packed_pad is not None:
+        packed_pad = packed_pad.to(dt).contiguous()
+        if v is None:
+            vpad_ptr = packed_pad.data_ptr() + 2 * c * es
+    table = bias_table.detach().to(torch.float32).contiguous()
+    hp, wp = -(-h // window) * window, -(-w // window) * window
+    o = torch.empty((b, h, w, c), dtype=dt, device=packed.device)
+    lse = torch.empty((b, hp, wp, num_heads) if need_lse else (0,), dtype=torch.float32, device=packed.device)
+    shp = _shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw)
+    qpad_ptr = None if packed_pad is None else packed_pad.data_ptr()
+    kpad_ptr = None if packed_pad is None else packed_pad.data_ptr() + c * es
+    with torch.cuda.device(packed.device):
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(lib.swin_attn_forward(
+            ctypes.byref(shp), ctypes.c_void_p(base), ctypes.c_void_p(base + c * es), ctypes.c_void_p(v_ptr),
+            ctypes.c_void_p(qpad_ptr), ctypes.c_void_p(kpad_ptr), ctypes.c_void_p(vpad_ptr),
+            _ptr(table), _ptr(mask), _ptr(o), _ptr(lse) if need_lse else None, ctypes.c_void_p(stream)))
+    return o, lse
+
+
+@_fwd.register_fake
+def _(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask=None):
+    b, h, w, _ = packed.shape
+    c = num_heads * 32
+    hp, wp = -(-h // window) * window, -(-w // window) * window
+    o = packed.new_empty((b, h, w, c))
+    lse = packed.new_empty((b, hp, wp, num_heads) if need_lse else (0,), dtype=torch.float32)
+    return o, lse
+
+
+@torch.library.custom_op("swin_attn::bwd", mutates_args=(), device_types="cuda")
+def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tensor, bias_table: Tensor,
+         window: int, shift: int, num_heads: int, scale: float,
+         attn_mask: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
+    c = _split(packed, v, num_heads)
+    mask, mask_nw = _mask_arg(attn_mask, window)
+    lib = _lib.load()
+    packed = _image_layout(packed)
+    b, h, w, pc = packed.shape
+    dt = packed.dtype
+    es = packed.element_size()
+    ps = packed.stride(2)
+    d_o = d_o.to(dt).contiguous()
+    o = o.contiguous()
+    d_packed = torch.empty((b, h, w, pc), dtype=dt, device=packed.device)
+    if v is None:
+        v_ptr, v_ps = packed.data_ptr() + 2 * c * es, ps
+        d_v = torch.empty((0,), dtype=dt, device=packed.device)
+        dv_ptr = d_packed.data_ptr() + 2 * c * es
+    else:
+        v = _image_layout(v.to(dt))
+        v_ptr, v_ps = v.data_ptr(), v.stride(2)
+        d_v = torch.empty((b, h, w, c), dtype=dt, device=packed.device)
+        dv_ptr = d_v.data_ptr()
+    table = bias_table.detach().to(torch.float32).contiguous()
+    d_table = torch.empty_like(table)
+    base = packed.data_ptr()
+    with torch.cuda.device(packed.device):
+        stream = torch.cuda.current_stream().cuda_stream
+        # Gradients are written with the strides of d_packed / d_v, which can
+        # differ from those of the inputs: run q/k and v through two shapes
+        # only when they do.
+        if ps == pc and (v is None or v_ps == c):
+            shp = _shape(b, h, w, num_heads, window, shift, dt, _lib.IMPL_AUTO, scale, ps, ps, v_ps, c, mask_nw)
+            _lib.check(lib.swin_attn_backward(
+                ctypes.byref(shp), ctypes.c_void_p(base), ctypes.c_void_p(base + c * es), ctypes.c_void_p(v_ptr),
+                _ptr(o), _ptr(d_o), _ptr(lse), _ptr(table), _ptr(mask),
+                ctypes.c_void_p(d_packed.data_ptr()), ctypes.c_void_p(d_packed.data_ptr() + c * es),
+                ctypes.c_void_p(dv_ptr), _ptr(d_table), ctypes.c_void_p(stream)))
+        else:
+            packed_c = packed.contiguous()
+            v_c = None if v is None else v.contiguous()
+            return _bwd(d_o, packed_c, v_c, o, lse, bias_table, window, shift, num_heads, scale, attn_mask)
+    return d_packed, d_v, d_table.to(bias_table.dtype)
+
+
+@_bwd.register_fake
+def _(d_o, packed, v, o, lse, bias_table, window, shift, num_heads, scale, attn_mask=None):
+    d_packed = packed.new_empty(packed.shape)
+    d_v = packed.new_empty((0,)) if v is None else packed.new_empty(v.shape)
+    return d_packed, d_v, torch.empty_like(bias_table)
+
+
+def _setup_context(ctx, inputs, output):
+    packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask = inputs
+    o, lse = output
+    ctx.save_for_backward(packed, v, o, lse, bias_table, attn_mask)
+    ctx.attrs = (window, shift, num_heads, scale)
+    ctx.padded = packed.shape[1] % window != 0 or packed.shape[2] % window != 0
+    ctx.has_lse = need_lse
+    ctx.v_dtype = None if v is None else v.dtype
+
+
+def _backward(ctx, d_o, d_lse):
+    packed, v, o, lse, bias_table, attn_mask = ctx.saved_tensors
+    window, shift, num_heads, scale = ctx.attrs
+    if ctx.padded or not ctx.has_lse:
+        raise RuntimeError(
+            "swin_attn: backward needs the forward to have run with need_lse=True on a tensor whose height and "
+            "width are multiples of the window (the layers pad explicitly whenever gradients are enabled)")
+    d_packed, d_v, d_table = torch.ops.swin_attn.bwd(d_o, packed, v, o, lse, bias_table, window, shift, num_heads, scale,
+                                                     attn_mask)
+    if v is None:
+        d_v = None
+    elif d_v.dtype != ctx.v_dtype:
+        d_v = d_v.to(ctx.v_dtype)
+    return d_packed, d_v, d_table, None, None, None, None, None, None, None, None, None
+
+
+_fwd.register_autograd(_backward, setup_context=_setup_context)
+
+
+def window_attention(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, window: int, shift: int,
+                     num_heads: int, scale: Optional[float] = None, packed_pad: Optional[Tensor] = None,
+                     v_pad: Optional[Tensor] = None, impl: int = _lib.IMPL_AUTO,
+                     attn_mask: Optional[Tensor] = None) -> Tensor:
+    """Fused shifted-window attention on image-order tensors (see module docstring).
+
+    ``packed``: (B,H,W,3C) qkv or (B,H,W,2C) qk with ``v`` (B,H,W,C) separate.
+    ``packed_pad`` / ``v_pad``: value of the projections at padding tokens
+    (the Linear bias; None = zeros).  Returns (B,H,W,C).
+    """
+    if not 0 <= shift < window:
+        raise AssertionError("shift_size must in 0-window_size")  # newcrf_layers.py:180
+    if scale is None:
+        scale = 32 ** -0.5
+    need_grad = torch.is_grad_enabled() and (
+        packed.requires_grad or bias_table.requires_grad or (v is not None and v.requires_grad))
+    o, _ = torch.ops.swin_attn.fwd(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads,
+                                   float(scale), need_grad, impl, attn_mask)
+    return o
+
+
+def window_attention_host(q, k, v, bias_table, window: int, shift: int, num_heads: int,
+                          scale: Optional[float] = None, q_pad=None, k_pad=None, v_pad=None,
+                          impl: int = _lib.IMPL_AUTO) -> Tensor:
+    """Host-buffer entry (``swin_attn_forward_host``): CPU tensors in, CPU tensor
+    out, host<->device copies inside the call.  q, k, v: dense (B,H,W,C)."""
+    lib = _lib.load()
+    q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+    b, h, w, c = q.shape
+    if scale is None:
+        scale = 32 ** -0.5
+    o = torch.empty_like(q)
+    table = bias_table.detach().to(torch.float32).contiguous()
+    pads = [None if t is None else t.to(q.dtype).contiguous() for t in (q_pad, k_pad, v_pad)]
+    shp = _shape(b, h, w, num_heads, window, shift, q.dtype, impl, scale, c, c, c, c)
+    _lib.check(lib.swin_attn_forward_host(ctypes.byref(shp), _ptr(q), _ptr(k), _ptr(v), _ptr(pads[0]),
+                                          _ptr(pads[1]), _ptr(pads[2]), _ptr(table), _ptr(o)))
+    return o
