@@ -1,0 +1,123 @@
+"""Synthetic-batch inference / training harness for NewCRFs.
+
+The reference's own entry script (``run.py``) and its loss module are absent
+from the snapshot; this is NEW code reconstructed from the
+configuration schema (json/kitti/newcrfs/newcrfs_github_eval.json: loss
+alpha=10, beta=0.15, per_image; AdamW lr 2e-5, wd 0; grad_norm 0.1) and from
+utils/dist_utils.py.  Data parallelism is stock ``DistributedDataParallel``
+over NCCL (one process per GPU); the attention itself is never sharded.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from .newcrfs import NewCRFDepth
+
+KITTI = dict(height=352, width=1216, max_depth=80.0)
+NYU = dict(height=480, width=640, max_depth=10.0)
+
+
+def synthetic_images(batch: int, height: int, width: int, seed: int = 0, device="cpu", pin: bool = False):
+    """ImageNet-normalised-like images (dataset/depth_dataset.py:290): N(0,1)."""
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(batch, 3, height, width, generator=g)
+    if pin and torch.cuda.is_available():
+        x = x.pin_memory()
+    return x.to(device) if device != "cpu" else x
+
+
+def synthetic_depth(batch: int, height: int, width: int, max_depth: float, seed: int = 1, sparsity: float = 0.7):
+    g = torch.Generator().manual_seed(seed)
+    gt = 1e-3 + (max_depth - 1e-3) * torch.rand(batch, 1, height, width, generator=g)
+    return gt * (torch.rand(batch, 1, height, width, generator=g) > sparsity)
+
+
+class SILogLoss(nn.Module):
+    """Scale-invariant log loss: alpha * sqrt(mean(d^2) - beta * mean(d)^2), d = log(pred) - log(gt),
+    over valid pixels; ``per_image`` averages the per-image losses."""
+
+    def __init__(self, alpha: float = 10.0, beta: float = 0.15, per_image: bool = True, min_depth: float = 1e-3):
+        super().__init__()
+        self.alpha, self.beta, self.per_image, self.min_depth = alpha, beta, per_image, min_depth
+
+    def forward(self, pred, gt):
+        valid = gt > self.min_depth
+        d = torch.where(valid, torch.log(pred.float().clamp_min(self.min_depth)) - torch.log(gt.clamp_min(self.min_depth)),
+                        torch.zeros_like(gt))
+        dims = (1, 2, 3) if self.per_image else (0, 1, 2, 3)
+        n = valid.sum(dim=dims).clamp_min(1).float()
+        m1 = d.sum(dim=dims) / n
+        m2 = (d * d).sum(dim=dims) / n
+        return (self.alpha * torch.sqrt((m2 - self.beta * m1 * m1).clamp_min(1e-12))).mean()
+
+
+def dist_env() -> Dict[str, int]:
+    return dict(rank=int(os.environ.get("RANK", 0)), local_rank=int(os.environ.get("LOCAL_RANK", 0)),
+                world=int(os.environ.get("WORLD_SIZE", 1)))
+
+
+def init_distributed(backend: Optional[str] = None) -> Dict[str, int]:
+    env = dist_env()
+    if env["world"] > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        backend = backend or ("nccl" if torch.cuda.is_available() else "gloo")
+        if backend == "nccl":
+            torch.cuda.set_device(env["local_rank"])
+        dist.init_process_group(backend=backend, rank=env["rank"], world_size=env["world"])
+    return env
+
+
+def shard_batch(t: torch.Tensor, rank: int, world: int) -> torch.Tensor:
+    """Contiguous split of the global batch, as DistributedSampler-without-shuffle would."""
+    per = t.shape[0] // world
+    return t[rank * per:(rank + 1) * per]
+
+
+def all_reduce_mean(value: torch.Tensor) -> torch.Tensor:
+    """utils/dist_utils.py:45-64 (all_reduce_tensor, SUM then / world)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        value = value.clone()
+        dist.all_reduce(value, op=dist.ReduceOp.SUM)
+        value = value / dist.get_world_size()
+    return value
+
+
+def build_model(version: str = "large07", max_depth: float = 80.0, seed: int = 0, device="cuda") -> NewCRFDepth:
+    torch.manual_seed(seed)
+    return NewCRFDepth(version=version, max_depth=max_depth).to(device)
+
+
+@torch.no_grad()
+def infer(model: nn.Module, images: torch.Tensor, bf16: bool = True) -> torch.Tensor:
+    """The call a user makes for inference: images (B,3,H,W) on the model's device -> depth (B,1,H,W)."""
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf16):
+        return model(images)
+
+
+class Trainer:
+    """fwd + SILog + bwd (+ DDP all-reduce) + clip + AdamW, per the reference's JSON schema."""
+
+    def __init__(self, model: nn.Module, lr: float = 2e-5, grad_norm: float = 0.1, bf16: bool = True,
+                 ddp: bool = False, device_ids=None):
+        self.raw = model
+        self.model = nn.parallel.DistributedDataParallel(model, device_ids=device_ids) if ddp else model
+        self.opt = torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=0.0)
+        self.loss_fn = SILogLoss()
+        self.grad_norm, self.bf16 = grad_norm, bf16
+
+    def step(self, images: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
+        self.opt.zero_grad(set_to_none=True)
+        with torch.autocast(images.device.type, dtype=torch.bfloat16, enabled=self.bf16):
+            pred = self.model(images)
+        loss = self.loss_fn(pred, gt)
+        loss.backward()
+        if self.grad_norm:
+            torch.nn.utils.clip_grad_norm_(self.raw.parameters(), self.grad_norm)
+        self.opt.step()
+        return loss.detach()

@@ -1,0 +1,135 @@
+"""Generate tests/golden/*.pt by RUNNING THE REFERENCE MODULES (fp32, CPU).
+
+Run in the build container only (needs /root/reference):
+
+    python -m oracle.make_golden
+
+TEST INFRASTRUCTURE ONLY.  Each fixture holds seeded inputs, the reference's
+outputs and the gradients autograd computes through the reference code; the
+weights are regenerated from parameter names by oracle/synthetic.py, so the
+fixtures stay a few hundred KB.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+from . import reference_shim as rs
+from .synthetic import depth_errors, randn, synthetic_depth_gt, synthetic_state
+from .window_attention import shift_mask
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _grads(out, inputs, seed_name):
+    w = randn(seed_name + ".cotangent", *out.shape)
+    gs = torch.autograd.grad((out * w).sum(), inputs, allow_unused=True)
+    return w, gs
+
+
+def crf_block(name, ws, shift, b, h, w, c, nh):
+    L = rs.newcrf_layers()
+    blk = L.CRFBlock(c, nh, c, window_size=ws, shift_size=shift).eval()
+    blk.load_state_dict(synthetic_state(blk))
+    x = randn(name + ".x", b, h * w, c).requires_grad_()
+    v = randn(name + ".v", b, h, w, c).requires_grad_()
+    hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
+    blk.H, blk.W = h, w
+    out = blk(x, v, shift_mask(hp, wp, ws, ws // 2) if shift else None)
+    params = [blk.attn.relative_position_bias_table, blk.attn.qk.weight, blk.attn.qk.bias, blk.attn.proj.weight]
+    cot, gs = _grads(out, [x, v] + params, name)
+    return dict(kind="crf_block", cfg=dict(ws=ws, shift=shift, b=b, h=h, w=w, c=c, nh=nh), x=x.detach(), v=v.detach(),
+                out=out.detach(), cot=cot, dx=gs[0], dv=gs[1], dtable=gs[2], dqk_w=gs[3], dqk_b=gs[4], dproj_w=gs[5])
+
+
+def swin_block(name, ws, shift, b, h, w, c, nh):
+    S = rs.swin_transformer()
+    blk = S.SwinTransformerBlock(c, nh, window_size=ws, shift_size=shift).eval()
+    blk.load_state_dict(synthetic_state(blk))
+    x = randn(name + ".x", b, h * w, c).requires_grad_()
+    hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
+    blk.H, blk.W = h, w
+    out = blk(x, shift_mask(hp, wp, ws, ws // 2) if shift else None)
+    params = [blk.attn.relative_position_bias_table, blk.attn.qkv.weight, blk.attn.qkv.bias]
+    cot, gs = _grads(out, [x] + params, name)
+    return dict(kind="swin_block", cfg=dict(ws=ws, shift=shift, b=b, h=h, w=w, c=c, nh=nh), x=x.detach(),
+                out=out.detach(), cot=cot, dx=gs[0], dtable=gs[1], dqkv_w=gs[2], dqkv_b=gs[3])
+
+
+def masked_windows(name, ws, nw, groups, c, nh):
+    """WindowAttention.forward(x, v, mask) on window-order tokens with an arbitrary mask."""
+    L = rs.newcrf_layers()
+    att = L.WindowAttention(c, (ws, ws), nh, c).eval()
+    att.load_state_dict(synthetic_state(att))
+    n = ws * ws
+    x = randn(name + ".x", nw * groups, n, c)
+    v = randn(name + ".v", nw * groups, n, c)
+    mask = torch.where(randn(name + ".m", nw, n, n) > 0.8, -100.0, 0.0)
+    with torch.no_grad():
+        out, out_nomask = att(x, v, mask), att(x, v, None)
+    return dict(kind="masked_windows", cfg=dict(ws=ws, nw=nw, groups=groups, c=c, nh=nh), x=x, v=v, mask=mask,
+                out=out, out_nomask=out_nomask)
+
+
+def newcrf_level(name, b, h, w, cin, embed, vdim, nh):
+    L = rs.newcrf_layers()
+    m = L.NewCRF(input_dim=cin, embed_dim=embed, v_dim=vdim, window_size=7, num_heads=nh).eval()
+    m.load_state_dict(synthetic_state(m))
+    x = randn(name + ".x", b, cin, h, w).requires_grad_()
+    v = randn(name + ".v", b, vdim, h, w).requires_grad_()
+    out = m(x, v)
+    cot, gs = _grads(out, [x, v, m.crf_layer.blocks[1].attn.relative_position_bias_table], name)
+    return dict(kind="newcrf_level", cfg=dict(b=b, h=h, w=w, cin=cin, embed=embed, vdim=vdim, nh=nh), x=x.detach(),
+                v=v.detach(), out=out.detach(), cot=cot, dx=gs[0], dv=gs[1], dtable1=gs[2])
+
+
+def full_model(name, version, b, h, w, max_depth=80.0):
+    D = rs.newcrf_depth()
+    m = D.NewCRFDepth(version=version, max_depth=max_depth).eval()
+    m.load_state_dict(synthetic_state(m))
+    img = randn(name + ".img", b, 3, h, w)
+    with torch.no_grad():
+        depth = m(img)
+    gt = synthetic_depth_gt(name + ".gt", b, h, w, max_depth)
+    valid = (gt > 1e-3).numpy()
+    pred = depth.clamp(1e-3, max_depth).numpy()
+    # the reference's own metric code (utils/depth_utils.py:32-54)
+    sys.path.insert(0, rs.REFERENCE_ROOT)
+    from utils.depth_utils import tcompute_errors
+    ref_err = tcompute_errors(gt.numpy()[valid], pred[valid])
+    mine = depth_errors(gt.numpy()[valid], pred[valid])
+    assert abs(mine["abs_rel"] - ref_err["abs_rel"]) < 1e-12 and abs(mine["rmse"] - ref_err["rmse"]) < 1e-12
+    return dict(kind="full_model", cfg=dict(version=version, b=b, h=h, w=w, max_depth=max_depth), img=img, depth=depth,
+                abs_rel=float(ref_err["abs_rel"]), rmse=float(ref_err["rmse"]))
+
+
+CASES = {
+    "crf_block_ws7_s0": lambda n: crf_block(n, 7, 0, 2, 9, 11, 64, 2),
+    "crf_block_ws7_s3": lambda n: crf_block(n, 7, 3, 2, 9, 11, 64, 2),
+    "crf_block_ws7_s3_exact": lambda n: crf_block(n, 7, 3, 1, 14, 21, 128, 4),
+    "swin_block_ws7_s0": lambda n: swin_block(n, 7, 0, 1, 10, 16, 96, 3),
+    "swin_block_ws7_s3": lambda n: swin_block(n, 7, 3, 1, 10, 16, 96, 3),
+    "swin_block_ws12_s6": lambda n: swin_block(n, 12, 6, 1, 13, 25, 64, 2),
+    "swin_block_ws12_s0": lambda n: swin_block(n, 12, 0, 1, 24, 12, 64, 2),
+    "masked_windows_ws7": lambda n: masked_windows(n, 7, 4, 2, 64, 2),
+    "newcrf_level": lambda n: newcrf_level(n, 1, 10, 13, 48, 64, 32, 2),
+    "newcrfdepth_tiny07": lambda n: full_model(n, "tiny07", 1, 64, 96),
+}
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(8)
+    for name, fn in CASES.items():
+        blob = fn(name)
+        blob = {k: (v.to(torch.float32).contiguous() if torch.is_tensor(v) else v) for k, v in blob.items()}
+        path = os.path.join(OUT, name + ".pt")
+        torch.save(blob, path)
+        print(f"{name}: {os.path.getsize(path) / 1024:.0f} KB")
+
+
+if __name__ == "__main__":
+    main()

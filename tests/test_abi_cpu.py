@@ -1,0 +1,73 @@
+"""The C-ABI library loads and exports every symbol include/swin_attn.h declares;
+argument validation answers without touching a GPU.  CPU only (no compute calls)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from mde_b200 import _lib
+from conftest import ROOT
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "swin_attn.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(swin_attn_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    names = _declared()
+    assert set(names) == set(_lib.EXPORTS), names
+    for n in names:
+        assert getattr(lib, n) is not None
+
+
+def test_shape_struct_matches_header_layout():
+    # 8 x int32, 2 x float, uint64, 4 x int64, 2 x int32
+    assert ctypes.sizeof(_lib.Shape) == 8 * 4 + 2 * 4 + 8 + 4 * 8 + 2 * 4
+
+
+@pytest.mark.parametrize("field,value,msg", [
+    ("window", 8, "window must be 7 or 12"),
+    ("shift", 7, "shift_size must in 0-window_size"),
+    ("dtype", 5, "dtype must be"),
+    ("num_heads", 0, "must be positive"),
+    ("q_pix_stride", 16, "pixel strides must be >="),
+    ("dropout_p", 0.5, "dropout"),
+])
+def test_validation_errors_without_gpu(field, value, msg):
+    lib = _lib.load()
+    shp = _lib.Shape(1, 7, 7, 2, 7, 0, _lib.F32, 0, 0.1767, 0.0, 0, 64, 64, 64, 64, 0, 0)
+    setattr(shp, field, value)
+    rc = lib.swin_attn_forward(ctypes.byref(shp), *([None] * 11))
+    assert rc != 0
+    assert msg in lib.swin_attn_last_error().decode()
+    with pytest.raises(RuntimeError, match=msg):
+        _lib.check(rc)
+
+
+def test_null_pointers_are_rejected():
+    lib = _lib.load()
+    shp = _lib.Shape(1, 7, 7, 2, 7, 0, _lib.F32, 0, 0.1767, 0.0, 0, 64, 64, 64, 64, 0, 0)
+    assert lib.swin_attn_forward(ctypes.byref(shp), *([None] * 11)) != 0
+    assert "non-null" in lib.swin_attn_last_error().decode()
+    shp.height = 8
+    assert lib.swin_attn_backward(ctypes.byref(shp), *([None] * 13)) != 0
+    assert "multiples of the window" in lib.swin_attn_last_error().decode()
+    assert lib.swin_attn_version().decode().startswith("swin_attn")
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/libswin_attn.so")
+    with pytest.raises(RuntimeError, match="no CPU or PyTorch fallback"):
+        _lib.load()
+
+
+def test_ops_have_no_cpu_kernel():
+    import torch
+    from mde_b200 import ops
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        ops.window_attention(torch.zeros(1, 7, 7, 96), None, torch.zeros(169, 1), 7, 0, 1)

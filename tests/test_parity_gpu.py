@@ -1,0 +1,300 @@
+"""GPU parity: the CUDA path (through the C ABI / torch.library ops / drop-in
+modules) against (a) the reference outputs in tests/golden and (b) the CPU
+oracle on seeded inputs.  Tolerances (north_star): max-normalised error
+<= 1e-5 in fp32, <= 1e-2 in bf16, activations and gradients."""
+import ctypes
+
+import pytest
+import torch
+
+import mde_b200
+from mde_b200 import _lib, layers, ops
+from oracle import window_attention as wa
+from oracle.synthetic import depth_errors, randn, synthetic_depth_gt, synthetic_state
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+TOL_F32 = 1e-5
+TOL_BF16 = 1e-2
+DEV = "cuda"
+IMPLS = {"simt": _lib.IMPL_SIMT, "auto": _lib.IMPL_AUTO}
+
+
+def _oracle(packed, v, table, ws, shift, nh, pads=None, v_pad=None):
+    c = nh * 32
+    packed = packed.double().cpu()
+    q, k = packed[..., :c], packed[..., c:2 * c]
+    vv = packed[..., 2 * c:] if v is None else v.double().cpu()
+    qp = kp = vp = None
+    if pads is not None:
+        pads = pads.double().cpu()
+        qp, kp = pads[:c], pads[c:2 * c]
+        vp = pads[2 * c:] if v is None else None
+    if v_pad is not None:
+        vp = v_pad.double().cpu()
+    return wa.window_attention(q, k, vv, table.double().cpu(), ws, shift, nh, None, qp, kp, vp)
+
+
+CASES = [  # ws, shift, B, H, W, nH, external_v
+    (7, 0, 2, 14, 21, 2, False), (7, 3, 2, 14, 21, 2, False), (7, 3, 1, 9, 11, 4, True), (7, 0, 3, 7, 7, 1, True),
+    (7, 3, 1, 1, 1, 2, False), (7, 3, 2, 22, 44, 6, False), (7, 2, 1, 15, 8, 3, True),
+    (12, 6, 1, 13, 25, 2, False), (12, 0, 2, 24, 12, 2, True), (12, 6, 1, 24, 36, 4, False),
+]
+
+
+@pytest.mark.parametrize("impl", list(IMPLS))
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("case", CASES)
+def test_forward_matches_oracle(case, dtype, impl):
+    ws, shift, b, h, w, nh, ext = case
+    c = nh * 32
+    name = f"fwd{case}"
+    packed = randn(name + ".p", b, h, w, (2 if ext else 3) * c).to(dtype)
+    v = randn(name + ".v", b, h, w, c).to(dtype) if ext else None
+    table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
+    pads = (0.3 * randn(name + ".pad", (2 if ext else 3) * c)).to(dtype)
+    want, want_lse = _oracle(packed.float(), None if v is None else v.float(), table, ws, shift, nh, pads.float())
+    got, lse = torch.ops.swin_attn.fwd(packed.to(DEV), None if v is None else v.to(DEV), table.to(DEV), pads.to(DEV),
+                                       None, ws, shift, nh, 32 ** -0.5, True, IMPLS[impl], None)
+    tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
+    assert got.shape == (b, h, w, c) and got.dtype == dtype
+    assert rel_err(got.float(), want) < tol
+    assert rel_err(lse, want_lse) < (1e-5 if dtype == torch.float32 else 2e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("case", [c for c in CASES if c[3] % c[0] == 0 and c[4] % c[0] == 0])
+def test_backward_matches_oracle_autograd(case, dtype):
+    ws, shift, b, h, w, nh, ext = case
+    c = nh * 32
+    name = f"bwd{case}"
+    packed = randn(name + ".p", b, h, w, (2 if ext else 3) * c).to(dtype)
+    v = randn(name + ".v", b, h, w, c).to(dtype) if ext else None
+    table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
+    cot = randn(name + ".c", b, h, w, c).to(dtype)
+    # oracle in fp64 with autograd
+    pr = packed.double().requires_grad_()
+    vr = None if v is None else v.double().requires_grad_()
+    tr = table.double().requires_grad_()
+    qq, kk = pr[..., :c], pr[..., c:2 * c]
+    o_ref, _ = wa.window_attention(qq, kk, pr[..., 2 * c:] if v is None else vr, tr, ws, shift, nh)
+    ins = [pr, tr] + ([] if v is None else [vr])
+    g_ref = torch.autograd.grad((o_ref * cot.double()).sum(), ins)
+    pg = packed.to(DEV).requires_grad_()
+    vg = None if v is None else v.to(DEV).requires_grad_()
+    tg = table.to(DEV).requires_grad_()
+    o = ops.window_attention(pg, vg, tg, ws, shift, nh)
+    g = torch.autograd.grad((o.float() * cot.to(DEV).float()).sum(), [pg, tg] + ([] if v is None else [vg]))
+    tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
+    assert rel_err(o.float(), o_ref) < tol
+    for got, want, what in zip(g, g_ref, ["d_packed", "d_table", "d_v"]):
+        assert got.dtype == (torch.float32 if what == "d_table" else dtype)
+        assert rel_err(got.float(), want) < tol, what
+
+
+def _block_from_golden(g, cuda=True):
+    cfg = g["cfg"]
+    if g["kind"] == "crf_block":
+        blk = layers.CRFBlock(cfg["c"], cfg["nh"], cfg["c"], window_size=cfg["ws"], shift_size=cfg["shift"])
+    else:
+        blk = layers.SwinTransformerBlock(cfg["c"], cfg["nh"], window_size=cfg["ws"], shift_size=cfg["shift"])
+    blk.load_state_dict(synthetic_state(blk), strict=True)
+    blk.H, blk.W = cfg["h"], cfg["w"]
+    return blk.to(DEV).eval() if cuda else blk.eval()
+
+
+@pytest.mark.parametrize("name", ["crf_block_ws7_s0", "crf_block_ws7_s3", "crf_block_ws7_s3_exact"])
+def test_crf_block_fp32_vs_reference_golden(golden, name):
+    g = golden(name)
+    blk = _block_from_golden(g)
+    x, v = g["x"].to(DEV).requires_grad_(), g["v"].to(DEV).requires_grad_()
+    out = blk(x, v, None)
+    assert rel_err(out, g["out"]) < TOL_F32
+    a = blk.attn
+    gs = torch.autograd.grad((out * g["cot"].to(DEV)).sum(),
+                             [x, v, a.relative_position_bias_table, a.qk.weight, a.qk.bias, a.proj.weight])
+    for got, key in zip(gs, ["dx", "dv", "dtable", "dqk_w", "dqk_b", "dproj_w"]):
+        assert rel_err(got, g[key]) < TOL_F32, key
+    with torch.no_grad():   # inference path: pad vectors instead of F.pad
+        assert rel_err(blk(x, v, None), g["out"]) < TOL_F32
+
+
+@pytest.mark.parametrize("name", ["swin_block_ws7_s0", "swin_block_ws7_s3", "swin_block_ws12_s6", "swin_block_ws12_s0"])
+def test_swin_block_fp32_vs_reference_golden(golden, name):
+    g = golden(name)
+    blk = _block_from_golden(g)
+    x = g["x"].to(DEV).requires_grad_()
+    out = blk(x, None)
+    assert rel_err(out, g["out"]) < TOL_F32
+    a = blk.attn
+    gs = torch.autograd.grad((out * g["cot"].to(DEV)).sum(), [x, a.relative_position_bias_table, a.qkv.weight, a.qkv.bias])
+    for got, key in zip(gs, ["dx", "dtable", "dqkv_w", "dqkv_b"]):
+        assert rel_err(got, g[key]) < TOL_F32, key
+    with torch.no_grad():
+        assert rel_err(blk(x, None), g["out"]) < TOL_F32
+
+
+@pytest.mark.parametrize("name", ["crf_block_ws7_s3", "swin_block_ws7_s3", "swin_block_ws12_s6", "crf_block_ws7_s3_exact"])
+def test_blocks_bf16_autocast_vs_reference_golden(golden, name):
+    """bf16 = torch.autocast, the only bf16 mode the reference runs in."""
+    g = golden(name)
+    blk = _block_from_golden(g)
+    x = g["x"].to(DEV).requires_grad_()
+    args = (x, g["v"].to(DEV).requires_grad_(), None) if g["kind"] == "crf_block" else (x, None)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = blk(*args)
+    assert rel_err(out.float(), g["out"]) < TOL_BF16
+    dx, dt = torch.autograd.grad((out.float() * g["cot"].to(DEV)).sum(), [x, blk.attn.relative_position_bias_table])
+    assert rel_err(dx, g["dx"]) < TOL_BF16
+    assert rel_err(dt, g["dtable"]) < 2 * TOL_BF16  # a sum over every window of bf16-rounded dS
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        assert rel_err(blk(*args).float(), g["out"]) < TOL_BF16
+
+
+def test_masked_window_attention_vs_reference_golden(golden):
+    g = golden("masked_windows_ws7")
+    cfg = g["cfg"]
+    att = layers.WindowAttention(cfg["c"], (cfg["ws"],) * 2, cfg["nh"], cfg["c"])
+    att.load_state_dict(synthetic_state(att), strict=True)
+    att = att.to(DEV).eval()
+    x, v, mask = g["x"].to(DEV), g["v"].to(DEV), g["mask"].to(DEV)
+    with torch.no_grad():
+        assert rel_err(att(x, v, mask), g["out"]) < TOL_F32
+        assert rel_err(att(x, v, None), g["out_nomask"]) < TOL_F32
+    xg = x.clone().requires_grad_()
+    out = att(xg, v, mask)
+    (dx,) = torch.autograd.grad(out.sum(), [xg])
+    from oracle.cpu_model import to_oracle
+    ref = to_oracle(att)
+    xr = g["x"].clone().requires_grad_()
+    (dxr,) = torch.autograd.grad(ref(xr, g["v"], g["mask"]).sum(), [xr])
+    assert rel_err(dx, dxr) < TOL_F32
+
+
+def test_newcrf_level_vs_reference_golden(golden):
+    g = golden("newcrf_level")
+    cfg = g["cfg"]
+    m = layers.NewCRF(input_dim=cfg["cin"], embed_dim=cfg["embed"], v_dim=cfg["vdim"], window_size=7, num_heads=cfg["nh"])
+    m.load_state_dict(synthetic_state(m), strict=True)
+    m = m.to(DEV).eval()
+    x, v = g["x"].to(DEV).requires_grad_(), g["v"].to(DEV).requires_grad_()
+    out = m(x, v)
+    assert rel_err(out, g["out"]) < 2e-5  # two stacked blocks + cuDNN convs
+    gs = torch.autograd.grad((out * g["cot"].to(DEV)).sum(), [x, v, m.crf_layer.blocks[1].attn.relative_position_bias_table])
+    for got, key in zip(gs, ["dx", "dv", "dtable1"]):
+        assert rel_err(got, g[key]) < 5e-5, key
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_full_model_depth_metrics_vs_reference_golden(golden, mode):
+    """NewCRFDepth depth map and AbsRel / RMSE on a fixed synthetic GT within 1e-3 of the reference."""
+    g = golden("newcrfdepth_tiny07")
+    cfg = g["cfg"]
+    m = mde_b200.NewCRFDepth(version=cfg["version"], max_depth=cfg["max_depth"])
+    m.load_state_dict(synthetic_state(m), strict=True)
+    m = m.to(DEV).eval()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=mode == "bf16"):
+        depth = m(g["img"].to(DEV)).float().cpu()
+    gt = synthetic_depth_gt("newcrfdepth_tiny07.gt", cfg["b"], cfg["h"], cfg["w"], cfg["max_depth"])
+    valid = (gt > 1e-3).numpy()
+    err = depth_errors(gt.numpy()[valid], depth.clamp(1e-3, cfg["max_depth"]).numpy()[valid])
+    if mode == "fp32":
+        assert rel_err(depth, g["depth"]) < 1e-4  # 12 + 8 blocks and cuDNN/cuBLAS fp32 reductions
+        assert abs(err["abs_rel"] - g["abs_rel"]) < 1e-3 and abs(err["rmse"] - g["rmse"]) < 1e-3
+    else:
+        assert rel_err(depth, g["depth"]) < 5e-2
+        assert abs(err["abs_rel"] - g["abs_rel"]) < 1e-2 and abs(err["rmse"] - g["rmse"]) / g["rmse"] < 1e-2
+
+
+def test_host_buffer_entry_matches_device_entry():
+    nh, ws, b, h, w = 4, 7, 2, 16, 23
+    c = nh * 32
+    q, k, v = (randn(f"host.{n}", b, h, w, c) for n in "qkv")
+    table = 0.5 * randn("host.t", 169, nh)
+    pads = [0.3 * randn(f"host.pad{n}", c) for n in "qkv"]
+    for dtype, tol in [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)]:
+        got = ops.window_attention_host(q.to(dtype), k.to(dtype), v.to(dtype), table, ws, 3, nh,
+                                        q_pad=pads[0], k_pad=pads[1], v_pad=pads[2])
+        want, _ = wa.window_attention(q.to(dtype).double(), k.to(dtype).double(), v.to(dtype).double(), table.double(),
+                                      ws, 3, nh, None, *[p.to(dtype).double() for p in pads])
+        assert got.device.type == "cpu" and rel_err(got.float(), want) < tol
+
+
+def test_error_behaviour_mirrors_reference_asserts():
+    x = torch.zeros(1, 7, 7, 64, device=DEV)
+    t = torch.zeros(169, 1, device=DEV)
+    with pytest.raises(AssertionError, match="shift_size must in 0-window_size"):
+        ops.window_attention(torch.zeros(1, 7, 7, 96, device=DEV), None, t, 7, 7, 1)
+    with pytest.raises(RuntimeError, match="self.dim != v.shape"):
+        ops.window_attention(x, torch.zeros(1, 7, 7, 64, device=DEV), t, 7, 0, 1)
+    with pytest.raises(RuntimeError, match="window must be 7 or 12"):
+        ops.window_attention(torch.zeros(1, 8, 8, 96, device=DEV), None, t, 8, 0, 1)
+    with pytest.raises(RuntimeError):  # fp16 is not a supported storage type
+        ops.window_attention(torch.zeros(1, 7, 7, 96, device=DEV, dtype=torch.float16), None, t, 7, 0, 1)
+    with pytest.raises((RuntimeError, NotImplementedError)):  # no CPU path, by design
+        ops.window_attention(torch.zeros(1, 7, 7, 96), None, torch.zeros(169, 1), 7, 0, 1)
+    blk = layers.CRFBlock(64, 2, 64).to(DEV)
+    blk.H, blk.W = 5, 5
+    with pytest.raises(AssertionError, match="input feature has wrong size"):
+        blk(torch.zeros(1, 24, 64, device=DEV), torch.zeros(1, 5, 5, 64, device=DEV), None)
+
+
+# ---- size-independent properties at BASELINE.json's full sizes --------------------------------
+
+FULL = [  # large07 stage-0 grids of the three BASELINE shapes, batch 8 / 2
+    (8, 88, 304, 6, 7), (8, 120, 160, 6, 7), (2, 88, 176, 4, 7),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", FULL)
+@pytest.mark.parametrize("shift", [0, 3])
+def test_full_size_properties(shape, shift, dtype):
+    b, h, w, nh, ws = shape
+    c = nh * 32
+    gen = torch.Generator(device=DEV).manual_seed(1234)
+    qkv = torch.randn(b, h, w, 3 * c, device=DEV, generator=gen).to(dtype)
+    table = 0.5 * torch.randn((2 * ws - 1) ** 2, nh, device=DEV, generator=gen)
+    pad = (0.3 * torch.randn(3 * c, device=DEV, generator=gen)).to(dtype)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+
+    def run(t, p=pad):
+        return torch.ops.swin_attn.fwd(t, None, table, p, None, ws, shift, nh, 32 ** -0.5, True, _lib.IMPL_AUTO, None)
+
+    o, lse = run(qkv)
+    assert torch.isfinite(o).all() and torch.isfinite(lse).all()
+    # (1) rows of P sum to one: v == const  =>  o == const, everywhere (pad tokens included)
+    ones = qkv.clone()
+    ones[..., 2 * c:] = 1.0
+    pad1 = pad.clone()
+    pad1[2 * c:] = 1.0
+    o1, _ = run(ones, pad1)
+    assert (o1.float() - 1.0).abs().max() < tol
+    # (2) linearity in v:  attn(q,k,a*v1+v2) == a*attn(q,k,v1) + attn(q,k,v2)
+    v2 = torch.randn(b, h, w, c, device=DEV, generator=gen).to(dtype)
+    mix = qkv.clone()
+    mix[..., 2 * c:] = v2
+    zpad = pad.clone()
+    zpad[2 * c:] = 0
+    oa, _ = run(qkv, zpad)
+    ob, _ = run(mix, zpad)
+    both = qkv.clone()
+    both[..., 2 * c:] = (0.5 * qkv[..., 2 * c:].float() + v2.float()).to(dtype)
+    oc, _ = run(both, zpad)
+    assert rel_err(oc.float(), 0.5 * oa.float() + ob.float()) < (1e-5 if dtype == torch.float32 else 3e-2)
+    # (3) checksum against the oracle on one image of the batch (seconds on the CPU)
+    want, want_lse = _oracle(qkv[:1].float(), None, table, ws, shift, nh, pad.float())
+    assert rel_err(o[:1].float(), want) < (TOL_F32 if dtype == torch.float32 else TOL_BF16)
+    # (4) simt and auto (tcgen05 when available) kernels agree on the whole batch
+    o_s, lse_s = torch.ops.swin_attn.fwd(qkv, None, table, pad, None, ws, shift, nh, 32 ** -0.5, True, _lib.IMPL_SIMT, None)
+    assert rel_err(o.float(), o_s.float()) < (1e-6 if dtype == torch.float32 else TOL_BF16)
+
+
+def test_library_counts_launches():
+    before = _lib.launch_count()
+    x = torch.zeros(1, 7, 7, 96, device=DEV)
+    ops.window_attention(x, None, torch.zeros(169, 1, device=DEV), 7, 0, 1)
+    torch.cuda.synchronize()
+    assert _lib.launch_count() == before + 1
