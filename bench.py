@@ -1,0 +1,248 @@
+#!/usr/bin/env python
+"""Headline benchmark: NewCRFs Swin-L (``large07``) inference images/s at
+352x1216, bf16 autocast, batch 8 per GPU, synthetic KITTI-shape input
+(BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One JSON line on rank 0.  ``value`` = device-resident throughput, ``e2e`` = the
+same through ``harness.infer`` with pinned-host images copied in and the depth
+map copied out every step.  ``roofline`` is for the window-attention forward
+kernel (all its launches inside the timed region, CUDA events on the launching
+stream); ``cpu_baseline`` / ``--impl reference`` time the oracle's CPU
+restatement of the reference model (the reference is Python + missing deps
+and cannot travel to the GPU box).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+VERSION, HEIGHT, WIDTH, BATCH, MAX_DEPTH = "large07", 352, 1216, 8, 80.0
+METRIC = "NewCRFs Swin-L images/sec @352x1216 (bf16 inference, batch 8/GPU)"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--version", default=VERSION)
+    ap.add_argument("--batch", type=int, default=BATCH)
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return d["hbm_gbs"], d["bf16_tflops_sustained"], "measured"
+    return 6650.0, 1400.0, "fallback"  # B200_PROFILING.md fallback
+
+
+class ClockSampler(threading.Thread):
+    """SM clock + throttle reasons during the timed region (pynvml)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {
+                nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+            }
+            while not self.stop_flag:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.reasons |= {n for bit, n in names.items() if r & bit}
+                time.sleep(0.1)
+        except Exception as e:  # clocks are a report, not a dependency
+            self.reasons.add(f"unavailable:{type(e).__name__}")
+
+    def summary(self):
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def cpu_model_and_sample(version):
+    from oracle.cpu_model import build_newcrfs
+    from mde_b200.harness import synthetic_images
+    model = build_newcrfs(version, seed=0, max_depth=MAX_DEPTH)
+    return model, synthetic_images(1, HEIGHT, WIDTH, seed=0)
+
+
+def time_cpu(model, img, steps, warmup):
+    with torch.no_grad():
+        for _ in range(warmup):
+            model(img)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            model(img)
+        dt = time.perf_counter() - t0
+    return img.shape[0] * steps / dt, dt / steps
+
+
+def run_reference(args, rank):
+    """Reference arm: the reference's CPU implementation of the path (oracle port;
+    see module docstring), every host thread, one image of the workload per step."""
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    model, img = cpu_model_and_sample(args.version)
+    ips, spstep = time_cpu(model, img, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": ips, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"NewCRFs {args.version} full-model inference, 352x1216 KITTI shape",
+                   "sample": "1 image per step on the host CPU"},
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
+                         "sample": "1 image (of the batch-8 workload) per step, fp32, torch CPU"},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, env):
+    from mde_b200 import _lib, ops
+    from mde_b200.harness import build_model, infer, synthetic_images
+
+    rank, world, local = env["rank"], env["world"], env["local_rank"]
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    model = build_model(args.version, MAX_DEPTH, seed=0, device=dev).eval()
+    host = synthetic_images(args.batch, HEIGHT, WIDTH, seed=rank, pin=True)
+    images = host.to(dev)
+    out_host = torch.empty(args.batch, 1, HEIGHT, WIDTH).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_steps(step_fn, steps):
+        """K steps, each bracketed by its own CUDA events with an L2 flush before it."""
+        evs = []
+        for _ in range(steps):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            step_fn()
+            b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in evs) / 1e3
+
+    def step_resident():
+        infer(model, images)
+
+    def step_e2e():
+        x = host.to(dev, non_blocking=True)
+        out_host.copy_(infer(model, x).float(), non_blocking=True)
+
+    for _ in range(args.warmup):
+        step_resident()
+        step_e2e()
+    sampler = ClockSampler(local)
+    records = []
+    barrier()
+    sampler.start()
+    launches0 = _lib.launch_count()
+    ops.set_kernel_timing(records)
+    t_res = timed_steps(step_resident, args.steps)
+    ops.set_kernel_timing(None)
+    launches = _lib.launch_count() - launches0
+    barrier()
+    t_e2e = timed_steps(step_e2e, args.steps)
+    barrier()
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    times = torch.tensor([t_res, t_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    t_res, t_e2e = times.tolist()
+    if rank != 0:
+        return
+    hbm, tf, which = peaks()
+    k_ms = sum(a.elapsed_time(b) for a, b, *_ in records)
+    k_bytes = sum(r[2] for r in records)
+    k_flops = sum(r[3] for r in records)
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9 if k_ms else None
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+    n_img = args.batch * world * args.steps
+    line = {
+        "metric": METRIC, "value": n_img / t_res, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": t_res / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"NewCRFs {args.version} full-model inference, batch {args.batch}/GPU, 3x352x1216 "
+                               "KITTI-shape synthetic images, torch.autocast(bf16), random-init weights",
+                   "parallelism": f"replicas x{world} (batch data-parallel, no data-path collective)",
+                   "l2_flush_between_steps": True, "timing": "CUDA events per step, max over ranks"},
+        "e2e": {"value": n_img / t_e2e, "unit": "images/s", "h2d_bytes_per_step": host.numel() * 4,
+                "d2h_bytes_per_step": out_host.numel() * 4},
+        "gpu_launches": int(launches),
+        "clocks": sampler.summary(),
+        "roofline": {"bound": "hbm", "kernel": "swin_attn forward (all window-attention launches of the step)",
+                     "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm if achieved else None,
+                     "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)", "traffic": traffic,
+                     "launches": len(records), "kernel_ms_per_step": k_ms / args.steps,
+                     "share_of_step": k_ms / 1e3 / t_res if t_res else None,
+                     "useful_tflops": k_flops / (k_ms * 1e-3) / 1e12 if k_ms else None,
+                     "tensor_frac_of_sustained_bf16": k_flops / (k_ms * 1e-3) / 1e12 / tf if k_ms else None},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        cm, img = cpu_model_and_sample(args.version)
+        ips, _ = time_cpu(cm, img, 1, 1)
+        line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
+                                "sample": "1 image of the batch-8 workload, 1 warm-up + 1 timed forward, fp32 torch CPU "
+                                          "(oracle restatement of the reference model)"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse()
+    from mde_b200.harness import dist_env, init_distributed
+    env = dist_env()
+    if args.impl == "reference":
+        run_reference(args, env["rank"])
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    env = init_distributed("nccl")
+    run_ours(args, env)
+    if env["world"] > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -24,6 +24,16 @@ from . import _lib
 
 _DTYPES = {torch.float32: _lib.F32, torch.bfloat16: _lib.BF16}
 
+# Optional per-launch timing (bench.py): a list that receives
+# (start_event, end_event, algorithmic_bytes, algorithmic_flops, tag) for every
+# forward launch, the events recorded on the launching (current) stream.
+_kernel_timing = None
+
+
+def set_kernel_timing(records):
+    global _kernel_timing
+    _kernel_timing = records
+
 
 def _ptr(t: Optional[Tensor]):
     return None if t is None else ctypes.c_void_p(t.data_ptr())
@@ -101,10 +111,20 @@ def _fwd(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, packed_pad: Op
     kpad_ptr = None if packed_pad is None else packed_pad.data_ptr() + c * es
     with torch.cuda.device(packed.device):
         stream = torch.cuda.current_stream().cuda_stream
+        if _kernel_timing is not None:
+            ev0 = torch.cuda.Event(enable_timing=True)
+            ev0.record()
         _lib.check(lib.swin_attn_forward(
             ctypes.byref(shp), ctypes.c_void_p(base), ctypes.c_void_p(base + c * es), ctypes.c_void_p(v_ptr),
             ctypes.c_void_p(qpad_ptr), ctypes.c_void_p(kpad_ptr), ctypes.c_void_p(vpad_ptr),
             _ptr(table), _ptr(mask), _ptr(o), _ptr(lse) if need_lse else None, ctypes.c_void_p(stream)))
+        if _kernel_timing is not None:
+            ev1 = torch.cuda.Event(enable_timing=True)
+            ev1.record()
+            tokens = b * h * w
+            # algorithmic traffic: read q, k, v and write o once, valid tokens only
+            _kernel_timing.append((ev0, ev1, 4 * tokens * c * es + (lse.numel() * 4 if need_lse else 0),
+                                   4 * b * hp * wp * window * window * c, (window, shift, num_heads, h, w)))
     return o, lse
 
 

@@ -81,9 +81,13 @@ class OracleEncoderWindowAttention(layers.EncoderWindowAttention):
 _SWAP = {layers.WindowAttention: OracleWindowAttention, layers.EncoderWindowAttention: OracleEncoderWindowAttention}
 
 
-def to_oracle(module: torch.nn.Module) -> torch.nn.Module:
-    """Deep copy of ``module`` on the CPU whose attention runs the oracle."""
-    clone = copy.deepcopy(module).cpu()
+def to_oracle(module: torch.nn.Module, device="cpu") -> torch.nn.Module:
+    """Deep copy of ``module`` (on the CPU by default) whose attention runs the oracle.
+
+    With ``device="cuda"`` the same restatement runs as PyTorch-eager ATen kernels on the GPU:
+    that is "the reference on the B200" (used to measure the reference's own bf16-autocast
+    error and the eager baseline), still never the product path."""
+    clone = copy.deepcopy(module).to(device)
     for m in clone.modules():
         if type(m) in _SWAP:
             m.__class__ = _SWAP[type(m)]

@@ -50,14 +50,14 @@ def unpartition(win: torch.Tensor, ws: int, b: int, hp: int, wp: int) -> torch.T
     return x.permute(0, 1, 3, 2, 4, 5).reshape(b, hp, wp, c)
 
 
-def shift_mask(hp: int, wp: int, ws: int, shift: int, dtype=torch.float32) -> torch.Tensor:
+def shift_mask(hp: int, wp: int, ws: int, shift: int, dtype=torch.float32, device="cpu") -> torch.Tensor:
     """(nW, N, N) additive SW-MSA mask with values {0, -100}.
 
     newcrf_layers.py:331-350 == swin_transformer.py:361-380: nine regions
     from the slices [0, -ws), [-ws, -shift), [-shift, end) along each axis of
     the *shifted, padded* image; pairs in different regions get -100.
     """
-    region = torch.zeros(1, hp, wp, 1, dtype=dtype)
+    region = torch.zeros(1, hp, wp, 1, dtype=dtype, device=device)
     cuts = (slice(0, -ws), slice(-ws, -shift), slice(-shift, None))
     n = 0
     for hs in cuts:
@@ -131,11 +131,11 @@ def window_attention(
 
     qw, kw, vw = heads(qp), heads(kp), heads(vp)
     logits = (qw * scale) @ kw.transpose(-2, -1)          # (B_, nH, N, N)
-    idx = relative_position_index(ws).reshape(-1)
+    idx = relative_position_index(ws).reshape(-1).to(q.device)
     bias = bias_table.to(logits.dtype)[idx].reshape(n, n, nh).permute(2, 0, 1)
     logits = logits + bias[None]
     if shift > 0:
-        m = shift_mask(hp, wp, ws, shift, logits.dtype)   # (nW, N, N)
+        m = shift_mask(hp, wp, ws, shift, torch.float32, q.device)   # (nW, N, N), fp32 as in the reference
         nw = m.shape[0]
         logits = (logits.reshape(b, nw, nh, n, n) + m[None, :, None]).reshape(-1, nh, n, n)
     lse = torch.logsumexp(logits, dim=-1)                 # (B_, nH, N)
