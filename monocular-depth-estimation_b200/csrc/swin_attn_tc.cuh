@@ -1,0 +1,207 @@
+// Shifted-window attention forward for sm_100a: tcgen05 bf16 MMAs with fp32
+// accumulators in tensor memory, one persistent CTA per SM.
+//
+// Tile = one (window, head): Q, K, V are 49 x 32 bf16 (padded to 64 rows in
+// shared memory).  Two tiles form a PAIR that shares TMEM columns: tile 0
+// lives in lanes 0-15 of each 32-lane TMEM sub-partition, tile 1 in lanes
+// 16-31 (an M=64 accumulator occupies 16 lanes per sub-partition), so one
+// `tcgen05.ld.32x32b` hands every thread of a softmax warp one complete row of
+// S -- no cross-lane reduction is needed for the row max / row sum.
+//
+//   producer warps (0,2,3): gather Q,K,V rows straight from the image-order
+//       tensors (pad / cyclic shift / window partition are address arithmetic)
+//       with 16-byte cp.async into 64B-swizzled K-major tiles
+//   MMA warp (1), one thread:  S = Q K^T   (M64 N56 K32, SS)  -> TMEM
+//                              O = P V     (M64 N32 K64, SS, V is MN-major)
+//   softmax warpgroups (3 x 4 warps): S row from TMEM, scale + relative
+//       position bias (table staged in smem) + analytic SW-MSA mask, exp2,
+//       row sum, P as bf16 into a 128B-swizzled smem tile; then O row from
+//       TMEM, normalise, store bf16 to un-shifted, cropped image coordinates.
+//
+// Everything is synchronised with mbarriers; the tensor pipe, the softmax
+// warps and the loads of the next pairs overlap.
+#pragma once
+#include "swin_common.cuh"
+
+namespace swin {
+namespace tc {
+
+constexpr int WS = 7;
+constexpr int N = 49;
+constexpr int kStages = 4;          // smem stages, one PAIR of tiles each
+constexpr int kSlots = 3;           // accumulator slots == softmax warpgroups
+constexpr int kThreads = 512;       // 4 control warps + 3 x 4 softmax warps
+constexpr int kProducerWarps = 3;
+constexpr int kTileBytes = 64 * 64;       // 64 rows x 32 bf16
+constexpr int kPTileBytes = 64 * 128;     // 64 rows x 64 bf16
+constexpr int kStageBytes = 6 * kTileBytes;  // q0 q1 k0 k1 v0 v1
+constexpr int kSlotCols = 96;       // S: 64 columns (56 used), O: 32 columns
+constexpr float kLog2e = 1.4426950408889634f;
+
+// ---- PTX wrappers -----------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+
+// D[tmem] (+)= A[smem] * B[smem]; issued by ONE thread.
+__device__ __forceinline__ void umma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc),
+      "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrives once every previously issued tcgen05.mma of this thread has completed.
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout): start address >> 4 in
+// [0,14), leading byte offset >> 4 in [16,30), stride byte offset >> 4 in [32,46), version = 1 in
+// [46,48), swizzle mode in [61,64) (2 = 128B, 4 = 64B).
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+         (1ull << 46) | ((uint64_t)layout << 61);
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = BF16 (1 << 7, 1 << 10),
+// b_major bit 16 (1 = MN-major), N >> 3 in [17,23), M >> 4 in [24,29).
+__host__ __device__ constexpr uint32_t instr_desc(int m, int n, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+#define TMEM_LD_X16(taddr, r)                                                                                      \
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];" \
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),  \
+                 "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]) \
+               : "r"(taddr))
+__device__ __forceinline__ uint32_t tmem_ld_x1(uint32_t taddr) {
+  uint32_t r;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr));
+  return r;
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// ---- shared memory map --------------------------------------------------------
+struct SmemMap {
+  uint32_t stages;    // kStages * kStageBytes
+  uint32_t pslots;    // kSlots * 2 * kPTileBytes
+  uint32_t bias;      // nH * 169 floats, already multiplied by log2(e)
+  uint32_t bars;      // mbarriers
+  uint32_t tmem_ptr;
+  uint32_t total;
+};
+__host__ __device__ inline SmemMap smem_map(int nH) {
+  SmemMap m;
+  m.stages = 0;
+  m.pslots = m.stages + kStages * kStageBytes;
+  m.bias = m.pslots + kSlots * 2 * kPTileBytes;
+  m.bars = (m.bias + nH * 169 * 4 + 15) & ~15u;
+  m.tmem_ptr = m.bars + 8 * (2 * kStages + 4 * kSlots);
+  m.total = m.tmem_ptr + 16;
+  return m;
+}
+
+struct TileCoord {
+  int b, wy, wx, h;
+  bool valid;
+};
+__device__ __forceinline__ TileCoord tile_coord(const Problem& p, int tile, int n_tiles) {
+  TileCoord c;
+  c.valid = tile < n_tiles;
+  int t = c.valid ? tile : 0;
+  int win = t / p.nH;
+  c.h = t - win * p.nH;
+  c.wx = win % p.nWx;
+  int r = win / p.nWx;
+  c.wy = r % p.nWy;
+  c.b = r / p.nWy;
+  return c;
+}
+// token (row of the window) -> un-shifted pixel; newcrf_layers.py:220-227 folded into addressing
+__device__ __forceinline__ void token_pixel(const Problem& p, const TileCoord& c, int tok, int& y, int& x) {
+  int i = tok / WS, j = tok - i * WS;
+  y = c.wy * WS + i + p.shift;
+  x = c.wx * WS + j + p.shift;
+  if (y >= p.Hp) y -= p.Hp;
+  if (x >= p.Wp) x -= p.Wp;
+}
+
+// ---- producer: one warp per tensor (q / k / v), both tiles of a pair ----------
+__device__ __forceinline__ void produce_pair(const Problem& p, const __nv_bfloat16* __restrict__ src,
+                                             const __nv_bfloat16* __restrict__ pad, int64_t ps, uint32_t dst_base,
+                                             const TileCoord& c0, const TileCoord& c1, int lane) {
+#pragma unroll 1
+  for (int it = 0; it < (2 * N * 4 + 31) / 32; ++it) {
+    int idx = lane + 32 * it;
+    if (idx >= 2 * N * 4) break;
+    int sel = idx >= N * 4 ? 1 : 0;
+    int rem = idx - sel * N * 4;
+    int tok = rem >> 2, chunk = rem & 3;
+    const TileCoord& c = sel ? c1 : c0;
+    if (!c.valid) continue;
+    int y, x;
+    token_pixel(p, c, tok, y, x);
+    uint32_t dst = dst_base + sel * kTileBytes + tok * 64 + ((chunk ^ ((tok >> 1) & 3)) << 4);
+    int co = c.h * kHeadDim + chunk * 8;
+    if (y < p.H && x < p.W) {
+      cp_async16(dst, src + ((int64_t)(c.b * p.H + y) * p.W + x) * ps + co);
+    } else {
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (pad != nullptr) v = *reinterpret_cast<const uint4*>(pad + co);
+      asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    }
+  }
+}
+
+}  // namespace tc
+}  // namespace swin
