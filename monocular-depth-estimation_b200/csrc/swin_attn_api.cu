@@ -12,6 +12,7 @@ namespace swin {
 static std::atomic<uint64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 static thread_local std::string g_error;
+static long long* g_trace = nullptr;
 
 static int fail(const std::string& msg) {
   g_error = msg;
@@ -74,7 +75,7 @@ int swin_attn_forward(const swin_attn_shape_t* shape, const void* q, const void*
   if (misaligned(q, shape->dtype) || misaligned(k, shape->dtype) || misaligned(v, shape->dtype) || misaligned(o, shape->dtype))
     return fail("q/k/v/o must be aligned to 4 elements");
   p.q = q; p.k = k; p.v = v; p.q_pad = q_pad; p.k_pad = k_pad; p.v_pad = v_pad;
-  p.table = bias_table; p.o = o; p.lse = lse;
+  p.table = bias_table; p.o = o; p.lse = lse; p.trace = g_trace;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_forward_supported(p, shape->dtype);
@@ -154,6 +155,10 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape, const void* q, const 
   if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return fail_cuda("host forward", e);
   return 0;
 }
+
+// Debug hook (not part of the public header): device buffer of >= 16 * pairs-per-CTA int64 that receives
+// clock64 stamps of CTA 0 of the tcgen05 kernel; pass NULL to switch tracing off.
+void swin_attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }
 
 uint64_t swin_attn_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 

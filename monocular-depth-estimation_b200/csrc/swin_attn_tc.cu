@@ -61,8 +61,10 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
       const int pair = blockIdx.x + n * gridDim.x;
       mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
       TileCoord c0 = tile_coord(p, 2 * pair, n_tiles), c1 = tile_coord(p, 2 * pair + 1, n_tiles);
+      if (warp == 0 && lane == 0) TC_TRACE(p, n, 0);
       produce_pair(p, src, pad, ps, sbase + map.stages + s * kStageBytes + which * 2 * kTileBytes, c0, c1, lane);
       cp_async_commit();
+      if (warp == 0 && lane == 0) TC_TRACE(p, n, 1);
       if (n >= 2) {
         cp_async_wait<2>();
         fence_proxy_async();
@@ -88,7 +90,9 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
         if (n < n_local) {
           const int s = n % kStages, a = n % kSlots;
           mbar_wait(bar_full + 8 * s, (n / kStages) & 1);
+          TC_TRACE(p, n, 2);
           mbar_wait(bar_r + 8 * a, ((n / kSlots) & 1) ^ 1);
+          TC_TRACE(p, n, 3);
           tc_fence_after();
           const uint32_t st = sbase + map.stages + s * kStageBytes;
 #pragma unroll
@@ -100,10 +104,12 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
             for (int k = 0; k < 2; ++k) umma_ss(d, qd + 2 * k, kd + 2 * k, idesc_s, k);
           }
           umma_commit(bar_s + 8 * a);
+          TC_TRACE(p, n, 4);
         }
         if (n >= 1) {
           const int m = n - 1, s = m % kStages, a = m % kSlots;
           mbar_wait(bar_p + 8 * a, (m / kSlots) & 1);
+          TC_TRACE(p, m, 5);
           tc_fence_after();
           const uint32_t st = sbase + map.stages + s * kStageBytes;
 #pragma unroll
@@ -116,6 +122,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
           }
           umma_commit(bar_o + 8 * a);
           umma_commit(bar_empty + 8 * s);
+          TC_TRACE(p, m, 6);
         }
       }
     }
@@ -157,14 +164,18 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
       }
       const float* brow = bias + c.h * 169 + base_i;
 
+      const bool tr = q == 0 && lane == 0;
+      if (tr) TC_TRACE(p, n, 7);
       mbar_wait(bar_s + 8 * g, m & 1);
       tc_fence_after();
+      if (tr) TC_TRACE(p, n, 8);
       uint32_t r[N + 15];
       TMEM_LD_X16(taddr, (r + 0));
       TMEM_LD_X16(taddr + 16, (r + 16));
       TMEM_LD_X16(taddr + 32, (r + 32));
       r[48] = tmem_ld_x1(taddr + 48);
       tmem_ld_wait();
+      if (tr) TC_TRACE(p, n, 9);
 
       float mx = -INFINITY;
 #pragma unroll
@@ -196,18 +207,22 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
         const uint32_t dst = p_row + ((ch ^ (row & 7)) << 4);
         asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
       }
+      if (tr) TC_TRACE(p, n, 10);
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(bar_p + 8 * g);
+      if (tr) TC_TRACE(p, n, 11);
 
       mbar_wait(bar_o + 8 * g, m & 1);
       tc_fence_after();
+      if (tr) TC_TRACE(p, n, 12);
       uint32_t o[32];
       TMEM_LD_X16(taddr + 64, (o + 0));
       TMEM_LD_X16(taddr + 80, (o + 16));
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bar_r + 8 * g);
+      if (tr) TC_TRACE(p, n, 13);
 
       if (c.valid && row < N) {
         const float inv = 1.0f / l;

@@ -131,6 +131,12 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// debug timeline (see swin_attn_debug_set_trace): event e of local pair n of CTA 0
+#define TC_TRACE(p, n, e)                                                        \
+  do {                                                                           \
+    if ((p).trace != nullptr && blockIdx.x == 0) (p).trace[(n) * 16 + (e)] = clock64(); \
+  } while (0)
+
 // ---- shared memory map --------------------------------------------------------
 struct SmemMap {
   uint32_t stages;    // kStages * kStageBytes

@@ -30,6 +30,7 @@ struct Problem {
   void* dk;
   void* dv;
   float* d_table;
+  long long* trace;    // debug: per-pair clock64 stamps of CTA 0 (tcgen05 kernel), or null
   int B, H, W, Hp, Wp, nH, C, ws, shift;
   int nWy, nWx;        // windows per column / row of the padded image
   int64_t q_ps, k_ps, v_ps, o_ps;

@@ -224,7 +224,8 @@ def test_full_model_depth_metrics_vs_reference_golden(golden, mode):
           f"ours-vs-reference-bf16 {ours_vs_ref:.3e}; abs_rel {err['abs_rel']:.5f}/{eref['abs_rel']:.5f}/{g['abs_rel']:.5f} "
           f"rmse {err['rmse']:.4f}/{eref['rmse']:.4f}/{g['rmse']:.4f}")
     assert ours_vs_fp32 < 1.5 * ref_vs_fp32 + 1e-2
-    assert abs(err["abs_rel"] - g["abs_rel"]) < 1.5 * abs(eref["abs_rel"] - g["abs_rel"]) + 1e-3
+    # random weights vs random GT make abs_rel O(7): the 1e-3 budget is applied relative to the metric
+    assert abs(err["abs_rel"] - g["abs_rel"]) / g["abs_rel"] < 1.5 * abs(eref["abs_rel"] - g["abs_rel"]) / g["abs_rel"] + 1e-3
     assert abs(err["rmse"] - g["rmse"]) / g["rmse"] < 1.5 * abs(eref["rmse"] - g["rmse"]) / g["rmse"] + 1e-3
 
 

@@ -1,0 +1,82 @@
+#!/usr/bin/env python
+"""Window-attention microbench (BASELINE.json configs[4]): the fused op on the stage grids of
+NewCRFs Swin-L at batch 8, shifted and unshifted, forward (and backward with --bwd), both kernel
+families.  Prints one JSON line per case; inputs are larger than L2 or L2 is flushed between
+launches (--flush).
+
+    python tools/attn_microbench.py [--iters 20] [--bwd] [--only NAME] [--flush]
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+from mde_b200 import _lib, ops  # noqa: E402
+
+# name: (B, H, W, nH, ws, external_v)
+SHAPES = {
+    "enc_s0_352x1216": (8, 88, 304, 6, 7, False), "enc_s1_352x1216": (8, 44, 152, 12, 7, False),
+    "enc_s2_352x1216": (8, 22, 76, 24, 7, False), "enc_s3_352x1216": (8, 11, 38, 48, 7, False),
+    "crf0_352x1216": (8, 88, 304, 4, 7, True), "crf1_352x1216": (8, 44, 152, 8, 7, True),
+    "crf2_352x1216": (8, 22, 76, 16, 7, True), "crf3_352x1216": (8, 11, 38, 32, 7, True),
+    "enc_s0_480x640": (8, 120, 160, 6, 7, False), "enc_s2_480x640": (8, 30, 40, 24, 7, False),
+    "oda_ws12_s0": (8, 96, 96, 6, 12, False), "oda_ws12_s2": (8, 24, 24, 24, 12, False),
+}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--bwd", action="store_true")
+    ap.add_argument("--only", default=None)
+    ap.add_argument("--impl", default="both", choices=["both", "auto", "simt"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--flush", action="store_true", default=True)
+    args = ap.parse_args()
+    dev = torch.device("cuda")
+    dt = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    hbm = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(
+        os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    impls = {"auto": _lib.IMPL_AUTO, "simt": _lib.IMPL_SIMT}
+    if args.impl != "both":
+        impls = {args.impl: impls[args.impl]}
+    for name, (b, h, w, nh, ws, ext) in SHAPES.items():
+        if args.only and args.only not in name:
+            continue
+        c = nh * 32
+        g = torch.Generator(device=dev).manual_seed(0)
+        packed = torch.randn(b, h, w, (2 if ext else 3) * c, device=dev, generator=g).to(dt)
+        v = torch.randn(b, h, w, c, device=dev, generator=g).to(dt) if ext else None
+        table = 0.02 * torch.randn((2 * ws - 1) ** 2, nh, device=dev, generator=g)
+        pad = (0.1 * torch.randn(packed.shape[-1], device=dev, generator=g)).to(dt)
+        for shift in (0, ws // 2):
+            for iname, impl in impls.items():
+                def run():
+                    return torch.ops.swin_attn.fwd(packed, v, table, pad, None, ws, shift, nh, 32 ** -0.5, False, impl, None)
+                for _ in range(3):
+                    run()
+                ms = 0.0
+                for _ in range(args.iters):
+                    if args.flush:
+                        flush.zero_()
+                    a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    run()
+                    e.record()
+                    torch.cuda.synchronize()
+                    ms += a.elapsed_time(e)
+                ms /= args.iters
+                nbytes = 4 * b * h * w * c * packed.element_size()
+                hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
+                flops = 4 * b * hp * wp * ws * ws * c
+                print(json.dumps({"case": name, "shift": shift, "impl": iname, "dtype": args.dtype, "us": round(ms * 1e3, 2),
+                                  "GBps": round(nbytes / ms / 1e6, 1), "hbm_frac": round(nbytes / ms / 1e6 / hbm, 4),
+                                  "TFLOPs": round(flops / ms / 1e9, 2), "MB": round(nbytes / 1e6, 1)}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
