@@ -78,7 +78,8 @@ typedef struct {
 } swin_attn_shape_t;
 
 /* Forward.  o: (B,H,W,C) un-shifted & cropped.  lse (nullable): fp32
- * (B,Hp,Wp,nH) log-sum-exp of every query row, kept for the backward. */
+ * (B,Hp,Wp,nH) log-sum-exp of every query row, kept for the backward; entries of
+ * padding tokens (y >= H or x >= W) are unspecified. */
 int swin_attn_forward(const swin_attn_shape_t* shape,
                       const void* q, const void* k, const void* v,
                       const void* q_pad, const void* k_pad, const void* v_pad,

@@ -4,7 +4,53 @@
 namespace swin {
 namespace tc {
 
-__global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, int n_tiles) {
+// stage layout (bytes): q0 0, q1 4096 | k0 8192, k1 8192+3584 | v0 16384, v1 20480
+__device__ __forceinline__ uint32_t q_off(int t) { return t * kTileBytes; }
+__device__ __forceinline__ uint32_t k_off(int t) { return 2 * kTileBytes + t * kKTile1; }
+__device__ __forceinline__ uint32_t v_off(int t) { return 4 * kTileBytes + t * kTileBytes; }
+
+// One window of one tensor: 1 box (un-shifted) or the 4 parts of a shifted window.
+template <bool kShifted>
+__device__ __forceinline__ void load_window(const CUtensorMap* maps, uint32_t dst, uint32_t bar, const Problem& p,
+                                            const TileCoord& c) {
+  const int ch = c.h * kHeadDim;
+  if (!kShifted) {
+    tma_load_4d(dst, maps, bar, ch, c.wx * WS, c.wy * WS, c.b);
+  } else {
+    // token (i, j) sits at ((wy*7 + i + 3) mod Hp, (wx*7 + j + 3) mod Wp): rows/cols [0,4) never wrap,
+    // rows/cols [4,7) start at wy*7 + 7, which wraps to 0 in the last window row/column.
+    const int xa = c.wx * WS + kShift, ya = c.wy * WS + kShift;
+    const int xb = c.wx == p.nWx - 1 ? 0 : c.wx * WS + WS, yb = c.wy == p.nWy - 1 ? 0 : c.wy * WS + WS;
+    tma_load_4d(dst, maps + 1, bar, ch, xa, ya, c.b);             // i<4,  j<4  -> rows [0,16)
+    tma_load_4d(dst + 16 * 64, maps + 2, bar, ch, xa, yb, c.b);   // i>=4, j<4  -> rows [16,28)
+    tma_load_4d(dst + 28 * 64, maps + 3, bar, ch, xb, ya, c.b);   // i<4,  j>=4 -> rows [28,40)
+    tma_load_4d(dst + 40 * 64, maps + 4, bar, ch, xb, yb, c.b);   // i>=4, j>=4 -> rows [40,49)
+  }
+}
+
+template <bool kPerm>
+struct Patterns {
+  uint64_t rowp[WS], colp[WS];   // tokens (as tile-row bits) of window row i / window column j
+};
+template <bool kPerm>
+__device__ __forceinline__ uint64_t pattern_row(int i) {
+  uint64_t m = 0;
+#pragma unroll
+  for (int j = 0; j < WS; ++j) m |= 1ull << token_row<kPerm>(i, j);
+  return m;
+}
+template <bool kPerm>
+__device__ __forceinline__ uint64_t pattern_col(int j) {
+  uint64_t m = 0;
+#pragma unroll
+  for (int i = 0; i < WS; ++i) m |= 1ull << token_row<kPerm>(i, j);
+  return m;
+}
+
+template <bool kShifted>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__ TmaMaps maps) {
+  constexpr bool kPerm = kShifted;
   extern __shared__ __align__(1024) unsigned char smem[];
   const SmemMap map = smem_map(p.nH);
   const uint32_t sbase = smem_u32(smem);
@@ -12,8 +58,8 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
   const int n_pairs = (n_tiles + 1) >> 1;
   const int n_local = (n_pairs - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-  const uint32_t bar_full = sbase + map.bars;              // [kStages] producers -> MMA
-  const uint32_t bar_empty = bar_full + 8 * kStages;       // [kStages] MMA -> producers
+  const uint32_t bar_full = sbase + map.bars;              // [kStages] TMA (+ pad helper) -> MMA
+  const uint32_t bar_empty = bar_full + 8 * kStages;       // [kStages] MMA -> producer
   const uint32_t bar_s = bar_empty + 8 * kStages;          // [kSlots]  S ready
   const uint32_t bar_p = bar_s + 8 * kSlots;               // [kSlots]  P written
   const uint32_t bar_o = bar_p + 8 * kSlots;               // [kSlots]  O ready
@@ -23,7 +69,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
   {
     uint4 z = make_uint4(0u, 0u, 0u, 0u);
     uint4* s4 = reinterpret_cast<uint4*>(smem);
-    for (int i = tid; i < (int)(map.bias / 16); i += kThreads) s4[i] = z;   // tiles + P slots (pad rows must be 0)
+    for (int i = tid; i < (int)(map.bias / 16); i += kThreads) s4[i] = z;   // rows TMA never writes must be 0
     float* bias = reinterpret_cast<float*>(smem + map.bias);
     for (int i = tid; i < p.nH * 169; i += kThreads) {
       int h = i / 169, e = i - h * 169;
@@ -31,7 +77,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
     }
     if (tid == 0) {
       for (int i = 0; i < kStages; ++i) {
-        mbar_init(bar_full + 8 * i, kProducerWarps * 32);
+        mbar_init(bar_full + 8 * i, has_pad ? 2 : 1);
         mbar_init(bar_empty + 8 * i, 1);
       }
       for (int i = 0; i < kSlots; ++i) {
@@ -41,6 +87,11 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
         mbar_init(bar_r + 8 * i, 128);
       }
       fence_barrier_init();
+      for (int i = kShifted ? 1 : 0; i < (kShifted ? 5 : 1); ++i) {
+        tma_prefetch_desc(&maps.q[i]);
+        tma_prefetch_desc(&maps.k[i]);
+        tma_prefetch_desc(&maps.v[i]);
+      }
     }
     if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
     fence_proxy_async();
@@ -50,36 +101,48 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
   }
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + map.tmem_ptr);
 
-  if (warp == 0 || warp == 2 || warp == 3) {
-    // ===== producers: warp 0 -> q, warp 2 -> k, warp 3 -> v =====================
-    const int which = warp == 0 ? 0 : warp - 1;
-    const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(which == 0 ? p.q : which == 1 ? p.k : p.v);
-    const __nv_bfloat16* pad = static_cast<const __nv_bfloat16*>(which == 0 ? p.q_pad : which == 1 ? p.k_pad : p.v_pad);
-    const int64_t ps = which == 0 ? p.q_ps : which == 1 ? p.k_ps : p.v_ps;
-    for (int n = 0; n < n_local; ++n) {
-      const int s = n % kStages;
-      const int pair = blockIdx.x + n * gridDim.x;
-      mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
-      TileCoord c0 = tile_coord(p, 2 * pair, n_tiles), c1 = tile_coord(p, 2 * pair + 1, n_tiles);
-      if (warp == 0 && lane == 0) TC_TRACE(p, n, 0);
-      produce_pair(p, src, pad, ps, sbase + map.stages + s * kStageBytes + which * 2 * kTileBytes, c0, c1, lane);
-      cp_async_commit();
-      if (warp == 0 && lane == 0) TC_TRACE(p, n, 1);
-      if (n >= 2) {
-        cp_async_wait<2>();
-        fence_proxy_async();
-        mbar_arrive(bar_full + 8 * ((n - 2) % kStages));
+  if (warp == 0) {
+    // ===== TMA producer (one thread) ==========================================
+    if (lane == 0) {
+      for (int n = 0; n < n_local; ++n) {
+        const int s = n % kStages;
+        const int pair = blockIdx.x + n * gridDim.x;
+        mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
+        TC_TRACE(p, n, 0);
+        const uint32_t st = sbase + map.stages + s * kStageBytes, bar = bar_full + 8 * s;
+        TileCoord c[2] = {tile_coord(p, 2 * pair, n_tiles), tile_coord(p, 2 * pair + 1, n_tiles)};
+        mbar_expect_tx(bar, ((int)c[0].valid + (int)c[1].valid) * 3 * kBoxBytes);
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+          if (!c[t].valid) continue;
+          load_window<kShifted>(maps.q, st + q_off(t), bar, p, c[t]);
+          load_window<kShifted>(maps.k, st + k_off(t), bar, p, c[t]);
+          load_window<kShifted>(maps.v, st + v_off(t), bar, p, c[t]);
+        }
+        TC_TRACE(p, n, 1);
       }
     }
-    if (n_local >= 2) {
-      cp_async_wait<1>();
-      fence_proxy_async();
-      mbar_arrive(bar_full + 8 * ((n_local - 2) % kStages));
-    }
-    if (n_local >= 1) {
-      cp_async_wait<0>();
-      fence_proxy_async();
-      mbar_arrive(bar_full + 8 * ((n_local - 1) % kStages));
+    __syncwarp();
+  } else if (warp == 2) {
+    // ===== pad helper: row 49 of the K and V tiles <- k_pad / v_pad of the tile's head ==========
+    if (has_pad) {
+      const int t = (lane >> 3) & 1, isv = (lane >> 2) & 1, chunk = lane & 3;
+      const __nv_bfloat16* padv = static_cast<const __nv_bfloat16*>(isv ? p.v_pad : p.k_pad);
+      for (int n = 0; n < n_local; ++n) {
+        const int s = n % kStages;
+        const int pair = blockIdx.x + n * gridDim.x;
+        mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
+        if (lane < 16) {
+          const TileCoord c = tile_coord(p, 2 * pair + t, n_tiles);
+          uint4 v = make_uint4(0u, 0u, 0u, 0u);
+          if (c.valid && padv != nullptr) v = *reinterpret_cast<const uint4*>(padv + c.h * kHeadDim + chunk * 8);
+          const uint32_t dst = sbase + map.stages + s * kStageBytes + (isv ? v_off(t) : k_off(t)) + 49 * 64 + chunk * 16;
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_full + 8 * s);
+      }
     }
   } else if (warp == 1) {
     // ===== MMA issuer (one thread) ==============================================
@@ -98,8 +161,8 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
             const uint32_t d = tmem_base + ((uint32_t)(t * 16) << 16) + a * kSlotCols;
-            const uint64_t qd = smem_desc(st + t * kTileBytes, 16, 512, 4);
-            const uint64_t kd = smem_desc(st + (2 + t) * kTileBytes, 16, 512, 4);
+            const uint64_t qd = smem_desc(st + q_off(t), 16, 512, 4);
+            const uint64_t kd = smem_desc(st + k_off(t), 16, 512, 4);
 #pragma unroll
             for (int k = 0; k < 2; ++k) umma_ss(d, qd + 2 * k, kd + 2 * k, idesc_s, k);
           }
@@ -116,7 +179,7 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
           for (int t = 0; t < 2; ++t) {
             const uint32_t d = tmem_base + ((uint32_t)(t * 16) << 16) + a * kSlotCols + 64;
             const uint64_t pd = smem_desc(sbase + map.pslots + (a * 2 + t) * kPTileBytes, 16, 1024, 2);
-            const uint64_t vd = smem_desc(st + (4 + t) * kTileBytes, 16, 512, 4);
+            const uint64_t vd = smem_desc(st + v_off(t), 16, 512, 4);
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_ss(d, pd + 2 * k, vd + 64 * k, idesc_o, k);
           }
@@ -127,24 +190,24 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
       }
     }
     __syncwarp();
-  } else {
+  } else if (warp >= 4) {
     // ===== softmax / epilogue warpgroups =======================================
     const int g = (warp >> 2) - 1;          // slot owned by this warpgroup
     const int q = warp & 3;                 // TMEM sub-partition
     const int sel = lane >> 4;              // which tile of the pair
     const int row = q * 16 + (lane & 15);   // row of S / O held by this thread
     const int rowc = row < N ? row : N - 1;
-    const int ri = rowc / WS, rj = rowc - ri * WS;
-    const int base_i = ri * 13 + rj + 84;
+    const int ri = row_i<kPerm>(rowc), rj = row_j<kPerm>(rowc);
+    const int base_i = ri * 13 + rj + 84;   // relative_position_index[row, col] = base_i - (ci*13 + cj)
     const float* bias = reinterpret_cast<const float*>(smem + map.bias);
     const float c1 = p.scale * kLog2e;
-    // tokens whose window-row (hb) / window-column (wb) index is >= ws - shift (SW-MSA regions)
+    // SW-MSA regions (newcrf_layers.py:335-345) as tile-row bit sets: window rows / columns >= ws - shift
     uint64_t hb = 0, wb = 0;
-    if (p.shift > 0) {
-      for (int t = 0; t < N; ++t) {
-        if (t / WS >= WS - p.shift) hb |= 1ull << t;
-        if (t % WS >= WS - p.shift) wb |= 1ull << t;
-      }
+    if (kShifted) {
+#pragma unroll
+      for (int i = WS - kShift; i < WS; ++i) hb |= pattern_row<kPerm>(i);
+#pragma unroll
+      for (int j = WS - kShift; j < WS; ++j) wb |= pattern_col<kPerm>(j);
     }
     const uint64_t all = (1ull << N) - 1;
     const uint32_t p_row = sbase + map.pslots + (g * 2 + sel) * kPTileBytes + row * 128;
@@ -155,13 +218,27 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
     for (int n = g; n < n_local; n += kSlots, ++m) {
       const int pair = blockIdx.x + n * gridDim.x;
       const TileCoord c = tile_coord(p, 2 * pair + sel, n_tiles);
-      int y, x;
-      token_pixel(p, c, rowc, y, x);
-      uint64_t masked = 0;
-      if (p.shift > 0) {
-        uint64_t hm = c.wy == p.nWy - 1 ? hb : 0, wm = c.wx == p.nWx - 1 ? wb : 0;
+      // un-shifted pixel of this thread's token
+      int y = c.wy * WS + ri + p.shift, x = c.wx * WS + rj + p.shift;
+      if (y >= p.Hp) y -= p.Hp;
+      if (x >= p.Wp) x -= p.Wp;
+      uint64_t masked = 0, padded = 0;
+      if (kShifted) {
+        const uint64_t hm = c.wy == p.nWy - 1 ? hb : 0, wm = c.wx == p.nWx - 1 ? wb : 0;
         masked = (((hm >> rowc) & 1) ? (~hm & all) : hm) | (((wm >> rowc) & 1) ? (~wm & all) : wm);
       }
+      if (has_pad) {
+        // window rows / columns of this tile that lie in the padding (y >= H or x >= W)
+#pragma unroll
+        for (int i = 0; i < WS; ++i) {
+          int yy = c.wy * WS + i + p.shift, xx = c.wx * WS + i + p.shift;
+          if (yy >= p.Hp) yy -= p.Hp;
+          if (xx >= p.Wp) xx -= p.Wp;
+          if (yy >= p.H) padded |= pattern_row<kPerm>(i);
+          if (xx >= p.W) padded |= pattern_col<kPerm>(i);
+        }
+      }
+      const bool special = __any_sync(0xffffffffu, (masked | padded) != 0);
       const float* brow = bias + c.h * 169 + base_i;
 
       const bool tr = q == 0 && lane == 0;
@@ -173,35 +250,56 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
       TMEM_LD_X16(taddr, (r + 0));
       TMEM_LD_X16(taddr + 16, (r + 16));
       TMEM_LD_X16(taddr + 32, (r + 32));
-      r[48] = tmem_ld_x1(taddr + 48);
+      TMEM_LD_X2(taddr + 48, r[48], r[49]);   // column 49 = q . k_pad (spare K row, see the pad helper)
       tmem_ld_wait();
       if (tr) TC_TRACE(p, n, 9);
 
-      float mx = -INFINITY;
+      float mx = -INFINITY, l = 0.f, pad_sum = 0.f;
+      if (!special) {
 #pragma unroll
-      for (int j = 0; j < N; ++j) {
-        const int cj = (j / WS) * 13 + (j % WS);
-        float t = fmaf(__uint_as_float(r[j]), c1, brow[-cj]);
-        if (p.shift > 0 && ((masked >> j) & 1)) t += -100.0f * kLog2e;
-        r[j] = __float_as_uint(t);
-        mx = fmaxf(mx, t);
-      }
-      float l = 0.f;
+        for (int j = 0; j < N; ++j) {
+          constexpr int dummy = 0;
+          (void)dummy;
+          const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
+          float t = fmaf(__uint_as_float(r[j]), c1, brow[-cj]);
+          r[j] = __float_as_uint(t);
+          mx = fmaxf(mx, t);
+        }
 #pragma unroll
-      for (int j = 0; j < N; ++j) {
-        float e = fast_exp2(__uint_as_float(r[j]) - mx);
-        l += e;
-        r[j] = __float_as_uint(e);
+        for (int j = 0; j < N; ++j) {
+          float e = fast_exp2(__uint_as_float(r[j]) - mx);
+          l += e;
+          r[j] = __float_as_uint(e);
+        }
+      } else {
+        const float a49 = __uint_as_float(r[49]);
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
+          const float acc = ((padded >> j) & 1) ? a49 : __uint_as_float(r[j]);
+          float t = fmaf(acc, c1, brow[-cj]);
+          if ((masked >> j) & 1) t += -100.0f * kLog2e;
+          r[j] = __float_as_uint(t);
+          mx = fmaxf(mx, t);
+        }
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          float e = fast_exp2(__uint_as_float(r[j]) - mx);
+          l += e;
+          if ((padded >> j) & 1) pad_sum += e;
+          r[j] = __float_as_uint(e);
+        }
       }
-      // P row (64 bf16, columns >= 49 zero) into the 128B-swizzled A tile of the PV MMA
+      r[49] = __float_as_uint(pad_sum);   // multiplies v_pad (row 49 of the V tile) in the PV MMA
+      // P row (64 bf16, columns >= 50 zero) into the 128B-swizzled A tile of the PV MMA
 #pragma unroll
       for (int ch = 0; ch < 8; ++ch) {
         uint32_t w[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int j0 = ch * 8 + 2 * e;
-          float lo = j0 < N ? __uint_as_float(r[j0 < N ? j0 : 0]) : 0.f;
-          float hi = j0 + 1 < N ? __uint_as_float(r[j0 + 1 < N ? j0 + 1 : 0]) : 0.f;
+          float lo = j0 <= N ? __uint_as_float(r[j0 <= N ? j0 : 0]) : 0.f;
+          float hi = j0 + 1 <= N ? __uint_as_float(r[j0 + 1 <= N ? j0 + 1 : 0]) : 0.f;
           w[e] = pack_bf16(lo, hi);
         }
         const uint32_t dst = p_row + ((ch ^ (row & 7)) << 4);
@@ -251,12 +349,52 @@ __global__ void __launch_bounds__(kThreads, 1) tc_fwd_kernel(const Problem p, in
 
 }  // namespace tc
 
+// ---- host side ------------------------------------------------------------------
+namespace {
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point: no link-time dependency on libcuda.
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      ptr = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(ptr);
+  }();
+  return fn;
+}
+
+// Tensor map over an image-order (B, H, W, pixel_stride) bf16 tensor whose base pointer already includes
+// the channel offset of q / k / v; box = (32 channels, bx pixels, by rows, 1 image), 64B swizzle,
+// out-of-bounds (the padding the reference adds with F.pad) zero-filled.
+bool encode_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pix_stride, int bx, int by) {
+  // the channel extent is what remains of the pixel after this tensor's channel offset; use C: boxes of
+  // head h start at channel 32 h and never leave [0, C)
+  const cuuint64_t dims[4] = {(cuuint64_t)p.C, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.B};
+  const cuuint64_t strides[3] = {(cuuint64_t)pix_stride * 2, (cuuint64_t)pix_stride * 2 * p.W,
+                                 (cuuint64_t)pix_stride * 2 * p.W * p.H};
+  const cuuint32_t box[4] = {(cuuint32_t)kHeadDim, (cuuint32_t)bx, (cuuint32_t)by, 1u};
+  const cuuint32_t estr[4] = {1u, 1u, 1u, 1u};
+  return encode_fn()(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+}  // namespace
+
 bool tc_forward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
-  // 16-byte cp.async / vector stores: pixel strides multiples of 8 bf16, pointers 16B aligned
+  if (p.shift != 0 && p.shift != tc::kShift) return false;
+  // TMA: 16-byte aligned base pointers and strides; vector stores of o
   if ((p.q_ps | p.k_ps | p.v_ps | p.o_ps) & 7) return false;
   auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
-  if (mis(p.q) || mis(p.k) || mis(p.v) || mis(p.o) || mis(p.q_pad) || mis(p.k_pad) || mis(p.v_pad)) return false;
+  if (mis(p.q) || mis(p.k) || mis(p.v) || mis(p.o) || mis(p.k_pad) || mis(p.v_pad)) return false;
+  if (encode_fn() == nullptr) return false;
   return tc::smem_map(p.nH).total <= 227 * 1024;
 }
 
@@ -268,16 +406,30 @@ cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** er
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms <= 0) sms = 148;
   }
+  tc::TmaMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  const bool shifted = p.shift != 0;
+  const int a = tc::WS - tc::kShift, s = tc::kShift;
+  const int bx[5] = {tc::WS, a, a, s, s}, by[5] = {tc::WS, a, s, a, s};
+  for (int i = shifted ? 1 : 0; i < (shifted ? 5 : 1); ++i) {
+    if (!encode_map(&maps.q[i], p.q, p, p.q_ps, bx[i], by[i]) || !encode_map(&maps.k[i], p.k, p, p.k_ps, bx[i], by[i]) ||
+        !encode_map(&maps.v[i], p.v, p, p.v_ps, bx[i], by[i])) {
+      if (err) *err = "cuTensorMapEncodeTiled failed";
+      return cudaErrorInvalidValue;
+    }
+  }
   const tc::SmemMap map = tc::smem_map(p.nH);
-  cudaError_t e = cudaFuncSetAttribute(tc::tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)map.total);
+  auto kernel = shifted ? tc::tc_fwd_kernel<true> : tc::tc_fwd_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)map.total);
   if (e != cudaSuccess) {
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
     return e;
   }
+  const int has_pad = (p.H != p.Hp || p.W != p.Wp) && (p.k_pad != nullptr || p.v_pad != nullptr) ? 1 : 0;
   const int n_tiles = p.B * p.nWy * p.nWx * p.nH;
   const int n_pairs = (n_tiles + 1) / 2;
   const int grid = n_pairs < sms ? n_pairs : sms;
-  tc::tc_fwd_kernel<<<grid, tc::kThreads, map.total, st>>>(p, n_tiles);
+  kernel<<<grid, tc::kThreads, map.total, st>>>(p, n_tiles, has_pad, maps);
   count_launch();
   return cudaGetLastError();
 }

@@ -1,26 +1,41 @@
-// Shifted-window attention forward for sm_100a: tcgen05 bf16 MMAs with fp32
-// accumulators in tensor memory, one persistent CTA per SM.
+// Shifted-window attention forward for sm_100a: TMA-gathered window tiles, tcgen05 bf16
+// MMAs with fp32 accumulators in tensor memory, one persistent CTA per SM.
 //
-// Tile = one (window, head): Q, K, V are 49 x 32 bf16 (padded to 64 rows in
-// shared memory).  Two tiles form a PAIR that shares TMEM columns: tile 0
-// lives in lanes 0-15 of each 32-lane TMEM sub-partition, tile 1 in lanes
-// 16-31 (an M=64 accumulator occupies 16 lanes per sub-partition), so one
-// `tcgen05.ld.32x32b` hands every thread of a softmax warp one complete row of
-// S -- no cross-lane reduction is needed for the row max / row sum.
+// Tile = one (window, head): Q, K, V are 49 x 32 bf16.  Two tiles form a PAIR that
+// shares TMEM columns: tile 0 lives in lanes 0-15 of each 32-lane TMEM sub-partition,
+// tile 1 in lanes 16-31 (an M=64 accumulator occupies 16 lanes per sub-partition), so
+// one `tcgen05.ld.32x32b` hands every thread of a softmax warp one complete row of S --
+// no cross-lane reduction is needed for the row max / row sum.
 //
-//   producer warps (0,2,3): gather Q,K,V rows straight from the image-order
-//       tensors (pad / cyclic shift / window partition are address arithmetic)
-//       with 16-byte cp.async into 64B-swizzled K-major tiles
+//   producer (warp 0, one thread): the window partition, the cyclic shift and the
+//       right/bottom padding are folded into TMA tensor-map addressing.  A tensor map
+//       over the image-order (B,H,W,channels) tensor with box (32 ch, 7 x, 7 y) lands a
+//       window's 49 rows in a 64B-swizzled K-major tile.  Shifted blocks split every
+//       window at the wrap point into four boxes (4x4, 3x4, 4x3, 3x3 for ws 7 / shift 3)
+//       whose start coordinates wrap modulo the padded extent; their rows are stored
+//       part after part ("permuted" token order, every part on an even row so that the
+//       TMA destination stays 128B-aligned).  Out-of-bounds (padding) elements are
+//       zero-filled by the TMA unit.
+//   pad helper (warp 2): padding tokens are not zero in the reference -- they carry the
+//       Linear bias (newcrf_layers.py:212-217).  All pad tokens of a head share ONE
+//       vector, so it is written once per tile into the spare row 49 of the K and V
+//       tiles: S[:,49] = q . k_pad comes out of the QK^T MMA for free and stands in for
+//       every pad column; P[:,49] = sum of the pad columns' probabilities multiplies
+//       v_pad in the PV MMA.
 //   MMA warp (1), one thread:  S = Q K^T   (M64 N56 K32, SS)  -> TMEM
 //                              O = P V     (M64 N32 K64, SS, V is MN-major)
-//   softmax warpgroups (3 x 4 warps): S row from TMEM, scale + relative
-//       position bias (table staged in smem) + analytic SW-MSA mask, exp2,
-//       row sum, P as bf16 into a 128B-swizzled smem tile; then O row from
-//       TMEM, normalise, store bf16 to un-shifted, cropped image coordinates.
+//   softmax warpgroups (3 x 4 warps): S row from TMEM, scale + relative position bias
+//       (table staged in smem) + analytic SW-MSA mask, exp2, row sum, P as bf16 into a
+//       128B-swizzled smem tile; then O row from TMEM, normalise, store bf16 to
+//       un-shifted, cropped image coordinates.
 //
-// Everything is synchronised with mbarriers; the tensor pipe, the softmax
-// warps and the loads of the next pairs overlap.
+// Everything is synchronised with mbarriers; the tensor pipe, the softmax warps and the
+// loads of the next pairs overlap.
 #pragma once
+#include <cuda.h>
+
+#include <cstring>
+
 #include "swin_common.cuh"
 
 namespace swin {
@@ -28,15 +43,25 @@ namespace tc {
 
 constexpr int WS = 7;
 constexpr int N = 49;
+constexpr int kShift = 3;           // the only non-zero shift served here (ws // 2, as the reference uses)
 constexpr int kStages = 4;          // smem stages, one PAIR of tiles each
 constexpr int kSlots = 3;           // accumulator slots == softmax warpgroups
 constexpr int kThreads = 512;       // 4 control warps + 3 x 4 softmax warps
-constexpr int kProducerWarps = 3;
 constexpr int kTileBytes = 64 * 64;       // 64 rows x 32 bf16
+constexpr int kKTile1 = 56 * 64;          // K tile 1 follows the 56 MMA rows of K tile 0
 constexpr int kPTileBytes = 64 * 128;     // 64 rows x 64 bf16
-constexpr int kStageBytes = 6 * kTileBytes;  // q0 q1 k0 k1 v0 v1
+constexpr int kStageBytes = 6 * kTileBytes;  // q0 q1 | k0 k1 | v0 v1
+constexpr int kBoxBytes = N * 64;         // bytes one tile of one tensor receives from TMA
 constexpr int kSlotCols = 96;       // S: 64 columns (56 used), O: 32 columns
 constexpr float kLog2e = 1.4426950408889634f;
+
+// Tensor maps of one launch: [0] = whole window (7x7); [1..4] = the four parts of a
+// shifted window, (x extent, y extent) = (4,4) (4,3) (3,4) (3,3), stored at rows 0/16/28/40.
+struct TmaMaps {
+  CUtensorMap q[5];
+  CUtensorMap k[5];
+  CUtensorMap v[5];
+};
 
 // ---- PTX wrappers -----------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -131,13 +156,30 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// ---- TMA ------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// box of tensor map `map` at (channel, x, y, image) -> shared memory, completion on `bar`
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+#define TMEM_LD_X2(taddr, r0, r1) \
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(taddr))
+
 // debug timeline (see swin_attn_debug_set_trace): event e of local pair n of CTA 0
 #define TC_TRACE(p, n, e)                                                        \
   do {                                                                           \
     if ((p).trace != nullptr && blockIdx.x == 0) (p).trace[(n) * 16 + (e)] = clock64(); \
   } while (0)
 
-// ---- shared memory map --------------------------------------------------------
+// ---- shared memory map ----------------------------------------------------------
 struct SmemMap {
   uint32_t stages;    // kStages * kStageBytes
   uint32_t pslots;    // kSlots * 2 * kPTileBytes
@@ -157,6 +199,7 @@ __host__ __device__ inline SmemMap smem_map(int nH) {
   return m;
 }
 
+// ---- tiles and token order --------------------------------------------------------
 struct TileCoord {
   int b, wy, wx, h;
   bool valid;
@@ -173,40 +216,24 @@ __device__ __forceinline__ TileCoord tile_coord(const Problem& p, int tile, int 
   c.b = r / p.nWy;
   return c;
 }
-// token (row of the window) -> un-shifted pixel; newcrf_layers.py:220-227 folded into addressing
-__device__ __forceinline__ void token_pixel(const Problem& p, const TileCoord& c, int tok, int& y, int& x) {
-  int i = tok / WS, j = tok - i * WS;
-  y = c.wy * WS + i + p.shift;
-  x = c.wx * WS + j + p.shift;
-  if (y >= p.Hp) y -= p.Hp;
-  if (x >= p.Wp) x -= p.Wp;
-}
 
-// ---- producer: one warp per tensor (q / k / v), both tiles of a pair ----------
-__device__ __forceinline__ void produce_pair(const Problem& p, const __nv_bfloat16* __restrict__ src,
-                                             const __nv_bfloat16* __restrict__ pad, int64_t ps, uint32_t dst_base,
-                                             const TileCoord& c0, const TileCoord& c1, int lane) {
-#pragma unroll 1
-  for (int it = 0; it < (2 * N * 4 + 31) / 32; ++it) {
-    int idx = lane + 32 * it;
-    if (idx >= 2 * N * 4) break;
-    int sel = idx >= N * 4 ? 1 : 0;
-    int rem = idx - sel * N * 4;
-    int tok = rem >> 2, chunk = rem & 3;
-    const TileCoord& c = sel ? c1 : c0;
-    if (!c.valid) continue;
-    int y, x;
-    token_pixel(p, c, tok, y, x);
-    uint32_t dst = dst_base + sel * kTileBytes + tok * 64 + ((chunk ^ ((tok >> 1) & 3)) << 4);
-    int co = c.h * kHeadDim + chunk * 8;
-    if (y < p.H && x < p.W) {
-      cp_async16(dst, src + ((int64_t)(c.b * p.H + y) * p.W + x) * ps + co);
-    } else {
-      uint4 v = make_uint4(0u, 0u, 0u, 0u);
-      if (pad != nullptr) v = *reinterpret_cast<const uint4*>(pad + co);
-      asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-    }
-  }
+// Row r of a tile <-> token (i, j) of the window.  Natural order for un-shifted blocks;
+// for shifted blocks the four TMA parts follow one another:
+//   rows [0,16): i<4, j<4   [16,28): i>=4, j<4   [28,40): i<4, j>=4   [40,49): i>=4, j>=4
+template <bool kPerm>
+__host__ __device__ constexpr int row_i(int r) {
+  if (!kPerm) return r / WS;
+  return r < 16 ? r / 4 : r < 28 ? 4 + (r - 16) / 4 : r < 40 ? (r - 28) / 3 : 4 + (r - 40) / 3;
+}
+template <bool kPerm>
+__host__ __device__ constexpr int row_j(int r) {
+  if (!kPerm) return r % WS;
+  return r < 16 ? r % 4 : r < 28 ? (r - 16) % 4 : r < 40 ? 4 + (r - 28) % 3 : 4 + (r - 40) % 3;
+}
+template <bool kPerm>
+__host__ __device__ constexpr int token_row(int i, int j) {
+  if (!kPerm) return i * WS + j;
+  return j < 4 ? (i < 4 ? i * 4 + j : 16 + (i - 4) * 4 + j) : (i < 4 ? 28 + i * 3 + (j - 4) : 40 + (i - 4) * 3 + (j - 4));
 }
 
 }  // namespace tc

@@ -59,7 +59,9 @@ def test_forward_matches_oracle(case, dtype, impl):
     tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
     assert got.shape == (b, h, w, c) and got.dtype == dtype
     assert rel_err(got.float(), want) < tol
-    assert rel_err(lse, want_lse) < (1e-5 if dtype == torch.float32 else 2e-2)
+    # lse of padding tokens (rows >= H, cols >= W) is unspecified: their outputs are cropped and the backward
+    # only accepts window-aligned inputs
+    assert rel_err(lse[:, :h, :w], want_lse[:, :h, :w]) < (1e-5 if dtype == torch.float32 else 2e-2)
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
