@@ -21,10 +21,15 @@ __device__ __forceinline__ void load_window(const CUtensorMap* maps, uint32_t ds
     // rows/cols [4,7) start at wy*7 + 7, which wraps to 0 in the last window row/column.
     const int xa = c.wx * WS + kShift, ya = c.wy * WS + kShift;
     const int xb = c.wx == p.nWx - 1 ? 0 : c.wx * WS + WS, yb = c.wy == p.nWy - 1 ? 0 : c.wy * WS + WS;
-    tma_load_4d(dst, maps + 1, bar, ch, xa, ya, c.b);             // i<4,  j<4  -> rows [0,16)
-    tma_load_4d(dst + 16 * 64, maps + 2, bar, ch, xa, yb, c.b);   // i>=4, j<4  -> rows [16,28)
-    tma_load_4d(dst + 28 * 64, maps + 3, bar, ch, xb, ya, c.b);   // i<4,  j>=4 -> rows [28,40)
-    tma_load_4d(dst + 40 * 64, maps + 4, bar, ch, xb, yb, c.b);   // i>=4, j>=4 -> rows [40,49)
+    if (c.wy == p.nWy - 1) {
+      tma_load_4d(dst, maps + 1, bar, ch, xa, ya, c.b);             // i<4,  j<4  -> rows [0,16)
+      tma_load_4d(dst + 16 * 64, maps + 2, bar, ch, xa, yb, c.b);   // i>=4, j<4  -> rows [16,28)
+      tma_load_4d(dst + 28 * 64, maps + 3, bar, ch, xb, ya, c.b);   // i<4,  j>=4 -> rows [28,40)
+      tma_load_4d(dst + 40 * 64, maps + 4, bar, ch, xb, yb, c.b);   // i>=4, j>=4 -> rows [40,49)
+    } else {                                                        // the 7 rows are contiguous in y
+      tma_load_4d(dst, maps + 5, bar, ch, xa, ya, c.b);             // j<4  -> rows [0,28)
+      tma_load_4d(dst + 28 * 64, maps + 6, bar, ch, xb, ya, c.b);   // j>=4 -> rows [28,49)
+    }
   }
 }
 
@@ -67,17 +72,28 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
 
   // ---- one-time setup -------------------------------------------------------
   {
-    uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    uint4* s4 = reinterpret_cast<uint4*>(smem);
-    for (int i = tid; i < (int)(map.bias / 16); i += kThreads) s4[i] = z;   // rows TMA never writes must be 0
+    // Rows the TMA boxes never write: K rows 49-55 feed S columns that are never read unless the pad helper
+    // filled row 49; V rows 49-63 are multiplied by P columns that are 0 and must therefore be finite.
+    for (int i = tid; i < kStages * 2 * 15 * 4; i += kThreads) {
+      const int chunk = i & 3, rr = (i >> 2) % 15, t = ((i >> 2) / 15) & 1, s = (i >> 2) / 30;
+      const uint32_t st = map.stages + s * kStageBytes;
+      *reinterpret_cast<uint4*>(smem + st + v_off(t) + (49 + rr) * 64 + chunk * 16) = make_uint4(0u, 0u, 0u, 0u);
+      if (rr < 7) *reinterpret_cast<uint4*>(smem + st + k_off(t) + (49 + rr) * 64 + chunk * 16) = make_uint4(0u, 0u, 0u, 0u);
+    }
     float* bias = reinterpret_cast<float*>(smem + map.bias);
     for (int i = tid; i < p.nH * 169; i += kThreads) {
-      int h = i / 169, e = i - h * 169;
-      bias[i] = p.table[e * p.nH + h] * kLog2e;
+      const int e = i / p.nH, h = i - e * p.nH;
+      bias[h * 169 + e] = p.table[i] * kLog2e;
+    }
+    for (int i = tid; i < 2 * p.nH * 4; i += kThreads) {   // 16-byte chunks of k_pad | v_pad
+      const int isv = i >= p.nH * 4, j = i - isv * p.nH * 4;
+      const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(isv ? p.v_pad : p.k_pad);
+      *reinterpret_cast<uint4*>(smem + map.padv + i * 16) =
+          src != nullptr ? *reinterpret_cast<const uint4*>(src + j * 8) : make_uint4(0u, 0u, 0u, 0u);
     }
     if (tid == 0) {
       for (int i = 0; i < kStages; ++i) {
-        mbar_init(bar_full + 8 * i, has_pad ? 2 : 1);
+        mbar_init(bar_full + 8 * i, has_pad ? 4 : 2);
         mbar_init(bar_empty + 8 * i, 1);
       }
       for (int i = 0; i < kSlots; ++i) {
@@ -87,7 +103,7 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
         mbar_init(bar_r + 8 * i, 128);
       }
       fence_barrier_init();
-      for (int i = kShifted ? 1 : 0; i < (kShifted ? 5 : 1); ++i) {
+      for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
         tma_prefetch_desc(&maps.q[i]);
         tma_prefetch_desc(&maps.k[i]);
         tma_prefetch_desc(&maps.v[i]);
@@ -101,101 +117,92 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
   }
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + map.tmem_ptr);
 
-  if (warp == 0) {
-    // ===== TMA producer (one thread) ==========================================
-    if (lane == 0) {
-      for (int n = 0; n < n_local; ++n) {
-        const int s = n % kStages;
-        const int pair = blockIdx.x + n * gridDim.x;
+  if (warp == 0 || warp == 3) {
+    // ===== TMA producers: warp 0 -> tile 0 of every pair, warp 3 -> tile 1 =====================
+    // lane 0 issues the TMA boxes; with padding, lanes 8-15 copy k_pad / v_pad of the tile's head into the
+    // spare row 49 of the K / V tile (see swin_attn_tc.cuh).
+    const int t = warp == 0 ? 0 : 1;
+    const int isv = (lane >> 2) & 1, chunk = lane & 3;
+    TileIter it;
+    it.init(p, 2 * (int)blockIdx.x + t, 2 * (int)gridDim.x);
+    for (int n = 0; n < n_local; ++n, it.next(p)) {
+      const int s = n % kStages;
+      const uint32_t st = sbase + map.stages + s * kStageBytes, bar = bar_full + 8 * s;
+      const TileCoord c = it.coord(n_tiles);
+      if (lane == 0) {
         mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
-        TC_TRACE(p, n, 0);
-        const uint32_t st = sbase + map.stages + s * kStageBytes, bar = bar_full + 8 * s;
-        TileCoord c[2] = {tile_coord(p, 2 * pair, n_tiles), tile_coord(p, 2 * pair + 1, n_tiles)};
-        mbar_expect_tx(bar, ((int)c[0].valid + (int)c[1].valid) * 3 * kBoxBytes);
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          if (!c[t].valid) continue;
-          load_window<kShifted>(maps.q, st + q_off(t), bar, p, c[t]);
-          load_window<kShifted>(maps.k, st + k_off(t), bar, p, c[t]);
-          load_window<kShifted>(maps.v, st + v_off(t), bar, p, c[t]);
+        if (t == 0) TC_TRACE(p, n, 0);
+        if (c.valid) {
+          mbar_expect_tx(bar, 3 * kBoxBytes);
+          load_window<kShifted>(maps.q, st + q_off(t), bar, p, c);
+          load_window<kShifted>(maps.k, st + k_off(t), bar, p, c);
+          load_window<kShifted>(maps.v, st + v_off(t), bar, p, c);
+        } else {
+          mbar_arrive(bar);
         }
-        TC_TRACE(p, n, 1);
+        if (t == 0) TC_TRACE(p, n, 1);
+      }
+      if (has_pad) {
+        __syncwarp();   // lane 0 has seen the stage empty
+        if (lane >= 8 && lane < 16) {
+          const uint4 v = *reinterpret_cast<const uint4*>(smem + map.padv + ((isv * p.nH + c.h) * 4 + chunk) * 16);
+          const uint32_t dst = st + (isv ? v_off(t) : k_off(t)) + 49 * 64 + chunk * 16;
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+          fence_proxy_async();
+        }
+        __syncwarp();
+        if (lane == 8) mbar_arrive(bar);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== S = Q K^T issuer (one thread, 2 instructions per pair) ===============================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = instr_desc(128, 112, 0);
+      for (int n = 0; n < n_local; ++n) {
+        const int s = n % kStages, a = n % kSlots;
+        mbar_wait(bar_full + 8 * s, (n / kStages) & 1);
+        TC_TRACE(p, n, 2);
+        mbar_wait(bar_r + 8 * a, ((n / kSlots) & 1) ^ 1);
+        TC_TRACE(p, n, 3);
+        tc_fence_after();
+        const uint32_t st = sbase + map.stages + s * kStageBytes;
+        const uint32_t d = tmem_base + a * kSlotCols;
+        const uint64_t qd = smem_desc(st + q_off(0), 16, 512, 4);   // 128 rows: q0 | q1
+        const uint64_t kd = smem_desc(st + k_off(0), 16, 512, 4);   // 112 rows: k0 (56) | k1 (56)
+#pragma unroll
+        for (int k = 0; k < 2; ++k) umma_ss(d, qd + 2 * k, kd + 2 * k, idesc_s, k);
+        umma_commit(bar_s + 8 * a);
+        TC_TRACE(p, n, 4);
       }
     }
     __syncwarp();
   } else if (warp == 2) {
-    // ===== pad helper: row 49 of the K and V tiles <- k_pad / v_pad of the tile's head ==========
-    if (has_pad) {
-      const int t = (lane >> 3) & 1, isv = (lane >> 2) & 1, chunk = lane & 3;
-      const __nv_bfloat16* padv = static_cast<const __nv_bfloat16*>(isv ? p.v_pad : p.k_pad);
-      for (int n = 0; n < n_local; ++n) {
-        const int s = n % kStages;
-        const int pair = blockIdx.x + n * gridDim.x;
-        mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
-        if (lane < 16) {
-          const TileCoord c = tile_coord(p, 2 * pair + t, n_tiles);
-          uint4 v = make_uint4(0u, 0u, 0u, 0u);
-          if (c.valid && padv != nullptr) v = *reinterpret_cast<const uint4*>(padv + c.h * kHeadDim + chunk * 8);
-          const uint32_t dst = sbase + map.stages + s * kStageBytes + (isv ? v_off(t) : k_off(t)) + 49 * 64 + chunk * 16;
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-        }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_full + 8 * s);
-      }
-    }
-  } else if (warp == 1) {
-    // ===== MMA issuer (one thread) ==============================================
+    // ===== O = P V issuer (one thread, 4 instructions per pair) =================================
     if (lane == 0) {
-      constexpr uint32_t idesc_s = instr_desc(64, 56, 0);
-      constexpr uint32_t idesc_o = instr_desc(64, 32, 1);
-      for (int n = 0; n <= n_local; ++n) {
-        if (n < n_local) {
-          const int s = n % kStages, a = n % kSlots;
-          mbar_wait(bar_full + 8 * s, (n / kStages) & 1);
-          TC_TRACE(p, n, 2);
-          mbar_wait(bar_r + 8 * a, ((n / kSlots) & 1) ^ 1);
-          TC_TRACE(p, n, 3);
-          tc_fence_after();
-          const uint32_t st = sbase + map.stages + s * kStageBytes;
+      constexpr uint32_t idesc_o = instr_desc(128, 64, 1);
+      for (int m = 0; m < n_local; ++m) {
+        const int s = m % kStages, a = m % kSlots;
+        mbar_wait(bar_p + 8 * a, (m / kSlots) & 1);
+        TC_TRACE(p, m, 5);
+        tc_fence_after();
+        const uint32_t st = sbase + map.stages + s * kStageBytes;
+        const uint32_t d = tmem_base + a * kSlotCols;                // O overwrites the S columns
+        const uint64_t pd = smem_desc(sbase + map.pslots + a * 2 * kPTileBytes, 16, 1024, 2);  // 128 rows: p0 | p1
+        const uint64_t vd = smem_desc(st + v_off(0), kTileBytes, 512, 4);   // N = 64: v0 | v1 one tile apart
 #pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            const uint32_t d = tmem_base + ((uint32_t)(t * 16) << 16) + a * kSlotCols;
-            const uint64_t qd = smem_desc(st + q_off(t), 16, 512, 4);
-            const uint64_t kd = smem_desc(st + k_off(t), 16, 512, 4);
-#pragma unroll
-            for (int k = 0; k < 2; ++k) umma_ss(d, qd + 2 * k, kd + 2 * k, idesc_s, k);
-          }
-          umma_commit(bar_s + 8 * a);
-          TC_TRACE(p, n, 4);
-        }
-        if (n >= 1) {
-          const int m = n - 1, s = m % kStages, a = m % kSlots;
-          mbar_wait(bar_p + 8 * a, (m / kSlots) & 1);
-          TC_TRACE(p, m, 5);
-          tc_fence_after();
-          const uint32_t st = sbase + map.stages + s * kStageBytes;
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            const uint32_t d = tmem_base + ((uint32_t)(t * 16) << 16) + a * kSlotCols + 64;
-            const uint64_t pd = smem_desc(sbase + map.pslots + (a * 2 + t) * kPTileBytes, 16, 1024, 2);
-            const uint64_t vd = smem_desc(st + v_off(t), 16, 512, 4);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) umma_ss(d, pd + 2 * k, vd + 64 * k, idesc_o, k);
-          }
-          umma_commit(bar_o + 8 * a);
-          umma_commit(bar_empty + 8 * s);
-          TC_TRACE(p, m, 6);
-        }
+        for (int k = 0; k < 4; ++k) umma_ss(d, pd + 2 * k, vd + 64 * k, idesc_o, k);
+        umma_commit(bar_o + 8 * a);
+        umma_commit(bar_empty + 8 * s);
+        TC_TRACE(p, m, 6);
       }
     }
     __syncwarp();
   } else if (warp >= 4) {
     // ===== softmax / epilogue warpgroups =======================================
     const int g = (warp >> 2) - 1;          // slot owned by this warpgroup
-    const int q = warp & 3;                 // TMEM sub-partition
-    const int sel = lane >> 4;              // which tile of the pair
-    const int row = q * 16 + (lane & 15);   // row of S / O held by this thread
+    const int q = warp & 3;                 // TMEM sub-partition: lanes 32q .. 32q+31
+    const int sel = q >> 1;                 // which tile of the pair (rows 0-63 / 64-127 of the accumulator)
+    const int row = (q & 1) * 32 + lane;    // row of this tile's S / O held by this thread
     const int rowc = row < N ? row : N - 1;
     const int ri = row_i<kPerm>(rowc), rj = row_j<kPerm>(rowc);
     const int base_i = ri * 13 + rj + 84;   // relative_position_index[row, col] = base_i - (ci*13 + cj)
@@ -212,12 +219,14 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
     const uint64_t all = (1ull << N) - 1;
     const uint32_t p_row = sbase + map.pslots + (g * 2 + sel) * kPTileBytes + row * 128;
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + g * kSlotCols;
+    const uint32_t s_addr = taddr + sel * 56, o_addr = taddr + sel * 32;   // this tile's columns of S and of O
+    TileIter it;
+    it.init(p, 2 * ((int)blockIdx.x + g * (int)gridDim.x) + sel, 2 * kSlots * (int)gridDim.x);
     __nv_bfloat16* out = static_cast<__nv_bfloat16*>(p.o);
 
     int m = 0;
-    for (int n = g; n < n_local; n += kSlots, ++m) {
-      const int pair = blockIdx.x + n * gridDim.x;
-      const TileCoord c = tile_coord(p, 2 * pair + sel, n_tiles);
+    for (int n = g; n < n_local; n += kSlots, ++m, it.next(p)) {
+      const TileCoord c = it.coord(n_tiles);
       // un-shifted pixel of this thread's token
       int y = c.wy * WS + ri + p.shift, x = c.wx * WS + rj + p.shift;
       if (y >= p.Hp) y -= p.Hp;
@@ -241,16 +250,16 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
       const bool special = __any_sync(0xffffffffu, (masked | padded) != 0);
       const float* brow = bias + c.h * 169 + base_i;
 
-      const bool tr = q == 0 && lane == 0;
+      const bool tr = q == 0 && lane == 0;   // timeline of tile 0, row 0
       if (tr) TC_TRACE(p, n, 7);
       mbar_wait(bar_s + 8 * g, m & 1);
       tc_fence_after();
       if (tr) TC_TRACE(p, n, 8);
       uint32_t r[N + 15];
-      TMEM_LD_X16(taddr, (r + 0));
-      TMEM_LD_X16(taddr + 16, (r + 16));
-      TMEM_LD_X16(taddr + 32, (r + 32));
-      TMEM_LD_X2(taddr + 48, r[48], r[49]);   // column 49 = q . k_pad (spare K row, see the pad helper)
+      TMEM_LD_X16(s_addr, (r + 0));
+      TMEM_LD_X16(s_addr + 16, (r + 16));
+      TMEM_LD_X16(s_addr + 32, (r + 32));
+      TMEM_LD_X2(s_addr + 48, r[48], r[49]);   // column 49 = q . k_pad (spare K row, see the pad helper)
       tmem_ld_wait();
       if (tr) TC_TRACE(p, n, 9);
 
@@ -258,8 +267,6 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
       if (!special) {
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          constexpr int dummy = 0;
-          (void)dummy;
           const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
           float t = fmaf(__uint_as_float(r[j]), c1, brow[-cj]);
           r[j] = __float_as_uint(t);
@@ -315,8 +322,8 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
       tc_fence_after();
       if (tr) TC_TRACE(p, n, 12);
       uint32_t o[32];
-      TMEM_LD_X16(taddr + 64, (o + 0));
-      TMEM_LD_X16(taddr + 80, (o + 16));
+      TMEM_LD_X16(o_addr, (o + 0));
+      TMEM_LD_X16(o_addr + 16, (o + 16));
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bar_r + 8 * g);
@@ -410,8 +417,8 @@ cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** er
   memset(&maps, 0, sizeof(maps));
   const bool shifted = p.shift != 0;
   const int a = tc::WS - tc::kShift, s = tc::kShift;
-  const int bx[5] = {tc::WS, a, a, s, s}, by[5] = {tc::WS, a, s, a, s};
-  for (int i = shifted ? 1 : 0; i < (shifted ? 5 : 1); ++i) {
+  const int bx[7] = {tc::WS, a, a, s, s, a, s}, by[7] = {tc::WS, a, s, a, s, tc::WS, tc::WS};
+  for (int i = shifted ? 1 : 0; i < (shifted ? 7 : 1); ++i) {
     if (!encode_map(&maps.q[i], p.q, p, p.q_ps, bx[i], by[i]) || !encode_map(&maps.k[i], p.k, p, p.k_ps, bx[i], by[i]) ||
         !encode_map(&maps.v[i], p.v, p, p.v_ps, bx[i], by[i])) {
       if (err) *err = "cuTensorMapEncodeTiled failed";

@@ -1,11 +1,10 @@
 // Shifted-window attention forward for sm_100a: TMA-gathered window tiles, tcgen05 bf16
 // MMAs with fp32 accumulators in tensor memory, one persistent CTA per SM.
 //
-// Tile = one (window, head): Q, K, V are 49 x 32 bf16.  Two tiles form a PAIR that
-// shares TMEM columns: tile 0 lives in lanes 0-15 of each 32-lane TMEM sub-partition,
-// tile 1 in lanes 16-31 (an M=64 accumulator occupies 16 lanes per sub-partition), so
-// one `tcgen05.ld.32x32b` hands every thread of a softmax warp one complete row of S --
-// no cross-lane reduction is needed for the row max / row sum.
+// Tile = one (window, head): Q, K, V are 49 x 32 bf16.  Two tiles form a PAIR that is
+// stacked along M: tile 0 owns TMEM lanes 0-63, tile 1 lanes 64-127, and one
+// `tcgen05.ld.32x32b` hands every thread of a softmax warp one complete row of S -- no
+// cross-lane reduction is needed for the row max / row sum.
 //
 //   producer (warp 0, one thread): the window partition, the cyclic shift and the
 //       right/bottom padding are folded into TMA tensor-map addressing.  A tensor map
@@ -22,8 +21,10 @@
 //       tiles: S[:,49] = q . k_pad comes out of the QK^T MMA for free and stands in for
 //       every pad column; P[:,49] = sum of the pad columns' probabilities multiplies
 //       v_pad in the PV MMA.
-//   MMA warp (1), one thread:  S = Q K^T   (M64 N56 K32, SS)  -> TMEM
-//                              O = P V     (M64 N32 K64, SS, V is MN-major)
+//   MMA warp (1), one thread: both tiles of a pair go through ONE accumulator (M = 128):
+//       S = [Q0;Q1] [K0;K1]^T (M128 N112 K32): tile t's scores are rows 64t.., columns 56t..
+//       O = [P0;P1] [V0|V1]   (M128 N64 K64, V MN-major): tile t's output is rows 64t.., cols 32t..
+//       (the off-diagonal blocks are computed and ignored; the tensor pipe is far from the bound)
 //   softmax warpgroups (3 x 4 warps): S row from TMEM, scale + relative position bias
 //       (table staged in smem) + analytic SW-MSA mask, exp2, row sum, P as bf16 into a
 //       128B-swizzled smem tile; then O row from TMEM, normalise, store bf16 to
@@ -52,15 +53,17 @@ constexpr int kKTile1 = 56 * 64;          // K tile 1 follows the 56 MMA rows of
 constexpr int kPTileBytes = 64 * 128;     // 64 rows x 64 bf16
 constexpr int kStageBytes = 6 * kTileBytes;  // q0 q1 | k0 k1 | v0 v1
 constexpr int kBoxBytes = N * 64;         // bytes one tile of one tensor receives from TMA
-constexpr int kSlotCols = 96;       // S: 64 columns (56 used), O: 32 columns
+constexpr int kSlotCols = 128;      // S: 112 columns (2 x 56); O (64 columns) reuses them once S has been read
 constexpr float kLog2e = 1.4426950408889634f;
 
-// Tensor maps of one launch: [0] = whole window (7x7); [1..4] = the four parts of a
-// shifted window, (x extent, y extent) = (4,4) (4,3) (3,4) (3,3), stored at rows 0/16/28/40.
+// Tensor maps of one launch: [0] = whole window (7x7); [1..4] = the four parts of a shifted
+// window that wraps in y, (x extent, y extent) = (4,4) (4,3) (3,4) (3,3), stored at rows
+// 0/16/28/40; [5..6] = the two parts (4,7) (3,7) of a shifted window that does not wrap in y,
+// stored at rows 0/28 (same token order).
 struct TmaMaps {
-  CUtensorMap q[5];
-  CUtensorMap k[5];
-  CUtensorMap v[5];
+  CUtensorMap q[7];
+  CUtensorMap k[7];
+  CUtensorMap v[7];
 };
 
 // ---- PTX wrappers -----------------------------------------------------------
@@ -184,6 +187,7 @@ struct SmemMap {
   uint32_t stages;    // kStages * kStageBytes
   uint32_t pslots;    // kSlots * 2 * kPTileBytes
   uint32_t bias;      // nH * 169 floats, already multiplied by log2(e)
+  uint32_t padv;      // k_pad then v_pad of every head (bf16, 64 B per head), zeros when absent
   uint32_t bars;      // mbarriers
   uint32_t tmem_ptr;
   uint32_t total;
@@ -193,7 +197,8 @@ __host__ __device__ inline SmemMap smem_map(int nH) {
   m.stages = 0;
   m.pslots = m.stages + kStages * kStageBytes;
   m.bias = m.pslots + kSlots * 2 * kPTileBytes;
-  m.bars = (m.bias + nH * 169 * 4 + 15) & ~15u;
+  m.padv = (m.bias + nH * 169 * 4 + 15) & ~15u;
+  m.bars = m.padv + 2 * nH * 64;
   m.tmem_ptr = m.bars + 8 * (2 * kStages + 4 * kSlots);
   m.total = m.tmem_ptr + 16;
   return m;
@@ -216,6 +221,31 @@ __device__ __forceinline__ TileCoord tile_coord(const Problem& p, int tile, int 
   c.b = r / p.nWy;
   return c;
 }
+
+
+// Tile index t -> (image, window row, window column, head) and t += stride without divisions.
+struct TileIter {
+  int b, wy, wx, h;     // current tile
+  int db, dwy, dwx, dh; // mixed-radix digits of the stride
+  int tile, stride;
+  __device__ __forceinline__ void init(const Problem& p, int first, int step) {
+    tile = first; stride = step;
+    int win = first / p.nH; h = first - win * p.nH;
+    wx = win % p.nWx; int r = win / p.nWx; wy = r % p.nWy; b = r / p.nWy;
+    int dw = step / p.nH; dh = step - dw * p.nH;
+    dwx = dw % p.nWx; int dr = dw / p.nWx; dwy = dr % p.nWy; db = dr / p.nWy;
+  }
+  __device__ __forceinline__ void next(const Problem& p) {
+    tile += stride;
+    h += dh; int c = h >= p.nH; h -= c ? p.nH : 0;
+    wx += dwx + c; c = wx >= p.nWx; wx -= c ? p.nWx : 0;
+    wy += dwy + c; c = wy >= p.nWy; wy -= c ? p.nWy : 0;
+    b += db + c;
+  }
+  __device__ __forceinline__ TileCoord coord(int n_tiles) const {
+    TileCoord c; c.b = b; c.wy = wy; c.wx = wx; c.h = h; c.valid = tile < n_tiles; return c;
+  }
+};
 
 // Row r of a tile <-> token (i, j) of the window.  Natural order for un-shifted blocks;
 // for shifted blocks the four TMA parts follow one another:
