@@ -4,7 +4,7 @@
 namespace swin {
 namespace tc {
 
-// stage layout (bytes): q0 0, q1 4096 | k0 8192, k1 8192+3584 | v0 16384, v1 20480
+// stage layout (bytes): q0 0, q1 4096 | k0 8192, k1 8192+3584 | v0 16384, v1 20480 | ones 24576
 __device__ __forceinline__ uint32_t q_off(int t) { return t * kTileBytes; }
 __device__ __forceinline__ uint32_t k_off(int t) { return 2 * kTileBytes + t * kKTile1; }
 __device__ __forceinline__ uint32_t v_off(int t) { return 4 * kTileBytes + t * kTileBytes; }
@@ -59,7 +59,8 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
   extern __shared__ __align__(1024) unsigned char smem[];
   const SmemMap map = smem_map(p.nH);
   const uint32_t sbase = smem_u32(smem);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler as well
   const int n_pairs = (n_tiles + 1) >> 1;
   const int n_local = (n_pairs - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
@@ -79,6 +80,12 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
       const uint32_t st = map.stages + s * kStageBytes;
       *reinterpret_cast<uint4*>(smem + st + v_off(t) + (49 + rr) * 64 + chunk * 16) = make_uint4(0u, 0u, 0u, 0u);
       if (rr < 7) *reinterpret_cast<uint4*>(smem + st + k_off(t) + (49 + rr) * 64 + chunk * 16) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    // ones tile of every stage: element 0 of each key row is 1.0 (bf16), so column 64 of O = sum_j P[i, j]
+    for (int i = tid; i < kStages * 64 * 4; i += kThreads) {
+      const int chunk = i & 3, rr = (i >> 2) & 63, s = i >> 8;
+      const uint4 v = make_uint4(chunk == 0 ? 0x00003f80u : 0u, 0u, 0u, 0u);
+      *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytes + 6 * kTileBytes + rr * 64 + ((chunk ^ ((rr >> 1) & 3)) << 4)) = v;
     }
     float* bias = reinterpret_cast<float*>(smem + map.bias);
     for (int i = tid; i < p.nH * 169; i += kThreads) {
@@ -129,8 +136,8 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
       const int s = n % kStages;
       const uint32_t st = sbase + map.stages + s * kStageBytes, bar = bar_full + 8 * s;
       const TileCoord c = it.coord(n_tiles);
-      if (lane == 0) {
-        mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
+      mbar_wait(bar_empty + 8 * s, ((n / kStages) & 1) ^ 1);
+      if (elect_one()) {
         if (t == 0) TC_TRACE(p, n, 0);
         if (c.valid) {
           mbar_expect_tx(bar, 3 * kBoxBytes);
@@ -143,7 +150,7 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
         if (t == 0) TC_TRACE(p, n, 1);
       }
       if (has_pad) {
-        __syncwarp();   // lane 0 has seen the stage empty
+        __syncwarp();
         if (lane >= 8 && lane < 16) {
           const uint4 v = *reinterpret_cast<const uint4*>(smem + map.padv + ((isv * p.nH + c.h) * 4 + chunk) * 16);
           const uint32_t dst = st + (isv ? v_off(t) : k_off(t)) + 49 * 64 + chunk * 16;
@@ -156,47 +163,46 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
     }
   } else if (warp == 1) {
     // ===== S = Q K^T issuer (one thread, 2 instructions per pair) ===============================
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = instr_desc(128, 112, 0);
-      for (int n = 0; n < n_local; ++n) {
-        const int s = n % kStages, a = n % kSlots;
-        mbar_wait(bar_full + 8 * s, (n / kStages) & 1);
-        TC_TRACE(p, n, 2);
-        mbar_wait(bar_r + 8 * a, ((n / kSlots) & 1) ^ 1);
+    constexpr uint32_t idesc_s = instr_desc(128, 112, 0);
+    for (int n = 0; n < n_local; ++n) {
+      const int s = n % kStages, a = n % kSlots;
+      mbar_wait(bar_full + 8 * s, (n / kStages) & 1);
+      mbar_wait(bar_r + 8 * a, ((n / kSlots) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t st = sbase + map.stages + s * kStageBytes;
+      const uint32_t d = tmem_base + a * kSlotCols;
+      const uint64_t qd = smem_desc(st + q_off(0), 16, 512, 4);   // 128 rows: q0 | q1
+      const uint64_t kd = smem_desc(st + k_off(0), 16, 512, 4);   // 112 rows: k0 (56) | k1 (56)
+      if (elect_one()) {
         TC_TRACE(p, n, 3);
-        tc_fence_after();
-        const uint32_t st = sbase + map.stages + s * kStageBytes;
-        const uint32_t d = tmem_base + a * kSlotCols;
-        const uint64_t qd = smem_desc(st + q_off(0), 16, 512, 4);   // 128 rows: q0 | q1
-        const uint64_t kd = smem_desc(st + k_off(0), 16, 512, 4);   // 112 rows: k0 (56) | k1 (56)
 #pragma unroll
         for (int k = 0; k < 2; ++k) umma_ss(d, qd + 2 * k, kd + 2 * k, idesc_s, k);
         umma_commit(bar_s + 8 * a);
         TC_TRACE(p, n, 4);
       }
+      __syncwarp();
     }
-    __syncwarp();
   } else if (warp == 2) {
     // ===== O = P V issuer (one thread, 4 instructions per pair) =================================
-    if (lane == 0) {
-      constexpr uint32_t idesc_o = instr_desc(128, 64, 1);
-      for (int m = 0; m < n_local; ++m) {
-        const int s = m % kStages, a = m % kSlots;
-        mbar_wait(bar_p + 8 * a, (m / kSlots) & 1);
+    constexpr uint32_t idesc_o = instr_desc(128, 96, 1);
+    for (int m = 0; m < n_local; ++m) {
+      const int s = m % kStages, a = m % kSlots;
+      mbar_wait(bar_p + 8 * a, (m / kSlots) & 1);
+      tc_fence_after();
+      const uint32_t st = sbase + map.stages + s * kStageBytes;
+      const uint32_t d = tmem_base + a * kSlotCols;                // O overwrites the S columns
+      const uint64_t pd = smem_desc(sbase + map.pslots + a * 2 * kPTileBytes, 16, 1024, 2);  // 128 rows: p0 | p1
+      const uint64_t vd = smem_desc(st + v_off(0), kTileBytes, 512, 4);   // N = 96: v0 | v1 | ones, one tile apart
+      if (elect_one()) {
         TC_TRACE(p, m, 5);
-        tc_fence_after();
-        const uint32_t st = sbase + map.stages + s * kStageBytes;
-        const uint32_t d = tmem_base + a * kSlotCols;                // O overwrites the S columns
-        const uint64_t pd = smem_desc(sbase + map.pslots + a * 2 * kPTileBytes, 16, 1024, 2);  // 128 rows: p0 | p1
-        const uint64_t vd = smem_desc(st + v_off(0), kTileBytes, 512, 4);   // N = 64: v0 | v1 one tile apart
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_ss(d, pd + 2 * k, vd + 64 * k, idesc_o, k);
         umma_commit(bar_o + 8 * a);
         umma_commit(bar_empty + 8 * s);
         TC_TRACE(p, m, 6);
       }
+      __syncwarp();
     }
-    __syncwarp();
   } else if (warp >= 4) {
     // ===== softmax / epilogue warpgroups =======================================
     const int g = (warp >> 2) - 1;          // slot owned by this warpgroup
@@ -207,7 +213,8 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
     const int ri = row_i<kPerm>(rowc), rj = row_j<kPerm>(rowc);
     const int base_i = ri * 13 + rj + 84;   // relative_position_index[row, col] = base_i - (ci*13 + cj)
     const float* bias = reinterpret_cast<const float*>(smem + map.bias);
-    const float c1 = p.scale * kLog2e;
+    const float2 c1 = make_float2(p.scale * kLog2e, p.scale * kLog2e);
+    const uint64_t all = (1ull << N) - 1;
     // SW-MSA regions (newcrf_layers.py:335-345) as tile-row bit sets: window rows / columns >= ws - shift
     uint64_t hb = 0, wb = 0;
     if (kShifted) {
@@ -216,7 +223,22 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
 #pragma unroll
       for (int j = WS - kShift; j < WS; ++j) wb |= pattern_col<kPerm>(j);
     }
-    const uint64_t all = (1ull << N) - 1;
+    // Padding tokens (y >= H or x >= W) can only occur in the last two window rows / columns: their
+    // tile-row bit sets, for window row nWy-2 ([0]) and nWy-1 ([1]), likewise for columns.
+    uint64_t pad_y[2] = {0, 0}, pad_x[2] = {0, 0};
+    if (has_pad) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+#pragma unroll
+        for (int i = 0; i < WS; ++i) {
+          int yy = (p.nWy - 2 + e) * WS + i + p.shift, xx = (p.nWx - 2 + e) * WS + i + p.shift;
+          if (yy >= p.Hp) yy -= p.Hp;
+          if (xx >= p.Wp) xx -= p.Wp;
+          if (yy >= p.H && p.nWy - 2 + e >= 0) pad_y[e] |= pattern_row<kPerm>(i);
+          if (xx >= p.W && p.nWx - 2 + e >= 0) pad_x[e] |= pattern_col<kPerm>(i);
+        }
+      }
+    }
     const uint32_t p_row = sbase + map.pslots + (g * 2 + sel) * kPTileBytes + row * 128;
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + g * kSlotCols;
     const uint32_t s_addr = taddr + sel * 56, o_addr = taddr + sel * 32;   // this tile's columns of S and of O
@@ -227,27 +249,16 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
     int m = 0;
     for (int n = g; n < n_local; n += kSlots, ++m, it.next(p)) {
       const TileCoord c = it.coord(n_tiles);
-      // un-shifted pixel of this thread's token
-      int y = c.wy * WS + ri + p.shift, x = c.wx * WS + rj + p.shift;
-      if (y >= p.Hp) y -= p.Hp;
-      if (x >= p.Wp) x -= p.Wp;
       uint64_t masked = 0, padded = 0;
       if (kShifted) {
         const uint64_t hm = c.wy == p.nWy - 1 ? hb : 0, wm = c.wx == p.nWx - 1 ? wb : 0;
         masked = (((hm >> rowc) & 1) ? (~hm & all) : hm) | (((wm >> rowc) & 1) ? (~wm & all) : wm);
       }
-      if (has_pad) {
-        // window rows / columns of this tile that lie in the padding (y >= H or x >= W)
-#pragma unroll
-        for (int i = 0; i < WS; ++i) {
-          int yy = c.wy * WS + i + p.shift, xx = c.wx * WS + i + p.shift;
-          if (yy >= p.Hp) yy -= p.Hp;
-          if (xx >= p.Wp) xx -= p.Wp;
-          if (yy >= p.H) padded |= pattern_row<kPerm>(i);
-          if (xx >= p.W) padded |= pattern_col<kPerm>(i);
-        }
-      }
-      const bool special = __any_sync(0xffffffffu, (masked | padded) != 0);
+      if (has_pad)
+        padded = (c.wy == p.nWy - 1 ? pad_y[1] : c.wy == p.nWy - 2 ? pad_y[0] : 0) |
+                 (c.wx == p.nWx - 1 ? pad_x[1] : c.wx == p.nWx - 2 ? pad_x[0] : 0);
+      // every row of a tile with a mask / padding has masked columns, so this is warp-uniform
+      const bool special = (kShifted && (c.wy == p.nWy - 1 || c.wx == p.nWx - 1)) || padded != 0;
       const float* brow = bias + c.h * 169 + base_i;
 
       const bool tr = q == 0 && lane == 0;   // timeline of tile 0, row 0
@@ -259,24 +270,27 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
       TMEM_LD_X16(s_addr, (r + 0));
       TMEM_LD_X16(s_addr + 16, (r + 16));
       TMEM_LD_X16(s_addr + 32, (r + 32));
-      TMEM_LD_X2(s_addr + 48, r[48], r[49]);   // column 49 = q . k_pad (spare K row, see the pad helper)
+      TMEM_LD_X2(s_addr + 48, r[48], r[49]);   // column 49 = q . k_pad (spare K row, see the producers)
       tmem_ld_wait();
       if (tr) TC_TRACE(p, n, 9);
 
-      float mx = -INFINITY, l = 0.f, pad_sum = 0.f;
+      // pass 1: t = S * scale*log2e + bias*log2e (+ mask), row max.  Packed fp32x2 FMAs.
+      float mx = -INFINITY;
       if (!special) {
 #pragma unroll
-        for (int j = 0; j < N; ++j) {
-          const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
-          float t = fmaf(__uint_as_float(r[j]), c1, brow[-cj]);
-          r[j] = __float_as_uint(t);
-          mx = fmaxf(mx, t);
+        for (int j = 0; j < N - 1; j += 2) {
+          const int cj0 = row_i<kPerm>(j) * 13 + row_j<kPerm>(j), cj1 = row_i<kPerm>(j + 1) * 13 + row_j<kPerm>(j + 1);
+          const float2 t = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), c1,
+                                      make_float2(brow[-cj0], brow[-cj1]));
+          r[j] = __float_as_uint(t.x);
+          r[j + 1] = __float_as_uint(t.y);
+          mx = fmaxf(mx, fmaxf(t.x, t.y));
         }
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-          float e = fast_exp2(__uint_as_float(r[j]) - mx);
-          l += e;
-          r[j] = __float_as_uint(e);
+        {
+          const int cj = row_i<kPerm>(N - 1) * 13 + row_j<kPerm>(N - 1);
+          const float t = fmaf(__uint_as_float(r[N - 1]), c1.x, brow[-cj]);
+          r[N - 1] = __float_as_uint(t);
+          mx = fmaxf(mx, t);
         }
       } else {
         const float a49 = __uint_as_float(r[49]);
@@ -284,33 +298,41 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
         for (int j = 0; j < N; ++j) {
           const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
           const float acc = ((padded >> j) & 1) ? a49 : __uint_as_float(r[j]);
-          float t = fmaf(acc, c1, brow[-cj]);
+          float t = fmaf(acc, c1.x, brow[-cj]);
           if ((masked >> j) & 1) t += -100.0f * kLog2e;
           r[j] = __float_as_uint(t);
           mx = fmaxf(mx, t);
         }
+      }
+      r[49] = __float_as_uint(-INFINITY);   // exp2 -> 0
+      // pass 2: p = exp2(t - max) evaluated as bf16x2 (P feeds a bf16 MMA anyway); the row sum comes out of
+      // the PV MMA through the ones column, i.e. it is the sum of exactly the rounded values in P.
+      const float2 nmx = make_float2(-mx, -mx);
+      uint32_t w[25];
+#pragma unroll
+      for (int e = 0; e < 25; ++e) {
+        const float2 x = __fadd2_rn(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), nmx);
+        w[e] = ex2_bf16x2(pack_bf16(x.x, x.y));
+      }
+      if (special && padded != 0) {
+        // pad columns: their V rows are zero (TMA fill); move their probability mass to column 49 (x v_pad)
+        float pad_sum = 0.f;
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          float e = fast_exp2(__uint_as_float(r[j]) - mx);
-          l += e;
-          if ((padded >> j) & 1) pad_sum += e;
-          r[j] = __float_as_uint(e);
+          if ((padded >> j) & 1) {
+            pad_sum += __uint_as_float((j & 1) ? (w[j >> 1] & 0xffff0000u) : (w[j >> 1] << 16));
+            w[j >> 1] &= (j & 1) ? 0x0000ffffu : 0xffff0000u;
+          }
         }
+        w[24] = (w[24] & 0x0000ffffu) | (pack_bf16(0.f, pad_sum) & 0xffff0000u);
       }
-      r[49] = __float_as_uint(pad_sum);   // multiplies v_pad (row 49 of the V tile) in the PV MMA
       // P row (64 bf16, columns >= 50 zero) into the 128B-swizzled A tile of the PV MMA
 #pragma unroll
       for (int ch = 0; ch < 8; ++ch) {
-        uint32_t w[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int j0 = ch * 8 + 2 * e;
-          float lo = j0 <= N ? __uint_as_float(r[j0 <= N ? j0 : 0]) : 0.f;
-          float hi = j0 + 1 <= N ? __uint_as_float(r[j0 + 1 <= N ? j0 + 1 : 0]) : 0.f;
-          w[e] = pack_bf16(lo, hi);
-        }
         const uint32_t dst = p_row + ((ch ^ (row & 7)) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+        const uint32_t w0 = 4 * ch < 25 ? w[4 * ch < 25 ? 4 * ch : 0] : 0u, w1 = 4 * ch + 1 < 25 ? w[4 * ch + 1 < 25 ? 4 * ch + 1 : 0] : 0u;
+        const uint32_t w2 = 4 * ch + 2 < 25 ? w[4 * ch + 2 < 25 ? 4 * ch + 2 : 0] : 0u, w3 = 4 * ch + 3 < 25 ? w[4 * ch + 3 < 25 ? 4 * ch + 3 : 0] : 0u;
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
       }
       if (tr) TC_TRACE(p, n, 10);
       fence_proxy_async();
@@ -318,29 +340,37 @@ tc_fwd_kernel(const Problem p, int n_tiles, int has_pad, const __grid_constant__
       mbar_arrive(bar_p + 8 * g);
       if (tr) TC_TRACE(p, n, 11);
 
+      // un-shifted pixel of this thread's token (computed while the PV MMA runs)
+      int y = c.wy * WS + ri + p.shift, x = c.wx * WS + rj + p.shift;
+      if (y >= p.Hp) y -= p.Hp;
+      if (x >= p.Wp) x -= p.Wp;
+
       mbar_wait(bar_o + 8 * g, m & 1);
       tc_fence_after();
       if (tr) TC_TRACE(p, n, 12);
       uint32_t o[32];
       TMEM_LD_X16(o_addr, (o + 0));
       TMEM_LD_X16(o_addr + 16, (o + 16));
+      const float l = __uint_as_float(tmem_ld_x1(taddr + 64));   // row sum: P x ones column
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bar_r + 8 * g);
       if (tr) TC_TRACE(p, n, 13);
 
       if (c.valid && row < N) {
-        const float inv = 1.0f / l;
+        const float inv1 = 1.0f / l;
+        const float2 inv = make_float2(inv1, inv1);
         if (y < p.H && x < p.W) {
           __nv_bfloat16* dst = out + ((int64_t)(c.b * p.H + y) * p.W + x) * p.o_ps + c.h * kHeadDim;
 #pragma unroll
           for (int ch = 0; ch < 4; ++ch) {
-            uint4 v;
-            v.x = pack_bf16(__uint_as_float(o[8 * ch + 0]) * inv, __uint_as_float(o[8 * ch + 1]) * inv);
-            v.y = pack_bf16(__uint_as_float(o[8 * ch + 2]) * inv, __uint_as_float(o[8 * ch + 3]) * inv);
-            v.z = pack_bf16(__uint_as_float(o[8 * ch + 4]) * inv, __uint_as_float(o[8 * ch + 5]) * inv);
-            v.w = pack_bf16(__uint_as_float(o[8 * ch + 6]) * inv, __uint_as_float(o[8 * ch + 7]) * inv);
-            *reinterpret_cast<uint4*>(dst + 8 * ch) = v;
+            uint32_t v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 s2 = __fmul2_rn(make_float2(__uint_as_float(o[8 * ch + 2 * e]), __uint_as_float(o[8 * ch + 2 * e + 1])), inv);
+              v[e] = pack_bf16(s2.x, s2.y);
+            }
+            *reinterpret_cast<uint4*>(dst + 8 * ch) = make_uint4(v[0], v[1], v[2], v[3]);
           }
         }
         if (p.lse != nullptr)

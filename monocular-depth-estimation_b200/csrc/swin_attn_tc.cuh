@@ -23,7 +23,8 @@
 //       v_pad in the PV MMA.
 //   MMA warp (1), one thread: both tiles of a pair go through ONE accumulator (M = 128):
 //       S = [Q0;Q1] [K0;K1]^T (M128 N112 K32): tile t's scores are rows 64t.., columns 56t..
-//       O = [P0;P1] [V0|V1]   (M128 N64 K64, V MN-major): tile t's output is rows 64t.., cols 32t..
+//       O = [P0;P1] [V0|V1|1] (M128 N96 K64, V MN-major): tile t's output is rows 64t.., cols 32t..;
+//           column 64 multiplies a constant ones tile and so holds the softmax row sums
 //       (the off-diagonal blocks are computed and ignored; the tensor pipe is far from the bound)
 //   softmax warpgroups (3 x 4 warps): S row from TMEM, scale + relative position bias
 //       (table staged in smem) + analytic SW-MSA mask, exp2, row sum, P as bf16 into a
@@ -51,7 +52,7 @@ constexpr int kThreads = 512;       // 4 control warps + 3 x 4 softmax warps
 constexpr int kTileBytes = 64 * 64;       // 64 rows x 32 bf16
 constexpr int kKTile1 = 56 * 64;          // K tile 1 follows the 56 MMA rows of K tile 0
 constexpr int kPTileBytes = 64 * 128;     // 64 rows x 64 bf16
-constexpr int kStageBytes = 6 * kTileBytes;  // q0 q1 | k0 k1 | v0 v1
+constexpr int kStageBytes = 7 * kTileBytes;  // q0 q1 | k0 k1 | v0 v1 | ones (row-sum column of the PV MMA)
 constexpr int kBoxBytes = N * 64;         // bytes one tile of one tensor receives from TMA
 constexpr int kSlotCols = 128;      // S: 112 columns (2 x 56); O (64 columns) reuses them once S has been read
 constexpr float kLog2e = 1.4426950408889634f;
@@ -79,10 +80,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(bar), "r"(parity)
+      : "r"(bar), "r"(parity), "r"(0x989680u)   // suspend-time hint: sleep in hardware instead of spinning
       : "memory");
   return ok != 0;
 }
@@ -153,10 +154,25 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
+// exp2 of two bf16 at once (one MUFU op for two probabilities; P is consumed as bf16 by the PV MMA)
+__device__ __forceinline__ uint32_t ex2_bf16x2(uint32_t x) {
+  uint32_t y;
+  asm("ex2.approx.ftz.bf16x2 %0, %1;" : "=r"(y) : "r"(x));
+  return y;
+}
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+
+// One elected lane of a fully converged warp.  Issuing TMA / tcgen05 instructions from `if (elect_one())`
+// inside warp-uniform control flow lets the compiler keep their operands in uniform registers; issuing them
+// from `if (lane == 0)` costs a R2UR broadcast loop (~100 cycles) per instruction.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 
 // ---- TMA ------------------------------------------------------------------------
