@@ -106,7 +106,16 @@ int swin_attn_backward(const swin_attn_shape_t* shape, const void* q, const void
   p.q = q; p.k = k; p.v = v; p.o_in = o; p.d_o = d_o; p.lse = const_cast<float*>(lse);
   p.table = bias_table; p.dq = dq; p.dk = dk; p.dv = dv; p.d_table = d_bias_table;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
-  cudaError_t e = launch_simt_backward(p, shape->dtype, static_cast<cudaStream_t>(stream));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_backward_supported(p, shape->dtype);
+  if (shape->impl == SWIN_ATTN_IMPL_TCGEN05 && !want_tc) return fail("tcgen05 backward does not support this shape/dtype");
+  if (want_tc) {
+    const char* why = nullptr;
+    cudaError_t e = launch_tc_backward(p, st, &why);
+    if (e != cudaSuccess) return why ? fail(std::string("tcgen05 backward: ") + why) : fail_cuda("tcgen05 backward launch", e);
+    return 0;
+  }
+  cudaError_t e = launch_simt_backward(p, shape->dtype, st);
   if (e != cudaSuccess) return fail_cuda("backward launch", e);
   return 0;
 }
@@ -165,7 +174,7 @@ uint64_t swin_attn_launch_count(void) { return g_launches.load(std::memory_order
 int swin_attn_uses_tcgen05(const swin_attn_shape_t* shape, int backward) {
   Problem p;
   if (make_problem(shape, p)) return 0;
-  if (backward) return 0;
+  if (backward) return shape->impl != SWIN_ATTN_IMPL_SIMT && tc_backward_supported(p, shape->dtype) ? 1 : 0;
   return shape->impl != SWIN_ATTN_IMPL_SIMT && tc_forward_supported(p, shape->dtype) ? 1 : 0;
 }
 

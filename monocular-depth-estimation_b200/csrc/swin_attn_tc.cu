@@ -409,7 +409,10 @@ EncodeTiledFn encode_fn() {
 // Tensor map over an image-order (B, H, W, pixel_stride) bf16 tensor whose base pointer already includes
 // the channel offset of q / k / v; box = (32 channels, bx pixels, by rows, 1 image), 64B swizzle,
 // out-of-bounds (the padding the reference adds with F.pad) zero-filled.
-bool encode_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pix_stride, int bx, int by) {
+}  // namespace
+
+bool tc::encode_window_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pix_stride, int bx, int by) {
+  if (encode_fn() == nullptr) return false;
   // the channel extent is what remains of the pixel after this tensor's channel offset; use C: boxes of
   // head h start at channel 32 h and never leave [0, C)
   const cuuint64_t dims[4] = {(cuuint64_t)p.C, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.B};
@@ -422,7 +425,7 @@ bool encode_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pi
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-}  // namespace
+bool tc::tma_available() { return encode_fn() != nullptr; }
 
 bool tc_forward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
@@ -449,8 +452,8 @@ cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** er
   const int a = tc::WS - tc::kShift, s = tc::kShift;
   const int bx[7] = {tc::WS, a, a, s, s, a, s}, by[7] = {tc::WS, a, s, a, s, tc::WS, tc::WS};
   for (int i = shifted ? 1 : 0; i < (shifted ? 7 : 1); ++i) {
-    if (!encode_map(&maps.q[i], p.q, p, p.q_ps, bx[i], by[i]) || !encode_map(&maps.k[i], p.k, p, p.k_ps, bx[i], by[i]) ||
-        !encode_map(&maps.v[i], p.v, p, p.v_ps, bx[i], by[i])) {
+    if (!tc::encode_window_map(&maps.q[i], p.q, p, p.q_ps, bx[i], by[i]) || !tc::encode_window_map(&maps.k[i], p.k, p, p.k_ps, bx[i], by[i]) ||
+        !tc::encode_window_map(&maps.v[i], p.v, p, p.v_ps, bx[i], by[i])) {
       if (err) *err = "cuTensorMapEncodeTiled failed";
       return cudaErrorInvalidValue;
     }

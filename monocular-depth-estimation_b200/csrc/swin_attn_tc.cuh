@@ -133,9 +133,10 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
          (1ull << 46) | ((uint64_t)layout << 61);
 }
 // Instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = BF16 (1 << 7, 1 << 10),
-// b_major bit 16 (1 = MN-major), N >> 3 in [17,23), M >> 4 in [24,29).
-__host__ __device__ constexpr uint32_t instr_desc(int m, int n, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+// a_major bit 15 / b_major bit 16 (1 = MN-major), N >> 3 in [17,23), M >> 4 in [24,29).
+__host__ __device__ constexpr uint32_t instr_desc(int m, int n, int b_mn_major, int a_mn_major = 0) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 #define TMEM_LD_X16(taddr, r)                                                                                      \
@@ -185,6 +186,19 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
       "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
+}
+// shared memory box -> tensor map `map` at (channel, x, y, image); out-of-bounds elements are not written
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(map), "r"(src),
+               "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all bulk groups of this thread have finished READING their shared-memory source
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void named_barrier(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
@@ -281,6 +295,13 @@ __host__ __device__ constexpr int token_row(int i, int j) {
   if (!kPerm) return i * WS + j;
   return j < 4 ? (i < 4 ? i * 4 + j : 16 + (i - 4) * 4 + j) : (i < 4 ? 28 + i * 3 + (j - 4) : 40 + (i - 4) * 3 + (j - 4));
 }
+
+// Host: tensor map over an image-order (B, H, W, pix_stride) bf16 tensor, box (32 ch, bx, by, 1), 64B swizzle
+// (swin_attn_tc.cu).  The seven box shapes of a launch, indexed like TmaMaps.
+bool encode_window_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pix_stride, int bx, int by);
+bool tma_available();
+constexpr int kBoxX[7] = {WS, WS - kShift, WS - kShift, kShift, kShift, WS - kShift, kShift};
+constexpr int kBoxY[7] = {WS, WS - kShift, kShift, WS - kShift, kShift, WS, WS};
 
 }  // namespace tc
 }  // namespace swin

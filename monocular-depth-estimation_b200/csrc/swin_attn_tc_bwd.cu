@@ -1,0 +1,535 @@
+// tcgen05 backward of the shifted-window attention (bf16, ws 7, shift 0 / 3) for sm_100a.
+//
+// Recomputes the probabilities from (q, k, lse) instead of storing them (the reference's autograd
+// keeps S-sized tensors per block).  Per (window, head) tile, N = 49, d = 32:
+//
+//   S  = Q K^T          dP = dO V^T                      (tensor pipe, phase 1)
+//   P  = exp2(S c + bias - lse)    delta_i = sum_j P_ij dP_ij   (= rowsum(dO o O); O is never read)
+//   dS = P o (dP - delta)                                 (registers, one thread per query row)
+//   dV = P^T dO    dK = scale dS^T Q    dQ = scale dS K   (tensor pipe, phase 2)
+//   dTable[rel_index(i, j), h] += dS_ij                   (tensor pipe: T += dS I, see below)
+//
+// HBM traffic per tile: read q, k, v, dO (4 x 49 x 64 B) + lse, write dq, dk, dv (3 x 49 x 64 B).
+//
+// Work decomposition: one CTA = one JOB = (head h, contiguous range of windows).  Consecutive CTAs
+// are consecutive heads over the SAME windows, so the 128-byte lines two heads share are fetched
+// at about the same time.  Two windows of the job form a PAIR stacked along M (as in the forward):
+// tile t owns TMEM lanes 64t .. 64t+63.
+//
+//   phase 1 (M128 N112 K32, twice):  S  = [Q0;Q1]  [K0;K1]^T     dP = [dO0;dO1] [V0;V1]^T
+//   phase 2 (M128 N64  K64, 4 times): every product pairs an A operand built from the bf16 P / dS
+//       rows the softmax threads wrote ONCE (row i, 128 B, 128B swizzle) with a B operand that is one
+//       of the TMA-landed tiles read MN-major:
+//         dV = [P0^T ;P1^T ] [dO0|dO1]    A = P  image read MN-major (M = key j, K = query i)
+//         dK = [dS0^T;dS1^T] [Q0 |Q1 ]    A = dS image read MN-major
+//         dQ = [dS0  ;dS1  ] [K0 |K1 ]    A = dS image read K-major  (M = query i, K = key j)
+//         T += [dS0  ;dS1  ] I            A = dS image read K-major, B = 64x64 identity
+//       T (128 lanes x 64 columns of TMEM) accumulates sum_windows dS for the job's head over the whole
+//       CTA lifetime; at the end each row is scattered once into 169 shared-memory bins and the bins
+//       are added to d_bias_table with 169 global atomics per CTA.
+//       The off-diagonal blocks of every stacked product are computed and ignored.
+//   epilogue: dQ/dK/dV rows TMEM -> registers -> bf16 -> 64B-swizzled staging tiles (they reuse the
+//       P / dS bytes of the slot) -> TMA tensor stores with the same boxes as the loads, so the
+//       window reverse and the inverse cyclic shift are tensor-map addressing as well.
+//
+// Warps: 0 / 3 TMA producers (tile 0 / tile 1), 1 phase-1 MMA issuer, 2 phase-2 MMA issuer,
+// 4-11 two softmax warpgroups (one accumulator slot each).
+#include "swin_attn_tc.cuh"
+
+namespace swin {
+namespace tcb {
+
+using namespace tc;
+
+constexpr int kStagesB = 4;
+constexpr int kSlotsB = 2;
+constexpr int kThreadsB = 128 + 128 * kSlotsB;
+constexpr int kStageBytesB = 8 * kTileBytes;   // q0 q1 | k0 k1 | v0 v1 | do0 do1
+constexpr int kSlotBytes = 4 * kPTileBytes;    // P0 P1 | dS0 dS1 ; reused as dq0 dq1 dk0 dk1 dv0 dv1 staging
+constexpr int kSlotColsB = 224;                // S 0..111, dP 112..223 ; then dQ 0..63, dK 64..127, dV 128..191
+constexpr int kDtCol = 448;                    // T accumulator: columns 448..511
+constexpr int kLoadBytes = 4 * kBoxBytes;      // per tile: q, k, v, dO
+
+__device__ __forceinline__ uint32_t bq_off(int t) { return t * kTileBytes; }
+__device__ __forceinline__ uint32_t bk_off(int t) { return 2 * kTileBytes + t * kKTile1; }
+__device__ __forceinline__ uint32_t bv_off(int t) { return 4 * kTileBytes + t * kKTile1; }
+__device__ __forceinline__ uint32_t bdo_off(int t) { return 6 * kTileBytes + t * kTileBytes; }
+
+struct TmaMapsB {
+  CUtensorMap q[7], k[7], v[7], d_o[7];   // loads
+  CUtensorMap dq[7], dk[7], dv[7];        // stores
+};
+
+struct SmemMapB {
+  uint32_t stages, slots, ident, bias, bins, bars, tmem_ptr, total;
+};
+__host__ __device__ inline SmemMapB smem_map_b() {
+  SmemMapB m;
+  m.stages = 0;
+  m.slots = m.stages + kStagesB * kStageBytesB;
+  m.ident = m.slots + kSlotsB * kSlotBytes;
+  m.bias = m.ident + kPTileBytes;
+  m.bins = m.bias + 176 * 4;
+  m.bars = m.bins + 176 * 4;
+  m.tmem_ptr = m.bars + 8 * (2 * kStagesB + 4 * kSlotsB);
+  m.total = m.tmem_ptr + 16;
+  return m;
+}
+
+// Window w of the job -> (image, window row, window column); advance by a few windows without divisions.
+struct WinIter {
+  int b, wy, wx, w;
+  __device__ __forceinline__ void init(const Problem& p, int first) {
+    w = first;
+    wx = first % p.nWx;
+    const int r = first / p.nWx;
+    wy = r % p.nWy;
+    b = r / p.nWy;
+  }
+  __device__ __forceinline__ void advance(const Problem& p, int step) {
+    w += step;
+    wx += step;
+    while (wx >= p.nWx) { wx -= p.nWx; ++wy; }
+    while (wy >= p.nWy) { wy -= p.nWy; ++b; }
+  }
+};
+
+// One window of one tensor, global -> shared (kStore = false) or shared -> global (kStore = true):
+// 1 box (un-shifted) or the 2 / 4 parts of a shifted window (see swin_attn_tc.cu::load_window).
+template <bool kShifted, bool kStore>
+__device__ __forceinline__ void move_window(const CUtensorMap* maps, uint32_t smem_addr, uint32_t bar, const Problem& p,
+                                            int b, int wy, int wx, int h) {
+  const int ch = h * kHeadDim;
+  auto go = [&](int map, uint32_t row, int x, int y) {
+    if (kStore) tma_store_4d(maps + map, smem_addr + row * 64, ch, x, y, b);
+    else tma_load_4d(smem_addr + row * 64, maps + map, bar, ch, x, y, b);
+  };
+  if (!kShifted) {
+    go(0, 0, wx * WS, wy * WS);
+  } else {
+    const int xa = wx * WS + kShift, ya = wy * WS + kShift;
+    const int xb = wx == p.nWx - 1 ? 0 : wx * WS + WS, yb = wy == p.nWy - 1 ? 0 : wy * WS + WS;
+    if (wy == p.nWy - 1) {
+      go(1, 0, xa, ya);
+      go(2, 16, xa, yb);
+      go(3, 28, xb, ya);
+      go(4, 40, xb, yb);
+    } else {
+      go(5, 0, xa, ya);
+      go(6, 28, xb, ya);
+    }
+  }
+}
+
+template <bool kPerm>
+__device__ __forceinline__ uint64_t rows_of_window_row(int i) {
+  uint64_t m = 0;
+#pragma unroll
+  for (int j = 0; j < WS; ++j) m |= 1ull << token_row<kPerm>(i, j);
+  return m;
+}
+template <bool kPerm>
+__device__ __forceinline__ uint64_t rows_of_window_col(int j) {
+  uint64_t m = 0;
+#pragma unroll
+  for (int i = 0; i < WS; ++i) m |= 1ull << token_row<kPerm>(i, j);
+  return m;
+}
+
+#define TMEM_LD_X1(taddr, r0) asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r0) : "r"(taddr))
+
+template <bool kShifted>
+__global__ void __launch_bounds__(kThreadsB, 1)
+tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant__ TmaMapsB maps) {
+  constexpr bool kPerm = kShifted;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const SmemMapB map = smem_map_b();
+  const uint32_t sbase = smem_u32(smem);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int h = (int)blockIdx.x % p.nH;
+  const int w0 = ((int)blockIdx.x / p.nH) * win_per_job;
+  const int w1 = min(w0 + win_per_job, n_win);
+  const int n_pairs = (w1 - w0 + 1) >> 1;
+
+  const uint32_t bar_full = sbase + map.bars;              // [kStagesB] TMA -> phase-1 MMA
+  const uint32_t bar_empty = bar_full + 8 * kStagesB;      // [kStagesB] phase-2 MMA -> producers
+  const uint32_t bar_s = bar_empty + 8 * kStagesB;         // [kSlotsB]  S, dP ready
+  const uint32_t bar_p = bar_s + 8 * kSlotsB;              // [kSlotsB]  P, dS written
+  const uint32_t bar_o = bar_p + 8 * kSlotsB;              // [kSlotsB]  dQ, dK, dV ready
+  const uint32_t bar_r = bar_o + 8 * kSlotsB;              // [kSlotsB]  outputs read, slot reusable
+
+  // ---- one-time setup -------------------------------------------------------
+  {
+    // Every row the TMA boxes never write (rows 49.. of each tile) must stay finite: as the K dimension
+    // of a phase-2 product they are multiplied by zero columns of P / dS.
+    for (int i = tid; i < kStagesB * kStageBytesB / 16; i += kThreadsB)
+      *reinterpret_cast<uint4*>(smem + map.stages + i * 16) = make_uint4(0u, 0u, 0u, 0u);
+    // identity, K-major 128B-swizzled 64 x 64 bf16: element (n, n) = 1
+    for (int i = tid; i < 64 * 8; i += kThreadsB) {
+      const int n = i >> 3, chunk = i & 7;
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (chunk == (n >> 3)) {
+        const uint32_t one = (n & 1) ? 0x3f800000u : 0x00003f80u;
+        const int wsel = (n & 7) >> 1;
+        v.x = wsel == 0 ? one : 0u; v.y = wsel == 1 ? one : 0u; v.z = wsel == 2 ? one : 0u; v.w = wsel == 3 ? one : 0u;
+      }
+      *reinterpret_cast<uint4*>(smem + map.ident + n * 128 + ((chunk ^ (n & 7)) << 4)) = v;
+    }
+    float* bias = reinterpret_cast<float*>(smem + map.bias);
+    float* bins = reinterpret_cast<float*>(smem + map.bins);
+    for (int i = tid; i < 176; i += kThreadsB) {
+      bias[i] = i < 169 ? p.table[i * p.nH + h] * kLog2e : 0.f;
+      bins[i] = 0.f;
+    }
+    if (tid == 0) {
+      for (int i = 0; i < kStagesB; ++i) {
+        mbar_init(bar_full + 8 * i, 2);
+        mbar_init(bar_empty + 8 * i, 1);
+      }
+      for (int i = 0; i < kSlotsB; ++i) {
+        mbar_init(bar_s + 8 * i, 1);
+        mbar_init(bar_p + 8 * i, 128);
+        mbar_init(bar_o + 8 * i, 1);
+        mbar_init(bar_r + 8 * i, 128);
+      }
+      fence_barrier_init();
+      for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
+        tma_prefetch_desc(&maps.q[i]); tma_prefetch_desc(&maps.k[i]); tma_prefetch_desc(&maps.v[i]);
+        tma_prefetch_desc(&maps.d_o[i]); tma_prefetch_desc(&maps.dq[i]); tma_prefetch_desc(&maps.dk[i]);
+        tma_prefetch_desc(&maps.dv[i]);
+      }
+    }
+    if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+  }
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + map.tmem_ptr);
+
+  if (warp == 0 || warp == 3) {
+    // ===== TMA producers: warp 0 -> tile 0 of every pair, warp 3 -> tile 1 =====================
+    const int t = warp == 0 ? 0 : 1;
+    WinIter it;
+    it.init(p, w0 + t);
+    for (int n = 0; n < n_pairs; ++n, it.advance(p, 2)) {
+      const int s = n % kStagesB;
+      const uint32_t st = sbase + map.stages + s * kStageBytesB, bar = bar_full + 8 * s;
+      mbar_wait(bar_empty + 8 * s, ((n / kStagesB) & 1) ^ 1);
+      if (elect_one()) {
+        if (it.w < w1) {
+          mbar_expect_tx(bar, kLoadBytes);
+          move_window<kShifted, false>(maps.q, st + bq_off(t), bar, p, it.b, it.wy, it.wx, h);
+          move_window<kShifted, false>(maps.k, st + bk_off(t), bar, p, it.b, it.wy, it.wx, h);
+          move_window<kShifted, false>(maps.d_o, st + bdo_off(t), bar, p, it.b, it.wy, it.wx, h);
+          move_window<kShifted, false>(maps.v, st + bv_off(t), bar, p, it.b, it.wy, it.wx, h);
+        } else {
+          mbar_arrive(bar);
+        }
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ===== phase 1: S = Q K^T, dP = dO V^T ======================================================
+    constexpr uint32_t idesc = instr_desc(128, 112, 0);
+    for (int n = 0; n < n_pairs; ++n) {
+      const int s = n % kStagesB, a = n % kSlotsB;
+      mbar_wait(bar_full + 8 * s, (n / kStagesB) & 1);
+      mbar_wait(bar_r + 8 * a, ((n / kSlotsB) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t st = sbase + map.stages + s * kStageBytesB;
+      const uint32_t d = tmem_base + a * kSlotColsB;
+      const uint64_t qd = smem_desc(st + bq_off(0), 16, 512, 4), kd = smem_desc(st + bk_off(0), 16, 512, 4);
+      const uint64_t gd = smem_desc(st + bdo_off(0), 16, 512, 4), vd = smem_desc(st + bv_off(0), 16, 512, 4);
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 2; ++k) umma_ss(d, qd + 2 * k, kd + 2 * k, idesc, k);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) umma_ss(d + 112, gd + 2 * k, vd + 2 * k, idesc, k);
+        umma_commit(bar_s + 8 * a);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 2) {
+    // ===== phase 2: dV, dK, dQ and the bias-gradient accumulator ================================
+    constexpr uint32_t idesc_tt = instr_desc(128, 64, 1, 1);   // A and B MN-major
+    constexpr uint32_t idesc_nt = instr_desc(128, 64, 1, 0);   // A K-major, B MN-major
+    constexpr uint32_t idesc_nn = instr_desc(128, 64, 0, 0);   // both K-major
+    const uint64_t id_k = smem_desc(sbase + map.ident, 16, 1024, 2);
+    for (int m = 0; m < n_pairs; ++m) {
+      const int s = m % kStagesB, a = m % kSlotsB;
+      mbar_wait(bar_p + 8 * a, (m / kSlotsB) & 1);
+      tc_fence_after();
+      const uint32_t st = sbase + map.stages + s * kStageBytesB;
+      const uint32_t sl = sbase + map.slots + a * kSlotBytes;
+      const uint32_t d = tmem_base + a * kSlotColsB;
+      const uint64_t p_mn = smem_desc(sl, 2 * kPTileBytes / 2, 1024, 2);                    // M blocks (tiles) 8 KB apart
+      const uint64_t ds_mn = smem_desc(sl + 2 * kPTileBytes, 2 * kPTileBytes / 2, 1024, 2);
+      const uint64_t ds_k = smem_desc(sl + 2 * kPTileBytes, 16, 1024, 2);
+      const uint64_t g_mn = smem_desc(st + bdo_off(0), kTileBytes, 512, 4);                 // N blocks: dO0 | dO1
+      const uint64_t q_mn = smem_desc(st + bq_off(0), kTileBytes, 512, 4);                  // Q0 | Q1
+      const uint64_t k_mn = smem_desc(st + bk_off(0), kKTile1, 512, 4);                     // K0 | K1
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ss(d + 128, p_mn + 128 * k, g_mn + 64 * k, idesc_tt, k);   // dV
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ss(d + 64, ds_mn + 128 * k, q_mn + 64 * k, idesc_tt, k);   // dK
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ss(d, ds_k + 2 * k, k_mn + 64 * k, idesc_nt, k);           // dQ
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ss(tmem_base + kDtCol, ds_k + 2 * k, id_k + 2 * k, idesc_nn, (m | k) != 0);
+        umma_commit(bar_o + 8 * a);
+        umma_commit(bar_empty + 8 * s);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===== softmax / gradient warpgroups ======================================================
+    const int g = (warp >> 2) - 1;          // accumulator slot owned by this warpgroup
+    const int q = warp & 3;                 // TMEM sub-partition: lanes 32q .. 32q+31
+    const int sel = q >> 1;                 // tile of the pair
+    const int row = (q & 1) * 32 + lane;    // row of this tile's S / dP / dQ / dK / dV held by this thread
+    const int rowc = row < N ? row : N - 1;
+    const int ri = row_i<kPerm>(rowc), rj = row_j<kPerm>(rowc);
+    const int base_i = ri * 13 + rj + 84;   // relative_position_index[row, col] = base_i - (ci*13 + cj)
+    const float* brow = reinterpret_cast<const float*>(smem + map.bias) + base_i;
+    const float c1s = p.scale * kLog2e;
+    const float2 c1 = make_float2(c1s, c1s);
+    const uint64_t all = (1ull << N) - 1;
+    uint64_t hb = 0, wb = 0;                // SW-MSA regions as tile-row bit sets (newcrf_layers.py:335-345)
+    if (kShifted) {
+#pragma unroll
+      for (int i = WS - kShift; i < WS; ++i) hb |= rows_of_window_row<kPerm>(i);
+#pragma unroll
+      for (int j = WS - kShift; j < WS; ++j) wb |= rows_of_window_col<kPerm>(j);
+    }
+    const uint32_t sl = sbase + map.slots + g * kSlotBytes;
+    const uint32_t p_row = sl + sel * kPTileBytes + row * 128;
+    const uint32_t ds_row = p_row + 2 * kPTileBytes;
+    const uint32_t stage_row = sl + sel * kTileBytes + row * 64;   // + 2 * kTileBytes per output tensor
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + g * kSlotColsB;
+    const uint32_t s_addr = taddr + sel * 56, dp_addr = taddr + 112 + sel * 56;
+    const bool issuer = (q & 1) == 0;       // warps 0 and 2 of the warpgroup store tile 0 / tile 1
+    WinIter it;
+    it.init(p, w0 + 2 * g + sel);
+
+    int m = 0;
+    for (int n = g; n < n_pairs; n += kSlotsB, ++m, it.advance(p, 2 * kSlotsB)) {
+      const bool valid = it.w < w1;
+      int y = it.wy * WS + ri + p.shift, x = it.wx * WS + rj + p.shift;
+      if (y >= p.Hp) y -= p.Hp;
+      if (x >= p.Wp) x -= p.Wp;
+      float lse2 = 0.f;
+      if (valid && row < N) lse2 = p.lse[((int64_t)(it.b * p.Hp + y) * p.Wp + x) * p.nH + h] * kLog2e;
+      uint64_t masked = 0;
+      if (kShifted) {
+        const uint64_t hm = it.wy == p.nWy - 1 ? hb : 0, wm = it.wx == p.nWx - 1 ? wb : 0;
+        masked = (((hm >> rowc) & 1) ? (~hm & all) : hm) | (((wm >> rowc) & 1) ? (~wm & all) : wm);
+      }
+      const bool special = kShifted && (it.wy == p.nWy - 1 || it.wx == p.nWx - 1);   // warp-uniform
+
+      mbar_wait(bar_s + 8 * g, m & 1);
+      tc_fence_after();
+      uint32_t r[N + 15], d[N + 15];
+      TMEM_LD_X16(s_addr, (r + 0));
+      TMEM_LD_X16(s_addr + 16, (r + 16));
+      TMEM_LD_X16(s_addr + 32, (r + 32));
+      TMEM_LD_X1(s_addr + 48, r[48]);
+      TMEM_LD_X16(dp_addr, (d + 0));
+      TMEM_LD_X16(dp_addr + 16, (d + 16));
+      TMEM_LD_X16(dp_addr + 32, (d + 32));
+      TMEM_LD_X1(dp_addr + 48, d[48]);
+      tmem_ld_wait();
+
+      // P = exp2(S * scale*log2e + bias*log2e (+ mask) - lse*log2e)
+      const float2 nl = make_float2(-lse2, -lse2);
+      if (!special) {
+#pragma unroll
+        for (int j = 0; j < N - 1; j += 2) {
+          const int cj0 = row_i<kPerm>(j) * 13 + row_j<kPerm>(j), cj1 = row_i<kPerm>(j + 1) * 13 + row_j<kPerm>(j + 1);
+          const float2 b2 = __fadd2_rn(make_float2(brow[-cj0], brow[-cj1]), nl);
+          const float2 t = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), c1, b2);
+          r[j] = __float_as_uint(fast_exp2(t.x));
+          r[j + 1] = __float_as_uint(fast_exp2(t.y));
+        }
+        const int cj = row_i<kPerm>(N - 1) * 13 + row_j<kPerm>(N - 1);
+        r[N - 1] = __float_as_uint(fast_exp2(fmaf(__uint_as_float(r[N - 1]), c1s, brow[-cj] - lse2)));
+      } else {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
+          float t = fmaf(__uint_as_float(r[j]), c1s, brow[-cj] - lse2);
+          if ((masked >> j) & 1) t += -100.0f * kLog2e;
+          r[j] = __float_as_uint(fast_exp2(t));
+        }
+      }
+      // delta = sum_j P_ij dP_ij ; dS = P (dP - delta)
+      float2 acc = make_float2(0.f, 0.f), acc_b = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < N - 1; j += 4) {
+        acc = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])),
+                         make_float2(__uint_as_float(d[j]), __uint_as_float(d[j + 1])), acc);
+        acc_b = __ffma2_rn(make_float2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])),
+                           make_float2(__uint_as_float(d[j + 2]), __uint_as_float(d[j + 3])), acc_b);
+      }
+      const float delta = fmaf(__uint_as_float(r[N - 1]), __uint_as_float(d[N - 1]), (acc.x + acc.y) + (acc_b.x + acc_b.y));
+      const float2 nd = make_float2(-delta, -delta);
+      const bool live = valid && row < N;
+      uint32_t wp[25], wd[25];
+#pragma unroll
+      for (int e = 0; e < 24; ++e) {
+        const float2 pp = make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]));
+        const float2 ds = __fmul2_rn(pp, __fadd2_rn(make_float2(__uint_as_float(d[2 * e]), __uint_as_float(d[2 * e + 1])), nd));
+        wp[e] = live ? pack_bf16(pp.x, pp.y) : 0u;
+        wd[e] = live ? pack_bf16(ds.x, ds.y) : 0u;
+      }
+      {
+        const float pl = __uint_as_float(r[N - 1]);
+        wp[24] = live ? pack_bf16(pl, 0.f) : 0u;
+        wd[24] = live ? pack_bf16(pl * (__uint_as_float(d[N - 1]) - delta), 0.f) : 0u;
+      }
+      // the TMA stores of this warpgroup's previous pair must have finished reading the staging tiles
+      // (same bytes as P / dS) before they are overwritten
+      if (issuer && elect_one()) bulk_wait_read();
+      named_barrier(1 + g, 128);
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) {
+        const uint32_t off = (uint32_t)((ch ^ (row & 7)) << 4);
+        auto word = [&](const uint32_t* w, int i) { return i < 25 ? w[i < 25 ? i : 0] : 0u; };
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(p_row + off), "r"(word(wp, 4 * ch)), "r"(word(wp, 4 * ch + 1)),
+                     "r"(word(wp, 4 * ch + 2)), "r"(word(wp, 4 * ch + 3)) : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(ds_row + off), "r"(word(wd, 4 * ch)), "r"(word(wd, 4 * ch + 1)),
+                     "r"(word(wd, 4 * ch + 2)), "r"(word(wd, 4 * ch + 3)) : "memory");
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      mbar_arrive(bar_p + 8 * g);
+
+      mbar_wait(bar_o + 8 * g, m & 1);
+      tc_fence_after();
+      // dQ (x scale), dK (x scale), dV rows -> bf16 -> 64B-swizzled staging tiles
+#pragma unroll
+      for (int t3 = 0; t3 < 3; ++t3) {
+        uint32_t o[32];
+        const uint32_t oaddr = taddr + t3 * 64 + sel * 32;
+        TMEM_LD_X16(oaddr, (o + 0));
+        TMEM_LD_X16(oaddr + 16, (o + 16));
+        tmem_ld_wait();
+        const float sc = t3 < 2 ? p.scale : 1.0f;
+        const float2 sc2 = make_float2(sc, sc);
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          uint32_t v[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 s2 = __fmul2_rn(make_float2(__uint_as_float(o[8 * ch + 2 * e]), __uint_as_float(o[8 * ch + 2 * e + 1])), sc2);
+            v[e] = pack_bf16(s2.x, s2.y);
+          }
+          const uint32_t dst = stage_row + t3 * 2 * kTileBytes + (uint32_t)((ch ^ ((row >> 1) & 3)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(bar_r + 8 * g);
+      fence_proxy_async();
+      named_barrier(1 + g, 128);
+      if (issuer && valid && elect_one()) {
+        const uint32_t src = sl + sel * kTileBytes;
+        move_window<kShifted, true>(maps.dq, src, 0, p, it.b, it.wy, it.wx, h);
+        move_window<kShifted, true>(maps.dk, src + 2 * kTileBytes, 0, p, it.b, it.wy, it.wx, h);
+        move_window<kShifted, true>(maps.dv, src + 4 * kTileBytes, 0, p, it.b, it.wy, it.wx, h);
+        bulk_commit();
+      }
+      __syncwarp();
+    }
+    if (issuer && elect_one()) bulk_wait_all();
+
+    // ---- bias-table gradient: T[row i, col j] = sum over the job's windows of dS -------------------
+    // The phase-2 MMAs complete in issue order, so once the warpgroup that owns the LAST pair has seen its
+    // bar_o, T is final; a barrier over both warpgroups publishes that to warpgroup 0, which scatters.
+    named_barrier(3, 128 * kSlotsB);
+    float* bins = reinterpret_cast<float*>(smem + map.bins);
+    if (g == 0 && n_pairs > 0) {
+      tc_fence_after();
+      uint32_t tr[N + 15];
+      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + kDtCol;
+      TMEM_LD_X16(t_addr, (tr + 0));
+      TMEM_LD_X16(t_addr + 16, (tr + 16));
+      TMEM_LD_X16(t_addr + 32, (tr + 32));
+      TMEM_LD_X1(t_addr + 48, tr[48]);
+      tmem_ld_wait();
+      if (row < N) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
+          atomicAdd(&bins[base_i - cj], __uint_as_float(tr[j]));
+        }
+      }
+      named_barrier(4, 128);
+      for (int i = tid - 128; i < 169; i += 128) atomicAdd(&p.d_table[i * p.nH + h], bins[i]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace tcb
+
+// ---- host side ------------------------------------------------------------------
+bool tc_backward_supported(const Problem& p, int dtype) {
+  if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
+  if (p.shift != 0 && p.shift != tc::kShift) return false;
+  if (p.H != p.Hp || p.W != p.Wp) return false;
+  if ((p.q_ps | p.k_ps | p.v_ps | p.C) & 7) return false;
+  auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
+  if (mis(p.q) || mis(p.k) || mis(p.v) || mis(p.d_o) || mis(p.dq) || mis(p.dk) || mis(p.dv)) return false;
+  return tc::tma_available();
+}
+
+cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** err) {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  tcb::TmaMapsB maps;
+  memset(&maps, 0, sizeof(maps));
+  const bool shifted = p.shift != 0;
+  for (int i = shifted ? 1 : 0; i < (shifted ? 7 : 1); ++i) {
+    const int bx = tc::kBoxX[i], by = tc::kBoxY[i];
+    const bool ok = tc::encode_window_map(&maps.q[i], p.q, p, p.q_ps, bx, by) && tc::encode_window_map(&maps.k[i], p.k, p, p.k_ps, bx, by) &&
+                    tc::encode_window_map(&maps.v[i], p.v, p, p.v_ps, bx, by) && tc::encode_window_map(&maps.d_o[i], p.d_o, p, p.C, bx, by) &&
+                    tc::encode_window_map(&maps.dq[i], p.dq, p, p.q_ps, bx, by) && tc::encode_window_map(&maps.dk[i], p.dk, p, p.k_ps, bx, by) &&
+                    tc::encode_window_map(&maps.dv[i], p.dv, p, p.v_ps, bx, by);
+    if (!ok) {
+      if (err) *err = "cuTensorMapEncodeTiled failed";
+      return cudaErrorInvalidValue;
+    }
+  }
+  const tcb::SmemMapB map = tcb::smem_map_b();
+  auto kernel = shifted ? tcb::tc_bwd_kernel<true> : tcb::tc_bwd_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)map.total);
+  if (e != cudaSuccess) {
+    if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
+    return e;
+  }
+  // jobs = heads x window chunks, at most one wave of CTAs; chunks hold an even number of windows
+  const int n_win = p.B * p.nWy * p.nWx;
+  int chunks = sms / p.nH;
+  if (chunks < 1) chunks = 1;
+  int per = (n_win + chunks - 1) / chunks;
+  per += per & 1;
+  chunks = (n_win + per - 1) / per;
+  e = cudaMemsetAsync(p.d_table, 0, sizeof(float) * 169 * p.nH, st);
+  if (e != cudaSuccess) return e;
+  kernel<<<chunks * p.nH, tcb::kThreadsB, map.total, st>>>(p, n_win, per, maps);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace swin

@@ -141,7 +141,7 @@ def _(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale,
 @torch.library.custom_op("swin_attn::bwd", mutates_args=(), device_types="cuda")
 def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tensor, bias_table: Tensor,
          window: int, shift: int, num_heads: int, scale: float,
-         attn_mask: Optional[Tensor] = None) -> Tuple[Tensor, Tensor, Tensor]:
+         attn_mask: Optional[Tensor] = None, impl: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
     c = _split(packed, v, num_heads)
     mask, mask_nw = _mask_arg(attn_mask, window)
     lib = _lib.load()
@@ -171,7 +171,7 @@ def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tenso
         # differ from those of the inputs: run q/k and v through two shapes
         # only when they do.
         if ps == pc and (v is None or v_ps == c):
-            shp = _shape(b, h, w, num_heads, window, shift, dt, _lib.IMPL_AUTO, scale, ps, ps, v_ps, c, mask_nw)
+            shp = _shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw)
             _lib.check(lib.swin_attn_backward(
                 ctypes.byref(shp), ctypes.c_void_p(base), ctypes.c_void_p(base + c * es), ctypes.c_void_p(v_ptr),
                 _ptr(o), _ptr(d_o), _ptr(lse), _ptr(table), _ptr(mask),
@@ -180,12 +180,12 @@ def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tenso
         else:
             packed_c = packed.contiguous()
             v_c = None if v is None else v.contiguous()
-            return _bwd(d_o, packed_c, v_c, o, lse, bias_table, window, shift, num_heads, scale, attn_mask)
+            return _bwd(d_o, packed_c, v_c, o, lse, bias_table, window, shift, num_heads, scale, attn_mask, impl)
     return d_packed, d_v, d_table.to(bias_table.dtype)
 
 
 @_bwd.register_fake
-def _(d_o, packed, v, o, lse, bias_table, window, shift, num_heads, scale, attn_mask=None):
+def _(d_o, packed, v, o, lse, bias_table, window, shift, num_heads, scale, attn_mask=None, impl=0):
     d_packed = packed.new_empty(packed.shape)
     d_v = packed.new_empty((0,)) if v is None else packed.new_empty(v.shape)
     return d_packed, d_v, torch.empty_like(bias_table)

@@ -64,8 +64,16 @@ def test_forward_matches_oracle(case, dtype, impl):
     assert rel_err(lse[:, :h, :w], want_lse[:, :h, :w]) < (1e-5 if dtype == torch.float32 else 2e-2)
 
 
+# window-aligned shapes for the backward: odd window counts (a job's last pair is half empty), several
+# window chunks per head, external v, shifted wrap rows / columns
+BWD_CASES = [c for c in CASES if c[3] % c[0] == 0 and c[4] % c[0] == 0] + [
+    (7, 0, 1, 7, 21, 3, False), (7, 3, 1, 21, 35, 4, True), (7, 3, 3, 28, 49, 6, False), (7, 0, 5, 35, 63, 2, True),
+    (7, 3, 1, 7, 7, 2, False), (7, 3, 2, 14, 7, 48, False),
+]
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("case", [c for c in CASES if c[3] % c[0] == 0 and c[4] % c[0] == 0])
+@pytest.mark.parametrize("case", BWD_CASES)
 def test_backward_matches_oracle_autograd(case, dtype):
     ws, shift, b, h, w, nh, ext = case
     c = nh * 32
@@ -89,6 +97,9 @@ def test_backward_matches_oracle_autograd(case, dtype):
     g = torch.autograd.grad((o.float() * cot.to(DEV).float()).sum(), [pg, tg] + ([] if v is None else [vg]))
     tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
     assert rel_err(o.float(), o_ref) < tol
+    if dtype == torch.bfloat16 and ws == 7 and shift in (0, 3):   # the tcgen05 backward serves these
+        shp = _lib.Shape(b, h, w, nh, ws, shift, _lib.BF16, _lib.IMPL_AUTO, 32 ** -0.5, 0.0, 0, 3 * c, 3 * c, 3 * c, c, 0, 0)
+        assert _lib.load().swin_attn_uses_tcgen05(ctypes.byref(shp), 1) == 1
     for got, want, what in zip(g, g_ref, ["d_packed", "d_table", "d_v"]):
         assert got.dtype == (torch.float32 if what == "d_table" else dtype)
         assert rel_err(got.float(), want) < tol, what

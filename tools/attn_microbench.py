@@ -53,10 +53,22 @@ def main():
         v = torch.randn(b, h, w, c, device=dev, generator=g).to(dt) if ext else None
         table = 0.02 * torch.randn((2 * ws - 1) ** 2, nh, device=dev, generator=g)
         pad = (0.1 * torch.randn(packed.shape[-1], device=dev, generator=g)).to(dt)
+        if args.bwd and (h % ws or w % ws):   # the backward takes window-aligned tensors (the layers pad explicitly)
+            hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
+            packed = torch.nn.functional.pad(packed, (0, 0, 0, wp - w, 0, hp - h)).contiguous()
+            v = None if v is None else torch.nn.functional.pad(v, (0, 0, 0, wp - w, 0, hp - h)).contiguous()
+            h, w = hp, wp
         for shift in (0, ws // 2):
             for iname, impl in impls.items():
-                def run():
-                    return torch.ops.swin_attn.fwd(packed, v, table, pad, None, ws, shift, nh, 32 ** -0.5, False, impl, None)
+                if args.bwd:
+                    o, lse = torch.ops.swin_attn.fwd(packed, v, table, None, None, ws, shift, nh, 32 ** -0.5, True, impl, None)
+                    d_o = torch.randn(b, h, w, c, device=dev, generator=g).to(dt)
+
+                    def run():
+                        return torch.ops.swin_attn.bwd(d_o, packed, v, o, lse, table, ws, shift, nh, 32 ** -0.5, None, impl)
+                else:
+                    def run():
+                        return torch.ops.swin_attn.fwd(packed, v, table, pad, None, ws, shift, nh, 32 ** -0.5, False, impl, None)
                 for _ in range(3):
                     run()
                 # back-to-back launches with an L2 flush in between; no host sync inside the loop, so the
@@ -73,10 +85,11 @@ def main():
                 torch.cuda.synchronize()
                 ms = sum(a.elapsed_time(e) for a, e in evs)
                 ms /= args.iters
-                nbytes = 4 * b * h * w * c * packed.element_size()
+                # algorithmic bytes: forward q,k,v in + o out; backward q,k,v,dO in + dq,dk,dv out + lse
+                nbytes = (7 if args.bwd else 4) * b * h * w * c * packed.element_size() + (b * h * w * nh * 4 if args.bwd else 0)
                 hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
-                flops = 4 * b * hp * wp * ws * ws * c
-                print(json.dumps({"case": name, "shift": shift, "impl": iname, "dtype": args.dtype, "us": round(ms * 1e3, 2),
+                flops = (10 if args.bwd else 4) * b * hp * wp * ws * ws * c
+                print(json.dumps({"case": name, "pass": "bwd" if args.bwd else "fwd", "shift": shift, "impl": iname, "dtype": args.dtype, "us": round(ms * 1e3, 2),
                                   "GBps": round(nbytes / ms / 1e6, 1), "hbm_frac": round(nbytes / ms / 1e6 / hbm, 4),
                                   "TFLOPs": round(flops / ms / 1e9, 2), "MB": round(nbytes / 1e6, 1)}), flush=True)
 
