@@ -39,6 +39,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"],
+                    help="infer: BASELINE configs[1] (the headline metric); train: configs[2], fwd+SILog+bwd+AdamW at 480x640")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--version", default=VERSION)
     ap.add_argument("--batch", type=int, default=BATCH)
@@ -133,10 +135,11 @@ def run_ours(args, env):
     rank, world, local = env["rank"], env["world"], env["local_rank"]
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    model = build_model(args.version, MAX_DEPTH, seed=0, device=dev).eval()
-    host = synthetic_images(args.batch, HEIGHT, WIDTH, seed=rank, pin=True)
+    train = args.mode == "train"
+    height, width, max_depth = (480, 640, 10.0) if train else (HEIGHT, WIDTH, MAX_DEPTH)
+    model = build_model(args.version, max_depth, seed=0, device=dev)
+    host = synthetic_images(args.batch, height, width, seed=rank, pin=True)
     images = host.to(dev)
-    out_host = torch.empty(args.batch, 1, HEIGHT, WIDTH).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def barrier():
@@ -157,12 +160,32 @@ def run_ours(args, env):
         torch.cuda.synchronize()
         return sum(a.elapsed_time(b) for a, b in evs) / 1e3
 
-    def step_resident():
-        infer(model, images)
+    if train:
+        from mde_b200.harness import Trainer, synthetic_depth
+        model.train()
+        trainer = Trainer(model, ddp=world > 1, device_ids=[local] if world > 1 else None)
+        gt_host = synthetic_depth(args.batch, height, width, max_depth, seed=100 + rank).pin_memory()
+        gt = gt_host.to(dev)
+        out_host = torch.empty(1).pin_memory()
 
-    def step_e2e():
-        x = host.to(dev, non_blocking=True)
-        out_host.copy_(infer(model, x).float(), non_blocking=True)
+        def step_resident():
+            trainer.step(images, gt)
+
+        def step_e2e():
+            x, y = host.to(dev, non_blocking=True), gt_host.to(dev, non_blocking=True)
+            out_host.copy_(trainer.step(x, y).reshape(1), non_blocking=True)
+        h2d, d2h = host.numel() * 4 + gt_host.numel() * 4, 4
+    else:
+        model.eval()
+        out_host = torch.empty(args.batch, 1, height, width).pin_memory()
+
+        def step_resident():
+            infer(model, images)
+
+        def step_e2e():
+            x = host.to(dev, non_blocking=True)
+            out_host.copy_(infer(model, x).float(), non_blocking=True)
+        h2d, d2h = host.numel() * 4, out_host.numel() * 4
 
     for _ in range(args.warmup):
         step_resident()
@@ -189,36 +212,51 @@ def run_ours(args, env):
     if rank != 0:
         return
     hbm, tf, which = peaks()
-    k_ms = sum(a.elapsed_time(b) for a, b, *_ in records)
-    k_bytes = sum(r[2] for r in records)
-    k_flops = sum(r[3] for r in records)
-    achieved = k_bytes / (k_ms * 1e-3) / 1e9 if k_ms else None
-    traffic = None
+
+    def roof(recs, name):
+        k_ms = sum(a.elapsed_time(b) for a, b, *_ in recs)
+        if not recs or not k_ms:
+            return None
+        k_bytes, k_flops = sum(r[2] for r in recs), sum(r[3] for r in recs)
+        achieved = k_bytes / (k_ms * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)", "traffic": traffic.get(name.split()[1]),
+                "launches": len(recs), "kernel_ms_per_step": k_ms / args.steps, "share_of_step": k_ms / 1e3 / t_res,
+                "useful_tflops": k_flops / (k_ms * 1e-3) / 1e12,
+                "tensor_frac_of_sustained_bf16": k_flops / (k_ms * 1e-3) / 1e12 / tf}
+    traffic = {}
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        traffic = json.load(open(tpath))
+    fwd_recs = [r for r in records if r[4][0] == "fwd"]
+    bwd_recs = [r for r in records if r[4][0] == "bwd"]
+    roof_fwd = roof(fwd_recs, "swin_attn forward (all window-attention forward launches of the step)")
+    roof_bwd = roof(bwd_recs, "swin_attn backward (all window-attention backward launches of the step)")
     n_img = args.batch * world * args.steps
+    if train:
+        metric = "NewCRFs Swin-L training images/sec @480x640 (bf16 autocast fwd + SILog + bwd + clip + AdamW, batch 8/GPU)"
+        workload = (f"NewCRFs {args.version} training step, batch {args.batch}/GPU, 3x480x640 NYU-shape synthetic images and "
+                    "depth, torch.autocast(bf16), random-init weights")
+        par = f"DDP x{world} (stock DistributedDataParallel, NCCL gradient all-reduce)" if world > 1 else "single GPU"
+    else:
+        metric = METRIC
+        workload = (f"NewCRFs {args.version} full-model inference, batch {args.batch}/GPU, 3x352x1216 "
+                    "KITTI-shape synthetic images, torch.autocast(bf16), random-init weights")
+        par = f"replicas x{world} (batch data-parallel, no data-path collective)"
     line = {
-        "metric": METRIC, "value": n_img / t_res, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "metric": metric, "value": n_img / t_res, "unit": "images/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t_res / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"NewCRFs {args.version} full-model inference, batch {args.batch}/GPU, 3x352x1216 "
-                               "KITTI-shape synthetic images, torch.autocast(bf16), random-init weights",
-                   "parallelism": f"replicas x{world} (batch data-parallel, no data-path collective)",
+        "config": {"workload": workload, "parallelism": par,
                    "l2_flush_between_steps": True, "timing": "CUDA events per step, max over ranks"},
-        "e2e": {"value": n_img / t_e2e, "unit": "images/s", "h2d_bytes_per_step": host.numel() * 4,
-                "d2h_bytes_per_step": out_host.numel() * 4},
+        "e2e": {"value": n_img / t_e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
-        "roofline": {"bound": "hbm", "kernel": "swin_attn forward (all window-attention launches of the step)",
-                     "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm if achieved else None,
-                     "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)", "traffic": traffic,
-                     "launches": len(records), "kernel_ms_per_step": k_ms / args.steps,
-                     "share_of_step": k_ms / 1e3 / t_res if t_res else None,
-                     "useful_tflops": k_flops / (k_ms * 1e-3) / 1e12 if k_ms else None,
-                     "tensor_frac_of_sustained_bf16": k_flops / (k_ms * 1e-3) / 1e12 / tf if k_ms else None},
+        "roofline": roof_bwd if train else roof_fwd,
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if train:
+        line["roofline_forward"] = roof_fwd
+    if world == 1 and not args.no_cpu_baseline and not train:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
         cm, img = cpu_model_and_sample(args.version)

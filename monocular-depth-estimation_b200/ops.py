@@ -124,7 +124,7 @@ def _fwd(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, packed_pad: Op
             tokens = b * h * w
             # algorithmic traffic: read q, k, v and write o once, valid tokens only
             _kernel_timing.append((ev0, ev1, 4 * tokens * c * es + (lse.numel() * 4 if need_lse else 0),
-                                   4 * b * hp * wp * window * window * c, (window, shift, num_heads, h, w)))
+                                   4 * b * hp * wp * window * window * c, ("fwd", window, shift, num_heads, h, w)))
     return o, lse
 
 
@@ -172,11 +172,20 @@ def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tenso
         # only when they do.
         if ps == pc and (v is None or v_ps == c):
             shp = _shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw)
+            if _kernel_timing is not None:
+                ev0 = torch.cuda.Event(enable_timing=True)
+                ev0.record()
             _lib.check(lib.swin_attn_backward(
                 ctypes.byref(shp), ctypes.c_void_p(base), ctypes.c_void_p(base + c * es), ctypes.c_void_p(v_ptr),
                 _ptr(o), _ptr(d_o), _ptr(lse), _ptr(table), _ptr(mask),
                 ctypes.c_void_p(d_packed.data_ptr()), ctypes.c_void_p(d_packed.data_ptr() + c * es),
                 ctypes.c_void_p(dv_ptr), _ptr(d_table), ctypes.c_void_p(stream)))
+            if _kernel_timing is not None:
+                ev1 = torch.cuda.Event(enable_timing=True)
+                ev1.record()
+                # algorithmic traffic of the recompute backward: read q, k, v, dO + lse, write dq, dk, dv
+                _kernel_timing.append((ev0, ev1, 7 * b * h * w * c * es + lse.numel() * 4,
+                                       10 * b * h * w * window * window * c, ("bwd", window, shift, num_heads, h, w)))
         else:
             packed_c = packed.contiguous()
             v_c = None if v is None else v.contiguous()

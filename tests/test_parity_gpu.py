@@ -326,6 +326,35 @@ def test_full_size_properties(shape, shift, dtype):
     assert rel_err(o.float(), o_s.float()) < (1e-6 if dtype == torch.float32 else TOL_BF16)
 
 
+@pytest.mark.parametrize("shift", [0, 3])
+@pytest.mark.parametrize("shape", [(8, 91, 308, 6, 7), (8, 28, 77, 24, 7)])   # large07 stage-0 / stage-2 padded grids, batch 8
+def test_full_size_backward_properties(shape, shift):
+    b, h, w, nh, ws = shape
+    c = nh * 32
+    gen = torch.Generator(device=DEV).manual_seed(4321)
+    qkv = torch.randn(b, h, w, 3 * c, device=DEV, generator=gen).bfloat16()
+    table = 0.5 * torch.randn((2 * ws - 1) ** 2, nh, device=DEV, generator=gen)
+    d_o = torch.randn(b, h, w, c, device=DEV, generator=gen).bfloat16()
+    o, lse = torch.ops.swin_attn.fwd(qkv, None, table, None, None, ws, shift, nh, 32 ** -0.5, True, _lib.IMPL_AUTO, None)
+    g_tc = torch.ops.swin_attn.bwd(d_o, qkv, None, o, lse, table, ws, shift, nh, 32 ** -0.5, None, _lib.IMPL_TCGEN05)
+    g_simt = torch.ops.swin_attn.bwd(d_o, qkv, None, o, lse, table, ws, shift, nh, 32 ** -0.5, None, _lib.IMPL_SIMT)
+    # (1) the tcgen05 and the CUDA-core backward agree (both bf16 storage, fp32 accumulation)
+    assert rel_err(g_tc[0].float(), g_simt[0].float()) < 2e-2
+    assert rel_err(g_tc[2], g_simt[2]) < 2e-2
+    # (2) every row of dS sums to zero, hence so does every head's column of the bias-table gradient
+    assert float(g_tc[2].sum(0).abs().max() / g_tc[2].abs().max()) < 2e-2
+    # (3) dV is linear in dO:  bwd(2 dO).dv == 2 bwd(dO).dv exactly in bf16 (power of two)
+    g2 = torch.ops.swin_attn.bwd((2 * d_o.float()).bfloat16(), qkv, None, o, lse, table, ws, shift, nh, 32 ** -0.5, None,
+                                 _lib.IMPL_TCGEN05)
+    assert rel_err(g2[0][..., 2 * c:].float(), 2 * g_tc[0][..., 2 * c:].float()) < 1e-6
+    # (4) one image against the fp64 oracle's autograd
+    pr = qkv[:1].double().cpu().requires_grad_()
+    tr = table.double().cpu().requires_grad_()
+    o_ref, _ = wa.window_attention(pr[..., :c], pr[..., c:2 * c], pr[..., 2 * c:], tr, ws, shift, nh)
+    gp, = torch.autograd.grad((o_ref * d_o[:1].double().cpu()).sum(), [pr])
+    assert rel_err(g_tc[0][:1].float(), gp) < TOL_BF16
+
+
 def test_library_counts_launches():
     before = _lib.launch_count()
     x = torch.zeros(1, 7, 7, 96, device=DEV)
