@@ -296,10 +296,74 @@ __host__ __device__ constexpr int token_row(int i, int j) {
   return j < 4 ? (i < 4 ? i * 4 + j : 16 + (i - 4) * 4 + j) : (i < 4 ? 28 + i * 3 + (j - 4) : 40 + (i - 4) * 3 + (j - 4));
 }
 
+// Window w of the job -> (image, window row, window column); advance by a few windows without divisions.
+struct WinIter {
+  int b, wy, wx, w;
+  __device__ __forceinline__ void init(const Problem& p, int first) {
+    w = first;
+    wx = first % p.nWx;
+    const int r = first / p.nWx;
+    wy = r % p.nWy;
+    b = r / p.nWy;
+  }
+  __device__ __forceinline__ void advance(const Problem& p, int step) {
+    w += step;
+    wx += step;
+    while (wx >= p.nWx) { wx -= p.nWx; ++wy; }
+    while (wy >= p.nWy) { wy -= p.nWy; ++b; }
+  }
+};
+
+// One window of one tensor, global -> shared (kStore = false) or shared -> global (kStore = true):
+// 1 box (un-shifted) or the 2 / 4 parts of a shifted window (see swin_attn_tc.cu::load_window).
+template <bool kShifted, bool kStore>
+__device__ __forceinline__ void move_window(const CUtensorMap* maps, uint32_t smem_addr, uint32_t bar, const Problem& p,
+                                            int b, int wy, int wx, int h) {
+  const int ch = h * kHeadDim;
+  auto go = [&](int map, uint32_t row, int x, int y) {
+    if (kStore) tma_store_4d(maps + map, smem_addr + row * 64, ch, x, y, b);
+    else tma_load_4d(smem_addr + row * 64, maps + map, bar, ch, x, y, b);
+  };
+  if (!kShifted) {
+    go(0, 0, wx * WS, wy * WS);
+  } else {
+    const int xa = wx * WS + kShift, ya = wy * WS + kShift;
+    const int xb = wx == p.nWx - 1 ? 0 : wx * WS + WS, yb = wy == p.nWy - 1 ? 0 : wy * WS + WS;
+    if (wy == p.nWy - 1) {
+      go(1, 0, xa, ya);
+      go(2, 16, xa, yb);
+      go(3, 28, xb, ya);
+      go(4, 40, xb, yb);
+    } else {
+      go(5, 0, xa, ya);
+      go(6, 28, xb, ya);
+    }
+  }
+}
+
+template <bool kPerm>
+__device__ __forceinline__ uint64_t rows_of_window_row(int i) {
+  uint64_t m = 0;
+#pragma unroll
+  for (int j = 0; j < WS; ++j) m |= 1ull << token_row<kPerm>(i, j);
+  return m;
+}
+template <bool kPerm>
+__device__ __forceinline__ uint64_t rows_of_window_col(int j) {
+  uint64_t m = 0;
+#pragma unroll
+  for (int i = 0; i < WS; ++i) m |= 1ull << token_row<kPerm>(i, j);
+  return m;
+}
+
+#define TMEM_LD_X1(taddr, r0) asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r0) : "r"(taddr))
+
 // Host: tensor map over an image-order (B, H, W, pix_stride) bf16 tensor, box (32 ch, bx, by, 1), 64B swizzle
 // (swin_attn_tc.cu).  The seven box shapes of a launch, indexed like TmaMaps.
 bool encode_window_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pix_stride, int bx, int by);
 bool tma_available();
+void job_grid(const Problem& p, int sms, int* n_win, int* win_per_job, int* grid);
+int sm_count();
 constexpr int kBoxX[7] = {WS, WS - kShift, WS - kShift, kShift, kShift, WS - kShift, kShift};
 constexpr int kBoxY[7] = {WS, WS - kShift, kShift, WS - kShift, kShift, WS, WS};
 

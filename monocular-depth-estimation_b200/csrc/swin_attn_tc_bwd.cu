@@ -76,68 +76,6 @@ __host__ __device__ inline SmemMapB smem_map_b() {
   return m;
 }
 
-// Window w of the job -> (image, window row, window column); advance by a few windows without divisions.
-struct WinIter {
-  int b, wy, wx, w;
-  __device__ __forceinline__ void init(const Problem& p, int first) {
-    w = first;
-    wx = first % p.nWx;
-    const int r = first / p.nWx;
-    wy = r % p.nWy;
-    b = r / p.nWy;
-  }
-  __device__ __forceinline__ void advance(const Problem& p, int step) {
-    w += step;
-    wx += step;
-    while (wx >= p.nWx) { wx -= p.nWx; ++wy; }
-    while (wy >= p.nWy) { wy -= p.nWy; ++b; }
-  }
-};
-
-// One window of one tensor, global -> shared (kStore = false) or shared -> global (kStore = true):
-// 1 box (un-shifted) or the 2 / 4 parts of a shifted window (see swin_attn_tc.cu::load_window).
-template <bool kShifted, bool kStore>
-__device__ __forceinline__ void move_window(const CUtensorMap* maps, uint32_t smem_addr, uint32_t bar, const Problem& p,
-                                            int b, int wy, int wx, int h) {
-  const int ch = h * kHeadDim;
-  auto go = [&](int map, uint32_t row, int x, int y) {
-    if (kStore) tma_store_4d(maps + map, smem_addr + row * 64, ch, x, y, b);
-    else tma_load_4d(smem_addr + row * 64, maps + map, bar, ch, x, y, b);
-  };
-  if (!kShifted) {
-    go(0, 0, wx * WS, wy * WS);
-  } else {
-    const int xa = wx * WS + kShift, ya = wy * WS + kShift;
-    const int xb = wx == p.nWx - 1 ? 0 : wx * WS + WS, yb = wy == p.nWy - 1 ? 0 : wy * WS + WS;
-    if (wy == p.nWy - 1) {
-      go(1, 0, xa, ya);
-      go(2, 16, xa, yb);
-      go(3, 28, xb, ya);
-      go(4, 40, xb, yb);
-    } else {
-      go(5, 0, xa, ya);
-      go(6, 28, xb, ya);
-    }
-  }
-}
-
-template <bool kPerm>
-__device__ __forceinline__ uint64_t rows_of_window_row(int i) {
-  uint64_t m = 0;
-#pragma unroll
-  for (int j = 0; j < WS; ++j) m |= 1ull << token_row<kPerm>(i, j);
-  return m;
-}
-template <bool kPerm>
-__device__ __forceinline__ uint64_t rows_of_window_col(int j) {
-  uint64_t m = 0;
-#pragma unroll
-  for (int i = 0; i < WS; ++i) m |= 1ull << token_row<kPerm>(i, j);
-  return m;
-}
-
-#define TMEM_LD_X1(taddr, r0) asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r0) : "r"(taddr))
-
 template <bool kShifted>
 __global__ void __launch_bounds__(kThreadsB, 1)
 tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant__ TmaMapsB maps) {
@@ -490,13 +428,6 @@ bool tc_backward_supported(const Problem& p, int dtype) {
 }
 
 cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** err) {
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
-  }
   tcb::TmaMapsB maps;
   memset(&maps, 0, sizeof(maps));
   const bool shifted = p.shift != 0;
@@ -518,16 +449,11 @@ cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** e
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
     return e;
   }
-  // jobs = heads x window chunks, at most one wave of CTAs; chunks hold an even number of windows
-  const int n_win = p.B * p.nWy * p.nWx;
-  int chunks = sms / p.nH;
-  if (chunks < 1) chunks = 1;
-  int per = (n_win + chunks - 1) / chunks;
-  per += per & 1;
-  chunks = (n_win + per - 1) / per;
+  int n_win, per, grid;
+  tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
   e = cudaMemsetAsync(p.d_table, 0, sizeof(float) * 169 * p.nH, st);
   if (e != cudaSuccess) return e;
-  kernel<<<chunks * p.nH, tcb::kThreadsB, map.total, st>>>(p, n_win, per, maps);
+  kernel<<<grid, tcb::kThreadsB, map.total, st>>>(p, n_win, per, maps);
   count_launch();
   return cudaGetLastError();
 }

@@ -36,7 +36,8 @@ def main():
     torch.cuda.synchronize()
     lib.swin_attn_debug_set_trace(None)
     t = trace.cpu().view(64, 16)
-    t0 = int(t[t > 0].min())
+    t0 = int(t[:, :14][t[:, :14] > 0].min())
+    print(f"kernel entry {int(t[0][14]) - t0}, exit {int(t[0][15]) - t0} (cycles relative to the first stamp)")
     print("pair " + " ".join(f"{e:>12s}" for e in EV))
     for n in range(30):
         if int(t[n].max()) == 0:
