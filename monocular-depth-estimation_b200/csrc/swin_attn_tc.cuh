@@ -1,38 +1,7 @@
-// Shifted-window attention forward for sm_100a: TMA-gathered window tiles, tcgen05 bf16
-// MMAs with fp32 accumulators in tensor memory, one persistent CTA per SM.
-//
-// Tile = one (window, head): Q, K, V are 49 x 32 bf16.  Two tiles form a PAIR that is
-// stacked along M: tile 0 owns TMEM lanes 0-63, tile 1 lanes 64-127, and one
-// `tcgen05.ld.32x32b` hands every thread of a softmax warp one complete row of S -- no
-// cross-lane reduction is needed for the row max / row sum.
-//
-//   producer (warp 0, one thread): the window partition, the cyclic shift and the
-//       right/bottom padding are folded into TMA tensor-map addressing.  A tensor map
-//       over the image-order (B,H,W,channels) tensor with box (32 ch, 7 x, 7 y) lands a
-//       window's 49 rows in a 64B-swizzled K-major tile.  Shifted blocks split every
-//       window at the wrap point into four boxes (4x4, 3x4, 4x3, 3x3 for ws 7 / shift 3)
-//       whose start coordinates wrap modulo the padded extent; their rows are stored
-//       part after part ("permuted" token order, every part on an even row so that the
-//       TMA destination stays 128B-aligned).  Out-of-bounds (padding) elements are
-//       zero-filled by the TMA unit.
-//   pad helper (warp 2): padding tokens are not zero in the reference -- they carry the
-//       Linear bias (newcrf_layers.py:212-217).  All pad tokens of a head share ONE
-//       vector, so it is written once per tile into the spare row 49 of the K and V
-//       tiles: S[:,49] = q . k_pad comes out of the QK^T MMA for free and stands in for
-//       every pad column; P[:,49] = sum of the pad columns' probabilities multiplies
-//       v_pad in the PV MMA.
-//   MMA warp (1), one thread: both tiles of a pair go through ONE accumulator (M = 128):
-//       S = [Q0;Q1] [K0;K1]^T (M128 N112 K32): tile t's scores are rows 64t.., columns 56t..
-//       O = [P0;P1] [V0|V1|1] (M128 N96 K64, V MN-major): tile t's output is rows 64t.., cols 32t..;
-//           column 64 multiplies a constant ones tile and so holds the softmax row sums
-//       (the off-diagonal blocks are computed and ignored; the tensor pipe is far from the bound)
-//   softmax warpgroups (3 x 4 warps): S row from TMEM, scale + relative position bias
-//       (table staged in smem) + analytic SW-MSA mask, exp2, row sum, P as bf16 into a
-//       128B-swizzled smem tile; then O row from TMEM, normalise, store bf16 to
-//       un-shifted, cropped image coordinates.
-//
-// Everything is synchronised with mbarriers; the tensor pipe, the softmax warps and the
-// loads of the next pairs overlap.
+// Shared pieces of the tcgen05 shifted-window attention kernels for sm_100a (forward: swin_attn_tc.cu,
+// backward: swin_attn_tc_bwd.cu): PTX wrappers (mbarrier, TMA tensor loads / stores, tcgen05 MMA / TMEM
+// load, descriptors), the window -> TMA box mapping that folds window partition, cyclic shift, padding,
+// window reverse and crop into tensor-map addressing, and the token order of a tile.
 #pragma once
 #include <cuda.h>
 
@@ -46,26 +15,16 @@ namespace tc {
 constexpr int WS = 7;
 constexpr int N = 49;
 constexpr int kShift = 3;           // the only non-zero shift served here (ws // 2, as the reference uses)
-constexpr int kStages = 4;          // smem stages, one PAIR of tiles each
-constexpr int kSlots = 3;           // accumulator slots == softmax warpgroups
-constexpr int kThreads = 512;       // 4 control warps + 3 x 4 softmax warps
 constexpr int kTileBytes = 64 * 64;       // 64 rows x 32 bf16
 constexpr int kKTile1 = 56 * 64;          // K tile 1 follows the 56 MMA rows of K tile 0
 constexpr int kPTileBytes = 64 * 128;     // 64 rows x 64 bf16
-constexpr int kStageBytes = 7 * kTileBytes;  // q0 q1 | k0 k1 | v0 v1 | ones (row-sum column of the PV MMA)
 constexpr int kBoxBytes = N * 64;         // bytes one tile of one tensor receives from TMA
-constexpr int kSlotCols = 128;      // S: 112 columns (2 x 56); O (64 columns) reuses them once S has been read
 constexpr float kLog2e = 1.4426950408889634f;
 
-// Tensor maps of one launch: [0] = whole window (7x7); [1..4] = the four parts of a shifted
-// window that wraps in y, (x extent, y extent) = (4,4) (4,3) (3,4) (3,3), stored at rows
-// 0/16/28/40; [5..6] = the two parts (4,7) (3,7) of a shifted window that does not wrap in y,
-// stored at rows 0/28 (same token order).
-struct TmaMaps {
-  CUtensorMap q[7];
-  CUtensorMap k[7];
-  CUtensorMap v[7];
-};
+// Tensor maps of one launch, per tensor: [0] = whole window (7x7); [1..4] = the four parts of a shifted
+// window that wraps in y, (x extent, y extent) = (4,4) (4,3) (3,4) (3,3), stored at rows 0/16/28/40;
+// [5..6] = the two parts (4,7) (3,7) of a shifted window that does not wrap in y, stored at rows 0/28
+// (same token order).  kBoxX / kBoxY below hold the extents.
 
 // ---- PTX wrappers -----------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -95,13 +54,6 @@ __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarr
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int kPending>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
 
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
@@ -212,71 +164,7 @@ __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     if ((p).trace != nullptr && blockIdx.x == 0) (p).trace[(n) * 16 + (e)] = clock64(); \
   } while (0)
 
-// ---- shared memory map ----------------------------------------------------------
-struct SmemMap {
-  uint32_t stages;    // kStages * kStageBytes
-  uint32_t pslots;    // kSlots * 2 * kPTileBytes
-  uint32_t bias;      // nH * 169 floats, already multiplied by log2(e)
-  uint32_t padv;      // k_pad then v_pad of every head (bf16, 64 B per head), zeros when absent
-  uint32_t bars;      // mbarriers
-  uint32_t tmem_ptr;
-  uint32_t total;
-};
-__host__ __device__ inline SmemMap smem_map(int nH) {
-  SmemMap m;
-  m.stages = 0;
-  m.pslots = m.stages + kStages * kStageBytes;
-  m.bias = m.pslots + kSlots * 2 * kPTileBytes;
-  m.padv = (m.bias + nH * 169 * 4 + 15) & ~15u;
-  m.bars = m.padv + 2 * nH * 64;
-  m.tmem_ptr = m.bars + 8 * (2 * kStages + 4 * kSlots);
-  m.total = m.tmem_ptr + 16;
-  return m;
-}
-
 // ---- tiles and token order --------------------------------------------------------
-struct TileCoord {
-  int b, wy, wx, h;
-  bool valid;
-};
-__device__ __forceinline__ TileCoord tile_coord(const Problem& p, int tile, int n_tiles) {
-  TileCoord c;
-  c.valid = tile < n_tiles;
-  int t = c.valid ? tile : 0;
-  int win = t / p.nH;
-  c.h = t - win * p.nH;
-  c.wx = win % p.nWx;
-  int r = win / p.nWx;
-  c.wy = r % p.nWy;
-  c.b = r / p.nWy;
-  return c;
-}
-
-
-// Tile index t -> (image, window row, window column, head) and t += stride without divisions.
-struct TileIter {
-  int b, wy, wx, h;     // current tile
-  int db, dwy, dwx, dh; // mixed-radix digits of the stride
-  int tile, stride;
-  __device__ __forceinline__ void init(const Problem& p, int first, int step) {
-    tile = first; stride = step;
-    int win = first / p.nH; h = first - win * p.nH;
-    wx = win % p.nWx; int r = win / p.nWx; wy = r % p.nWy; b = r / p.nWy;
-    int dw = step / p.nH; dh = step - dw * p.nH;
-    dwx = dw % p.nWx; int dr = dw / p.nWx; dwy = dr % p.nWy; db = dr / p.nWy;
-  }
-  __device__ __forceinline__ void next(const Problem& p) {
-    tile += stride;
-    h += dh; int c = h >= p.nH; h -= c ? p.nH : 0;
-    wx += dwx + c; c = wx >= p.nWx; wx -= c ? p.nWx : 0;
-    wy += dwy + c; c = wy >= p.nWy; wy -= c ? p.nWy : 0;
-    b += db + c;
-  }
-  __device__ __forceinline__ TileCoord coord(int n_tiles) const {
-    TileCoord c; c.b = b; c.wy = wy; c.wx = wx; c.h = h; c.valid = tile < n_tiles; return c;
-  }
-};
-
 // Row r of a tile <-> token (i, j) of the window.  Natural order for un-shifted blocks;
 // for shifted blocks the four TMA parts follow one another:
 //   rows [0,16): i<4, j<4   [16,28): i>=4, j<4   [28,40): i<4, j>=4   [40,49): i>=4, j>=4

@@ -98,13 +98,38 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
   const uint32_t bar_r = bar_o + 8 * kSlotsB;              // [kSlotsB]  outputs read, slot reusable
 
   // ---- one-time setup -------------------------------------------------------
-  {
-    // Every row the TMA boxes never write (rows 49.. of each tile) must stay finite: as the K dimension
-    // of a phase-2 product they are multiplied by zero columns of P / dS.
-    for (int i = tid; i < kStagesB * kStageBytesB / 16; i += kThreadsB)
-      *reinterpret_cast<uint4*>(smem + map.stages + i * 16) = make_uint4(0u, 0u, 0u, 0u);
+  // As in the forward: mbarrier init, one CTA barrier, then the producers start loading while the other 10
+  // warps fill what TMA never writes, stage the bias, build the identity and allocate TMEM.
+  if (tid == 0) {
+    for (int i = 0; i < kStagesB; ++i) {
+      mbar_init(bar_full + 8 * i, 2);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < kSlotsB; ++i) {
+      mbar_init(bar_s + 8 * i, 1);
+      mbar_init(bar_p + 8 * i, 128);
+      mbar_init(bar_o + 8 * i, 1);
+      mbar_init(bar_r + 8 * i, 128);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (warp != 0 && warp != 3) {
+    constexpr int kFill = kThreadsB - 64;
+    const int t10 = tid - (warp < 3 ? 32 : 64);   // 0 .. 319 over the 10 non-producer warps
+    const float bias_v = t10 < 169 ? p.table[t10 * p.nH + h] * kLog2e : 0.f;
+    if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
+    // Rows 49-63 of every tile (the TMA boxes write rows 0-48) must stay finite: as the K dimension of a
+    // phase-2 product they are multiplied by zero columns of P / dS.  K / V tile 1 start at row 56 of tile 0.
+    for (int i = t10; i < kStagesB * 8 * 15 * 4; i += kFill) {
+      const int chunk = i & 3, rr = (i >> 2) % 15, t8 = ((i >> 2) / 15) & 7, s = (i >> 2) / 120;
+      const int kind = t8 >> 1, t = t8 & 1;       // 0 q, 1 k, 2 v, 3 dO
+      if ((kind == 1 || kind == 2) && t == 0 && rr >= 7) continue;
+      const uint32_t base = kind == 0 ? bq_off(t) : kind == 1 ? bk_off(t) : kind == 2 ? bv_off(t) : bdo_off(t);
+      *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytesB + base + (49 + rr) * 64 + (chunk << 4)) = make_uint4(0u, 0u, 0u, 0u);
+    }
     // identity, K-major 128B-swizzled 64 x 64 bf16: element (n, n) = 1
-    for (int i = tid; i < 64 * 8; i += kThreadsB) {
+    for (int i = t10; i < 64 * 8; i += kFill) {
       const int n = i >> 3, chunk = i & 7;
       uint4 v = make_uint4(0u, 0u, 0u, 0u);
       if (chunk == (n >> 3)) {
@@ -114,37 +139,21 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
       }
       *reinterpret_cast<uint4*>(smem + map.ident + n * 128 + ((chunk ^ (n & 7)) << 4)) = v;
     }
-    float* bias = reinterpret_cast<float*>(smem + map.bias);
-    float* bins = reinterpret_cast<float*>(smem + map.bins);
-    for (int i = tid; i < 176; i += kThreadsB) {
-      bias[i] = i < 169 ? p.table[i * p.nH + h] * kLog2e : 0.f;
-      bins[i] = 0.f;
+    if (t10 < 176) {
+      reinterpret_cast<float*>(smem + map.bias)[t10] = bias_v;
+      reinterpret_cast<float*>(smem + map.bins)[t10] = 0.f;
     }
-    if (tid == 0) {
-      for (int i = 0; i < kStagesB; ++i) {
-        mbar_init(bar_full + 8 * i, 2);
-        mbar_init(bar_empty + 8 * i, 1);
-      }
-      for (int i = 0; i < kSlotsB; ++i) {
-        mbar_init(bar_s + 8 * i, 1);
-        mbar_init(bar_p + 8 * i, 128);
-        mbar_init(bar_o + 8 * i, 1);
-        mbar_init(bar_r + 8 * i, 128);
-      }
-      fence_barrier_init();
-      for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
-        tma_prefetch_desc(&maps.q[i]); tma_prefetch_desc(&maps.k[i]); tma_prefetch_desc(&maps.v[i]);
-        tma_prefetch_desc(&maps.d_o[i]); tma_prefetch_desc(&maps.dq[i]); tma_prefetch_desc(&maps.dk[i]);
-        tma_prefetch_desc(&maps.dv[i]);
-      }
-    }
-    if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
     fence_proxy_async();
     tc_fence_before();
-    __syncthreads();
+    named_barrier(5, kFill);
     tc_fence_after();
+  } else if (lane == 0) {
+    for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
+      tma_prefetch_desc(&maps.q[i]); tma_prefetch_desc(&maps.k[i]); tma_prefetch_desc(&maps.v[i]);
+      tma_prefetch_desc(&maps.d_o[i]);
+    }
   }
-  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + map.tmem_ptr);
+  const uint32_t tmem_base = warp != 0 && warp != 3 ? *reinterpret_cast<volatile uint32_t*>(smem + map.tmem_ptr) : 0u;
 
   if (warp == 0 || warp == 3) {
     // ===== TMA producers: warp 0 -> tile 0 of every pair, warp 3 -> tile 1 =====================
@@ -155,16 +164,21 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
       const int s = n % kStagesB;
       const uint32_t st = sbase + map.stages + s * kStageBytesB, bar = bar_full + 8 * s;
       mbar_wait(bar_empty + 8 * s, ((n / kStagesB) & 1) ^ 1);
-      if (elect_one()) {
-        if (it.w < w1) {
+      if (it.w < w1) {
+        if (elect_one()) {
           mbar_expect_tx(bar, kLoadBytes);
           move_window<kShifted, false>(maps.q, st + bq_off(t), bar, p, it.b, it.wy, it.wx, h);
           move_window<kShifted, false>(maps.k, st + bk_off(t), bar, p, it.b, it.wy, it.wx, h);
           move_window<kShifted, false>(maps.d_o, st + bdo_off(t), bar, p, it.b, it.wy, it.wx, h);
           move_window<kShifted, false>(maps.v, st + bv_off(t), bar, p, it.b, it.wy, it.wx, h);
-        } else {
-          mbar_arrive(bar);
         }
+      } else {
+        // Half-empty last pair of the job.  Rows 0-7 of K tile 1 are rows 56-63 of the K dimension of the dQ
+        // product of tile 0 (multiplied by zero columns of dS): they must be finite even if never loaded.
+        *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytesB + bk_off(t) + lane * 16) = make_uint4(0u, 0u, 0u, 0u);
+        fence_proxy_async();
+        __syncwarp();
+        if (elect_one()) mbar_arrive(bar);
       }
       __syncwarp();
     }
