@@ -111,6 +111,14 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape,
                            const void* q_pad, const void* k_pad, const void* v_pad,
                            const float* bias_table, void* o);
 
+/* LayerNorm of the residual stream (fp32, or bf16 once an autocast Linear has produced it) over the last
+ * dimension, in fp32 arithmetic, written as the (bf16 or fp32) operand of the following Linear: the norm1 / norm2 of the block forwards (newcrf_layers.py:207,253, swin_transformer.py:201,243)
+ * fused with the casts torch.autocast inserts around it.  x: (rows, channels) of x_dtype, dense;
+ * gamma, beta: (channels) fp32; out: (rows, channels) of out_dtype.  channels in {128, 192, 256, 384, 512, 768,
+ * 1024, 1536, 3072}.  Biased variance, eps inside the square root, as nn.LayerNorm. */
+int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, const float* beta, float eps, int64_t rows,
+                           int32_t channels, void* out, int32_t out_dtype, void* stream);
+
 /* Number of kernel launches issued by this library since load (all threads). */
 uint64_t swin_attn_launch_count(void);
 

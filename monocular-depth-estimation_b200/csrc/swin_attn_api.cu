@@ -165,6 +165,23 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape, const void* q, const 
   return 0;
 }
 
+int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, const float* beta, float eps, int64_t rows, int32_t channels,
+                           void* out, int32_t out_dtype, void* stream) {
+  if (!x || !gamma || !beta || !out) return fail("layernorm: x, gamma, beta and out must be non-null");
+  if (rows < 0 || rows > (int64_t)8 * 0x7fffffff) return fail("layernorm: bad row count");
+  if ((out_dtype != SWIN_ATTN_F32 && out_dtype != SWIN_ATTN_BF16) || (x_dtype != SWIN_ATTN_F32 && x_dtype != SWIN_ATTN_BF16))
+    return fail("layernorm: x_dtype / out_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
+  if (!layernorm_supported(channels))
+    return fail("layernorm: channels must be one of 128, 192, 256, 384, 512, 768, 1024, 1536, 3072 (got " + std::to_string(channels) + ")");
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta) |
+       reinterpret_cast<uintptr_t>(out)) & 7)
+    return fail("layernorm: pointers must be 8-byte aligned");
+  if (rows == 0) return 0;
+  cudaError_t e = launch_layernorm(x, x_dtype, gamma, beta, eps, rows, channels, out, out_dtype, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail_cuda("layernorm launch", e);
+  return 0;
+}
+
 // Debug hook (not part of the public header): device buffer of >= 16 * pairs-per-CTA int64 that receives
 // clock64 stamps of CTA 0 of the tcgen05 kernel; pass NULL to switch tracing off.
 void swin_attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }

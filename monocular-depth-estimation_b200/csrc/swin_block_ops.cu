@@ -1,0 +1,103 @@
+// Block plumbing around the attention kernels: LayerNorm of the residual stream
+// (fp32 in stage 0, bf16 after the first autocast Linear) written directly as the bf16 operand of the following Linear.
+//
+// Under torch.autocast the reference runs  x(fp32) -> LayerNorm (fp32 out) -> cast to bf16 -> Linear
+// (newcrf_layers.py:207,253 / swin_transformer.py:201,243): 4+4 bytes per element for the norm and 4+2 for the
+// cast.  This kernel reads x once and writes bf16 once (6 bytes per element), with the same fp32 arithmetic
+// (mean, biased variance, rsqrt(var + eps), affine), so the Linear sees the same bf16 values up to the
+// rounding of the fp32 statistics.
+//
+// One warp per row; every lane keeps its C/32 elements in registers (two-pass variance, no re-read).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "swin_common.cuh"
+
+namespace swin {
+
+__device__ __forceinline__ float2 load2(const float* p, int i) { return reinterpret_cast<const float2*>(p)[i]; }
+__device__ __forceinline__ float2 load2(const __nv_bfloat16* p, int i) {
+  return __bfloat1622float2(reinterpret_cast<const __nv_bfloat162*>(p)[i]);
+}
+
+template <int NC, typename TIn, typename TOut>   // NC pairs of elements per lane: C = 64 * NC
+__global__ void __launch_bounds__(256) layernorm_rows_kernel(const TIn* __restrict__ x, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps, int64_t rows,
+                                                             TOut* __restrict__ out) {
+  constexpr int C = 64 * NC;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const TIn* xr = x + row * C;
+  float2 v[NC];
+  float sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    v[k] = load2(xr, lane + 32 * k);
+    sum += v[k].x + v[k].y;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float mean = sum * (1.0f / C);
+  float sq = 0.f;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const float a = v[k].x - mean, b = v[k].y - mean;
+    sq = fmaf(a, a, sq);
+    sq = fmaf(b, b, sq);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq * (1.0f / C) + eps);
+  const float2* g2 = reinterpret_cast<const float2*>(gamma);
+  const float2* b2 = reinterpret_cast<const float2*>(beta);
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const float2 g = g2[lane + 32 * k], b = b2[lane + 32 * k];
+    const float y0 = fmaf((v[k].x - mean) * rstd, g.x, b.x), y1 = fmaf((v[k].y - mean) * rstd, g.y, b.y);
+    if constexpr (sizeof(TOut) == 2) {
+      reinterpret_cast<__nv_bfloat162*>(out + row * C)[lane + 32 * k] = __floats2bfloat162_rn(y0, y1);
+    } else {
+      reinterpret_cast<float2*>(out + row * C)[lane + 32 * k] = make_float2(y0, y1);
+    }
+  }
+}
+
+template <int NC>
+static cudaError_t launch_ln(const void* x, int x_dtype, const float* g, const float* b, float eps, int64_t rows, void* out,
+                             int out_dtype, cudaStream_t st) {
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  using bf = __nv_bfloat16;
+  if (x_dtype == SWIN_ATTN_F32 && out_dtype == SWIN_ATTN_BF16)
+    layernorm_rows_kernel<NC, float, bf><<<grid, 256, 0, st>>>(static_cast<const float*>(x), g, b, eps, rows, static_cast<bf*>(out));
+  else if (x_dtype == SWIN_ATTN_F32)
+    layernorm_rows_kernel<NC, float, float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), g, b, eps, rows, static_cast<float*>(out));
+  else if (out_dtype == SWIN_ATTN_BF16)
+    layernorm_rows_kernel<NC, bf, bf><<<grid, 256, 0, st>>>(static_cast<const bf*>(x), g, b, eps, rows, static_cast<bf*>(out));
+  else
+    layernorm_rows_kernel<NC, bf, float><<<grid, 256, 0, st>>>(static_cast<const bf*>(x), g, b, eps, rows, static_cast<float*>(out));
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_layernorm(const void* x, int x_dtype, const float* g, const float* b, float eps, int64_t rows, int channels,
+                             void* out, int out_dtype, cudaStream_t st) {
+  switch (channels / 64) {
+#define SWIN_LN_CASE(NC) case NC: return launch_ln<NC>(x, x_dtype, g, b, eps, rows, out, out_dtype, st)
+    SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
+    SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24); SWIN_LN_CASE(48);
+#undef SWIN_LN_CASE
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+bool layernorm_supported(int channels) {
+  if (channels % 64) return false;
+  switch (channels / 64) {
+    case 2: case 3: case 4: case 6: case 8: case 12: case 16: case 24: case 48: return true;
+    default: return false;
+  }
+}
+
+}  // namespace swin

@@ -102,6 +102,10 @@ cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** er
 bool tc_backward_supported(const Problem& p, int dtype);
 cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** err);
 
+cudaError_t launch_layernorm(const void* x, int x_dtype, const float* gamma, const float* beta, float eps, int64_t rows, int channels,
+                             void* out, int out_dtype, cudaStream_t st);
+bool layernorm_supported(int channels);
+
 void count_launch(int n = 1);
 
 }  // namespace swin

@@ -192,9 +192,9 @@ class CRFBlock(nn.Module):
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(self.norm1(x).view(b, h, w, c), v, self.shift_size)
+        a = self.attn.forward_image(ops.norm_for_linear(self.norm1, x).view(b, h, w, c), v, self.shift_size)
         x = x + self.drop_path(a.reshape(b, h * w, self.v_dim))
-        return x + self.drop_path(self.mlp(self.norm2(x)))
+        return x + self.drop_path(self.mlp(ops.norm_for_linear(self.norm2, x)))
 
 
 class BasicCRFLayer(nn.Module):
@@ -273,9 +273,9 @@ class SwinTransformerBlock(nn.Module):
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(self.norm1(x).view(b, h, w, c), self.shift_size)
+        a = self.attn.forward_image(ops.norm_for_linear(self.norm1, x).view(b, h, w, c), self.shift_size)
         x = x + self.drop_path(a.reshape(b, h * w, c))
-        return x + self.drop_path(self.mlp(self.norm2(x)))
+        return x + self.drop_path(self.mlp(ops.norm_for_linear(self.norm2, x)))
 
 
 class PatchMerging(nn.Module):
@@ -294,7 +294,7 @@ class PatchMerging(nn.Module):
         if H % 2 or W % 2:
             x = F.pad(x, (0, 0, 0, W % 2, 0, H % 2))
         x = torch.cat([x[:, 0::2, 0::2], x[:, 1::2, 0::2], x[:, 0::2, 1::2], x[:, 1::2, 1::2]], -1)
-        return self.reduction(self.norm(x.view(b, -1, 4 * c)))
+        return self.reduction(ops.norm_for_linear(self.norm, x.view(b, -1, 4 * c)))
 
 
 class BasicLayer(nn.Module):

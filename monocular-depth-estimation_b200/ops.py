@@ -229,6 +229,44 @@ def _backward(ctx, d_o, d_lse):
 _fwd.register_autograd(_backward, setup_context=_setup_context)
 
 
+_LN_CHANNELS = (128, 192, 256, 384, 512, 768, 1024, 1536, 3072)
+
+
+@torch.library.custom_op("swin_attn::layer_norm", mutates_args=(), device_types="cuda")
+def _layer_norm(x: Tensor, weight: Tensor, bias: Tensor, eps: float, out_bf16: bool) -> Tensor:
+    """LayerNorm over the last dim of an fp32 / bf16 tensor in fp32 arithmetic, written as bf16 (or fp32):
+    ``swin_layernorm_forward``."""
+    if x.dtype not in _DTYPES:
+        raise RuntimeError(f"swin_attn::layer_norm: dtype {x.dtype} is not supported (float32 or bfloat16)")
+    lib = _lib.load()
+    x = x.contiguous()
+    c = x.shape[-1]
+    out = torch.empty(x.shape, dtype=torch.bfloat16 if out_bf16 else torch.float32, device=x.device)
+    w, b = weight.detach().float().contiguous(), bias.detach().float().contiguous()
+    with torch.cuda.device(x.device):
+        _lib.check(lib.swin_layernorm_forward(_ptr(x), _DTYPES[x.dtype], _ptr(w), _ptr(b), float(eps), x.numel() // c, c, _ptr(out),
+                                              _lib.BF16 if out_bf16 else _lib.F32,
+                                              ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return out
+
+
+@_layer_norm.register_fake
+def _(x, weight, bias, eps, out_bf16):
+    return x.new_empty(x.shape, dtype=torch.bfloat16 if out_bf16 else torch.float32)
+
+
+def norm_for_linear(norm: torch.nn.Module, x: Tensor) -> Tensor:
+    """``norm(x)`` for a LayerNorm whose output only feeds a Linear.  Inference under bf16 autocast takes the
+    fused kernel (fp32 in, bf16 out: the values autocast would hand the Linear); every other case -- training,
+    fp32 mode, unsupported widths, non-LayerNorm ``norm_layer`` -- is the module itself."""
+    if (type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
+            and x.dtype in _DTYPES and not torch.is_grad_enabled() and torch.is_autocast_enabled()
+            and torch.get_autocast_dtype("cuda") == torch.bfloat16 and len(norm.normalized_shape) == 1
+            and x.shape[-1] in _LN_CHANNELS):
+        return torch.ops.swin_attn.layer_norm(x, norm.weight, norm.bias, norm.eps, True)
+    return norm(x)
+
+
 def window_attention(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, window: int, shift: int,
                      num_heads: int, scale: Optional[float] = None, packed_pad: Optional[Tensor] = None,
                      v_pad: Optional[Tensor] = None, impl: int = _lib.IMPL_AUTO,

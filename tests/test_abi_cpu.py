@@ -13,7 +13,7 @@ from conftest import ROOT
 def _declared():
     text = open(os.path.join(ROOT, "include", "swin_attn.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(swin_attn_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(swin_(?:attn|layernorm)_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_library_exports_every_declared_symbol():
@@ -71,3 +71,13 @@ def test_ops_have_no_cpu_kernel():
     from mde_b200 import ops
     with pytest.raises((RuntimeError, NotImplementedError)):
         ops.window_attention(torch.zeros(1, 7, 7, 96), None, torch.zeros(169, 1), 7, 0, 1)
+
+
+def test_layernorm_validation_without_gpu():
+    lib = _lib.load()
+    buf = (ctypes.c_float * 256)()
+    ptr = ctypes.cast(buf, ctypes.c_void_p)
+    assert lib.swin_layernorm_forward(ptr, _lib.F32, ptr, ptr, 1e-5, 1, 100, ptr, _lib.BF16, None) != 0
+    assert b"channels must be one of" in lib.swin_attn_last_error()
+    assert lib.swin_layernorm_forward(None, _lib.F32, ptr, ptr, 1e-5, 1, 128, ptr, _lib.BF16, None) != 0
+    assert lib.swin_layernorm_forward(ptr, _lib.BF16, ptr, ptr, 1e-5, 0, 128, ptr, _lib.F32, None) == 0   # empty input: no launch

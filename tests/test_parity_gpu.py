@@ -359,6 +359,39 @@ def test_full_size_backward_properties(shape, shift):
     assert rel_err(g_tc[0][:1].float(), gp) < TOL_BF16
 
 
+@pytest.mark.parametrize("c", [128, 192, 256, 384, 512, 768, 1024, 1536, 3072])
+def test_fused_layernorm_matches_torch(c):
+    """swin_layernorm_forward: fp32 out within 2e-6 of F.layer_norm; bf16 out == what autocast hands the Linear
+    (F.layer_norm in fp32, then a bf16 cast) up to one bf16 ulp on a vanishing fraction of elements."""
+    gen = torch.Generator(device=DEV).manual_seed(c)
+    x = (3.0 * torch.randn(1003, c, device=DEV, generator=gen) + 0.7).view(17, 59, c)   # rows not a multiple of 8
+    w = 1.0 + 0.3 * torch.randn(c, device=DEV, generator=gen)
+    b = 0.2 * torch.randn(c, device=DEV, generator=gen)
+    want = torch.nn.functional.layer_norm(x, (c,), w, b, 1e-5)
+    got32 = torch.ops.swin_attn.layer_norm(x, w, b, 1e-5, False)
+    assert got32.dtype == torch.float32 and got32.shape == x.shape
+    assert rel_err(got32, want.double()) < 2e-6
+    got16 = torch.ops.swin_attn.layer_norm(x, w, b, 1e-5, True)
+    assert got16.dtype == torch.bfloat16
+    diff = (got16.float() - want.bfloat16().float()).abs()
+    assert float((diff > 0).float().mean()) < 5e-3                       # rounding-boundary flips only
+    assert float((diff / want.abs().clamp_min(1e-3)).max()) < 2 ** -7    # and never more than one bf16 ulp
+    # bf16 residual stream (what the stages after the first autocast Linear carry): fp32 arithmetic on the bf16 values
+    xb = x.bfloat16()
+    want_b = torch.nn.functional.layer_norm(xb.float(), (c,), w, b, 1e-5)
+    got_b = torch.ops.swin_attn.layer_norm(xb, w, b, 1e-5, True)
+    diff = (got_b.float() - want_b.bfloat16().float()).abs()
+    assert float((diff > 0).float().mean()) < 5e-3 and float((diff / want_b.abs().clamp_min(1e-3)).max()) < 2 ** -7
+    # the layer helper takes the fused path only for inference under bf16 autocast
+    ln = torch.nn.LayerNorm(c).to(DEV)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        assert ops.norm_for_linear(ln, x).dtype == torch.bfloat16
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        assert ops.norm_for_linear(ln, x).dtype == torch.float32        # grad mode: the module itself
+    with torch.no_grad():
+        assert ops.norm_for_linear(ln, x).dtype == torch.float32        # fp32 mode
+
+
 def test_library_counts_launches():
     before = _lib.launch_count()
     x = torch.zeros(1, 7, 7, 96, device=DEV)
