@@ -220,7 +220,9 @@ def run_ours(args, env):
         k_bytes, k_flops = sum(r[2] for r in recs), sum(r[3] for r in recs)
         achieved = k_bytes / (k_ms * 1e-3) / 1e9
         return {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)", "traffic": traffic.get(name.split()[1]),
+                "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
+                "traffic": (traffic.get(name.split()[1]) or {}).get("dram_bytes_per_launch"),
+                "traffic_of": traffic.get(name.split()[1]),
                 "launches": len(recs), "kernel_ms_per_step": k_ms / args.steps, "share_of_step": k_ms / 1e3 / t_res,
                 "useful_tflops": k_flops / (k_ms * 1e-3) / 1e12,
                 "tensor_frac_of_sustained_bf16": k_flops / (k_ms * 1e-3) / 1e12 / tf}

@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Error statistics of the bf16 forward kernels against the fp64 oracle: max-normalised error, RMS error and
+"""(diagnostic script, not collected by pytest; lives under tests/ because it uses the oracle)
+Error statistics of the bf16 forward kernels against the fp64 oracle: max-normalised error, RMS error and
 mean signed error (bias), tcgen05 vs CUDA-core kernel, padded / shifted cases."""
 import os
 import sys
