@@ -30,16 +30,20 @@ namespace tcf {
 
 using namespace tc;
 
-constexpr int kStagesF = 6;      // 3 pairs in flight in the softmax warpgroups + 3 prefetched
-constexpr int kSlotsF = 3;
+// Two rings: Q/K tiles live only until the S MMA has consumed them, V tiles until the PV MMA has.
+constexpr int kQKStages = 4;     // (q0 q1 | k0 k1): 4 pairs prefetched ahead of the S MMA
+constexpr int kVStages = 6;      // (v0 v1 | ones): 4 pairs inside the softmax warpgroups + 2 prefetched
+constexpr int kSlotsF = 4;
 constexpr int kThreadsF = 128 + 128 * kSlotsF;
-constexpr int kStageBytesF = 7 * kTileBytes;   // q0 q1 | k0 k1 | v0 v1 | ones
+constexpr int kFillF = kThreadsF - 64;         // threads of the non-producer warps
+constexpr int kQKBytes = 4 * kTileBytes;
+constexpr int kVBytes = 3 * kTileBytes;
 constexpr int kSlotBytesF = 2 * kPTileBytes;   // P0 P1 ; reused as o0 o1 staging
 constexpr int kSlotColsF = 128;                // S: 112 columns; O (65 columns) reuses them once S has been read
 
 __device__ __forceinline__ uint32_t q_off(int t) { return t * kTileBytes; }
-__device__ __forceinline__ uint32_t k_off(int t) { return 2 * kTileBytes + t * kKTile1; }
-__device__ __forceinline__ uint32_t v_off(int t) { return 4 * kTileBytes + t * kTileBytes; }
+__device__ __forceinline__ uint32_t k_off(int t) { return 2 * kTileBytes + t * kKTile1; }   // in a QK stage
+__device__ __forceinline__ uint32_t v_off(int t) { return t * kTileBytes; }                    // in a V stage
 
 struct TmaMapsF {
   CUtensorMap q[7], k[7], v[7];   // loads
@@ -47,15 +51,16 @@ struct TmaMapsF {
 };
 
 struct SmemMapF {
-  uint32_t stages, slots, bias, bars, tmem_ptr, total;
+  uint32_t qk, v, slots, bias, bars, tmem_ptr, total;
 };
 __host__ __device__ inline SmemMapF smem_map_f() {
   SmemMapF m;
-  m.stages = 0;
-  m.slots = m.stages + kStagesF * kStageBytesF;
+  m.qk = 0;
+  m.v = m.qk + kQKStages * kQKBytes;
+  m.slots = m.v + kVStages * kVBytes;
   m.bias = m.slots + kSlotsF * kSlotBytesF;
   m.bars = m.bias + 176 * 4;
-  m.tmem_ptr = m.bars + 8 * (2 * kStagesF + 4 * kSlotsF);
+  m.tmem_ptr = m.bars + 8 * (2 * kQKStages + 2 * kVStages + 4 * kSlotsF);
   m.total = m.tmem_ptr + 16;
   return m;
 }
@@ -75,21 +80,27 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   const int n_pairs = (w1 - w0 + 1) >> 1;
   if (tid == 0) TC_TRACE(p, 0, 14);   // kernel entry
 
-  const uint32_t bar_full = sbase + map.bars;              // [kStagesF] TMA -> S MMA
-  const uint32_t bar_empty = bar_full + 8 * kStagesF;      // [kStagesF] PV MMA -> producers
-  const uint32_t bar_s = bar_empty + 8 * kStagesF;         // [kSlotsF]  S ready
+  const uint32_t bar_qk_full = sbase + map.bars;               // [kQKStages] TMA -> S MMA
+  const uint32_t bar_qk_empty = bar_qk_full + 8 * kQKStages;   // [kQKStages] S MMA -> producers
+  const uint32_t bar_v_full = bar_qk_empty + 8 * kQKStages;    // [kVStages]  TMA -> PV MMA
+  const uint32_t bar_v_empty = bar_v_full + 8 * kVStages;      // [kVStages]  PV MMA -> producers
+  const uint32_t bar_s = bar_v_empty + 8 * kVStages;           // [kSlotsF]  S ready
   const uint32_t bar_p = bar_s + 8 * kSlotsF;              // [kSlotsF]  P written
   const uint32_t bar_o = bar_p + 8 * kSlotsF;              // [kSlotsF]  O ready
   const uint32_t bar_r = bar_o + 8 * kSlotsF;              // [kSlotsF]  O read, slot reusable
 
   // ---- one-time setup -------------------------------------------------------
   // Thread 0 initialises the mbarriers; after one CTA barrier the producers start loading right away while the
-  // other 14 warps fill the bytes TMA never writes, stage the bias and allocate TMEM, then meet on a named
+  // other warps fill the bytes TMA never writes, stage the bias and allocate TMEM, then meet on a named
   // barrier (the MMA issuers are among them, so no MMA reads a tile before the fills are complete).
   if (tid == 0) {
-    for (int i = 0; i < kStagesF; ++i) {
-      mbar_init(bar_full + 8 * i, 2);
-      mbar_init(bar_empty + 8 * i, 1);
+    for (int i = 0; i < kQKStages; ++i) {
+      mbar_init(bar_qk_full + 8 * i, 2);
+      mbar_init(bar_qk_empty + 8 * i, 1);
+    }
+    for (int i = 0; i < kVStages; ++i) {
+      mbar_init(bar_v_full + 8 * i, 2);
+      mbar_init(bar_v_empty + 8 * i, 1);
     }
     for (int i = 0; i < kSlotsF; ++i) {
       mbar_init(bar_s + 8 * i, 1);
@@ -101,12 +112,15 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   }
   __syncthreads();
   if (warp != 0 && warp != 3) {
-    const int t14 = tid - (warp < 3 ? 32 : 64);   // 0 .. 447 over the 14 non-producer warps
+    const int t14 = tid - (warp < 3 ? 32 : 64);   // 0 .. kFillF-1 over the non-producer warps
     // global loads first, so that their latency overlaps the fills: this head's bias column and pad vectors
     const float bias_v = t14 < 169 ? p.table[t14 * p.nH + h] * kLog2e : 0.f;
     uint4 pad_v = make_uint4(0u, 0u, 0u, 0u);
-    const bool pad_is_v = (t14 >> 2) & 1;            // items 0 .. 8*kStagesF*... : (stage, tile t, k|v, chunk)
-    if (has_pad && t14 < kStagesF * 16) {
+    // row-49 items: [0, 8 kQKStages) = (QK stage, tile, chunk) for k_pad; then (V stage, tile, chunk) for v_pad
+    const bool pad_is_v = t14 >= 8 * kQKStages;
+    const int pad_item = pad_is_v ? t14 - 8 * kQKStages : t14;
+    const bool pad_thread = t14 < 8 * (kQKStages + kVStages);
+    if (has_pad && pad_thread) {
       const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(pad_is_v ? p.v_pad : p.k_pad);
       if (src != nullptr) pad_v = *reinterpret_cast<const uint4*>(src + h * kHeadDim + (t14 & 3) * 8);
     }
@@ -114,30 +128,34 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     // Rows 49-63 of the K / V tiles (TMA boxes write rows 0-48 only) must be finite: K rows 49-55 feed S
     // columns that are never read, V rows 49-63 are multiplied by P columns that are 0.  Row 49 of both holds
     // the head's pad vector (see the file header); the rest is zero.  K tile 1 starts at row 56 of K tile 0.
-    for (int i = t14; i < kStagesF * 4 * 14 * 4; i += 448) {
-      const int chunk = i & 3, rr = (i >> 2) % 14, t4 = ((i >> 2) / 14) & 3, s = (i >> 2) / 56;
-      const bool is_v = t4 >= 2;
-      const int t = t4 & 1;
-      if (!is_v && rr >= 6) continue;             // K: rows 50-55 only (rows 56.. of K tile 0 are K tile 1)
+    for (int i = t14; i < kQKStages * 2 * 6 * 4; i += kFillF) {          // K rows 50-55
+      const int chunk = i & 3, rr = (i >> 2) % 6, t = ((i >> 2) / 6) & 1, st = (i >> 2) / 12;
       const int r50 = 50 + rr;
-      *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytesF + (is_v ? v_off(t) : k_off(t)) + r50 * 64 +
-                                ((chunk ^ ((r50 >> 1) & 3)) << 4)) = make_uint4(0u, 0u, 0u, 0u);
+      *reinterpret_cast<uint4*>(smem + map.qk + st * kQKBytes + k_off(t) + r50 * 64 + ((chunk ^ ((r50 >> 1) & 3)) << 4)) =
+          make_uint4(0u, 0u, 0u, 0u);
     }
-    if (t14 < kStagesF * 16) {                     // row 49 (swizzle term (49 >> 1) & 3 = 0)
-      const int chunk = t14 & 3, t = (t14 >> 3) & 1, s = t14 >> 4;
-      *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytesF + (pad_is_v ? v_off(t) : k_off(t)) + 49 * 64 + (chunk << 4)) = pad_v;
+    for (int i = t14; i < kVStages * 2 * 14 * 4; i += kFillF) {          // V rows 50-63
+      const int chunk = i & 3, rr = (i >> 2) % 14, t = ((i >> 2) / 14) & 1, st = (i >> 2) / 28;
+      const int r50 = 50 + rr;
+      *reinterpret_cast<uint4*>(smem + map.v + st * kVBytes + v_off(t) + r50 * 64 + ((chunk ^ ((r50 >> 1) & 3)) << 4)) =
+          make_uint4(0u, 0u, 0u, 0u);
     }
-    // ones tile of every stage (64B-swizzled, MN-major B of the PV MMA): element 0 of each key row is 1.0
+    if (pad_thread) {                               // row 49 (swizzle term (49 >> 1) & 3 = 0)
+      const int chunk = pad_item & 3, t = (pad_item >> 2) & 1, st = pad_item >> 3;
+      *reinterpret_cast<uint4*>(smem + (pad_is_v ? map.v + st * kVBytes + v_off(t) : map.qk + st * kQKBytes + k_off(t)) + 49 * 64 +
+                                (chunk << 4)) = pad_v;
+    }
+    // ones tile of every V stage (64B-swizzled, MN-major B of the PV MMA): element 0 of each key row is 1.0
     // (bf16), so column 64 of O = sum_j P[i, j]
-    for (int i = t14; i < kStagesF * 64 * 4; i += 448) {
-      const int chunk = i & 3, rr = (i >> 2) & 63, s = i >> 8;
-      *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytesF + 6 * kTileBytes + rr * 64 +
-                                ((chunk ^ ((rr >> 1) & 3)) << 4)) = make_uint4(chunk == 0 ? 0x00003f80u : 0u, 0u, 0u, 0u);
+    for (int i = t14; i < kVStages * 64 * 4; i += kFillF) {
+      const int chunk = i & 3, rr = (i >> 2) & 63, st = i >> 8;
+      *reinterpret_cast<uint4*>(smem + map.v + st * kVBytes + 2 * kTileBytes + rr * 64 + ((chunk ^ ((rr >> 1) & 3)) << 4)) =
+          make_uint4(chunk == 0 ? 0x00003f80u : 0u, 0u, 0u, 0u);
     }
     if (t14 < 176) reinterpret_cast<float*>(smem + map.bias)[t14] = bias_v;
     fence_proxy_async();
     tc_fence_before();
-    named_barrier(5, 448);
+    named_barrier(6, kFillF);
     tc_fence_after();
   } else if (lane == 0) {
     for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
@@ -154,18 +172,29 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     WinIter it;
     it.init(p, w0 + t);
     for (int n = 0; n < n_pairs; ++n, it.advance(p, 2)) {
-      const int s = n % kStagesF;
-      const uint32_t st = sbase + map.stages + s * kStageBytesF, bar = bar_full + 8 * s;
-      mbar_wait(bar_empty + 8 * s, ((n / kStagesF) & 1) ^ 1);
+      const int s = n % kQKStages, sv = n % kVStages;
+      const uint32_t st = sbase + map.qk + s * kQKBytes, bar = bar_qk_full + 8 * s;
+      const uint32_t stv = sbase + map.v + sv * kVBytes, barv = bar_v_full + 8 * sv;
+      const bool valid = it.w < w1;
+      mbar_wait(bar_qk_empty + 8 * s, ((n / kQKStages) & 1) ^ 1);
       if (elect_one()) {
         if (t == 0) TC_TRACE(p, n, 0);
-        if (it.w < w1) {
-          mbar_expect_tx(bar, 3 * kBoxBytes);
+        if (valid) {
+          mbar_expect_tx(bar, 2 * kBoxBytes);
           move_window<kShifted, false>(maps.q, st + q_off(t), bar, p, it.b, it.wy, it.wx, h);
           move_window<kShifted, false>(maps.k, st + k_off(t), bar, p, it.b, it.wy, it.wx, h);
-          move_window<kShifted, false>(maps.v, st + v_off(t), bar, p, it.b, it.wy, it.wx, h);
         } else {
           mbar_arrive(bar);
+        }
+      }
+      __syncwarp();
+      mbar_wait(bar_v_empty + 8 * sv, ((n / kVStages) & 1) ^ 1);
+      if (elect_one()) {
+        if (valid) {
+          mbar_expect_tx(barv, kBoxBytes);
+          move_window<kShifted, false>(maps.v, stv + v_off(t), barv, p, it.b, it.wy, it.wx, h);
+        } else {
+          mbar_arrive(barv);
         }
         if (t == 0) TC_TRACE(p, n, 1);
       }
@@ -175,11 +204,11 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     // ===== S = Q K^T issuer (2 instructions per pair) ===========================================
     constexpr uint32_t idesc_s = instr_desc(128, 112, 0);
     for (int n = 0; n < n_pairs; ++n) {
-      const int s = n % kStagesF, a = n % kSlotsF;
-      mbar_wait(bar_full + 8 * s, (n / kStagesF) & 1);
+      const int s = n % kQKStages, a = n % kSlotsF;
+      mbar_wait(bar_qk_full + 8 * s, (n / kQKStages) & 1);
       mbar_wait(bar_r + 8 * a, ((n / kSlotsF) & 1) ^ 1);
       tc_fence_after();
-      const uint32_t st = sbase + map.stages + s * kStageBytesF;
+      const uint32_t st = sbase + map.qk + s * kQKBytes;
       const uint32_t d = tmem_base + a * kSlotColsF;
       const uint64_t qd = smem_desc(st + q_off(0), 16, 512, 4);   // 128 rows: q0 | q1
       const uint64_t kd = smem_desc(st + k_off(0), 16, 512, 4);   // 112 rows: k0 (56) | k1 (56)
@@ -188,6 +217,7 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
 #pragma unroll
         for (int k = 0; k < 2; ++k) umma_ss(d, qd + 2 * k, kd + 2 * k, idesc_s, k);
         umma_commit(bar_s + 8 * a);
+        umma_commit(bar_qk_empty + 8 * s);
         TC_TRACE(p, n, 4);
       }
       __syncwarp();
@@ -196,10 +226,11 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     // ===== O = P V issuer (4 instructions per pair) =============================================
     constexpr uint32_t idesc_o = instr_desc(128, 96, 1);
     for (int m = 0; m < n_pairs; ++m) {
-      const int s = m % kStagesF, a = m % kSlotsF;
+      const int s = m % kVStages, a = m % kSlotsF;
+      mbar_wait(bar_v_full + 8 * s, (m / kVStages) & 1);
       mbar_wait(bar_p + 8 * a, (m / kSlotsF) & 1);
       tc_fence_after();
-      const uint32_t st = sbase + map.stages + s * kStageBytesF;
+      const uint32_t st = sbase + map.v + s * kVBytes;
       const uint32_t d = tmem_base + a * kSlotColsF;               // O overwrites the S columns
       const uint64_t pd = smem_desc(sbase + map.slots + a * kSlotBytesF, 16, 1024, 2);   // 128 rows: p0 | p1
       const uint64_t vd = smem_desc(st + v_off(0), kTileBytes, 512, 4);   // N = 96: v0 | v1 | ones, one tile apart
@@ -208,7 +239,7 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_ss(d, pd + 2 * k, vd + 64 * k, idesc_o, k);
         umma_commit(bar_o + 8 * a);
-        umma_commit(bar_empty + 8 * s);
+        umma_commit(bar_v_empty + 8 * s);
         TC_TRACE(p, m, 6);
       }
       __syncwarp();

@@ -67,9 +67,11 @@ def init_distributed(backend: Optional[str] = None) -> Dict[str, int]:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
         backend = backend or ("nccl" if torch.cuda.is_available() else "gloo")
+        kwargs = {}
         if backend == "nccl":
             torch.cuda.set_device(env["local_rank"])
-        dist.init_process_group(backend=backend, rank=env["rank"], world_size=env["world"])
+            kwargs["device_id"] = torch.device("cuda", env["local_rank"])
+        dist.init_process_group(backend=backend, rank=env["rank"], world_size=env["world"], **kwargs)
     return env
 
 
