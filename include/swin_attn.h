@@ -119,6 +119,13 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape,
 int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, const float* beta, float eps, int64_t rows,
                            int32_t channels, void* out, int32_t out_dtype, void* stream);
 
+/* Backward of swin_layernorm_forward for training under autocast (autograd of nn.LayerNorm in the reference).
+ * dy: (rows, channels) bf16, the gradient of the bf16 output; x: the forward's input (mean / rstd are recomputed).
+ * dx: (rows, channels) of x_dtype; dgamma, dbeta: (channels) fp32, OVERWRITTEN (zeroed, then accumulated).
+ * channels in {128, 192, 256, 384, 512, 768, 1024, 1536}. */
+int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, const float* gamma, float eps, int64_t rows,
+                            int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream);
+
 /* Number of kernel launches issued by this library since load (all threads). */
 uint64_t swin_attn_launch_count(void);
 

@@ -64,6 +64,133 @@ __global__ void __launch_bounds__(256) layernorm_rows_kernel(const TIn* __restri
   }
 }
 
+// Backward of the kernel above, for training under autocast: dy is the bf16 gradient the Linear's dgrad produced,
+// x the saved residual stream; mean / rstd are recomputed from the row (it is in registers anyway), so nothing but x
+// is saved.  dx = rstd (g - mean(g) - xhat mean(g xhat)), g = dy gamma;  dgamma = sum_rows dy xhat;  dbeta = sum_rows dy.
+// One warp per row, grid-stride over rows; every warp accumulates its dgamma / dbeta partials in a private shared-
+// memory row (lane l owns the same channels for every row, so there are no conflicts and no atomics), the CTA
+// reduces its 8 rows at the end and adds them to global memory with one atomic per channel.
+template <int NC, typename TX>
+__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const TX* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                                            const float* __restrict__ gamma, float eps, int64_t rows,
+                                                            TX* __restrict__ dx, float* __restrict__ dgamma,
+                                                            float* __restrict__ dbeta) {
+  constexpr int C = 64 * NC;
+  extern __shared__ __align__(16) float2 acc[];   // [8 warps][2 (dgamma, dbeta)][C / 2]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float2* ag = acc + (warp * 2) * (C / 2);
+  float2* ab = ag + C / 2;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    ag[lane + 32 * k] = make_float2(0.f, 0.f);
+    ab[lane + 32 * k] = make_float2(0.f, 0.f);
+  }
+  const float2* g2 = reinterpret_cast<const float2*>(gamma);
+  for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < rows; row += (int64_t)gridDim.x * 8) {
+    float2 v[NC], d[NC];
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+      v[k] = load2(x + row * C, lane + 32 * k);
+      d[k] = load2(dy + row * C, lane + 32 * k);
+      sum += v[k].x + v[k].y;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float mean = sum * (1.0f / C);
+    float sq = 0.f;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+      v[k].x -= mean;
+      v[k].y -= mean;
+      sq = fmaf(v[k].x, v[k].x, sq);
+      sq = fmaf(v[k].y, v[k].y, sq);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    const float rstd = rsqrtf(sq * (1.0f / C) + eps);
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+      const float2 g = g2[lane + 32 * k];
+      v[k].x *= rstd;   // xhat
+      v[k].y *= rstd;
+      float2 a = ag[lane + 32 * k], b = ab[lane + 32 * k];
+      a.x = fmaf(d[k].x, v[k].x, a.x); a.y = fmaf(d[k].y, v[k].y, a.y);
+      b.x += d[k].x; b.y += d[k].y;
+      ag[lane + 32 * k] = a;
+      ab[lane + 32 * k] = b;
+      d[k].x *= g.x;    // g = dy gamma
+      d[k].y *= g.y;
+      s1 += d[k].x + d[k].y;
+      s2 = fmaf(d[k].x, v[k].x, s2);
+      s2 = fmaf(d[k].y, v[k].y, s2);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    s1 *= (1.0f / C);
+    s2 *= (1.0f / C);
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+      const float y0 = rstd * (d[k].x - s1 - v[k].x * s2), y1 = rstd * (d[k].y - s1 - v[k].y * s2);
+      if constexpr (sizeof(TX) == 2) {
+        reinterpret_cast<__nv_bfloat162*>(dx + row * C)[lane + 32 * k] = __floats2bfloat162_rn(y0, y1);
+      } else {
+        reinterpret_cast<float2*>(dx + row * C)[lane + 32 * k] = make_float2(y0, y1);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += 256) {
+    float sg = 0.f, sb = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      sg += reinterpret_cast<const float*>(acc + (w * 2) * (C / 2))[i];
+      sb += reinterpret_cast<const float*>(acc + (w * 2 + 1) * (C / 2))[i];
+    }
+    atomicAdd(dgamma + i, sg);
+    atomicAdd(dbeta + i, sb);
+  }
+}
+
+template <int NC>
+static cudaError_t launch_ln_bwd(const void* x, int x_dtype, const void* dy, const float* g, float eps, int64_t rows, void* dx,
+                                 float* dgamma, float* dbeta, int sms, cudaStream_t st) {
+  const size_t smem = (size_t)8 * 2 * 64 * NC * sizeof(float);
+  int64_t want = (rows + 7) / 8;
+  const int64_t cap = (int64_t)sms * (smem > 96 * 1024 ? 1 : smem > 48 * 1024 ? 2 : 4);
+  const unsigned grid = (unsigned)(want < cap ? want : cap);
+  cudaError_t e = cudaMemsetAsync(dgamma, 0, sizeof(float) * 64 * NC, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(dbeta, 0, sizeof(float) * 64 * NC, st);
+  if (e != cudaSuccess) return e;
+  using bf = __nv_bfloat16;
+  if (x_dtype == SWIN_ATTN_F32) {
+    auto k = layernorm_bwd_kernel<NC, float>;
+    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    k<<<grid, 256, smem, st>>>(static_cast<const float*>(x), static_cast<const bf*>(dy), g, eps, rows, static_cast<float*>(dx), dgamma, dbeta);
+  } else {
+    auto k = layernorm_bwd_kernel<NC, bf>;
+    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    k<<<grid, 256, smem, st>>>(static_cast<const bf*>(x), static_cast<const bf*>(dy), g, eps, rows, static_cast<bf*>(dx), dgamma, dbeta);
+  }
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_layernorm_backward(const void* x, int x_dtype, const void* dy, const float* g, float eps, int64_t rows,
+                                      int channels, void* dx, float* dgamma, float* dbeta, int sms, cudaStream_t st) {
+  switch (channels / 64) {
+#define SWIN_LN_CASE(NC) case NC: return launch_ln_bwd<NC>(x, x_dtype, dy, g, eps, rows, dx, dgamma, dbeta, sms, st)
+    SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
+    SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24);   // 3072 channels: the row does not fit in registers
+#undef SWIN_LN_CASE
+    default: return cudaErrorInvalidValue;
+  }
+}
+
 template <int NC>
 static cudaError_t launch_ln(const void* x, int x_dtype, const float* g, const float* b, float eps, int64_t rows, void* out,
                              int out_dtype, cudaStream_t st) {

@@ -255,15 +255,59 @@ def _(x, weight, bias, eps, out_bf16):
     return x.new_empty(x.shape, dtype=torch.bfloat16 if out_bf16 else torch.float32)
 
 
+@torch.library.custom_op("swin_attn::layer_norm_bwd", mutates_args=(), device_types="cuda")
+def _layer_norm_bwd(dy: Tensor, x: Tensor, weight: Tensor, eps: float) -> Tuple[Tensor, Tensor, Tensor]:
+    """``swin_layernorm_backward``: (dx, dweight, dbias) from the bf16 output gradient and the saved input."""
+    lib = _lib.load()
+    x = x.contiguous()
+    dy = dy.to(torch.bfloat16).contiguous()
+    c = x.shape[-1]
+    dx = torch.empty_like(x)
+    w = weight.detach().float().contiguous()
+    dw, db = torch.empty_like(w), torch.empty_like(w)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.swin_layernorm_backward(_ptr(x), _DTYPES[x.dtype], _ptr(dy), _ptr(w), float(eps), x.numel() // c, c,
+                                               _ptr(dx), _ptr(dw), _ptr(db),
+                                               ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return dx, dw, db
+
+
+@_layer_norm_bwd.register_fake
+def _(dy, x, weight, eps):
+    w = weight.new_empty(weight.shape, dtype=torch.float32)
+    return torch.empty_like(x), w, torch.empty_like(w)
+
+
+def _ln_setup_context(ctx, inputs, output):
+    x, weight, bias, eps, out_bf16 = inputs
+    ctx.save_for_backward(x, weight)
+    ctx.eps, ctx.out_bf16 = eps, out_bf16
+    ctx.param_dtype = weight.dtype
+
+
+def _ln_backward(ctx, dy):
+    x, weight = ctx.saved_tensors
+    if not ctx.out_bf16 or x.shape[-1] > 1536:
+        raise RuntimeError("swin_attn::layer_norm: backward exists for the bf16-output form with <= 1536 channels")
+    dx, dw, db = torch.ops.swin_attn.layer_norm_bwd(dy, x, weight, ctx.eps)
+    return dx, dw.to(ctx.param_dtype), db.to(ctx.param_dtype), None, None
+
+
+_layer_norm.register_autograd(_ln_backward, setup_context=_ln_setup_context)
+
+
 def norm_for_linear(norm: torch.nn.Module, x: Tensor) -> Tensor:
-    """``norm(x)`` for a LayerNorm whose output only feeds a Linear.  Inference under bf16 autocast takes the
-    fused kernel (fp32 in, bf16 out: the values autocast would hand the Linear); every other case -- training,
-    fp32 mode, unsupported widths, non-LayerNorm ``norm_layer`` -- is the module itself."""
+    """``norm(x)`` for a LayerNorm whose output only feeds a Linear.  Under bf16 autocast this is the fused kernel
+    (fp32 / bf16 residual in, bf16 out: the values autocast would hand the Linear, and in training the matching
+    fused backward); every other case -- fp32 mode, unsupported widths, non-LayerNorm ``norm_layer`` -- is the
+    module itself."""
     if (type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
-            and x.dtype in _DTYPES and not torch.is_grad_enabled() and torch.is_autocast_enabled()
+            and x.dtype in _DTYPES and torch.is_autocast_enabled()
             and torch.get_autocast_dtype("cuda") == torch.bfloat16 and len(norm.normalized_shape) == 1
             and x.shape[-1] in _LN_CHANNELS):
-        return torch.ops.swin_attn.layer_norm(x, norm.weight, norm.bias, norm.eps, True)
+        needs_grad = torch.is_grad_enabled() and (x.requires_grad or norm.weight.requires_grad or norm.bias.requires_grad)
+        if not needs_grad or x.shape[-1] <= 1536:
+            return torch.ops.swin_attn.layer_norm(x, norm.weight, norm.bias, norm.eps, True)
     return norm(x)
 
 

@@ -382,14 +382,56 @@ def test_fused_layernorm_matches_torch(c):
     got_b = torch.ops.swin_attn.layer_norm(xb, w, b, 1e-5, True)
     diff = (got_b.float() - want_b.bfloat16().float()).abs()
     assert float((diff > 0).float().mean()) < 5e-3 and float((diff / want_b.abs().clamp_min(1e-3)).max()) < 2 ** -7
-    # the layer helper takes the fused path only for inference under bf16 autocast
+    # the layer helper takes the fused path only under bf16 autocast
     ln = torch.nn.LayerNorm(c).to(DEV)
     with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
         assert ops.norm_for_linear(ln, x).dtype == torch.bfloat16
-    with torch.autocast("cuda", dtype=torch.bfloat16):
-        assert ops.norm_for_linear(ln, x).dtype == torch.float32        # grad mode: the module itself
+    with torch.autocast("cuda", dtype=torch.bfloat16):                  # training: fused up to 1536 channels
+        assert ops.norm_for_linear(ln, x).dtype == (torch.bfloat16 if c <= 1536 else torch.float32)
     with torch.no_grad():
-        assert ops.norm_for_linear(ln, x).dtype == torch.float32        # fp32 mode
+        assert ops.norm_for_linear(ln, x).dtype == torch.float32        # fp32 mode: the module itself
+
+
+@pytest.mark.parametrize("xdtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("c", [128, 192, 256, 384, 512, 768, 1024, 1536])
+def test_fused_layernorm_backward_matches_torch_autograd(c, xdtype):
+    """swin_layernorm_backward vs autograd through F.layer_norm in fp32 on the same (bf16-rounded) dy."""
+    gen = torch.Generator(device=DEV).manual_seed(100 + c)
+    x = (2.0 * torch.randn(2051, c, device=DEV, generator=gen) - 0.4).to(xdtype)
+    w = (1.0 + 0.3 * torch.randn(c, device=DEV, generator=gen)).requires_grad_()
+    b = (0.2 * torch.randn(c, device=DEV, generator=gen)).requires_grad_()
+    dy = torch.randn(2051, c, device=DEV, generator=gen).bfloat16()
+    xr = x.float().requires_grad_()
+    want = torch.autograd.grad((torch.nn.functional.layer_norm(xr, (c,), w, b, 1e-5) * dy.float()).sum(), [xr, w, b])
+    xg = x.clone().requires_grad_()
+    y = torch.ops.swin_attn.layer_norm(xg, w, b, 1e-5, True)
+    got = torch.autograd.grad((y.float() * dy.float()).sum(), [xg, w, b])
+    assert got[0].dtype == xdtype and got[1].dtype == torch.float32
+    assert rel_err(got[0].float(), want[0]) < (1e-5 if xdtype == torch.float32 else 4e-3)   # bf16 dx: one rounding
+    assert rel_err(got[1], want[1]) < 2e-5 and rel_err(got[2], want[2]) < 2e-5
+
+
+def test_ops_pass_opcheck_and_trace_under_compile():
+    """The torch.library registration (schema, fake kernels, autograd formula) is what lets DDP, autocast and
+    torch.compile carry the ops: opcheck validates it, and a compiled module must agree with eager."""
+    nh, ws = 2, 7
+    c = nh * 32
+    qkv = randn("opcheck.p", 1, 14, 14, 3 * c).bfloat16().to(DEV).requires_grad_()
+    table = (0.5 * randn("opcheck.t", 169, nh)).to(DEV).requires_grad_()
+    torch.library.opcheck(torch.ops.swin_attn.fwd.default,
+                          (qkv, None, table, None, None, ws, 3, nh, 32 ** -0.5, True, _lib.IMPL_AUTO, None),
+                          test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+    o, lse = torch.ops.swin_attn.fwd(qkv.detach(), None, table.detach(), None, None, ws, 3, nh, 32 ** -0.5, True, _lib.IMPL_AUTO, None)
+    torch.library.opcheck(torch.ops.swin_attn.bwd.default,
+                          (torch.ones_like(o), qkv.detach(), None, o, lse, table.detach(), ws, 3, nh, 32 ** -0.5, None, _lib.IMPL_AUTO),
+                          test_utils=("test_schema", "test_faketensor"))
+    blk = layers.SwinTransformerBlock(c, nh, window_size=ws, shift_size=3).to(DEV).eval()
+    blk.H, blk.W = 14, 14
+    x = randn("opcheck.x", 1, 196, c).to(DEV)
+    with torch.no_grad():
+        want = blk(x, None)
+        got = torch.compile(blk, fullgraph=False)(x, None)
+    assert rel_err(got, want) < 1e-5
 
 
 def test_library_counts_launches():
