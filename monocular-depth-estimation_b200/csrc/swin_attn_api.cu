@@ -33,7 +33,7 @@ static int make_problem(const swin_attn_shape_t* s, Problem& p) {
   if (s->window != 7 && s->window != 12) return fail("window must be 7 or 12 (got " + std::to_string(s->window) + ")");
   if (s->shift < 0 || s->shift >= s->window) return fail("shift_size must in 0-window_size");
   if (s->batch <= 0 || s->height <= 0 || s->width <= 0 || s->num_heads <= 0) return fail("batch/height/width/num_heads must be positive");
-  if (s->dropout_p != 0.0f) return fail("attention dropout > 0 is not implemented (every NewCRFs configuration uses 0)");
+  if (!(s->dropout_p >= 0.0f && s->dropout_p < 1.0f)) return fail("dropout_p must be in [0, 1)");
   memset(&p, 0, sizeof(p));
   p.B = s->batch; p.H = s->height; p.W = s->width; p.nH = s->num_heads;
   p.C = s->num_heads * kHeadDim;

@@ -128,6 +128,7 @@ __global__ void __launch_bounds__(kThreads) simt_fwd_kernel(const Problem p) {
   float4* ps = sm.ps + warp * TL::NCOL;
   T* o = static_cast<T*>(p.o);
   const float* mask_w = p.mask ? p.mask + (int64_t)((item / p.nH) % p.mask_nw) * N * N : nullptr;
+  const Dropout drop = make_dropout(p, item / p.nH, h, N);
 
   for (int g = warp; g < TL::NG; g += kWarps) {
     float acc[4][NC];
@@ -180,7 +181,8 @@ __global__ void __launch_bounds__(kThreads) simt_fwd_kernel(const Problem p) {
       inv[r] = 1.0f / l;
       lse[r] = m + logf(l);
 #pragma unroll
-      for (int c = 0; c < NC; ++c) reinterpret_cast<float*>(&ps[lane + 32 * c])[r] = pr[c];
+      for (int c = 0; c < NC; ++c)
+        reinterpret_cast<float*>(&ps[lane + 32 * c])[r] = pr[c] * drop.scale_of(N, row, min(lane + 32 * c, N - 1));
     }
     __syncwarp();
     float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
@@ -278,6 +280,7 @@ __global__ void __launch_bounds__(kThreads) simt_bwd_kernel(const Problem p, int
     int b, wy, wx;
     decode_item(p, item - h * n_win, b, wy, wx);
     const float* mask_w = p.mask ? p.mask + (int64_t)((item - h * n_win) % p.mask_nw) * N * N : nullptr;
+    const Dropout drop = make_dropout(p, item - h * n_win, h, N);
     __syncthreads();  // previous item fully consumed
     if (h != cur_h) {
       for (int i = tid; i < TL::NT; i += kThreads) {
@@ -368,7 +371,7 @@ __global__ void __launch_bounds__(kThreads) simt_bwd_kernel(const Problem p, int
             if (mask_w != nullptr) s += mask_w[row * N + j];
             else if (sm.reg[j] != rreg) s += -100.0f;
             float pr = expf(s - rl);
-            ds = pr * (ad[r][c] - rd);
+            ds = pr * (ad[r][c] * drop.scale_of(N, row, j) - rd);
             atomicAdd(&sm.dtab[bi], ds);
           }
           reinterpret_cast<float*>(&p1[j])[r] = ds;
@@ -429,7 +432,9 @@ __global__ void __launch_bounds__(kThreads) simt_bwd_kernel(const Problem p, int
             if (mask_w != nullptr) s += mask_w[i * N + col];
             else if (sm.reg[i] != creg) s += -100.0f;
             pr = expf(s - sm.lse[i]);
-            ds = pr * (ad[r][c] - sm.delta[i]);
+            const float keep = drop.scale_of(N, i, col);
+            ds = pr * (ad[r][c] * keep - sm.delta[i]);
+            pr *= keep;   // dV = (dropout(P))^T dO
           }
           reinterpret_cast<float*>(&p1[i])[r] = pr;
           reinterpret_cast<float*>(&p2[i])[r] = ds;

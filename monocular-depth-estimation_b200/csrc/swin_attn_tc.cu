@@ -504,6 +504,7 @@ int tc::sm_count() {
 
 bool tc_forward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
+  if (p.dropout_p > 0.0f) return false;   // attention dropout (unused by NewCRFs) is served by the CUDA-core kernels
   if (p.shift != 0 && p.shift != tc::kShift) return false;
   // TMA: 16-byte aligned base pointers and strides
   if ((p.q_ps | p.k_ps | p.v_ps | p.o_ps) & 7) return false;

@@ -433,6 +433,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
 // ---- host side ------------------------------------------------------------------
 bool tc_backward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
+  if (p.dropout_p > 0.0f) return false;   // attention dropout (unused by NewCRFs) is served by the CUDA-core kernels
   if (p.shift != 0 && p.shift != tc::kShift) return false;
   if (p.H != p.Hp || p.W != p.Wp) return false;
   if ((p.q_ps | p.k_ps | p.v_ps | p.C) & 7) return false;

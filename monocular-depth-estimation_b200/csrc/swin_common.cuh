@@ -60,11 +60,45 @@ __device__ __forceinline__ int region_id(const Problem& p, int wy, int wx, int t
   return 3 * rh + rw;
 }
 
+// Attention dropout (nn.Dropout on the softmax output, newcrf_layers.py:137 / swin_transformer.py:139): element
+// (window, head, query row, key column) is kept iff a counter-based hash of (seed, element index) is >= p 2^32,
+// and kept probabilities are scaled by 1 / (1 - p).  The same function regenerates the mask in the backward.
+// (Bitwise parity with torch's Philox stream is out of scope; every NewCRFs configuration uses p = 0.)
+__host__ __device__ __forceinline__ uint32_t dropout_hash(uint64_t seed, uint64_t index) {
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * (index + 1);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (uint32_t)(z >> 32);
+}
+struct Dropout {
+  uint64_t seed, base;   // base = ((window * nH + head) * N) * N
+  uint32_t threshold;    // keep iff hash >= threshold
+  float keep_scale;      // 1 / (1 - p); 1 when p == 0
+  bool on;
+  __device__ __forceinline__ float scale_of(int n, int row, int col) const {
+    if (!on) return 1.0f;
+    return dropout_hash(seed, base + (uint64_t)row * n + col) >= threshold ? keep_scale : 0.0f;
+  }
+};
+__device__ __forceinline__ Dropout make_dropout(const struct Problem& p, int win, int head, int n);
+
 // relative_position_index[i, j] (newcrf_layers.py:89-100).
 __device__ __forceinline__ int rel_index(int ws, int ti, int tj) {
   int yi = ti / ws, xi = ti - yi * ws;
   int yj = tj / ws, xj = tj - yj * ws;
   return (yi - yj + ws - 1) * (2 * ws - 1) + (xi - xj + ws - 1);
+}
+
+__device__ __forceinline__ Dropout make_dropout(const Problem& p, int win, int head, int n) {
+  Dropout d;
+  d.on = p.dropout_p > 0.0f;
+  d.seed = p.seed;
+  d.base = ((uint64_t)win * p.nH + head) * (uint64_t)n * n;
+  const double t = (double)p.dropout_p * 4294967296.0;
+  d.threshold = t >= 4294967295.0 ? 0xffffffffu : (uint32_t)t;
+  d.keep_scale = d.on ? 1.0f / (1.0f - p.dropout_p) : 1.0f;
+  return d;
 }
 
 template <typename T>

@@ -85,14 +85,15 @@ class _WindowAttentionBase(nn.Module):
         wh, ww = self.window_size
         self.relative_position_bias_table = nn.Parameter(torch.zeros((2 * wh - 1) * (2 * ww - 1), num_heads))
         self.register_buffer("relative_position_index", _relative_position_index(wh, ww))
-        if attn_drop != 0.0:
-            raise NotImplementedError("attn_drop > 0 is not implemented in the fused kernel "
-                                      "(every NewCRFs configuration uses 0, SURVEY.md F7)")
+        # applied to the softmax output inside the kernel while training (0 in every NewCRFs configuration)
         self.attn_drop = nn.Dropout(attn_drop)
         self.proj = nn.Linear(out_dim, out_dim)
         self.proj_drop = nn.Dropout(proj_drop)
         nn.init.trunc_normal_(self.relative_position_bias_table, std=0.02)
         self.softmax = nn.Softmax(dim=-1)  # kept for module-tree parity; the kernel does the softmax
+
+    def _drop_p(self):
+        return self.attn_drop.p if self.training else 0.0
 
     def _windows_as_images(self, t):
         ws = self.window_size[0]
@@ -112,7 +113,8 @@ class WindowAttention(_WindowAttentionBase):
         assert self.dim == v.shape[-1], "self.dim != v.shape[-1]"
         qk = self._windows_as_images(self.qk(x))
         o = ops.window_attention(qk, self._windows_as_images(v), self.relative_position_bias_table,
-                                 self.window_size[0], 0, self.num_heads, self.scale, attn_mask=mask)
+                                 self.window_size[0], 0, self.num_heads, self.scale, attn_mask=mask,
+                                 dropout_p=self._drop_p())
         return self.proj_drop(self.proj(o.reshape(b_, n, c)))
 
     def forward_image(self, x_img, v_img, shift):
@@ -128,11 +130,12 @@ class WindowAttention(_WindowAttentionBase):
                 x_img = F.pad(x_img, (0, 0, 0, pr, 0, pb))
                 v_img = F.pad(v_img, (0, 0, 0, pr, 0, pb))
             o = ops.window_attention(self.qk(x_img), v_img, self.relative_position_bias_table, ws, shift,
-                                     self.num_heads, self.scale)
+                                     self.num_heads, self.scale, dropout_p=self._drop_p())
             o = o[:, :h, :w, :]
         else:
             o = ops.window_attention(self.qk(x_img), v_img, self.relative_position_bias_table, ws, shift,
-                                     self.num_heads, self.scale, packed_pad=self.qk.bias, v_pad=None)
+                                     self.num_heads, self.scale, packed_pad=self.qk.bias, v_pad=None,
+                                     dropout_p=self._drop_p())
         return self.proj_drop(self.proj(o))
 
 
@@ -147,7 +150,7 @@ class EncoderWindowAttention(_WindowAttentionBase):
         b_, n, c = x.shape
         qkv = self._windows_as_images(self.qkv(x))
         o = ops.window_attention(qkv, None, self.relative_position_bias_table, self.window_size[0], 0,
-                                 self.num_heads, self.scale, attn_mask=mask)
+                                 self.num_heads, self.scale, attn_mask=mask, dropout_p=self._drop_p())
         return self.proj_drop(self.proj(o.reshape(b_, n, c)))
 
     def forward_image(self, x_img, shift):
@@ -158,11 +161,11 @@ class EncoderWindowAttention(_WindowAttentionBase):
             if pb or pr:
                 x_img = F.pad(x_img, (0, 0, 0, pr, 0, pb))
             o = ops.window_attention(self.qkv(x_img), None, self.relative_position_bias_table, ws, shift,
-                                     self.num_heads, self.scale)
+                                     self.num_heads, self.scale, dropout_p=self._drop_p())
             o = o[:, :h, :w, :]
         else:
             o = ops.window_attention(self.qkv(x_img), None, self.relative_position_bias_table, ws, shift,
-                                     self.num_heads, self.scale, packed_pad=self.qkv.bias)
+                                     self.num_heads, self.scale, packed_pad=self.qkv.bias, dropout_p=self._drop_p())
         return self.proj_drop(self.proj(o))
 
 

@@ -49,11 +49,11 @@ def _image_layout(t: Tensor) -> Tensor:
 
 
 def _shape(batch, height, width, num_heads, window, shift, dtype, impl, scale, q_ps, k_ps, v_ps, o_ps,
-           mask_windows=0) -> _lib.Shape:
+           mask_windows=0, dropout_p=0.0, seed=0) -> _lib.Shape:
     if dtype not in _DTYPES:
         raise RuntimeError(f"swin_attn: dtype {dtype} is not supported (float32 or bfloat16)")
     return _lib.Shape(batch, height, width, num_heads, window, shift, _DTYPES[dtype], impl,
-                      float(scale), 0.0, 0, q_ps, k_ps, v_ps, o_ps, mask_windows, 0)
+                      float(scale), float(dropout_p), int(seed), q_ps, k_ps, v_ps, o_ps, mask_windows, 0)
 
 
 def _mask_arg(attn_mask: Optional[Tensor], window: int):
@@ -79,7 +79,8 @@ def _split(packed: Tensor, v: Optional[Tensor], num_heads: int):
 @torch.library.custom_op("swin_attn::fwd", mutates_args=(), device_types="cuda")
 def _fwd(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, packed_pad: Optional[Tensor],
          v_pad: Optional[Tensor], window: int, shift: int, num_heads: int, scale: float,
-         need_lse: bool, impl: int, attn_mask: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
+         need_lse: bool, impl: int, attn_mask: Optional[Tensor] = None, dropout_p: float = 0.0,
+         seed: int = 0) -> Tuple[Tensor, Tensor]:
     c = _split(packed, v, num_heads)
     mask, mask_nw = _mask_arg(attn_mask, window)
     lib = _lib.load()
@@ -106,7 +107,7 @@ def _fwd(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, packed_pad: Op
     hp, wp = -(-h // window) * window, -(-w // window) * window
     o = torch.empty((b, h, w, c), dtype=dt, device=packed.device)
     lse = torch.empty((b, hp, wp, num_heads) if need_lse else (0,), dtype=torch.float32, device=packed.device)
-    shp = _shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw)
+    shp = _shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw, dropout_p, seed)
     qpad_ptr = None if packed_pad is None else packed_pad.data_ptr()
     kpad_ptr = None if packed_pad is None else packed_pad.data_ptr() + c * es
     with torch.cuda.device(packed.device):
@@ -129,7 +130,8 @@ def _fwd(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, packed_pad: Op
 
 
 @_fwd.register_fake
-def _(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask=None):
+def _(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask=None,
+      dropout_p=0.0, seed=0):
     b, h, w, _ = packed.shape
     c = num_heads * 32
     hp, wp = -(-h // window) * window, -(-w // window) * window
@@ -141,7 +143,8 @@ def _(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale,
 @torch.library.custom_op("swin_attn::bwd", mutates_args=(), device_types="cuda")
 def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tensor, bias_table: Tensor,
          window: int, shift: int, num_heads: int, scale: float,
-         attn_mask: Optional[Tensor] = None, impl: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
+         attn_mask: Optional[Tensor] = None, impl: int = 0, dropout_p: float = 0.0,
+         seed: int = 0) -> Tuple[Tensor, Tensor, Tensor]:
     c = _split(packed, v, num_heads)
     mask, mask_nw = _mask_arg(attn_mask, window)
     lib = _lib.load()
@@ -171,7 +174,7 @@ def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tenso
         # differ from those of the inputs: run q/k and v through two shapes
         # only when they do.
         if ps == pc and (v is None or v_ps == c):
-            shp = _shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw)
+            shp = _shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw, dropout_p, seed)
             if _kernel_timing is not None:
                 ev0 = torch.cuda.Event(enable_timing=True)
                 ev0.record()
@@ -189,22 +192,25 @@ def _bwd(d_o: Tensor, packed: Tensor, v: Optional[Tensor], o: Tensor, lse: Tenso
         else:
             packed_c = packed.contiguous()
             v_c = None if v is None else v.contiguous()
-            return _bwd(d_o, packed_c, v_c, o, lse, bias_table, window, shift, num_heads, scale, attn_mask, impl)
+            return _bwd(d_o, packed_c, v_c, o, lse, bias_table, window, shift, num_heads, scale, attn_mask, impl,
+                        dropout_p, seed)
     return d_packed, d_v, d_table.to(bias_table.dtype)
 
 
 @_bwd.register_fake
-def _(d_o, packed, v, o, lse, bias_table, window, shift, num_heads, scale, attn_mask=None, impl=0):
+def _(d_o, packed, v, o, lse, bias_table, window, shift, num_heads, scale, attn_mask=None, impl=0, dropout_p=0.0, seed=0):
     d_packed = packed.new_empty(packed.shape)
     d_v = packed.new_empty((0,)) if v is None else packed.new_empty(v.shape)
     return d_packed, d_v, torch.empty_like(bias_table)
 
 
 def _setup_context(ctx, inputs, output):
-    packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask = inputs
+    (packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask,
+     dropout_p, seed) = inputs
     o, lse = output
     ctx.save_for_backward(packed, v, o, lse, bias_table, attn_mask)
     ctx.attrs = (window, shift, num_heads, scale)
+    ctx.dropout = (dropout_p, seed)
     ctx.padded = packed.shape[1] % window != 0 or packed.shape[2] % window != 0
     ctx.has_lse = need_lse
     ctx.v_dtype = None if v is None else v.dtype
@@ -218,12 +224,12 @@ def _backward(ctx, d_o, d_lse):
             "swin_attn: backward needs the forward to have run with need_lse=True on a tensor whose height and "
             "width are multiples of the window (the layers pad explicitly whenever gradients are enabled)")
     d_packed, d_v, d_table = torch.ops.swin_attn.bwd(d_o, packed, v, o, lse, bias_table, window, shift, num_heads, scale,
-                                                     attn_mask)
+                                                     attn_mask, _lib.IMPL_AUTO, ctx.dropout[0], ctx.dropout[1])
     if v is None:
         d_v = None
     elif d_v.dtype != ctx.v_dtype:
         d_v = d_v.to(ctx.v_dtype)
-    return d_packed, d_v, d_table, None, None, None, None, None, None, None, None, None
+    return d_packed, d_v, d_table, None, None, None, None, None, None, None, None, None, None, None
 
 
 _fwd.register_autograd(_backward, setup_context=_setup_context)
@@ -314,12 +320,13 @@ def norm_for_linear(norm: torch.nn.Module, x: Tensor) -> Tensor:
 def window_attention(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, window: int, shift: int,
                      num_heads: int, scale: Optional[float] = None, packed_pad: Optional[Tensor] = None,
                      v_pad: Optional[Tensor] = None, impl: int = _lib.IMPL_AUTO,
-                     attn_mask: Optional[Tensor] = None) -> Tensor:
+                     attn_mask: Optional[Tensor] = None, dropout_p: float = 0.0, seed: Optional[int] = None) -> Tensor:
     """Fused shifted-window attention on image-order tensors (see module docstring).
 
     ``packed``: (B,H,W,3C) qkv or (B,H,W,2C) qk with ``v`` (B,H,W,C) separate.
     ``packed_pad`` / ``v_pad``: value of the projections at padding tokens
-    (the Linear bias; None = zeros).  Returns (B,H,W,C).
+    (the Linear bias; None = zeros).  ``dropout_p`` > 0 drops attention probabilities (nn.Dropout on the softmax
+    output in the reference); ``seed`` defaults to a draw from torch's CPU generator.  Returns (B,H,W,C).
     """
     if not 0 <= shift < window:
         raise AssertionError("shift_size must in 0-window_size")  # newcrf_layers.py:180
@@ -327,8 +334,10 @@ def window_attention(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, wi
         scale = 32 ** -0.5
     need_grad = torch.is_grad_enabled() and (
         packed.requires_grad or bias_table.requires_grad or (v is not None and v.requires_grad))
+    if dropout_p > 0.0 and seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())   # CPU generator: reproducible under torch.manual_seed, no sync
     o, _ = torch.ops.swin_attn.fwd(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads,
-                                   float(scale), need_grad, impl, attn_mask)
+                                   float(scale), need_grad, impl, attn_mask, float(dropout_p), int(seed or 0))
     return o
 
 

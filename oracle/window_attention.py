@@ -100,6 +100,7 @@ def window_attention(
     q_pad: Optional[torch.Tensor] = None,
     k_pad: Optional[torch.Tensor] = None,
     v_pad: Optional[torch.Tensor] = None,
+    drop_scale: Optional[torch.Tensor] = None,
 ) -> Tuple[torch.Tensor, torch.Tensor]:
     """Shifted-window multi-head attention on image-order tensors.
 
@@ -107,6 +108,8 @@ def window_attention(
     ``o`` (B, H, W, C) in un-shifted image coordinates, cropped to (H, W), and
     ``lse`` (B, Hp, Wp, nH): log-sum-exp of each query row's logits (natural
     log), also in un-shifted coordinates of the *padded* image.
+
+    ``drop_scale``: optional multiplicative dropout mask on the probabilities.
 
     Restates WindowAttention.forward (newcrf_layers.py:117-146,
     swin_transformer.py:120-141) plus the pad/roll/partition/reverse/crop of
@@ -140,6 +143,8 @@ def window_attention(
         logits = (logits.reshape(b, nw, nh, n, n) + m[None, :, None]).reshape(-1, nh, n, n)
     lse = torch.logsumexp(logits, dim=-1)                 # (B_, nH, N)
     p = torch.softmax(logits, dim=-1)
+    if drop_scale is not None:                            # nn.Dropout on the softmax output (newcrf_layers.py:137):
+        p = p * drop_scale.to(p.dtype)                    # (B_, nH, N, N) of {0, 1/(1-p)}, supplied by the test
     ow = (p @ vw).transpose(1, 2).reshape(-1, n, c)
     o = unpartition(ow, ws, b, hp, wp)
     lse_img = unpartition(lse.transpose(1, 2), ws, b, hp, wp)

@@ -434,6 +434,65 @@ def test_ops_pass_opcheck_and_trace_under_compile():
     assert rel_err(got, want) < 1e-5
 
 
+def _dropout_scale(seed, n_win, nh, n, p):
+    """numpy restatement of swin_common.cuh::dropout_hash / Dropout::scale_of -> (n_win, nh, n, n) of {0, 1/(1-p)}."""
+    import numpy as np
+    idx = np.arange(n_win * nh * n * n, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        z = np.uint64(seed) + np.uint64(0x9E3779B97F4A7C15) * (idx + np.uint64(1))
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z ^= z >> np.uint64(31)
+    keep = (z >> np.uint64(32)) >= np.uint64(int(np.float32(p).astype(np.float64) * 4294967296.0))
+    scale = np.float32(1.0) / (np.float32(1.0) - np.float32(p))
+    return torch.from_numpy(keep.reshape(n_win, nh, n, n).astype(np.float32) * scale)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("case", [(7, 3, 2, 14, 21, 2), (12, 6, 1, 24, 12, 3)])
+def test_attention_dropout_matches_oracle_with_the_same_mask(case, dtype):
+    """p > 0 (unused by NewCRFs, but part of the module signature): forward and backward against the oracle fed
+    with the numpy restatement of the kernel's counter-based mask; plus keep-rate statistics."""
+    ws, shift, b, h, w, nh = case
+    c, n, p, seed = nh * 32, ws * ws, 0.25, 123456789
+    name = f"drop{case}"
+    packed = randn(name + ".p", b, h, w, 3 * c).to(dtype)
+    table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
+    cot = randn(name + ".c", b, h, w, c).to(dtype)
+    n_win = b * (h // ws) * (w // ws)
+    scale = _dropout_scale(seed, n_win, nh, n, p)
+    assert abs(float((scale > 0).float().mean()) - (1 - p)) < 0.01
+    pr, tr = packed.double().requires_grad_(), table.double().requires_grad_()
+    o_ref, _ = wa.window_attention(pr[..., :c], pr[..., c:2 * c], pr[..., 2 * c:], tr, ws, shift, nh, drop_scale=scale.double())
+    g_ref = torch.autograd.grad((o_ref * cot.double()).sum(), [pr, tr])
+    pg, tg = packed.to(DEV).requires_grad_(), table.to(DEV).requires_grad_()
+    o = ops.window_attention(pg, None, tg, ws, shift, nh, dropout_p=p, seed=seed)
+    g = torch.autograd.grad((o.float() * cot.to(DEV).float()).sum(), [pg, tg])
+    tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
+    assert rel_err(o.float(), o_ref) < tol
+    assert rel_err(g[0].float(), g_ref[0]) < tol and rel_err(g[1], g_ref[1]) < tol
+    # a different seed gives a different mask; p = 0 ignores the seed
+    o2 = ops.window_attention(pg, None, tg, ws, shift, nh, dropout_p=p, seed=seed + 1)
+    assert rel_err(o2.float(), o_ref) > 0.05
+    o0 = ops.window_attention(pg, None, tg, ws, shift, nh, dropout_p=0.0, seed=seed)
+    assert torch.equal(o0, ops.window_attention(pg, None, tg, ws, shift, nh))
+
+
+def test_attn_drop_module_is_identity_in_eval_and_unbiased_in_training():
+    blk = layers.SwinTransformerBlock(64, 2, window_size=7, shift_size=3, attn_drop=0.2).to(DEV)
+    ref = layers.SwinTransformerBlock(64, 2, window_size=7, shift_size=3).to(DEV)
+    ref.load_state_dict(blk.state_dict())
+    blk.H = blk.W = ref.H = ref.W = 14
+    x = randn("attndrop.x", 2, 196, 64).to(DEV)
+    with torch.no_grad():
+        assert torch.equal(blk.eval()(x, None), ref.eval()(x, None))
+        torch.manual_seed(0)
+        attn_ref = ref.attn.forward_image(x.view(2, 14, 14, 64), 3)
+        blk.train()
+        mean = sum(blk.attn.forward_image(x.view(2, 14, 14, 64), 3) for _ in range(200)) / 200
+    assert rel_err(mean, attn_ref) < 0.1   # E[dropout(P)] = P
+
+
 def test_library_counts_launches():
     before = _lib.launch_count()
     x = torch.zeros(1, 7, 7, 96, device=DEV)
