@@ -35,7 +35,7 @@ def test_shape_struct_matches_header_layout():
     ("dtype", 5, "dtype must be"),
     ("num_heads", 0, "must be positive"),
     ("q_pix_stride", 16, "pixel strides must be >="),
-    ("dropout_p", 0.5, "dropout"),
+    ("dropout_p", 1.5, "dropout_p must be in"),
 ])
 def test_validation_errors_without_gpu(field, value, msg):
     lib = _lib.load()
