@@ -78,11 +78,12 @@ int swin_attn_forward(const swin_attn_shape_t* shape, const void* q, const void*
   p.table = bias_table; p.o = o; p.lse = lse; p.trace = g_trace;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_forward_supported(p, shape->dtype);
+  const bool want_tc12 = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc12_forward_supported(p, shape->dtype);
+  bool want_tc = want_tc12 || (shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_forward_supported(p, shape->dtype));
   if (shape->impl == SWIN_ATTN_IMPL_TCGEN05 && !want_tc) return fail("tcgen05 forward does not support this shape/dtype");
   if (want_tc) {
     const char* why = nullptr;
-    cudaError_t e = launch_tc_forward(p, st, &why);
+    cudaError_t e = want_tc12 ? launch_tc12_forward(p, st, &why) : launch_tc_forward(p, st, &why);
     if (e != cudaSuccess) return why ? fail(std::string("tcgen05 forward: ") + why) : fail_cuda("tcgen05 forward launch", e);
     return 0;
   }
@@ -214,7 +215,7 @@ int swin_attn_uses_tcgen05(const swin_attn_shape_t* shape, int backward) {
   Problem p;
   if (make_problem(shape, p)) return 0;
   if (backward) return shape->impl != SWIN_ATTN_IMPL_SIMT && tc_backward_supported(p, shape->dtype) ? 1 : 0;
-  return shape->impl != SWIN_ATTN_IMPL_SIMT && tc_forward_supported(p, shape->dtype) ? 1 : 0;
+  return shape->impl != SWIN_ATTN_IMPL_SIMT && (tc_forward_supported(p, shape->dtype) || tc12_forward_supported(p, shape->dtype)) ? 1 : 0;
 }
 
 const char* swin_attn_last_error(void) { return g_error.c_str(); }

@@ -133,6 +133,8 @@ cudaError_t launch_simt_forward(const Problem& p, int dtype, cudaStream_t st);
 cudaError_t launch_simt_backward(const Problem& p, int dtype, cudaStream_t st);
 bool tc_forward_supported(const Problem& p, int dtype);
 cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** err);
+bool tc12_forward_supported(const Problem& p, int dtype);
+cudaError_t launch_tc12_forward(const Problem& p, cudaStream_t st, const char** err);
 bool tc_backward_supported(const Problem& p, int dtype);
 cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** err);
 

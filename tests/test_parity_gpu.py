@@ -64,6 +64,33 @@ def test_forward_matches_oracle(case, dtype, impl):
     assert rel_err(lse[:, :h, :w], want_lse[:, :h, :w]) < (1e-5 if dtype == torch.float32 else 2e-2)
 
 
+# window-12 shapes the tcgen05 window-12 forward serves (window-aligned, shift 0 / 6): single window (every wrap at
+# once), odd window counts, external v, several window chunks per head, many heads
+TC12_CASES = [(12, 0, 2, 24, 12, 2, True), (12, 6, 1, 24, 36, 4, False), (12, 6, 2, 12, 12, 1, False),
+              (12, 0, 1, 36, 60, 3, False), (12, 6, 3, 48, 24, 6, True), (12, 6, 1, 12, 24, 24, False)]
+
+
+@pytest.mark.parametrize("case", TC12_CASES)
+def test_forward_ws12_tcgen05_matches_oracle(case):
+    ws, shift, b, h, w, nh, ext = case
+    c = nh * 32
+    name = f"fwd12{case}"
+    packed = randn(name + ".p", b, h, w, (2 if ext else 3) * c).bfloat16()
+    v = randn(name + ".v", b, h, w, c).bfloat16() if ext else None
+    table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
+    want, want_lse = _oracle(packed.float(), None if v is None else v.float(), table, ws, shift, nh, None)
+    shp = _lib.Shape(b, h, w, nh, ws, shift, _lib.BF16, _lib.IMPL_TCGEN05, 32 ** -0.5, 0.0, 0, 3 * c, 3 * c, 3 * c, c, 0, 0)
+    assert _lib.load().swin_attn_uses_tcgen05(ctypes.byref(shp), 0) == 1
+    got, lse = torch.ops.swin_attn.fwd(packed.to(DEV), None if v is None else v.to(DEV), table.to(DEV), None,
+                                       None, ws, shift, nh, 32 ** -0.5, True, _lib.IMPL_TCGEN05, None)
+    assert rel_err(got.float(), want) < TOL_BF16
+    assert rel_err(lse, want_lse) < 2e-2
+    # against the CUDA-core kernel on the same bf16 inputs (same rounding points except P)
+    ref, _ = torch.ops.swin_attn.fwd(packed.to(DEV), None if v is None else v.to(DEV), table.to(DEV), None,
+                                     None, ws, shift, nh, 32 ** -0.5, False, _lib.IMPL_SIMT, None)
+    assert rel_err(got.float(), ref.float()) < TOL_BF16
+
+
 # window-aligned shapes for the backward: odd window counts (a job's last pair is half empty), several
 # window chunks per head, external v, shifted wrap rows / columns
 BWD_CASES = [c for c in CASES if c[3] % c[0] == 0 and c[4] % c[0] == 0] + [
