@@ -130,7 +130,7 @@ def run_reference(args, rank):
 
 def run_ours(args, env):
     from mde_b200 import _lib, ops
-    from mde_b200.harness import build_model, infer, synthetic_images
+    from mde_b200.harness import build_model, infer, prepare_inference, synthetic_images
 
     rank, world, local = env["rank"], env["world"], env["local_rank"]
     dev = torch.device("cuda", local)
@@ -176,7 +176,7 @@ def run_ours(args, env):
             out_host.copy_(trainer.step(x, y).reshape(1), non_blocking=True)
         h2d, d2h = host.numel() * 4 + gt_host.numel() * 4, 4
     else:
-        model.eval()
+        prepare_inference(model)   # eval, no grads, GEMM / conv weights stored in bf16 (what autocast reads anyway)
         out_host = torch.empty(args.batch, 1, height, width).pin_memory()
 
         def step_resident():

@@ -282,15 +282,21 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
       float l = 0.f, m_ub = 0.f;
       if (warp_on) {
         // pass 1: maximum of the raw scores
-        float mx = -INFINITY;
+        // (batches of 64 + 64 + 16 columns, four independent 3-input max chains per batch)
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int c = 0; c < 9; ++c) {
-          uint32_t r[16];
-          TMEM_LD_X16(taddr + 16 * c, r);
+        for (int blk = 0; blk < 3; ++blk) {
+          const int cols = blk < 2 ? 64 : 16;
+          uint32_t r[64];
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
+            if (16 * c < cols) TMEM_LD_X16(taddr + 64 * blk + 16 * c, (r + 16 * c));
           tmem_ld_wait();
 #pragma unroll
-          for (int e = 0; e < 16; e += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(r[e]), __uint_as_float(r[e + 1])));
+          for (int e = 0; e < 64; e += 2)
+            if (e < cols) mx4[(e >> 1) & 3] = fmaxf(mx4[(e >> 1) & 3], fmaxf(__uint_as_float(r[e]), __uint_as_float(r[e + 1])));
         }
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
         m_ub = fmaf(mx, c1s, bmax);
         float nm[2][2];
 #pragma unroll

@@ -95,6 +95,22 @@ def build_model(version: str = "large07", max_depth: float = 80.0, seed: int = 0
     return NewCRFDepth(version=version, max_depth=max_depth).to(device)
 
 
+def prepare_inference(model: nn.Module, bf16: bool = True) -> nn.Module:
+    """Deployment transform for ``infer``: eval mode, gradients off, and the Linear / Conv2d parameters stored in
+    bf16.  Under ``torch.autocast`` those are exactly the values every GEMM / conv already reads (autocast rounds
+    the fp32 parameters to bf16 on each call and drops the copies when the context exits), so outputs are bit
+    identical while ~400 cast kernels per forward disappear.  Norm parameters and the relative-position bias
+    tables stay fp32.  In place; returns the model."""
+    model.eval()
+    for p in model.parameters():
+        p.requires_grad_(False)
+    if bf16:
+        for m in model.modules():
+            if isinstance(m, (nn.Linear, nn.Conv2d)):
+                m.to(torch.bfloat16)
+    return model
+
+
 @torch.no_grad()
 def infer(model: nn.Module, images: torch.Tensor, bf16: bool = True) -> torch.Tensor:
     """The call a user makes for inference: images (B,3,H,W) on the model's device -> depth (B,1,H,W)."""

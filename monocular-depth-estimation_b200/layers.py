@@ -218,6 +218,9 @@ class BasicCRFLayer(nn.Module):
         self.downsample = downsample(dim=dim, norm_layer=norm_layer) if downsample is not None else None
 
     def forward(self, x, v, H, W):
+        if v.is_cuda and v.dtype == torch.float32 and torch.is_autocast_enabled() and \
+                torch.get_autocast_dtype("cuda") == torch.bfloat16:
+            v = v.to(torch.bfloat16)   # the value every block's kernel reads; cast once per level instead of per block
         for blk in self.blocks:
             blk.H, blk.W = H, W
             x = blk(x, v, None)
@@ -242,6 +245,11 @@ class NewCRF(nn.Module):
         self.norm_crf = norm_layer(embed_dim)
 
     def forward(self, x, v):
+        # channels-last strides through the level: the token views below are then free, and cuDNN's NHWC kernels
+        # take the conv inputs as they are (no layout conversion kernels around every conv)
+        if x.is_cuda:
+            x = x.contiguous(memory_format=torch.channels_last)
+            v = v.contiguous(memory_format=torch.channels_last)
         if self.proj_x is not None:
             x = self.proj_x(x)
         if self.proj_v is not None:
@@ -250,8 +258,9 @@ class NewCRF(nn.Module):
         x = x.flatten(2).transpose(1, 2)
         v = v.permute(0, 2, 3, 1)
         x_out, h, w, _, _, _ = self.crf_layer(x, v, h, w)
-        x_out = self.norm_crf(x_out)
-        return x_out.view(-1, h, w, self.embed_dim).permute(0, 3, 1, 2).contiguous()
+        x_out = ops.norm_fp32(self.norm_crf, x_out)
+        x_out = x_out.view(-1, h, w, self.embed_dim).permute(0, 3, 1, 2)
+        return x_out if x_out.is_cuda else x_out.contiguous()
 
 
 class SwinTransformerBlock(nn.Module):
@@ -346,8 +355,10 @@ class PatchEmbed(nn.Module):
             x = F.pad(x, (0, pw - w % pw))
         if h % ph:
             x = F.pad(x, (0, 0, 0, ph - h % ph))
+        if x.is_cuda:
+            x = x.contiguous(memory_format=torch.channels_last)   # conv output in NHWC: the token view below is free
         x = self.proj(x)
         if self.norm is not None:
             hh, ww = x.shape[2], x.shape[3]
-            x = self.norm(x.flatten(2).transpose(1, 2)).transpose(1, 2).view(-1, self.embed_dim, hh, ww)
+            x = ops.norm_fp32(self.norm, x.flatten(2).transpose(1, 2)).transpose(1, 2).view(-1, self.embed_dim, hh, ww)
         return x

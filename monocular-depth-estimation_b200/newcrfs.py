@@ -15,6 +15,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from . import ops
 from .layers import BasicLayer, NewCRF, PatchEmbed, PatchMerging
 
 _VARIANTS = {
@@ -93,8 +94,10 @@ class SwinTransformer(nn.Module):
         for i, layer in enumerate(self.layers):
             x_out, h, w, x, wh, ww = layer(x, wh, ww)
             if i in self.out_indices:
-                x_out = getattr(self, f"norm{i}")(x_out)
-                outs.append(x_out.view(-1, h, w, self.num_features[i]).permute(0, 3, 1, 2).contiguous())
+                x_out = ops.norm_fp32(getattr(self, f"norm{i}"), x_out)
+                # (B, C, H, W) in channels-last strides: the values and shape of the reference's contiguous NCHW
+                # copy (swin_transformer.py:607-608) without the copy; the decoder convs run NHWC in cuDNN anyway
+                outs.append(x_out.view(-1, h, w, self.num_features[i]).permute(0, 3, 1, 2))
         return tuple(outs)
 
     def train(self, mode=True):

@@ -317,6 +317,19 @@ def norm_for_linear(norm: torch.nn.Module, x: Tensor) -> Tensor:
     return norm(x)
 
 
+def norm_fp32(norm: torch.nn.Module, x: Tensor) -> Tensor:
+    """``norm(x)`` for a LayerNorm whose output is kept (stage outputs, ``norm_crf``, the patch-embedding norm).
+    Under bf16 autocast without gradients this is the fused kernel with an fp32 result -- the dtype autocast gives
+    ``nn.LayerNorm`` -- every other case is the module itself (the fused backward exists for the bf16-output form)."""
+    if (type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
+            and x.dtype in _DTYPES and torch.is_autocast_enabled()
+            and torch.get_autocast_dtype("cuda") == torch.bfloat16 and len(norm.normalized_shape) == 1
+            and x.shape[-1] in _LN_CHANNELS
+            and not (torch.is_grad_enabled() and (x.requires_grad or norm.weight.requires_grad or norm.bias.requires_grad))):
+        return torch.ops.swin_attn.layer_norm(x, norm.weight, norm.bias, norm.eps, False)
+    return norm(x)
+
+
 def window_attention(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, window: int, shift: int,
                      num_heads: int, scale: Optional[float] = None, packed_pad: Optional[Tensor] = None,
                      v_pad: Optional[Tensor] = None, impl: int = _lib.IMPL_AUTO,

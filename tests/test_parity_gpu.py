@@ -526,3 +526,29 @@ def test_library_counts_launches():
     ops.window_attention(x, None, torch.zeros(169, 1, device=DEV), 7, 0, 1)
     torch.cuda.synchronize()
     assert _lib.launch_count() == before + 1
+
+
+def test_prepare_inference_is_bit_identical_and_outputs_keep_reference_shapes(golden):
+    """harness.prepare_inference (GEMM / conv weights stored in bf16) reads the values autocast would cast on every
+    call: same bits out.  Stage outputs are channels-last strided but have the reference's NCHW shape and values."""
+    import copy
+    from mde_b200.harness import infer, prepare_inference
+    g = golden("newcrfdepth_tiny07")
+    cfg = g["cfg"]
+    m = mde_b200.NewCRFDepth(version=cfg["version"], max_depth=cfg["max_depth"])
+    m.load_state_dict(synthetic_state(m), strict=True)
+    m = m.to(DEV).eval()
+    img = g["img"].to(DEV)
+    want = infer(m, img)
+    prepared = prepare_inference(copy.deepcopy(m))
+    assert prepared.backbone.layers[0].blocks[0].attn.qkv.weight.dtype == torch.bfloat16
+    assert prepared.backbone.layers[0].blocks[0].attn.relative_position_bias_table.dtype == torch.float32
+    assert prepared.backbone.layers[0].blocks[0].norm1.weight.dtype == torch.float32
+    got = infer(prepared, img)
+    assert got.shape == want.shape and torch.equal(got, want)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        feats = m.backbone(img)
+    b, _, h, w = img.shape
+    for i, f in enumerate(feats):
+        assert f.shape == (b, m.backbone.num_features[i], -(-h // (4 << i)), -(-w // (4 << i))) and f.dtype == torch.float32
+        assert torch.equal(f.contiguous().permute(0, 2, 3, 1), f.permute(0, 2, 3, 1))

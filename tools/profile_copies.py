@@ -1,0 +1,27 @@
+#!/usr/bin/env python
+"""Where do the elementwise / copy kernels of one inference step come from?  torch.profiler with Python stacks,
+grouped by call site, for the ops outside the attention path (copy_, add, gelu, native_layer_norm, cat)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+from torch.profiler import ProfilerActivity, profile  # noqa: E402
+from mde_b200.harness import build_model, infer, synthetic_images  # noqa: E402
+
+dev = torch.device("cuda")
+model = build_model("large07", 80.0, seed=0, device=dev).eval()
+images = synthetic_images(8, 352, 1216, seed=0).to(dev)
+for _ in range(3):
+    infer(model, images)
+torch.cuda.synchronize()
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True, record_shapes=True) as prof:
+    infer(model, images)
+    torch.cuda.synchronize()
+want = ("aten::copy_", "aten::add", "aten::add_", "aten::gelu", "aten::native_layer_norm", "aten::cat", "aten::mul", "aten::_to_copy")
+rows = [e for e in prof.key_averages(group_by_stack_n=12, group_by_input_shape=True) if e.key in want]
+rows.sort(key=lambda e: -e.self_device_time_total)
+for e in rows[:28]:
+    stack = [s for s in e.stack if "mde_b200" in s or "monocular" in s or "harness" in s][:3]
+    print(f"{e.key:26s} {e.self_device_time_total / 1e3:8.3f} ms  x{e.count:<4d} {str(e.input_shapes)[:70]:70s} | " + " <- ".join(s.split('/')[-1] for s in stack))
