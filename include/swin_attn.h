@@ -120,10 +120,11 @@ int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, c
                            int32_t channels, void* out, int32_t out_dtype, void* stream);
 
 /* Backward of swin_layernorm_forward for training under autocast (autograd of nn.LayerNorm in the reference).
- * dy: (rows, channels) bf16, the gradient of the bf16 output; x: the forward's input (mean / rstd are recomputed).
+ * dy: (rows, channels) of dy_dtype (bf16 for the bf16-output form, fp32 for the fp32-output form); x: the forward's
+ * input (mean / rstd are recomputed).
  * dx: (rows, channels) of x_dtype; dgamma, dbeta: (channels) fp32, OVERWRITTEN (zeroed, then accumulated).
  * channels in {128, 192, 256, 384, 512, 768, 1024, 1536}. */
-int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, const float* gamma, float eps, int64_t rows,
+int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int32_t dy_dtype, const float* gamma, float eps, int64_t rows,
                             int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream);
 
 /* Number of kernel launches issued by this library since load (all threads). */

@@ -63,7 +63,7 @@ def load() -> ctypes.CDLL:
     lib.swin_attn_forward_host.restype = c_int
     lib.swin_layernorm_forward.argtypes = [vp, c_int32, vp, vp, c_float, c_int64, c_int32, vp, c_int32, vp]
     lib.swin_layernorm_forward.restype = c_int
-    lib.swin_layernorm_backward.argtypes = [vp, c_int32, vp, vp, c_float, c_int64, c_int32, vp, vp, vp, vp]
+    lib.swin_layernorm_backward.argtypes = [vp, c_int32, vp, c_int32, vp, c_float, c_int64, c_int32, vp, vp, vp, vp]
     lib.swin_layernorm_backward.restype = c_int
     lib.swin_attn_launch_count.argtypes = []
     lib.swin_attn_launch_count.restype = c_uint64

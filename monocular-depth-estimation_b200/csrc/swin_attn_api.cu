@@ -183,23 +183,24 @@ int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, c
   return 0;
 }
 
-int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, const float* gamma, float eps, int64_t rows,
+int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int32_t dy_dtype, const float* gamma, float eps, int64_t rows,
                             int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream) {
   if (!x || !dy || !gamma || !dx || !dgamma || !dbeta) return fail("layernorm backward: all pointers must be non-null");
   if (rows < 0) return fail("layernorm backward: bad row count");
   if (x_dtype != SWIN_ATTN_F32 && x_dtype != SWIN_ATTN_BF16) return fail("layernorm backward: x_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
+  if (dy_dtype != SWIN_ATTN_F32 && dy_dtype != SWIN_ATTN_BF16) return fail("layernorm backward: dy_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
   if (!layernorm_supported(channels) || channels > 1536)
     return fail("layernorm backward: channels must be one of 128, 192, 256, 384, 512, 768, 1024, 1536 (got " + std::to_string(channels) + ")");
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(gamma)) & 7 ||
-      (reinterpret_cast<uintptr_t>(dy) & 3))
-    return fail("layernorm backward: pointers must be 8-byte aligned (dy: 4)");
+      (reinterpret_cast<uintptr_t>(dy) & (dy_dtype == SWIN_ATTN_F32 ? 7 : 3)))
+    return fail("layernorm backward: pointers must be 8-byte aligned (bf16 dy: 4)");
   static int sms = 0;
   if (sms == 0) {
     int dev = 0;
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
   }
-  cudaError_t e = launch_layernorm_backward(x, x_dtype, dy, gamma, eps, rows, channels, dx, dgamma, dbeta, sms,
+  cudaError_t e = launch_layernorm_backward(x, x_dtype, dy, dy_dtype, gamma, eps, rows, channels, dx, dgamma, dbeta, sms,
                                             static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) return fail_cuda("layernorm backward launch", e);
   return 0;

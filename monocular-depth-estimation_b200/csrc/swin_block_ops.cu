@@ -70,8 +70,8 @@ __global__ void __launch_bounds__(256) layernorm_rows_kernel(const TIn* __restri
 // One warp per row, grid-stride over rows; every warp accumulates its dgamma / dbeta partials in a private shared-
 // memory row (lane l owns the same channels for every row, so there are no conflicts and no atomics), the CTA
 // reduces its 8 rows at the end and adds them to global memory with one atomic per channel.
-template <int NC, typename TX>
-__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const TX* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+template <int NC, typename TX, typename TDy>
+__global__ void __launch_bounds__(256) layernorm_bwd_kernel(const TX* __restrict__ x, const TDy* __restrict__ dy,
                                                             const float* __restrict__ gamma, float eps, int64_t rows,
                                                             TX* __restrict__ dx, float* __restrict__ dgamma,
                                                             float* __restrict__ dbeta) {
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const TX* __restrict
 }
 
 template <int NC>
-static cudaError_t launch_ln_bwd(const void* x, int x_dtype, const void* dy, const float* g, float eps, int64_t rows, void* dx,
+static cudaError_t launch_ln_bwd(const void* x, int x_dtype, const void* dy, int dy_dtype, const float* g, float eps, int64_t rows, void* dx,
                                  float* dgamma, float* dbeta, int sms, cudaStream_t st) {
   const size_t smem = (size_t)8 * 2 * 64 * NC * sizeof(float);
   int64_t want = (rows + 7) / 8;
@@ -167,23 +167,25 @@ static cudaError_t launch_ln_bwd(const void* x, int x_dtype, const void* dy, con
   if (e == cudaSuccess) e = cudaMemsetAsync(dbeta, 0, sizeof(float) * 64 * NC, st);
   if (e != cudaSuccess) return e;
   using bf = __nv_bfloat16;
-  if (x_dtype == SWIN_ATTN_F32) {
-    auto k = layernorm_bwd_kernel<NC, float>;
-    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-    k<<<grid, 256, smem, st>>>(static_cast<const float*>(x), static_cast<const bf*>(dy), g, eps, rows, static_cast<float*>(dx), dgamma, dbeta);
-  } else {
-    auto k = layernorm_bwd_kernel<NC, bf>;
-    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-    k<<<grid, 256, smem, st>>>(static_cast<const bf*>(x), static_cast<const bf*>(dy), g, eps, rows, static_cast<bf*>(dx), dgamma, dbeta);
-  }
+#define SWIN_LN_BWD(TX, TDY)                                                                                        \
+  do {                                                                                                              \
+    auto k = layernorm_bwd_kernel<NC, TX, TDY>;                                                                     \
+    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e; \
+    k<<<grid, 256, smem, st>>>(static_cast<const TX*>(x), static_cast<const TDY*>(dy), g, eps, rows, static_cast<TX*>(dx), dgamma, dbeta); \
+  } while (0)
+  if (x_dtype == SWIN_ATTN_F32 && dy_dtype == SWIN_ATTN_F32) SWIN_LN_BWD(float, float);
+  else if (x_dtype == SWIN_ATTN_F32) SWIN_LN_BWD(float, bf);
+  else if (dy_dtype == SWIN_ATTN_F32) SWIN_LN_BWD(bf, float);
+  else SWIN_LN_BWD(bf, bf);
+#undef SWIN_LN_BWD
   count_launch();
   return cudaGetLastError();
 }
 
-cudaError_t launch_layernorm_backward(const void* x, int x_dtype, const void* dy, const float* g, float eps, int64_t rows,
+cudaError_t launch_layernorm_backward(const void* x, int x_dtype, const void* dy, int dy_dtype, const float* g, float eps, int64_t rows,
                                       int channels, void* dx, float* dgamma, float* dbeta, int sms, cudaStream_t st) {
   switch (channels / 64) {
-#define SWIN_LN_CASE(NC) case NC: return launch_ln_bwd<NC>(x, x_dtype, dy, g, eps, rows, dx, dgamma, dbeta, sms, st)
+#define SWIN_LN_CASE(NC) case NC: return launch_ln_bwd<NC>(x, x_dtype, dy, dy_dtype, g, eps, rows, dx, dgamma, dbeta, sms, st)
     SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
     SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24);   // 3072 channels: the row does not fit in registers
 #undef SWIN_LN_CASE

@@ -140,7 +140,7 @@ cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** e
 
 cudaError_t launch_layernorm(const void* x, int x_dtype, const float* gamma, const float* beta, float eps, int64_t rows, int channels,
                              void* out, int out_dtype, cudaStream_t st);
-cudaError_t launch_layernorm_backward(const void* x, int x_dtype, const void* dy, const float* gamma, float eps, int64_t rows,
+cudaError_t launch_layernorm_backward(const void* x, int x_dtype, const void* dy, int dy_dtype, const float* gamma, float eps, int64_t rows,
                                       int channels, void* dx, float* dgamma, float* dbeta, int sms, cudaStream_t st);
 bool layernorm_supported(int channels);
 

@@ -125,7 +125,8 @@ class Trainer:
                  ddp: bool = False, device_ids=None):
         self.raw = model
         self.model = nn.parallel.DistributedDataParallel(model, device_ids=device_ids) if ddp else model
-        self.opt = torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=0.0)
+        self.opt = torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=0.0,
+                                     fused=next(model.parameters()).is_cuda)   # one multi-tensor kernel per step
         self.loss_fn = SILogLoss()
         self.grad_norm, self.bf16 = grad_norm, bf16
 

@@ -45,7 +45,7 @@ class DropPath(nn.Module):
             return x
         keep = 1.0 - self.drop_prob
         gate = x.new_empty((x.shape[0],) + (1,) * (x.ndim - 1)).bernoulli_(keep)
-        return x * gate / keep
+        return x * (gate / keep)   # one pass over x (timm: x.div(keep) * gate)
 
 
 class Mlp(nn.Module):

@@ -263,16 +263,19 @@ def _(x, weight, bias, eps, out_bf16):
 
 @torch.library.custom_op("swin_attn::layer_norm_bwd", mutates_args=(), device_types="cuda")
 def _layer_norm_bwd(dy: Tensor, x: Tensor, weight: Tensor, eps: float) -> Tuple[Tensor, Tensor, Tensor]:
-    """``swin_layernorm_backward``: (dx, dweight, dbias) from the bf16 output gradient and the saved input."""
+    """``swin_layernorm_backward``: (dx, dweight, dbias) from the output gradient (bf16 or fp32, the dtype of the
+    forward's output) and the saved input."""
     lib = _lib.load()
     x = x.contiguous()
-    dy = dy.to(torch.bfloat16).contiguous()
+    if dy.dtype not in _DTYPES:
+        dy = dy.to(torch.float32)
+    dy = dy.contiguous()
     c = x.shape[-1]
     dx = torch.empty_like(x)
     w = weight.detach().float().contiguous()
     dw, db = torch.empty_like(w), torch.empty_like(w)
     with torch.cuda.device(x.device):
-        _lib.check(lib.swin_layernorm_backward(_ptr(x), _DTYPES[x.dtype], _ptr(dy), _ptr(w), float(eps), x.numel() // c, c,
+        _lib.check(lib.swin_layernorm_backward(_ptr(x), _DTYPES[x.dtype], _ptr(dy), _DTYPES[dy.dtype], _ptr(w), float(eps), x.numel() // c, c,
                                                _ptr(dx), _ptr(dw), _ptr(db),
                                                ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
     return dx, dw, db
@@ -293,8 +296,9 @@ def _ln_setup_context(ctx, inputs, output):
 
 def _ln_backward(ctx, dy):
     x, weight = ctx.saved_tensors
-    if not ctx.out_bf16 or x.shape[-1] > 1536:
-        raise RuntimeError("swin_attn::layer_norm: backward exists for the bf16-output form with <= 1536 channels")
+    if x.shape[-1] > 1536:
+        raise RuntimeError("swin_attn::layer_norm: the backward covers <= 1536 channels")
+    dy = dy.to(torch.bfloat16 if ctx.out_bf16 else torch.float32)
     dx, dw, db = torch.ops.swin_attn.layer_norm_bwd(dy, x, weight, ctx.eps)
     return dx, dw.to(ctx.param_dtype), db.to(ctx.param_dtype), None, None
 
@@ -319,14 +323,15 @@ def norm_for_linear(norm: torch.nn.Module, x: Tensor) -> Tensor:
 
 def norm_fp32(norm: torch.nn.Module, x: Tensor) -> Tensor:
     """``norm(x)`` for a LayerNorm whose output is kept (stage outputs, ``norm_crf``, the patch-embedding norm).
-    Under bf16 autocast without gradients this is the fused kernel with an fp32 result -- the dtype autocast gives
-    ``nn.LayerNorm`` -- every other case is the module itself (the fused backward exists for the bf16-output form)."""
+    Under bf16 autocast this is the fused kernel with an fp32 result -- the dtype autocast gives ``nn.LayerNorm`` --
+    every other case (fp32 mode, unsupported widths, training above 1536 channels) is the module itself."""
     if (type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
             and x.dtype in _DTYPES and torch.is_autocast_enabled()
             and torch.get_autocast_dtype("cuda") == torch.bfloat16 and len(norm.normalized_shape) == 1
-            and x.shape[-1] in _LN_CHANNELS
-            and not (torch.is_grad_enabled() and (x.requires_grad or norm.weight.requires_grad or norm.bias.requires_grad))):
-        return torch.ops.swin_attn.layer_norm(x, norm.weight, norm.bias, norm.eps, False)
+            and x.shape[-1] in _LN_CHANNELS):
+        needs_grad = torch.is_grad_enabled() and (x.requires_grad or norm.weight.requires_grad or norm.bias.requires_grad)
+        if not needs_grad or x.shape[-1] <= 1536:
+            return torch.ops.swin_attn.layer_norm(x, norm.weight, norm.bias, norm.eps, False)
     return norm(x)
 
 

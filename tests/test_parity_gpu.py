@@ -419,20 +419,25 @@ def test_fused_layernorm_matches_torch(c):
         assert ops.norm_for_linear(ln, x).dtype == torch.float32        # fp32 mode: the module itself
 
 
+@pytest.mark.parametrize("out_bf16", [True, False])
 @pytest.mark.parametrize("xdtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("c", [128, 192, 256, 384, 512, 768, 1024, 1536])
-def test_fused_layernorm_backward_matches_torch_autograd(c, xdtype):
-    """swin_layernorm_backward vs autograd through F.layer_norm in fp32 on the same (bf16-rounded) dy."""
+def test_fused_layernorm_backward_matches_torch_autograd(c, xdtype, out_bf16):
+    """swin_layernorm_backward vs autograd through F.layer_norm in fp32 on the same dy (bf16-rounded for the
+    bf16-output form, fp32 for the fp32-output form of the kept norms)."""
     gen = torch.Generator(device=DEV).manual_seed(100 + c)
     x = (2.0 * torch.randn(2051, c, device=DEV, generator=gen) - 0.4).to(xdtype)
     w = (1.0 + 0.3 * torch.randn(c, device=DEV, generator=gen)).requires_grad_()
     b = (0.2 * torch.randn(c, device=DEV, generator=gen)).requires_grad_()
-    dy = torch.randn(2051, c, device=DEV, generator=gen).bfloat16()
+    dy = torch.randn(2051, c, device=DEV, generator=gen)
+    if out_bf16:
+        dy = dy.bfloat16()
     xr = x.float().requires_grad_()
     want = torch.autograd.grad((torch.nn.functional.layer_norm(xr, (c,), w, b, 1e-5) * dy.float()).sum(), [xr, w, b])
     xg = x.clone().requires_grad_()
-    y = torch.ops.swin_attn.layer_norm(xg, w, b, 1e-5, True)
-    got = torch.autograd.grad((y.float() * dy.float()).sum(), [xg, w, b])
+    y = torch.ops.swin_attn.layer_norm(xg, w, b, 1e-5, out_bf16)
+    assert y.dtype == (torch.bfloat16 if out_bf16 else torch.float32)
+    got = torch.autograd.grad(y, [xg, w, b], grad_outputs=dy)
     assert got[0].dtype == xdtype and got[1].dtype == torch.float32
     assert rel_err(got[0].float(), want[0]) < (1e-5 if xdtype == torch.float32 else 4e-3)   # bf16 dx: one rounding
     assert rel_err(got[1], want[1]) < 2e-5 and rel_err(got[2], want[2]) < 2e-5
