@@ -214,10 +214,10 @@ def run_ours(args, env):
     hbm, tf, which = peaks()
 
     def roof(recs, name):
-        k_ms = sum(a.elapsed_time(b) for a, b, *_ in recs)
+        k_ms = sum(r[0] for r in recs)
         if not recs or not k_ms:
             return None
-        k_bytes, k_flops = sum(r[2] for r in recs), sum(r[3] for r in recs)
+        k_bytes, k_flops = sum(r[1] for r in recs), sum(r[2] for r in recs)
         achieved = k_bytes / (k_ms * 1e-3) / 1e9
         return {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                 "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
@@ -230,8 +230,8 @@ def run_ours(args, env):
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
         traffic = json.load(open(tpath))
-    fwd_recs = [r for r in records if r[4][0] == "fwd"]
-    bwd_recs = [r for r in records if r[4][0] == "bwd"]
+    fwd_recs = [r for r in records if r[3][0] == "fwd"]
+    bwd_recs = [r for r in records if r[3][0] == "bwd"]
     roof_fwd = roof(fwd_recs, "swin_attn forward (all window-attention forward launches of the step)")
     roof_bwd = roof(bwd_recs, "swin_attn backward (all window-attention backward launches of the step)")
     n_img = args.batch * world * args.steps

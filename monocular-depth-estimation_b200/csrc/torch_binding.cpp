@@ -1,0 +1,453 @@
+// torch.library registration of the C ABI (include/swin_attn.h) as dispatcher ops with C++ kernels:
+//   swin_attn::fwd / swin_attn::bwd / swin_attn::layer_norm / swin_attn::layer_norm_bwd
+// CUDA implementations (argument checks, layout normalisation, output allocation, one C-ABI call on the current
+// stream), Meta implementations (shape inference for FakeTensor / torch.compile / DDP), and Autograd-key
+// implementations (torch::autograd::Function) so that a training step pays a few microseconds of host time per op
+// instead of the ~60-300 us of Python-defined custom ops -- the step was host-bound with those.
+//
+// Nothing here computes: every number comes from libswin_attn.so.  No CPU kernels are registered on purpose.
+#include <ATen/ATen.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <cuda_runtime.h>
+#include <torch/csrc/autograd/custom_function.h>
+#include <torch/library.h>
+
+#include <mutex>
+#include <vector>
+
+#include "../../include/swin_attn.h"
+
+namespace {
+
+using at::Tensor;
+using c10::optional;
+using torch::autograd::AutogradContext;
+using torch::autograd::variable_list;
+
+// ---- optional per-launch timing (bench.py's live roofline) --------------------------------------------------
+struct TimingRecord {
+  cudaEvent_t start, stop;
+  int64_t bytes, flops;
+  int64_t tag[6];   // kind (0 fwd, 1 bwd), window, shift, heads, height, width
+};
+std::mutex g_timing_mutex;
+bool g_timing_on = false;
+std::vector<TimingRecord> g_records;
+
+struct TimedLaunch {
+  bool on;
+  TimingRecord rec;
+  cudaStream_t stream;
+  explicit TimedLaunch(cudaStream_t st) : on(g_timing_on), stream(st) {
+    if (on) {
+      cudaEventCreate(&rec.start);
+      cudaEventCreate(&rec.stop);
+      cudaEventRecord(rec.start, stream);
+    }
+  }
+  void finish(int64_t bytes, int64_t flops, int64_t kind, int64_t window, int64_t shift, int64_t heads, int64_t h, int64_t w) {
+    if (!on) return;
+    cudaEventRecord(rec.stop, stream);
+    rec.bytes = bytes;
+    rec.flops = flops;
+    const int64_t tag[6] = {kind, window, shift, heads, h, w};
+    for (int i = 0; i < 6; ++i) rec.tag[i] = tag[i];
+    std::lock_guard<std::mutex> lock(g_timing_mutex);
+    g_records.push_back(rec);
+  }
+};
+
+inline void check_rc(int rc) { TORCH_CHECK(rc == 0, "swin_attn: ", swin_attn_last_error()); }
+
+inline int32_t dtype_code(at::ScalarType t) {
+  TORCH_CHECK(t == at::kFloat || t == at::kBFloat16, "swin_attn: dtype ", t, " is not supported (float32 or bfloat16)");
+  return t == at::kFloat ? SWIN_ATTN_F32 : SWIN_ATTN_BF16;
+}
+
+// Dense rows / images with unit channel stride (the pixel stride may exceed C: slices of a packed projection).
+inline Tensor image_layout(const Tensor& t) {
+  const auto s = t.strides();
+  const auto d = t.sizes();
+  if (s[3] == 1 && s[1] == d[2] * s[2] && s[0] == d[1] * s[1] && s[2] % 4 == 0 && s[2] >= d[3]) return t;
+  return t.contiguous();
+}
+
+inline int64_t split_channels(const Tensor& packed, const optional<Tensor>& v, int64_t num_heads) {
+  const int64_t c = num_heads * 32;
+  const int64_t want = v.has_value() ? 2 * c : 3 * c;
+  TORCH_CHECK(packed.dim() == 4 && packed.size(3) == want, "swin_attn: packed projection must be (B,H,W,", want, ") for ",
+              num_heads, " heads of dim 32, got ", packed.sizes());
+  if (v.has_value())   // reference assert, newcrf_layers.py:143
+    TORCH_CHECK(v->dim() == 4 && v->size(0) == packed.size(0) && v->size(1) == packed.size(1) && v->size(2) == packed.size(2) &&
+                    v->size(3) == c, "self.dim != v.shape[-1]");
+  return c;
+}
+
+inline Tensor mask_arg(const optional<Tensor>& attn_mask, int64_t window, int32_t* n_windows) {
+  *n_windows = 0;
+  if (!attn_mask.has_value()) return Tensor();
+  const int64_t n = window * window;
+  TORCH_CHECK(attn_mask->dim() == 3 && attn_mask->size(1) == n && attn_mask->size(2) == n, "swin_attn: attn_mask must be (nW, ", n,
+              ", ", n, "), got ", attn_mask->sizes());
+  *n_windows = (int32_t)attn_mask->size(0);
+  return attn_mask->detach().to(at::kFloat).contiguous();
+}
+
+inline swin_attn_shape_t make_shape(int64_t b, int64_t h, int64_t w, int64_t heads, int64_t window, int64_t shift, at::ScalarType dt,
+                                    int64_t impl, double scale, int64_t q_ps, int64_t k_ps, int64_t v_ps, int64_t o_ps,
+                                    int32_t mask_windows, double dropout_p, int64_t seed) {
+  swin_attn_shape_t s;
+  memset(&s, 0, sizeof(s));
+  s.batch = (int32_t)b; s.height = (int32_t)h; s.width = (int32_t)w; s.num_heads = (int32_t)heads;
+  s.window = (int32_t)window; s.shift = (int32_t)shift; s.dtype = dtype_code(dt); s.impl = (int32_t)impl;
+  s.scale = (float)scale; s.dropout_p = (float)dropout_p; s.seed = (uint64_t)seed;
+  s.q_pix_stride = q_ps; s.k_pix_stride = k_ps; s.v_pix_stride = v_ps; s.o_pix_stride = o_ps;
+  s.mask_windows = mask_windows;
+  return s;
+}
+
+inline const char* byte_ptr(const Tensor& t) { return static_cast<const char*>(t.data_ptr()); }
+
+// ---- swin_attn::fwd ------------------------------------------------------------------------------------------
+std::tuple<Tensor, Tensor> fwd_cuda(const Tensor& packed_in, const optional<Tensor>& v_in, const Tensor& bias_table,
+                                    const optional<Tensor>& packed_pad_in, const optional<Tensor>& v_pad_in, int64_t window,
+                                    int64_t shift, int64_t num_heads, double scale, bool need_lse, int64_t impl,
+                                    const optional<Tensor>& attn_mask, double dropout_p, int64_t seed) {
+  TORCH_CHECK(window > 0, "swin_attn: window must be positive");
+  const int64_t c = split_channels(packed_in, v_in, num_heads);
+  int32_t mask_nw = 0;
+  const Tensor mask = mask_arg(attn_mask, window, &mask_nw);
+  const Tensor packed = image_layout(packed_in);
+  const auto dt = packed.scalar_type();
+  dtype_code(dt);
+  const int64_t b = packed.size(0), h = packed.size(1), w = packed.size(2);
+  const int64_t ps = packed.stride(2), es = packed.element_size();
+  const char* base = byte_ptr(packed);
+  Tensor v, packed_pad, v_pad;
+  const char *v_ptr, *qpad = nullptr, *kpad = nullptr, *vpad = nullptr;
+  int64_t v_ps;
+  if (packed_pad_in.has_value()) {
+    packed_pad = packed_pad_in->to(dt).contiguous();
+    qpad = byte_ptr(packed_pad);
+    kpad = qpad + c * es;
+  }
+  if (!v_in.has_value()) {
+    v_ptr = base + 2 * c * es;
+    v_ps = ps;
+    if (qpad) vpad = qpad + 2 * c * es;
+  } else {
+    v = image_layout(v_in->to(dt));
+    v_ptr = byte_ptr(v);
+    v_ps = v.stride(2);
+    if (v_pad_in.has_value()) {
+      v_pad = v_pad_in->to(dt).contiguous();
+      vpad = byte_ptr(v_pad);
+    }
+  }
+  const Tensor table = bias_table.detach().to(at::kFloat).contiguous();
+  const int64_t hp = (h + window - 1) / window * window, wp = (w + window - 1) / window * window;
+  Tensor o = at::empty({b, h, w, c}, packed.options());
+  Tensor lse = need_lse ? at::empty({b, hp, wp, num_heads}, packed.options().dtype(at::kFloat))
+                        : at::empty({0}, packed.options().dtype(at::kFloat));
+  const swin_attn_shape_t shp = make_shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw, dropout_p, seed);
+  c10::cuda::CUDAGuard guard(packed.device());
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  TimedLaunch timed(stream);
+  check_rc(swin_attn_forward(&shp, base, base + c * es, v_ptr, qpad, kpad, vpad, table.data_ptr<float>(),
+                             mask.defined() ? mask.data_ptr<float>() : nullptr, o.data_ptr(),
+                             need_lse ? lse.data_ptr<float>() : nullptr, stream));
+  // algorithmic traffic: read q, k, v and write o once, valid tokens only
+  timed.finish(4 * b * h * w * c * es + (need_lse ? lse.numel() * 4 : 0), 4 * b * hp * wp * window * window * c, 0, window, shift,
+               num_heads, h, w);
+  return {o, lse};
+}
+
+std::tuple<Tensor, Tensor> fwd_meta(const Tensor& packed, const optional<Tensor>& v, const Tensor&, const optional<Tensor>&,
+                                    const optional<Tensor>&, int64_t window, int64_t, int64_t num_heads, double, bool need_lse,
+                                    int64_t, const optional<Tensor>&, double, int64_t) {
+  const auto b = packed.sym_size(0), h = packed.sym_size(1), w = packed.sym_size(2);
+  const c10::SymInt c = num_heads * 32;
+  const auto hp = (h + (window - 1)) / window * window, wp = (w + (window - 1)) / window * window;
+  Tensor o = at::empty_symint({b, h, w, c}, packed.options());
+  Tensor lse = need_lse ? at::empty_symint({b, hp, wp, c10::SymInt(num_heads)}, packed.options().dtype(at::kFloat))
+                        : at::empty({0}, packed.options().dtype(at::kFloat));
+  return {o, lse};
+}
+
+// ---- swin_attn::bwd ------------------------------------------------------------------------------------------
+std::tuple<Tensor, Tensor, Tensor> bwd_cuda(const Tensor& d_o_in, const Tensor& packed_in, const optional<Tensor>& v_in,
+                                            const Tensor& o_in, const Tensor& lse, const Tensor& bias_table, int64_t window,
+                                            int64_t shift, int64_t num_heads, double scale, const optional<Tensor>& attn_mask,
+                                            int64_t impl, double dropout_p, int64_t seed) {
+  const int64_t c = split_channels(packed_in, v_in, num_heads);
+  int32_t mask_nw = 0;
+  const Tensor mask = mask_arg(attn_mask, window, &mask_nw);
+  Tensor packed = image_layout(packed_in);
+  const auto dt = packed.scalar_type();
+  dtype_code(dt);
+  const int64_t b = packed.size(0), h = packed.size(1), w = packed.size(2), pc = packed.size(3);
+  const int64_t es = packed.element_size();
+  Tensor v;
+  if (v_in.has_value()) v = image_layout(v_in->to(dt));
+  // Gradients are written with the strides of d_packed / d_v (dense): the inputs must be dense as well, because one
+  // shape struct carries one stride per tensor role.
+  if (packed.stride(2) != pc) packed = packed.contiguous();
+  if (v.defined() && v.stride(2) != c) v = v.contiguous();
+  const int64_t ps = packed.stride(2);
+  const Tensor d_o = d_o_in.to(dt).contiguous();
+  const Tensor o = o_in.contiguous();
+  Tensor d_packed = at::empty({b, h, w, pc}, packed.options());
+  Tensor d_v;
+  const char* v_ptr;
+  char* dv_ptr;
+  int64_t v_ps;
+  char* dbase = static_cast<char*>(d_packed.data_ptr());
+  const char* base = byte_ptr(packed);
+  if (!v.defined()) {
+    v_ptr = base + 2 * c * es;
+    v_ps = ps;
+    d_v = at::empty({0}, packed.options());
+    dv_ptr = dbase + 2 * c * es;
+  } else {
+    v_ptr = byte_ptr(v);
+    v_ps = v.stride(2);
+    d_v = at::empty({b, h, w, c}, packed.options());
+    dv_ptr = static_cast<char*>(d_v.data_ptr());
+  }
+  const Tensor table = bias_table.detach().to(at::kFloat).contiguous();
+  Tensor d_table = at::empty_like(table);
+  const swin_attn_shape_t shp = make_shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw, dropout_p, seed);
+  c10::cuda::CUDAGuard guard(packed.device());
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  TimedLaunch timed(stream);
+  check_rc(swin_attn_backward(&shp, base, base + c * es, v_ptr, o.data_ptr(), d_o.data_ptr(), lse.data_ptr<float>(),
+                              table.data_ptr<float>(), mask.defined() ? mask.data_ptr<float>() : nullptr, dbase, dbase + c * es,
+                              dv_ptr, d_table.data_ptr<float>(), stream));
+  // algorithmic traffic of the recompute backward: read q, k, v, dO + lse, write dq, dk, dv
+  timed.finish(7 * b * h * w * c * es + lse.numel() * 4, 10 * b * h * w * window * window * c, 1, window, shift, num_heads, h, w);
+  return {d_packed, d_v, d_table.to(bias_table.scalar_type())};
+}
+
+std::tuple<Tensor, Tensor, Tensor> bwd_meta(const Tensor&, const Tensor& packed, const optional<Tensor>& v, const Tensor&,
+                                            const Tensor&, const Tensor& bias_table, int64_t, int64_t, int64_t, double,
+                                            const optional<Tensor>&, int64_t, double, int64_t) {
+  Tensor d_packed = at::empty_symint(packed.sym_sizes(), packed.options());
+  Tensor d_v = v.has_value() ? at::empty_symint(v->sym_sizes(), packed.options()) : at::empty({0}, packed.options());
+  return {d_packed, d_v, at::empty_like(bias_table)};
+}
+
+// ---- swin_attn::layer_norm / layer_norm_bwd ------------------------------------------------------------------
+Tensor layer_norm_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& bias, double eps, bool out_bf16) {
+  const int32_t xd = dtype_code(x_in.scalar_type());
+  const Tensor x = x_in.contiguous();
+  const int64_t c = x.size(-1);
+  Tensor out = at::empty(x.sizes(), x.options().dtype(out_bf16 ? at::kBFloat16 : at::kFloat));
+  const Tensor w = weight.detach().to(at::kFloat).contiguous(), b = bias.detach().to(at::kFloat).contiguous();
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(swin_layernorm_forward(x.data_ptr(), xd, w.data_ptr<float>(), b.data_ptr<float>(), (float)eps, c ? x.numel() / c : 0,
+                                  (int32_t)c, out.data_ptr(), out_bf16 ? SWIN_ATTN_BF16 : SWIN_ATTN_F32,
+                                  at::cuda::getCurrentCUDAStream()));
+  return out;
+}
+
+Tensor layer_norm_meta(const Tensor& x, const Tensor&, const Tensor&, double, bool out_bf16) {
+  return at::empty_symint(x.sym_sizes(), x.options().dtype(out_bf16 ? at::kBFloat16 : at::kFloat));
+}
+
+std::tuple<Tensor, Tensor, Tensor> layer_norm_bwd_cuda(const Tensor& dy_in, const Tensor& x_in, const Tensor& weight, double eps) {
+  const int32_t xd = dtype_code(x_in.scalar_type());
+  const Tensor x = x_in.contiguous();
+  Tensor dy = dy_in;
+  if (dy.scalar_type() != at::kFloat && dy.scalar_type() != at::kBFloat16) dy = dy.to(at::kFloat);
+  dy = dy.contiguous();
+  const int64_t c = x.size(-1);
+  Tensor dx = at::empty_like(x);
+  const Tensor w = weight.detach().to(at::kFloat).contiguous();
+  Tensor dw = at::empty_like(w), db = at::empty_like(w);
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(swin_layernorm_backward(x.data_ptr(), xd, dy.data_ptr(), dtype_code(dy.scalar_type()), w.data_ptr<float>(), (float)eps,
+                                   c ? x.numel() / c : 0, (int32_t)c, dx.data_ptr(), dw.data_ptr<float>(), db.data_ptr<float>(),
+                                   at::cuda::getCurrentCUDAStream()));
+  return {dx, dw, db};
+}
+
+std::tuple<Tensor, Tensor, Tensor> layer_norm_bwd_meta(const Tensor&, const Tensor& x, const Tensor& weight, double) {
+  Tensor w = at::empty_symint(weight.sym_sizes(), weight.options().dtype(at::kFloat));
+  return {at::empty_symint(x.sym_sizes(), x.options()), w, at::empty_like(w)};
+}
+
+// ---- dispatcher handles ----------------------------------------------------------------------------------------
+using FwdSig = std::tuple<Tensor, Tensor>(const Tensor&, const optional<Tensor>&, const Tensor&, const optional<Tensor>&,
+                                          const optional<Tensor>&, int64_t, int64_t, int64_t, double, bool, int64_t,
+                                          const optional<Tensor>&, double, int64_t);
+using BwdSig = std::tuple<Tensor, Tensor, Tensor>(const Tensor&, const Tensor&, const optional<Tensor>&, const Tensor&, const Tensor&,
+                                                  const Tensor&, int64_t, int64_t, int64_t, double, const optional<Tensor>&, int64_t,
+                                                  double, int64_t);
+using LnSig = Tensor(const Tensor&, const Tensor&, const Tensor&, double, bool);
+using LnBwdSig = std::tuple<Tensor, Tensor, Tensor>(const Tensor&, const Tensor&, const Tensor&, double);
+
+inline auto fwd_op() {
+  static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::fwd", "").typed<FwdSig>();
+  return op;
+}
+inline auto bwd_op() {
+  static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::bwd", "").typed<BwdSig>();
+  return op;
+}
+inline auto ln_op() {
+  static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::layer_norm", "").typed<LnSig>();
+  return op;
+}
+inline auto ln_bwd_op() {
+  static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::layer_norm_bwd", "").typed<LnBwdSig>();
+  return op;
+}
+
+// ---- autograd ------------------------------------------------------------------------------------------------
+struct AttnFunction : public torch::autograd::Function<AttnFunction> {
+  static variable_list forward(AutogradContext* ctx, const Tensor& packed, const optional<Tensor>& v, const Tensor& bias_table,
+                               const optional<Tensor>& packed_pad, const optional<Tensor>& v_pad, int64_t window, int64_t shift,
+                               int64_t num_heads, double scale, bool need_lse, int64_t impl, const optional<Tensor>& attn_mask,
+                               double dropout_p, int64_t seed) {
+    at::AutoDispatchBelowADInplaceOrView guard;
+    auto out = fwd_op().call(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask,
+                             dropout_p, seed);
+    const Tensor& o = std::get<0>(out);
+    const Tensor& lse = std::get<1>(out);
+    ctx->save_for_backward({packed, v.has_value() ? *v : Tensor(), o, lse, bias_table, attn_mask.has_value() ? *attn_mask : Tensor()});
+    ctx->saved_data["window"] = window;
+    ctx->saved_data["shift"] = shift;
+    ctx->saved_data["heads"] = num_heads;
+    ctx->saved_data["scale"] = scale;
+    ctx->saved_data["dropout_p"] = dropout_p;
+    ctx->saved_data["seed"] = seed;
+    ctx->saved_data["ok"] = need_lse && packed.size(1) % window == 0 && packed.size(2) % window == 0;
+    ctx->mark_non_differentiable({lse});
+    return {o, lse};
+  }
+
+  static variable_list backward(AutogradContext* ctx, variable_list grads) {
+    TORCH_CHECK(ctx->saved_data["ok"].toBool(),
+                "swin_attn: backward needs the forward to have run with need_lse=True on a tensor whose height and width are "
+                "multiples of the window (the layers pad explicitly whenever gradients are enabled)");
+    const auto saved = ctx->get_saved_variables();
+    const Tensor &packed = saved[0], &v = saved[1], &o = saved[2], &lse = saved[3], &table = saved[4], &mask = saved[5];
+    auto out = bwd_op().call(grads[0], packed, v.defined() ? optional<Tensor>(v) : c10::nullopt, o, lse, table,
+                             ctx->saved_data["window"].toInt(), ctx->saved_data["shift"].toInt(), ctx->saved_data["heads"].toInt(),
+                             ctx->saved_data["scale"].toDouble(), mask.defined() ? optional<Tensor>(mask) : c10::nullopt,
+                             SWIN_ATTN_IMPL_AUTO, ctx->saved_data["dropout_p"].toDouble(), ctx->saved_data["seed"].toInt());
+    Tensor d_v;
+    if (v.defined()) {
+      d_v = std::get<1>(out);
+      if (d_v.scalar_type() != v.scalar_type()) d_v = d_v.to(v.scalar_type());
+    }
+    return {std::get<0>(out), d_v, std::get<2>(out), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(),
+            Tensor(), Tensor(), Tensor()};
+  }
+};
+
+std::tuple<Tensor, Tensor> fwd_autograd(const Tensor& packed, const optional<Tensor>& v, const Tensor& bias_table,
+                                        const optional<Tensor>& packed_pad, const optional<Tensor>& v_pad, int64_t window,
+                                        int64_t shift, int64_t num_heads, double scale, bool need_lse, int64_t impl,
+                                        const optional<Tensor>& attn_mask, double dropout_p, int64_t seed) {
+  auto out = AttnFunction::apply(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads, scale, need_lse, impl, attn_mask,
+                                 dropout_p, seed);
+  return {out[0], out[1]};
+}
+
+struct LayerNormFunction : public torch::autograd::Function<LayerNormFunction> {
+  static Tensor forward(AutogradContext* ctx, const Tensor& x, const Tensor& weight, const Tensor& bias, double eps, bool out_bf16) {
+    at::AutoDispatchBelowADInplaceOrView guard;
+    ctx->save_for_backward({x, weight});
+    ctx->saved_data["eps"] = eps;
+    ctx->saved_data["out_bf16"] = out_bf16;
+    return ln_op().call(x, weight, bias, eps, out_bf16);
+  }
+
+  static variable_list backward(AutogradContext* ctx, variable_list grads) {
+    const auto saved = ctx->get_saved_variables();
+    const Tensor &x = saved[0], &weight = saved[1];
+    TORCH_CHECK(x.size(-1) <= 1536, "swin_attn::layer_norm: the backward covers <= 1536 channels");
+    const Tensor dy = grads[0].to(ctx->saved_data["out_bf16"].toBool() ? at::kBFloat16 : at::kFloat);
+    auto out = ln_bwd_op().call(dy, x, weight, ctx->saved_data["eps"].toDouble());
+    return {std::get<0>(out), std::get<1>(out).to(weight.scalar_type()), std::get<2>(out).to(weight.scalar_type()), Tensor(), Tensor()};
+  }
+};
+
+Tensor layer_norm_autograd(const Tensor& x, const Tensor& weight, const Tensor& bias, double eps, bool out_bf16) {
+  return LayerNormFunction::apply(x, weight, bias, eps, out_bf16);
+}
+
+}  // namespace
+
+TORCH_LIBRARY(swin_attn, m) {
+  m.def("fwd(Tensor packed, Tensor? v, Tensor bias_table, Tensor? packed_pad, Tensor? v_pad, int window, int shift, "
+        "int num_heads, float scale, bool need_lse, int impl, Tensor? attn_mask=None, float dropout_p=0.0, int seed=0) "
+        "-> (Tensor, Tensor)");
+  m.def("bwd(Tensor d_o, Tensor packed, Tensor? v, Tensor o, Tensor lse, Tensor bias_table, int window, int shift, "
+        "int num_heads, float scale, Tensor? attn_mask=None, int impl=0, float dropout_p=0.0, int seed=0) "
+        "-> (Tensor, Tensor, Tensor)");
+  m.def("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps, bool out_bf16) -> Tensor");
+  m.def("layer_norm_bwd(Tensor dy, Tensor x, Tensor weight, float eps) -> (Tensor, Tensor, Tensor)");
+}
+
+TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
+  m.impl("fwd", fwd_cuda);
+  m.impl("bwd", bwd_cuda);
+  m.impl("layer_norm", layer_norm_cuda);
+  m.impl("layer_norm_bwd", layer_norm_bwd_cuda);
+}
+
+TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
+  m.impl("fwd", fwd_meta);
+  m.impl("bwd", bwd_meta);
+  m.impl("layer_norm", layer_norm_meta);
+  m.impl("layer_norm_bwd", layer_norm_bwd_meta);
+}
+
+TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
+  m.impl("fwd", fwd_autograd);
+  m.impl("layer_norm", layer_norm_autograd);
+}
+
+// ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------
+extern "C" {
+
+void swin_torch_set_timing(int on) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  g_timing_on = on != 0;
+}
+
+// Synchronises on the recorded events and moves up to `cap` records out: ms[i], meta[8 i .. 8 i + 7] =
+// {bytes, flops, kind, window, shift, heads, height, width}.  Returns the number written.
+int swin_torch_take_timing(double* ms, int64_t* meta, int cap) {
+  std::vector<TimingRecord> recs;
+  {
+    std::lock_guard<std::mutex> lock(g_timing_mutex);
+    recs.swap(g_records);
+  }
+  int n = 0;
+  for (auto& r : recs) {
+    cudaEventSynchronize(r.stop);
+    float t = 0.f;
+    cudaEventElapsedTime(&t, r.start, r.stop);
+    if (n < cap) {
+      ms[n] = t;
+      meta[8 * n] = r.bytes;
+      meta[8 * n + 1] = r.flops;
+      for (int i = 0; i < 6; ++i) meta[8 * n + 2 + i] = r.tag[i];
+      ++n;
+    }
+    cudaEventDestroy(r.start);
+    cudaEventDestroy(r.stop);
+  }
+  return n;
+}
+
+int swin_torch_pending_timing(void) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  return (int)g_records.size();
+}
+
+}  // extern "C"

@@ -81,3 +81,24 @@ def test_layernorm_validation_without_gpu():
     assert b"channels must be one of" in lib.swin_attn_last_error()
     assert lib.swin_layernorm_forward(None, _lib.F32, ptr, ptr, 1e-5, 1, 128, ptr, _lib.BF16, None) != 0
     assert lib.swin_layernorm_forward(ptr, _lib.BF16, ptr, ptr, 1e-5, 0, 128, ptr, _lib.F32, None) == 0   # empty input: no launch
+
+
+def test_torch_binding_registers_ops_without_a_gpu():
+    """libswin_attn_torch.so (csrc/torch_binding.cpp) loads on a CPU-only host, registers the four dispatcher ops with
+    the documented schemas, has Meta kernels for shape inference and no CPU kernels (CPU tensors raise)."""
+    import torch
+    from mde_b200 import ops
+    assert os.path.exists(ops.TORCH_LIB_PATH)
+    for name in ("fwd", "bwd", "layer_norm", "layer_norm_bwd"):
+        assert hasattr(torch.ops.swin_attn, name)
+    s = str(torch.ops.swin_attn.fwd.default._schema)
+    assert "Tensor? attn_mask=None, float dropout_p=0., int seed=0" in s and s.endswith("-> (Tensor, Tensor)")
+    qkv = torch.empty(2, 14, 21, 192, device="meta", dtype=torch.bfloat16)
+    o, lse = torch.ops.swin_attn.fwd(qkv, None, torch.empty(169, 2, device="meta"), None, None, 7, 3, 2, 0.17, True, 0)
+    assert o.shape == (2, 14, 21, 64) and lse.shape == (2, 14, 21, 2) and lse.dtype == torch.float32
+    y = torch.ops.swin_attn.layer_norm(torch.empty(5, 192, device="meta"), torch.empty(192, device="meta"),
+                                       torch.empty(192, device="meta"), 1e-5, True)
+    assert y.shape == (5, 192) and y.dtype == torch.bfloat16
+    with pytest.raises(NotImplementedError):
+        torch.ops.swin_attn.fwd(torch.zeros(1, 7, 7, 192), None, torch.zeros(169, 2), None, None, 7, 0, 2, 0.17, False, 0)
+    assert ops._torch_lib.swin_torch_pending_timing() == 0

@@ -26,11 +26,18 @@ else:
 for _ in range(3):
     step()
 torch.cuda.synchronize()
+a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+a.record()
+for _ in range(3):
+    step()
+b.record()
+torch.cuda.synchronize()
+print(f"step (events, no profiler): {a.elapsed_time(b) / 3:.3f} ms")
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True, record_shapes=True) as prof:
     step()
     torch.cuda.synchronize()
-tot = sum(e.self_device_time_total for e in prof.key_averages())
-print(f"step CUDA total {tot / 1e3:.3f} ms")
+tot = sum(e.self_device_time_total for e in prof.key_averages() if not e.key.startswith(("aten::", "swin_attn::", "Optimizer", "Generated", "autograd::", "torch")) and "Backward" not in e.key)
+print(f"kernel time total {tot / 1e3:.3f} ms")
 for e in sorted(prof.key_averages(), key=lambda e: -e.self_device_time_total)[:45]:
     print(f"  {e.key[:80]:80s} {e.self_device_time_total / 1e3:8.3f} ms x{e.count}")
 want = ("aten::copy_", "aten::add", "aten::add_", "aten::gelu", "aten::native_layer_norm", "aten::cat", "aten::mul", "aten::_to_copy", "aten::pixel_shuffle", "aten::cudnn_convolution", "aten::addmm", "aten::mm",
