@@ -119,6 +119,14 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape,
 int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, const float* beta, float eps, int64_t rows,
                            int32_t channels, void* out, int32_t out_dtype, void* stream);
 
+/* Residual add fused with the LayerNorm that follows it in the block forwards (`x = shortcut + attn` then `norm2(x)`,
+ * newcrf_layers.py:251-253, swin_transformer.py:240-243; `x + mlp(...)` then the next block's `norm1`):
+ * sum_out = x + delta in x_dtype (torch's type promotion: fp32 + bf16 -> fp32, bf16 + bf16 -> bf16, rounded once),
+ * y_out = LayerNorm(sum_out) as bf16.  delta, y_out: (rows, channels) bf16; x, sum_out: (rows, channels) of x_dtype
+ * (may alias).  channels in {128, 192, 256, 384, 512, 768, 1024, 1536}.  Inference only (no backward entry). */
+int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta, float eps,
+                               int64_t rows, int32_t channels, void* sum_out, void* y_out, void* stream);
+
 /* Backward of swin_layernorm_forward for training under autocast (autograd of nn.LayerNorm in the reference).
  * dy: (rows, channels) of dy_dtype (bf16 for the bf16-output form, fp32 for the fp32-output form); x: the forward's
  * input (mean / rstd are recomputed).

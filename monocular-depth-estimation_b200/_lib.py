@@ -23,6 +23,7 @@ EXPORTS = (
     "swin_attn_forward_host",
     "swin_layernorm_forward",
     "swin_layernorm_backward",
+    "swin_add_layernorm_forward",
     "swin_attn_launch_count",
     "swin_attn_uses_tcgen05",
     "swin_attn_last_error",
@@ -65,6 +66,8 @@ def load() -> ctypes.CDLL:
     lib.swin_layernorm_forward.restype = c_int
     lib.swin_layernorm_backward.argtypes = [vp, c_int32, vp, c_int32, vp, c_float, c_int64, c_int32, vp, vp, vp, vp]
     lib.swin_layernorm_backward.restype = c_int
+    lib.swin_add_layernorm_forward.argtypes = [vp, c_int32, vp, vp, vp, c_float, c_int64, c_int32, vp, vp, vp]
+    lib.swin_add_layernorm_forward.restype = c_int
     lib.swin_attn_launch_count.argtypes = []
     lib.swin_attn_launch_count.restype = c_uint64
     lib.swin_attn_uses_tcgen05.argtypes = [POINTER(Shape), c_int]

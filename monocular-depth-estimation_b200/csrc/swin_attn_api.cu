@@ -183,6 +183,22 @@ int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, c
   return 0;
 }
 
+int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta, float eps,
+                               int64_t rows, int32_t channels, void* sum_out, void* y_out, void* stream) {
+  if (!x || !delta || !gamma || !beta || !sum_out || !y_out) return fail("add+layernorm: all pointers must be non-null");
+  if (rows < 0) return fail("add+layernorm: bad row count");
+  if (x_dtype != SWIN_ATTN_F32 && x_dtype != SWIN_ATTN_BF16) return fail("add+layernorm: x_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
+  if (!layernorm_supported(channels) || channels > 1536)
+    return fail("add+layernorm: channels must be one of 128, 192, 256, 384, 512, 768, 1024, 1536 (got " + std::to_string(channels) + ")");
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(sum_out) | reinterpret_cast<uintptr_t>(gamma) |
+       reinterpret_cast<uintptr_t>(beta)) & 7 || (reinterpret_cast<uintptr_t>(delta) | reinterpret_cast<uintptr_t>(y_out)) & 3)
+    return fail("add+layernorm: pointers must be 8-byte aligned (bf16 delta / y: 4)");
+  if (rows == 0) return 0;
+  cudaError_t e = launch_add_layernorm(x, x_dtype, delta, gamma, beta, eps, rows, channels, sum_out, y_out, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail_cuda("add+layernorm launch", e);
+  return 0;
+}
+
 int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int32_t dy_dtype, const float* gamma, float eps, int64_t rows,
                             int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream) {
   if (!x || !dy || !gamma || !dx || !dgamma || !dbeta) return fail("layernorm backward: all pointers must be non-null");

@@ -64,6 +64,58 @@ __global__ void __launch_bounds__(256) layernorm_rows_kernel(const TIn* __restri
   }
 }
 
+// Residual add fused with the LayerNorm that follows it (block plumbing, swin_transformer.py:240-244 /
+// newcrf_layers.py:251-255: `x = shortcut + attn; ... norm2(x)`, and `x + mlp` followed by the next block's norm1):
+// s = x + delta rounded to the dtype of the residual stream (what torch's type promotion gives: fp32 + bf16 -> fp32,
+// bf16 + bf16 -> bf16), y = LayerNorm(s) as bf16.  One read of x and delta, one write of s and y, instead of
+// add (2 reads, 1 write) + norm (1 read, 1 write).
+template <int NC, typename TX>
+__global__ void __launch_bounds__(256) add_layernorm_rows_kernel(const TX* __restrict__ x, const __nv_bfloat16* __restrict__ delta,
+                                                                 const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                 float eps, int64_t rows, TX* __restrict__ sum_out,
+                                                                 __nv_bfloat16* __restrict__ y_out) {
+  constexpr int C = 64 * NC;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  float2 v[NC];
+  float sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const float2 a = load2(x + row * C, lane + 32 * k), d = load2(delta + row * C, lane + 32 * k);
+    if constexpr (sizeof(TX) == 2) {
+      const __nv_bfloat162 r = __floats2bfloat162_rn(a.x + d.x, a.y + d.y);
+      reinterpret_cast<__nv_bfloat162*>(sum_out + row * C)[lane + 32 * k] = r;
+      v[k] = __bfloat1622float2(r);
+    } else {
+      v[k] = make_float2(a.x + d.x, a.y + d.y);
+      reinterpret_cast<float2*>(sum_out + row * C)[lane + 32 * k] = v[k];
+    }
+    sum += v[k].x + v[k].y;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float mean = sum * (1.0f / C);
+  float sq = 0.f;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const float a = v[k].x - mean, b = v[k].y - mean;
+    sq = fmaf(a, a, sq);
+    sq = fmaf(b, b, sq);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq * (1.0f / C) + eps);
+  const float2* g2 = reinterpret_cast<const float2*>(gamma);
+  const float2* b2 = reinterpret_cast<const float2*>(beta);
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const float2 g = g2[lane + 32 * k], b = b2[lane + 32 * k];
+    const float y0 = fmaf((v[k].x - mean) * rstd, g.x, b.x), y1 = fmaf((v[k].y - mean) * rstd, g.y, b.y);
+    reinterpret_cast<__nv_bfloat162*>(y_out + row * C)[lane + 32 * k] = __floats2bfloat162_rn(y0, y1);
+  }
+}
+
 // Backward of the kernel above, for training under autocast: dy is the bf16 gradient the Linear's dgrad produced,
 // x the saved residual stream; mean / rstd are recomputed from the row (it is in registers anyway), so nothing but x
 // is saved.  dx = rstd (g - mean(g) - xhat mean(g xhat)), g = dy gamma;  dgamma = sum_rows dy xhat;  dbeta = sum_rows dy.
@@ -216,6 +268,32 @@ cudaError_t launch_layernorm(const void* x, int x_dtype, const float* g, const f
 #define SWIN_LN_CASE(NC) case NC: return launch_ln<NC>(x, x_dtype, g, b, eps, rows, out, out_dtype, st)
     SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
     SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24); SWIN_LN_CASE(48);
+#undef SWIN_LN_CASE
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+template <int NC>
+static cudaError_t launch_add_ln(const void* x, int x_dtype, const void* delta, const float* g, const float* b, float eps, int64_t rows,
+                                 void* sum_out, void* y_out, cudaStream_t st) {
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  using bf = __nv_bfloat16;
+  if (x_dtype == SWIN_ATTN_F32)
+    add_layernorm_rows_kernel<NC, float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), static_cast<const bf*>(delta), g, b, eps, rows,
+                                                               static_cast<float*>(sum_out), static_cast<bf*>(y_out));
+  else
+    add_layernorm_rows_kernel<NC, bf><<<grid, 256, 0, st>>>(static_cast<const bf*>(x), static_cast<const bf*>(delta), g, b, eps, rows,
+                                                            static_cast<bf*>(sum_out), static_cast<bf*>(y_out));
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, const float* g, const float* b, float eps, int64_t rows,
+                                 int channels, void* sum_out, void* y_out, cudaStream_t st) {
+  switch (channels / 64) {
+#define SWIN_LN_CASE(NC) case NC: return launch_add_ln<NC>(x, x_dtype, delta, g, b, eps, rows, sum_out, y_out, st)
+    SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
+    SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24);
 #undef SWIN_LN_CASE
     default: return cudaErrorInvalidValue;
   }

@@ -10,6 +10,7 @@
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
 #include <cuda_runtime.h>
+#include <torch/csrc/autograd/autograd_not_implemented_fallback.h>
 #include <torch/csrc/autograd/custom_function.h>
 #include <torch/library.h>
 
@@ -255,6 +256,27 @@ Tensor layer_norm_meta(const Tensor& x, const Tensor&, const Tensor&, double, bo
   return at::empty_symint(x.sym_sizes(), x.options().dtype(out_bf16 ? at::kBFloat16 : at::kFloat));
 }
 
+std::tuple<Tensor, Tensor> add_layer_norm_cuda(const Tensor& x_in, const Tensor& delta_in, const Tensor& weight, const Tensor& bias,
+                                               double eps) {
+  const int32_t xd = dtype_code(x_in.scalar_type());
+  TORCH_CHECK(delta_in.scalar_type() == at::kBFloat16, "swin_attn::add_layer_norm: delta must be bfloat16");
+  TORCH_CHECK(delta_in.sizes() == x_in.sizes(), "swin_attn::add_layer_norm: x and delta must have the same shape");
+  const Tensor x = x_in.contiguous(), delta = delta_in.contiguous();
+  const int64_t c = x.size(-1);
+  Tensor sum = at::empty_like(x);
+  Tensor y = at::empty(x.sizes(), x.options().dtype(at::kBFloat16));
+  const Tensor w = weight.detach().to(at::kFloat).contiguous(), b = bias.detach().to(at::kFloat).contiguous();
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(swin_add_layernorm_forward(x.data_ptr(), xd, delta.data_ptr(), w.data_ptr<float>(), b.data_ptr<float>(), (float)eps,
+                                      c ? x.numel() / c : 0, (int32_t)c, sum.data_ptr(), y.data_ptr(),
+                                      at::cuda::getCurrentCUDAStream()));
+  return {sum, y};
+}
+
+std::tuple<Tensor, Tensor> add_layer_norm_meta(const Tensor& x, const Tensor&, const Tensor&, const Tensor&, double) {
+  return {at::empty_symint(x.sym_sizes(), x.options()), at::empty_symint(x.sym_sizes(), x.options().dtype(at::kBFloat16))};
+}
+
 std::tuple<Tensor, Tensor, Tensor> layer_norm_bwd_cuda(const Tensor& dy_in, const Tensor& x_in, const Tensor& weight, double eps) {
   const int32_t xd = dtype_code(x_in.scalar_type());
   const Tensor x = x_in.contiguous();
@@ -390,6 +412,7 @@ TORCH_LIBRARY(swin_attn, m) {
         "-> (Tensor, Tensor, Tensor)");
   m.def("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps, bool out_bf16) -> Tensor");
   m.def("layer_norm_bwd(Tensor dy, Tensor x, Tensor weight, float eps) -> (Tensor, Tensor, Tensor)");
+  m.def("add_layer_norm(Tensor x, Tensor delta, Tensor weight, Tensor bias, float eps) -> (Tensor, Tensor)");
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
@@ -397,6 +420,7 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("bwd", bwd_cuda);
   m.impl("layer_norm", layer_norm_cuda);
   m.impl("layer_norm_bwd", layer_norm_bwd_cuda);
+  m.impl("add_layer_norm", add_layer_norm_cuda);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
@@ -404,11 +428,13 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("bwd", bwd_meta);
   m.impl("layer_norm", layer_norm_meta);
   m.impl("layer_norm_bwd", layer_norm_bwd_meta);
+  m.impl("add_layer_norm", add_layer_norm_meta);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
   m.impl("fwd", fwd_autograd);
   m.impl("layer_norm", layer_norm_autograd);
+  m.impl("add_layer_norm", torch::autograd::autogradNotImplementedFallback());   // inference only
 }
 
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------

@@ -192,12 +192,19 @@ class CRFBlock(nn.Module):
         self.W = None
 
     def forward(self, x, v, mask_matrix=None):
+        x, pending = self.forward_parts(x, v, ops.norm_for_linear(self.norm1, x))
+        return x + pending
+
+    def forward_parts(self, x, v, y):
+        """The block without its last residual add: ``y`` is ``norm1(x)``; returns the stream after the attention
+        residual and the (drop-path'ed) MLP branch still to be added, so that a stage can fuse that add with the
+        next block's ``norm1`` (BasicCRFLayer.forward)."""
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(ops.norm_for_linear(self.norm1, x).view(b, h, w, c), v, self.shift_size)
-        x = x + self.drop_path(a.reshape(b, h * w, self.v_dim))
-        return x + self.drop_path(self.mlp(ops.norm_for_linear(self.norm2, x)))
+        a = self.attn.forward_image(y.view(b, h, w, c), v, self.shift_size)
+        x, y2 = ops.add_norm(self.norm2, x, self.drop_path(a.reshape(b, h * w, self.v_dim)))
+        return x, self.drop_path(self.mlp(y2))
 
 
 class BasicCRFLayer(nn.Module):
@@ -221,9 +228,16 @@ class BasicCRFLayer(nn.Module):
         if v.is_cuda and v.dtype == torch.float32 and torch.is_autocast_enabled() and \
                 torch.get_autocast_dtype("cuda") == torch.bfloat16:
             v = v.to(torch.bfloat16)   # the value every block's kernel reads; cast once per level instead of per block
+        pending = None
         for blk in self.blocks:
             blk.H, blk.W = H, W
-            x = blk(x, v, None)
+            if pending is None:
+                y = ops.norm_for_linear(blk.norm1, x)
+            else:
+                x, y = ops.add_norm(blk.norm1, x, pending)   # previous block's last residual add + this norm1
+            x, pending = blk.forward_parts(x, v, y)
+        if pending is not None:
+            x = x + pending
         if self.downsample is not None:
             return x, H, W, self.downsample(x, H, W), (H + 1) // 2, (W + 1) // 2
         return x, H, W, x, H, W
@@ -282,12 +296,17 @@ class SwinTransformerBlock(nn.Module):
         self.W = None
 
     def forward(self, x, mask_matrix=None):
+        x, pending = self.forward_parts(x, ops.norm_for_linear(self.norm1, x))
+        return x + pending
+
+    def forward_parts(self, x, y):
+        """The block without its last residual add (see CRFBlock.forward_parts)."""
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(ops.norm_for_linear(self.norm1, x).view(b, h, w, c), self.shift_size)
-        x = x + self.drop_path(a.reshape(b, h * w, c))
-        return x + self.drop_path(self.mlp(ops.norm_for_linear(self.norm2, x)))
+        a = self.attn.forward_image(y.view(b, h, w, c), self.shift_size)
+        x, y2 = ops.add_norm(self.norm2, x, self.drop_path(a.reshape(b, h * w, c)))
+        return x, self.drop_path(self.mlp(y2))
 
 
 class PatchMerging(nn.Module):
@@ -327,12 +346,21 @@ class BasicLayer(nn.Module):
         self.downsample = downsample(dim=dim, norm_layer=norm_layer) if downsample is not None else None
 
     def forward(self, x, H, W):
+        pending = None
         for blk in self.blocks:
             blk.H, blk.W = H, W
             if self.use_checkpoint and torch.is_grad_enabled():
+                if pending is not None:
+                    x, pending = x + pending, None
                 x = torch.utils.checkpoint.checkpoint(blk, x, None, use_reentrant=False)
+                continue
+            if pending is None:
+                y = ops.norm_for_linear(blk.norm1, x)
             else:
-                x = blk(x, None)
+                x, y = ops.add_norm(blk.norm1, x, pending)   # previous block's last residual add + this norm1
+            x, pending = blk.forward_parts(x, y)
+        if pending is not None:
+            x = x + pending
         if self.downsample is not None:
             return x, H, W, self.downsample(x, H, W), (H + 1) // 2, (W + 1) // 2
         return x, H, W, x, H, W

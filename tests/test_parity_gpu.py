@@ -557,3 +557,32 @@ def test_prepare_inference_is_bit_identical_and_outputs_keep_reference_shapes(go
     for i, f in enumerate(feats):
         assert f.shape == (b, m.backbone.num_features[i], -(-h // (4 << i)), -(-w // (4 << i))) and f.dtype == torch.float32
         assert torch.equal(f.contiguous().permute(0, 2, 3, 1), f.permute(0, 2, 3, 1))
+
+
+@pytest.mark.parametrize("xdtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("c", [128, 192, 256, 384, 512, 768, 1024, 1536])
+def test_fused_add_layernorm_matches_the_two_steps(c, xdtype):
+    """swin_add_layernorm_forward: the sum is BIT-identical to torch's promoted add, the norm equals the fused LayerNorm
+    of that sum (same kernel arithmetic) and F.layer_norm in fp32 within bf16 rounding."""
+    gen = torch.Generator(device=DEV).manual_seed(300 + c)
+    x = (2.0 * torch.randn(3, 683, c, device=DEV, generator=gen) - 0.4).to(xdtype)
+    d = torch.randn(3, 683, c, device=DEV, generator=gen).bfloat16()
+    ln = torch.nn.LayerNorm(c).to(DEV)
+    with torch.no_grad():
+        ln.weight.copy_(1.0 + 0.3 * torch.randn(c, device=DEV, generator=gen))
+        ln.bias.copy_(0.2 * torch.randn(c, device=DEV, generator=gen))
+        s, y = torch.ops.swin_attn.add_layer_norm(x, d, ln.weight, ln.bias, ln.eps)
+        want_s = x + d
+        assert s.dtype == xdtype and torch.equal(s, want_s)
+        assert y.dtype == torch.bfloat16 and torch.equal(y, torch.ops.swin_attn.layer_norm(want_s, ln.weight, ln.bias, ln.eps, True))
+        assert rel_err(y.float(), torch.nn.functional.layer_norm(want_s.float(), (c,), ln.weight, ln.bias, ln.eps)) < 4e-3
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            s2, y2 = ops.add_norm(ln, x, d)            # the fused path
+        assert torch.equal(s2, s) and torch.equal(y2, y)
+        if xdtype == torch.float32:
+            s3, y3 = ops.add_norm(ln, x, d)            # fp32 mode: two separate steps, module LayerNorm
+            assert torch.equal(s3, want_s) and y3.dtype == torch.float32
+    xg = x.clone().requires_grad_()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        s4, y4 = ops.add_norm(ln, xg, d)               # gradients needed: unfused, differentiable
+    assert s4.requires_grad and y4.requires_grad and torch.equal(y4.detach(), y)
