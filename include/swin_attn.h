@@ -127,6 +127,12 @@ int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, c
 int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta, float eps,
                                int64_t rows, int32_t channels, void* sum_out, void* y_out, void* stream);
 
+/* Exact (erf) GELU of the block MLPs, `nn.GELU()` between fc1 and fc2 (newcrf_layers.py:9-27, swin_transformer.py Mlp),
+ * on the bf16 output of the autocast fc1: y = x Phi(x), elementwise, x and y: n bf16 elements, n a multiple of 8,
+ * 16-byte aligned (may alias).  Backward: dx = dy (Phi(x) + x phi(x)). */
+int swin_gelu_forward(const void* x, void* y, int64_t n, void* stream);
+int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void* stream);
+
 /* Backward of swin_layernorm_forward for training under autocast (autograd of nn.LayerNorm in the reference).
  * dy: (rows, channels) of dy_dtype (bf16 for the bf16-output form, fp32 for the fp32-output form); x: the forward's
  * input (mean / rstd are recomputed).

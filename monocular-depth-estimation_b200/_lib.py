@@ -24,6 +24,8 @@ EXPORTS = (
     "swin_layernorm_forward",
     "swin_layernorm_backward",
     "swin_add_layernorm_forward",
+    "swin_gelu_forward",
+    "swin_gelu_backward",
     "swin_attn_launch_count",
     "swin_attn_uses_tcgen05",
     "swin_attn_last_error",
@@ -68,6 +70,10 @@ def load() -> ctypes.CDLL:
     lib.swin_layernorm_backward.restype = c_int
     lib.swin_add_layernorm_forward.argtypes = [vp, c_int32, vp, vp, vp, c_float, c_int64, c_int32, vp, vp, vp]
     lib.swin_add_layernorm_forward.restype = c_int
+    lib.swin_gelu_forward.argtypes = [vp, vp, c_int64, vp]
+    lib.swin_gelu_forward.restype = c_int
+    lib.swin_gelu_backward.argtypes = [vp, vp, vp, c_int64, vp]
+    lib.swin_gelu_backward.restype = c_int
     lib.swin_attn_launch_count.argtypes = []
     lib.swin_attn_launch_count.restype = c_uint64
     lib.swin_attn_uses_tcgen05.argtypes = [POINTER(Shape), c_int]

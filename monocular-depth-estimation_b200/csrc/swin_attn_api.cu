@@ -199,6 +199,24 @@ int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta
   return 0;
 }
 
+static int gelu_entry(const char* what, const void* x, const void* dy, void* out, int64_t n, void* stream) {
+  if (!x || !out) return fail(std::string(what) + ": all pointers must be non-null");
+  if (n < 0 || n % 8) return fail(std::string(what) + ": the element count must be a non-negative multiple of 8");
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(dy)) & 15)
+    return fail(std::string(what) + ": pointers must be 16-byte aligned");
+  if (n == 0) return 0;
+  cudaError_t e = launch_gelu(x, dy, out, n, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail_cuda(what, e);
+  return 0;
+}
+
+int swin_gelu_forward(const void* x, void* y, int64_t n, void* stream) { return gelu_entry("gelu forward", x, nullptr, y, n, stream); }
+
+int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void* stream) {
+  if (!dy) return fail("gelu backward: all pointers must be non-null");
+  return gelu_entry("gelu backward", x, dy, dx, n, stream);
+}
+
 int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int32_t dy_dtype, const float* gamma, float eps, int64_t rows,
                             int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream) {
   if (!x || !dy || !gamma || !dx || !dgamma || !dbeta) return fail("layernorm backward: all pointers must be non-null");

@@ -299,6 +299,85 @@ cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, 
   }
 }
 
+// ---- exact (erf) GELU of the MLP, bf16 -> bf16 ------------------------------------------------------------------
+// nn.GELU() between fc1 and fc2 (newcrf_layers.py:9-27, swin_transformer.py Mlp).  ATen's kernel evaluates
+// x/2 (1 + erff(x/sqrt 2)) and is bound by erff's instruction count (~0.6 of copy speed); here erfc is the
+// exp(-z^2 + P(t)) t form with t = 1/(1 + z/2) (fractional error < 1.2e-7 everywhere, Numerical Recipes erfcc), i.e.
+// two MUFU ops and ten FMAs, and the negative tail x/2 erfc(|x|/sqrt 2) has no cancellation -- closer to the fp64 value
+// than 1 + erff is.  16-byte vectors, two per thread.
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ float erfc_abs(float z) {   // erfc(z), z >= 0
+  const float t = __fdividef(1.0f, fmaf(0.5f, z, 1.0f));
+  float p = 0.17087277f;
+  p = fmaf(p, t, -0.82215223f);
+  p = fmaf(p, t, 1.48851587f);
+  p = fmaf(p, t, -1.13520398f);
+  p = fmaf(p, t, 0.27886807f);
+  p = fmaf(p, t, -0.18628806f);
+  p = fmaf(p, t, 0.09678418f);
+  p = fmaf(p, t, 0.37409196f);
+  p = fmaf(p, t, 1.00002368f);
+  p = fmaf(p, t, -1.26551223f);
+  return t * ex2_approx((p - z * z) * 1.4426950408889634f);
+}
+
+template <bool kBackward>
+__device__ __forceinline__ float gelu_value(float x, float dy) {
+  const float e = erfc_abs(fabsf(x) * 0.70710678118654752440f);
+  const float cdf = x >= 0.f ? fmaf(-0.5f, e, 1.0f) : 0.5f * e;   // Phi(x)
+  if (!kBackward) return x * cdf;
+  const float pdf = 0.3989422804014327f * ex2_approx(x * x * -0.72134752044448170f);   // exp(-x^2 / 2) / sqrt(2 pi)
+  return dy * fmaf(x, pdf, cdf);
+}
+
+template <bool kBackward>
+__global__ void __launch_bounds__(256) gelu_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, uint4* __restrict__ out,
+                                                   int64_t nvec) {
+  const int64_t half = (nvec + 1) / 2;
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i >= half) return;
+  const int64_t j = i + half;
+  const bool two = j < nvec;
+  uint4 a[2], g[2];
+  a[0] = x[i];
+  a[1] = two ? x[j] : make_uint4(0, 0, 0, 0);
+  if (kBackward) {
+    g[0] = dy[i];
+    g[1] = two ? dy[j] : make_uint4(0, 0, 0, 0);
+  }
+#pragma unroll
+  for (int v = 0; v < 2; ++v) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(&a[v]);
+    const uint32_t* gw = reinterpret_cast<const uint32_t*>(&g[v]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[k]));
+      float2 d = make_float2(0.f, 0.f);
+      if (kBackward) d = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gw[k]));
+      const __nv_bfloat162 r = __floats2bfloat162_rn(gelu_value<kBackward>(f.x, d.x), gelu_value<kBackward>(f.y, d.y));
+      w[k] = *reinterpret_cast<const uint32_t*>(&r);
+    }
+  }
+  out[i] = a[0];
+  if (two) out[j] = a[1];
+}
+
+cudaError_t launch_gelu(const void* x, const void* dy, void* out, int64_t n, cudaStream_t st) {
+  const int64_t nvec = n / 8, half = (nvec + 1) / 2;
+  const unsigned grid = (unsigned)((half + 255) / 256);
+  if (dy == nullptr)
+    gelu_kernel<false><<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), nullptr, static_cast<uint4*>(out), nvec);
+  else
+    gelu_kernel<true><<<grid, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<const uint4*>(dy), static_cast<uint4*>(out), nvec);
+  count_launch();
+  return cudaGetLastError();
+}
+
 bool layernorm_supported(int channels) {
   if (channels % 64) return false;
   switch (channels / 64) {

@@ -277,6 +277,28 @@ std::tuple<Tensor, Tensor> add_layer_norm_meta(const Tensor& x, const Tensor&, c
   return {at::empty_symint(x.sym_sizes(), x.options()), at::empty_symint(x.sym_sizes(), x.options().dtype(at::kBFloat16))};
 }
 
+Tensor gelu_cuda(const Tensor& x_in) {
+  TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && x_in.numel() % 8 == 0, "swin_attn::gelu: bfloat16 with a multiple of 8 elements");
+  const Tensor x = x_in.contiguous();
+  Tensor y = at::empty_like(x);
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(swin_gelu_forward(x.data_ptr(), y.data_ptr(), x.numel(), at::cuda::getCurrentCUDAStream()));
+  return y;
+}
+
+Tensor gelu_bwd_cuda(const Tensor& dy_in, const Tensor& x_in) {
+  TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && x_in.numel() % 8 == 0, "swin_attn::gelu_bwd: bfloat16 with a multiple of 8 elements");
+  TORCH_CHECK(dy_in.sizes() == x_in.sizes(), "swin_attn::gelu_bwd: dy and x must have the same shape");
+  const Tensor x = x_in.contiguous(), dy = dy_in.to(at::kBFloat16).contiguous();
+  Tensor dx = at::empty_like(x);
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(swin_gelu_backward(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), x.numel(), at::cuda::getCurrentCUDAStream()));
+  return dx;
+}
+
+Tensor gelu_meta(const Tensor& x) { return at::empty_symint(x.sym_sizes(), x.options()); }
+Tensor gelu_bwd_meta(const Tensor&, const Tensor& x) { return at::empty_symint(x.sym_sizes(), x.options()); }
+
 std::tuple<Tensor, Tensor, Tensor> layer_norm_bwd_cuda(const Tensor& dy_in, const Tensor& x_in, const Tensor& weight, double eps) {
   const int32_t xd = dtype_code(x_in.scalar_type());
   const Tensor x = x_in.contiguous();
@@ -397,6 +419,21 @@ struct LayerNormFunction : public torch::autograd::Function<LayerNormFunction> {
   }
 };
 
+struct GeluFunction : public torch::autograd::Function<GeluFunction> {
+  static Tensor forward(AutogradContext* ctx, const Tensor& x) {
+    at::AutoDispatchBelowADInplaceOrView guard;
+    ctx->save_for_backward({x});
+    static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::gelu", "").typed<Tensor(const Tensor&)>();
+    return op.call(x);
+  }
+  static variable_list backward(AutogradContext* ctx, variable_list grads) {
+    static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::gelu_bwd", "").typed<Tensor(const Tensor&, const Tensor&)>();
+    return {op.call(grads[0], ctx->get_saved_variables()[0])};
+  }
+};
+
+Tensor gelu_autograd(const Tensor& x) { return GeluFunction::apply(x); }
+
 Tensor layer_norm_autograd(const Tensor& x, const Tensor& weight, const Tensor& bias, double eps, bool out_bf16) {
   return LayerNormFunction::apply(x, weight, bias, eps, out_bf16);
 }
@@ -413,6 +450,8 @@ TORCH_LIBRARY(swin_attn, m) {
   m.def("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps, bool out_bf16) -> Tensor");
   m.def("layer_norm_bwd(Tensor dy, Tensor x, Tensor weight, float eps) -> (Tensor, Tensor, Tensor)");
   m.def("add_layer_norm(Tensor x, Tensor delta, Tensor weight, Tensor bias, float eps) -> (Tensor, Tensor)");
+  m.def("gelu(Tensor x) -> Tensor");
+  m.def("gelu_bwd(Tensor dy, Tensor x) -> Tensor");
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
@@ -421,6 +460,8 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("layer_norm", layer_norm_cuda);
   m.impl("layer_norm_bwd", layer_norm_bwd_cuda);
   m.impl("add_layer_norm", add_layer_norm_cuda);
+  m.impl("gelu", gelu_cuda);
+  m.impl("gelu_bwd", gelu_bwd_cuda);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
@@ -429,12 +470,15 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("layer_norm", layer_norm_meta);
   m.impl("layer_norm_bwd", layer_norm_bwd_meta);
   m.impl("add_layer_norm", add_layer_norm_meta);
+  m.impl("gelu", gelu_meta);
+  m.impl("gelu_bwd", gelu_bwd_meta);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
   m.impl("fwd", fwd_autograd);
   m.impl("layer_norm", layer_norm_autograd);
   m.impl("add_layer_norm", torch::autograd::autogradNotImplementedFallback());   // inference only
+  m.impl("gelu", gelu_autograd);
 }
 
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------

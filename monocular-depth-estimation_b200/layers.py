@@ -59,7 +59,7 @@ class Mlp(nn.Module):
         self.drop = nn.Dropout(drop)
 
     def forward(self, x):
-        return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
+        return self.drop(self.fc2(self.drop(ops.gelu(self.act, self.fc1(x)))))
 
 
 def _relative_position_index(wh: int, ww: int) -> torch.Tensor:

@@ -114,6 +114,15 @@ def norm_fp32(norm: torch.nn.Module, x: Tensor) -> Tensor:
     return norm(x)
 
 
+def gelu(act: torch.nn.Module, x: Tensor) -> Tensor:
+    """``act(x)`` for the MLP activation: the fused exact-GELU kernel when ``act`` is ``nn.GELU()`` (erf form) and ``x``
+    is the bf16 output of an autocast Linear; otherwise the module itself."""
+    if (type(act) is torch.nn.GELU and act.approximate == "none" and x.is_cuda and x.dtype == torch.bfloat16
+            and x.numel() % 8 == 0):
+        return torch.ops.swin_attn.gelu(x)
+    return act(x)
+
+
 def add_norm(norm: torch.nn.Module, x: Tensor, delta: Tensor) -> Tuple[Tensor, Tensor]:
     """``x + delta`` and ``norm(x + delta)`` as the operand of the following Linear: the residual add of a block
     with the LayerNorm behind it (``norm2`` of the same block, ``norm1`` of the next one).  One fused kernel for

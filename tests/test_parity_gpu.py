@@ -586,3 +586,34 @@ def test_fused_add_layernorm_matches_the_two_steps(c, xdtype):
     with torch.autocast("cuda", dtype=torch.bfloat16):
         s4, y4 = ops.add_norm(ln, xg, d)               # gradients needed: unfused, differentiable
     assert s4.requires_grad and y4.requires_grad and torch.equal(y4.detach(), y)
+
+
+def test_fused_gelu_forward_backward_vs_fp64():
+    """swin_gelu_forward/backward (exact erf GELU, bf16 in/out) against nn.GELU in fp64 on the same bf16 inputs.  One
+    bf16 rounding of the exact value is the bar: <= 1 bf16 ulp everywhere, and no further from the fp64 value than
+    ATen's own bf16 kernel is."""
+    gen = torch.Generator(device=DEV).manual_seed(77)
+    x = (2.5 * torch.randn(257, 1544, device=DEV, generator=gen)).bfloat16()
+    x[0, :8] = torch.tensor([0.0, -0.0, 1e-3, -1e-3, 12.0, -12.0, 40.0, -40.0], device=DEV)
+    dy = torch.randn(257, 1544, device=DEV, generator=gen).bfloat16()
+    xr = x.double().requires_grad_()
+    want = torch.nn.functional.gelu(xr)
+    (want_dx,) = torch.autograd.grad(want, xr, dy.double())
+    xg = x.clone().requires_grad_()
+    got = ops.gelu(torch.nn.GELU(), xg)
+    (got_dx,) = torch.autograd.grad(got, xg, dy)
+    assert got.dtype == torch.bfloat16 and got_dx.dtype == torch.bfloat16
+    aten = torch.nn.functional.gelu(x)
+    for g, w, a in ((got, want, aten), (got_dx, want_dx, None)):
+        exact = w.detach().float().bfloat16()
+        assert torch.isfinite(g.float()).all()
+        # within one bf16 ulp of the exact value; the absolute floor covers the zero crossing of gelu' at x = -0.75,
+        # where fp32 arithmetic (ours and ATen's) leaves ~1e-7 |dy| of absolute error on a value that is ~0
+        ulp = (exact.float().abs() * 2.0 ** -7).clamp_min(2e-6)
+        assert ((g.float() - w.detach().float()).abs() <= ulp).all()
+        ours = (g != exact).float().mean().item()
+        assert ours < 2e-3, ours                                                  # almost always THE correctly rounded value
+        if a is not None:
+            assert ours <= (a != exact).float().mean().item() + 1e-4
+    assert ops.gelu(torch.nn.GELU(approximate="tanh"), x).dtype == torch.bfloat16   # other activations: the module itself
+    assert ops.gelu(torch.nn.GELU(), x.float()).dtype == torch.float32
