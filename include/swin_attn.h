@@ -133,6 +133,11 @@ int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta
 int swin_gelu_forward(const void* x, void* y, int64_t n, void* stream);
 int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void* stream);
 
+/* Bias gradient of the per-token Linears either side of the attention (qkv / qk / proj, fc1 / fc2;
+ * newcrf_layers.py:102,118,147, swin_transformer.py:104,120,142): dbias[c] = sum over rows of dy[row, c].
+ * dy: (rows, cols) bf16, dense, 16-byte aligned, cols a multiple of 8; dbias: (cols) fp32, OVERWRITTEN. */
+int swin_linear_bias_grad(const void* dy, int64_t rows, int32_t cols, float* dbias, void* stream);
+
 /* Backward of swin_layernorm_forward for training under autocast (autograd of nn.LayerNorm in the reference).
  * dy: (rows, channels) of dy_dtype (bf16 for the bf16-output form, fp32 for the fp32-output form); x: the forward's
  * input (mean / rstd are recomputed).

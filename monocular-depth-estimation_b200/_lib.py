@@ -26,6 +26,7 @@ EXPORTS = (
     "swin_add_layernorm_forward",
     "swin_gelu_forward",
     "swin_gelu_backward",
+    "swin_linear_bias_grad",
     "swin_attn_launch_count",
     "swin_attn_uses_tcgen05",
     "swin_attn_last_error",
@@ -74,6 +75,8 @@ def load() -> ctypes.CDLL:
     lib.swin_gelu_forward.restype = c_int
     lib.swin_gelu_backward.argtypes = [vp, vp, vp, c_int64, vp]
     lib.swin_gelu_backward.restype = c_int
+    lib.swin_linear_bias_grad.argtypes = [vp, c_int64, c_int32, vp, vp]
+    lib.swin_linear_bias_grad.restype = c_int
     lib.swin_attn_launch_count.argtypes = []
     lib.swin_attn_launch_count.restype = c_uint64
     lib.swin_attn_uses_tcgen05.argtypes = [POINTER(Shape), c_int]

@@ -217,6 +217,22 @@ int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void*
   return gelu_entry("gelu backward", x, dy, dx, n, stream);
 }
 
+int swin_linear_bias_grad(const void* dy, int64_t rows, int32_t cols, float* dbias, void* stream) {
+  if (!dy || !dbias) return fail("linear bias grad: all pointers must be non-null");
+  if (rows < 0 || cols <= 0 || cols % 8) return fail("linear bias grad: rows >= 0 and cols a positive multiple of 8");
+  if (reinterpret_cast<uintptr_t>(dy) & 15 || reinterpret_cast<uintptr_t>(dbias) & 3)
+    return fail("linear bias grad: dy must be 16-byte aligned, dbias 4-byte aligned");
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  }
+  cudaError_t e = launch_colsum(dy, rows, cols, dbias, sms, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail_cuda("linear bias grad launch", e);
+  return 0;
+}
+
 int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int32_t dy_dtype, const float* gamma, float eps, int64_t rows,
                             int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream) {
   if (!x || !dy || !gamma || !dx || !dgamma || !dbeta) return fail("layernorm backward: all pointers must be non-null");

@@ -299,6 +299,25 @@ Tensor gelu_bwd_cuda(const Tensor& dy_in, const Tensor& x_in) {
 Tensor gelu_meta(const Tensor& x) { return at::empty_symint(x.sym_sizes(), x.options()); }
 Tensor gelu_bwd_meta(const Tensor&, const Tensor& x) { return at::empty_symint(x.sym_sizes(), x.options()); }
 
+// ---- swin_attn::linear: the autocast Linear with a fused bias gradient ---------------------------------------------
+Tensor bias_grad_cuda(const Tensor& dy_in) {
+  TORCH_CHECK(dy_in.dim() == 2 && dy_in.scalar_type() == at::kBFloat16 && dy_in.size(1) % 8 == 0,
+              "swin_attn::bias_grad: (rows, cols) bfloat16 with cols a multiple of 8");
+  const Tensor dy = dy_in.contiguous();
+  Tensor out = at::empty({dy.size(1)}, dy.options().dtype(at::kFloat));
+  c10::cuda::CUDAGuard guard(dy.device());
+  check_rc(swin_linear_bias_grad(dy.data_ptr(), dy.size(0), (int32_t)dy.size(1), out.data_ptr<float>(), at::cuda::getCurrentCUDAStream()));
+  return out;
+}
+
+Tensor bias_grad_meta(const Tensor& dy) { return at::empty_symint({dy.sym_size(1)}, dy.options().dtype(at::kFloat)); }
+
+// what torch.autocast(bf16) computes for nn.Linear: operands rounded to bf16, cuBLAS addmm with fp32 accumulation
+Tensor linear_any(const Tensor& x, const Tensor& weight, const optional<Tensor>& bias) {
+  return at::linear(x.to(at::kBFloat16), weight.to(at::kBFloat16),
+                    bias.has_value() ? optional<Tensor>(bias->to(at::kBFloat16)) : c10::nullopt);
+}
+
 std::tuple<Tensor, Tensor, Tensor> layer_norm_bwd_cuda(const Tensor& dy_in, const Tensor& x_in, const Tensor& weight, double eps) {
   const int32_t xd = dtype_code(x_in.scalar_type());
   const Tensor x = x_in.contiguous();
@@ -434,6 +453,37 @@ struct GeluFunction : public torch::autograd::Function<GeluFunction> {
 
 Tensor gelu_autograd(const Tensor& x) { return GeluFunction::apply(x); }
 
+struct LinearFunction : public torch::autograd::Function<LinearFunction> {
+  static Tensor forward(AutogradContext* ctx, const Tensor& x, const Tensor& weight, const optional<Tensor>& bias) {
+    at::AutoDispatchBelowADInplaceOrView guard;
+    const Tensor xb = x.to(at::kBFloat16), wb = weight.to(at::kBFloat16);
+    ctx->save_for_backward({xb, wb});
+    ctx->saved_data["x_dtype"] = (int64_t)x.scalar_type();
+    ctx->saved_data["w_dtype"] = (int64_t)weight.scalar_type();
+    ctx->saved_data["b_dtype"] = bias.has_value() ? (int64_t)bias->scalar_type() : (int64_t)-1;
+    return at::linear(xb, wb, bias.has_value() ? optional<Tensor>(bias->to(at::kBFloat16)) : c10::nullopt);
+  }
+  static variable_list backward(AutogradContext* ctx, variable_list grads) {
+    static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::bias_grad", "").typed<Tensor(const Tensor&)>();
+    const auto saved = ctx->get_saved_variables();
+    const Tensor &xb = saved[0], &wb = saved[1];
+    const int64_t n = wb.size(0), k = wb.size(1);
+    const Tensor dy = grads[0].to(at::kBFloat16).reshape({-1, n}).contiguous();
+    Tensor dx, dw, db;
+    if (ctx->needs_input_grad(0))
+      dx = at::mm(dy, wb).view(xb.sizes()).to((at::ScalarType)ctx->saved_data["x_dtype"].toInt());
+    if (ctx->needs_input_grad(1))
+      dw = at::mm(dy.t(), xb.reshape({-1, k})).to((at::ScalarType)ctx->saved_data["w_dtype"].toInt());
+    const int64_t bd = ctx->saved_data["b_dtype"].toInt();
+    if (bd >= 0 && ctx->needs_input_grad(2)) db = (n % 8 == 0 ? op.call(dy) : dy.sum(0)).to((at::ScalarType)bd);
+    return {dx, dw, db};
+  }
+};
+
+Tensor linear_autograd(const Tensor& x, const Tensor& weight, const optional<Tensor>& bias) {
+  return LinearFunction::apply(x, weight, bias);
+}
+
 Tensor layer_norm_autograd(const Tensor& x, const Tensor& weight, const Tensor& bias, double eps, bool out_bf16) {
   return LayerNormFunction::apply(x, weight, bias, eps, out_bf16);
 }
@@ -450,6 +500,8 @@ TORCH_LIBRARY(swin_attn, m) {
   m.def("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps, bool out_bf16) -> Tensor");
   m.def("layer_norm_bwd(Tensor dy, Tensor x, Tensor weight, float eps) -> (Tensor, Tensor, Tensor)");
   m.def("add_layer_norm(Tensor x, Tensor delta, Tensor weight, Tensor bias, float eps) -> (Tensor, Tensor)");
+  m.def("linear(Tensor x, Tensor weight, Tensor? bias) -> Tensor");
+  m.def("bias_grad(Tensor dy) -> Tensor");
   m.def("gelu(Tensor x) -> Tensor");
   m.def("gelu_bwd(Tensor dy, Tensor x) -> Tensor");
 }
@@ -460,6 +512,8 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("layer_norm", layer_norm_cuda);
   m.impl("layer_norm_bwd", layer_norm_bwd_cuda);
   m.impl("add_layer_norm", add_layer_norm_cuda);
+  m.impl("linear", linear_any);
+  m.impl("bias_grad", bias_grad_cuda);
   m.impl("gelu", gelu_cuda);
   m.impl("gelu_bwd", gelu_bwd_cuda);
 }
@@ -470,6 +524,8 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("layer_norm", layer_norm_meta);
   m.impl("layer_norm_bwd", layer_norm_bwd_meta);
   m.impl("add_layer_norm", add_layer_norm_meta);
+  m.impl("linear", linear_any);
+  m.impl("bias_grad", bias_grad_meta);
   m.impl("gelu", gelu_meta);
   m.impl("gelu_bwd", gelu_bwd_meta);
 }
@@ -479,6 +535,7 @@ TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
   m.impl("layer_norm", layer_norm_autograd);
   m.impl("add_layer_norm", torch::autograd::autogradNotImplementedFallback());   // inference only
   m.impl("gelu", gelu_autograd);
+  m.impl("linear", linear_autograd);
 }
 
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------

@@ -59,7 +59,7 @@ class Mlp(nn.Module):
         self.drop = nn.Dropout(drop)
 
     def forward(self, x):
-        return self.drop(self.fc2(self.drop(ops.gelu(self.act, self.fc1(x)))))
+        return self.drop(ops.linear(self.fc2, self.drop(ops.gelu(self.act, ops.linear(self.fc1, x)))))
 
 
 def _relative_position_index(wh: int, ww: int) -> torch.Tensor:
@@ -129,14 +129,14 @@ class WindowAttention(_WindowAttentionBase):
             if pb or pr:
                 x_img = F.pad(x_img, (0, 0, 0, pr, 0, pb))
                 v_img = F.pad(v_img, (0, 0, 0, pr, 0, pb))
-            o = ops.window_attention(self.qk(x_img), v_img, self.relative_position_bias_table, ws, shift,
+            o = ops.window_attention(ops.linear(self.qk, x_img), v_img, self.relative_position_bias_table, ws, shift,
                                      self.num_heads, self.scale, dropout_p=self._drop_p())
             o = o[:, :h, :w, :]
         else:
-            o = ops.window_attention(self.qk(x_img), v_img, self.relative_position_bias_table, ws, shift,
+            o = ops.window_attention(ops.linear(self.qk, x_img), v_img, self.relative_position_bias_table, ws, shift,
                                      self.num_heads, self.scale, packed_pad=self.qk.bias, v_pad=None,
                                      dropout_p=self._drop_p())
-        return self.proj_drop(self.proj(o))
+        return self.proj_drop(ops.linear(self.proj, o))
 
 
 class EncoderWindowAttention(_WindowAttentionBase):
@@ -160,13 +160,13 @@ class EncoderWindowAttention(_WindowAttentionBase):
             pb, pr = (-h) % ws, (-w) % ws
             if pb or pr:
                 x_img = F.pad(x_img, (0, 0, 0, pr, 0, pb))
-            o = ops.window_attention(self.qkv(x_img), None, self.relative_position_bias_table, ws, shift,
+            o = ops.window_attention(ops.linear(self.qkv, x_img), None, self.relative_position_bias_table, ws, shift,
                                      self.num_heads, self.scale, dropout_p=self._drop_p())
             o = o[:, :h, :w, :]
         else:
-            o = ops.window_attention(self.qkv(x_img), None, self.relative_position_bias_table, ws, shift,
+            o = ops.window_attention(ops.linear(self.qkv, x_img), None, self.relative_position_bias_table, ws, shift,
                                      self.num_heads, self.scale, packed_pad=self.qkv.bias, dropout_p=self._drop_p())
-        return self.proj_drop(self.proj(o))
+        return self.proj_drop(ops.linear(self.proj, o))
 
 
 class CRFBlock(nn.Module):

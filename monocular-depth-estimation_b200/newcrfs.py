@@ -138,6 +138,25 @@ def _bilinear_resize_small(x, size):
         return torch.matmul(x.float().reshape(n * c, h * w), k).view(n, c, size[0], size[1]).to(x.dtype)
 
 
+def _adaptive_avg_pool_small(x, out_size):
+    """``F.adaptive_avg_pool2d(x, out_size)`` of the last encoder feature (11x38 .. 15x20 pixels) as one fp32 matmul
+    with the pooling matrix (ATen's NHWC kernel takes ~100 us per pool scale at batch 8 for 0.4 MFLOP of work).  The
+    matrix is the response of the same ATen op to the identity, so the bin boundaries and weights are identical."""
+    n, c, h, w = x.shape
+    s = out_size if isinstance(out_size, (tuple, list)) else (out_size, out_size)
+    key = ("pool", h, w, s[0], s[1], x.device)
+    k = _RESIZE_CACHE.get(key)
+    if k is None:
+        eye = torch.eye(h * w, device=x.device, dtype=torch.float32).view(1, h * w, h, w)
+        k = F.adaptive_avg_pool2d(eye, s).reshape(h * w, s[0] * s[1])
+        _RESIZE_CACHE[key] = k
+    with torch.autocast(x.device.type, enabled=False):
+        # (n, hw, c) is a free view of a channels-last feature; one batched (s*s, hw) x (hw, c) product
+        tokens = x.permute(0, 2, 3, 1).reshape(n, h * w, c).float()
+        pooled = torch.matmul(k.t(), tokens)                       # (n, s*s, c)
+        return pooled.transpose(1, 2).reshape(n, c, s[0], s[1]).to(x.dtype)
+
+
 class PSP(nn.Module):
     """Pyramid pooling over the last encoder feature (uper_crf_head.py:9-58, 318-364).
 
@@ -161,7 +180,10 @@ class PSP(nn.Module):
 
     def forward(self, inputs):
         x = inputs[-1]
-        outs = [x] + [_bilinear_resize_small(m(x), x.shape[2:]) for m in self.psp_modules]
+        outs = [x]
+        for m in self.psp_modules:   # Sequential(AdaptiveAvgPool2d(s), ConvModule): same modules, the pool as a matmul
+            pooled = _adaptive_avg_pool_small(x, m[0].output_size) if x.is_cuda else m[0](x)
+            outs.append(_bilinear_resize_small(m[1](pooled), x.shape[2:]))
         return self.bottleneck(torch.cat(outs, dim=1))
 
 

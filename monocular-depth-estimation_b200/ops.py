@@ -114,6 +114,18 @@ def norm_fp32(norm: torch.nn.Module, x: Tensor) -> Tensor:
     return norm(x)
 
 
+def linear(lin: torch.nn.Module, x: Tensor) -> Tensor:
+    """``lin(x)`` for the per-token Linears of the blocks.  In training under bf16 autocast this is one C++ autograd
+    node computing what autocast computes (bf16 operands, cuBLAS addmm) whose backward sums the bias gradient with the
+    fused column-sum kernel instead of ATen's generic reduction; every other case is the module itself."""
+    if (type(lin) is torch.nn.Linear and lin.bias is not None and x.is_cuda and torch.is_grad_enabled()
+            and torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") == torch.bfloat16
+            and lin.out_features % 8 == 0 and x.dtype in _DTYPES and lin.weight.dtype in _DTYPES
+            and (x.requires_grad or lin.weight.requires_grad)):
+        return torch.ops.swin_attn.linear(x, lin.weight, lin.bias)
+    return lin(x)
+
+
 def gelu(act: torch.nn.Module, x: Tensor) -> Tensor:
     """``act(x)`` for the MLP activation: the fused exact-GELU kernel when ``act`` is ``nn.GELU()`` (erf form) and ``x``
     is the bf16 output of an autocast Linear; otherwise the module itself."""

@@ -13,7 +13,7 @@ from conftest import ROOT
 def _declared():
     text = open(os.path.join(ROOT, "include", "swin_attn.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(swin_(?:attn|layernorm|add_layernorm|gelu)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(swin_(?:attn|layernorm|add_layernorm|gelu|linear)_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_library_exports_every_declared_symbol():

@@ -617,3 +617,29 @@ def test_fused_gelu_forward_backward_vs_fp64():
             assert ours <= (a != exact).float().mean().item() + 1e-4
     assert ops.gelu(torch.nn.GELU(approximate="tanh"), x).dtype == torch.bfloat16   # other activations: the module itself
     assert ops.gelu(torch.nn.GELU(), x.float()).dtype == torch.float32
+
+
+@pytest.mark.parametrize("shape", [(3, 50, 192, 576), (2, 7, 9, 128, 256), (1, 4099, 768, 3072), (5, 33, 1024, 1024)])
+def test_linear_with_fused_bias_grad_matches_autocast_linear(shape):
+    """swin_attn::linear (training path of qkv / qk / proj / fc1 / fc2): same output and input / weight gradients as
+    nn.Linear under autocast (same cuBLAS calls on the same bf16 operands); the bias gradient is the fp32 column sum
+    of the bf16 dy -- at least as close to the fp64 sum as autocast's bf16-rounded one."""
+    *lead, k, n = shape
+    gen = torch.Generator(device=DEV).manual_seed(sum(shape))
+    lin = torch.nn.Linear(k, n).to(DEV)
+    x = torch.randn(*lead, k, device=DEV, generator=gen).requires_grad_()
+    cot = torch.randn(*lead, n, device=DEV, generator=gen).bfloat16()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        want = lin(x)
+        got = ops.linear(lin, x)
+    assert got.dtype == torch.bfloat16 and torch.equal(got, want)
+    gw = torch.autograd.grad(want, [x, lin.weight, lin.bias], cot)
+    gg = torch.autograd.grad(got, [x, lin.weight, lin.bias], cot)
+    for a, b in zip(gg, gw):
+        assert a.dtype == b.dtype == torch.float32 and a.shape == b.shape
+    assert torch.equal(gg[0], gw[0]) and torch.equal(gg[1], gw[1])
+    exact = cot.double().reshape(-1, n).sum(0)
+    assert rel_err(gg[2], exact) < 1e-5
+    assert rel_err(gg[2], exact) <= rel_err(gw[2], exact) + 1e-6
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        assert torch.equal(ops.linear(lin, x), want)          # no gradients: the module itself
