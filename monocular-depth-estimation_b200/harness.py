@@ -124,7 +124,9 @@ class Trainer:
     def __init__(self, model: nn.Module, lr: float = 2e-5, grad_norm: float = 0.1, bf16: bool = True,
                  ddp: bool = False, device_ids=None):
         self.raw = model
-        self.model = nn.parallel.DistributedDataParallel(model, device_ids=device_ids) if ddp else model
+        # gradients live inside the all-reduce buckets: no per-parameter copy kernel (~600 launches per step)
+        self.model = nn.parallel.DistributedDataParallel(model, device_ids=device_ids,
+                                                         gradient_as_bucket_view=True) if ddp else model
         self.opt = torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=0.0,
                                      fused=next(model.parameters()).is_cuda)   # one multi-tensor kernel per step
         self.loss_fn = SILogLoss()
