@@ -7,6 +7,11 @@ head merge, window_reverse, roll, crop (oracle/window_attention.py, the restatem
 reference modules) -- next to the fused kernel, on the stage grids of NewCRFs Swin-L at batch 8.
 
     python tests/bench_reference_eager_gpu.py [--iters 10] [--only NAME] [--bwd]
+    python tests/bench_reference_eager_gpu.py --model     # whole NewCRFs Swin-L forward, reference op sequence on the GPU
+
+``--model`` is the "stronger bar" of SURVEY.md 8d / BASELINE.md 4: the reference's own eager op sequence (oracle/cpu_model.py,
+the restatement pinned against the reference modules) on the same B200 in fp32 and under torch.autocast(bf16), batch 8 at
+352x1216, beside this repo's model (harness.infer on a prepare_inference'd model).
 """
 import argparse
 import json
@@ -40,12 +45,40 @@ def timed(fn, iters, flush):
     return sum(a.elapsed_time(b) for a, b in evs) / iters * 1e3
 
 
+def model_mode(iters):
+    import mde_b200
+    from mde_b200.harness import build_model, infer, prepare_inference, synthetic_images
+    from oracle.cpu_model import to_oracle
+    dev = torch.device("cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    model = build_model("large07", 80.0, seed=0, device=dev).eval()
+    ref = to_oracle(model, dev).eval()
+    images = synthetic_images(8, 352, 1216, seed=0).to(dev)
+    out = {}
+    with torch.no_grad():
+        out["reference_eager_fp32_ms"] = timed(lambda: ref(images), iters, flush) / 1e3
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out["reference_eager_bf16_autocast_ms"] = timed(lambda: ref(images), iters, flush) / 1e3
+        out["ours_fp32_ms"] = timed(lambda: infer(model, images, bf16=False), iters, flush) / 1e3
+    prepare_inference(model)
+    out["ours_bf16_autocast_ms"] = timed(lambda: infer(model, images), iters, flush) / 1e3
+    out = {k: round(v, 3) for k, v in out.items()}
+    out.update({"workload": "NewCRFs large07 forward, batch 8, 3x352x1216, random-init weights, L2 flushed between steps",
+                "images_per_s": {k[:-3]: round(8e3 / v, 1) for k, v in out.items()},
+                "speedup_vs_reference_bf16": round(out["reference_eager_bf16_autocast_ms"] / out["ours_bf16_autocast_ms"], 2),
+                "speedup_vs_reference_fp32": round(out["reference_eager_fp32_ms"] / out["ours_fp32_ms"], 2)})
+    print(json.dumps(out), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--model", action="store_true")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--only", default=None)
     ap.add_argument("--bwd", action="store_true")
     args = ap.parse_args()
+    if args.model:
+        return model_mode(args.iters)
     dev = torch.device("cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     for name, (b, h, w, nh, ws) in SHAPES.items():
