@@ -83,13 +83,37 @@ def test_layernorm_validation_without_gpu():
     assert lib.swin_layernorm_forward(ptr, _lib.BF16, ptr, ptr, 1e-5, 0, 128, ptr, _lib.F32, None) == 0   # empty input: no launch
 
 
+def test_block_plumbing_entries_validate_without_gpu():
+    """swin_add_layernorm_forward / swin_gelu_* / swin_linear_bias_grad / swin_layernorm_backward reject bad arguments
+    before touching the device and treat empty inputs as a no-op."""
+    lib = _lib.load()
+    buf = (ctypes.c_float * 256)()
+    base = ctypes.addressof(buf)
+    base += (-base) % 16
+    ptr, odd = ctypes.c_void_p(base), ctypes.c_void_p(base + 2)
+    err = lib.swin_attn_last_error
+    assert lib.swin_add_layernorm_forward(ptr, _lib.F32, ptr, ptr, ptr, 1e-5, 1, 3072, ptr, ptr, None) != 0
+    assert b"channels must be one of" in err()
+    assert lib.swin_add_layernorm_forward(ptr, 7, ptr, ptr, ptr, 1e-5, 1, 128, ptr, ptr, None) != 0 and b"x_dtype" in err()
+    assert lib.swin_add_layernorm_forward(ptr, _lib.F32, None, ptr, ptr, 1e-5, 1, 128, ptr, ptr, None) != 0
+    assert lib.swin_add_layernorm_forward(ptr, _lib.BF16, ptr, ptr, ptr, 1e-5, 0, 128, ptr, ptr, None) == 0
+    assert lib.swin_gelu_forward(ptr, ptr, 12, None) != 0 and b"multiple of 8" in err()
+    assert lib.swin_gelu_forward(odd, ptr, 16, None) != 0 and b"16-byte aligned" in err()
+    assert lib.swin_gelu_backward(ptr, None, ptr, 16, None) != 0
+    assert lib.swin_gelu_forward(ptr, ptr, 0, None) == 0
+    assert lib.swin_linear_bias_grad(ptr, 4, 12, ptr, None) != 0 and b"multiple of 8" in err()
+    assert lib.swin_linear_bias_grad(None, 4, 16, ptr, None) != 0
+    assert lib.swin_layernorm_backward(ptr, _lib.F32, ptr, 9, ptr, 1e-5, 1, 128, ptr, ptr, ptr, None) != 0 and b"dy_dtype" in err()
+    assert lib.swin_layernorm_backward(ptr, _lib.F32, ptr, _lib.BF16, ptr, 1e-5, 1, 3072, ptr, ptr, ptr, None) != 0
+
+
 def test_torch_binding_registers_ops_without_a_gpu():
     """libswin_attn_torch.so (csrc/torch_binding.cpp) loads on a CPU-only host, registers the four dispatcher ops with
     the documented schemas, has Meta kernels for shape inference and no CPU kernels (CPU tensors raise)."""
     import torch
     from mde_b200 import ops
     assert os.path.exists(ops.TORCH_LIB_PATH)
-    for name in ("fwd", "bwd", "layer_norm", "layer_norm_bwd"):
+    for name in ("fwd", "bwd", "layer_norm", "layer_norm_bwd", "add_layer_norm", "gelu", "gelu_bwd", "linear", "bias_grad"):
         assert hasattr(torch.ops.swin_attn, name)
     s = str(torch.ops.swin_attn.fwd.default._schema)
     assert "Tensor? attn_mask=None, float dropout_p=0., int seed=0" in s and s.endswith("-> (Tensor, Tensor)")
