@@ -9,16 +9,18 @@
 //
 //   producers (warps 0 / 3, one elected lane): window partition, cyclic shift, right/bottom zero
 //       padding are TMA tensor-map addressing over the image-order (B,H,W,channels) tensors
-//       (swin_attn_tc.cuh::move_window); 4 stages of (q0 q1 | k0 k1 | v0 v1 | ones).
-//   pad tokens carry the Linear bias in the reference (newcrf_layers.py:212-217).  All pad tokens of
-//       a head share ONE vector and the head is fixed per CTA, so k_pad / v_pad are written once into
-//       the spare row 49 of every stage's K / V tiles: S[:,49] = q . k_pad comes out of the QK^T MMA and
-//       stands in for every pad column; P[:,49] = sum of the pad columns' probabilities multiplies v_pad.
+//       (swin_attn_tc.cuh::move_window); two rings: 4 stages of (q0 q1 | k0 k1), 6 of (v0 v1 | ones).
+//   pad tokens carry the Linear bias in the reference (newcrf_layers.py:212-217) while TMA zero-fills
+//       them.  All pad tokens of a head share ONE vector and the head is fixed per CTA: once a K / V
+//       tile has landed, the warp that issues its MMA overwrites the rows of the tile's pad tokens with
+//       k_pad / v_pad (write_pad_rows), so both MMAs see the reference's operands and the softmax has no
+//       padding code path (an earlier version substituted q . k_pad per column in registers: ~620 extra
+//       instructions per row on half of the stage-2 tiles).
 //   MMA issuers (warps 1 / 2, one elected lane):
 //       S = [Q0;Q1] [K0;K1]^T   (M128 N112 K32)   tile t: rows 64t.., columns 56t..
 //       O = [P0;P1] [V0|V1|1]   (M128 N96  K64, V MN-major)   tile t: rows 64t.., columns 32t..;
 //           column 64 multiplies a constant ones tile and holds the softmax row sums
-//   softmax warpgroups (3 x 4 warps, one accumulator slot each): scale + relative position bias (the
+//   softmax warpgroups (4 x 4 warps, one accumulator slot each): scale + relative position bias (the
 //       head's 169 table entries staged in smem) + analytic SW-MSA mask, row max, exp2, P as bf16 into
 //       a 128B-swizzled smem tile; then the O row x 1/rowsum -> bf16 -> 64B-swizzled staging tile -> TMA
 //       tensor store with the same boxes as the loads (window reverse, inverse shift and crop are
@@ -44,6 +46,49 @@ constexpr int kSlotColsF = 128;                // S: 112 columns; O (65 columns)
 __device__ __forceinline__ uint32_t q_off(int t) { return t * kTileBytes; }
 __device__ __forceinline__ uint32_t k_off(int t) { return 2 * kTileBytes + t * kKTile1; }   // in a QK stage
 __device__ __forceinline__ uint32_t v_off(int t) { return t * kTileBytes; }                    // in a V stage
+
+// Padding tokens (y >= H or x >= W) can only occur in the last two window rows / columns: their tile-row bit sets,
+// for window row nWy-2 ([0]) and nWy-1 ([1]), likewise for columns.
+template <bool kPerm>
+struct PadSets {
+  uint64_t y[2], x[2];
+  __device__ __forceinline__ void init(const Problem& p) {
+    y[0] = y[1] = x[0] = x[1] = 0;
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+#pragma unroll
+      for (int i = 0; i < WS; ++i) {
+        int yy = (p.nWy - 2 + e) * WS + i + p.shift, xx = (p.nWx - 2 + e) * WS + i + p.shift;
+        if (yy >= p.Hp) yy -= p.Hp;
+        if (xx >= p.Wp) xx -= p.Wp;
+        if (yy >= p.H && p.nWy - 2 + e >= 0) y[e] |= rows_of_window_row<kPerm>(i);
+        if (xx >= p.W && p.nWx - 2 + e >= 0) x[e] |= rows_of_window_col<kPerm>(i);
+      }
+    }
+  }
+  __device__ __forceinline__ uint64_t of(const Problem& p, int wy, int wx) const {
+    return (wy == p.nWy - 1 ? y[1] : wy == p.nWy - 2 ? y[0] : 0) | (wx == p.nWx - 1 ? x[1] : wx == p.nWx - 2 ? x[0] : 0);
+  }
+};
+
+// Pad tokens carry the projection bias (the reference pads before the Linear), but TMA zero-fills them: after a
+// K / V tile has landed, the issuing warp overwrites the rows of its pad tokens with the head's pad vector, so the
+// S and PV MMAs see exactly the reference's operands and the softmax needs no pad handling at all.  `vec` holds the
+// 64 bytes of the vector (4 x 16 B); rows are 64 B with the 64B swizzle of the TMA box.
+__device__ __forceinline__ void write_pad_rows(uint32_t tile, uint64_t padded, const uint4 (&vec)[4], int lane) {
+#pragma unroll
+  for (int r0 = 0; r0 < 64; r0 += 32) {
+    const int r = r0 + lane;
+    if (r < N && ((padded >> r) & 1)) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const uint32_t dst = tile + r * 64 + ((c ^ ((r >> 1) & 3)) << 4);
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(vec[c].x), "r"(vec[c].y), "r"(vec[c].z), "r"(vec[c].w)
+                     : "memory");
+      }
+    }
+  }
+}
 
 struct TmaMapsF {
   CUtensorMap q[7], k[7], v[7];   // loads
@@ -115,35 +160,21 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     const int t14 = tid - (warp < 3 ? 32 : 64);   // 0 .. kFillF-1 over the non-producer warps
     // global loads first, so that their latency overlaps the fills: this head's bias column and pad vectors
     const float bias_v = t14 < 169 ? p.table[t14 * p.nH + h] * kLog2e : 0.f;
-    uint4 pad_v = make_uint4(0u, 0u, 0u, 0u);
-    // row-49 items: [0, 8 kQKStages) = (QK stage, tile, chunk) for k_pad; then (V stage, tile, chunk) for v_pad
-    const bool pad_is_v = t14 >= 8 * kQKStages;
-    const int pad_item = pad_is_v ? t14 - 8 * kQKStages : t14;
-    const bool pad_thread = t14 < 8 * (kQKStages + kVStages);
-    if (has_pad && pad_thread) {
-      const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(pad_is_v ? p.v_pad : p.k_pad);
-      if (src != nullptr) pad_v = *reinterpret_cast<const uint4*>(src + h * kHeadDim + (t14 & 3) * 8);
-    }
     if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
     // Rows 49-63 of the K / V tiles (TMA boxes write rows 0-48 only) must be finite: K rows 49-55 feed S
-    // columns that are never read, V rows 49-63 are multiplied by P columns that are 0.  Row 49 of both holds
-    // the head's pad vector (see the file header); the rest is zero.  K tile 1 starts at row 56 of K tile 0.
-    for (int i = t14; i < kQKStages * 2 * 6 * 4; i += kFillF) {          // K rows 50-55
-      const int chunk = i & 3, rr = (i >> 2) % 6, t = ((i >> 2) / 6) & 1, st = (i >> 2) / 12;
-      const int r50 = 50 + rr;
+    // columns that are never read, V rows 49-63 are multiplied by P columns that are 0.  K tile 1 starts at row 56 of
+    // K tile 0.
+    for (int i = t14; i < kQKStages * 2 * 7 * 4; i += kFillF) {          // K rows 49-55
+      const int chunk = i & 3, rr = (i >> 2) % 7, t = ((i >> 2) / 7) & 1, st = (i >> 2) / 14;
+      const int r50 = 49 + rr;
       *reinterpret_cast<uint4*>(smem + map.qk + st * kQKBytes + k_off(t) + r50 * 64 + ((chunk ^ ((r50 >> 1) & 3)) << 4)) =
           make_uint4(0u, 0u, 0u, 0u);
     }
-    for (int i = t14; i < kVStages * 2 * 14 * 4; i += kFillF) {          // V rows 50-63
-      const int chunk = i & 3, rr = (i >> 2) % 14, t = ((i >> 2) / 14) & 1, st = (i >> 2) / 28;
-      const int r50 = 50 + rr;
+    for (int i = t14; i < kVStages * 2 * 15 * 4; i += kFillF) {          // V rows 49-63
+      const int chunk = i & 3, rr = (i >> 2) % 15, t = ((i >> 2) / 15) & 1, st = (i >> 2) / 30;
+      const int r50 = 49 + rr;
       *reinterpret_cast<uint4*>(smem + map.v + st * kVBytes + v_off(t) + r50 * 64 + ((chunk ^ ((r50 >> 1) & 3)) << 4)) =
           make_uint4(0u, 0u, 0u, 0u);
-    }
-    if (pad_thread) {                               // row 49 (swizzle term (49 >> 1) & 3 = 0)
-      const int chunk = pad_item & 3, t = (pad_item >> 2) & 1, st = pad_item >> 3;
-      *reinterpret_cast<uint4*>(smem + (pad_is_v ? map.v + st * kVBytes + v_off(t) : map.qk + st * kQKBytes + k_off(t)) + 49 * 64 +
-                                (chunk << 4)) = pad_v;
     }
     // ones tile of every V stage (64B-swizzled, MN-major B of the PV MMA): element 0 of each key row is 1.0
     // (bf16), so column 64 of O = sum_j P[i, j]
@@ -203,12 +234,34 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   } else if (warp == 1) {
     // ===== S = Q K^T issuer (2 instructions per pair) ===========================================
     constexpr uint32_t idesc_s = instr_desc(128, 112, 0);
+    const bool fix = has_pad && p.k_pad != nullptr;
+    PadSets<kPerm> pads;
+    uint4 kvec[4] = {};
+    WinIter it;
+    it.init(p, w0);
+    if (fix) {
+      pads.init(p);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) kvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.k_pad) + h * kHeadDim)[c];
+    }
     for (int n = 0; n < n_pairs; ++n) {
       const int s = n % kQKStages, a = n % kSlotsF;
+      const uint32_t st = sbase + map.qk + s * kQKBytes;
       mbar_wait(bar_qk_full + 8 * s, (n / kQKStages) & 1);
+      if (fix) {   // pad tokens of the two K tiles <- k_pad (generic-proxy writes after the TMA boxes have landed)
+        const uint64_t pad0 = pads.of(p, it.wy, it.wx);
+        it.advance(p, 1);
+        const uint64_t pad1 = it.w < w1 ? pads.of(p, it.wy, it.wx) : 0;
+        it.advance(p, 1);
+        if (pad0 | pad1) {
+          write_pad_rows(st + k_off(0), pad0, kvec, lane);
+          write_pad_rows(st + k_off(1), pad1, kvec, lane);
+          fence_proxy_async();
+        }
+        __syncwarp();
+      }
       mbar_wait(bar_r + 8 * a, ((n / kSlotsF) & 1) ^ 1);
       tc_fence_after();
-      const uint32_t st = sbase + map.qk + s * kQKBytes;
       const uint32_t d = tmem_base + a * kSlotColsF;
       const uint64_t qd = smem_desc(st + q_off(0), 16, 512, 4);   // 128 rows: q0 | q1
       const uint64_t kd = smem_desc(st + k_off(0), 16, 512, 4);   // 112 rows: k0 (56) | k1 (56)
@@ -225,12 +278,34 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   } else if (warp == 2) {
     // ===== O = P V issuer (4 instructions per pair) =============================================
     constexpr uint32_t idesc_o = instr_desc(128, 96, 1);
+    const bool fix = has_pad && p.v_pad != nullptr;
+    PadSets<kPerm> pads;
+    uint4 vvec[4] = {};
+    WinIter it;
+    it.init(p, w0);
+    if (fix) {
+      pads.init(p);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) vvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.v_pad) + h * kHeadDim)[c];
+    }
     for (int m = 0; m < n_pairs; ++m) {
       const int s = m % kVStages, a = m % kSlotsF;
+      const uint32_t st = sbase + map.v + s * kVBytes;
       mbar_wait(bar_v_full + 8 * s, (m / kVStages) & 1);
+      if (fix) {   // pad tokens of the two V tiles <- v_pad, while the softmax of the pair is still running
+        const uint64_t pad0 = pads.of(p, it.wy, it.wx);
+        it.advance(p, 1);
+        const uint64_t pad1 = it.w < w1 ? pads.of(p, it.wy, it.wx) : 0;
+        it.advance(p, 1);
+        if (pad0 | pad1) {
+          write_pad_rows(st + v_off(0), pad0, vvec, lane);
+          write_pad_rows(st + v_off(1), pad1, vvec, lane);
+          fence_proxy_async();
+        }
+        __syncwarp();
+      }
       mbar_wait(bar_p + 8 * a, (m / kSlotsF) & 1);
       tc_fence_after();
-      const uint32_t st = sbase + map.v + s * kVBytes;
       const uint32_t d = tmem_base + a * kSlotColsF;               // O overwrites the S columns
       const uint64_t pd = smem_desc(sbase + map.slots + a * kSlotBytesF, 16, 1024, 2);   // 128 rows: p0 | p1
       const uint64_t vd = smem_desc(st + v_off(0), kTileBytes, 512, 4);   // N = 96: v0 | v1 | ones, one tile apart
@@ -265,22 +340,6 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
 #pragma unroll
       for (int j = WS - kShift; j < WS; ++j) wb |= rows_of_window_col<kPerm>(j);
     }
-    // Padding tokens (y >= H or x >= W) can only occur in the last two window rows / columns: their
-    // tile-row bit sets, for window row nWy-2 ([0]) and nWy-1 ([1]), likewise for columns.
-    uint64_t pad_y[2] = {0, 0}, pad_x[2] = {0, 0};
-    if (has_pad) {
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-#pragma unroll
-        for (int i = 0; i < WS; ++i) {
-          int yy = (p.nWy - 2 + e) * WS + i + p.shift, xx = (p.nWx - 2 + e) * WS + i + p.shift;
-          if (yy >= p.Hp) yy -= p.Hp;
-          if (xx >= p.Wp) xx -= p.Wp;
-          if (yy >= p.H && p.nWy - 2 + e >= 0) pad_y[e] |= rows_of_window_row<kPerm>(i);
-          if (xx >= p.W && p.nWx - 2 + e >= 0) pad_x[e] |= rows_of_window_col<kPerm>(i);
-        }
-      }
-    }
     const uint32_t sl = sbase + map.slots + g * kSlotBytesF;
     const uint32_t p_row = sl + sel * kPTileBytes + row * 128;
     const uint32_t o_row = sl + sel * kTileBytes + row * 64;     // staging tile of this thread's output row
@@ -293,16 +352,14 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     int m = 0;
     for (int n = g; n < n_pairs; n += kSlotsF, ++m, it.advance(p, 2 * kSlotsF)) {
       const bool valid = it.w < w1;
-      uint64_t masked = 0, padded = 0;
+      // Padding needs nothing here: the issuer warps have put the pad vectors into the K / V rows of pad tokens.
+      uint64_t masked = 0;
       if (kShifted) {
         const uint64_t hm = it.wy == p.nWy - 1 ? hb : 0, wm = it.wx == p.nWx - 1 ? wb : 0;
         masked = (((hm >> rowc) & 1) ? (~hm & all) : hm) | (((wm >> rowc) & 1) ? (~wm & all) : wm);
       }
-      if (has_pad)
-        padded = (it.wy == p.nWy - 1 ? pad_y[1] : it.wy == p.nWy - 2 ? pad_y[0] : 0) |
-                 (it.wx == p.nWx - 1 ? pad_x[1] : it.wx == p.nWx - 2 ? pad_x[0] : 0);
-      // every row of a tile with a mask / padding has masked columns, so this is warp-uniform
-      const bool special = (kShifted && (it.wy == p.nWy - 1 || it.wx == p.nWx - 1)) || padded != 0;
+      // every row of a tile with a mask has masked columns, so this is warp-uniform
+      const bool special = kShifted && (it.wy == p.nWy - 1 || it.wx == p.nWx - 1);
 
       const bool tr = q == 0 && lane == 0;   // timeline of tile 0, row 0
       if (tr) TC_TRACE(p, n, 7);
@@ -313,7 +370,7 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       TMEM_LD_X16(s_addr, (r + 0));
       TMEM_LD_X16(s_addr + 16, (r + 16));
       TMEM_LD_X16(s_addr + 32, (r + 32));
-      TMEM_LD_X2(s_addr + 48, r[48], r[49]);   // column 49 = q . k_pad (spare K row)
+      TMEM_LD_X2(s_addr + 48, r[48], r[49]);   // column 49 belongs to the zero rows and is not used
       tmem_ld_wait();
       if (tr) TC_TRACE(p, n, 9);
 
@@ -336,12 +393,10 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
           mx = fmaxf(mx, t);
         }
       } else {
-        const float a49 = __uint_as_float(r[49]);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
           const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
-          const float acc = ((padded >> j) & 1) ? a49 : __uint_as_float(r[j]);
-          float t = fmaf(acc, c1s, brow[-cj]);
+          float t = fmaf(__uint_as_float(r[j]), c1s, brow[-cj]);
           if ((masked >> j) & 1) t += -100.0f * kLog2e;
           r[j] = __float_as_uint(t);
           mx = fmaxf(mx, t);
@@ -350,24 +405,13 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       // pass 2: p = exp2(t - max), rounded to bf16 for the PV MMA; the row sum comes out of that MMA through the
       // ones column, i.e. it is the sum of exactly the rounded values in P.
       const float2 nmx = make_float2(-mx, -mx);
-      float pad_sum = 0.f;
-      if (special && padded != 0) {
-        // pad columns: their V rows are zero (TMA fill); move their probability mass to column 49 (x v_pad)
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-          if ((padded >> j) & 1) {
-            pad_sum += fast_exp2(__uint_as_float(r[j]) - mx);
-            r[j] = __float_as_uint(-INFINITY);
-          }
-        }
-      }
       uint32_t w[25];
 #pragma unroll
       for (int e = 0; e < 24; ++e) {
         const float2 x = __fadd2_rn(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), nmx);
         w[e] = pack_bf16(fast_exp2(x.x), fast_exp2(x.y));
       }
-      w[24] = pack_bf16(fast_exp2(__uint_as_float(r[N - 1]) - mx), pad_sum);
+      w[24] = pack_bf16(fast_exp2(__uint_as_float(r[N - 1]) - mx), 0.f);
       // the TMA stores of this warpgroup's previous pair must have finished reading the staging tiles (same
       // bytes as P) before P is overwritten
       if (issuer && elect_one()) bulk_wait_read();
