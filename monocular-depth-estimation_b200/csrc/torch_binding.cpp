@@ -151,6 +151,7 @@ std::tuple<Tensor, Tensor> fwd_cuda(const Tensor& packed_in, const optional<Tens
   Tensor o = at::empty({b, h, w, c}, packed.options());
   Tensor lse = need_lse ? at::empty({b, hp, wp, num_heads}, packed.options().dtype(at::kFloat))
                         : at::empty({0}, packed.options().dtype(at::kFloat));
+  if (o.numel() == 0) return {o, lse};   // empty batch: nothing to launch (the reference returns empty tensors too)
   const swin_attn_shape_t shp = make_shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw, dropout_p, seed);
   c10::cuda::CUDAGuard guard(packed.device());
   cudaStream_t stream = at::cuda::getCurrentCUDAStream();
@@ -218,6 +219,7 @@ std::tuple<Tensor, Tensor, Tensor> bwd_cuda(const Tensor& d_o_in, const Tensor& 
   }
   const Tensor table = bias_table.detach().to(at::kFloat).contiguous();
   Tensor d_table = at::empty_like(table);
+  if (d_packed.numel() == 0) return {d_packed, d_v, at::zeros_like(bias_table)};   // empty batch
   const swin_attn_shape_t shp = make_shape(b, h, w, num_heads, window, shift, dt, impl, scale, ps, ps, v_ps, c, mask_nw, dropout_p, seed);
   c10::cuda::CUDAGuard guard(packed.device());
   cudaStream_t stream = at::cuda::getCurrentCUDAStream();
@@ -245,6 +247,7 @@ Tensor layer_norm_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& b
   const int64_t c = x.size(-1);
   Tensor out = at::empty(x.sizes(), x.options().dtype(out_bf16 ? at::kBFloat16 : at::kFloat));
   const Tensor w = weight.detach().to(at::kFloat).contiguous(), b = bias.detach().to(at::kFloat).contiguous();
+  if (x.numel() == 0) return out;
   c10::cuda::CUDAGuard guard(x.device());
   check_rc(swin_layernorm_forward(x.data_ptr(), xd, w.data_ptr<float>(), b.data_ptr<float>(), (float)eps, c ? x.numel() / c : 0,
                                   (int32_t)c, out.data_ptr(), out_bf16 ? SWIN_ATTN_BF16 : SWIN_ATTN_F32,
@@ -266,6 +269,7 @@ std::tuple<Tensor, Tensor> add_layer_norm_cuda(const Tensor& x_in, const Tensor&
   Tensor sum = at::empty_like(x);
   Tensor y = at::empty(x.sizes(), x.options().dtype(at::kBFloat16));
   const Tensor w = weight.detach().to(at::kFloat).contiguous(), b = bias.detach().to(at::kFloat).contiguous();
+  if (x.numel() == 0) return {sum, y};
   c10::cuda::CUDAGuard guard(x.device());
   check_rc(swin_add_layernorm_forward(x.data_ptr(), xd, delta.data_ptr(), w.data_ptr<float>(), b.data_ptr<float>(), (float)eps,
                                       c ? x.numel() / c : 0, (int32_t)c, sum.data_ptr(), y.data_ptr(),
@@ -281,6 +285,7 @@ Tensor gelu_cuda(const Tensor& x_in) {
   TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && x_in.numel() % 8 == 0, "swin_attn::gelu: bfloat16 with a multiple of 8 elements");
   const Tensor x = x_in.contiguous();
   Tensor y = at::empty_like(x);
+  if (x.numel() == 0) return y;
   c10::cuda::CUDAGuard guard(x.device());
   check_rc(swin_gelu_forward(x.data_ptr(), y.data_ptr(), x.numel(), at::cuda::getCurrentCUDAStream()));
   return y;
@@ -291,6 +296,7 @@ Tensor gelu_bwd_cuda(const Tensor& dy_in, const Tensor& x_in) {
   TORCH_CHECK(dy_in.sizes() == x_in.sizes(), "swin_attn::gelu_bwd: dy and x must have the same shape");
   const Tensor x = x_in.contiguous(), dy = dy_in.to(at::kBFloat16).contiguous();
   Tensor dx = at::empty_like(x);
+  if (x.numel() == 0) return dx;
   c10::cuda::CUDAGuard guard(x.device());
   check_rc(swin_gelu_backward(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), x.numel(), at::cuda::getCurrentCUDAStream()));
   return dx;
@@ -305,6 +311,7 @@ Tensor bias_grad_cuda(const Tensor& dy_in) {
               "swin_attn::bias_grad: (rows, cols) bfloat16 with cols a multiple of 8");
   const Tensor dy = dy_in.contiguous();
   Tensor out = at::empty({dy.size(1)}, dy.options().dtype(at::kFloat));
+  if (dy.numel() == 0) return out.zero_();
   c10::cuda::CUDAGuard guard(dy.device());
   check_rc(swin_linear_bias_grad(dy.data_ptr(), dy.size(0), (int32_t)dy.size(1), out.data_ptr<float>(), at::cuda::getCurrentCUDAStream()));
   return out;
@@ -328,6 +335,7 @@ std::tuple<Tensor, Tensor, Tensor> layer_norm_bwd_cuda(const Tensor& dy_in, cons
   Tensor dx = at::empty_like(x);
   const Tensor w = weight.detach().to(at::kFloat).contiguous();
   Tensor dw = at::empty_like(w), db = at::empty_like(w);
+  if (x.numel() == 0) return {dx, at::zeros_like(w), at::zeros_like(w)};
   c10::cuda::CUDAGuard guard(x.device());
   check_rc(swin_layernorm_backward(x.data_ptr(), xd, dy.data_ptr(), dtype_code(dy.scalar_type()), w.data_ptr<float>(), (float)eps,
                                    c ? x.numel() / c : 0, (int32_t)c, dx.data_ptr(), dw.data_ptr<float>(), db.data_ptr<float>(),

@@ -43,9 +43,19 @@ class DropPath(nn.Module):
     def forward(self, x):
         if self.drop_prob == 0.0 or not self.training:
             return x
+        return x * self.gate(x)   # one pass over x (timm: x.div(keep) * gate)
+
+    def gate(self, x):
+        """Per-sample scale 0 | 1/keep of shape (B, 1, ..), or None when the path is never dropped (eval, rate 0):
+        lets the caller fold the scaling into the residual add (``ops.residual``)."""
+        if self.drop_prob == 0.0 or not self.training:
+            return None
         keep = 1.0 - self.drop_prob
-        gate = x.new_empty((x.shape[0],) + (1,) * (x.ndim - 1)).bernoulli_(keep)
-        return x * (gate / keep)   # one pass over x (timm: x.div(keep) * gate)
+        return x.new_empty((x.shape[0],) + (1,) * (x.ndim - 1)).bernoulli_(keep) / keep
+
+
+def _gate(drop_path, x):
+    return drop_path.gate(x) if isinstance(drop_path, DropPath) else None
 
 
 class Mlp(nn.Module):
@@ -192,8 +202,8 @@ class CRFBlock(nn.Module):
         self.W = None
 
     def forward(self, x, v, mask_matrix=None):
-        x, pending = self.forward_parts(x, v, ops.norm_for_linear(self.norm1, x))
-        return x + pending
+        x, pending, scale = self.forward_parts(x, v, ops.norm_for_linear(self.norm1, x))
+        return ops.residual(x, pending, scale)
 
     def forward_parts(self, x, v, y):
         """The block without its last residual add: ``y`` is ``norm1(x)``; returns the stream after the attention
@@ -202,9 +212,10 @@ class CRFBlock(nn.Module):
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(y.view(b, h, w, c), v, self.shift_size)
-        x, y2 = ops.add_norm(self.norm2, x, self.drop_path(a.reshape(b, h * w, self.v_dim)))
-        return x, self.drop_path(self.mlp(y2))
+        a = self.attn.forward_image(y.view(b, h, w, c), v, self.shift_size).reshape(b, h * w, self.v_dim)
+        x, y2 = ops.add_norm(self.norm2, x, a, _gate(self.drop_path, a))
+        m = self.mlp(y2)
+        return x, m, _gate(self.drop_path, m)
 
 
 class BasicCRFLayer(nn.Module):
@@ -228,16 +239,16 @@ class BasicCRFLayer(nn.Module):
         if v.is_cuda and v.dtype == torch.float32 and torch.is_autocast_enabled() and \
                 torch.get_autocast_dtype("cuda") == torch.bfloat16:
             v = v.to(torch.bfloat16)   # the value every block's kernel reads; cast once per level instead of per block
-        pending = None
+        pending = scale = None
         for blk in self.blocks:
             blk.H, blk.W = H, W
             if pending is None:
                 y = ops.norm_for_linear(blk.norm1, x)
             else:
-                x, y = ops.add_norm(blk.norm1, x, pending)   # previous block's last residual add + this norm1
-            x, pending = blk.forward_parts(x, v, y)
+                x, y = ops.add_norm(blk.norm1, x, pending, scale)   # previous block's last residual add + this norm1
+            x, pending, scale = blk.forward_parts(x, v, y)
         if pending is not None:
-            x = x + pending
+            x = ops.residual(x, pending, scale)
         if self.downsample is not None:
             return x, H, W, self.downsample(x, H, W), (H + 1) // 2, (W + 1) // 2
         return x, H, W, x, H, W
@@ -296,17 +307,18 @@ class SwinTransformerBlock(nn.Module):
         self.W = None
 
     def forward(self, x, mask_matrix=None):
-        x, pending = self.forward_parts(x, ops.norm_for_linear(self.norm1, x))
-        return x + pending
+        x, pending, scale = self.forward_parts(x, ops.norm_for_linear(self.norm1, x))
+        return ops.residual(x, pending, scale)
 
     def forward_parts(self, x, y):
         """The block without its last residual add (see CRFBlock.forward_parts)."""
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(y.view(b, h, w, c), self.shift_size)
-        x, y2 = ops.add_norm(self.norm2, x, self.drop_path(a.reshape(b, h * w, c)))
-        return x, self.drop_path(self.mlp(y2))
+        a = self.attn.forward_image(y.view(b, h, w, c), self.shift_size).reshape(b, h * w, c)
+        x, y2 = ops.add_norm(self.norm2, x, a, _gate(self.drop_path, a))
+        m = self.mlp(y2)
+        return x, m, _gate(self.drop_path, m)
 
 
 class PatchMerging(nn.Module):
@@ -346,21 +358,21 @@ class BasicLayer(nn.Module):
         self.downsample = downsample(dim=dim, norm_layer=norm_layer) if downsample is not None else None
 
     def forward(self, x, H, W):
-        pending = None
+        pending = scale = None
         for blk in self.blocks:
             blk.H, blk.W = H, W
             if self.use_checkpoint and torch.is_grad_enabled():
                 if pending is not None:
-                    x, pending = x + pending, None
+                    x, pending = ops.residual(x, pending, scale), None
                 x = torch.utils.checkpoint.checkpoint(blk, x, None, use_reentrant=False)
                 continue
             if pending is None:
                 y = ops.norm_for_linear(blk.norm1, x)
             else:
-                x, y = ops.add_norm(blk.norm1, x, pending)   # previous block's last residual add + this norm1
-            x, pending = blk.forward_parts(x, y)
+                x, y = ops.add_norm(blk.norm1, x, pending, scale)   # previous block's last residual add + this norm1
+            x, pending, scale = blk.forward_parts(x, y)
         if pending is not None:
-            x = x + pending
+            x = ops.residual(x, pending, scale)
         if self.downsample is not None:
             return x, H, W, self.downsample(x, H, W), (H + 1) // 2, (W + 1) // 2
         return x, H, W, x, H, W

@@ -643,3 +643,27 @@ def test_linear_with_fused_bias_grad_matches_autocast_linear(shape):
     assert rel_err(gg[2], exact) <= rel_err(gw[2], exact) + 1e-6
     with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
         assert torch.equal(ops.linear(lin, x), want)          # no gradients: the module itself
+
+
+def test_empty_batch_returns_empty_tensors_and_zero_table_gradient():
+    """B = 0 (the reference's window_partition / bmm chain returns empty tensors): no launch, shapes kept, the
+    relative-position-bias table gets a zero gradient."""
+    nh, ws = 2, 7
+    c = nh * 32
+    qkv = torch.zeros(0, 14, 14, 3 * c, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    table = torch.zeros(169, nh, device=DEV, requires_grad=True)
+    before = _lib.launch_count()
+    o = ops.window_attention(qkv, None, table, ws, 3, nh)
+    assert o.shape == (0, 14, 14, c) and o.dtype == torch.bfloat16
+    g_qkv, g_table = torch.autograd.grad(o.sum(), [qkv, table])
+    assert g_qkv.shape == qkv.shape and g_table.shape == table.shape and float(g_table.abs().sum()) == 0.0
+    assert _lib.launch_count() == before
+    blk = layers.SwinTransformerBlock(c, nh, window_size=ws, shift_size=3).to(DEV).eval()
+    blk.H, blk.W = 14, 14
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        assert blk(torch.zeros(0, 196, c, device=DEV), None).shape == (0, 196, c)
+    x = torch.zeros(0, 196, c, device=DEV, requires_grad=True)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = blk.train()(x, None)                      # fused LayerNorm / GELU / Linear autograd nodes on empty inputs
+    gs = torch.autograd.grad(out.sum(), [x, blk.norm1.weight, blk.mlp.fc1.bias, blk.attn.relative_position_bias_table])
+    assert gs[0].shape == x.shape and all(float(g.abs().sum()) == 0.0 for g in gs[1:])
