@@ -111,6 +111,18 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape,
                            const void* q_pad, const void* k_pad, const void* v_pad,
                            const float* bias_table, void* o);
 
+/* Backward on UN-PADDED tensors (height / width need not be multiples of the window): the counterpart of calling
+ * swin_attn_forward with pad vectors, i.e. the autograd of pad -> Linear -> attention -> crop of the reference
+ * (newcrf_layers.py:212-217,248-249) without materialising the padded tensors.  TMA zero-fills the padding tokens, the
+ * kernel substitutes k_pad / v_pad for their K / V rows (q_pad is irrelevant: padded query rows are cropped, their
+ * gradient is zero), drops their dq / dk / dv rows and returns instead d_k_pad / d_v_pad (C fp32 each, OVERWRITTEN): the
+ * sums of dK / dV over all padding tokens, which the caller adds to the gradient of the projection bias.  k_pad / v_pad may
+ * be NULL (zero padding; then the matching d_*_pad must be NULL).  lse: (B, Hp, Wp, nH) as written by the forward.
+ * tcgen05 kernel only: bf16, window 7, shift 0 or 3, no mask, no dropout; returns an error otherwise. */
+int swin_attn_backward_unpadded(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v, const void* k_pad,
+                                const void* v_pad, const void* o, const void* d_o, const float* lse, const float* bias_table,
+                                void* dq, void* dk, void* dv, float* d_bias_table, float* d_k_pad, float* d_v_pad, void* stream);
+
 /* LayerNorm of the residual stream (fp32, or bf16 once an autocast Linear has produced it) over the last
  * dimension, in fp32 arithmetic, written as the (bf16 or fp32) operand of the following Linear: the norm1 / norm2 of the block forwards (newcrf_layers.py:207,253, swin_transformer.py:201,243)
  * fused with the casts torch.autocast inserts around it.  x: (rows, channels) of x_dtype, dense;

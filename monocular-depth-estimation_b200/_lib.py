@@ -20,6 +20,7 @@ IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05 = 0, 1, 2
 EXPORTS = (
     "swin_attn_forward",
     "swin_attn_backward",
+    "swin_attn_backward_unpadded",
     "swin_attn_forward_host",
     "swin_layernorm_forward",
     "swin_layernorm_backward",
@@ -63,6 +64,8 @@ def load() -> ctypes.CDLL:
     lib.swin_attn_forward.restype = c_int
     lib.swin_attn_backward.argtypes = [POINTER(Shape)] + [vp] * 13
     lib.swin_attn_backward.restype = c_int
+    lib.swin_attn_backward_unpadded.argtypes = [POINTER(Shape)] + [vp] * 16
+    lib.swin_attn_backward_unpadded.restype = c_int
     lib.swin_attn_forward_host.argtypes = [POINTER(Shape)] + [vp] * 8
     lib.swin_attn_forward_host.restype = c_int
     lib.swin_layernorm_forward.argtypes = [vp, c_int32, vp, vp, c_float, c_int64, c_int32, vp, c_int32, vp]

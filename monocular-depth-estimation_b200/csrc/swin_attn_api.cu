@@ -92,12 +92,14 @@ int swin_attn_forward(const swin_attn_shape_t* shape, const void* q, const void*
   return 0;
 }
 
-int swin_attn_backward(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v,
-                       const void* o, const void* d_o, const float* lse, const float* bias_table,
-                       const float* attn_mask, void* dq, void* dk, void* dv, float* d_bias_table, void* stream) {
+static int backward_impl(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v, const void* k_pad,
+                         const void* v_pad, const void* o, const void* d_o, const float* lse, const float* bias_table,
+                         const float* attn_mask, void* dq, void* dk, void* dv, float* d_bias_table, float* d_k_pad, float* d_v_pad,
+                         bool unpadded, void* stream) {
   Problem p;
   if (int rc = make_problem(shape, p)) return rc;
-  if (p.H != p.Hp || p.W != p.Wp) return fail("backward needs height and width to be multiples of the window (pad explicitly)");
+  const bool ragged = p.H != p.Hp || p.W != p.Wp;
+  if (ragged && !unpadded) return fail("backward needs height and width to be multiples of the window (pad explicitly)");
   if (!q || !k || !v || !o || !d_o || !lse || !bias_table || !dq || !dk || !dv || !d_bias_table)
     return fail("backward: all pointers must be non-null");
   if (p.o_ps != p.C) return fail("backward: o and d_o must be dense (pixel stride == C)");
@@ -106,10 +108,14 @@ int swin_attn_backward(const swin_attn_shape_t* shape, const void* q, const void
     return fail("backward: tensors must be aligned to 4 elements");
   p.q = q; p.k = k; p.v = v; p.o_in = o; p.d_o = d_o; p.lse = const_cast<float*>(lse);
   p.table = bias_table; p.dq = dq; p.dk = dk; p.dv = dv; p.d_table = d_bias_table;
+  p.k_pad = k_pad; p.v_pad = v_pad; p.d_kpad = d_k_pad; p.d_vpad = d_v_pad;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_backward_supported(p, shape->dtype);
   if (shape->impl == SWIN_ATTN_IMPL_TCGEN05 && !want_tc) return fail("tcgen05 backward does not support this shape/dtype");
+  if (ragged && !want_tc)
+    return fail("backward on un-padded tensors needs the tcgen05 kernel (bf16, window 7, shift 0 or 3, no mask, no dropout, 16-byte "
+                "aligned tensors); pad explicitly otherwise");
   if (want_tc) {
     const char* why = nullptr;
     cudaError_t e = launch_tc_backward(p, st, &why);
@@ -119,6 +125,22 @@ int swin_attn_backward(const swin_attn_shape_t* shape, const void* q, const void
   cudaError_t e = launch_simt_backward(p, shape->dtype, st);
   if (e != cudaSuccess) return fail_cuda("backward launch", e);
   return 0;
+}
+
+int swin_attn_backward(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v,
+                       const void* o, const void* d_o, const float* lse, const float* bias_table,
+                       const float* attn_mask, void* dq, void* dk, void* dv, float* d_bias_table, void* stream) {
+  return backward_impl(shape, q, k, v, nullptr, nullptr, o, d_o, lse, bias_table, attn_mask, dq, dk, dv, d_bias_table, nullptr, nullptr,
+                       false, stream);
+}
+
+int swin_attn_backward_unpadded(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v, const void* k_pad,
+                                const void* v_pad, const void* o, const void* d_o, const float* lse, const float* bias_table,
+                                void* dq, void* dk, void* dv, float* d_bias_table, float* d_k_pad, float* d_v_pad, void* stream) {
+  if ((k_pad != nullptr) != (d_k_pad != nullptr) || (v_pad != nullptr) != (d_v_pad != nullptr))
+    return fail("backward (un-padded): d_k_pad / d_v_pad must be given exactly when k_pad / v_pad are");
+  return backward_impl(shape, q, k, v, k_pad, v_pad, o, d_o, lse, bias_table, nullptr, dq, dk, dv, d_bias_table, d_k_pad, d_v_pad, true,
+                       stream);
 }
 
 // Device scratch for the host-buffer entry point; grown on demand, reused.

@@ -47,49 +47,6 @@ __device__ __forceinline__ uint32_t q_off(int t) { return t * kTileBytes; }
 __device__ __forceinline__ uint32_t k_off(int t) { return 2 * kTileBytes + t * kKTile1; }   // in a QK stage
 __device__ __forceinline__ uint32_t v_off(int t) { return t * kTileBytes; }                    // in a V stage
 
-// Padding tokens (y >= H or x >= W) can only occur in the last two window rows / columns: their tile-row bit sets,
-// for window row nWy-2 ([0]) and nWy-1 ([1]), likewise for columns.
-template <bool kPerm>
-struct PadSets {
-  uint64_t y[2], x[2];
-  __device__ __forceinline__ void init(const Problem& p) {
-    y[0] = y[1] = x[0] = x[1] = 0;
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-#pragma unroll
-      for (int i = 0; i < WS; ++i) {
-        int yy = (p.nWy - 2 + e) * WS + i + p.shift, xx = (p.nWx - 2 + e) * WS + i + p.shift;
-        if (yy >= p.Hp) yy -= p.Hp;
-        if (xx >= p.Wp) xx -= p.Wp;
-        if (yy >= p.H && p.nWy - 2 + e >= 0) y[e] |= rows_of_window_row<kPerm>(i);
-        if (xx >= p.W && p.nWx - 2 + e >= 0) x[e] |= rows_of_window_col<kPerm>(i);
-      }
-    }
-  }
-  __device__ __forceinline__ uint64_t of(const Problem& p, int wy, int wx) const {
-    return (wy == p.nWy - 1 ? y[1] : wy == p.nWy - 2 ? y[0] : 0) | (wx == p.nWx - 1 ? x[1] : wx == p.nWx - 2 ? x[0] : 0);
-  }
-};
-
-// Pad tokens carry the projection bias (the reference pads before the Linear), but TMA zero-fills them: after a
-// K / V tile has landed, the issuing warp overwrites the rows of its pad tokens with the head's pad vector, so the
-// S and PV MMAs see exactly the reference's operands and the softmax needs no pad handling at all.  `vec` holds the
-// 64 bytes of the vector (4 x 16 B); rows are 64 B with the 64B swizzle of the TMA box.
-__device__ __forceinline__ void write_pad_rows(uint32_t tile, uint64_t padded, const uint4 (&vec)[4], int lane) {
-#pragma unroll
-  for (int r0 = 0; r0 < 64; r0 += 32) {
-    const int r = r0 + lane;
-    if (r < N && ((padded >> r) & 1)) {
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const uint32_t dst = tile + r * 64 + ((c ^ ((r >> 1) & 3)) << 4);
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(vec[c].x), "r"(vec[c].y), "r"(vec[c].z), "r"(vec[c].w)
-                     : "memory");
-      }
-    }
-  }
-}
-
 struct TmaMapsF {
   CUtensorMap q[7], k[7], v[7];   // loads
   CUtensorMap o[7];               // stores

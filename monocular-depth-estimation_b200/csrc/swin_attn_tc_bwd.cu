@@ -61,7 +61,7 @@ struct TmaMapsB {
 };
 
 struct SmemMapB {
-  uint32_t stages, slots, ident, bias, bins, bars, tmem_ptr, total;
+  uint32_t stages, slots, ident, bias, bins, padacc, bars, tmem_ptr, total;
 };
 __host__ __device__ inline SmemMapB smem_map_b() {
   SmemMapB m;
@@ -70,7 +70,8 @@ __host__ __device__ inline SmemMapB smem_map_b() {
   m.ident = m.slots + kSlotsB * kSlotBytes;
   m.bias = m.ident + kPTileBytes;
   m.bins = m.bias + 176 * 4;
-  m.bars = m.bins + 176 * 4;
+  m.padacc = (m.bins + 176 * 4 + 15) & ~15u;   // [slot][tile][dK | dV][32] fp32: sums over padding tokens (un-padded mode)
+  m.bars = m.padacc + kSlotsB * 2 * 64 * 4;
   m.tmem_ptr = m.bars + 8 * (2 * kStagesB + 4 * kSlotsB);
   m.total = m.tmem_ptr + 16;
   return m;
@@ -78,7 +79,7 @@ __host__ __device__ inline SmemMapB smem_map_b() {
 
 template <bool kShifted>
 __global__ void __launch_bounds__(kThreadsB, 1)
-tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant__ TmaMapsB maps) {
+tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __grid_constant__ TmaMapsB maps) {
   constexpr bool kPerm = kShifted;
   extern __shared__ __align__(1024) unsigned char smem[];
   const SmemMapB map = smem_map_b();
@@ -143,6 +144,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
       reinterpret_cast<float*>(smem + map.bias)[t10] = bias_v;
       reinterpret_cast<float*>(smem + map.bins)[t10] = 0.f;
     }
+    if (t10 < kSlotsB * 2 * 64) reinterpret_cast<float*>(smem + map.padacc)[t10] = 0.f;
     fence_proxy_async();
     tc_fence_before();
     named_barrier(5, kFill);
@@ -185,12 +187,41 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
   } else if (warp == 1) {
     // ===== phase 1: S = Q K^T, dP = dO V^T ======================================================
     constexpr uint32_t idesc = instr_desc(128, 112, 0);
+    // Un-padded mode (H, W not multiples of the window): TMA zero-fills the padding tokens, which carry the projection
+    // bias in the reference; their K / V rows are overwritten with k_pad / v_pad once the tiles have landed.
+    const bool fix = has_pad && (p.k_pad != nullptr || p.v_pad != nullptr);
+    PadSets<kPerm> pads;
+    uint4 kvec[4] = {}, vvec[4] = {};
+    WinIter it;
+    it.init(p, w0);
+    if (fix) {
+      pads.init(p);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        if (p.k_pad != nullptr) kvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.k_pad) + h * kHeadDim)[c];
+        if (p.v_pad != nullptr) vvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.v_pad) + h * kHeadDim)[c];
+      }
+    }
     for (int n = 0; n < n_pairs; ++n) {
       const int s = n % kStagesB, a = n % kSlotsB;
+      const uint32_t st = sbase + map.stages + s * kStageBytesB;
       mbar_wait(bar_full + 8 * s, (n / kStagesB) & 1);
+      if (fix) {
+        const uint64_t pad0 = pads.of(p, it.wy, it.wx);
+        it.advance(p, 1);
+        const uint64_t pad1 = it.w < w1 ? pads.of(p, it.wy, it.wx) : 0;
+        it.advance(p, 1);
+        if (pad0 | pad1) {
+          write_pad_rows(st + bk_off(0), pad0, kvec, lane);
+          write_pad_rows(st + bk_off(1), pad1, kvec, lane);
+          write_pad_rows(st + bv_off(0), pad0, vvec, lane);
+          write_pad_rows(st + bv_off(1), pad1, vvec, lane);
+          fence_proxy_async();
+        }
+        __syncwarp();
+      }
       mbar_wait(bar_r + 8 * a, ((n / kSlotsB) & 1) ^ 1);
       tc_fence_after();
-      const uint32_t st = sbase + map.stages + s * kStageBytesB;
       const uint32_t d = tmem_base + a * kSlotColsB;
       const uint64_t qd = smem_desc(st + bq_off(0), 16, 512, 4), kd = smem_desc(st + bk_off(0), 16, 512, 4);
       const uint64_t gd = smem_desc(st + bdo_off(0), 16, 512, 4), vd = smem_desc(st + bv_off(0), 16, 512, 4);
@@ -256,6 +287,10 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
 #pragma unroll
       for (int j = WS - kShift; j < WS; ++j) wb |= rows_of_window_col<kPerm>(j);
     }
+    PadSets<kPerm> pads;
+    if (has_pad) pads.init(p);
+    // one owner thread (row 49) per slot and tile: plain read-modify-write, no atomics
+    float4* padacc = reinterpret_cast<float4*>(smem + map.padacc) + (g * 2 + sel) * 16;
     const uint32_t sl = sbase + map.slots + g * kSlotBytes;
     const uint32_t p_row = sl + sel * kPTileBytes + row * 128;
     const uint32_t ds_row = p_row + 2 * kPTileBytes;
@@ -272,8 +307,13 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
       int y = it.wy * WS + ri + p.shift, x = it.wx * WS + rj + p.shift;
       if (y >= p.Hp) y -= p.Hp;
       if (x >= p.Wp) x -= p.Wp;
+      // padding tokens of this tile (un-padded mode): as QUERY rows they get P = 0 (lse = +inf: their output was
+      // cropped, the forward's lse there is unspecified); as KEY columns their dS / P mass is summed into column 49,
+      // so that row 49 of the dK / dV products is the gradient of k_pad / v_pad (rows 49+ of K, Q, dO tiles are zero).
+      const uint64_t padded = has_pad && valid ? pads.of(p, it.wy, it.wx) : 0;
+      const bool row_pad = (padded >> rowc) & 1;
       float lse2 = 0.f;
-      if (valid && row < N) lse2 = p.lse[((int64_t)(it.b * p.Hp + y) * p.Wp + x) * p.nH + h] * kLog2e;
+      if (valid && row < N) lse2 = row_pad ? INFINITY : p.lse[((int64_t)(it.b * p.Hp + y) * p.Wp + x) * p.nH + h] * kLog2e;
       uint64_t masked = 0;
       if (kShifted) {
         const uint64_t hm = it.wy == p.nWy - 1 ? hb : 0, wm = it.wx == p.nWx - 1 ? wb : 0;
@@ -338,8 +378,20 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
       }
       {
         const float pl = __uint_as_float(r[N - 1]);
-        wp[24] = live ? pack_bf16(pl, 0.f) : 0u;
-        wd[24] = live ? pack_bf16(pl * (__uint_as_float(d[N - 1]) - delta), 0.f) : 0u;
+        const float dl = pl * (__uint_as_float(d[N - 1]) - delta);
+        float u_pad = 0.f, s_pad = 0.f;
+        if (padded != 0) {   // warp-uniform
+#pragma unroll
+          for (int j = 0; j < N; ++j) {
+            if ((padded >> j) & 1) {
+              const float pj = __uint_as_float(r[j]);
+              u_pad += pj;
+              s_pad = fmaf(pj, __uint_as_float(d[j]) - delta, s_pad);
+            }
+          }
+        }
+        wp[24] = live ? pack_bf16(pl, u_pad) : 0u;
+        wd[24] = live ? pack_bf16(dl, s_pad) : 0u;
       }
       // the TMA stores of this warpgroup's previous pair must have finished reading the staging tiles
       // (same bytes as P / dS) before they are overwritten
@@ -370,6 +422,17 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
         tmem_ld_wait();
         const float sc = t3 < 2 ? p.scale : 1.0f;
         const float2 sc2 = make_float2(sc, sc);
+        if (t3 > 0 && row == N && padded != 0) {   // row 49 of dK / dV = this tile's gradient of k_pad / v_pad
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            float4 a = padacc[(t3 - 1) * 8 + c];
+            a.x = fmaf(__uint_as_float(o[4 * c]), sc, a.x);
+            a.y = fmaf(__uint_as_float(o[4 * c + 1]), sc, a.y);
+            a.z = fmaf(__uint_as_float(o[4 * c + 2]), sc, a.z);
+            a.w = fmaf(__uint_as_float(o[4 * c + 3]), sc, a.w);
+            padacc[(t3 - 1) * 8 + c] = a;
+          }
+        }
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
           uint32_t v[4];
@@ -420,6 +483,15 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant
       }
       named_barrier(4, 128);
       for (int i = tid - 128; i < 169; i += 128) atomicAdd(&p.d_table[i * p.nH + h], bins[i]);
+      // (the named barrier over both warpgroups above also ordered every padacc update before these reads)
+      if (has_pad && tid - 128 < 64) {
+        float* dst = tid - 128 < 32 ? p.d_kpad : p.d_vpad;
+        const float* acc = reinterpret_cast<const float*>(smem + map.padacc) + (tid - 128);
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < kSlotsB * 2; ++i) sum += acc[i * 64];
+        if (dst != nullptr) atomicAdd(&dst[h * kHeadDim + ((tid - 128) & 31)], sum);
+      }
     }
   }
 
@@ -435,10 +507,10 @@ bool tc_backward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
   if (p.dropout_p > 0.0f) return false;   // attention dropout (unused by NewCRFs) is served by the CUDA-core kernels
   if (p.shift != 0 && p.shift != tc::kShift) return false;
-  if (p.H != p.Hp || p.W != p.Wp) return false;
+  // un-padded tensors (H, W not multiples of the window) are served here and only here: TMA zero fill + pad vectors
   if ((p.q_ps | p.k_ps | p.v_ps | p.C) & 7) return false;
   auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
-  if (mis(p.q) || mis(p.k) || mis(p.v) || mis(p.d_o) || mis(p.dq) || mis(p.dk) || mis(p.dv)) return false;
+  if (mis(p.q) || mis(p.k) || mis(p.v) || mis(p.d_o) || mis(p.dq) || mis(p.dk) || mis(p.dv) || mis(p.k_pad) || mis(p.v_pad)) return false;
   return tc::tma_available();
 }
 
@@ -468,7 +540,10 @@ cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** e
   tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
   e = cudaMemsetAsync(p.d_table, 0, sizeof(float) * 169 * p.nH, st);
   if (e != cudaSuccess) return e;
-  kernel<<<grid, tcb::kThreadsB, map.total, st>>>(p, n_win, per, maps);
+  const int has_pad = (p.H != p.Hp || p.W != p.Wp) ? 1 : 0;
+  if (p.d_kpad != nullptr && (e = cudaMemsetAsync(p.d_kpad, 0, sizeof(float) * p.C, st)) != cudaSuccess) return e;
+  if (p.d_vpad != nullptr && (e = cudaMemsetAsync(p.d_vpad, 0, sizeof(float) * p.C, st)) != cudaSuccess) return e;
+  kernel<<<grid, tcb::kThreadsB, map.total, st>>>(p, n_win, per, has_pad, maps);
   count_launch();
   return cudaGetLastError();
 }

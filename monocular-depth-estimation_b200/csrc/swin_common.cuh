@@ -30,6 +30,8 @@ struct Problem {
   void* dk;
   void* dv;
   float* d_table;
+  float* d_kpad;       // (C) fp32 or null: gradient of k_pad / v_pad (sum of dK / dV over the padding tokens) when
+  float* d_vpad;       //   the backward runs on un-padded tensors (tcgen05 kernel only)
   long long* trace;    // debug: per-pair clock64 stamps of CTA 0 (tcgen05 kernel), or null
   int B, H, W, Hp, Wp, nH, C, ws, shift;
   int nWy, nWx;        // windows per column / row of the padded image

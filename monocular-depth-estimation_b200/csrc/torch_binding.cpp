@@ -240,6 +240,85 @@ std::tuple<Tensor, Tensor, Tensor> bwd_meta(const Tensor&, const Tensor& packed,
   return {d_packed, d_v, at::empty_like(bias_table)};
 }
 
+// ---- swin_attn::bwd_unpadded: backward on un-padded tensors, pad vectors as differentiable inputs ------------------
+std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor> bwd_unpadded_cuda(const Tensor& d_o_in, const Tensor& packed_in, const optional<Tensor>& v_in,
+                                                                     const Tensor& o_in, const Tensor& lse, const Tensor& bias_table,
+                                                                     const optional<Tensor>& packed_pad_in, const optional<Tensor>& v_pad_in,
+                                                                     int64_t window, int64_t shift, int64_t num_heads, double scale) {
+  TORCH_CHECK(window > 0, "swin_attn: window must be positive");
+  const int64_t c = split_channels(packed_in, v_in, num_heads);
+  Tensor packed = image_layout(packed_in);
+  const auto dt = packed.scalar_type();
+  dtype_code(dt);
+  const int64_t b = packed.size(0), h = packed.size(1), w = packed.size(2), pc = packed.size(3);
+  const int64_t es = packed.element_size();
+  Tensor v;
+  if (v_in.has_value()) v = image_layout(v_in->to(dt));
+  if (packed.stride(2) != pc) packed = packed.contiguous();
+  if (v.defined() && v.stride(2) != c) v = v.contiguous();
+  const Tensor d_o = d_o_in.to(dt).contiguous();
+  const Tensor o = o_in.contiguous();
+  Tensor d_packed = at::empty({b, h, w, pc}, packed.options());
+  Tensor d_v = v.defined() ? at::empty({b, h, w, c}, packed.options()) : at::empty({0}, packed.options());
+  const Tensor table = bias_table.detach().to(at::kFloat).contiguous();
+  Tensor d_table = at::empty_like(table);
+  // pad vectors: k_pad = packed_pad[C:2C]; v_pad = packed_pad[2C:3C] (fused qkv) or the separate v_pad (external v)
+  Tensor packed_pad, v_pad, d_packed_pad, d_v_pad;
+  const char *kpad = nullptr, *vpad = nullptr;
+  float *d_kpad = nullptr, *d_vpad = nullptr;
+  const auto fopt = packed.options().dtype(at::kFloat);
+  if (packed_pad_in.has_value()) {
+    TORCH_CHECK(packed_pad_in->numel() == pc, "swin_attn: packed_pad must have ", pc, " elements");
+    packed_pad = packed_pad_in->detach().to(dt).contiguous();
+    d_packed_pad = at::zeros({pc}, fopt);
+    kpad = byte_ptr(packed_pad) + c * es;
+    d_kpad = d_packed_pad.data_ptr<float>() + c;
+    if (!v.defined()) {
+      vpad = byte_ptr(packed_pad) + 2 * c * es;
+      d_vpad = d_packed_pad.data_ptr<float>() + 2 * c;
+    }
+  } else {
+    d_packed_pad = at::empty({0}, fopt);
+  }
+  if (v.defined() && v_pad_in.has_value()) {
+    TORCH_CHECK(v_pad_in->numel() == c, "swin_attn: v_pad must have ", c, " elements");
+    v_pad = v_pad_in->detach().to(dt).contiguous();
+    d_v_pad = at::zeros({c}, fopt);
+    vpad = byte_ptr(v_pad);
+    d_vpad = d_v_pad.data_ptr<float>();
+  } else {
+    d_v_pad = at::empty({0}, fopt);
+  }
+  if (d_packed.numel() == 0) return {d_packed, d_v, at::zeros_like(bias_table), d_packed_pad, d_v_pad};
+  const int64_t ps = packed.stride(2);
+  const char* base = byte_ptr(packed);
+  char* dbase = static_cast<char*>(d_packed.data_ptr());
+  const char* v_ptr = v.defined() ? byte_ptr(v) : base + 2 * c * es;
+  char* dv_ptr = v.defined() ? static_cast<char*>(d_v.data_ptr()) : dbase + 2 * c * es;
+  const int64_t v_ps = v.defined() ? v.stride(2) : ps;
+  const swin_attn_shape_t shp = make_shape(b, h, w, num_heads, window, shift, dt, SWIN_ATTN_IMPL_AUTO, scale, ps, ps, v_ps, c, 0, 0.0, 0);
+  c10::cuda::CUDAGuard guard(packed.device());
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  TimedLaunch timed(stream);
+  check_rc(swin_attn_backward_unpadded(&shp, base, base + c * es, v_ptr, kpad, vpad, o.data_ptr(), d_o.data_ptr(), lse.data_ptr<float>(),
+                                       table.data_ptr<float>(), dbase, dbase + c * es, dv_ptr, d_table.data_ptr<float>(), d_kpad, d_vpad,
+                                       stream));
+  timed.finish(7 * b * h * w * c * es + lse.numel() * 4, 10 * b * lse.size(1) * lse.size(2) * window * window * c, 1, window, shift, num_heads, h, w);
+  return {d_packed, d_v, d_table.to(bias_table.scalar_type()), d_packed_pad, d_v_pad};
+}
+
+std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor> bwd_unpadded_meta(const Tensor&, const Tensor& packed, const optional<Tensor>& v, const Tensor&,
+                                                                     const Tensor&, const Tensor& bias_table,
+                                                                     const optional<Tensor>& packed_pad, const optional<Tensor>& v_pad, int64_t,
+                                                                     int64_t, int64_t, double) {
+  const auto fopt = packed.options().dtype(at::kFloat);
+  Tensor d_packed = at::empty_symint(packed.sym_sizes(), packed.options());
+  Tensor d_v = v.has_value() ? at::empty_symint(v->sym_sizes(), packed.options()) : at::empty({0}, packed.options());
+  Tensor dpp = packed_pad.has_value() ? at::empty_symint({packed.sym_size(3)}, fopt) : at::empty({0}, fopt);
+  Tensor dvp = v.has_value() && v_pad.has_value() ? at::empty_symint({v->sym_size(3)}, fopt) : at::empty({0}, fopt);
+  return {d_packed, d_v, at::empty_like(bias_table), dpp, dvp};
+}
+
 // ---- swin_attn::layer_norm / layer_norm_bwd ------------------------------------------------------------------
 Tensor layer_norm_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& bias, double eps, bool out_bf16) {
   const int32_t xd = dtype_code(x_in.scalar_type());
@@ -366,6 +445,13 @@ inline auto bwd_op() {
   static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::bwd", "").typed<BwdSig>();
   return op;
 }
+using BwdUnpaddedSig = std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor>(const Tensor&, const Tensor&, const optional<Tensor>&, const Tensor&,
+                                                                          const Tensor&, const Tensor&, const optional<Tensor>&,
+                                                                          const optional<Tensor>&, int64_t, int64_t, int64_t, double);
+inline auto bwd_unpadded_op() {
+  static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::bwd_unpadded", "").typed<BwdUnpaddedSig>();
+  return op;
+}
 inline auto ln_op() {
   static auto op = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::layer_norm", "").typed<LnSig>();
   return op;
@@ -386,14 +472,20 @@ struct AttnFunction : public torch::autograd::Function<AttnFunction> {
                              dropout_p, seed);
     const Tensor& o = std::get<0>(out);
     const Tensor& lse = std::get<1>(out);
-    ctx->save_for_backward({packed, v.has_value() ? *v : Tensor(), o, lse, bias_table, attn_mask.has_value() ? *attn_mask : Tensor()});
+    ctx->save_for_backward({packed, v.has_value() ? *v : Tensor(), o, lse, bias_table, attn_mask.has_value() ? *attn_mask : Tensor(),
+                            packed_pad.has_value() ? *packed_pad : Tensor(), v_pad.has_value() ? *v_pad : Tensor()});
     ctx->saved_data["window"] = window;
     ctx->saved_data["shift"] = shift;
     ctx->saved_data["heads"] = num_heads;
     ctx->saved_data["scale"] = scale;
     ctx->saved_data["dropout_p"] = dropout_p;
     ctx->saved_data["seed"] = seed;
-    ctx->saved_data["ok"] = need_lse && packed.size(1) % window == 0 && packed.size(2) % window == 0;
+    const bool aligned = packed.size(1) % window == 0 && packed.size(2) % window == 0;
+    // un-padded tensors: the tcgen05 backward takes them with the pad vectors (swin_attn_backward_unpadded)
+    const bool unpadded_ok = !aligned && packed.scalar_type() == at::kBFloat16 && window == 7 && (shift == 0 || shift == 3) &&
+                             !attn_mask.has_value() && dropout_p == 0.0;
+    ctx->saved_data["ok"] = need_lse && (aligned || unpadded_ok);
+    ctx->saved_data["unpadded"] = !aligned;
     ctx->mark_non_differentiable({lse});
     return {o, lse};
   }
@@ -404,6 +496,20 @@ struct AttnFunction : public torch::autograd::Function<AttnFunction> {
                 "multiples of the window (the layers pad explicitly whenever gradients are enabled)");
     const auto saved = ctx->get_saved_variables();
     const Tensor &packed = saved[0], &v = saved[1], &o = saved[2], &lse = saved[3], &table = saved[4], &mask = saved[5];
+    if (ctx->saved_data["unpadded"].toBool()) {
+      const Tensor &packed_pad = saved[6], &v_pad = saved[7];
+      auto out = bwd_unpadded_op().call(grads[0], packed, v.defined() ? optional<Tensor>(v) : c10::nullopt, o, lse, table,
+                                        packed_pad.defined() ? optional<Tensor>(packed_pad) : c10::nullopt,
+                                        v_pad.defined() ? optional<Tensor>(v_pad) : c10::nullopt, ctx->saved_data["window"].toInt(),
+                                        ctx->saved_data["shift"].toInt(), ctx->saved_data["heads"].toInt(),
+                                        ctx->saved_data["scale"].toDouble());
+      Tensor d_v, d_pp, d_vp;
+      if (v.defined()) d_v = std::get<1>(out).to(v.scalar_type());
+      if (packed_pad.defined()) d_pp = std::get<3>(out).to(packed_pad.scalar_type()).view(packed_pad.sizes());
+      if (v.defined() && v_pad.defined()) d_vp = std::get<4>(out).to(v_pad.scalar_type()).view(v_pad.sizes());
+      return {std::get<0>(out), d_v, std::get<2>(out), d_pp, d_vp, Tensor(), Tensor(), Tensor(), Tensor(), Tensor(), Tensor(),
+              Tensor(), Tensor(), Tensor()};
+    }
     auto out = bwd_op().call(grads[0], packed, v.defined() ? optional<Tensor>(v) : c10::nullopt, o, lse, table,
                              ctx->saved_data["window"].toInt(), ctx->saved_data["shift"].toInt(), ctx->saved_data["heads"].toInt(),
                              ctx->saved_data["scale"].toDouble(), mask.defined() ? optional<Tensor>(mask) : c10::nullopt,
@@ -505,6 +611,8 @@ TORCH_LIBRARY(swin_attn, m) {
   m.def("bwd(Tensor d_o, Tensor packed, Tensor? v, Tensor o, Tensor lse, Tensor bias_table, int window, int shift, "
         "int num_heads, float scale, Tensor? attn_mask=None, int impl=0, float dropout_p=0.0, int seed=0) "
         "-> (Tensor, Tensor, Tensor)");
+  m.def("bwd_unpadded(Tensor d_o, Tensor packed, Tensor? v, Tensor o, Tensor lse, Tensor bias_table, Tensor? packed_pad, "
+        "Tensor? v_pad, int window, int shift, int num_heads, float scale) -> (Tensor, Tensor, Tensor, Tensor, Tensor)");
   m.def("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps, bool out_bf16) -> Tensor");
   m.def("layer_norm_bwd(Tensor dy, Tensor x, Tensor weight, float eps) -> (Tensor, Tensor, Tensor)");
   m.def("add_layer_norm(Tensor x, Tensor delta, Tensor weight, Tensor bias, float eps) -> (Tensor, Tensor)");
@@ -517,6 +625,7 @@ TORCH_LIBRARY(swin_attn, m) {
 TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("fwd", fwd_cuda);
   m.impl("bwd", bwd_cuda);
+  m.impl("bwd_unpadded", bwd_unpadded_cuda);
   m.impl("layer_norm", layer_norm_cuda);
   m.impl("layer_norm_bwd", layer_norm_bwd_cuda);
   m.impl("add_layer_norm", add_layer_norm_cuda);
@@ -529,6 +638,7 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
 TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("fwd", fwd_meta);
   m.impl("bwd", bwd_meta);
+  m.impl("bwd_unpadded", bwd_unpadded_meta);
   m.impl("layer_norm", layer_norm_meta);
   m.impl("layer_norm_bwd", layer_norm_bwd_meta);
   m.impl("add_layer_norm", add_layer_norm_meta);

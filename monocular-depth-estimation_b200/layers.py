@@ -102,6 +102,13 @@ class _WindowAttentionBase(nn.Module):
         nn.init.trunc_normal_(self.relative_position_bias_table, std=0.02)
         self.softmax = nn.Softmax(dim=-1)  # kept for module-tree parity; the kernel does the softmax
 
+    def _fused_pad_backward(self, shift):
+        """True when the tcgen05 backward takes un-padded tensors (bf16 autocast, window 7, shift 0 / 3, no attention
+        dropout): training then runs the same call as inference -- no F.pad before the Linear, no crop after the
+        attention -- and the gradient of the pad tokens reaches the Linear bias through the op's ``packed_pad`` input."""
+        return (self.window_size[0] == 7 and shift in (0, 3) and self._drop_p() == 0.0 and torch.is_autocast_enabled()
+                and torch.get_autocast_dtype("cuda") == torch.bfloat16)
+
     def _drop_p(self):
         return self.attn_drop.p if self.training else 0.0
 
@@ -132,8 +139,8 @@ class WindowAttention(_WindowAttentionBase):
         tokens take the Linear bias for q/k and zero for v, as in the reference
         where ``F.pad`` precedes the Linear (newcrf_layers.py:212-216)."""
         ws = self.window_size[0]
-        if torch.is_grad_enabled() and (x_img.requires_grad or v_img.requires_grad or
-                                        self.relative_position_bias_table.requires_grad):
+        if torch.is_grad_enabled() and not self._fused_pad_backward(shift) and (
+                x_img.requires_grad or v_img.requires_grad or self.relative_position_bias_table.requires_grad):
             h, w = x_img.shape[1:3]
             pb, pr = (-h) % ws, (-w) % ws
             if pb or pr:
@@ -165,7 +172,8 @@ class EncoderWindowAttention(_WindowAttentionBase):
 
     def forward_image(self, x_img, shift):
         ws = self.window_size[0]
-        if torch.is_grad_enabled() and (x_img.requires_grad or self.relative_position_bias_table.requires_grad):
+        if torch.is_grad_enabled() and not self._fused_pad_backward(shift) and (
+                x_img.requires_grad or self.relative_position_bias_table.requires_grad):
             h, w = x_img.shape[1:3]
             pb, pr = (-h) % ws, (-w) % ws
             if pb or pr:

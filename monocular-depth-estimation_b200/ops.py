@@ -172,7 +172,8 @@ def window_attention(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, wi
     if scale is None:
         scale = 32 ** -0.5
     need_grad = torch.is_grad_enabled() and (
-        packed.requires_grad or bias_table.requires_grad or (v is not None and v.requires_grad))
+        packed.requires_grad or bias_table.requires_grad or (v is not None and v.requires_grad)
+        or (packed_pad is not None and packed_pad.requires_grad) or (v_pad is not None and v_pad.requires_grad))
     if dropout_p > 0.0 and seed is None:
         seed = int(torch.randint(0, 2 ** 62, (1,)).item())   # CPU generator: reproducible under torch.manual_seed, no sync
     o, _ = torch.ops.swin_attn.fwd(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads,

@@ -667,3 +667,45 @@ def test_empty_batch_returns_empty_tensors_and_zero_table_gradient():
         out = blk.train()(x, None)                      # fused LayerNorm / GELU / Linear autograd nodes on empty inputs
     gs = torch.autograd.grad(out.sum(), [x, blk.norm1.weight, blk.mlp.fc1.bias, blk.attn.relative_position_bias_table])
     assert gs[0].shape == x.shape and all(float(g.abs().sum()) == 0.0 for g in gs[1:])
+
+
+UNPADDED_BWD_CASES = [  # ws, shift, B, H, W, nH, external_v : H or W not a multiple of the window
+    (7, 3, 2, 22, 44, 6, False), (7, 0, 2, 16, 23, 2, True), (7, 3, 1, 9, 11, 4, True), (7, 3, 1, 1, 1, 2, False),
+    (7, 0, 3, 30, 40, 3, False), (7, 3, 2, 15, 20, 48, False), (7, 0, 1, 8, 7, 1, True),
+]
+
+
+@pytest.mark.parametrize("case", UNPADDED_BWD_CASES)
+def test_backward_on_unpadded_tensors_matches_oracle_autograd(case):
+    """swin_attn_backward_unpadded (training without F.pad / crop): gradients of the packed projection, v, the bias
+    table AND the pad vectors (= what reaches the Linear bias through the padding tokens in the reference,
+    newcrf_layers.py:212-217) against fp64 autograd through the oracle with explicit padding."""
+    ws, shift, b, h, w, nh, ext = case
+    c = nh * 32
+    name = f"ubwd{case}"
+    packed = randn(name + ".p", b, h, w, (2 if ext else 3) * c).bfloat16()
+    v = randn(name + ".v", b, h, w, c).bfloat16() if ext else None
+    table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
+    pads = (0.3 * randn(name + ".pad", (2 if ext else 3) * c)).bfloat16().float()   # a Linear bias (fp32 parameter)
+    cot = randn(name + ".c", b, h, w, c).bfloat16()
+    pr = packed.double().requires_grad_()
+    vr = None if v is None else v.double().requires_grad_()
+    tr = table.double().requires_grad_()
+    dr = pads.double().requires_grad_()
+    o_ref, _ = wa.window_attention(pr[..., :c], pr[..., c:2 * c], pr[..., 2 * c:] if v is None else vr, tr, ws, shift, nh, None,
+                                   dr[:c], dr[c:2 * c], dr[2 * c:] if v is None else None)
+    ins = [pr, tr, dr] + ([] if v is None else [vr])
+    g_ref = torch.autograd.grad((o_ref * cot.double()).sum(), ins)
+    pg = packed.to(DEV).requires_grad_()
+    vg = None if v is None else v.to(DEV).requires_grad_()
+    tg = table.to(DEV).requires_grad_()
+    dg = pads.to(DEV).requires_grad_()
+    o = ops.window_attention(pg, vg, tg, ws, shift, nh, packed_pad=dg)
+    assert o.shape == (b, h, w, c) and rel_err(o.float(), o_ref) < TOL_BF16
+    g = torch.autograd.grad((o.float() * cot.to(DEV).float()).sum(), [pg, tg, dg] + ([] if v is None else [vg]))
+    for got, want, what in zip(g, g_ref, ["d_packed", "d_table", "d_pad", "d_v"]):
+        assert got.shape == want.shape and got.dtype == (torch.bfloat16 if what in ("d_packed", "d_v") else torch.float32)
+        assert rel_err(got.float(), want) < TOL_BF16, what
+    assert float(g[2][:c].abs().max()) == 0.0          # padded QUERY rows are cropped: no gradient reaches q_pad
+    if h % ws or w % ws:
+        assert float(g_ref[2][c:].abs().max()) > 0.0   # ... but the padded keys / values do carry gradient
