@@ -154,7 +154,8 @@ def _adaptive_avg_pool_small(x, out_size):
         # (n, hw, c) is a free view of a channels-last feature; one batched (s*s, hw) x (hw, c) product
         tokens = x.permute(0, 2, 3, 1).reshape(n, h * w, c).float()
         pooled = torch.matmul(k.t(), tokens)                       # (n, s*s, c)
-        return pooled.transpose(1, 2).reshape(n, c, s[0], s[1]).to(x.dtype)
+        # dense NCHW: the 1x1 conv behind it then returns a dense weight gradient (DDP bucket views want that)
+        return pooled.transpose(1, 2).reshape(n, c, s[0], s[1]).to(x.dtype).contiguous()
 
 
 class PSP(nn.Module):
