@@ -107,13 +107,42 @@ def test_block_plumbing_entries_validate_without_gpu():
     assert lib.swin_layernorm_backward(ptr, _lib.F32, ptr, _lib.BF16, ptr, 1e-5, 1, 3072, ptr, ptr, ptr, None) != 0
 
 
+def test_backward_unpadded_entry_validates_without_gpu():
+    """swin_attn_backward_unpadded: pad-gradient outputs must mirror the pad inputs; ragged shapes are accepted by the
+    argument checks of this entry (and only this one); fp32 cannot be served (CUDA-core kernels need explicit padding)."""
+    lib = _lib.load()
+    buf = (ctypes.c_float * 4096)()
+    base = ctypes.addressof(buf)
+    base += (-base) % 16
+    ptr = ctypes.c_void_p(base)
+    c = 64
+    shp = _lib.Shape(1, 9, 11, 2, 7, 3, _lib.BF16, _lib.IMPL_AUTO, 32 ** -0.5, 0.0, 0, 3 * c, 3 * c, 3 * c, c, 0, 0)
+    err = lib.swin_attn_last_error
+    # k_pad given without d_k_pad
+    assert lib.swin_attn_backward_unpadded(ctypes.byref(shp), ptr, ptr, ptr, ptr, None, ptr, ptr, ptr, ptr, ptr, ptr, ptr, ptr, None, None,
+                                           None) != 0
+    assert b"d_k_pad / d_v_pad must be given exactly when" in err()
+    # the aligned-only entry rejects the same ragged shape
+    assert lib.swin_attn_backward(ctypes.byref(shp), ptr, ptr, ptr, ptr, ptr, ptr, ptr, None, ptr, ptr, ptr, ptr, None) != 0
+    assert b"multiples of the window" in err()
+    # fp32 on ragged tensors: no tensor-core kernel, explicit padding required
+    shp32 = _lib.Shape(1, 9, 11, 2, 7, 3, _lib.F32, _lib.IMPL_AUTO, 32 ** -0.5, 0.0, 0, 3 * c, 3 * c, 3 * c, c, 0, 0)
+    assert lib.swin_attn_backward_unpadded(ctypes.byref(shp32), ptr, ptr, ptr, None, None, ptr, ptr, ptr, ptr, ptr, ptr, ptr, ptr, None,
+                                           None, None) != 0
+    assert b"needs the tcgen05 kernel" in err()
+    assert lib.swin_attn_backward_unpadded(ctypes.byref(shp), ptr, ptr, None, None, None, ptr, ptr, ptr, ptr, ptr, ptr, ptr, ptr, None, None,
+                                           None) != 0
+    assert b"non-null" in err()
+
+
 def test_torch_binding_registers_ops_without_a_gpu():
     """libswin_attn_torch.so (csrc/torch_binding.cpp) loads on a CPU-only host, registers the four dispatcher ops with
     the documented schemas, has Meta kernels for shape inference and no CPU kernels (CPU tensors raise)."""
     import torch
     from mde_b200 import ops
     assert os.path.exists(ops.TORCH_LIB_PATH)
-    for name in ("fwd", "bwd", "layer_norm", "layer_norm_bwd", "add_layer_norm", "gelu", "gelu_bwd", "linear", "bias_grad"):
+    for name in ("fwd", "bwd", "layer_norm", "layer_norm_bwd", "add_layer_norm", "gelu", "gelu_bwd", "linear", "bias_grad",
+                 "bwd_unpadded"):
         assert hasattr(torch.ops.swin_attn, name)
     s = str(torch.ops.swin_attn.fwd.default._schema)
     assert "Tensor? attn_mask=None, float dropout_p=0., int seed=0" in s and s.endswith("-> (Tensor, Tensor)")
