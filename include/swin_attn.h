@@ -145,6 +145,19 @@ int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta
 int swin_gelu_forward(const void* x, void* y, int64_t n, void* stream);
 int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void* stream);
 
+/* Per-token Linear with the activation folded into its epilogue, tcgen05 GEMM:
+ *   y = act(x W^T + b),  x: (rows, in_features) bf16 dense, weight: (out_features, in_features) bf16 (nn.Linear.weight),
+ *   bias: (out_features) bf16, y: (rows, out_features) bf16.
+ * activation = SWIN_ACT_GELU replaces `self.act(self.fc1(x))` of the block MLP (newcrf_layers.py:21-23; Mlp of
+ * swin_transformer.py) under bf16 autocast: fp32 accumulation, + bias, rounded to bf16 (the value the autocast Linear
+ * returns), exact GELU in fp32 on that value, rounded to bf16 -- bit-identical to swin_gelu_forward applied to the
+ * bf16 Linear output of the same accumulation.  SWIN_ACT_NONE is the plain Linear.
+ * in_features a multiple of 64, out_features a multiple of 256, all pointers 16-byte aligned.  Inference only. */
+#define SWIN_ACT_NONE 0
+#define SWIN_ACT_GELU 1
+int swin_linear_forward(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int32_t in_features,
+                        int32_t out_features, int32_t activation, void* stream);
+
 /* Bias gradient of the per-token Linears either side of the attention (qkv / qk / proj, fc1 / fc2;
  * newcrf_layers.py:102,118,147, swin_transformer.py:104,120,142): dbias[c] = sum over rows of dy[row, c].
  * dy: (rows, cols) bf16, dense, 16-byte aligned, cols a multiple of 8; dbias: (cols) fp32, OVERWRITTEN. */

@@ -27,6 +27,7 @@ EXPORTS = (
     "swin_add_layernorm_forward",
     "swin_gelu_forward",
     "swin_gelu_backward",
+    "swin_linear_forward",
     "swin_linear_bias_grad",
     "swin_attn_launch_count",
     "swin_attn_uses_tcgen05",
@@ -78,6 +79,8 @@ def load() -> ctypes.CDLL:
     lib.swin_gelu_forward.restype = c_int
     lib.swin_gelu_backward.argtypes = [vp, vp, vp, c_int64, vp]
     lib.swin_gelu_backward.restype = c_int
+    lib.swin_linear_forward.argtypes = [vp, vp, vp, vp, c_int64, c_int32, c_int32, c_int32, vp]
+    lib.swin_linear_forward.restype = c_int
     lib.swin_linear_bias_grad.argtypes = [vp, c_int64, c_int32, vp, vp]
     lib.swin_linear_bias_grad.restype = c_int
     lib.swin_attn_launch_count.argtypes = []

@@ -239,6 +239,24 @@ int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void*
   return gelu_entry("gelu backward", x, dy, dx, n, stream);
 }
 
+int swin_linear_forward(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int32_t in_features,
+                        int32_t out_features, int32_t activation, void* stream) {
+  if (!x || !weight || !bias || !y) return fail("linear forward: all pointers must be non-null");
+  if (activation != SWIN_ACT_NONE && activation != SWIN_ACT_GELU) return fail("linear forward: activation must be SWIN_ACT_NONE or SWIN_ACT_GELU");
+  if (rows < 0 || rows >= (1ll << 31) - 128) return fail("linear forward: bad row count");
+  if (in_features < 64 || in_features % 64) return fail("linear forward: in_features must be a positive multiple of 64");
+  if (out_features < 256 || out_features % 256) return fail("linear forward: out_features must be a positive multiple of 256");
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(weight) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(bias)) & 15)
+    return fail("linear forward: x, weight, bias and y must be 16-byte aligned");
+  if (rows == 0) return 0;
+  if (!tc_linear_supported(rows, in_features, out_features))
+    return fail("linear forward: the tcgen05 kernel is unavailable (cuTensorMapEncodeTiled not found in the driver)");
+  const char* why = nullptr;
+  cudaError_t e = launch_tc_linear(x, weight, bias, y, rows, in_features, out_features, activation, static_cast<cudaStream_t>(stream), &why);
+  if (e != cudaSuccess) return fail_cuda(why ? why : "linear forward launch", e);
+  return 0;
+}
+
 int swin_linear_bias_grad(const void* dy, int64_t rows, int32_t cols, float* dbias, void* stream) {
   if (!dy || !dbias) return fail("linear bias grad: all pointers must be non-null");
   if (rows < 0 || cols <= 0 || cols % 8) return fail("linear bias grad: rows >= 0 and cols a positive multiple of 8");

@@ -480,6 +480,20 @@ bool tc::encode_window_map(CUtensorMap* out, const void* base, const Problem& p,
 
 bool tc::tma_available() { return encode_fn() != nullptr; }
 
+// Tensor map over a row-major (rows, cols) bf16 matrix with `pitch_bytes` between rows; box = (box_cols, box_rows),
+// 128B swizzle for box_cols = 64, 64B swizzle for box_cols = 32.  Out-of-bounds rows load as zeros and are not stored.
+bool tc::encode_matrix_map(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t pitch_bytes, int box_cols, int box_rows) {
+  if (encode_fn() == nullptr) return false;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)pitch_bytes};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  return encode_fn()(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // jobs = heads x window chunks, at most one wave of CTAs; chunks hold an even number of windows
 void tc::job_grid(const Problem& p, int sms, int* n_win, int* win_per_job, int* grid) {
   *n_win = p.B * p.nWy * p.nWx;

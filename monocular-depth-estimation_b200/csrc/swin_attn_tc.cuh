@@ -293,6 +293,7 @@ __device__ __forceinline__ void write_pad_rows(uint32_t tile, uint64_t padded, c
 // (swin_attn_tc.cu).  The seven box shapes of a launch, indexed like TmaMaps.
 bool encode_window_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pix_stride, int bx, int by);
 bool tma_available();
+bool encode_matrix_map(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t pitch_bytes, int box_cols, int box_rows);
 void job_grid(const Problem& p, int sms, int* n_win, int* win_per_job, int* grid);
 int sm_count();
 constexpr int kBoxX[7] = {WS, WS - kShift, WS - kShift, kShift, kShift, WS - kShift, kShift};

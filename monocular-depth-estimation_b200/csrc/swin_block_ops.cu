@@ -13,6 +13,7 @@
 #include <stdint.h>
 
 #include "swin_common.cuh"
+#include "swin_gelu.cuh"
 
 namespace swin {
 
@@ -305,49 +306,6 @@ cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, 
 // exp(-z^2 + P(t)) t form with t = 1/(1 + z/2) (fractional error < 1.2e-7 everywhere, Numerical Recipes erfcc), i.e.
 // two MUFU ops and ten FMAs, and the negative tail x/2 erfc(|x|/sqrt 2) has no cancellation -- closer to the fp64 value
 // than 1 + erff is.  16-byte vectors, two per thread.
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-// two elements at a time: packed fp32x2 FMAs halve the instruction count of the polynomial (the kernel is issue-bound
-// otherwise: ~25 scalar instructions per element against ~4 bytes of traffic)
-__device__ __forceinline__ float rcp_approx(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-__device__ __forceinline__ float2 splat(float v) { return make_float2(v, v); }
-
-__device__ __forceinline__ float2 erfc_abs2(float2 z) {   // erfc(z), z >= 0
-  const float2 d = __ffma2_rn(splat(0.5f), z, splat(1.0f));
-  const float2 t = make_float2(rcp_approx(d.x), rcp_approx(d.y));
-  float2 p = splat(0.17087277f);
-  p = __ffma2_rn(p, t, splat(-0.82215223f));
-  p = __ffma2_rn(p, t, splat(1.48851587f));
-  p = __ffma2_rn(p, t, splat(-1.13520398f));
-  p = __ffma2_rn(p, t, splat(0.27886807f));
-  p = __ffma2_rn(p, t, splat(-0.18628806f));
-  p = __ffma2_rn(p, t, splat(0.09678418f));
-  p = __ffma2_rn(p, t, splat(0.37409196f));
-  p = __ffma2_rn(p, t, splat(1.00002368f));
-  p = __ffma2_rn(p, t, splat(-1.26551223f));
-  const float2 a = __fmul2_rn(__ffma2_rn(z, make_float2(-z.x, -z.y), p), splat(1.4426950408889634f));
-  return __fmul2_rn(t, make_float2(ex2_approx(a.x), ex2_approx(a.y)));
-}
-
-template <bool kBackward>
-__device__ __forceinline__ float2 gelu_value2(float2 x, float2 dy) {
-  const float2 h = __fmul2_rn(erfc_abs2(__fmul2_rn(make_float2(fabsf(x.x), fabsf(x.y)), splat(0.70710678118654752440f))), splat(0.5f));
-  const float2 cdf = make_float2(x.x >= 0.f ? 1.0f - h.x : h.x, x.y >= 0.f ? 1.0f - h.y : h.y);   // Phi(x)
-  if (!kBackward) return __fmul2_rn(x, cdf);
-  const float2 q = __fmul2_rn(__fmul2_rn(x, x), splat(-0.72134752044448170f));
-  const float2 pdf = __fmul2_rn(splat(0.3989422804014327f), make_float2(ex2_approx(q.x), ex2_approx(q.y)));   // exp(-x^2/2)/sqrt(2 pi)
-  return __fmul2_rn(dy, __ffma2_rn(x, pdf, cdf));
-}
-
 template <bool kBackward>
 __global__ void __launch_bounds__(256) gelu_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, uint4* __restrict__ out,
                                                    int64_t nvec) {

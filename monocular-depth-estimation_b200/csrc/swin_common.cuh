@@ -149,6 +149,9 @@ cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, 
 cudaError_t launch_gelu(const void* x, const void* dy, void* out, int64_t n, cudaStream_t st);
 cudaError_t launch_colsum(const void* dy, int64_t rows, int cols, float* out, int sms, cudaStream_t st);
 bool layernorm_supported(int channels);
+bool tc_linear_supported(int64_t rows, int in_features, int out_features);
+cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int in_features, int out_features,
+                             int activation, cudaStream_t st, const char** err);
 
 void count_launch(int n = 1);
 

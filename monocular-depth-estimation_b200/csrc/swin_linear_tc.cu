@@ -1,0 +1,289 @@
+// Per-token Linear of the blocks with its activation folded into the epilogue, tcgen05 / TMEM / TMA, sm_100a.
+//
+//   y = act(x W^T + b)      x (M, K) bf16 tokens, W (N, K) bf16 = nn.Linear.weight, b (N) bf16, y (M, N) bf16
+//
+// Replaces `Mlp.fc1` followed by `nn.GELU()` (newcrf_layers.py:9-27; the same Mlp in swin_transformer.py) for
+// inference under bf16 autocast: the hidden tensor (M x 4C) is written once instead of written, read and written
+// again (the per-token Linears as tcgen05 GEMMs with fused epilogues).  Numerics are the
+// reference's step by step: fp32 accumulation, bias added in fp32, rounded to bf16 (what the cuBLASLt bias epilogue
+// stores), GELU evaluated in fp32 on that bf16 value and rounded to bf16 (what nn.GELU does on a bf16 tensor).
+//
+// Persistent kernel, one CTA per SM, tiles of 128 tokens x 256 outputs, K in blocks of 64 (one 128B-swizzle atom):
+//   warp 0      TMA producer: x tile (128 x 64) and W tile (256 x 64) per K block into a 4-stage ring
+//   warp 1      MMA issuer: 4 x tcgen05.mma M128 N256 K16 per K block, accumulators double-buffered in TMEM (2 x 256 cols)
+//   warp 2      TMEM allocation
+//   warp 3      bias of the tile's 256 outputs -> fp32 in shared memory (double-buffered with the accumulators)
+//   warps 4-19  epilogue (the GELU is ~16 instructions per element, 2 of them MUFU: it needs all four schedulers busy):
+//               warp = (TMEM lane quarter, 64-column quarter of the tile); tcgen05.ld 16 columns at a time, + bias, bf16
+//               round, GELU, bf16 round, 64B-swizzled staging of 32 x 32 boxes in shared memory, TMA tensor store (rows
+//               beyond M are clipped by the tensor map)
+// The epilogue of tile t overlaps the MMAs of tile t + 1.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "swin_attn_tc.cuh"
+#include "swin_gelu.cuh"
+
+namespace swin {
+namespace tcl {
+
+using namespace tc;
+
+constexpr int BM = 128, BN = 256, BK = 64;
+constexpr int kStages = 4;
+constexpr int kABytes = BM * BK * 2;                      // 16 KB
+constexpr int kBBytes = BN * BK * 2;                      // 32 KB
+constexpr int kStageBytes = kABytes + kBBytes;            // 48 KB
+constexpr int kStagingOff = kStages * kStageBytes;        // 192 KB
+constexpr int kStagingWarp = 32 * 64;                     // 32 rows x 32 bf16 per epilogue warp
+constexpr int kEpiWarps = 16;
+constexpr int kBiasOff = kStagingOff + kEpiWarps * kStagingWarp;
+constexpr int kBarOff = kBiasOff + 2 * BN * 4;
+constexpr int kSmemBytes = kBarOff + 128;
+constexpr int kThreads = 128 + kEpiWarps * 32;
+static_assert(kSmemBytes <= 232448, "shared memory budget");
+
+struct Maps {
+  CUtensorMap x, w, y;
+};
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+               "l"(map), "r"(bar), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+}
+
+#define TMEM_LD_X32(taddr, r)                                                                                          \
+  asm volatile(                                                                                                        \
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                        \
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];" \
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),  \
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),     \
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),    \
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                                                                       \
+      : "r"(taddr))
+
+template <bool kGelu>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restrict__ bias, int M, int N, int K) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const uint32_t sbase = smem_u32(smem);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  const uint32_t bar_full = sbase + kBarOff;            // [kStages]
+  const uint32_t bar_empty = bar_full + 8 * kStages;    // [kStages]
+  const uint32_t bar_acc_full = bar_empty + 8 * kStages;   // [2]
+  const uint32_t bar_acc_empty = bar_acc_full + 16;        // [2]
+  const uint32_t bar_bias_full = bar_acc_empty + 16;       // [2]
+  const uint32_t tmem_slot = bar_bias_full + 16;
+  float* bias_s = reinterpret_cast<float*>(smem + kBiasOff);   // [2][BN]
+
+  const int n_blocks = N / BN, m_blocks = (M + BM - 1) / BM, k_blocks = K / BK;
+  const int tiles = n_blocks * m_blocks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&maps.x);
+    tma_prefetch_desc(&maps.w);
+    tma_prefetch_desc(&maps.y);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(bar_acc_full + 8 * a, 1);
+      mbar_init(bar_acc_empty + 8 * a, kEpiWarps);
+      mbar_init(bar_bias_full + 8 * a, 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - sbase));
+
+  if (warp == 0) {
+    // ---- TMA producer ----
+    int s = 0;
+    uint32_t ph = 0;
+    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+      const int m0 = (t / n_blocks) * BM, n0 = (t % n_blocks) * BN;
+      for (int kb = 0; kb < k_blocks; ++kb) {
+        mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        if (elect_one()) {
+          const uint32_t st = sbase + s * kStageBytes;
+          mbar_expect_tx(bar_full + 8 * s, kStageBytes);
+          tma_load_2d(st, &maps.x, bar_full + 8 * s, kb * BK, m0);
+          tma_load_2d(st + kABytes, &maps.w, bar_full + 8 * s, kb * BK, n0);
+        }
+        __syncwarp();
+        if (++s == kStages) {
+          s = 0;
+          ph ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---- MMA issuer ----
+    constexpr uint32_t idesc = instr_desc(BM, BN, 0);
+    int s = 0, a = 0;
+    uint32_t ph = 0, aph = 0;
+    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+      mbar_wait(bar_acc_empty + 8 * a, aph ^ 1);
+      tc_fence_after();
+      for (int kb = 0; kb < k_blocks; ++kb) {
+        mbar_wait(bar_full + 8 * s, ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t st = sbase + s * kStageBytes;
+          const uint64_t ad = smem_desc(st, 16, 1024, 2);
+          const uint64_t bd = smem_desc(st + kABytes, 16, 1024, 2);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) umma_ss(tmem_base + a * BN, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+          umma_commit(bar_empty + 8 * s);
+          if (kb == k_blocks - 1) umma_commit(bar_acc_full + 8 * a);
+        }
+        __syncwarp();
+        if (++s == kStages) {
+          s = 0;
+          ph ^= 1;
+        }
+      }
+      a ^= 1;
+      if (a == 0) aph ^= 1;
+    }
+  } else if (warp == 3) {
+    // ---- bias loader: keeps the epilogue warps free of CTA-wide barriers ----
+    int a = 0;
+    uint32_t aph = 0;
+    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+      const int n0 = (t % n_blocks) * BN;
+      mbar_wait(bar_acc_empty + 8 * a, aph ^ 1);   // the epilogue of the tile that used this buffer is done with it
+      const uint4 raw = __ldg(reinterpret_cast<const uint4*>(bias + n0) + lane);
+      const uint32_t* rw = reinterpret_cast<const uint32_t*>(&raw);
+      float4* dst = reinterpret_cast<float4*>(bias_s + a * BN + lane * 8);
+      const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[0]));
+      const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[1]));
+      const float2 f2 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[2]));
+      const float2 f3 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[3]));
+      dst[0] = make_float4(f0.x, f0.y, f1.x, f1.y);
+      dst[1] = make_float4(f2.x, f2.y, f3.x, f3.y);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_bias_full + 8 * a);
+      a ^= 1;
+      if (a == 0) aph ^= 1;
+    }
+  } else if (warp >= 4) {
+    // ---- epilogue ----
+    const int e = warp - 4, q = warp & 3, quarter = e >> 2;   // TMEM lane quarter of this warp, 64-column quarter of the tile
+    const uint32_t staging = sbase + kStagingOff + e * kStagingWarp;
+    const uint32_t row_off = lane * 64, sw = (lane >> 1) & 3;
+    int a = 0;
+    uint32_t aph = 0;
+    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+      const int m0 = (t / n_blocks) * BM, n0 = (t % n_blocks) * BN;
+      mbar_wait(bar_bias_full + 8 * a, aph);
+      mbar_wait(bar_acc_full + 8 * a, aph);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + a * BN + quarter * 64;
+      const bool rows_live = m0 + q * 32 < M;
+#pragma unroll 1
+      for (int box = 0; box < 2; ++box) {
+        if (lane == 0) bulk_wait_read();   // the previous store of this warp has read the staging buffer
+        __syncwarp();
+#pragma unroll
+        for (int sub = 0; sub < 2; ++sub) {
+          uint32_t r[16];
+          TMEM_LD_X16(tacc + box * 32 + sub * 16, r);
+          tmem_ld_wait();
+          const float4* b4 = reinterpret_cast<const float4*>(bias_s + a * BN + quarter * 64 + box * 32 + sub * 16);
+          uint32_t w[8];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 b = b4[i];
+            const float2 v0 = __fadd2_rn(make_float2(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1])), make_float2(b.x, b.y));
+            const float2 v1 = __fadd2_rn(make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3])), make_float2(b.z, b.w));
+            uint32_t h0 = pack_bf16(v0.x, v0.y), h1 = pack_bf16(v1.x, v1.y);
+            if (kGelu) {
+              const float2 g0 = gelu_value2<false>(__bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h0)), make_float2(0.f, 0.f));
+              const float2 g1 = gelu_value2<false>(__bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h1)), make_float2(0.f, 0.f));
+              h0 = pack_bf16(g0.x, g0.y);
+              h1 = pack_bf16(g1.x, g1.y);
+            }
+            w[2 * i] = h0;
+            w[2 * i + 1] = h1;
+          }
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const uint32_t chunk = (uint32_t)(sub * 2 + j) ^ sw;
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(staging + row_off + chunk * 16), "r"(w[4 * j]), "r"(w[4 * j + 1]),
+                         "r"(w[4 * j + 2]), "r"(w[4 * j + 3])
+                         : "memory");
+          }
+        }
+        if (box == 1) {
+          // the accumulator buffer is in registers / shared memory: hand it back to the MMA issuer
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * a);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0 && rows_live) {
+          tma_store_2d(&maps.y, staging, n0 + quarter * 64 + box * 32, m0 + q * 32);
+          bulk_commit();
+        }
+      }
+      a ^= 1;
+      if (a == 0) aph ^= 1;
+    }
+    if (lane == 0) bulk_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace tcl
+
+bool tc_linear_supported(int64_t rows, int in_features, int out_features) {
+  return rows > 0 && rows < (1ll << 31) - tcl::BM && in_features >= tcl::BK && in_features % tcl::BK == 0 && out_features >= tcl::BN &&
+         out_features % tcl::BN == 0 && tc::tma_available();
+}
+
+cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int in_features, int out_features,
+                             int activation, cudaStream_t st, const char** err) {
+  tcl::Maps maps;
+  memset(&maps, 0, sizeof(maps));
+  if (!tc::encode_matrix_map(&maps.x, x, rows, in_features, (int64_t)in_features * 2, tcl::BK, tcl::BM) ||
+      !tc::encode_matrix_map(&maps.w, weight, out_features, in_features, (int64_t)in_features * 2, tcl::BK, tcl::BN) ||
+      !tc::encode_matrix_map(&maps.y, y, rows, out_features, (int64_t)out_features * 2, 32, 32)) {
+    if (err) *err = "cuTensorMapEncodeTiled failed";
+    return cudaErrorInvalidValue;
+  }
+  auto kernel = activation ? tcl::tc_linear_kernel<true> : tcl::tc_linear_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcl::kSmemBytes);
+  if (e != cudaSuccess) {
+    if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
+    return e;
+  }
+  const int64_t tiles = ((rows + tcl::BM - 1) / tcl::BM) * (out_features / tcl::BN);
+  const int sms = tc::sm_count();
+  const int grid = (int)(tiles < sms ? tiles : sms);
+  kernel<<<grid, tcl::kThreads, tcl::kSmemBytes, st>>>(maps, static_cast<const __nv_bfloat16*>(bias), (int)rows, out_features, in_features);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace swin

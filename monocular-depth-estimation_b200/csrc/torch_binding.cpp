@@ -370,6 +370,29 @@ Tensor gelu_cuda(const Tensor& x_in) {
   return y;
 }
 
+// act(x W^T + b) with the tcgen05 GEMM (inference; activation: 0 none, 1 exact GELU)
+Tensor linear_act_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& bias, int64_t activation) {
+  TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && weight.scalar_type() == at::kBFloat16 && bias.scalar_type() == at::kBFloat16,
+              "swin_attn::linear_act: x, weight and bias must be bfloat16");
+  TORCH_CHECK(weight.dim() == 2 && bias.dim() == 1 && x_in.dim() >= 1 && x_in.size(-1) == weight.size(1) && bias.size(0) == weight.size(0),
+              "swin_attn::linear_act: x (..., in), weight (out, in), bias (out)");
+  const Tensor x = x_in.contiguous(), w = weight.contiguous(), b = bias.contiguous();
+  std::vector<int64_t> shape(x.sizes().begin(), x.sizes().end());
+  shape.back() = w.size(0);
+  Tensor y = at::empty(shape, x.options());
+  if (y.numel() == 0) return y;
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(swin_linear_forward(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), x.numel() / x.size(-1), (int32_t)w.size(1),
+                               (int32_t)w.size(0), (int32_t)activation, at::cuda::getCurrentCUDAStream()));
+  return y;
+}
+
+Tensor linear_act_meta(const Tensor& x, const Tensor& weight, const Tensor&, int64_t) {
+  std::vector<c10::SymInt> shape(x.sym_sizes().begin(), x.sym_sizes().end());
+  shape.back() = weight.sym_size(0);
+  return at::empty_symint(shape, x.options());
+}
+
 Tensor gelu_bwd_cuda(const Tensor& dy_in, const Tensor& x_in) {
   TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && x_in.numel() % 8 == 0, "swin_attn::gelu_bwd: bfloat16 with a multiple of 8 elements");
   TORCH_CHECK(dy_in.sizes() == x_in.sizes(), "swin_attn::gelu_bwd: dy and x must have the same shape");
@@ -620,6 +643,7 @@ TORCH_LIBRARY(swin_attn, m) {
   m.def("bias_grad(Tensor dy) -> Tensor");
   m.def("gelu(Tensor x) -> Tensor");
   m.def("gelu_bwd(Tensor dy, Tensor x) -> Tensor");
+  m.def("linear_act(Tensor x, Tensor weight, Tensor bias, int activation) -> Tensor");
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
@@ -633,6 +657,7 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("bias_grad", bias_grad_cuda);
   m.impl("gelu", gelu_cuda);
   m.impl("gelu_bwd", gelu_bwd_cuda);
+  m.impl("linear_act", linear_act_cuda);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
@@ -646,6 +671,7 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("bias_grad", bias_grad_meta);
   m.impl("gelu", gelu_meta);
   m.impl("gelu_bwd", gelu_bwd_meta);
+  m.impl("linear_act", linear_act_meta);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
@@ -654,6 +680,7 @@ TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
   m.impl("add_layer_norm", torch::autograd::autogradNotImplementedFallback());   // inference only
   m.impl("gelu", gelu_autograd);
   m.impl("linear", linear_autograd);
+  m.impl("linear_act", torch::autograd::autogradNotImplementedFallback());   // inference only
 }
 
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------

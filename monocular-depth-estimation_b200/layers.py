@@ -69,7 +69,7 @@ class Mlp(nn.Module):
         self.drop = nn.Dropout(drop)
 
     def forward(self, x):
-        return self.drop(ops.linear(self.fc2, self.drop(ops.gelu(self.act, ops.linear(self.fc1, x)))))
+        return self.drop(ops.linear(self.fc2, self.drop(ops.linear_gelu(self.fc1, self.act, x))))
 
 
 def _relative_position_index(wh: int, ww: int) -> torch.Tensor:

@@ -619,6 +619,60 @@ def test_fused_gelu_forward_backward_vs_fp64():
     assert ops.gelu(torch.nn.GELU(), x.float()).dtype == torch.float32
 
 
+LINEAR_ACT_CASES = [  # rows, in_features, out_features
+    (77, 64, 256), (128, 128, 512), (1000, 192, 768), (4099, 768, 3072), (300, 1536, 6144), (129, 1024, 4096), (8 * 22 * 76, 384, 1536),
+]
+
+
+@pytest.mark.parametrize("case", LINEAR_ACT_CASES)
+def test_linear_gelu_tcgen05_matches_autocast_linear_then_gelu(case):
+    """swin_linear_forward (tcgen05 GEMM with bias / GELU epilogue, the inference path of Mlp.fc1 + act): against the
+    fp64 product on the same bf16 operands, against the autocast nn.Linear (cuBLAS) + nn.GELU the reference runs, and
+    GELU epilogue == swin_gelu_forward of the plain epilogue, bit for bit."""
+    rows, k, n = case
+    gen = torch.Generator(device=DEV).manual_seed(rows + k + n)
+    x = torch.randn(rows, k, device=DEV, generator=gen).bfloat16()
+    lin = torch.nn.Linear(k, n).to(DEV)
+    with torch.no_grad():
+        lin.weight.copy_(torch.randn(n, k, device=DEV, generator=gen) * k ** -0.5)
+        lin.bias.copy_(torch.randn(n, device=DEV, generator=gen))
+    w, b = lin.weight.detach().bfloat16(), lin.bias.detach().bfloat16()
+    plain = torch.ops.swin_attn.linear_act(x, w, b, 0)
+    fused = torch.ops.swin_attn.linear_act(x, w, b, 1)
+    assert plain.shape == (rows, n) and plain.dtype == torch.bfloat16 and fused.shape == (rows, n)
+    h64 = x.double() @ w.double().t() + b.double()
+    assert rel_err(plain, h64) <= TOL_BF16
+    # one bf16 rounding of an fp32 accumulation: within one ulp of the exact value, and mostly THE rounded value
+    ulp = (h64.abs() * 2.0 ** -7).clamp_min(1e-3).float()
+    assert ((plain.float() - h64.float()).abs() <= ulp).all()
+    assert (plain != h64.float().bfloat16()).float().mean().item() < 0.02
+    assert torch.equal(fused, torch.ops.swin_attn.gelu(plain))
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        ref_h = lin(x)
+        ref = torch.nn.functional.gelu(ref_h)
+        got = ops.linear_gelu(lin, torch.nn.GELU(), x)
+    assert torch.equal(got, fused)
+    assert rel_err(plain, ref_h) <= TOL_BF16 and rel_err(got, ref) <= TOL_BF16
+    assert (plain != ref_h).float().mean().item() < 0.02      # same operands, same fp32 accumulate: rare 1-ulp ties only
+    # training keeps the differentiable path
+    xg = x.clone().requires_grad_()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        y = ops.linear_gelu(lin, torch.nn.GELU(), xg)
+    assert y.requires_grad and rel_err(y.detach(), ref) <= TOL_BF16
+
+
+def test_linear_gelu_in_model_is_bit_identical_to_unfused(monkeypatch):
+    """The Mlp of a block with the fused fc1 + GELU against the same block with the two-kernel path."""
+    torch.manual_seed(5)
+    mlp = layers.Mlp(192, 768).to(DEV).eval()
+    x = torch.randn(3, 500, 192, device=DEV).bfloat16()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        got = mlp(x)
+        monkeypatch.setattr(ops, "linear_gelu", lambda lin, act, t: ops.gelu(act, ops.linear(lin, t)))
+        want = mlp(x)
+    assert rel_err(got, want) <= 2e-3 and (got != want).float().mean().item() < 0.05
+
+
 @pytest.mark.parametrize("shape", [(3, 50, 192, 576), (2, 7, 9, 128, 256), (1, 4099, 768, 3072), (5, 33, 1024, 1024)])
 def test_linear_with_fused_bias_grad_matches_autocast_linear(shape):
     """swin_attn::linear (training path of qkv / qk / proj / fc1 / fc2): same output and input / weight gradients as
