@@ -10,7 +10,7 @@ over NCCL (one process per GPU); the attention itself is never sharded.
 from __future__ import annotations
 
 import os
-from typing import Dict, Optional
+from typing import Callable, Dict, Iterable, List, Optional
 
 import torch
 import torch.distributed as dist
@@ -116,6 +116,60 @@ def infer(model: nn.Module, images: torch.Tensor, bf16: bool = True) -> torch.Te
     """The call a user makes for inference: images (B,3,H,W) on the model's device -> depth (B,1,H,W)."""
     with torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf16):
         return model(images)
+
+
+@torch.no_grad()
+def infer_host_batches(model: nn.Module, batches: Iterable[torch.Tensor], outs: Optional[List[torch.Tensor]] = None,
+                       bf16: bool = True, before_step: Optional[Callable[[], None]] = None) -> List[torch.Tensor]:
+    """Inference over a sequence of HOST batches (pinned (B,3,H,W) tensors) -> host depth maps.
+
+    The serving loop of a deployment: the host-to-device copy of batch i + 1 and the device-to-host copy of result
+    i - 1 run on two copy streams while batch i computes on the current stream (at most two uploads in flight).
+    ``outs`` are optional pinned result buffers, one per batch (reused by the caller); ``before_step`` is called on the
+    compute stream before every forward (bench.py flushes L2 there).  The last result is complete once the current
+    stream has been synchronised (the function joins the download stream into it before returning)."""
+    dev = next(model.parameters()).device
+    cur = torch.cuda.current_stream(dev)
+    up, down = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    up.wait_stream(cur)
+    it = iter(batches)
+
+    def upload(after: Optional[torch.cuda.Event]):
+        b = next(it, None)
+        if b is None:
+            return None
+        if after is not None:
+            up.wait_event(after)          # bounded prefetch: batch i + 2 waits for forward i
+        with torch.cuda.stream(up):
+            x = b.to(dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(up)
+        return x, ev
+
+    results: List[torch.Tensor] = []
+    done_prev: Optional[torch.cuda.Event] = None
+    nxt = upload(None)
+    i = 0
+    while nxt is not None:
+        x, ready = nxt
+        nxt = upload(done_prev)
+        cur.wait_event(ready)
+        x.record_stream(cur)
+        if before_step is not None:
+            before_step()
+        y = infer(model, x, bf16).float()
+        done = torch.cuda.Event()
+        done.record(cur)
+        out = outs[i] if outs is not None else torch.empty(y.shape, dtype=y.dtype).pin_memory()
+        down.wait_event(done)
+        with torch.cuda.stream(down):
+            out.copy_(y, non_blocking=True)
+        y.record_stream(down)
+        results.append(out)
+        done_prev = done
+        i += 1
+    cur.wait_stream(down)
+    return results
 
 
 class Trainer:

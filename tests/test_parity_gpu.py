@@ -763,3 +763,26 @@ def test_backward_on_unpadded_tensors_matches_oracle_autograd(case):
     assert float(g[2][:c].abs().max()) == 0.0          # padded QUERY rows are cropped: no gradient reaches q_pad
     if h % ws or w % ws:
         assert float(g_ref[2][c:].abs().max()) > 0.0   # ... but the padded keys / values do carry gradient
+
+
+def test_infer_host_batches_pipeline_matches_per_batch_inference():
+    """harness.infer_host_batches (upload / compute / download on three streams) returns, for every pinned host batch,
+    exactly what harness.infer returns for it, in order, also with reused result buffers and a before_step hook."""
+    from mde_b200 import harness
+    torch.manual_seed(11)
+    model = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3, padding=1), torch.nn.GELU(), torch.nn.Conv2d(8, 1, 3, padding=1)).to(DEV).eval()
+    batches = [torch.randn(2, 3, 64, 96).pin_memory() for _ in range(5)]
+    want = [harness.infer(model, b.to(DEV)).float().cpu() for b in batches]
+    got = harness.infer_host_batches(model, batches)
+    torch.cuda.synchronize()
+    assert len(got) == 5 and all(g.is_pinned() for g in got)
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)
+    outs = [torch.empty(2, 1, 64, 96).pin_memory() for _ in range(5)]
+    calls = []
+    got = harness.infer_host_batches(model, iter(batches), outs, before_step=lambda: calls.append(1))
+    torch.cuda.synchronize()
+    assert len(calls) == 5 and all(g is o for g, o in zip(got, outs))
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)
+    assert harness.infer_host_batches(model, []) == []
