@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--mode", default="infer", choices=["infer", "train"],
                     help="infer: BASELINE configs[1] (the headline metric); train: configs[2], fwd+SILog+bwd+AdamW at 480x640")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="e2e leg launches the forward eagerly instead of replaying a CUDA graph")
     ap.add_argument("--version", default=VERSION)
     ap.add_argument("--batch", type=int, default=BATCH)
     return ap.parse_args()
@@ -130,7 +131,7 @@ def run_reference(args, rank):
 
 def run_ours(args, env):
     from mde_b200 import _lib, ops
-    from mde_b200.harness import build_model, infer, infer_host_batches, prepare_inference, synthetic_images
+    from mde_b200.harness import GraphedInference, build_model, infer, infer_host_batches, prepare_inference, synthetic_images
 
     rank, world, local = env["rank"], env["world"], env["local_rank"]
     dev = torch.device("cuda", local)
@@ -183,6 +184,7 @@ def run_ours(args, env):
             infer(model, images)
 
         out_hosts = [out_host, torch.empty_like(out_host).pin_memory()]
+        graphed = None if args.no_graph else GraphedInference(model, images)
 
         def region_e2e(steps):
             """K steps through the serving loop (harness.infer_host_batches): every step's images come from pinned host
@@ -192,7 +194,7 @@ def run_ours(args, env):
             torch.cuda.synchronize()
             a.record()
             infer_host_batches(model, (host for _ in range(steps)), [out_hosts[i & 1] for i in range(steps)],
-                               before_step=flush.zero_)
+                               before_step=flush.zero_, graphed=graphed)
             b.record()
             torch.cuda.synchronize()
             return a.elapsed_time(b) / 1e3
@@ -215,14 +217,18 @@ def run_ours(args, env):
     launches = _lib.launch_count() - launches0
     barrier()
     t_e2e = timed_steps(step_e2e, args.steps) if train else region_e2e(args.steps)
+    t_graph = None
+    if not train and graphed is not None:
+        barrier()
+        t_graph = timed_steps(lambda: graphed(images), args.steps)   # device-resident, the forward replayed as one graph
     barrier()
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
-    times = torch.tensor([t_res, t_e2e], dtype=torch.float64, device=dev)
+    times = torch.tensor([t_res, t_e2e, t_graph or 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    t_res, t_e2e = times.tolist()
+    t_res, t_e2e, t_graph = times.tolist()
     if rank != 0:
         return
     hbm, tf, which = peaks()
@@ -267,12 +273,18 @@ def run_ours(args, env):
                    "l2_flush_between_steps": True, "timing": "CUDA events per step, max over ranks",
                    "e2e_timing": ("per step: H2D -> step -> D2H on one stream" if train else
                                   "one event pair around K steps of harness.infer_host_batches (pinned host in / out, "
-                                  "copies of neighbouring steps overlapped on copy streams, L2 flush inside)")},
+                                  "copies of neighbouring steps overlapped on copy streams, L2 flush inside"
+                                  + (")" if args.no_graph else "; the forward is replayed from a CUDA graph, "
+                                     "harness.GraphedInference, while `value` is the eager forward so that the attention "
+                                     "launches can be bracketed by CUDA events for the roofline)"))},
         "e2e": {"value": n_img / t_e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         "roofline": roof_bwd if train else roof_fwd,
     }
+    if t_graph:
+        line["graph_replay"] = {"value": n_img / t_graph, "unit": "images/s", "ms_per_step": t_graph / args.steps * 1e3,
+                                "note": "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)"}
     if train:
         line["roofline_forward"] = roof_fwd
     if world == 1 and not args.no_cpu_baseline and not train:

@@ -118,16 +118,50 @@ def infer(model: nn.Module, images: torch.Tensor, bf16: bool = True) -> torch.Te
         return model(images)
 
 
+class GraphedInference:
+    """``infer(model, x)`` for one input shape as a CUDA graph: the ~440 launches of a forward are captured once (after
+    ``prepare_inference``) and replayed as one graph launch, which removes the launch gaps between the small kernels of
+    stages 2 / 3.  The forward has no host synchronisation and no data-dependent control flow, and the tensor maps of
+    the tcgen05 kernels are kernel parameters encoded at capture time over the graph's private memory pool, so a replay
+    computes exactly what the eager forward computes (tests/test_parity_gpu.py).  ``__call__`` copies ``x`` into the
+    static input and returns the static output, valid until the next call."""
+
+    def __init__(self, model: nn.Module, example: torch.Tensor, bf16: bool = True, warmup: int = 2):
+        self.model, self.bf16 = model, bf16
+        self.static_in = example.detach().clone()
+        side = torch.cuda.Stream(example.device)
+        side.wait_stream(torch.cuda.current_stream(example.device))
+        with torch.cuda.stream(side):                      # allocator and cuBLAS / cuDNN workspaces warm before the capture
+            for _ in range(warmup):
+                infer(model, self.static_in, bf16)
+        torch.cuda.current_stream(example.device).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.static_out = infer(model, self.static_in, bf16)
+
+    @torch.no_grad()
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        if x.shape != self.static_in.shape or x.dtype != self.static_in.dtype:
+            raise ValueError(f"graph captured for {tuple(self.static_in.shape)} {self.static_in.dtype}, "
+                             f"got {tuple(x.shape)} {x.dtype}")
+        self.static_in.copy_(x)
+        self.graph.replay()
+        return self.static_out
+
+
 @torch.no_grad()
 def infer_host_batches(model: nn.Module, batches: Iterable[torch.Tensor], outs: Optional[List[torch.Tensor]] = None,
-                       bf16: bool = True, before_step: Optional[Callable[[], None]] = None) -> List[torch.Tensor]:
+                       bf16: bool = True, before_step: Optional[Callable[[], None]] = None,
+                       graphed: Optional[GraphedInference] = None) -> List[torch.Tensor]:
     """Inference over a sequence of HOST batches (pinned (B,3,H,W) tensors) -> host depth maps.
 
     The serving loop of a deployment: the host-to-device copy of batch i + 1 and the device-to-host copy of result
     i - 1 run on two copy streams while batch i computes on the current stream (at most two uploads in flight).
     ``outs`` are optional pinned result buffers, one per batch (reused by the caller); ``before_step`` is called on the
-    compute stream before every forward (bench.py flushes L2 there).  The last result is complete once the current
-    stream has been synchronised (the function joins the download stream into it before returning)."""
+    compute stream before every forward (bench.py flushes L2 there).  ``graphed`` (a ``GraphedInference`` of ``model``
+    for this batch shape) replays the captured forward instead of launching it kernel by kernel.  The last result is
+    complete once the current stream has been synchronised (the function joins the download stream into it before
+    returning)."""
     dev = next(model.parameters()).device
     cur = torch.cuda.current_stream(dev)
     up, down = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
@@ -157,7 +191,8 @@ def infer_host_batches(model: nn.Module, batches: Iterable[torch.Tensor], outs: 
         x.record_stream(cur)
         if before_step is not None:
             before_step()
-        y = infer(model, x, bf16).float()
+        # the static output of a graph is overwritten by the next replay: detach the result from it
+        y = infer(model, x, bf16).float() if graphed is None else graphed(x).float().clone()
         done = torch.cuda.Event()
         done.record(cur)
         out = outs[i] if outs is not None else torch.empty(y.shape, dtype=y.dtype).pin_memory()

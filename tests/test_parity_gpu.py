@@ -786,3 +786,25 @@ def test_infer_host_batches_pipeline_matches_per_batch_inference():
     for g, w in zip(got, want):
         assert torch.equal(g, w)
     assert harness.infer_host_batches(model, []) == []
+
+
+def test_graphed_inference_replays_the_eager_forward_bit_for_bit():
+    """harness.GraphedInference (CUDA-graph capture of the full forward incl. the tcgen05 kernels and their tensor
+    maps): replays on new inputs equal the eager forward on the same inputs, also through infer_host_batches."""
+    from mde_b200 import harness
+    m = mde_b200.NewCRFDepth(version="tiny07", max_depth=10.0)
+    m.load_state_dict(synthetic_state(m), strict=True)
+    m = m.to(DEV)
+    harness.prepare_inference(m)
+    xs = [randn(f"graph.x{i}", 2, 3, 96, 128) for i in range(3)]
+    g = harness.GraphedInference(m, xs[0].to(DEV))
+    for x in xs[::-1]:
+        want = harness.infer(m, x.to(DEV)).clone()
+        got = g(x.to(DEV))
+        assert torch.equal(got, want)
+    with pytest.raises(ValueError):
+        g(torch.zeros(1, 3, 96, 128, device=DEV))
+    got = harness.infer_host_batches(m, [x.pin_memory() for x in xs], graphed=g)
+    torch.cuda.synchronize()
+    for x, o in zip(xs, got):
+        assert torch.equal(o, harness.infer(m, x.to(DEV)).float().cpu())
