@@ -282,6 +282,15 @@ def run_ours(args, env):
         "clocks": sampler.summary(),
         "roofline": roof_bwd if train else roof_fwd,
     }
+    lin_recs = [r for r in records if r[3][0] == "lin"]
+    if lin_recs:
+        l_ms, l_bytes, l_flops = (sum(r[i] for r in lin_recs) for i in range(3))
+        line["roofline_linear"] = {
+            "bound": "tensor", "kernel": "tc_linear_kernel (fc1 + bias + GELU of every block MLP, tcgen05 GEMM with fused epilogue)",
+            "achieved": l_flops / (l_ms * 1e-3) / 1e12, "peak": tf, "unit": "TFLOP/s", "frac": l_flops / (l_ms * 1e-3) / 1e12 / tf,
+            "peak_source": f"{which} (MEASURED_PEAKS.json dense bf16)", "traffic": None,
+            "algorithmic_GBps": l_bytes / (l_ms * 1e-3) / 1e9, "hbm_frac": l_bytes / (l_ms * 1e-3) / 1e9 / hbm,
+            "launches": len(lin_recs), "kernel_ms_per_step": l_ms / args.steps, "share_of_step": l_ms / 1e3 / t_res}
     if t_graph:
         line["graph_replay"] = {"value": n_img / t_graph, "unit": "images/s", "ms_per_step": t_graph / args.steps * 1e3,
                                 "note": "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)"}

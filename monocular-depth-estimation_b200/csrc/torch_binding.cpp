@@ -382,8 +382,13 @@ Tensor linear_act_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& b
   Tensor y = at::empty(shape, x.options());
   if (y.numel() == 0) return y;
   c10::cuda::CUDAGuard guard(x.device());
-  check_rc(swin_linear_forward(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), x.numel() / x.size(-1), (int32_t)w.size(1),
-                               (int32_t)w.size(0), (int32_t)activation, at::cuda::getCurrentCUDAStream()));
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const int64_t rows = x.numel() / x.size(-1), k = w.size(1), n = w.size(0);
+  TimedLaunch timed(stream);
+  check_rc(swin_linear_forward(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), rows, (int32_t)k, (int32_t)n, (int32_t)activation,
+                               stream));
+  // algorithmic traffic: x, W and y once; flops of the product (the GELU is not counted)
+  timed.finish(2 * (rows * k + n * k + rows * n), 2 * rows * n * k, 2, k, activation, n, rows, 0);
   return y;
 }
 

@@ -403,6 +403,19 @@ class PatchEmbed(nn.Module):
             x = F.pad(x, (0, pw - w % pw))
         if h % ph:
             x = F.pad(x, (0, 0, 0, ph - h % ph))
+        if (x.is_cuda and not torch.is_grad_enabled() and torch.is_autocast_enabled()
+                and torch.get_autocast_dtype("cuda") == torch.bfloat16 and (self.in_chans * ph * pw) % 8 == 0):
+            # A stride == kernel conv is a per-patch Linear: gather the patches as bf16 rows (one strided copy) and run
+            # one GEMM with the bias in its epilogue, instead of cuDNN's small-channel conv (10x off the memory
+            # roofline here) + layout copy + separate bias add.  Same bf16 operands and fp32 accumulation as autocast's conv.
+            b, c, hh, ww = x.shape[0], x.shape[1], x.shape[2] // ph, x.shape[3] // pw
+            cols = torch.empty(b, hh, ww, c, ph, pw, dtype=torch.bfloat16, device=x.device)
+            cols.copy_(x.contiguous().view(b, c, hh, ph, ww, pw).permute(0, 2, 4, 1, 3, 5))
+            bias = None if self.proj.bias is None else self.proj.bias.to(torch.bfloat16)
+            y = F.linear(cols.view(b, hh * ww, c * ph * pw), self.proj.weight.reshape(self.embed_dim, -1).to(torch.bfloat16), bias)
+            if self.norm is not None:
+                y = ops.norm_fp32(self.norm, y)
+            return y.transpose(1, 2).view(b, self.embed_dim, hh, ww)
         if x.is_cuda:
             x = x.contiguous(memory_format=torch.channels_last)   # conv output in NHWC: the token view below is free
         x = self.proj(x)

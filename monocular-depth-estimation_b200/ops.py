@@ -63,7 +63,7 @@ def set_kernel_timing(records):
             n = _torch_lib.swin_torch_take_timing(ms, meta, n)
             for i in range(n):
                 m = meta[8 * i:8 * i + 8]
-                _kernel_timing.append((ms[i], m[0], m[1], ("bwd" if m[2] else "fwd",) + tuple(m[3:8])))
+                _kernel_timing.append((ms[i], m[0], m[1], (("fwd", "bwd", "lin")[m[2]],) + tuple(m[3:8])))
         _kernel_timing = None
     else:
         _kernel_timing = records

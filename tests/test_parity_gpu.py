@@ -808,3 +808,24 @@ def test_graphed_inference_replays_the_eager_forward_bit_for_bit():
     torch.cuda.synchronize()
     for x, o in zip(xs, got):
         assert torch.equal(o, harness.infer(m, x.to(DEV)).float().cpu())
+
+
+@pytest.mark.parametrize("hw", [(32, 48), (30, 45)])
+def test_patch_embed_gemm_path_matches_autocast_conv(hw):
+    """PatchEmbed at inference (patch gather + one GEMM) against the reference's conv under the same autocast
+    (swin_transformer.py:396-436), with and without the right / bottom padding to a patch multiple."""
+    torch.manual_seed(3)
+    pe = layers.PatchEmbed(4, 3, 192, torch.nn.LayerNorm).to(DEV).eval()
+    x = torch.randn(2, 3, *hw, device=DEV)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        got = pe(x)
+        xp = torch.nn.functional.pad(x, (0, -hw[1] % 4, 0, -hw[0] % 4))
+        ref = torch.nn.functional.conv2d(xp, pe.proj.weight, pe.proj.bias, stride=4)
+        hh, ww = ref.shape[2:]
+        want = torch.nn.functional.layer_norm(ref.flatten(2).transpose(1, 2), (192,), pe.norm.weight, pe.norm.bias, pe.norm.eps)
+        want = want.transpose(1, 2).view(2, 192, hh, ww)
+    assert got.shape == want.shape and got.dtype == want.dtype == torch.float32
+    assert rel_err(got, want) <= TOL_BF16
+    with torch.autocast("cuda", dtype=torch.bfloat16):          # training keeps the conv (differentiable, same values)
+        trained = pe(x)
+    assert trained.requires_grad and rel_err(trained.detach(), want) <= TOL_BF16
