@@ -290,7 +290,16 @@ def run_ours(args, env):
             "achieved": l_flops / (l_ms * 1e-3) / 1e12, "peak": tf, "unit": "TFLOP/s", "frac": l_flops / (l_ms * 1e-3) / 1e12 / tf,
             "peak_source": f"{which} (MEASURED_PEAKS.json dense bf16)", "traffic": None,
             "algorithmic_GBps": l_bytes / (l_ms * 1e-3) / 1e9, "hbm_frac": l_bytes / (l_ms * 1e-3) / 1e9 / hbm,
-            "launches": len(lin_recs), "kernel_ms_per_step": l_ms / args.steps, "share_of_step": l_ms / 1e3 / t_res}
+            "launches": len(lin_recs), "kernel_ms_per_step": l_ms / args.steps, "share_of_step": l_ms / 1e3 / t_res,
+            "by_shape": {}}
+        shapes = {}
+        for r in lin_recs:                                   # tag = ("lin", in_features, activation, out_features, rows, 0)
+            shapes.setdefault((r[3][4], r[3][1], r[3][3]), []).append(r)
+        for (rows, k, n), rs in sorted(shapes.items(), reverse=True):
+            ms = sum(r[0] for r in rs)
+            line["roofline_linear"]["by_shape"][f"{rows}x{k}x{n}"] = {
+                "launches": len(rs), "us_per_launch": ms / len(rs) * 1e3, "TFLOPs": sum(r[2] for r in rs) / (ms * 1e-3) / 1e12,
+                "GBps": sum(r[1] for r in rs) / (ms * 1e-3) / 1e9}
     if t_graph:
         line["graph_replay"] = {"value": n_img / t_graph, "unit": "images/s", "ms_per_step": t_graph / args.steps * 1e3,
                                 "note": "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)"}
