@@ -107,6 +107,23 @@ def test_block_plumbing_entries_validate_without_gpu():
     assert lib.swin_layernorm_backward(ptr, _lib.F32, ptr, _lib.BF16, ptr, 1e-5, 1, 3072, ptr, ptr, ptr, None) != 0
 
 
+def test_linear_forward_entry_validates_without_gpu():
+    """swin_linear_forward (tcgen05 GEMM with bias / GELU epilogue): argument checks before any device work."""
+    lib = _lib.load()
+    buf = (ctypes.c_float * 256)()
+    base = ctypes.addressof(buf)
+    base += (-base) % 16
+    ptr, odd = ctypes.c_void_p(base), ctypes.c_void_p(base + 2)
+    err = lib.swin_attn_last_error
+    assert lib.swin_linear_forward(ptr, ptr, ptr, ptr, 4, 192, 768, 2, None) != 0 and b"activation" in err()
+    assert lib.swin_linear_forward(ptr, ptr, ptr, ptr, 4, 100, 768, 1, None) != 0 and b"in_features" in err()
+    assert lib.swin_linear_forward(ptr, ptr, ptr, ptr, 4, 192, 576, 1, None) != 0 and b"out_features" in err()
+    assert lib.swin_linear_forward(ptr, ptr, ptr, ptr, -1, 192, 768, 1, None) != 0 and b"row count" in err()
+    assert lib.swin_linear_forward(ptr, None, ptr, ptr, 4, 192, 768, 1, None) != 0 and b"non-null" in err()
+    assert lib.swin_linear_forward(ptr, ptr, odd, ptr, 4, 192, 768, 0, None) != 0 and b"16-byte aligned" in err()
+    assert lib.swin_linear_forward(ptr, ptr, ptr, ptr, 0, 192, 768, 1, None) == 0          # empty batch: no-op
+
+
 def test_backward_unpadded_entry_validates_without_gpu():
     """swin_attn_backward_unpadded: pad-gradient outputs must mirror the pad inputs; ragged shapes are accepted by the
     argument checks of this entry (and only this one); fp32 cannot be served (CUDA-core kernels need explicit padding)."""
