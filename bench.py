@@ -126,7 +126,7 @@ def run_reference(args, rank):
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args, env):
@@ -313,11 +313,24 @@ def run_ours(args, env):
         line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
                                 "sample": "1 image of the batch-8 workload, 1 warm-up + 1 timed forward, fp32 torch CPU "
                                           "(oracle restatement of the reference model)"}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+def emit(line):
+    """The one JSON line, on the process's original stdout."""
+    print(json.dumps(line), file=_STDOUT, flush=True)
+
+
+_STDOUT = sys.stdout
 
 
 def main():
+    global _STDOUT
     args = parse()
+    # stdout carries exactly one line: banners that libraries write to fd 1 (NCCL's version line) go to stderr
+    sys.stdout.flush()
+    _STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     from mde_b200.harness import dist_env, init_distributed
     env = dist_env()
     if args.impl == "reference":

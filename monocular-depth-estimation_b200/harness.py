@@ -136,7 +136,9 @@ class GraphedInference:
                 infer(model, self.static_in, bf16)
         torch.cuda.current_stream(example.device).wait_stream(side)
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # thread-local capture mode: CUDA calls of other threads (the NCCL watchdog of a multi-GPU job polls events)
+        # must not invalidate the capture
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
             self.static_out = infer(model, self.static_in, bf16)
 
     @torch.no_grad()
