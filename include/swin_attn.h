@@ -135,9 +135,25 @@ int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, c
  * newcrf_layers.py:251-253, swin_transformer.py:240-243; `x + mlp(...)` then the next block's `norm1`):
  * sum_out = x + delta in x_dtype (torch's type promotion: fp32 + bf16 -> fp32, bf16 + bf16 -> bf16, rounded once),
  * y_out = LayerNorm(sum_out) as bf16.  delta, y_out: (rows, channels) bf16; x, sum_out: (rows, channels) of x_dtype
- * (may alias).  channels in {128, 192, 256, 384, 512, 768, 1024, 1536}.  Inference only (no backward entry). */
+ * (may alias).  channels in {128, 192, 256, 384, 512, 768, 1024, 1536}. */
 int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta, float eps,
                                int64_t rows, int32_t channels, void* sum_out, void* y_out, void* stream);
+
+/* The same with the stochastic-depth gate of the branch folded in (training: `x + drop_path(branch)`,
+ * newcrf_layers.py:251,255; timm DropPath): sum_out = x + delta * gate[row / rows_per_sample] as torch.addcmul
+ * computes it (one FMA), gate: one fp32 per sample (0 or 1 / keep) or NULL (no gate); x must be fp32 with a gate.
+ * Backward of the pair (autograd of the add, the DropPath scaling and nn.LayerNorm in one pass):
+ *   dx = d_sum + LayerNormBackward(dy; sum, gamma)    (x_dtype)   -- gradient of the residual stream before the add
+ *   d_delta = bf16(dx * gate)                                      -- gradient of the bf16 branch output
+ *   dgamma, dbeta (channels) fp32, OVERWRITTEN.
+ * sum: the forward's sum_out (mean / rstd are recomputed); dy: (rows, channels) bf16 gradient of y_out;
+ * d_sum: (rows, channels) x_dtype gradient reaching sum_out through the residual stream. */
+int swin_add_layernorm_forward_gated(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta,
+                                     const float* gate, int64_t rows_per_sample, float eps, int64_t rows, int32_t channels, void* sum_out,
+                                     void* y_out, void* stream);
+int swin_add_layernorm_backward(const void* sum, int32_t x_dtype, const void* dy, const void* d_sum, const float* gamma, const float* gate,
+                                int64_t rows_per_sample, float eps, int64_t rows, int32_t channels, void* dx, void* d_delta, float* dgamma,
+                                float* dbeta, void* stream);
 
 /* Exact (erf) GELU of the block MLPs, `nn.GELU()` between fc1 and fc2 (newcrf_layers.py:9-27, swin_transformer.py Mlp),
  * on the bf16 output of the autocast fc1: y = x Phi(x), elementwise, x and y: n bf16 elements, n a multiple of 8,

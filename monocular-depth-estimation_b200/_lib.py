@@ -25,6 +25,8 @@ EXPORTS = (
     "swin_layernorm_forward",
     "swin_layernorm_backward",
     "swin_add_layernorm_forward",
+    "swin_add_layernorm_forward_gated",
+    "swin_add_layernorm_backward",
     "swin_gelu_forward",
     "swin_gelu_backward",
     "swin_linear_forward",
@@ -75,6 +77,10 @@ def load() -> ctypes.CDLL:
     lib.swin_layernorm_backward.restype = c_int
     lib.swin_add_layernorm_forward.argtypes = [vp, c_int32, vp, vp, vp, c_float, c_int64, c_int32, vp, vp, vp]
     lib.swin_add_layernorm_forward.restype = c_int
+    lib.swin_add_layernorm_forward_gated.argtypes = [vp, c_int32, vp, vp, vp, vp, c_int64, c_float, c_int64, c_int32, vp, vp, vp]
+    lib.swin_add_layernorm_forward_gated.restype = c_int
+    lib.swin_add_layernorm_backward.argtypes = [vp, c_int32, vp, vp, vp, vp, c_int64, c_float, c_int64, c_int32, vp, vp, vp, vp, vp]
+    lib.swin_add_layernorm_backward.restype = c_int
     lib.swin_gelu_forward.argtypes = [vp, vp, c_int64, vp]
     lib.swin_gelu_forward.restype = c_int
     lib.swin_gelu_backward.argtypes = [vp, vp, vp, c_int64, vp]

@@ -205,19 +205,60 @@ int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, c
   return 0;
 }
 
-int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta, float eps,
-                               int64_t rows, int32_t channels, void* sum_out, void* y_out, void* stream) {
-  if (!x || !delta || !gamma || !beta || !sum_out || !y_out) return fail("add+layernorm: all pointers must be non-null");
-  if (rows < 0) return fail("add+layernorm: bad row count");
-  if (x_dtype != SWIN_ATTN_F32 && x_dtype != SWIN_ATTN_BF16) return fail("add+layernorm: x_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
+static int add_ln_checks(const char* what, int32_t x_dtype, int64_t rows, int32_t channels, const float* gate, int64_t rows_per_sample) {
+  if (rows < 0) return fail(std::string(what) + ": bad row count");
+  if (x_dtype != SWIN_ATTN_F32 && x_dtype != SWIN_ATTN_BF16) return fail(std::string(what) + ": x_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
   if (!layernorm_supported(channels) || channels > 1536)
-    return fail("add+layernorm: channels must be one of 128, 192, 256, 384, 512, 768, 1024, 1536 (got " + std::to_string(channels) + ")");
+    return fail(std::string(what) + ": channels must be one of 128, 192, 256, 384, 512, 768, 1024, 1536 (got " + std::to_string(channels) + ")");
+  if (gate != nullptr && (rows_per_sample <= 0 || rows % rows_per_sample))
+    return fail(std::string(what) + ": with a gate, rows must be a multiple of rows_per_sample > 0");
+  if (gate != nullptr && x_dtype != SWIN_ATTN_F32) return fail(std::string(what) + ": a gate needs an fp32 residual stream");
+  return 0;
+}
+
+int swin_add_layernorm_forward_gated(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta,
+                                     const float* gate, int64_t rows_per_sample, float eps, int64_t rows, int32_t channels, void* sum_out,
+                                     void* y_out, void* stream) {
+  if (!x || !delta || !gamma || !beta || !sum_out || !y_out) return fail("add+layernorm: all pointers must be non-null");
+  if (int rc = add_ln_checks("add+layernorm", x_dtype, rows, channels, gate, rows_per_sample)) return rc;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(sum_out) | reinterpret_cast<uintptr_t>(gamma) |
        reinterpret_cast<uintptr_t>(beta)) & 7 || (reinterpret_cast<uintptr_t>(delta) | reinterpret_cast<uintptr_t>(y_out)) & 3)
     return fail("add+layernorm: pointers must be 8-byte aligned (bf16 delta / y: 4)");
   if (rows == 0) return 0;
-  cudaError_t e = launch_add_layernorm(x, x_dtype, delta, gamma, beta, eps, rows, channels, sum_out, y_out, static_cast<cudaStream_t>(stream));
+  cudaError_t e = launch_add_layernorm(x, x_dtype, delta, gamma, beta, gate, rows_per_sample, eps, rows, channels, sum_out, y_out,
+                                       static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) return fail_cuda("add+layernorm launch", e);
+  return 0;
+}
+
+int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta, const float* gamma, const float* beta, float eps,
+                               int64_t rows, int32_t channels, void* sum_out, void* y_out, void* stream) {
+  return swin_add_layernorm_forward_gated(x, x_dtype, delta, gamma, beta, nullptr, 1, eps, rows, channels, sum_out, y_out, stream);
+}
+
+int swin_add_layernorm_backward(const void* sum, int32_t x_dtype, const void* dy, const void* d_sum, const float* gamma, const float* gate,
+                                int64_t rows_per_sample, float eps, int64_t rows, int32_t channels, void* dx, void* d_delta, float* dgamma,
+                                float* dbeta, void* stream) {
+  if (!sum || !dy || !d_sum || !gamma || !dx || !d_delta || !dgamma || !dbeta)
+    return fail("add+layernorm backward: all pointers (except gate) must be non-null");
+  if (int rc = add_ln_checks("add+layernorm backward", x_dtype, rows, channels, gate, rows_per_sample)) return rc;
+  if ((reinterpret_cast<uintptr_t>(sum) | reinterpret_cast<uintptr_t>(d_sum) | reinterpret_cast<uintptr_t>(dx) |
+       reinterpret_cast<uintptr_t>(gamma)) & 7 || (reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(d_delta)) & 3)
+    return fail("add+layernorm backward: pointers must be 8-byte aligned (bf16 dy / d_delta: 4)");
+  if (rows == 0) {
+    cudaMemsetAsync(dgamma, 0, sizeof(float) * channels, static_cast<cudaStream_t>(stream));
+    cudaMemsetAsync(dbeta, 0, sizeof(float) * channels, static_cast<cudaStream_t>(stream));
+    return 0;
+  }
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  }
+  cudaError_t e = launch_add_layernorm_backward(sum, x_dtype, dy, d_sum, gamma, gate, rows_per_sample, eps, rows, channels, dx, d_delta, dgamma,
+                                                dbeta, sms, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail_cuda("add+layernorm backward launch", e);
   return 0;
 }
 

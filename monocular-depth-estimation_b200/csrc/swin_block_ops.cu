@@ -70,26 +70,32 @@ __global__ void __launch_bounds__(256) layernorm_rows_kernel(const TIn* __restri
 // s = x + delta rounded to the dtype of the residual stream (what torch's type promotion gives: fp32 + bf16 -> fp32,
 // bf16 + bf16 -> bf16), y = LayerNorm(s) as bf16.  One read of x and delta, one write of s and y, instead of
 // add (2 reads, 1 write) + norm (1 read, 1 write).
+// `gate` (optional): the stochastic-depth scale of delta, one fp32 per sample (DropPath.gate: 0 or 1 / keep), applied as
+// torch.addcmul does (one FMA): s = x + delta * gate[row / rows_per_sample].
 template <int NC, typename TX>
 __global__ void __launch_bounds__(256) add_layernorm_rows_kernel(const TX* __restrict__ x, const __nv_bfloat16* __restrict__ delta,
                                                                  const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                 const float* __restrict__ gate, int64_t rows_per_sample,
                                                                  float eps, int64_t rows, TX* __restrict__ sum_out,
                                                                  __nv_bfloat16* __restrict__ y_out) {
   constexpr int C = 64 * NC;
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows) return;
+  const float sc = gate != nullptr ? gate[row / rows_per_sample] : 1.0f;
   float2 v[NC];
   float sum = 0.f;
 #pragma unroll
   for (int k = 0; k < NC; ++k) {
     const float2 a = load2(x + row * C, lane + 32 * k), d = load2(delta + row * C, lane + 32 * k);
+    // without a gate sc == 1 and fmaf(d, 1, a) == a + d exactly
+    const float s0 = fmaf(d.x, sc, a.x), s1 = fmaf(d.y, sc, a.y);
     if constexpr (sizeof(TX) == 2) {
-      const __nv_bfloat162 r = __floats2bfloat162_rn(a.x + d.x, a.y + d.y);
+      const __nv_bfloat162 r = __floats2bfloat162_rn(s0, s1);
       reinterpret_cast<__nv_bfloat162*>(sum_out + row * C)[lane + 32 * k] = r;
       v[k] = __bfloat1622float2(r);
     } else {
-      v[k] = make_float2(a.x + d.x, a.y + d.y);
+      v[k] = make_float2(s0, s1);
       reinterpret_cast<float2*>(sum_out + row * C)[lane + 32 * k] = v[k];
     }
     sum += v[k].x + v[k].y;
@@ -123,11 +129,17 @@ __global__ void __launch_bounds__(256) add_layernorm_rows_kernel(const TX* __res
 // One warp per row, grid-stride over rows; every warp accumulates its dgamma / dbeta partials in a private shared-
 // memory row (lane l owns the same channels for every row, so there are no conflicts and no atomics), the CTA
 // reduces its 8 rows at the end and adds them to global memory with one atomic per channel.
-template <int NC, typename TX, typename TDy>
+// kResidual: backward of the fused residual add + LayerNorm (add_layernorm_rows_kernel).  `gsum` is the gradient that
+// reaches the sum through the residual stream; dx = gsum + (LayerNorm backward of dy) is the gradient of the stream
+// before the add, and ddelta = bf16(dx * gate) that of the bf16 branch output -- one pass instead of LayerNorm
+// backward + autograd's gradient accumulation + the cast / gate multiply of the branch gradient.
+template <int NC, typename TX, typename TDy, bool kResidual = false>
 __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const TX* __restrict__ x, const TDy* __restrict__ dy,
                                                             const float* __restrict__ gamma, float eps, int64_t rows,
                                                             TX* __restrict__ dx, float* __restrict__ dgamma,
-                                                            float* __restrict__ dbeta) {
+                                                            float* __restrict__ dbeta, const TX* __restrict__ gsum = nullptr,
+                                                            const float* __restrict__ gate = nullptr, int64_t rows_per_sample = 1,
+                                                            __nv_bfloat16* __restrict__ ddelta = nullptr) {
   constexpr int C = 64 * NC;
   extern __shared__ __align__(16) float2 acc[];   // [8 warps][2 (dgamma, dbeta)][C / 2]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -186,9 +198,17 @@ __global__ void __launch_bounds__(256) layernorm_bwd_kernel(const TX* __restrict
     }
     s1 *= (1.0f / C);
     s2 *= (1.0f / C);
+    float sc = 1.0f;
+    if constexpr (kResidual) sc = gate != nullptr ? gate[row / rows_per_sample] : 1.0f;
 #pragma unroll
     for (int k = 0; k < NC; ++k) {
-      const float y0 = rstd * (d[k].x - s1 - v[k].x * s2), y1 = rstd * (d[k].y - s1 - v[k].y * s2);
+      float y0 = rstd * (d[k].x - s1 - v[k].x * s2), y1 = rstd * (d[k].y - s1 - v[k].y * s2);
+      if constexpr (kResidual) {
+        const float2 g = load2(gsum + row * C, lane + 32 * k);
+        y0 += g.x;
+        y1 += g.y;
+        reinterpret_cast<__nv_bfloat162*>(ddelta + row * C)[lane + 32 * k] = __floats2bfloat162_rn(y0 * sc, y1 * sc);
+      }
       if constexpr (sizeof(TX) == 2) {
         reinterpret_cast<__nv_bfloat162*>(dx + row * C)[lane + 32 * k] = __floats2bfloat162_rn(y0, y1);
       } else {
@@ -224,7 +244,8 @@ static cudaError_t launch_ln_bwd(const void* x, int x_dtype, const void* dy, int
   do {                                                                                                              \
     auto k = layernorm_bwd_kernel<NC, TX, TDY>;                                                                     \
     if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e; \
-    k<<<grid, 256, smem, st>>>(static_cast<const TX*>(x), static_cast<const TDY*>(dy), g, eps, rows, static_cast<TX*>(dx), dgamma, dbeta); \
+    k<<<grid, 256, smem, st>>>(static_cast<const TX*>(x), static_cast<const TDY*>(dy), g, eps, rows, static_cast<TX*>(dx), dgamma, dbeta, \
+                               nullptr, nullptr, 1, nullptr);                                                        \
   } while (0)
   if (x_dtype == SWIN_ATTN_F32 && dy_dtype == SWIN_ATTN_F32) SWIN_LN_BWD(float, float);
   else if (x_dtype == SWIN_ATTN_F32) SWIN_LN_BWD(float, bf);
@@ -233,6 +254,46 @@ static cudaError_t launch_ln_bwd(const void* x, int x_dtype, const void* dy, int
 #undef SWIN_LN_BWD
   count_launch();
   return cudaGetLastError();
+}
+
+template <int NC>
+static cudaError_t launch_add_ln_bwd(const void* x, int x_dtype, const void* dy, const void* gsum, const float* g, const float* gate,
+                                     int64_t rows_per_sample, float eps, int64_t rows, void* dx, void* ddelta, float* dgamma, float* dbeta,
+                                     int sms, cudaStream_t st) {
+  const size_t smem = (size_t)8 * 2 * 64 * NC * sizeof(float);
+  int64_t want = (rows + 7) / 8;
+  const int64_t cap = (int64_t)sms * (smem > 96 * 1024 ? 1 : smem > 48 * 1024 ? 2 : 4);
+  const unsigned grid = (unsigned)(want < cap ? want : cap);
+  cudaError_t e = cudaMemsetAsync(dgamma, 0, sizeof(float) * 64 * NC, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(dbeta, 0, sizeof(float) * 64 * NC, st);
+  if (e != cudaSuccess) return e;
+  using bf = __nv_bfloat16;
+  if (x_dtype == SWIN_ATTN_F32) {
+    auto k = layernorm_bwd_kernel<NC, float, bf, true>;
+    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    k<<<grid, 256, smem, st>>>(static_cast<const float*>(x), static_cast<const bf*>(dy), g, eps, rows, static_cast<float*>(dx), dgamma, dbeta,
+                               static_cast<const float*>(gsum), gate, rows_per_sample, static_cast<bf*>(ddelta));
+  } else {
+    auto k = layernorm_bwd_kernel<NC, bf, bf, true>;
+    if ((e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    k<<<grid, 256, smem, st>>>(static_cast<const bf*>(x), static_cast<const bf*>(dy), g, eps, rows, static_cast<bf*>(dx), dgamma, dbeta,
+                               static_cast<const bf*>(gsum), gate, rows_per_sample, static_cast<bf*>(ddelta));
+  }
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_add_layernorm_backward(const void* x, int x_dtype, const void* dy, const void* gsum, const float* g, const float* gate,
+                                          int64_t rows_per_sample, float eps, int64_t rows, int channels, void* dx, void* ddelta,
+                                          float* dgamma, float* dbeta, int sms, cudaStream_t st) {
+  switch (channels / 64) {
+#define SWIN_LN_CASE(NC) \
+  case NC: return launch_add_ln_bwd<NC>(x, x_dtype, dy, gsum, g, gate, rows_per_sample, eps, rows, dx, ddelta, dgamma, dbeta, sms, st)
+    SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
+    SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24);
+#undef SWIN_LN_CASE
+    default: return cudaErrorInvalidValue;
+  }
 }
 
 cudaError_t launch_layernorm_backward(const void* x, int x_dtype, const void* dy, int dy_dtype, const float* g, float eps, int64_t rows,
@@ -275,24 +336,25 @@ cudaError_t launch_layernorm(const void* x, int x_dtype, const float* g, const f
 }
 
 template <int NC>
-static cudaError_t launch_add_ln(const void* x, int x_dtype, const void* delta, const float* g, const float* b, float eps, int64_t rows,
-                                 void* sum_out, void* y_out, cudaStream_t st) {
+static cudaError_t launch_add_ln(const void* x, int x_dtype, const void* delta, const float* g, const float* b, const float* gate,
+                                 int64_t rows_per_sample, float eps, int64_t rows, void* sum_out, void* y_out, cudaStream_t st) {
   const unsigned grid = (unsigned)((rows + 7) / 8);
   using bf = __nv_bfloat16;
   if (x_dtype == SWIN_ATTN_F32)
-    add_layernorm_rows_kernel<NC, float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), static_cast<const bf*>(delta), g, b, eps, rows,
-                                                               static_cast<float*>(sum_out), static_cast<bf*>(y_out));
+    add_layernorm_rows_kernel<NC, float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), static_cast<const bf*>(delta), g, b, gate, rows_per_sample,
+                                                               eps, rows, static_cast<float*>(sum_out), static_cast<bf*>(y_out));
   else
-    add_layernorm_rows_kernel<NC, bf><<<grid, 256, 0, st>>>(static_cast<const bf*>(x), static_cast<const bf*>(delta), g, b, eps, rows,
-                                                            static_cast<bf*>(sum_out), static_cast<bf*>(y_out));
+    add_layernorm_rows_kernel<NC, bf><<<grid, 256, 0, st>>>(static_cast<const bf*>(x), static_cast<const bf*>(delta), g, b, gate, rows_per_sample, eps,
+                                                            rows, static_cast<bf*>(sum_out), static_cast<bf*>(y_out));
   count_launch();
   return cudaGetLastError();
 }
 
-cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, const float* g, const float* b, float eps, int64_t rows,
-                                 int channels, void* sum_out, void* y_out, cudaStream_t st) {
+cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, const float* g, const float* b, const float* gate,
+                                 int64_t rows_per_sample, float eps, int64_t rows, int channels, void* sum_out, void* y_out,
+                                 cudaStream_t st) {
   switch (channels / 64) {
-#define SWIN_LN_CASE(NC) case NC: return launch_add_ln<NC>(x, x_dtype, delta, g, b, eps, rows, sum_out, y_out, st)
+#define SWIN_LN_CASE(NC) case NC: return launch_add_ln<NC>(x, x_dtype, delta, g, b, gate, rows_per_sample, eps, rows, sum_out, y_out, st)
     SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
     SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24);
 #undef SWIN_LN_CASE

@@ -144,8 +144,12 @@ cudaError_t launch_layernorm(const void* x, int x_dtype, const float* gamma, con
                              void* out, int out_dtype, cudaStream_t st);
 cudaError_t launch_layernorm_backward(const void* x, int x_dtype, const void* dy, int dy_dtype, const float* gamma, float eps, int64_t rows,
                                       int channels, void* dx, float* dgamma, float* dbeta, int sms, cudaStream_t st);
-cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, const float* gamma, const float* beta, float eps,
-                                 int64_t rows, int channels, void* sum_out, void* y_out, cudaStream_t st);
+cudaError_t launch_add_layernorm(const void* x, int x_dtype, const void* delta, const float* gamma, const float* beta, const float* gate,
+                                 int64_t rows_per_sample, float eps, int64_t rows, int channels, void* sum_out, void* y_out,
+                                 cudaStream_t st);
+cudaError_t launch_add_layernorm_backward(const void* x, int x_dtype, const void* dy, const void* gsum, const float* gamma, const float* gate,
+                                          int64_t rows_per_sample, float eps, int64_t rows, int channels, void* dx, void* ddelta,
+                                          float* dgamma, float* dbeta, int sms, cudaStream_t st);
 cudaError_t launch_gelu(const void* x, const void* dy, void* out, int64_t n, cudaStream_t st);
 cudaError_t launch_colsum(const void* dy, int64_t rows, int cols, float* out, int sms, cudaStream_t st);
 bool layernorm_supported(int channels);

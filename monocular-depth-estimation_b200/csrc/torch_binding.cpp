@@ -338,8 +338,19 @@ Tensor layer_norm_meta(const Tensor& x, const Tensor&, const Tensor&, double, bo
   return at::empty_symint(x.sym_sizes(), x.options().dtype(out_bf16 ? at::kBFloat16 : at::kFloat));
 }
 
+// gate: per-sample stochastic-depth scale (B, 1, .., 1) fp32 or None; rows_per_sample = rows / B
+static const float* gate_ptr(const optional<Tensor>& scale, const Tensor& x, Tensor& holder, int64_t& rows_per_sample) {
+  rows_per_sample = 1;
+  if (!scale.has_value() || !scale->defined()) return nullptr;
+  TORCH_CHECK(x.dim() >= 2 && scale->numel() == x.size(0), "swin_attn::add_layer_norm: scale must hold one value per sample");
+  TORCH_CHECK(x.scalar_type() == at::kFloat, "swin_attn::add_layer_norm: a scale needs an fp32 residual stream");
+  holder = scale->detach().to(at::kFloat).contiguous();
+  rows_per_sample = x.numel() / x.size(-1) / x.size(0);
+  return holder.data_ptr<float>();
+}
+
 std::tuple<Tensor, Tensor> add_layer_norm_cuda(const Tensor& x_in, const Tensor& delta_in, const Tensor& weight, const Tensor& bias,
-                                               double eps) {
+                                               double eps, const optional<Tensor>& scale) {
   const int32_t xd = dtype_code(x_in.scalar_type());
   TORCH_CHECK(delta_in.scalar_type() == at::kBFloat16, "swin_attn::add_layer_norm: delta must be bfloat16");
   TORCH_CHECK(delta_in.sizes() == x_in.sizes(), "swin_attn::add_layer_norm: x and delta must have the same shape");
@@ -349,15 +360,50 @@ std::tuple<Tensor, Tensor> add_layer_norm_cuda(const Tensor& x_in, const Tensor&
   Tensor y = at::empty(x.sizes(), x.options().dtype(at::kBFloat16));
   const Tensor w = weight.detach().to(at::kFloat).contiguous(), b = bias.detach().to(at::kFloat).contiguous();
   if (x.numel() == 0) return {sum, y};
+  Tensor gate_holder;
+  int64_t rps = 1;
+  const float* gate = gate_ptr(scale, x, gate_holder, rps);
   c10::cuda::CUDAGuard guard(x.device());
-  check_rc(swin_add_layernorm_forward(x.data_ptr(), xd, delta.data_ptr(), w.data_ptr<float>(), b.data_ptr<float>(), (float)eps,
-                                      c ? x.numel() / c : 0, (int32_t)c, sum.data_ptr(), y.data_ptr(),
-                                      at::cuda::getCurrentCUDAStream()));
+  check_rc(swin_add_layernorm_forward_gated(x.data_ptr(), xd, delta.data_ptr(), w.data_ptr<float>(), b.data_ptr<float>(), gate, rps,
+                                            (float)eps, c ? x.numel() / c : 0, (int32_t)c, sum.data_ptr(), y.data_ptr(),
+                                            at::cuda::getCurrentCUDAStream()));
   return {sum, y};
 }
 
-std::tuple<Tensor, Tensor> add_layer_norm_meta(const Tensor& x, const Tensor&, const Tensor&, const Tensor&, double) {
+std::tuple<Tensor, Tensor> add_layer_norm_meta(const Tensor& x, const Tensor&, const Tensor&, const Tensor&, double,
+                                               const optional<Tensor>&) {
   return {at::empty_symint(x.sym_sizes(), x.options()), at::empty_symint(x.sym_sizes(), x.options().dtype(at::kBFloat16))};
+}
+
+// backward of the pair: (dx, d_delta, dgamma, dbeta)
+std::tuple<Tensor, Tensor, Tensor, Tensor> add_layer_norm_bwd_cuda(const Tensor& d_sum_in, const Tensor& dy_in, const Tensor& sum_in,
+                                                                   const Tensor& weight, double eps, const optional<Tensor>& scale) {
+  const int32_t xd = dtype_code(sum_in.scalar_type());
+  TORCH_CHECK(dy_in.scalar_type() == at::kBFloat16 && d_sum_in.scalar_type() == sum_in.scalar_type(),
+              "swin_attn::add_layer_norm_bwd: dy must be bfloat16 and d_sum of the stream dtype");
+  TORCH_CHECK(dy_in.sizes() == sum_in.sizes() && d_sum_in.sizes() == sum_in.sizes(), "swin_attn::add_layer_norm_bwd: shape mismatch");
+  const Tensor sum = sum_in.contiguous(), dy = dy_in.contiguous(), d_sum = d_sum_in.contiguous();
+  const int64_t c = sum.size(-1);
+  Tensor dx = at::empty_like(sum);
+  Tensor d_delta = at::empty(sum.sizes(), sum.options().dtype(at::kBFloat16));
+  Tensor dgamma = at::zeros({c}, sum.options().dtype(at::kFloat)), dbeta = at::zeros({c}, sum.options().dtype(at::kFloat));
+  if (sum.numel() == 0) return {dx, d_delta, dgamma, dbeta};
+  const Tensor w = weight.detach().to(at::kFloat).contiguous();
+  Tensor gate_holder;
+  int64_t rps = 1;
+  const float* gate = gate_ptr(scale, sum, gate_holder, rps);
+  c10::cuda::CUDAGuard guard(sum.device());
+  check_rc(swin_add_layernorm_backward(sum.data_ptr(), xd, dy.data_ptr(), d_sum.data_ptr(), w.data_ptr<float>(), gate, rps, (float)eps,
+                                       sum.numel() / c, (int32_t)c, dx.data_ptr(), d_delta.data_ptr(), dgamma.data_ptr<float>(),
+                                       dbeta.data_ptr<float>(), at::cuda::getCurrentCUDAStream()));
+  return {dx, d_delta, dgamma, dbeta};
+}
+
+std::tuple<Tensor, Tensor, Tensor, Tensor> add_layer_norm_bwd_meta(const Tensor&, const Tensor&, const Tensor& sum, const Tensor& weight, double,
+                                                                   const optional<Tensor>&) {
+  return {at::empty_symint(sum.sym_sizes(), sum.options()), at::empty_symint(sum.sym_sizes(), sum.options().dtype(at::kBFloat16)),
+          at::empty_symint({sum.sym_size(-1)}, sum.options().dtype(at::kFloat)),
+          at::empty_symint({sum.sym_size(-1)}, sum.options().dtype(at::kFloat))};
 }
 
 Tensor gelu_cuda(const Tensor& x_in) {
@@ -580,6 +626,43 @@ struct LayerNormFunction : public torch::autograd::Function<LayerNormFunction> {
   }
 };
 
+// (sum, y) = add_layer_norm(x, delta, weight, bias, eps, scale): residual add (+ DropPath gate) + LayerNorm as one node
+struct AddLayerNormFunction : public torch::autograd::Function<AddLayerNormFunction> {
+  static variable_list forward(AutogradContext* ctx, const Tensor& x, const Tensor& delta, const Tensor& weight, const Tensor& bias,
+                               double eps, const optional<Tensor>& scale) {
+    at::AutoDispatchBelowADInplaceOrView guard;
+    static auto op = c10::Dispatcher::singleton()
+                         .findSchemaOrThrow("swin_attn::add_layer_norm", "")
+                         .typed<std::tuple<Tensor, Tensor>(const Tensor&, const Tensor&, const Tensor&, const Tensor&, double,
+                                                           const optional<Tensor>&)>();
+    auto out = op.call(x, delta, weight, bias, eps, scale);
+    ctx->save_for_backward({std::get<0>(out), weight, scale.has_value() ? *scale : Tensor()});
+    ctx->saved_data["eps"] = eps;
+    return {std::get<0>(out), std::get<1>(out)};
+  }
+
+  static variable_list backward(AutogradContext* ctx, variable_list grads) {
+    static auto op = c10::Dispatcher::singleton()
+                         .findSchemaOrThrow("swin_attn::add_layer_norm_bwd", "")
+                         .typed<std::tuple<Tensor, Tensor, Tensor, Tensor>(const Tensor&, const Tensor&, const Tensor&, const Tensor&, double,
+                                                                           const optional<Tensor>&)>();
+    const auto saved = ctx->get_saved_variables();
+    const Tensor &sum = saved[0], &weight = saved[1];
+    const optional<Tensor> scale = saved[2].defined() ? optional<Tensor>(saved[2]) : c10::nullopt;
+    const Tensor d_sum = grads[0].defined() ? grads[0].to(sum.scalar_type()) : at::zeros_like(sum);
+    const Tensor dy = grads[1].defined() ? grads[1].to(at::kBFloat16) : at::zeros(sum.sizes(), sum.options().dtype(at::kBFloat16));
+    auto out = op.call(d_sum, dy, sum, weight, ctx->saved_data["eps"].toDouble(), scale);
+    return {std::get<0>(out), std::get<1>(out), std::get<2>(out).to(weight.scalar_type()), std::get<3>(out).to(weight.scalar_type()),
+            Tensor(), Tensor()};
+  }
+};
+
+std::tuple<Tensor, Tensor> add_layer_norm_autograd(const Tensor& x, const Tensor& delta, const Tensor& weight, const Tensor& bias, double eps,
+                                                   const optional<Tensor>& scale) {
+  auto out = AddLayerNormFunction::apply(x, delta, weight, bias, eps, scale);
+  return {out[0], out[1]};
+}
+
 struct GeluFunction : public torch::autograd::Function<GeluFunction> {
   static Tensor forward(AutogradContext* ctx, const Tensor& x) {
     at::AutoDispatchBelowADInplaceOrView guard;
@@ -614,8 +697,12 @@ struct LinearFunction : public torch::autograd::Function<LinearFunction> {
     Tensor dx, dw, db;
     if (ctx->needs_input_grad(0))
       dx = at::mm(dy, wb).view(xb.sizes()).to((at::ScalarType)ctx->saved_data["x_dtype"].toInt());
-    if (ctx->needs_input_grad(1))
-      dw = at::mm(dy.t(), xb.reshape({-1, k})).to((at::ScalarType)ctx->saved_data["w_dtype"].toInt());
+    if (ctx->needs_input_grad(1)) {
+      // fp32 master weights: cuBLAS writes the fp32 gradient directly (autocast rounds it to bf16 and casts it back
+      // in a second kernel)
+      const auto wd = (at::ScalarType)ctx->saved_data["w_dtype"].toInt();
+      dw = wd == at::kFloat ? at::mm(dy.t(), xb.reshape({-1, k}), at::kFloat) : at::mm(dy.t(), xb.reshape({-1, k})).to(wd);
+    }
     const int64_t bd = ctx->saved_data["b_dtype"].toInt();
     if (bd >= 0 && ctx->needs_input_grad(2)) db = (n % 8 == 0 ? op.call(dy) : dy.sum(0)).to((at::ScalarType)bd);
     return {dx, dw, db};
@@ -643,7 +730,9 @@ TORCH_LIBRARY(swin_attn, m) {
         "Tensor? v_pad, int window, int shift, int num_heads, float scale) -> (Tensor, Tensor, Tensor, Tensor, Tensor)");
   m.def("layer_norm(Tensor x, Tensor weight, Tensor bias, float eps, bool out_bf16) -> Tensor");
   m.def("layer_norm_bwd(Tensor dy, Tensor x, Tensor weight, float eps) -> (Tensor, Tensor, Tensor)");
-  m.def("add_layer_norm(Tensor x, Tensor delta, Tensor weight, Tensor bias, float eps) -> (Tensor, Tensor)");
+  m.def("add_layer_norm(Tensor x, Tensor delta, Tensor weight, Tensor bias, float eps, Tensor? scale=None) -> (Tensor, Tensor)");
+  m.def("add_layer_norm_bwd(Tensor d_sum, Tensor dy, Tensor sum, Tensor weight, float eps, Tensor? scale=None) "
+        "-> (Tensor, Tensor, Tensor, Tensor)");
   m.def("linear(Tensor x, Tensor weight, Tensor? bias) -> Tensor");
   m.def("bias_grad(Tensor dy) -> Tensor");
   m.def("gelu(Tensor x) -> Tensor");
@@ -658,6 +747,7 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("layer_norm", layer_norm_cuda);
   m.impl("layer_norm_bwd", layer_norm_bwd_cuda);
   m.impl("add_layer_norm", add_layer_norm_cuda);
+  m.impl("add_layer_norm_bwd", add_layer_norm_bwd_cuda);
   m.impl("linear", linear_any);
   m.impl("bias_grad", bias_grad_cuda);
   m.impl("gelu", gelu_cuda);
@@ -672,6 +762,7 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("layer_norm", layer_norm_meta);
   m.impl("layer_norm_bwd", layer_norm_bwd_meta);
   m.impl("add_layer_norm", add_layer_norm_meta);
+  m.impl("add_layer_norm_bwd", add_layer_norm_bwd_meta);
   m.impl("linear", linear_any);
   m.impl("bias_grad", bias_grad_meta);
   m.impl("gelu", gelu_meta);
@@ -682,7 +773,7 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
 TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
   m.impl("fwd", fwd_autograd);
   m.impl("layer_norm", layer_norm_autograd);
-  m.impl("add_layer_norm", torch::autograd::autogradNotImplementedFallback());   // inference only
+  m.impl("add_layer_norm", add_layer_norm_autograd);
   m.impl("gelu", gelu_autograd);
   m.impl("linear", linear_autograd);
   m.impl("linear_act", torch::autograd::autogradNotImplementedFallback());   // inference only

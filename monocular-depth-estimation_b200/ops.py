@@ -157,16 +157,18 @@ def residual(x: Tensor, delta: Tensor, scale: Optional[Tensor] = None) -> Tensor
 
 def add_norm(norm: torch.nn.Module, x: Tensor, delta: Tensor, scale: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
     """``x + delta`` and ``norm(x + delta)`` as the operand of the following Linear: the residual add of a block
-    with the LayerNorm behind it (``norm2`` of the same block, ``norm1`` of the next one).  One fused kernel for
-    inference under bf16 autocast (bf16 ``delta``, <= 1536 channels); otherwise the two separate steps.  ``scale`` is
-    the stochastic-depth gate of ``delta`` (training only)."""
-    if (scale is None and type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
+    with the LayerNorm behind it (``norm2`` of the same block, ``norm1`` of the next one).  One fused kernel under bf16
+    autocast (bf16 ``delta``, <= 1536 channels), in training one autograd node whose backward is one kernel as well
+    (LayerNorm backward + the gradient arriving through the residual stream + the bf16 / gated gradient of the branch);
+    otherwise the two separate steps.  ``scale`` is the stochastic-depth gate of ``delta`` (training only, one value
+    per sample, fp32 stream)."""
+    if (type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
             and x.dtype in _DTYPES and delta.dtype == torch.bfloat16 and delta.shape == x.shape
             and torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") == torch.bfloat16
             and len(norm.normalized_shape) == 1 and x.shape[-1] in _LN_CHANNELS and x.shape[-1] <= 1536
-            and not (torch.is_grad_enabled() and (x.requires_grad or delta.requires_grad or norm.weight.requires_grad
-                                                  or norm.bias.requires_grad))):
-        return torch.ops.swin_attn.add_layer_norm(x, delta, norm.weight, norm.bias, norm.eps)
+            and (scale is None or (x.dtype == torch.float32 and x.dim() >= 2 and scale.numel() == x.shape[0]))):
+        out = torch.ops.swin_attn.add_layer_norm(x, delta, norm.weight, norm.bias, norm.eps, scale)
+        return out[0], out[1]
     x = residual(x, delta, scale)
     return x, norm_for_linear(norm, x)
 

@@ -675,9 +675,10 @@ def test_linear_gelu_in_model_is_bit_identical_to_unfused(monkeypatch):
 
 @pytest.mark.parametrize("shape", [(3, 50, 192, 576), (2, 7, 9, 128, 256), (1, 4099, 768, 3072), (5, 33, 1024, 1024)])
 def test_linear_with_fused_bias_grad_matches_autocast_linear(shape):
-    """swin_attn::linear (training path of qkv / qk / proj / fc1 / fc2): same output and input / weight gradients as
-    nn.Linear under autocast (same cuBLAS calls on the same bf16 operands); the bias gradient is the fp32 column sum
-    of the bf16 dy -- at least as close to the fp64 sum as autocast's bf16-rounded one."""
+    """swin_attn::linear (training path of qkv / qk / proj / fc1 / fc2): same output and input gradient as nn.Linear
+    under autocast (same cuBLAS calls on the same bf16 operands); the weight gradient is the same product written in
+    fp32, the bias gradient the fp32 column sum of the bf16 dy -- both at least as close to the fp64 values as
+    autocast's bf16-rounded ones."""
     *lead, k, n = shape
     gen = torch.Generator(device=DEV).manual_seed(sum(shape))
     lin = torch.nn.Linear(k, n).to(DEV)
@@ -691,7 +692,10 @@ def test_linear_with_fused_bias_grad_matches_autocast_linear(shape):
     gg = torch.autograd.grad(got, [x, lin.weight, lin.bias], cot)
     for a, b in zip(gg, gw):
         assert a.dtype == b.dtype == torch.float32 and a.shape == b.shape
-    assert torch.equal(gg[0], gw[0]) and torch.equal(gg[1], gw[1])
+    assert torch.equal(gg[0], gw[0])
+    # weight gradient: written in fp32 by the GEMM (autocast rounds it to bf16 first) -- closer to the fp64 product
+    exact_w = cot.double().reshape(-1, n).t() @ x.detach().bfloat16().double().reshape(-1, k)
+    assert rel_err(gg[1], gw[1]) <= 4e-3 and rel_err(gg[1], exact_w) <= rel_err(gw[1], exact_w) + 1e-6
     exact = cot.double().reshape(-1, n).sum(0)
     assert rel_err(gg[2], exact) < 1e-5
     assert rel_err(gg[2], exact) <= rel_err(gw[2], exact) + 1e-6
@@ -829,3 +833,57 @@ def test_patch_embed_gemm_path_matches_autocast_conv(hw):
     with torch.autocast("cuda", dtype=torch.bfloat16):          # training keeps the conv (differentiable, same values)
         trained = pe(x)
     assert trained.requires_grad and rel_err(trained.detach(), want) <= TOL_BF16
+
+
+@pytest.mark.parametrize("channels,gated", [(192, True), (768, True), (128, False), (1536, False)])
+def test_add_norm_training_node_matches_unfused_autograd(channels, gated):
+    """swin_add_layernorm_forward_gated / swin_add_layernorm_backward through ops.add_norm in training: outputs and all
+    gradients (residual stream, bf16 branch, LayerNorm weight / bias) against the unfused autograd graph
+    (torch.addcmul + the fused LayerNorm node) and against fp64."""
+    gen = torch.Generator(device=DEV).manual_seed(channels)
+    b, l = 3, 70
+    ln = torch.nn.LayerNorm(channels).to(DEV)
+    with torch.no_grad():
+        ln.weight.copy_(1 + 0.3 * torch.randn(channels, device=DEV, generator=gen))
+        ln.bias.copy_(0.3 * torch.randn(channels, device=DEV, generator=gen))
+    x = torch.randn(b, l, channels, device=DEV, generator=gen)
+    delta = torch.randn(b, l, channels, device=DEV, generator=gen).bfloat16()
+    scale = (torch.tensor([0.0, 1 / 0.9, 1 / 0.9], device=DEV).view(b, 1, 1).bfloat16() if gated else None)
+    cot_s = torch.randn(b, l, channels, device=DEV, generator=gen)
+    cot_y = torch.randn(b, l, channels, device=DEV, generator=gen).bfloat16()
+
+    def run(fn, dtype=None):
+        xs = (x if dtype is None else x.to(dtype)).clone().requires_grad_()
+        ds = (delta if dtype is None else delta.to(dtype)).clone().requires_grad_()
+        mod = ln if dtype is None else torch.nn.LayerNorm(channels).to(DEV, dtype)
+        if dtype is not None:
+            mod.load_state_dict({k: v.to(dtype) for k, v in ln.state_dict().items()})
+        s, y = fn(mod, xs, ds)
+        gs = torch.autograd.grad([s, y], [xs, ds, mod.weight, mod.bias], [cot_s.to(s.dtype), cot_y.to(y.dtype)])
+        return (s, y) + gs
+
+    def unfused(mod, xs, ds):
+        s = ops.residual(xs, ds, scale)
+        return s, ops.norm_for_linear(mod, s)
+
+    def exact(mod, xs, ds):
+        s = xs + ds * (scale.double() if gated else 1.0)
+        return s, mod(s)
+
+    before = _lib.launch_count()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        got = run(lambda m, a, d: ops.add_norm(m, a, d, scale))
+        fused_launches = _lib.launch_count() - before
+        want = run(unfused)
+    ref = run(exact, torch.float64)
+    assert fused_launches == 2                                   # one forward kernel, one backward kernel
+    assert got[0].dtype == torch.float32 and got[1].dtype == torch.bfloat16 and got[3].dtype == torch.bfloat16
+    assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+    names = ["sum", "y", "dx", "d_delta", "dgamma", "dbeta"]
+    for n, g, w, r in zip(names, got, want, ref):
+        assert g.shape == w.shape and g.dtype == w.dtype, n
+        tol = TOL_BF16 if g.dtype == torch.bfloat16 else 2e-5
+        assert rel_err(g, r) <= tol, (n, rel_err(g, r))
+        assert rel_err(g, r) <= rel_err(w, r) * 1.5 + 1e-6, (n, rel_err(g, r), rel_err(w, r))
+    if gated:
+        assert float(got[3][0].float().abs().max()) == 0.0       # dropped sample: no gradient into the branch
