@@ -187,6 +187,13 @@ int swin_linear_bias_grad(const void* dy, int64_t rows, int32_t cols, float* dbi
 int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int32_t dy_dtype, const float* gamma, float eps, int64_t rows,
                             int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream);
 
+/* Measurement hook: arms a pair of cudaEvent_t for the calling thread.  The next attention / linear entry point this
+ * thread calls records `start_event` immediately before and `stop_event` immediately after its device work (kernel
+ * plus its memsets) on the op's stream -- after the host-side preparation (tensor-map encoding), so a host-bound
+ * caller does not count its own launch path as kernel time -- and disarms.  NULL, NULL disarms.  (No counterpart in
+ * the reference, which has no timing of its own; used by bench.py's live roofline.) */
+void swin_attn_time_next_launch(void* start_event, void* stop_event);
+
 /* Number of kernel launches issued by this library since load (all threads). */
 uint64_t swin_attn_launch_count(void);
 

@@ -31,6 +31,7 @@ EXPORTS = (
     "swin_gelu_backward",
     "swin_linear_forward",
     "swin_linear_bias_grad",
+    "swin_attn_time_next_launch",
     "swin_attn_launch_count",
     "swin_attn_uses_tcgen05",
     "swin_attn_last_error",

@@ -12,6 +12,12 @@ namespace swin {
 static std::atomic<uint64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 static thread_local std::string g_error;
+static thread_local LaunchEvents g_launch_events;
+LaunchEvents take_launch_events() {
+  const LaunchEvents ev = g_launch_events;
+  g_launch_events = LaunchEvents();
+  return ev;
+}
 static long long* g_trace = nullptr;
 
 static int fail(const std::string& msg) {
@@ -340,6 +346,11 @@ int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int3
 // Debug hook (not part of the public header): device buffer of >= 16 * pairs-per-CTA int64 that receives
 // clock64 stamps of CTA 0 of the tcgen05 kernel; pass NULL to switch tracing off.
 void swin_attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }
+
+void swin_attn_time_next_launch(void* start_event, void* stop_event) {
+  g_launch_events.start = static_cast<cudaEvent_t>(start_event);
+  g_launch_events.stop = static_cast<cudaEvent_t>(stop_event);
+}
 
 uint64_t swin_attn_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 

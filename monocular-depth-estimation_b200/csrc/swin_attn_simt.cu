@@ -476,7 +476,10 @@ static cudaError_t launch_fwd(const Problem& p, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(simt_fwd_kernel<T, WS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int items = p.B * p.nWy * p.nWx * p.nH;
-  simt_fwd_kernel<T, WS><<<items, kThreads, smem, st>>>(p);
+  {
+    TimedRegion timed(st);
+    simt_fwd_kernel<T, WS><<<items, kThreads, smem, st>>>(p);
+  }
   count_launch();
   return cudaGetLastError();
 }
@@ -498,6 +501,7 @@ static cudaError_t launch_bwd(const Problem& p, cudaStream_t st) {
   if (ctas > items) ctas = items;
   int chunk = (items + ctas - 1) / ctas;
   ctas = (items + chunk - 1) / chunk;
+  TimedRegion timed(st);
   e = cudaMemsetAsync(p.d_table, 0, sizeof(float) * Tile<WS>::NT * p.nH, st);
   if (e != cudaSuccess) return e;
   simt_bwd_kernel<T, WS><<<ctas, kThreads, smem, st>>>(p, n_win, chunk);

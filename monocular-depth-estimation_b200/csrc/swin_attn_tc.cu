@@ -81,6 +81,7 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   const int w1 = min(w0 + win_per_job, n_win);
   const int n_pairs = (w1 - w0 + 1) >> 1;
   if (tid == 0) TC_TRACE(p, 0, 14);   // kernel entry
+  if (tid == 0) TC_TRACE_CTA(p, 0);
 
   const uint32_t bar_qk_full = sbase + map.bars;               // [kQKStages] TMA -> S MMA
   const uint32_t bar_qk_empty = bar_qk_full + 8 * kQKStages;   // [kQKStages] S MMA -> producers
@@ -434,6 +435,7 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 512);
   if (tid == 0) TC_TRACE(p, 0, 15);   // kernel exit
+  if (tid == 0) TC_TRACE_CTA(p, 1);
 }
 
 }  // namespace tcf
@@ -550,7 +552,10 @@ cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** er
   const int has_pad = (p.H != p.Hp || p.W != p.Wp) && (p.k_pad != nullptr || p.v_pad != nullptr) ? 1 : 0;
   int n_win, per, grid;
   tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
-  kernel<<<grid, tcf::kThreadsF, map.total, st>>>(p, n_win, per, has_pad, maps);
+  {
+    TimedRegion timed(st);
+    kernel<<<grid, tcf::kThreadsF, map.total, st>>>(p, n_win, per, has_pad, maps);
+  }
   count_launch();
   return cudaGetLastError();
 }

@@ -158,10 +158,20 @@ __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
 #define TMEM_LD_X2(taddr, r0, r1) \
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(taddr))
 
-// debug timeline (see swin_attn_debug_set_trace): event e of local pair n of CTA 0
+// debug timeline (see swin_attn_debug_set_trace): event e of local pair n (< 256) of CTA 0; the buffer holds 8192 int64
 #define TC_TRACE(p, n, e)                                                        \
   do {                                                                           \
     if ((p).trace != nullptr && blockIdx.x == 0) (p).trace[(n) * 16 + (e)] = clock64(); \
+  } while (0)
+
+// debug timeline, every CTA: globaltimer (ns) at entry (which = 0) / exit (1) in trace[4096 + 2 * blockIdx.x + which]
+#define TC_TRACE_CTA(p, which)                                                   \
+  do {                                                                           \
+    if ((p).trace != nullptr) {                                                  \
+      unsigned long long t_;                                                     \
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_));                      \
+      (p).trace[4096 + 2 * blockIdx.x + (which)] = (long long)t_;                \
+    }                                                                            \
   } while (0)
 
 // ---- tiles and token order --------------------------------------------------------

@@ -433,7 +433,10 @@ cudaError_t launch_tc12_forward(const Problem& p, cudaStream_t st, const char** 
   }
   int n_win, per, grid;
   tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
-  kernel<<<grid, tc12::kThreads12, map.total, st>>>(p, n_win, per, maps);
+  {
+    TimedRegion timed(st);
+    kernel<<<grid, tc12::kThreads12, map.total, st>>>(p, n_win, per, maps);
+  }
   count_launch();
   return cudaGetLastError();
 }

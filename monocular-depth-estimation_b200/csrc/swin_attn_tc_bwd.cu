@@ -538,6 +538,7 @@ cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** e
   }
   int n_win, per, grid;
   tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
+  TimedRegion timed(st);   // the memsets are device work of the op: inside the timed region
   e = cudaMemsetAsync(p.d_table, 0, sizeof(float) * 169 * p.nH, st);
   if (e != cudaSuccess) return e;
   const int has_pad = (p.H != p.Hp || p.W != p.Wp) ? 1 : 0;

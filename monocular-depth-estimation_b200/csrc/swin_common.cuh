@@ -159,4 +159,24 @@ cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias
 
 void count_launch(int n = 1);
 
+// Launch-adjacent timing (swin_attn_time_next_launch): a pair of events armed by the calling thread is recorded
+// immediately before and after the op's device work, i.e. after the host-side preparation (tensor-map encoding,
+// attribute calls), so that a host-bound caller does not count its own launch path as kernel time.
+struct LaunchEvents {
+  cudaEvent_t start = nullptr, stop = nullptr;
+};
+LaunchEvents take_launch_events();   // returns and disarms the calling thread's events (null when none are armed)
+struct TimedRegion {
+  LaunchEvents ev;
+  cudaStream_t st;
+  explicit TimedRegion(cudaStream_t s) : ev(take_launch_events()), st(s) {
+    if (ev.start) cudaEventRecord(ev.start, st);
+  }
+  ~TimedRegion() {
+    if (ev.stop) cudaEventRecord(ev.stop, st);
+  }
+  TimedRegion(const TimedRegion&) = delete;
+  TimedRegion& operator=(const TimedRegion&) = delete;
+};
+
 }  // namespace swin

@@ -281,7 +281,10 @@ cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias
   const int64_t tiles = ((rows + tcl::BM - 1) / tcl::BM) * (out_features / tcl::BN);
   const int sms = tc::sm_count();
   const int grid = (int)(tiles < sms ? tiles : sms);
-  kernel<<<grid, tcl::kThreads, tcl::kSmemBytes, st>>>(maps, static_cast<const __nv_bfloat16*>(bias), (int)rows, out_features, in_features);
+  {
+    TimedRegion timed(st);
+    kernel<<<grid, tcl::kThreads, tcl::kSmemBytes, st>>>(maps, static_cast<const __nv_bfloat16*>(bias), (int)rows, out_features, in_features);
+  }
   count_launch();
   return cudaGetLastError();
 }

@@ -15,8 +15,10 @@ EV = ["prod_start", "prod_issued", "mma_full", "mma_slotfree", "S_issued", "mma_
 
 
 def main():
-    b, h, w, nh, ws = 8, 22, 76, 24, 7
     shift = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+    stage = int(sys.argv[2]) if len(sys.argv) > 2 else 2          # Swin-L stage grid at 352x1216, batch 8
+    b, ws = 8, 7
+    h, w, nh = {0: (88, 304, 6), 1: (44, 152, 12), 2: (22, 76, 24), 3: (11, 38, 48)}[stage]
     dev = torch.device("cuda")
     c = nh * 32
     qkv = torch.randn(b, h, w, 3 * c, device=dev).bfloat16()
@@ -24,7 +26,7 @@ def main():
     pad = (0.1 * torch.randn(3 * c, device=dev)).bfloat16()
     lib = _lib.load()
     lib.swin_attn_debug_set_trace.argtypes = [ctypes.c_void_p]
-    trace = torch.zeros(64 * 16, dtype=torch.int64, device=dev)
+    trace = torch.zeros(8192, dtype=torch.int64, device=dev)   # 256 x 16 pair stamps of CTA 0, then (entry, exit) ns per CTA at 4096
 
     def run():
         return torch.ops.swin_attn.fwd(qkv, None, table, pad, None, ws, shift, nh, 32 ** -0.5, False, _lib.IMPL_AUTO, None)
@@ -33,14 +35,25 @@ def main():
     torch.cuda.synchronize()
     torch.empty(256 << 20, dtype=torch.uint8, device=dev).zero_()   # cold L2, as between the blocks of the model
     lib.swin_attn_debug_set_trace(ctypes.c_void_p(trace.data_ptr()))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
     run()
+    e1.record()
     torch.cuda.synchronize()
     lib.swin_attn_debug_set_trace(None)
-    t = trace.cpu().view(64, 16)
+    cta = trace.cpu()[4096:4096 + 2 * 148].view(148, 2)
+    cta = cta[cta[:, 1] > 0]
+    g0 = int(cta[:, 0].min())
+    ent, ext = (cta[:, 0] - g0).float() / 1e3, (cta[:, 1] - g0).float() / 1e3
+    print(f"stage {stage} shift {shift}: {cta.shape[0]} CTAs; CUDA events around the launch {e0.elapsed_time(e1) * 1e3:.1f} us; "
+          f"globaltimer: CTA entry {ent.min():.1f}..{ent.max():.1f} us, exit min/median/max "
+          f"{ext.min():.1f}/{ext.median():.1f}/{ext.max():.1f} us, CTA lifetime min/median/max "
+          f"{(ext - ent).min():.1f}/{(ext - ent).median():.1f}/{(ext - ent).max():.1f} us")
+    t = trace.cpu()[:4096].view(256, 16)
     t0 = int(t[:, :14][t[:, :14] > 0].min())
     print(f"kernel entry {int(t[0][14]) - t0}, exit {int(t[0][15]) - t0} (cycles relative to the first stamp)")
     print("pair " + " ".join(f"{e:>12s}" for e in EV))
-    for n in range(30):
+    for n in range(0, 256, 1 if stage >= 2 else 8):
         if int(t[n].max()) == 0:
             break
         print(f"{n:4d} " + " ".join(f"{(int(v) - t0) if v > 0 else -1:12d}" for v in t[n][:len(EV)]))
