@@ -174,6 +174,15 @@ int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void*
 int swin_linear_forward(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int32_t in_features,
                         int32_t out_features, int32_t activation, void* stream);
 
+/* Per-token Linear with the block's residual add folded into its epilogue (same tcgen05 GEMM):
+ *   y = residual + (x W^T + b),  residual, y: (rows, out_features) bf16 (may not alias), other operands as above.
+ * Replaces `shortcut + drop_path(self.attn(...))` behind `attn.proj` and `x + drop_path(self.mlp(...))` behind `Mlp.fc2`
+ * (swin_transformer.py:240-244, newcrf_layers.py:251-255) at inference under bf16 autocast where the residual stream is
+ * bf16: the Linear output is rounded to bf16 (what the autocast Linear returns), added to the residual in fp32 and the
+ * sum rounded to bf16 (torch's bf16 + bf16) -- bit-identical to the two separate steps.  Inference only. */
+int swin_linear_residual_forward(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows,
+                                 int32_t in_features, int32_t out_features, void* stream);
+
 /* Bias gradient of the per-token Linears either side of the attention (qkv / qk / proj, fc1 / fc2;
  * newcrf_layers.py:102,118,147, swin_transformer.py:104,120,142): dbias[c] = sum over rows of dy[row, c].
  * dy: (rows, cols) bf16, dense, 16-byte aligned, cols a multiple of 8; dbias: (cols) fp32, OVERWRITTEN. */
@@ -186,6 +195,14 @@ int swin_linear_bias_grad(const void* dy, int64_t rows, int32_t cols, float* dbi
  * channels in {128, 192, 256, 384, 512, 768, 1024, 1536}. */
 int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int32_t dy_dtype, const float* gamma, float eps, int64_t rows,
                             int32_t channels, void* dx, float* dgamma, float* dbeta, void* stream);
+
+/* PatchMerging's 2x2 gather fused with its LayerNorm (swin_transformer.py:271-287: `F.pad` to even H / W, `torch.cat` of
+ * x[:, 0::2, 0::2], x[:, 1::2, 0::2], x[:, 0::2, 1::2], x[:, 1::2, 1::2] along channels, `self.norm`): x is the stage
+ * output (batch, height, width, channels) in x_dtype, out is bf16 (batch, ceil(height/2) * ceil(width/2), 4 * channels)
+ * -- the operand of the `reduction` Linear under bf16 autocast.  channels: 128, 192, 256, 384, 512 or 768 (Swin-B / Swin-L stages).  Bit-identical to
+ * the concatenation followed by swin_layernorm_forward. */
+int swin_patch_merge_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, const float* beta, float eps, int32_t batch,
+                                       int32_t height, int32_t width, int32_t channels, void* out, void* stream);
 
 /* Measurement hook: arms a pair of cudaEvent_t for the calling thread.  The next attention / linear entry point this
  * thread calls records `start_event` immediately before and `stop_event` immediately after its device work (kernel

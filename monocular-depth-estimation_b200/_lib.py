@@ -24,12 +24,14 @@ EXPORTS = (
     "swin_attn_forward_host",
     "swin_layernorm_forward",
     "swin_layernorm_backward",
+    "swin_patch_merge_layernorm_forward",
     "swin_add_layernorm_forward",
     "swin_add_layernorm_forward_gated",
     "swin_add_layernorm_backward",
     "swin_gelu_forward",
     "swin_gelu_backward",
     "swin_linear_forward",
+    "swin_linear_residual_forward",
     "swin_linear_bias_grad",
     "swin_attn_time_next_launch",
     "swin_attn_launch_count",
@@ -90,6 +92,12 @@ def load() -> ctypes.CDLL:
     lib.swin_linear_forward.restype = c_int
     lib.swin_linear_bias_grad.argtypes = [vp, c_int64, c_int32, vp, vp]
     lib.swin_linear_bias_grad.restype = c_int
+    lib.swin_linear_residual_forward.argtypes = [vp, vp, vp, vp, vp, c_int64, c_int32, c_int32, vp]
+    lib.swin_linear_residual_forward.restype = c_int
+    lib.swin_patch_merge_layernorm_forward.argtypes = [vp, c_int32, vp, vp, c_float, c_int32, c_int32, c_int32, c_int32, vp, vp]
+    lib.swin_patch_merge_layernorm_forward.restype = c_int
+    lib.swin_attn_time_next_launch.argtypes = [vp, vp]
+    lib.swin_attn_time_next_launch.restype = None
     lib.swin_attn_launch_count.argtypes = []
     lib.swin_attn_launch_count.restype = c_uint64
     lib.swin_attn_uses_tcgen05.argtypes = [POINTER(Shape), c_int]

@@ -211,6 +211,22 @@ int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, c
   return 0;
 }
 
+int swin_patch_merge_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, const float* beta, float eps, int32_t batch,
+                                       int32_t height, int32_t width, int32_t channels, void* out, void* stream) {
+  if (!x || !gamma || !beta || !out) return fail("patch merge + layernorm: x, gamma, beta and out must be non-null");
+  if (batch < 0 || height < 0 || width < 0) return fail("patch merge + layernorm: bad batch / height / width");
+  if (x_dtype != SWIN_ATTN_F32 && x_dtype != SWIN_ATTN_BF16) return fail("patch merge + layernorm: x_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
+  if (!merge_layernorm_supported(channels))
+    return fail("patch merge + layernorm: channels must be one of 128, 192, 256, 384, 512, 768 (got " + std::to_string(channels) + ")");
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta) |
+       reinterpret_cast<uintptr_t>(out)) & 7)
+    return fail("patch merge + layernorm: pointers must be 8-byte aligned");
+  if ((int64_t)batch * height * width == 0) return 0;
+  cudaError_t e = launch_merge_layernorm(x, x_dtype, gamma, beta, eps, batch, height, width, channels, out, static_cast<cudaStream_t>(stream));
+  if (e != cudaSuccess) return fail_cuda("patch merge + layernorm launch", e);
+  return 0;
+}
+
 static int add_ln_checks(const char* what, int32_t x_dtype, int64_t rows, int32_t channels, const float* gate, int64_t rows_per_sample) {
   if (rows < 0) return fail(std::string(what) + ": bad row count");
   if (x_dtype != SWIN_ATTN_F32 && x_dtype != SWIN_ATTN_BF16) return fail(std::string(what) + ": x_dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
@@ -299,8 +315,26 @@ int swin_linear_forward(const void* x, const void* weight, const void* bias, voi
   if (!tc_linear_supported(rows, in_features, out_features))
     return fail("linear forward: the tcgen05 kernel is unavailable (cuTensorMapEncodeTiled not found in the driver)");
   const char* why = nullptr;
-  cudaError_t e = launch_tc_linear(x, weight, bias, y, rows, in_features, out_features, activation, static_cast<cudaStream_t>(stream), &why);
+  cudaError_t e = launch_tc_linear(x, weight, bias, nullptr, y, rows, in_features, out_features, activation, static_cast<cudaStream_t>(stream), &why);
   if (e != cudaSuccess) return fail_cuda(why ? why : "linear forward launch", e);
+  return 0;
+}
+
+int swin_linear_residual_forward(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows,
+                                 int32_t in_features, int32_t out_features, void* stream) {
+  if (!x || !weight || !bias || !residual || !y) return fail("linear + residual: all pointers must be non-null");
+  if (rows < 0 || rows >= (1ll << 31) - 128) return fail("linear + residual: bad row count");
+  if (in_features < 64 || in_features % 64) return fail("linear + residual: in_features must be a positive multiple of 64");
+  if (out_features < 256 || out_features % 256) return fail("linear + residual: out_features must be a positive multiple of 256");
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(weight) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(bias) |
+       reinterpret_cast<uintptr_t>(residual)) & 15)
+    return fail("linear + residual: x, weight, bias, residual and y must be 16-byte aligned");
+  if (rows == 0) return 0;
+  if (!tc_linear_supported(rows, in_features, out_features))
+    return fail("linear + residual: the tcgen05 kernel is unavailable (cuTensorMapEncodeTiled not found in the driver)");
+  const char* why = nullptr;
+  cudaError_t e = launch_tc_linear(x, weight, bias, residual, y, rows, in_features, out_features, SWIN_ACT_NONE, static_cast<cudaStream_t>(stream), &why);
+  if (e != cudaSuccess) return fail_cuda(why ? why : "linear + residual launch", e);
   return 0;
 }
 

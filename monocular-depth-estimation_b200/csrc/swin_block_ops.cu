@@ -65,6 +65,59 @@ __global__ void __launch_bounds__(256) layernorm_rows_kernel(const TIn* __restri
   }
 }
 
+// PatchMerging's gather fused with its LayerNorm (swin_transformer.py:271-287: pad H, W to even, concatenate the 2x2
+// neighbourhood x[0::2,0::2] | x[1::2,0::2] | x[0::2,1::2] | x[1::2,1::2] along channels, then norm(4C)): output row
+// (b, i, j) is read straight from the four pixels (2i + (s & 1), 2j + (s >> 1)), s = 0..3, of the (B, H, W, C) stage
+// output (zeros beyond an odd H / W), so the concatenated tensor is never written.  Same lane <-> channel mapping and
+// summation order as layernorm_rows_kernel on the concatenated row: bit-identical to cat + LayerNorm.
+template <int NC, typename TIn>   // 4C = 64 * NC channels per output row, NC / 4 pairs per lane and segment
+__global__ void __launch_bounds__(256) merge_layernorm_rows_kernel(const TIn* __restrict__ x, const float* __restrict__ gamma,
+                                                                   const float* __restrict__ beta, float eps, int batch, int height,
+                                                                   int width, __nv_bfloat16* __restrict__ out) {
+  constexpr int C4 = 64 * NC, C = C4 / 4, KS = NC / 4;
+  const int lane = threadIdx.x & 31;
+  const int h2 = (height + 1) >> 1, w2 = (width + 1) >> 1;
+  const int64_t rows = (int64_t)batch * h2 * w2;
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int j = (int)(row % w2), i = (int)((row / w2) % h2), b = (int)(row / ((int64_t)w2 * h2));
+  float2 v[NC];
+  float sum = 0.f;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    const int y = 2 * i + (s & 1), xx = 2 * j + (s >> 1);
+    const bool inside = y < height && xx < width;
+    const TIn* src = x + (((int64_t)b * height + y) * width + xx) * C;
+#pragma unroll
+    for (int k = 0; k < KS; ++k) {
+      v[s * KS + k] = inside ? load2(src, lane + 32 * k) : make_float2(0.f, 0.f);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NC; ++k) sum += v[k].x + v[k].y;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float mean = sum * (1.0f / C4);
+  float sq = 0.f;
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const float a = v[k].x - mean, c = v[k].y - mean;
+    sq = fmaf(a, a, sq);
+    sq = fmaf(c, c, sq);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+  const float rstd = rsqrtf(sq * (1.0f / C4) + eps);
+  const float2* g2 = reinterpret_cast<const float2*>(gamma);
+  const float2* b2 = reinterpret_cast<const float2*>(beta);
+#pragma unroll
+  for (int k = 0; k < NC; ++k) {
+    const float2 g = g2[lane + 32 * k], bb = b2[lane + 32 * k];
+    const float y0 = fmaf((v[k].x - mean) * rstd, g.x, bb.x), y1 = fmaf((v[k].y - mean) * rstd, g.y, bb.y);
+    reinterpret_cast<__nv_bfloat162*>(out + row * C4)[lane + 32 * k] = __floats2bfloat162_rn(y0, y1);
+  }
+}
+
 // Residual add fused with the LayerNorm that follows it (block plumbing, swin_transformer.py:240-244 /
 // newcrf_layers.py:251-255: `x = shortcut + attn; ... norm2(x)`, and `x + mlp` followed by the next block's norm1):
 // s = x + delta rounded to the dtype of the residual stream (what torch's type promotion gives: fp32 + bf16 -> fp32,
@@ -331,6 +384,37 @@ cudaError_t launch_layernorm(const void* x, int x_dtype, const float* g, const f
     SWIN_LN_CASE(2); SWIN_LN_CASE(3); SWIN_LN_CASE(4); SWIN_LN_CASE(6); SWIN_LN_CASE(8);
     SWIN_LN_CASE(12); SWIN_LN_CASE(16); SWIN_LN_CASE(24); SWIN_LN_CASE(48);
 #undef SWIN_LN_CASE
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+template <int NC>
+static cudaError_t launch_merge_ln(const void* x, int x_dtype, const float* g, const float* b, float eps, int batch, int height, int width,
+                                   void* out, cudaStream_t st) {
+  const int64_t rows = (int64_t)batch * ((height + 1) / 2) * ((width + 1) / 2);
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  using bf = __nv_bfloat16;
+  if (x_dtype == SWIN_ATTN_F32)
+    merge_layernorm_rows_kernel<NC, float><<<grid, 256, 0, st>>>(static_cast<const float*>(x), g, b, eps, batch, height, width, static_cast<bf*>(out));
+  else
+    merge_layernorm_rows_kernel<NC, bf><<<grid, 256, 0, st>>>(static_cast<const bf*>(x), g, b, eps, batch, height, width, static_cast<bf*>(out));
+  count_launch();
+  return cudaGetLastError();
+}
+
+bool merge_layernorm_supported(int channels) {
+  return channels == 128 || channels == 192 || channels == 256 || channels == 384 || channels == 512 || channels == 768;
+}
+
+cudaError_t launch_merge_layernorm(const void* x, int x_dtype, const float* g, const float* b, float eps, int batch, int height, int width,
+                                   int channels, void* out, cudaStream_t st) {
+  switch (channels / 16) {   // 4C / 64
+    case 8: return launch_merge_ln<8>(x, x_dtype, g, b, eps, batch, height, width, out, st);
+    case 12: return launch_merge_ln<12>(x, x_dtype, g, b, eps, batch, height, width, out, st);
+    case 16: return launch_merge_ln<16>(x, x_dtype, g, b, eps, batch, height, width, out, st);
+    case 32: return launch_merge_ln<32>(x, x_dtype, g, b, eps, batch, height, width, out, st);
+    case 24: return launch_merge_ln<24>(x, x_dtype, g, b, eps, batch, height, width, out, st);
+    case 48: return launch_merge_ln<48>(x, x_dtype, g, b, eps, batch, height, width, out, st);
     default: return cudaErrorInvalidValue;
   }
 }

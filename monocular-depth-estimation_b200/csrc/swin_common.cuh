@@ -153,9 +153,12 @@ cudaError_t launch_add_layernorm_backward(const void* x, int x_dtype, const void
 cudaError_t launch_gelu(const void* x, const void* dy, void* out, int64_t n, cudaStream_t st);
 cudaError_t launch_colsum(const void* dy, int64_t rows, int cols, float* out, int sms, cudaStream_t st);
 bool layernorm_supported(int channels);
+bool merge_layernorm_supported(int channels);
+cudaError_t launch_merge_layernorm(const void* x, int x_dtype, const float* g, const float* b, float eps, int batch, int height, int width,
+                                   int channels, void* out, cudaStream_t st);
 bool tc_linear_supported(int64_t rows, int in_features, int out_features);
-cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int in_features, int out_features,
-                             int activation, cudaStream_t st, const char** err);
+cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
+                             int out_features, int activation, cudaStream_t st, const char** err);
 
 void count_launch(int n = 1);
 

@@ -1,12 +1,17 @@
 // Per-token Linear of the blocks with its activation folded into the epilogue, tcgen05 / TMEM / TMA, sm_100a.
 //
 //   y = act(x W^T + b)      x (M, K) bf16 tokens, W (N, K) bf16 = nn.Linear.weight, b (N) bf16, y (M, N) bf16
+//   y = r + (x W^T + b)     r (M, N) bf16: the residual stream (kEpi == kEpiResidual)
 //
 // Replaces `Mlp.fc1` followed by `nn.GELU()` (newcrf_layers.py:9-27; the same Mlp in swin_transformer.py) for
 // inference under bf16 autocast: the hidden tensor (M x 4C) is written once instead of written, read and written
-// again (the per-token Linears as tcgen05 GEMMs with fused epilogues).  Numerics are the
+// again (the per-token Linears as tcgen05 GEMMs with fused epilogues).  The residual form replaces
+// `attn.proj` / `Mlp.fc2` followed by `shortcut + drop_path(x)` (swin_transformer.py:240-244, newcrf_layers.py:251-255)
+// where the stream is bf16 (every stage behind the first PatchMerging and the decoder levels under autocast): the branch
+// output is never written, the stream is read and written once by the GEMM.  Numerics are the
 // reference's step by step: fp32 accumulation, bias added in fp32, rounded to bf16 (what the cuBLASLt bias epilogue
-// stores), GELU evaluated in fp32 on that bf16 value and rounded to bf16 (what nn.GELU does on a bf16 tensor).
+// stores), GELU evaluated in fp32 on that bf16 value and rounded to bf16 (what nn.GELU does on a bf16 tensor); the
+// residual is added in fp32 to that bf16 value and the sum rounded to bf16 (what `bf16 + bf16` does in torch).
 //
 // Persistent kernel, one CTA per SM, tiles of 128 tokens x 256 outputs, K in blocks of 64 (one 128B-swizzle atom):
 //   warp 0      TMA producer: x tile (128 x 64) and W tile (256 x 64) per K block into a 4-stage ring
@@ -68,9 +73,13 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
         "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                                                                       \
       : "r"(taddr))
 
-template <bool kGelu>
+constexpr int kEpiNone = 0, kEpiGelu = 1, kEpiResidual = 2;
+
+template <int kEpi>
 __global__ void __launch_bounds__(kThreads, 1)
-tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restrict__ bias, int M, int N, int K) {
+tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
+                 int M, int N, int K) {
+  constexpr bool kGelu = kEpi == kEpiGelu;
   extern __shared__ __align__(1024) unsigned char smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -198,6 +207,19 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
       for (int box = 0; box < 2; ++box) {
         if (lane == 0) bulk_wait_read();   // the previous store of this warp has read the staging buffer
         __syncwarp();
+        // residual: this lane's row, the box's 32 columns (64 contiguous bytes), issued ahead of the TMEM load
+        uint4 res[4];
+        if constexpr (kEpi == kEpiResidual) {
+          const int row = m0 + q * 32 + lane;
+          if (row < M) {
+            const uint4* rp = reinterpret_cast<const uint4*>(residual + (int64_t)row * N + n0 + quarter * 64 + box * 32);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) res[i] = __ldg(rp + i);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) res[i] = make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
 #pragma unroll
         for (int sub = 0; sub < 2; ++sub) {
           uint32_t r[16];
@@ -216,6 +238,16 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
               const float2 g1 = gelu_value2<false>(__bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h1)), make_float2(0.f, 0.f));
               h0 = pack_bf16(g0.x, g0.y);
               h1 = pack_bf16(g1.x, g1.y);
+            }
+            if constexpr (kEpi == kEpiResidual) {
+              // columns sub * 16 + 4 i .. + 3 of the box = 32-bit words 2 i, 2 i + 1 of res[2 sub + (i >> 1)]
+              const uint32_t* rw = reinterpret_cast<const uint32_t*>(&res[2 * sub + (i >> 1)]) + 2 * (i & 1);
+              const float2 a0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h0));
+              const float2 a1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h1));
+              const float2 r0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[0]));
+              const float2 r1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[1]));
+              h0 = pack_bf16(r0.x + a0.x, r0.y + a0.y);
+              h1 = pack_bf16(r1.x + a1.x, r1.y + a1.y);
             }
             w[2 * i] = h0;
             w[2 * i + 1] = h1;
@@ -262,8 +294,8 @@ bool tc_linear_supported(int64_t rows, int in_features, int out_features) {
          out_features % tcl::BN == 0 && tc::tma_available();
 }
 
-cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int in_features, int out_features,
-                             int activation, cudaStream_t st, const char** err) {
+cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
+                             int out_features, int activation, cudaStream_t st, const char** err) {
   tcl::Maps maps;
   memset(&maps, 0, sizeof(maps));
   if (!tc::encode_matrix_map(&maps.x, x, rows, in_features, (int64_t)in_features * 2, tcl::BK, tcl::BM) ||
@@ -272,7 +304,9 @@ cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias
     if (err) *err = "cuTensorMapEncodeTiled failed";
     return cudaErrorInvalidValue;
   }
-  auto kernel = activation ? tcl::tc_linear_kernel<true> : tcl::tc_linear_kernel<false>;
+  auto kernel = residual != nullptr ? tcl::tc_linear_kernel<tcl::kEpiResidual>
+                : activation        ? tcl::tc_linear_kernel<tcl::kEpiGelu>
+                                    : tcl::tc_linear_kernel<tcl::kEpiNone>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcl::kSmemBytes);
   if (e != cudaSuccess) {
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
@@ -283,7 +317,8 @@ cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias
   const int grid = (int)(tiles < sms ? tiles : sms);
   {
     TimedRegion timed(st);
-    kernel<<<grid, tcl::kThreads, tcl::kSmemBytes, st>>>(maps, static_cast<const __nv_bfloat16*>(bias), (int)rows, out_features, in_features);
+    kernel<<<grid, tcl::kThreads, tcl::kSmemBytes, st>>>(maps, static_cast<const __nv_bfloat16*>(bias), static_cast<const __nv_bfloat16*>(residual),
+                                                         (int)rows, out_features, in_features);
   }
   count_launch();
   return cudaGetLastError();

@@ -339,6 +339,30 @@ Tensor layer_norm_meta(const Tensor& x, const Tensor&, const Tensor&, double, bo
   return at::empty_symint(x.sym_sizes(), x.options().dtype(out_bf16 ? at::kBFloat16 : at::kFloat));
 }
 
+// ---- swin_attn::patch_merge_norm (inference) ------------------------------------------------------------------
+// x: (B, H*W, C) or (B, H, W, C) stage output; returns bf16 (B, ceil(H/2)*ceil(W/2), 4C) = norm(cat of the 2x2 neighbourhood)
+Tensor patch_merge_norm_cuda(const Tensor& x_in, int64_t height, int64_t width, const Tensor& weight, const Tensor& bias, double eps) {
+  const int32_t xd = dtype_code(x_in.scalar_type());
+  const Tensor x = x_in.contiguous();
+  const int64_t c = x.size(-1), b = x.size(0);
+  TORCH_CHECK(height >= 0 && width >= 0 && x.numel() == b * height * width * c, "swin_attn::patch_merge_norm: input feature has wrong size");
+  TORCH_CHECK(weight.numel() == 4 * c && bias.numel() == 4 * c, "swin_attn::patch_merge_norm: the norm must have 4C channels");
+  const int64_t h2 = (height + 1) / 2, w2 = (width + 1) / 2;
+  Tensor out = at::empty({b, h2 * w2, 4 * c}, x.options().dtype(at::kBFloat16));
+  const Tensor w = weight.detach().to(at::kFloat).contiguous(), bb = bias.detach().to(at::kFloat).contiguous();
+  if (out.numel() == 0) return out;
+  c10::cuda::CUDAGuard guard(x.device());
+  check_rc(swin_patch_merge_layernorm_forward(x.data_ptr(), xd, w.data_ptr<float>(), bb.data_ptr<float>(), (float)eps, (int32_t)b,
+                                              (int32_t)height, (int32_t)width, (int32_t)c, out.data_ptr(),
+                                              at::cuda::getCurrentCUDAStream()));
+  return out;
+}
+
+Tensor patch_merge_norm_meta(const Tensor& x, int64_t height, int64_t width, const Tensor&, const Tensor&, double) {
+  const auto b = x.sym_size(0), c = x.sym_size(-1);
+  return at::empty_symint({b, c10::SymInt(((height + 1) / 2) * ((width + 1) / 2)), c * 4}, x.options().dtype(at::kBFloat16));
+}
+
 // gate: per-sample stochastic-depth scale (B, 1, .., 1) fp32 or None; rows_per_sample = rows / B
 static const float* gate_ptr(const optional<Tensor>& scale, const Tensor& x, Tensor& holder, int64_t& rows_per_sample) {
   rows_per_sample = 1;
@@ -437,6 +461,34 @@ Tensor linear_act_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& b
   // algorithmic traffic: x, W and y once; flops of the product (the GELU is not counted)
   timed.finish(2 * (rows * k + n * k + rows * n), 2 * rows * n * k, 2, k, activation, n, rows, 0);
   return y;
+}
+
+// residual + (x W^T + b) with the tcgen05 GEMM (inference; bf16 residual stream)
+Tensor linear_residual_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& bias, const Tensor& residual_in) {
+  TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && weight.scalar_type() == at::kBFloat16 && bias.scalar_type() == at::kBFloat16 &&
+                  residual_in.scalar_type() == at::kBFloat16,
+              "swin_attn::linear_residual: x, weight, bias and residual must be bfloat16");
+  TORCH_CHECK(weight.dim() == 2 && bias.dim() == 1 && x_in.dim() >= 1 && x_in.size(-1) == weight.size(1) && bias.size(0) == weight.size(0),
+              "swin_attn::linear_residual: x (..., in), weight (out, in), bias (out)");
+  TORCH_CHECK(residual_in.dim() >= 1 && residual_in.size(-1) == weight.size(0) &&
+                  residual_in.numel() / weight.size(0) == x_in.numel() / weight.size(1),
+              "swin_attn::linear_residual: residual must hold one row of out_features per row of x");
+  const Tensor x = x_in.contiguous(), w = weight.contiguous(), b = bias.contiguous(), r = residual_in.contiguous();
+  Tensor y = at::empty(r.sizes(), r.options());
+  if (y.numel() == 0) return y;
+  c10::cuda::CUDAGuard guard(x.device());
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const int64_t rows = x.numel() / x.size(-1), k = w.size(1), n = w.size(0);
+  TimedLaunch timed(stream);
+  check_rc(swin_linear_residual_forward(x.data_ptr(), w.data_ptr(), b.data_ptr(), r.data_ptr(), y.data_ptr(), rows, (int32_t)k, (int32_t)n,
+                                        stream));
+  // algorithmic traffic: x, W, the residual and y once; flops of the product
+  timed.finish(2 * (rows * k + n * k + 2 * rows * n), 2 * rows * n * k, 2, k, 2, n, rows, 0);
+  return y;
+}
+
+Tensor linear_residual_meta(const Tensor&, const Tensor&, const Tensor&, const Tensor& residual) {
+  return at::empty_symint(residual.sym_sizes(), residual.options());
 }
 
 Tensor linear_act_meta(const Tensor& x, const Tensor& weight, const Tensor&, int64_t) {
@@ -734,11 +786,13 @@ TORCH_LIBRARY(swin_attn, m) {
   m.def("add_layer_norm(Tensor x, Tensor delta, Tensor weight, Tensor bias, float eps, Tensor? scale=None) -> (Tensor, Tensor)");
   m.def("add_layer_norm_bwd(Tensor d_sum, Tensor dy, Tensor sum, Tensor weight, float eps, Tensor? scale=None) "
         "-> (Tensor, Tensor, Tensor, Tensor)");
+  m.def("patch_merge_norm(Tensor x, int height, int width, Tensor weight, Tensor bias, float eps) -> Tensor");
   m.def("linear(Tensor x, Tensor weight, Tensor? bias) -> Tensor");
   m.def("bias_grad(Tensor dy) -> Tensor");
   m.def("gelu(Tensor x) -> Tensor");
   m.def("gelu_bwd(Tensor dy, Tensor x) -> Tensor");
   m.def("linear_act(Tensor x, Tensor weight, Tensor bias, int activation) -> Tensor");
+  m.def("linear_residual(Tensor x, Tensor weight, Tensor bias, Tensor residual) -> Tensor");
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
@@ -749,11 +803,13 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("layer_norm_bwd", layer_norm_bwd_cuda);
   m.impl("add_layer_norm", add_layer_norm_cuda);
   m.impl("add_layer_norm_bwd", add_layer_norm_bwd_cuda);
+  m.impl("patch_merge_norm", patch_merge_norm_cuda);
   m.impl("linear", linear_any);
   m.impl("bias_grad", bias_grad_cuda);
   m.impl("gelu", gelu_cuda);
   m.impl("gelu_bwd", gelu_bwd_cuda);
   m.impl("linear_act", linear_act_cuda);
+  m.impl("linear_residual", linear_residual_cuda);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
@@ -764,11 +820,13 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("layer_norm_bwd", layer_norm_bwd_meta);
   m.impl("add_layer_norm", add_layer_norm_meta);
   m.impl("add_layer_norm_bwd", add_layer_norm_bwd_meta);
+  m.impl("patch_merge_norm", patch_merge_norm_meta);
   m.impl("linear", linear_any);
   m.impl("bias_grad", bias_grad_meta);
   m.impl("gelu", gelu_meta);
   m.impl("gelu_bwd", gelu_bwd_meta);
   m.impl("linear_act", linear_act_meta);
+  m.impl("linear_residual", linear_residual_meta);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
@@ -778,6 +836,8 @@ TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
   m.impl("gelu", gelu_autograd);
   m.impl("linear", linear_autograd);
   m.impl("linear_act", torch::autograd::autogradNotImplementedFallback());   // inference only
+  m.impl("patch_merge_norm", torch::autograd::autogradNotImplementedFallback());   // inference only
+  m.impl("linear_residual", torch::autograd::autogradNotImplementedFallback());    // inference only
 }
 
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------

@@ -58,6 +58,24 @@ def _gate(drop_path, x):
     return drop_path.gate(x) if isinstance(drop_path, DropPath) else None
 
 
+# Residual adds in the proj / fc2 GEMM epilogues (ops.linear_residual, csrc/swin_linear_tc.cu).  Off by default: measured
+# on the B200 the 128 x 256-tile, one-CTA tcgen05 GEMM loses more against cuBLAS on these shapes
+# (N = C: three n-blocks, 2.1 waves; 0.90 vs 1.52 PFLOP/s at 13376 x 3072 x 768) than the saved pass over the stream
+# gains, so the default keeps cuBLAS + the add fused into the following LayerNorm (ops.add_norm).
+FUSE_RESIDUAL_EPILOGUE = False
+
+
+def _linear_into_stream(lin, drop, drop_path, x, t):
+    """``x + drop_path(drop(lin(t)))`` with the add in the GEMM epilogue (``ops.linear_residual``) when nothing random
+    sits between the Linear and the add (inference; bf16 residual stream); None otherwise."""
+    if not FUSE_RESIDUAL_EPILOGUE:
+        return None
+    if torch.is_grad_enabled() or (drop.training and drop.p > 0.0) or \
+            (isinstance(drop_path, DropPath) and drop_path.training and drop_path.drop_prob > 0.0):
+        return None
+    return ops.linear_residual(lin, t, x)
+
+
 class Mlp(nn.Module):
     """fc1 -> act -> drop -> fc2 -> drop (newcrf_layers.py:9-27)."""
 
@@ -68,8 +86,11 @@ class Mlp(nn.Module):
         self.fc2 = nn.Linear(hidden_features or in_features, out_features or in_features)
         self.drop = nn.Dropout(drop)
 
+    def hidden(self, x):
+        return self.drop(ops.linear_gelu(self.fc1, self.act, x))
+
     def forward(self, x):
-        return self.drop(ops.linear(self.fc2, self.drop(ops.linear_gelu(self.fc1, self.act, x))))
+        return self.drop(ops.linear(self.fc2, self.hidden(x)))
 
 
 def _relative_position_index(wh: int, ww: int) -> torch.Tensor:
@@ -135,7 +156,10 @@ class WindowAttention(_WindowAttentionBase):
         return self.proj_drop(self.proj(o.reshape(b_, n, c)))
 
     def forward_image(self, x_img, v_img, shift):
-        """x_img, v_img: (B, H, W, C) image-order (x already normalised).  Pad
+        return self.proj_drop(ops.linear(self.proj, self.attend_image(x_img, v_img, shift)))
+
+    def attend_image(self, x_img, v_img, shift):
+        """x_img, v_img: (B, H, W, C) image-order (x already normalised) -> attention output before ``proj``.  Pad
         tokens take the Linear bias for q/k and zero for v, as in the reference
         where ``F.pad`` precedes the Linear (newcrf_layers.py:212-216)."""
         ws = self.window_size[0]
@@ -153,7 +177,7 @@ class WindowAttention(_WindowAttentionBase):
             o = ops.window_attention(ops.linear(self.qk, x_img), v_img, self.relative_position_bias_table, ws, shift,
                                      self.num_heads, self.scale, packed_pad=self.qk.bias, v_pad=None,
                                      dropout_p=self._drop_p())
-        return self.proj_drop(ops.linear(self.proj, o))
+        return o
 
 
 class EncoderWindowAttention(_WindowAttentionBase):
@@ -171,6 +195,10 @@ class EncoderWindowAttention(_WindowAttentionBase):
         return self.proj_drop(self.proj(o.reshape(b_, n, c)))
 
     def forward_image(self, x_img, shift):
+        return self.proj_drop(ops.linear(self.proj, self.attend_image(x_img, shift)))
+
+    def attend_image(self, x_img, shift):
+        """(B, H, W, C) normalised image-order tokens -> attention output before ``proj``."""
         ws = self.window_size[0]
         if torch.is_grad_enabled() and not self._fused_pad_backward(shift) and (
                 x_img.requires_grad or self.relative_position_bias_table.requires_grad):
@@ -184,7 +212,28 @@ class EncoderWindowAttention(_WindowAttentionBase):
         else:
             o = ops.window_attention(ops.linear(self.qkv, x_img), None, self.relative_position_bias_table, ws, shift,
                                      self.num_heads, self.scale, packed_pad=self.qkv.bias, dropout_p=self._drop_p())
-        return self.proj_drop(ops.linear(self.proj, o))
+        return o
+
+
+def _block_tail(blk, x, o):
+    """Everything of a block behind the attention core (swin_transformer.py:228-246, newcrf_layers.py:239-257):
+    ``x = x + drop_path(proj(o))``, ``norm2``, MLP.  Returns ``(stream, pending, scale)``: the MLP branch still to be
+    added (with its stochastic-depth gate), or ``pending = None`` when the add already happened in the fc2 GEMM.
+    At inference on a bf16 stream both residual adds ride in the epilogues of the proj / fc2 GEMMs
+    (``ops.linear_residual``); otherwise the add is fused with the LayerNorm behind it (``ops.add_norm``)."""
+    attn = blk.attn
+    s = _linear_into_stream(attn.proj, attn.proj_drop, blk.drop_path, x, o)
+    if s is not None:
+        x, y2 = s, ops.norm_for_linear(blk.norm2, s)
+    else:
+        a = attn.proj_drop(ops.linear(attn.proj, o))
+        x, y2 = ops.add_norm(blk.norm2, x, a, _gate(blk.drop_path, a))
+    hidden = blk.mlp.hidden(y2)
+    s = _linear_into_stream(blk.mlp.fc2, blk.mlp.drop, blk.drop_path, x, hidden)
+    if s is not None:
+        return s, None, None
+    m = blk.mlp.drop(ops.linear(blk.mlp.fc2, hidden))
+    return x, m, _gate(blk.drop_path, m)
 
 
 class CRFBlock(nn.Module):
@@ -211,7 +260,7 @@ class CRFBlock(nn.Module):
 
     def forward(self, x, v, mask_matrix=None):
         x, pending, scale = self.forward_parts(x, v, ops.norm_for_linear(self.norm1, x))
-        return ops.residual(x, pending, scale)
+        return x if pending is None else ops.residual(x, pending, scale)
 
     def forward_parts(self, x, v, y):
         """The block without its last residual add: ``y`` is ``norm1(x)``; returns the stream after the attention
@@ -220,10 +269,8 @@ class CRFBlock(nn.Module):
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(y.view(b, h, w, c), v, self.shift_size).reshape(b, h * w, self.v_dim)
-        x, y2 = ops.add_norm(self.norm2, x, a, _gate(self.drop_path, a))
-        m = self.mlp(y2)
-        return x, m, _gate(self.drop_path, m)
+        o = self.attn.attend_image(y.view(b, h, w, c), v, self.shift_size).reshape(b, h * w, self.v_dim)
+        return _block_tail(self, x, o)
 
 
 class BasicCRFLayer(nn.Module):
@@ -316,17 +363,15 @@ class SwinTransformerBlock(nn.Module):
 
     def forward(self, x, mask_matrix=None):
         x, pending, scale = self.forward_parts(x, ops.norm_for_linear(self.norm1, x))
-        return ops.residual(x, pending, scale)
+        return x if pending is None else ops.residual(x, pending, scale)
 
     def forward_parts(self, x, y):
         """The block without its last residual add (see CRFBlock.forward_parts)."""
         b, l, c = x.shape
         h, w = self.H, self.W
         assert l == h * w, "input feature has wrong size"
-        a = self.attn.forward_image(y.view(b, h, w, c), self.shift_size).reshape(b, h * w, c)
-        x, y2 = ops.add_norm(self.norm2, x, a, _gate(self.drop_path, a))
-        m = self.mlp(y2)
-        return x, m, _gate(self.drop_path, m)
+        o = self.attn.attend_image(y.view(b, h, w, c), self.shift_size).reshape(b, h * w, c)
+        return _block_tail(self, x, o)
 
 
 class PatchMerging(nn.Module):
@@ -341,6 +386,9 @@ class PatchMerging(nn.Module):
     def forward(self, x, H, W):
         b, l, c = x.shape
         assert l == H * W, "input feature has wrong size"
+        y = ops.patch_merge_norm(self.norm, x, H, W)   # inference: gather + norm in one kernel
+        if y is not None:
+            return self.reduction(y)
         x = x.view(b, H, W, c)
         if H % 2 or W % 2:
             x = F.pad(x, (0, 0, 0, W % 2, 0, H % 2))

@@ -114,6 +114,19 @@ def norm_fp32(norm: torch.nn.Module, x: Tensor) -> Tensor:
     return norm(x)
 
 
+def patch_merge_norm(norm: torch.nn.Module, x: Tensor, height: int, width: int) -> Optional[Tensor]:
+    """``norm(cat(2x2 neighbourhood of x))`` of PatchMerging (swin_transformer.py:271-287) as one kernel that gathers
+    the four pixels while normalising -- the concatenated (B, H/2*W/2, 4C) tensor is never written.  Inference under
+    bf16 autocast only (bit-identical to the concatenation followed by ``norm_for_linear``); returns None when the
+    fused kernel does not apply and the caller takes the reference's steps."""
+    if (type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
+            and x.dtype in _DTYPES and not torch.is_grad_enabled() and torch.is_autocast_enabled()
+            and torch.get_autocast_dtype("cuda") == torch.bfloat16 and len(norm.normalized_shape) == 1
+            and x.shape[-1] in (128, 192, 256, 384, 512, 768) and norm.normalized_shape[0] == 4 * x.shape[-1]):
+        return torch.ops.swin_attn.patch_merge_norm(x, height, width, norm.weight, norm.bias, norm.eps)
+    return None
+
+
 def linear(lin: torch.nn.Module, x: Tensor) -> Tensor:
     """``lin(x)`` for the per-token Linears of the blocks.  In training under bf16 autocast this is one C++ autograd
     node computing what autocast computes (bf16 operands, cuBLAS addmm) whose backward sums the bias gradient with the
@@ -139,6 +152,23 @@ def linear_gelu(lin: torch.nn.Module, act: torch.nn.Module, x: Tensor) -> Tensor
         bf = torch.bfloat16
         return torch.ops.swin_attn.linear_act(x.to(bf), lin.weight.to(bf), lin.bias.to(bf), 1)
     return gelu(act, linear(lin, x))
+
+
+def linear_residual(lin: torch.nn.Module, x: Tensor, residual: Tensor) -> Optional[Tensor]:
+    """``residual + lin(x)`` -- the residual add behind ``attn.proj`` / ``Mlp.fc2`` (swin_transformer.py:240-244,
+    newcrf_layers.py:251-255) -- as ONE tcgen05 GEMM whose epilogue rounds the Linear output to bf16 (as the autocast
+    Linear does), adds the bf16 residual stream in fp32 and rounds the sum to bf16 (torch's bf16 + bf16): the branch
+    output is never written.  Inference with a bf16 stream only; returns None when the fused kernel does not apply
+    (fp32 stream of stage 0, widths that are not a multiple of 256, training) and the caller takes the separate steps."""
+    if (type(lin) is torch.nn.Linear and lin.bias is not None and x.is_cuda and not torch.is_grad_enabled()
+            and residual.dtype == torch.bfloat16 and lin.in_features % 64 == 0 and lin.out_features % 256 == 0
+            and (x.dtype == torch.bfloat16 or x.dtype == torch.float32)
+            and residual.shape[-1] == lin.out_features and residual.numel() // lin.out_features == x.numel() // lin.in_features
+            and ((torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") == torch.bfloat16)
+                 or (x.dtype == torch.bfloat16 and lin.weight.dtype == torch.bfloat16))):
+        bf = torch.bfloat16
+        return torch.ops.swin_attn.linear_residual(x.to(bf), lin.weight.to(bf), lin.bias.to(bf), residual)
+    return None
 
 
 def gelu(act: torch.nn.Module, x: Tensor) -> Tensor:

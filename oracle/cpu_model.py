@@ -49,7 +49,7 @@ class OracleWindowAttention(layers.WindowAttention):
         o = _windows_forward(self, qk[..., :c], qk[..., c:], v.to(qk.dtype), mask)
         return self.proj_drop(self.proj(o))
 
-    def forward_image(self, x_img, v_img, shift):
+    def attend_image(self, x_img, v_img, shift):   # the attention core before ``proj`` (the block applies proj)
         c = self.dim
         qk = self.qk(x_img)
         bias = self.qk.bias
@@ -57,7 +57,7 @@ class OracleWindowAttention(layers.WindowAttention):
                                 self.window_size[0], shift, self.num_heads, self.scale,
                                 q_pad=None if bias is None else bias[:c].to(qk.dtype),
                                 k_pad=None if bias is None else bias[c:].to(qk.dtype), v_pad=None)
-        return self.proj_drop(self.proj(o))
+        return o
 
 
 class OracleEncoderWindowAttention(layers.EncoderWindowAttention):
@@ -67,7 +67,7 @@ class OracleEncoderWindowAttention(layers.EncoderWindowAttention):
         o = _windows_forward(self, qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], mask)
         return self.proj_drop(self.proj(o))
 
-    def forward_image(self, x_img, shift):
+    def attend_image(self, x_img, shift):
         c = self.dim
         qkv = self.qkv(x_img)
         bias = self.qkv.bias
@@ -75,7 +75,7 @@ class OracleEncoderWindowAttention(layers.EncoderWindowAttention):
         o, _ = window_attention(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], self.relative_position_bias_table,
                                 self.window_size[0], shift, self.num_heads, self.scale,
                                 q_pad=pads[0], k_pad=pads[1], v_pad=pads[2])
-        return self.proj_drop(self.proj(o))
+        return o
 
 
 _SWAP = {layers.WindowAttention: OracleWindowAttention, layers.EncoderWindowAttention: OracleEncoderWindowAttention}

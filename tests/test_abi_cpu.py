@@ -13,7 +13,7 @@ from conftest import ROOT
 def _declared():
     text = open(os.path.join(ROOT, "include", "swin_attn.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(swin_(?:attn|layernorm|add_layernorm|gelu|linear)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b(swin_(?:attn|layernorm|add_layernorm|patch_merge_layernorm|gelu|linear)_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_library_exports_every_declared_symbol():
@@ -81,6 +81,20 @@ def test_layernorm_validation_without_gpu():
     assert b"channels must be one of" in lib.swin_attn_last_error()
     assert lib.swin_layernorm_forward(None, _lib.F32, ptr, ptr, 1e-5, 1, 128, ptr, _lib.BF16, None) != 0
     assert lib.swin_layernorm_forward(ptr, _lib.BF16, ptr, ptr, 1e-5, 0, 128, ptr, _lib.F32, None) == 0   # empty input: no launch
+
+
+def test_patch_merge_layernorm_validation_without_gpu():
+    """swin_patch_merge_layernorm_forward (PatchMerging gather + norm, swin_transformer.py:271-287)."""
+    lib = _lib.load()
+    buf = (ctypes.c_float * 256)()
+    ptr = ctypes.cast(buf, ctypes.c_void_p)
+    err = lib.swin_attn_last_error
+    assert lib.swin_patch_merge_layernorm_forward(ptr, _lib.F32, ptr, ptr, 1e-5, 1, 4, 4, 96, ptr, None) != 0
+    assert b"channels must be one of" in err()
+    assert lib.swin_patch_merge_layernorm_forward(ptr, 5, ptr, ptr, 1e-5, 1, 4, 4, 192, ptr, None) != 0 and b"x_dtype" in err()
+    assert lib.swin_patch_merge_layernorm_forward(None, _lib.F32, ptr, ptr, 1e-5, 1, 4, 4, 192, ptr, None) != 0
+    assert lib.swin_patch_merge_layernorm_forward(ptr, _lib.F32, ptr, ptr, 1e-5, 1, -1, 4, 192, ptr, None) != 0
+    assert lib.swin_patch_merge_layernorm_forward(ptr, _lib.BF16, ptr, ptr, 1e-5, 0, 4, 4, 192, ptr, None) == 0   # empty: no launch
 
 
 def test_block_plumbing_entries_validate_without_gpu():

@@ -419,6 +419,43 @@ def test_fused_layernorm_matches_torch(c):
         assert ops.norm_for_linear(ln, x).dtype == torch.float32        # fp32 mode: the module itself
 
 
+@pytest.mark.parametrize("xdtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(3, 11, 38, 192), (2, 10, 7, 384), (2, 5, 6, 768), (1, 9, 9, 128), (2, 4, 4, 512)])
+def test_patch_merge_norm_matches_the_reference_steps(shape, xdtype):
+    """swin_patch_merge_layernorm_forward == PatchMerging's pad + 2x2 concat + norm (swin_transformer.py:271-287), odd
+    and even H / W: bit-identical to the concatenation followed by the fused LayerNorm, and the module's inference
+    output equals the reference op sequence under autocast."""
+    b, h, w, c = shape
+    gen = torch.Generator(device=DEV).manual_seed(h * w + c)
+    x = (2.0 * torch.randn(b, h * w, c, device=DEV, generator=gen) + 0.3).to(xdtype)
+    pm = layers.PatchMerging(c).to(DEV)
+    with torch.no_grad():
+        pm.norm.weight.copy_(1.0 + 0.3 * torch.randn(4 * c, device=DEV, generator=gen))
+        pm.norm.bias.copy_(0.2 * torch.randn(4 * c, device=DEV, generator=gen))
+    xi = torch.nn.functional.pad(x.view(b, h, w, c), (0, 0, 0, w % 2, 0, h % 2))
+    cat = torch.cat([xi[:, 0::2, 0::2], xi[:, 1::2, 0::2], xi[:, 0::2, 1::2], xi[:, 1::2, 1::2]], -1).reshape(b, -1, 4 * c)
+    got = torch.ops.swin_attn.patch_merge_norm(x, h, w, pm.norm.weight, pm.norm.bias, pm.norm.eps)
+    assert got.dtype == torch.bfloat16 and got.shape == cat.shape
+    ref = torch.nn.functional.layer_norm(cat.float(), (4 * c,), pm.norm.weight, pm.norm.bias, pm.norm.eps)
+    assert rel_err(got.float(), ref.double()) < 2 ** -7
+    if 4 * c in ops._LN_CHANNELS:     # the un-fused path of the product: concatenation, then the fused LayerNorm
+        want = torch.ops.swin_attn.layer_norm(cat, pm.norm.weight, pm.norm.bias, pm.norm.eps, True)
+        assert torch.equal(got, want)
+    else:                             # 2048 channels (Swin-B stage 2 -> 3): autocast's LayerNorm, then the bf16 cast
+        want = ref.bfloat16()
+        assert float(((got.float() - want.float()).abs() > 0).float().mean()) < 5e-3
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        assert ops.patch_merge_norm(pm.norm, x, h, w) is not None
+        fused = pm(x, h, w)
+        unfused = pm.reduction(want)
+    assert torch.equal(fused, unfused)
+    with torch.autocast("cuda", dtype=torch.bfloat16):          # training: the reference's steps (autograd)
+        assert ops.patch_merge_norm(pm.norm, x, h, w) is None
+    with torch.no_grad():                                        # fp32 mode: the reference's steps
+        assert ops.patch_merge_norm(pm.norm, x, h, w) is None
+        assert pm(x.float(), h, w).dtype == torch.float32
+
+
 @pytest.mark.parametrize("out_bf16", [True, False])
 @pytest.mark.parametrize("xdtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("c", [128, 192, 256, 384, 512, 768, 1024, 1536])
@@ -659,6 +696,62 @@ def test_linear_gelu_tcgen05_matches_autocast_linear_then_gelu(case):
     with torch.autocast("cuda", dtype=torch.bfloat16):
         y = ops.linear_gelu(lin, torch.nn.GELU(), xg)
     assert y.requires_grad and rel_err(y.detach(), ref) <= TOL_BF16
+
+
+@pytest.mark.parametrize("case", [(77, 64, 256), (1000, 768, 768), (4099, 3072, 768), (300, 6144, 1536), (8 * 22 * 76 + 5, 2048, 512),
+                                  (129, 1024, 1024)])
+def test_linear_residual_tcgen05_matches_linear_then_add(case):
+    """swin_linear_residual_forward (proj / fc2 with the block's residual add in the GEMM epilogue): bit-identical to the
+    plain epilogue followed by torch's bf16 + bf16, and within bf16 tolerance of the autocast nn.Linear + add the
+    reference runs (swin_transformer.py:240-244)."""
+    rows, k, n = case
+    gen = torch.Generator(device=DEV).manual_seed(rows + k + n)
+    x = torch.randn(rows, k, device=DEV, generator=gen).bfloat16()
+    res = (2.0 * torch.randn(rows, n, device=DEV, generator=gen)).bfloat16()
+    lin = torch.nn.Linear(k, n).to(DEV)
+    with torch.no_grad():
+        lin.weight.copy_(torch.randn(n, k, device=DEV, generator=gen) * k ** -0.5)
+        lin.bias.copy_(torch.randn(n, device=DEV, generator=gen))
+    w, b = lin.weight.detach().bfloat16(), lin.bias.detach().bfloat16()
+    plain = torch.ops.swin_attn.linear_act(x, w, b, 0)
+    fused = torch.ops.swin_attn.linear_residual(x, w, b, res)
+    assert fused.shape == (rows, n) and fused.dtype == torch.bfloat16
+    assert torch.equal(fused, res + plain)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        ref = res + lin(x)
+        got = ops.linear_residual(lin, x.view(1, rows, k), res.view(1, rows, n))
+        assert got is not None and got.shape == (1, rows, n) and torch.equal(got.view(rows, n), fused)
+        assert ops.linear_residual(lin, x, res.float()) is None           # fp32 stream (stage 0): the separate steps
+    assert rel_err(fused, ref) <= TOL_BF16 and (fused != ref).float().mean().item() < 0.02
+    with torch.autocast("cuda", dtype=torch.bfloat16):                    # training: the separate steps
+        assert ops.linear_residual(lin, x, res) is None
+
+
+@pytest.mark.parametrize("kind", ["swin", "crf"])
+def test_residual_epilogue_in_block_is_bit_identical_to_add_norm_path(monkeypatch, kind):
+    """A block at inference on a bf16 stream: both residual adds in the proj / fc2 GEMM epilogues against the same block
+    with the adds fused into the following LayerNorm (ops.add_norm), whose GEMMs are cuBLAS: same rounding points, so
+    the outputs agree up to rare accumulation-order ties."""
+    torch.manual_seed(11)
+    c, nh, h, w = 256, 8, 16, 23
+    if kind == "swin":
+        blk = layers.SwinTransformerBlock(c, nh, window_size=7, shift_size=3).to(DEV).eval()
+        args = ()
+    else:
+        blk = layers.CRFBlock(c, nh, c, window_size=7, shift_size=3).to(DEV).eval()
+        args = (torch.randn(2, h, w, c, device=DEV).bfloat16(),)
+    blk.H, blk.W = h, w
+    x = torch.randn(2, h * w, c, device=DEV).bfloat16()
+    monkeypatch.setattr(layers, "FUSE_RESIDUAL_EPILOGUE", True)   # opt-in (off by default: slower than cuBLAS + add_norm)
+    before = _lib.launch_count()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        got = blk(x, *args, None)
+        fused_launches = _lib.launch_count() - before
+        monkeypatch.setattr(ops, "linear_residual", lambda lin, t, r: None)
+        want = blk(x, *args, None)
+    assert got.dtype == torch.bfloat16 and got.shape == want.shape
+    assert fused_launches == 6      # norm1, attention, proj + add, norm2, fc1 + GELU, fc2 + add
+    assert rel_err(got, want) <= 4e-3 and (got != want).float().mean().item() < 0.05
 
 
 def test_linear_gelu_in_model_is_bit_identical_to_unfused(monkeypatch):
