@@ -216,7 +216,15 @@ def run_ours(args, env):
     ops.set_kernel_timing(None)
     launches = _lib.launch_count() - launches0
     barrier()
-    t_e2e = timed_steps(step_e2e, args.steps) if train else region_e2e(args.steps)
+    if train:
+        t_e2e = timed_steps(step_e2e, args.steps)
+    else:
+        # One event pair brackets the whole K-step serving region, so a single host hiccup (GC, the clock sampler taking
+        # the GIL, a page fault in a pinned buffer) while the ~100 ms region is being enqueued lands in the number in full
+        # (observed: 464 / 649 images/s on runs whose other regions gave 770-800).  The region is therefore timed three
+        # times, each with exactly K steps and a synchronize on both sides, and the median is reported.
+        e2e_regions = sorted(region_e2e(args.steps) for _ in range(3))
+        t_e2e = e2e_regions[1]
     t_graph = None
     if not train and graphed is not None:
         barrier()
@@ -272,12 +280,13 @@ def run_ours(args, env):
         "config": {"workload": workload, "parallelism": par,
                    "l2_flush_between_steps": True, "timing": "CUDA events per step, max over ranks",
                    "e2e_timing": ("per step: H2D -> step -> D2H on one stream" if train else
-                                  "one event pair around K steps of harness.infer_host_batches (pinned host in / out, "
+                                  "median of 3 regions, each one event pair around K steps of harness.infer_host_batches (pinned host in / out, "
                                   "copies of neighbouring steps overlapped on copy streams, L2 flush inside"
                                   + (")" if args.no_graph else "; the forward is replayed from a CUDA graph, "
                                      "harness.GraphedInference, while `value` is the eager forward so that the attention "
                                      "launches can be bracketed by CUDA events for the roofline)"))},
-        "e2e": {"value": n_img / t_e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "e2e": {"value": n_img / t_e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                **({} if train else {"regions_images_per_s": [n_img / t for t in e2e_regions]})},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         "roofline": roof_bwd if train else roof_fwd,
@@ -286,7 +295,7 @@ def run_ours(args, env):
     if lin_recs:
         l_ms, l_bytes, l_flops = (sum(r[i] for r in lin_recs) for i in range(3))
         line["roofline_linear"] = {
-            "bound": "tensor", "kernel": "tc_linear_kernel (fc1 + bias + GELU of every block MLP, tcgen05 GEMM with fused epilogue)",
+            "bound": "tensor", "kernel": "tc_linear_kernel (fc1 + bias + GELU of every block MLP, tcgen05 GEMM with fused epilogue; CTA pairs / cta_group::2 where K >= 1536)",
             "achieved": l_flops / (l_ms * 1e-3) / 1e12, "peak": tf, "unit": "TFLOP/s", "frac": l_flops / (l_ms * 1e-3) / 1e12 / tf,
             "peak_source": f"{which} (MEASURED_PEAKS.json dense bf16)", "traffic": None,
             "algorithmic_GBps": l_bytes / (l_ms * 1e-3) / 1e9, "hbm_frac": l_bytes / (l_ms * 1e-3) / 1e9 / hbm,

@@ -379,6 +379,9 @@ int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int3
 
 // Debug hook (not part of the public header): device buffer of >= 16 * pairs-per-CTA int64 that receives
 // clock64 stamps of CTA 0 of the tcgen05 kernel; pass NULL to switch tracing off.
+// Debug hook (not part of the public header): CTA-pair mode of the tcgen05 linear kernel, -1 automatic, 0 off, 1 on.
+void swin_linear_debug_set_pair_mode(int mode) { set_tc_linear_pair_mode(mode); }
+
 void swin_attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }
 
 void swin_attn_time_next_launch(void* start_event, void* stop_event) {

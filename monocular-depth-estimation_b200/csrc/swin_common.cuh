@@ -160,6 +160,7 @@ bool tc_linear_supported(int64_t rows, int in_features, int out_features);
 cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
                              int out_features, int activation, cudaStream_t st, const char** err);
 
+void set_tc_linear_pair_mode(int mode);
 void count_launch(int n = 1);
 
 // Launch-adjacent timing (swin_attn_time_next_launch): a pair of events armed by the calling thread is recorded

@@ -36,18 +36,27 @@ namespace tcl {
 using namespace tc;
 
 constexpr int BM = 128, BN = 256, BK = 64;
-constexpr int kStages = 4;
 constexpr int kABytes = BM * BK * 2;                      // 16 KB
-constexpr int kBBytes = BN * BK * 2;                      // 32 KB
-constexpr int kStageBytes = kABytes + kBBytes;            // 48 KB
-constexpr int kStagingOff = kStages * kStageBytes;        // 192 KB
+// One CTA per tile: W tile 256 x 64 (32 KB), 4 stages of 48 KB.  CTA pair (cta_group::2, M = 256 over two SMs): each CTA
+// stages its own 128 tokens and HALF of the W tile (128 x 64, 16 KB), 6 stages of 32 KB -- 2/3 of the shared-memory
+// fill per MMA cycle, which is what limited the one-CTA kernel on the tensor-bound shapes.
+template <int kCtas> struct Ring {
+  static constexpr int kBRows = BN / kCtas;
+  static constexpr int kBBytes = kBRows * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = kCtas == 1 ? 4 : 6;
+  static_assert(kStages * kStageBytes == 192 * 1024, "ring size");
+};
+constexpr int kMaxStages = 6;
+constexpr int kStagingOff = 192 * 1024;
 constexpr int kStagingWarp = 32 * 64;                     // 32 rows x 32 bf16 per epilogue warp
 constexpr int kEpiWarps = 16;
 constexpr int kBiasOff = kStagingOff + kEpiWarps * kStagingWarp;
 constexpr int kBarOff = kBiasOff + 2 * BN * 4;
-constexpr int kSmemBytes = kBarOff + 128;
+constexpr int kSmemBytes = kBarOff + 256;
 constexpr int kThreads = 128 + kEpiWarps * 32;
 static_assert(kSmemBytes <= 232448, "shared memory budget");
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // shared::cluster address of the same offset in the pair's leader CTA (rank 0)
 
 struct Maps {
   CUtensorMap x, w, y;
@@ -63,6 +72,49 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
                : "memory");
 }
 
+// ---- CTA-pair (cta_group::2) forms ----
+// TMA load issued by either CTA of the pair into its own shared memory; the bytes are counted on the LEADER's mbarrier
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar & kPeerMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_ss_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc),
+      "r"(accumulate)
+      : "memory");
+}
+// the mbarrier at this offset in BOTH CTAs of the pair arrives once the pair's MMAs issued so far have completed
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+// arrive on the mbarrier at this offset in the pair's leader CTA (from either CTA)
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerMask) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_cta_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+
 #define TMEM_LD_X32(taddr, r)                                                                                          \
   asm volatile(                                                                                                        \
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                        \
@@ -75,25 +127,35 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t sr
 
 constexpr int kEpiNone = 0, kEpiGelu = 1, kEpiResidual = 2;
 
-template <int kEpi>
+template <int kEpi, int kCtas>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
                  int M, int N, int K) {
   constexpr bool kGelu = kEpi == kEpiGelu;
+  constexpr bool kPair = kCtas == 2;
+  constexpr int kStages = Ring<kCtas>::kStages, kStageBytes = Ring<kCtas>::kStageBytes;
   extern __shared__ __align__(1024) unsigned char smem[];
   const uint32_t sbase = smem_u32(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // CTA pair: rank 0 (the leader) issues the MMAs of the pair's 256-token tile; both CTAs load, both run the epilogue of
+  // their own 128 tokens.  The persistent loop walks pair tiles with the pair index.
+  const int rank = kPair ? (int)cluster_cta_rank() : 0;
+  const int worker = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int workers = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
-  const uint32_t bar_full = sbase + kBarOff;            // [kStages]
-  const uint32_t bar_empty = bar_full + 8 * kStages;    // [kStages]
-  const uint32_t bar_acc_full = bar_empty + 8 * kStages;   // [2]
-  const uint32_t bar_acc_empty = bar_acc_full + 16;        // [2]
-  const uint32_t bar_bias_full = bar_acc_empty + 16;       // [2]
-  const uint32_t tmem_slot = bar_bias_full + 16;
+  const uint32_t bar_full = sbase + kBarOff;                  // [kStages]  (pair: the leader's counts both CTAs' bytes)
+  const uint32_t bar_empty = bar_full + 8 * kMaxStages;       // [kStages]
+  const uint32_t bar_acc_full = bar_empty + 8 * kMaxStages;   // [2]
+  const uint32_t bar_acc_empty = bar_acc_full + 16;           // [2]  (pair: the leader's, kCtas * kEpiWarps arrivals)
+  const uint32_t bar_bias_full = bar_acc_empty + 16;          // [2]
+  const uint32_t bar_bias_empty = bar_bias_full + 16;         // [2]
+  const uint32_t tmem_slot = bar_bias_empty + 16;
   float* bias_s = reinterpret_cast<float*>(smem + kBiasOff);   // [2][BN]
 
-  const int n_blocks = N / BN, m_blocks = (M + BM - 1) / BM, k_blocks = K / BK;
+  const int n_blocks = N / BN, m_blocks = (M + kCtas * BM - 1) / (kCtas * BM), k_blocks = K / BK;
   const int tiles = n_blocks * m_blocks;
+  auto tile_m0 = [&](int t) { return (t / n_blocks) * (kCtas * BM) + rank * BM; };   // first token of THIS CTA's rows
+  auto tile_n0 = [&](int t) { return (t % n_blocks) * BN; };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&maps.x);
@@ -107,14 +169,19 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(bar_acc_full + 8 * a, 1);
-      mbar_init(bar_acc_empty + 8 * a, kEpiWarps);
+      mbar_init(bar_acc_empty + 8 * a, kCtas * kEpiWarps);
       mbar_init(bar_bias_full + 8 * a, 1);
+      mbar_init(bar_bias_empty + 8 * a, kEpiWarps);
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, 512);
+  if (warp == 2) {
+    if constexpr (kPair) tmem_alloc_pair(tmem_slot, 512);
+    else tmem_alloc(tmem_slot, 512);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all();   // the peer's barriers are initialised before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - sbase));
 
@@ -122,15 +189,21 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
     // ---- TMA producer ----
     int s = 0;
     uint32_t ph = 0;
-    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-      const int m0 = (t / n_blocks) * BM, n0 = (t % n_blocks) * BN;
+    for (int t = worker; t < tiles; t += workers) {
+      const int m0 = tile_m0(t), n0 = tile_n0(t);
       for (int kb = 0; kb < k_blocks; ++kb) {
         mbar_wait(bar_empty + 8 * s, ph ^ 1);
         if (elect_one()) {
           const uint32_t st = sbase + s * kStageBytes;
-          mbar_expect_tx(bar_full + 8 * s, kStageBytes);
-          tma_load_2d(st, &maps.x, bar_full + 8 * s, kb * BK, m0);
-          tma_load_2d(st + kABytes, &maps.w, bar_full + 8 * s, kb * BK, n0);
+          if constexpr (kPair) {
+            if (rank == 0) mbar_expect_tx(bar_full + 8 * s, 2 * kStageBytes);
+            tma_load_2d_pair(st, &maps.x, bar_full + 8 * s, kb * BK, m0);
+            tma_load_2d_pair(st + kABytes, &maps.w, bar_full + 8 * s, kb * BK, n0 + rank * (BN / 2));
+          } else {
+            mbar_expect_tx(bar_full + 8 * s, kStageBytes);
+            tma_load_2d(st, &maps.x, bar_full + 8 * s, kb * BK, m0);
+            tma_load_2d(st + kABytes, &maps.w, bar_full + 8 * s, kb * BK, n0);
+          }
         }
         __syncwarp();
         if (++s == kStages) {
@@ -139,12 +212,12 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
         }
       }
     }
-  } else if (warp == 1) {
-    // ---- MMA issuer ----
-    constexpr uint32_t idesc = instr_desc(BM, BN, 0);
+  } else if (warp == 1 && rank == 0) {
+    // ---- MMA issuer (pair: the leader only; M = 256 spans both CTAs' tokens, each CTA supplies half of the W tile) ----
+    constexpr uint32_t idesc = instr_desc(kCtas * BM, BN, 0);
     int s = 0, a = 0;
     uint32_t ph = 0, aph = 0;
-    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+    for (int t = worker; t < tiles; t += workers) {
       mbar_wait(bar_acc_empty + 8 * a, aph ^ 1);
       tc_fence_after();
       for (int kb = 0; kb < k_blocks; ++kb) {
@@ -154,10 +227,17 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
           const uint32_t st = sbase + s * kStageBytes;
           const uint64_t ad = smem_desc(st, 16, 1024, 2);
           const uint64_t bd = smem_desc(st + kABytes, 16, 1024, 2);
+          if constexpr (kPair) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) umma_ss(tmem_base + a * BN, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
-          umma_commit(bar_empty + 8 * s);
-          if (kb == k_blocks - 1) umma_commit(bar_acc_full + 8 * a);
+            for (int k = 0; k < BK / 16; ++k) umma_ss_pair(tmem_base + a * BN, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+            umma_commit_pair(bar_empty + 8 * s);
+            if (kb == k_blocks - 1) umma_commit_pair(bar_acc_full + 8 * a);
+          } else {
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) umma_ss(tmem_base + a * BN, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+            umma_commit(bar_empty + 8 * s);
+            if (kb == k_blocks - 1) umma_commit(bar_acc_full + 8 * a);
+          }
         }
         __syncwarp();
         if (++s == kStages) {
@@ -172,9 +252,9 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
     // ---- bias loader: keeps the epilogue warps free of CTA-wide barriers ----
     int a = 0;
     uint32_t aph = 0;
-    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-      const int n0 = (t % n_blocks) * BN;
-      mbar_wait(bar_acc_empty + 8 * a, aph ^ 1);   // the epilogue of the tile that used this buffer is done with it
+    for (int t = worker; t < tiles; t += workers) {
+      const int n0 = tile_n0(t);
+      mbar_wait(bar_bias_empty + 8 * a, aph ^ 1);   // the epilogue of the tile that used this buffer is done with it
       const uint4 raw = __ldg(reinterpret_cast<const uint4*>(bias + n0) + lane);
       const uint32_t* rw = reinterpret_cast<const uint32_t*>(&raw);
       float4* dst = reinterpret_cast<float4*>(bias_s + a * BN + lane * 8);
@@ -196,8 +276,8 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
     const uint32_t row_off = lane * 64, sw = (lane >> 1) & 3;
     int a = 0;
     uint32_t aph = 0;
-    for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
-      const int m0 = (t / n_blocks) * BM, n0 = (t % n_blocks) * BN;
+    for (int t = worker; t < tiles; t += workers) {
+      const int m0 = tile_m0(t), n0 = tile_n0(t);
       mbar_wait(bar_bias_full + 8 * a, aph);
       mbar_wait(bar_acc_full + 8 * a, aph);
       tc_fence_after();
@@ -264,7 +344,11 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
           // the accumulator buffer is in registers / shared memory: hand it back to the MMA issuer
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * a);
+          if (lane == 0) {
+            mbar_arrive(bar_bias_empty + 8 * a);
+            if constexpr (kPair) mbar_arrive_leader(bar_acc_empty + 8 * a);
+            else mbar_arrive(bar_acc_empty + 8 * a);
+          }
         }
         fence_proxy_async();
         __syncwarp();
@@ -280,10 +364,12 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all();   // neither CTA leaves (or frees TMEM) while the pair's MMAs / arrivals are in flight
+  else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if constexpr (kPair) tmem_dealloc_pair(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -294,34 +380,64 @@ bool tc_linear_supported(int64_t rows, int in_features, int out_features) {
          out_features % tcl::BN == 0 && tc::tma_available();
 }
 
-cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
-                             int out_features, int activation, cudaStream_t st, const char** err) {
-  tcl::Maps maps;
-  memset(&maps, 0, sizeof(maps));
-  if (!tc::encode_matrix_map(&maps.x, x, rows, in_features, (int64_t)in_features * 2, tcl::BK, tcl::BM) ||
-      !tc::encode_matrix_map(&maps.w, weight, out_features, in_features, (int64_t)in_features * 2, tcl::BK, tcl::BN) ||
-      !tc::encode_matrix_map(&maps.y, y, rows, out_features, (int64_t)out_features * 2, 32, 32)) {
-    if (err) *err = "cuTensorMapEncodeTiled failed";
-    return cudaErrorInvalidValue;
-  }
-  auto kernel = residual != nullptr ? tcl::tc_linear_kernel<tcl::kEpiResidual>
-                : activation        ? tcl::tc_linear_kernel<tcl::kEpiGelu>
-                                    : tcl::tc_linear_kernel<tcl::kEpiNone>;
+// -1: automatic (CTA pairs on the tensor-bound shapes), 0: one CTA per tile, 1: CTA pairs.  Debug / microbench hook.
+static int g_pair_mode = -1;
+void set_tc_linear_pair_mode(int mode) { g_pair_mode = mode; }
+
+template <int kEpi, int kCtas>
+static cudaError_t launch_tc_linear_as(const tcl::Maps& maps, const void* bias, const void* residual, int64_t rows, int in_features,
+                                       int out_features, cudaStream_t st, const char** err) {
+  auto kernel = tcl::tc_linear_kernel<kEpi, kCtas>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcl::kSmemBytes);
   if (e != cudaSuccess) {
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
     return e;
   }
-  const int64_t tiles = ((rows + tcl::BM - 1) / tcl::BM) * (out_features / tcl::BN);
-  const int sms = tc::sm_count();
-  const int grid = (int)(tiles < sms ? tiles : sms);
+  const int64_t tiles = ((rows + kCtas * tcl::BM - 1) / (kCtas * tcl::BM)) * (out_features / tcl::BN);
+  const int workers = tc::sm_count() / kCtas;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(kCtas * (tiles < workers ? tiles : workers)));
+  cfg.blockDim = dim3(tcl::kThreads);
+  cfg.dynamicSmemBytes = tcl::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCtas;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = kCtas > 1 ? 1 : 0;
   {
     TimedRegion timed(st);
-    kernel<<<grid, tcl::kThreads, tcl::kSmemBytes, st>>>(maps, static_cast<const __nv_bfloat16*>(bias), static_cast<const __nv_bfloat16*>(residual),
-                                                         (int)rows, out_features, in_features);
+    e = cudaLaunchKernelEx(&cfg, kernel, maps, static_cast<const __nv_bfloat16*>(bias), static_cast<const __nv_bfloat16*>(residual), (int)rows,
+                           out_features, in_features);
   }
+  if (e != cudaSuccess) return e;
   count_launch();
   return cudaGetLastError();
+}
+
+cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
+                             int out_features, int activation, cudaStream_t st, const char** err) {
+  // CTA pairs pay off where the MMAs, not the epilogue or HBM, bound the tile (profiles/r1_micro_linear_pair.jsonl):
+  // K >= 512 with the plain / residual epilogues, K >= 1536 with the GELU epilogue (below that its ~4.3 us per tile
+  // hide the MMAs either way).
+  const bool pair = g_pair_mode < 0 ? in_features >= (activation && residual == nullptr ? 1536 : 512) : g_pair_mode != 0;
+  tcl::Maps maps;
+  memset(&maps, 0, sizeof(maps));
+  if (!tc::encode_matrix_map(&maps.x, x, rows, in_features, (int64_t)in_features * 2, tcl::BK, tcl::BM) ||
+      !tc::encode_matrix_map(&maps.w, weight, out_features, in_features, (int64_t)in_features * 2, tcl::BK, pair ? tcl::BN / 2 : tcl::BN) ||
+      !tc::encode_matrix_map(&maps.y, y, rows, out_features, (int64_t)out_features * 2, 32, 32)) {
+    if (err) *err = "cuTensorMapEncodeTiled failed";
+    return cudaErrorInvalidValue;
+  }
+#define SWIN_TCL_LAUNCH(EPI)                                                                                                   \
+  (pair ? launch_tc_linear_as<EPI, 2>(maps, bias, residual, rows, in_features, out_features, st, err)                          \
+        : launch_tc_linear_as<EPI, 1>(maps, bias, residual, rows, in_features, out_features, st, err))
+  if (residual != nullptr) return SWIN_TCL_LAUNCH(tcl::kEpiResidual);
+  if (activation) return SWIN_TCL_LAUNCH(tcl::kEpiGelu);
+  return SWIN_TCL_LAUNCH(tcl::kEpiNone);
+#undef SWIN_TCL_LAUNCH
 }
 
 }  // namespace swin

@@ -22,6 +22,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -62,7 +64,7 @@ def _gate(drop_path, x):
 # on the B200 the 128 x 256-tile, one-CTA tcgen05 GEMM loses more against cuBLAS on these shapes
 # (N = C: three n-blocks, 2.1 waves; 0.90 vs 1.52 PFLOP/s at 13376 x 3072 x 768) than the saved pass over the stream
 # gains, so the default keeps cuBLAS + the add fused into the following LayerNorm (ops.add_norm).
-FUSE_RESIDUAL_EPILOGUE = False
+FUSE_RESIDUAL_EPILOGUE = os.environ.get("SWIN_FUSE_RESIDUAL", "0") == "1"
 
 
 def _linear_into_stream(lin, drop, drop_path, x, t):

@@ -570,6 +570,29 @@ def test_library_counts_launches():
     assert _lib.launch_count() == before + 1
 
 
+def test_launch_adjacent_timing_records_every_attention_and_linear_launch():
+    """swin_attn_time_next_launch through ops.set_kernel_timing (bench.py's live roofline): one record per attention /
+    tcgen05-linear launch with a positive CUDA-event duration, the op's algorithmic bytes and flops, and nothing armed
+    once timing is switched off."""
+    qkv = torch.randn(2, 14, 21, 3 * 64, device=DEV).bfloat16()
+    table = torch.zeros(169, 2, device=DEV)
+    x = torch.randn(300, 128, device=DEV).bfloat16()
+    w, b = torch.randn(256, 128, device=DEV).bfloat16(), torch.zeros(256, device=DEV).bfloat16()
+    records = []
+    ops.set_kernel_timing(records)
+    ops.window_attention(qkv, None, table, 7, 3, 2)
+    ops.window_attention(qkv.float(), None, table, 7, 0, 2)         # CUDA-core kernel
+    torch.ops.swin_attn.linear_act(x, w, b, 1)
+    ops.set_kernel_timing(None)
+    assert [r[3][0] for r in records] == ["fwd", "fwd", "lin"]
+    assert all(0.0 < r[0] < 5.0 for r in records)                   # ms
+    assert records[0][1] == 4 * 2 * 14 * 21 * 64 * 2 and records[2][2] == 2 * 300 * 128 * 256
+    before = len(records)
+    ops.window_attention(qkv, None, table, 7, 3, 2)                 # timing off: no record, no stale events
+    torch.cuda.synchronize()
+    assert len(records) == before
+
+
 def test_prepare_inference_is_bit_identical_and_outputs_keep_reference_shapes(golden):
     """harness.prepare_inference (GEMM / conv weights stored in bf16) reads the values autocast would cast on every
     call: same bits out.  Stage outputs are channels-last strided but have the reference's NCHW shape and values."""
@@ -752,6 +775,33 @@ def test_residual_epilogue_in_block_is_bit_identical_to_add_norm_path(monkeypatc
     assert got.dtype == torch.bfloat16 and got.shape == want.shape
     assert fused_launches == 6      # norm1, attention, proj + add, norm2, fc1 + GELU, fc2 + add
     assert rel_err(got, want) <= 4e-3 and (got != want).float().mean().item() < 0.05
+
+
+@pytest.mark.parametrize("case", [(77, 64, 256), (256, 128, 512), (300, 768, 768), (4099, 768, 3072), (3344, 1536, 6144), (513, 3072, 768)])
+def test_linear_cta_pair_kernel_is_bit_identical_to_the_single_cta_kernel(case):
+    """tc_linear_kernel<.., 2> (cta_group::2: a 256-token tile over two SMs, each CTA staging half of the W tile) against
+    the one-CTA kernel on the same operands -- same K order of the fp32 accumulation, so every epilogue (plain, GELU,
+    residual) must agree bit for bit, including ragged last tiles (rows not a multiple of 256, an odd number of
+    128-row blocks) -- and against the fp64 product."""
+    rows, k, n = case
+    gen = torch.Generator(device=DEV).manual_seed(rows * 3 + k + n)
+    x = torch.randn(rows, k, device=DEV, generator=gen).bfloat16()
+    w = (torch.randn(n, k, device=DEV, generator=gen) * k ** -0.5).bfloat16()
+    b = torch.randn(n, device=DEV, generator=gen).bfloat16()
+    res = torch.randn(rows, n, device=DEV, generator=gen).bfloat16()
+    lib = _lib.load()
+    outs = {}
+    try:
+        for mode in (0, 1):
+            lib.swin_linear_debug_set_pair_mode(mode)
+            outs[mode] = (torch.ops.swin_attn.linear_act(x, w, b, 0), torch.ops.swin_attn.linear_act(x, w, b, 1),
+                          torch.ops.swin_attn.linear_residual(x, w, b, res))
+            torch.cuda.synchronize()
+    finally:
+        lib.swin_linear_debug_set_pair_mode(-1)
+    for single, pair in zip(outs[0], outs[1]):
+        assert torch.equal(single, pair)
+    assert rel_err(outs[1][0], x.double() @ w.double().t() + b.double()) <= TOL_BF16
 
 
 def test_linear_gelu_in_model_is_bit_identical_to_unfused(monkeypatch):

@@ -11,7 +11,7 @@ import torch
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 
 import mde_b200  # noqa: F401
-from mde_b200 import ops  # noqa: F401
+from mde_b200 import _lib, ops  # noqa: F401
 
 SHAPES = [  # name, rows, in, out
     ("enc.s0", 8 * 88 * 304, 192, 768), ("enc.s1", 8 * 44 * 152, 384, 1536), ("enc.s2", 8 * 22 * 76, 768, 3072),
@@ -46,13 +46,22 @@ def main():
         x = torch.randn(rows, k, device=dev).bfloat16()
         w = (torch.randn(n, k, device=dev) * k ** -0.5).bfloat16()
         b = torch.randn(n, device=dev).bfloat16()
+        lib = _lib.load()
+        lib.swin_linear_debug_set_pair_mode(0)                       # one CTA per 128 x 256 tile
         t_fused = timed(lambda: torch.ops.swin_attn.linear_act(x, w, b, 1), flush)
         t_plain = timed(lambda: torch.ops.swin_attn.linear_act(x, w, b, 0), flush)
+        ref1 = torch.ops.swin_attn.linear_act(x, w, b, 1)
+        lib.swin_linear_debug_set_pair_mode(1)                       # CTA pairs (cta_group::2), 256 x 256 tile over two SMs
+        t_fused2 = timed(lambda: torch.ops.swin_attn.linear_act(x, w, b, 1), flush)
+        t_plain2 = timed(lambda: torch.ops.swin_attn.linear_act(x, w, b, 0), flush)
+        same = bool(torch.equal(ref1, torch.ops.swin_attn.linear_act(x, w, b, 1)))
+        lib.swin_linear_debug_set_pair_mode(-1)
         t_cublas = timed(lambda: torch.nn.functional.linear(x, w, b), flush)
         h = torch.nn.functional.linear(x, w, b)
         t_gelu = timed(lambda: torch.ops.swin_attn.gelu(h), flush)
         byt = 2 * (rows * k + n * k + rows * n)
         print(json.dumps({"shape": name, "rows": rows, "in": k, "out": n, "fused_us": round(t_fused, 1), "plain_us": round(t_plain, 1),
+                          "pair_fused_us": round(t_fused2, 1), "pair_plain_us": round(t_plain2, 1), "pair_equals_single": same,
                           "cublas_us": round(t_cublas, 1), "gelu_us": round(t_gelu, 1),
                           "speedup_vs_two_kernels": round((t_cublas + t_gelu) / t_fused, 2),
                           "fused_GBps": round(byt / t_fused / 1e3, 1), "fused_TFLOPs": round(2 * rows * k * n / t_fused / 1e6, 1)}))
