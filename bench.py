@@ -295,7 +295,7 @@ def run_ours(args, env):
     if lin_recs:
         l_ms, l_bytes, l_flops = (sum(r[i] for r in lin_recs) for i in range(3))
         line["roofline_linear"] = {
-            "bound": "tensor", "kernel": "tc_linear_kernel (fc1 + bias + GELU of every block MLP, tcgen05 GEMM with fused epilogue; CTA pairs / cta_group::2 where K >= 1536)",
+            "bound": "tensor", "kernel": "tc_linear_kernel (fc1 + bias + GELU of every block MLP, tcgen05 GEMM with fused epilogue; CTA pairs / cta_group::2 from K = 192 up)",
             "achieved": l_flops / (l_ms * 1e-3) / 1e12, "peak": tf, "unit": "TFLOP/s", "frac": l_flops / (l_ms * 1e-3) / 1e12 / tf,
             "peak_source": f"{which} (MEASURED_PEAKS.json dense bf16)", "traffic": None,
             "algorithmic_GBps": l_bytes / (l_ms * 1e-3) / 1e9, "hbm_frac": l_bytes / (l_ms * 1e-3) / 1e9 / hbm,

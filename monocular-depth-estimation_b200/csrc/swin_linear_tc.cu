@@ -96,7 +96,9 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
 }
 // arrive on the mbarrier at this offset in the pair's leader CTA (from either CTA)
 __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerMask) : "memory");
+  // default semantics (release at CTA scope): the TMEM reads it orders are fenced by tcgen05.fence::before_thread_sync;
+  // .release.cluster costs a cluster-scope memory barrier per arrival (7 % of the stall samples in ncu)
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerMask) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t cols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
@@ -419,10 +421,17 @@ static cudaError_t launch_tc_linear_as(const tcl::Maps& maps, const void* bias, 
 
 cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
                              int out_features, int activation, cudaStream_t st, const char** err) {
-  // CTA pairs pay off where the MMAs, not the epilogue or HBM, bound the tile (profiles/r1_micro_linear_pair.jsonl):
-  // K >= 512 with the plain / residual epilogues, K >= 1536 with the GELU epilogue (below that its ~4.3 us per tile
-  // hide the MMAs either way).
-  const bool pair = g_pair_mode < 0 ? in_features >= (activation && residual == nullptr ? 1536 : 512) : g_pair_mode != 0;
+  // CTA pairs (cta_group::2) halve the W fill per CTA; they win from K = 192 up (profiles/r1_micro_linear_pair.jsonl)
+  // unless the coarser 256-token tiles cost an extra round of the persistent loop (3 344 x 1024 x 4096: 224 pair tiles on
+  // 74 pairs = 4 rounds against 3 rounds of 432 tiles on 148 CTAs).
+  bool pair = g_pair_mode > 0;
+  if (g_pair_mode < 0) {
+    const int sms = tc::sm_count();
+    const int64_t nb = out_features / tcl::BN;
+    const int64_t tiles1 = ((rows + tcl::BM - 1) / tcl::BM) * nb, tiles2 = ((rows + 2 * tcl::BM - 1) / (2 * tcl::BM)) * nb;
+    const int64_t rounds1 = (tiles1 + sms - 1) / sms, rounds2 = (tiles2 + sms / 2 - 1) / (sms / 2);
+    pair = in_features >= 192 && sms >= 2 && rounds2 <= rounds1;
+  }
   tcl::Maps maps;
   memset(&maps, 0, sizeof(maps));
   if (!tc::encode_matrix_map(&maps.x, x, rows, in_features, (int64_t)in_features * 2, tcl::BK, tcl::BM) ||
