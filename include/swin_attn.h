@@ -141,7 +141,7 @@ int swin_add_layernorm_forward(const void* x, int32_t x_dtype, const void* delta
 
 /* The same with the stochastic-depth gate of the branch folded in (training: `x + drop_path(branch)`,
  * newcrf_layers.py:251,255; timm DropPath): sum_out = x + delta * gate[row / rows_per_sample] as torch.addcmul
- * computes it (one FMA), gate: one fp32 per sample (0 or 1 / keep) or NULL (no gate); x must be fp32 with a gate.
+ * computes it (one FMA), gate: one fp32 per sample (0 or 1 / keep) or NULL (no gate); x may be fp32 (stage 0) or bf16 (later stages).
  * Backward of the pair (autograd of the add, the DropPath scaling and nn.LayerNorm in one pass):
  *   dx = d_sum + LayerNormBackward(dy; sum, gamma)    (x_dtype)   -- gradient of the residual stream before the add
  *   d_delta = bf16(dx * gate)                                      -- gradient of the bf16 branch output

@@ -234,7 +234,6 @@ static int add_ln_checks(const char* what, int32_t x_dtype, int64_t rows, int32_
     return fail(std::string(what) + ": channels must be one of 128, 192, 256, 384, 512, 768, 1024, 1536 (got " + std::to_string(channels) + ")");
   if (gate != nullptr && (rows_per_sample <= 0 || rows % rows_per_sample))
     return fail(std::string(what) + ": with a gate, rows must be a multiple of rows_per_sample > 0");
-  if (gate != nullptr && x_dtype != SWIN_ATTN_F32) return fail(std::string(what) + ": a gate needs an fp32 residual stream");
   return 0;
 }
 

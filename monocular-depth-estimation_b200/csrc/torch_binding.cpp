@@ -368,7 +368,6 @@ static const float* gate_ptr(const optional<Tensor>& scale, const Tensor& x, Ten
   rows_per_sample = 1;
   if (!scale.has_value() || !scale->defined()) return nullptr;
   TORCH_CHECK(x.dim() >= 2 && scale->numel() == x.size(0), "swin_attn::add_layer_norm: scale must hold one value per sample");
-  TORCH_CHECK(x.scalar_type() == at::kFloat, "swin_attn::add_layer_norm: a scale needs an fp32 residual stream");
   holder = scale->detach().to(at::kFloat).contiguous();
   rows_per_sample = x.numel() / x.size(-1) / x.size(0);
   return holder.data_ptr<float>();

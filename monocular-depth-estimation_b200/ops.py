@@ -191,12 +191,13 @@ def add_norm(norm: torch.nn.Module, x: Tensor, delta: Tensor, scale: Optional[Te
     autocast (bf16 ``delta``, <= 1536 channels), in training one autograd node whose backward is one kernel as well
     (LayerNorm backward + the gradient arriving through the residual stream + the bf16 / gated gradient of the branch);
     otherwise the two separate steps.  ``scale`` is the stochastic-depth gate of ``delta`` (training only, one value
-    per sample, fp32 stream)."""
+    per sample; fp32 stream of stage 0 or the bf16 stream behind the first PatchMerging -- the fused add is the single
+    fp32 FMA + rounding ``torch.addcmul`` performs, bit for bit)."""
     if (type(norm) is torch.nn.LayerNorm and norm.elementwise_affine and norm.bias is not None and x.is_cuda
             and x.dtype in _DTYPES and delta.dtype == torch.bfloat16 and delta.shape == x.shape
             and torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") == torch.bfloat16
             and len(norm.normalized_shape) == 1 and x.shape[-1] in _LN_CHANNELS and x.shape[-1] <= 1536
-            and (scale is None or (x.dtype == torch.float32 and x.dim() >= 2 and scale.numel() == x.shape[0]))):
+            and (scale is None or (x.dim() >= 2 and scale.numel() == x.shape[0]))):
         out = torch.ops.swin_attn.add_layer_norm(x, delta, norm.weight, norm.bias, norm.eps, scale)
         return out[0], out[1]
     x = residual(x, delta, scale)

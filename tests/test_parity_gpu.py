@@ -978,8 +978,9 @@ def test_patch_embed_gemm_path_matches_autocast_conv(hw):
     assert trained.requires_grad and rel_err(trained.detach(), want) <= TOL_BF16
 
 
+@pytest.mark.parametrize("stream", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("channels,gated", [(192, True), (768, True), (128, False), (1536, False)])
-def test_add_norm_training_node_matches_unfused_autograd(channels, gated):
+def test_add_norm_training_node_matches_unfused_autograd(channels, gated, stream):
     """swin_add_layernorm_forward_gated / swin_add_layernorm_backward through ops.add_norm in training: outputs and all
     gradients (residual stream, bf16 branch, LayerNorm weight / bias) against the unfused autograd graph
     (torch.addcmul + the fused LayerNorm node) and against fp64."""
@@ -989,14 +990,15 @@ def test_add_norm_training_node_matches_unfused_autograd(channels, gated):
     with torch.no_grad():
         ln.weight.copy_(1 + 0.3 * torch.randn(channels, device=DEV, generator=gen))
         ln.bias.copy_(0.3 * torch.randn(channels, device=DEV, generator=gen))
-    x = torch.randn(b, l, channels, device=DEV, generator=gen)
+    # the residual stream is fp32 in stage 0 and bf16 behind the first PatchMerging (autocast); the gate is bf16 either way
+    x = torch.randn(b, l, channels, device=DEV, generator=gen).to(stream)
     delta = torch.randn(b, l, channels, device=DEV, generator=gen).bfloat16()
     scale = (torch.tensor([0.0, 1 / 0.9, 1 / 0.9], device=DEV).view(b, 1, 1).bfloat16() if gated else None)
     cot_s = torch.randn(b, l, channels, device=DEV, generator=gen)
     cot_y = torch.randn(b, l, channels, device=DEV, generator=gen).bfloat16()
 
     def run(fn, dtype=None):
-        xs = (x if dtype is None else x.to(dtype)).clone().requires_grad_()
+        xs = (x if dtype is None else x.to(dtype)).clone().requires_grad_()   # fp64 run: from the (rounded) stream values
         ds = (delta if dtype is None else delta.to(dtype)).clone().requires_grad_()
         mod = ln if dtype is None else torch.nn.LayerNorm(channels).to(DEV, dtype)
         if dtype is not None:
@@ -1020,7 +1022,7 @@ def test_add_norm_training_node_matches_unfused_autograd(channels, gated):
         want = run(unfused)
     ref = run(exact, torch.float64)
     assert fused_launches == 2                                   # one forward kernel, one backward kernel
-    assert got[0].dtype == torch.float32 and got[1].dtype == torch.bfloat16 and got[3].dtype == torch.bfloat16
+    assert got[0].dtype == stream and got[1].dtype == torch.bfloat16 and got[3].dtype == torch.bfloat16
     assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
     names = ["sum", "y", "dx", "d_delta", "dgamma", "dbeta"]
     for n, g, w, r in zip(names, got, want, ref):
