@@ -174,6 +174,13 @@ int swin_gelu_backward(const void* x, const void* dy, void* dx, int64_t n, void*
 int swin_linear_forward(const void* x, const void* weight, const void* bias, void* y, int64_t rows, int32_t in_features,
                         int32_t out_features, int32_t activation, void* stream);
 
+/* Training form of fc1 + GELU: the same GEMM writes BOTH h = x W^T + b (bf16, what the autocast Linear returns and what
+ * the GELU backward needs) and y = GELU(h) (bf16), so `self.act(self.fc1(x))` (newcrf_layers.py:21-23) costs one kernel
+ * and one read of x / W in training as well; h, y: (rows, out_features) bf16.  y is bit-identical to
+ * swin_linear_forward(.., SWIN_ACT_GELU), h to swin_linear_forward(.., SWIN_ACT_NONE). */
+int swin_linear_gelu_forward_train(const void* x, const void* weight, const void* bias, void* h, void* y, int64_t rows, int32_t in_features,
+                                   int32_t out_features, void* stream);
+
 /* Per-token Linear with the block's residual add folded into its epilogue (same tcgen05 GEMM):
  *   y = residual + (x W^T + b),  residual, y: (rows, out_features) bf16 (may not alias), other operands as above.
  * Replaces `shortcut + drop_path(self.attn(...))` behind `attn.proj` and `x + drop_path(self.mlp(...))` behind `Mlp.fc2`

@@ -32,6 +32,7 @@ EXPORTS = (
     "swin_gelu_backward",
     "swin_linear_forward",
     "swin_linear_residual_forward",
+    "swin_linear_gelu_forward_train",
     "swin_linear_bias_grad",
     "swin_attn_time_next_launch",
     "swin_attn_launch_count",
@@ -92,6 +93,8 @@ def load() -> ctypes.CDLL:
     lib.swin_linear_forward.restype = c_int
     lib.swin_linear_bias_grad.argtypes = [vp, c_int64, c_int32, vp, vp]
     lib.swin_linear_bias_grad.restype = c_int
+    lib.swin_linear_gelu_forward_train.argtypes = [vp, vp, vp, vp, vp, c_int64, c_int32, c_int32, vp]
+    lib.swin_linear_gelu_forward_train.restype = c_int
     lib.swin_linear_residual_forward.argtypes = [vp, vp, vp, vp, vp, c_int64, c_int32, c_int32, vp]
     lib.swin_linear_residual_forward.restype = c_int
     lib.swin_patch_merge_layernorm_forward.argtypes = [vp, c_int32, vp, vp, c_float, c_int32, c_int32, c_int32, c_int32, vp, vp]

@@ -314,8 +314,26 @@ int swin_linear_forward(const void* x, const void* weight, const void* bias, voi
   if (!tc_linear_supported(rows, in_features, out_features))
     return fail("linear forward: the tcgen05 kernel is unavailable (cuTensorMapEncodeTiled not found in the driver)");
   const char* why = nullptr;
-  cudaError_t e = launch_tc_linear(x, weight, bias, nullptr, y, rows, in_features, out_features, activation, static_cast<cudaStream_t>(stream), &why);
+  cudaError_t e = launch_tc_linear(x, weight, bias, nullptr, nullptr, y, rows, in_features, out_features, activation, static_cast<cudaStream_t>(stream), &why);
   if (e != cudaSuccess) return fail_cuda(why ? why : "linear forward launch", e);
+  return 0;
+}
+
+int swin_linear_gelu_forward_train(const void* x, const void* weight, const void* bias, void* h, void* y, int64_t rows, int32_t in_features,
+                                   int32_t out_features, void* stream) {
+  if (!x || !weight || !bias || !h || !y) return fail("linear + GELU (training): all pointers must be non-null");
+  if (rows < 0 || rows >= (1ll << 31) - 128) return fail("linear + GELU (training): bad row count");
+  if (in_features < 64 || in_features % 64) return fail("linear + GELU (training): in_features must be a positive multiple of 64");
+  if (out_features < 256 || out_features % 256) return fail("linear + GELU (training): out_features must be a positive multiple of 256");
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(weight) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(bias) |
+       reinterpret_cast<uintptr_t>(h)) & 15)
+    return fail("linear + GELU (training): x, weight, bias, h and y must be 16-byte aligned");
+  if (rows == 0) return 0;
+  if (!tc_linear_supported(rows, in_features, out_features))
+    return fail("linear + GELU (training): the tcgen05 kernel is unavailable (cuTensorMapEncodeTiled not found in the driver)");
+  const char* why = nullptr;
+  cudaError_t e = launch_tc_linear(x, weight, bias, nullptr, h, y, rows, in_features, out_features, SWIN_ACT_GELU, static_cast<cudaStream_t>(stream), &why);
+  if (e != cudaSuccess) return fail_cuda(why ? why : "linear + GELU (training) launch", e);
   return 0;
 }
 
@@ -332,7 +350,7 @@ int swin_linear_residual_forward(const void* x, const void* weight, const void* 
   if (!tc_linear_supported(rows, in_features, out_features))
     return fail("linear + residual: the tcgen05 kernel is unavailable (cuTensorMapEncodeTiled not found in the driver)");
   const char* why = nullptr;
-  cudaError_t e = launch_tc_linear(x, weight, bias, residual, y, rows, in_features, out_features, SWIN_ACT_NONE, static_cast<cudaStream_t>(stream), &why);
+  cudaError_t e = launch_tc_linear(x, weight, bias, residual, nullptr, y, rows, in_features, out_features, SWIN_ACT_NONE, static_cast<cudaStream_t>(stream), &why);
   if (e != cudaSuccess) return fail_cuda(why ? why : "linear + residual launch", e);
   return 0;
 }

@@ -157,8 +157,8 @@ bool merge_layernorm_supported(int channels);
 cudaError_t launch_merge_layernorm(const void* x, int x_dtype, const float* g, const float* b, float eps, int batch, int height, int width,
                                    int channels, void* out, cudaStream_t st);
 bool tc_linear_supported(int64_t rows, int in_features, int out_features);
-cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
-                             int out_features, int activation, cudaStream_t st, const char** err);
+cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* pre_act, void* y, int64_t rows,
+                             int in_features, int out_features, int activation, cudaStream_t st, const char** err);
 
 void set_tc_linear_pair_mode(int mode);
 void count_launch(int n = 1);

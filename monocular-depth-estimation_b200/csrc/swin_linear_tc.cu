@@ -127,13 +127,13 @@ __device__ __forceinline__ uint32_t cluster_cta_rank() {
         "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])                                                                       \
       : "r"(taddr))
 
-constexpr int kEpiNone = 0, kEpiGelu = 1, kEpiResidual = 2;
+constexpr int kEpiNone = 0, kEpiGelu = 1, kEpiResidual = 2, kEpiGeluBoth = 3;   // Both: y = GELU(h) AND h (training)
 
 template <int kEpi, int kCtas>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restrict__ bias, const __nv_bfloat16* __restrict__ residual,
-                 int M, int N, int K) {
-  constexpr bool kGelu = kEpi == kEpiGelu;
+                 __nv_bfloat16* __restrict__ pre_act, int M, int N, int K) {
+  constexpr bool kGelu = kEpi == kEpiGelu || kEpi == kEpiGeluBoth;
   constexpr bool kPair = kCtas == 2;
   constexpr int kStages = Ring<kCtas>::kStages, kStageBytes = Ring<kCtas>::kStageBytes;
   extern __shared__ __align__(1024) unsigned char smem[];
@@ -309,12 +309,17 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
           tmem_ld_wait();
           const float4* b4 = reinterpret_cast<const float4*>(bias_s + a * BN + quarter * 64 + box * 32 + sub * 16);
           uint32_t w[8];
+          [[maybe_unused]] uint32_t hw[8];   // kEpiGeluBoth: the bf16 Linear output h, kept for the GELU backward
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const float4 b = b4[i];
             const float2 v0 = __fadd2_rn(make_float2(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1])), make_float2(b.x, b.y));
             const float2 v1 = __fadd2_rn(make_float2(__uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3])), make_float2(b.z, b.w));
             uint32_t h0 = pack_bf16(v0.x, v0.y), h1 = pack_bf16(v1.x, v1.y);
+            if constexpr (kEpi == kEpiGeluBoth) {
+              hw[2 * i] = h0;
+              hw[2 * i + 1] = h1;
+            }
             if (kGelu) {
               const float2 g0 = gelu_value2<false>(__bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h0)), make_float2(0.f, 0.f));
               const float2 g1 = gelu_value2<false>(__bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&h1)), make_float2(0.f, 0.f));
@@ -333,6 +338,15 @@ tc_linear_kernel(const __grid_constant__ Maps maps, const __nv_bfloat16* __restr
             }
             w[2 * i] = h0;
             w[2 * i + 1] = h1;
+          }
+          if constexpr (kEpi == kEpiGeluBoth) {
+            // h goes straight from registers to global memory: this lane's row, 16 columns = one full 32-byte sector
+            const int row = m0 + q * 32 + lane;
+            if (row < M) {
+              uint4* hp = reinterpret_cast<uint4*>(pre_act + (int64_t)row * N + n0 + quarter * 64 + box * 32 + sub * 16);
+              hp[0] = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+              hp[1] = make_uint4(hw[4], hw[5], hw[6], hw[7]);
+            }
           }
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
@@ -387,8 +401,8 @@ static int g_pair_mode = -1;
 void set_tc_linear_pair_mode(int mode) { g_pair_mode = mode; }
 
 template <int kEpi, int kCtas>
-static cudaError_t launch_tc_linear_as(const tcl::Maps& maps, const void* bias, const void* residual, int64_t rows, int in_features,
-                                       int out_features, cudaStream_t st, const char** err) {
+static cudaError_t launch_tc_linear_as(const tcl::Maps& maps, const void* bias, const void* residual, void* pre_act, int64_t rows,
+                                       int in_features, int out_features, cudaStream_t st, const char** err) {
   auto kernel = tcl::tc_linear_kernel<kEpi, kCtas>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tcl::kSmemBytes);
   if (e != cudaSuccess) {
@@ -411,16 +425,16 @@ static cudaError_t launch_tc_linear_as(const tcl::Maps& maps, const void* bias, 
   cfg.numAttrs = kCtas > 1 ? 1 : 0;
   {
     TimedRegion timed(st);
-    e = cudaLaunchKernelEx(&cfg, kernel, maps, static_cast<const __nv_bfloat16*>(bias), static_cast<const __nv_bfloat16*>(residual), (int)rows,
-                           out_features, in_features);
+    e = cudaLaunchKernelEx(&cfg, kernel, maps, static_cast<const __nv_bfloat16*>(bias), static_cast<const __nv_bfloat16*>(residual),
+                           static_cast<__nv_bfloat16*>(pre_act), (int)rows, out_features, in_features);
   }
   if (e != cudaSuccess) return e;
   count_launch();
   return cudaGetLastError();
 }
 
-cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* y, int64_t rows, int in_features,
-                             int out_features, int activation, cudaStream_t st, const char** err) {
+cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* pre_act, void* y, int64_t rows,
+                             int in_features, int out_features, int activation, cudaStream_t st, const char** err) {
   // CTA pairs (cta_group::2) halve the W fill per CTA; they win from K = 192 up (profiles/r1_micro_linear_pair.jsonl)
   // unless the coarser 256-token tiles cost an extra round of the persistent loop (3 344 x 1024 x 4096: 224 pair tiles on
   // 74 pairs = 4 rounds against 3 rounds of 432 tiles on 148 CTAs).
@@ -441,9 +455,10 @@ cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias
     return cudaErrorInvalidValue;
   }
 #define SWIN_TCL_LAUNCH(EPI)                                                                                                   \
-  (pair ? launch_tc_linear_as<EPI, 2>(maps, bias, residual, rows, in_features, out_features, st, err)                          \
-        : launch_tc_linear_as<EPI, 1>(maps, bias, residual, rows, in_features, out_features, st, err))
+  (pair ? launch_tc_linear_as<EPI, 2>(maps, bias, residual, pre_act, rows, in_features, out_features, st, err)                 \
+        : launch_tc_linear_as<EPI, 1>(maps, bias, residual, pre_act, rows, in_features, out_features, st, err))
   if (residual != nullptr) return SWIN_TCL_LAUNCH(tcl::kEpiResidual);
+  if (pre_act != nullptr) return SWIN_TCL_LAUNCH(tcl::kEpiGeluBoth);
   if (activation) return SWIN_TCL_LAUNCH(tcl::kEpiGelu);
   return SWIN_TCL_LAUNCH(tcl::kEpiNone);
 #undef SWIN_TCL_LAUNCH

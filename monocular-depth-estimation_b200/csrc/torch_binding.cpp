@@ -462,6 +462,33 @@ Tensor linear_act_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& b
   return y;
 }
 
+// (h, GELU(h)) = linear_gelu_both(x, W, b): the training form of fc1 + GELU, one tcgen05 GEMM writing both tensors
+std::tuple<Tensor, Tensor> linear_gelu_both_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& bias) {
+  TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && weight.scalar_type() == at::kBFloat16 && bias.scalar_type() == at::kBFloat16,
+              "swin_attn::linear_gelu_both: x, weight and bias must be bfloat16");
+  TORCH_CHECK(weight.dim() == 2 && bias.dim() == 1 && x_in.dim() >= 1 && x_in.size(-1) == weight.size(1) && bias.size(0) == weight.size(0),
+              "swin_attn::linear_gelu_both: x (..., in), weight (out, in), bias (out)");
+  const Tensor x = x_in.contiguous(), w = weight.contiguous(), b = bias.contiguous();
+  std::vector<int64_t> shape(x.sizes().begin(), x.sizes().end());
+  shape.back() = w.size(0);
+  Tensor h = at::empty(shape, x.options()), y = at::empty(shape, x.options());
+  if (y.numel() == 0) return {h, y};
+  c10::cuda::CUDAGuard guard(x.device());
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  const int64_t rows = x.numel() / x.size(-1), k = w.size(1), n = w.size(0);
+  TimedLaunch timed(stream);
+  check_rc(swin_linear_gelu_forward_train(x.data_ptr(), w.data_ptr(), b.data_ptr(), h.data_ptr(), y.data_ptr(), rows, (int32_t)k, (int32_t)n,
+                                          stream));
+  timed.finish(2 * (rows * k + n * k + 2 * rows * n), 2 * rows * n * k, 2, k, 3, n, rows, 0);
+  return {h, y};
+}
+
+std::tuple<Tensor, Tensor> linear_gelu_both_meta(const Tensor& x, const Tensor& weight, const Tensor&) {
+  std::vector<c10::SymInt> shape(x.sym_sizes().begin(), x.sym_sizes().end());
+  shape.back() = weight.sym_size(0);
+  return {at::empty_symint(shape, x.options()), at::empty_symint(shape, x.options())};
+}
+
 // residual + (x W^T + b) with the tcgen05 GEMM (inference; bf16 residual stream)
 Tensor linear_residual_cuda(const Tensor& x_in, const Tensor& weight, const Tensor& bias, const Tensor& residual_in) {
   TORCH_CHECK(x_in.scalar_type() == at::kBFloat16 && weight.scalar_type() == at::kBFloat16 && bias.scalar_type() == at::kBFloat16 &&
@@ -761,6 +788,54 @@ struct LinearFunction : public torch::autograd::Function<LinearFunction> {
   }
 };
 
+// GELU(x W^T + b) in training under bf16 autocast: ONE forward kernel (the tcgen05 GEMM writes h and GELU(h)); backward =
+// the fused GELU backward on the saved h, then the Linear backward of LinearFunction (cuBLAS dgrad / wgrad in fp32 for
+// fp32 master weights, fused column sum for the bias).
+struct LinearGeluFunction : public torch::autograd::Function<LinearGeluFunction> {
+  static Tensor forward(AutogradContext* ctx, const Tensor& x, const Tensor& weight, const Tensor& bias) {
+    at::AutoDispatchBelowADInplaceOrView guard;
+    static auto op = c10::Dispatcher::singleton()
+                         .findSchemaOrThrow("swin_attn::linear_gelu_both", "")
+                         .typed<std::tuple<Tensor, Tensor>(const Tensor&, const Tensor&, const Tensor&)>();
+    const Tensor xb = x.to(at::kBFloat16), wb = weight.to(at::kBFloat16);
+    auto out = op.call(xb, wb, bias.to(at::kBFloat16));
+    ctx->save_for_backward({xb, wb, std::get<0>(out)});
+    ctx->saved_data["x_dtype"] = (int64_t)x.scalar_type();
+    ctx->saved_data["w_dtype"] = (int64_t)weight.scalar_type();
+    ctx->saved_data["b_dtype"] = (int64_t)bias.scalar_type();
+    return std::get<1>(out);
+  }
+  static variable_list backward(AutogradContext* ctx, variable_list grads) {
+    static auto colsum = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::bias_grad", "").typed<Tensor(const Tensor&)>();
+    static auto gelu_bwd = c10::Dispatcher::singleton().findSchemaOrThrow("swin_attn::gelu_bwd", "").typed<Tensor(const Tensor&, const Tensor&)>();
+    const auto saved = ctx->get_saved_variables();
+    const Tensor &xb = saved[0], &wb = saved[1], &h = saved[2];
+    const int64_t n = wb.size(0), k = wb.size(1);
+    const Tensor dy = gelu_bwd.call(grads[0], h).reshape({-1, n});
+    Tensor dx, dw, db;
+    if (ctx->needs_input_grad(0))
+      dx = at::mm(dy, wb).view(xb.sizes()).to((at::ScalarType)ctx->saved_data["x_dtype"].toInt());
+    if (ctx->needs_input_grad(1)) {
+      const auto wd = (at::ScalarType)ctx->saved_data["w_dtype"].toInt();
+      dw = wd == at::kFloat ? at::mm(dy.t(), xb.reshape({-1, k}), at::kFloat) : at::mm(dy.t(), xb.reshape({-1, k})).to(wd);
+    }
+    if (ctx->needs_input_grad(2)) db = colsum.call(dy).to((at::ScalarType)ctx->saved_data["b_dtype"].toInt());
+    return {dx, dw, db};
+  }
+};
+
+Tensor linear_gelu_autograd(const Tensor& x, const Tensor& weight, const Tensor& bias) {
+  return LinearGeluFunction::apply(x, weight, bias);
+}
+
+// below autograd (no_grad callers): the fused forward alone
+Tensor linear_gelu_plain(const Tensor& x, const Tensor& weight, const Tensor& bias) {
+  static auto op = c10::Dispatcher::singleton()
+                       .findSchemaOrThrow("swin_attn::linear_act", "")
+                       .typed<Tensor(const Tensor&, const Tensor&, const Tensor&, int64_t)>();
+  return op.call(x.to(at::kBFloat16), weight.to(at::kBFloat16), bias.to(at::kBFloat16), 1);
+}
+
 Tensor linear_autograd(const Tensor& x, const Tensor& weight, const optional<Tensor>& bias) {
   return LinearFunction::apply(x, weight, bias);
 }
@@ -792,6 +867,8 @@ TORCH_LIBRARY(swin_attn, m) {
   m.def("gelu_bwd(Tensor dy, Tensor x) -> Tensor");
   m.def("linear_act(Tensor x, Tensor weight, Tensor bias, int activation) -> Tensor");
   m.def("linear_residual(Tensor x, Tensor weight, Tensor bias, Tensor residual) -> Tensor");
+  m.def("linear_gelu_both(Tensor x, Tensor weight, Tensor bias) -> (Tensor, Tensor)");
+  m.def("linear_gelu(Tensor x, Tensor weight, Tensor bias) -> Tensor");
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
@@ -809,6 +886,8 @@ TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
   m.impl("gelu_bwd", gelu_bwd_cuda);
   m.impl("linear_act", linear_act_cuda);
   m.impl("linear_residual", linear_residual_cuda);
+  m.impl("linear_gelu_both", linear_gelu_both_cuda);
+  m.impl("linear_gelu", linear_gelu_plain);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
@@ -826,6 +905,8 @@ TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
   m.impl("gelu_bwd", gelu_bwd_meta);
   m.impl("linear_act", linear_act_meta);
   m.impl("linear_residual", linear_residual_meta);
+  m.impl("linear_gelu_both", linear_gelu_both_meta);
+  m.impl("linear_gelu", linear_gelu_plain);
 }
 
 TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
@@ -837,6 +918,8 @@ TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
   m.impl("linear_act", torch::autograd::autogradNotImplementedFallback());   // inference only
   m.impl("patch_merge_norm", torch::autograd::autogradNotImplementedFallback());   // inference only
   m.impl("linear_residual", torch::autograd::autogradNotImplementedFallback());    // inference only
+  m.impl("linear_gelu_both", torch::autograd::autogradNotImplementedFallback());   // differentiated through linear_gelu
+  m.impl("linear_gelu", linear_gelu_autograd);
 }
 
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------

@@ -143,7 +143,9 @@ def linear_gelu(lin: torch.nn.Module, act: torch.nn.Module, x: Tensor) -> Tensor
     """``act(lin(x))`` of the block MLP (fc1 -> GELU, newcrf_layers.py:21-23).  Inference under bf16 autocast (or with
     bf16 parameters after ``harness.prepare_inference``) runs ONE tcgen05 GEMM whose epilogue adds the bias, rounds to
     bf16 as the autocast Linear does, applies the exact GELU and rounds again: the hidden tensor is written once.
-    Every other case is ``gelu(act, linear(lin, x))``."""
+    Training under bf16 autocast runs the same GEMM with both h and GELU(h) written (``swin_attn::linear_gelu``, one
+    autograd node: GELU backward on the saved h, then the Linear backward).  Every other case is
+    ``gelu(act, linear(lin, x))``."""
     if (type(lin) is torch.nn.Linear and lin.bias is not None and type(act) is torch.nn.GELU and act.approximate == "none"
             and x.is_cuda and not torch.is_grad_enabled() and lin.in_features % 64 == 0 and lin.out_features % 256 == 0
             and (x.dtype == torch.bfloat16 or x.dtype == torch.float32)
@@ -151,6 +153,12 @@ def linear_gelu(lin: torch.nn.Module, act: torch.nn.Module, x: Tensor) -> Tensor
                  or (x.dtype == torch.bfloat16 and lin.weight.dtype == torch.bfloat16))):
         bf = torch.bfloat16
         return torch.ops.swin_attn.linear_act(x.to(bf), lin.weight.to(bf), lin.bias.to(bf), 1)
+    if (type(lin) is torch.nn.Linear and lin.bias is not None and type(act) is torch.nn.GELU and act.approximate == "none"
+            and x.is_cuda and torch.is_grad_enabled() and lin.in_features % 64 == 0 and lin.out_features % 256 == 0
+            and x.dtype in _DTYPES and lin.weight.dtype in _DTYPES and (x.requires_grad or lin.weight.requires_grad)
+            and torch.is_autocast_enabled() and torch.get_autocast_dtype("cuda") == torch.bfloat16):
+        # training: one autograd node; its forward is the same GEMM writing h (for the GELU backward) and GELU(h)
+        return torch.ops.swin_attn.linear_gelu(x, lin.weight, lin.bias)
     return gelu(act, linear(lin, x))
 
 
