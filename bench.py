@@ -164,7 +164,7 @@ def run_ours(args, env):
     if train:
         from mde_b200.harness import Trainer, synthetic_depth
         model.train()
-        trainer = Trainer(model, ddp=world > 1, device_ids=[local] if world > 1 else None)
+        trainer = Trainer(model, ddp=world > 1, device_ids=[local] if world > 1 else None, capturable=world == 1)
         gt_host = synthetic_depth(args.batch, height, width, max_depth, seed=100 + rank).pin_memory()
         gt = gt_host.to(dev)
         out_host = torch.empty(1).pin_memory()
@@ -217,7 +217,19 @@ def run_ours(args, env):
     ops.set_kernel_timing(None)
     launches = _lib.launch_count() - launches0
     barrier()
+    gstep = None
     if train:
+        if world == 1 and not args.no_graph:
+            # single-process training: the whole step (fwd + loss + bwd + clip + AdamW) replayed from a CUDA graph
+            # (harness.GraphedTrainStep); captured after the eager region, whose launches carry the roofline events
+            from mde_b200.harness import GraphedTrainStep
+            gstep = GraphedTrainStep(trainer, images, gt, warmup=2)
+
+            def step_e2e():   # noqa: F811  (the end-to-end step through the graph: H2D -> static inputs -> replay -> D2H)
+                x, y = host.to(dev, non_blocking=True), gt_host.to(dev, non_blocking=True)
+                out_host.copy_(gstep(x, y).reshape(1), non_blocking=True)
+            for _ in range(2):
+                step_e2e()
         t_e2e = timed_steps(step_e2e, args.steps)
     else:
         # One event pair brackets the whole K-step serving region, so a single host hiccup (GC, the clock sampler taking
@@ -231,6 +243,8 @@ def run_ours(args, env):
     if not train and graphed is not None:
         barrier()
         t_graph = timed_steps(lambda: graphed(images), args.steps)   # device-resident, the forward replayed as one graph
+    if gstep is not None:
+        t_graph = timed_steps(lambda: gstep(images, gt), args.steps)  # device-resident, the training step as one graph
     barrier()
     sampler.stop_flag = True
     if sampler.is_alive():
@@ -282,7 +296,10 @@ def run_ours(args, env):
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload, "parallelism": par,
                    "l2_flush_between_steps": True, "timing": "CUDA events per step, max over ranks",
-                   "e2e_timing": ("per step: H2D -> step -> D2H on one stream" if train else
+                   "e2e_timing": (("per step: H2D -> step -> D2H on one stream" + ("" if gstep is None else
+                                   "; the step is replayed from a CUDA graph (harness.GraphedTrainStep), while `value` is the eager "
+                                   "step so that the attention launches can be bracketed by CUDA events for the roofline"))
+                                  if train else
                                   "median of 5 regions, each one event pair around K steps of harness.infer_host_batches (pinned host in / out, "
                                   "copies of neighbouring steps overlapped on copy streams, L2 flush inside"
                                   + (")" if args.no_graph else "; the forward is replayed from a CUDA graph, "
@@ -314,7 +331,9 @@ def run_ours(args, env):
                 "GBps": sum(r[1] for r in rs) / (ms * 1e-3) / 1e9}
     if t_graph:
         line["graph_replay"] = {"value": n_img / t_graph, "unit": "images/s", "ms_per_step": t_graph / args.steps * 1e3,
-                                "note": "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)"}
+                                "note": ("device-resident like `value`, the whole training step replayed from a CUDA graph "
+                                         "(harness.GraphedTrainStep)" if train else
+                                         "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)")}
     if train:
         line["roofline_forward"] = roof_fwd
     if world == 1 and not args.no_cpu_baseline and not train:

@@ -215,13 +215,14 @@ class Trainer:
     """fwd + SILog + bwd (+ DDP all-reduce) + clip + AdamW, per the reference's JSON schema."""
 
     def __init__(self, model: nn.Module, lr: float = 2e-5, grad_norm: float = 0.1, bf16: bool = True,
-                 ddp: bool = False, device_ids=None):
+                 ddp: bool = False, device_ids=None, capturable: bool = False):
         self.raw = model
         # gradients live inside the all-reduce buckets: no per-parameter copy kernel (~600 launches per step)
         self.model = nn.parallel.DistributedDataParallel(model, device_ids=device_ids,
                                                          gradient_as_bucket_view=True) if ddp else model
-        self.opt = torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=0.0,
-                                     fused=next(model.parameters()).is_cuda)   # one multi-tensor kernel per step
+        # one multi-tensor kernel per step; ``capturable``: the step counter lives on the device (GraphedTrainStep)
+        self.opt = torch.optim.AdamW(model.parameters(), lr=lr, weight_decay=0.0, fused=next(model.parameters()).is_cuda,
+                                     capturable=capturable and next(model.parameters()).is_cuda)
         self.loss_fn = SILogLoss()
         self.grad_norm, self.bf16 = grad_norm, bf16
 
@@ -235,3 +236,40 @@ class Trainer:
             torch.nn.utils.clip_grad_norm_(self.raw.parameters(), self.grad_norm)
         self.opt.step()
         return loss.detach()
+
+
+class GraphedTrainStep:
+    """``trainer.step(images, gt)`` for one batch shape as a CUDA graph: forward, SILog loss, backward, gradient clipping
+    and the fused AdamW update (~4 000 launches, no host synchronisation, no data-dependent control flow; the tensor
+    maps of the tcgen05 kernels are kernel parameters encoded at capture time over the graph's private memory pool)
+    captured once and replayed as one graph launch.  The eager training step is close to launch-bound -- its time follows
+    the host CPU from box to box -- and the replay is not.  Single-process training only (the DDP step stays eager);
+    the trainer needs ``capturable=True``.  The ``warmup`` eager steps before the capture are real training steps.
+    ``__call__`` copies the batch into the static inputs and returns the static loss, valid until the next call."""
+
+    def __init__(self, trainer: "Trainer", images: torch.Tensor, gt: torch.Tensor, warmup: int = 3):
+        if isinstance(trainer.model, nn.parallel.DistributedDataParallel):
+            raise ValueError("GraphedTrainStep captures the single-process step; the DDP step stays eager")
+        if not trainer.opt.defaults.get("capturable", False):
+            raise ValueError("build the Trainer with capturable=True (device-side AdamW step counter)")
+        self.trainer = trainer
+        self.static_images, self.static_gt = images.detach().clone(), gt.detach().clone()
+        side = torch.cuda.Stream(images.device)
+        side.wait_stream(torch.cuda.current_stream(images.device))
+        with torch.cuda.stream(side):               # allocator, cuBLAS / cuDNN workspaces and optimizer state warm
+            for _ in range(warmup):
+                trainer.step(self.static_images, self.static_gt)
+        torch.cuda.current_stream(images.device).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):
+            self.static_loss = trainer.step(self.static_images, self.static_gt)
+
+    def __call__(self, images: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
+        if images.shape != self.static_images.shape or gt.shape != self.static_gt.shape:
+            raise ValueError(f"graph captured for {tuple(self.static_images.shape)} / {tuple(self.static_gt.shape)}, "
+                             f"got {tuple(images.shape)} / {tuple(gt.shape)}")
+        self.static_images.copy_(images, non_blocking=True)
+        self.static_gt.copy_(gt, non_blocking=True)
+        self.graph.replay()
+        return self.static_loss
+

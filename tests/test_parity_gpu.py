@@ -1074,3 +1074,46 @@ def test_add_norm_training_node_matches_unfused_autograd(channels, gated, stream
         assert rel_err(g, r) <= rel_err(w, r) * 1.5 + 1e-6, (n, rel_err(g, r), rel_err(w, r))
     if gated:
         assert float(got[3][0].float().abs().max()) == 0.0       # dropped sample: no gradient into the branch
+
+
+def test_graphed_train_step_follows_the_eager_training_steps():
+    """harness.GraphedTrainStep (forward + SILog + backward + clip + AdamW captured as one CUDA graph) against the eager
+    Trainer.step on the same batches from the same initial state: same losses step by step (up to the order of the
+    atomic sums in the backward kernels) and the same parameters afterwards."""
+    from mde_b200 import harness
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.level = layers.NewCRF(input_dim=64, embed_dim=128, window_size=7, v_dim=64, num_heads=4)
+            self.head = torch.nn.Conv2d(128, 1, 3, padding=1)
+
+        def forward(self, x):
+            return torch.sigmoid(self.head(self.level(x, x))) * 10.0 + 1e-3
+
+    gen = torch.Generator(device=DEV).manual_seed(5)
+    batches = [(torch.randn(2, 64, 16, 23, device=DEV, generator=gen), torch.rand(2, 1, 16, 23, device=DEV, generator=gen) * 9 + 0.5)
+               for _ in range(6)]
+
+    def run(graphed):
+        torch.manual_seed(3)
+        net = Net().to(DEV).train()
+        tr = harness.Trainer(net, lr=1e-3, grad_norm=0.1, capturable=True)
+        losses = []
+        step = None
+        for i, (x, gt) in enumerate(batches):
+            if graphed and i == 3:                                   # three eager steps, then capture and replay
+                step = harness.GraphedTrainStep(tr, x, gt, warmup=0)
+            losses.append(float(step(x, gt)) if graphed and i >= 3 else float(tr.step(x, gt)))
+        return net, losses
+
+    net_e, loss_e = run(False)
+    net_g, loss_g = run(True)
+    assert loss_e[:3] == loss_g[:3] or all(abs(a - b) <= 1e-4 * abs(a) for a, b in zip(loss_e[:3], loss_g[:3]))
+    for a, b in zip(loss_e[3:], loss_g[3:]):
+        assert abs(a - b) <= 2e-3 * abs(a), (loss_e, loss_g)
+    for (n, p), (_, q) in zip(net_e.named_parameters(), net_g.named_parameters()):
+        assert float(((p - q).abs() > 5e-4).float().mean()) < 1e-2, n
+    with pytest.raises(ValueError):
+        harness.GraphedTrainStep(harness.Trainer(Net().to(DEV)), *batches[0])     # needs capturable=True
+
