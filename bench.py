@@ -137,6 +137,9 @@ def run_ours(args, env):
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     train = args.mode == "train"
+    if train and world > 1 and not args.no_graph:
+        # the DDP step is captured in a CUDA graph (harness.GraphedTrainStep): the whole job runs on one non-default stream
+        torch.cuda.set_stream(torch.cuda.Stream(dev))
     height, width, max_depth = (480, 640, 10.0) if train else (HEIGHT, WIDTH, MAX_DEPTH)
     model = build_model(args.version, max_depth, seed=0, device=dev)
     host = synthetic_images(args.batch, height, width, seed=rank, pin=True)
@@ -164,7 +167,8 @@ def run_ours(args, env):
     if train:
         from mde_b200.harness import Trainer, synthetic_depth
         model.train()
-        trainer = Trainer(model, ddp=world > 1, device_ids=[local] if world > 1 else None, capturable=world == 1)
+        graph_step = not args.no_graph and (world == 1 or os.environ.get("TORCH_NCCL_ASYNC_ERROR_HANDLING") == "0")
+        trainer = Trainer(model, ddp=world > 1, device_ids=[local] if world > 1 else None, capturable=graph_step)
         gt_host = synthetic_depth(args.batch, height, width, max_depth, seed=100 + rank).pin_memory()
         gt = gt_host.to(dev)
         out_host = torch.empty(1).pin_memory()
@@ -219,7 +223,7 @@ def run_ours(args, env):
     barrier()
     gstep = None
     if train:
-        if world == 1 and not args.no_graph:
+        if graph_step:
             # single-process training: the whole step (fwd + loss + bwd + clip + AdamW) replayed from a CUDA graph
             # (harness.GraphedTrainStep); captured after the eager region, whose launches carry the roofline events
             from mde_b200.harness import GraphedTrainStep
@@ -243,8 +247,14 @@ def run_ours(args, env):
     if not train and graphed is not None:
         barrier()
         t_graph = timed_steps(lambda: graphed(images), args.steps)   # device-resident, the forward replayed as one graph
+    in_sync = None
     if gstep is not None:
         t_graph = timed_steps(lambda: gstep(images, gt), args.steps)  # device-resident, the training step as one graph
+        if world > 1:
+            # every rank trains on its own images: the replicas stay identical only if the captured step really
+            # all-reduces the gradients
+            from mde_b200.harness import replicas_in_sync
+            in_sync = replicas_in_sync(model)
     barrier()
     sampler.stop_flag = True
     if sampler.is_alive():
@@ -336,6 +346,8 @@ def run_ours(args, env):
                                          "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)")}
     if train:
         line["roofline_forward"] = roof_fwd
+        if in_sync is not None:
+            line["graph_replay"]["ddp_replicas_in_sync"] = in_sync
     if world == 1 and not args.no_cpu_baseline and not train:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
@@ -369,6 +381,10 @@ def main():
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
+    if args.mode == "train" and not args.no_graph:
+        # precondition of capturing NCCL collectives in a CUDA graph (torch's DDP + whole-network-capture recipe)
+        # (torchrun exports TORCH_NCCL_ASYNC_ERROR_HANDLING=1 to its workers: override, not setdefault)
+        os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"
     env = init_distributed("nccl")
     run_ours(args, env)
     if env["world"] > 1:

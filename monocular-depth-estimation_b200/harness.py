@@ -75,6 +75,19 @@ def init_distributed(backend: Optional[str] = None) -> Dict[str, int]:
     return env
 
 
+def replicas_in_sync(model: nn.Module, rtol: float = 0.0) -> bool:
+    """True when every rank holds the same parameters (the invariant DDP maintains: identical initial values, identical
+    all-reduced gradients, identical optimizer steps): compares an fp64 checksum of every parameter across ranks."""
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+        return True
+    with torch.no_grad():
+        chk = torch.stack([p.detach().double().sum() for p in model.parameters()])
+        lo, hi = chk.clone(), chk.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        return bool(((hi - lo).abs() <= rtol * hi.abs()).all())
+
+
 def shard_batch(t: torch.Tensor, rank: int, world: int) -> torch.Tensor:
     """Contiguous split of the global batch, as DistributedSampler-without-shuffle would."""
     per = t.shape[0] // world
@@ -218,6 +231,13 @@ class Trainer:
                  ddp: bool = False, device_ids=None, capturable: bool = False):
         self.raw = model
         # gradients live inside the all-reduce buckets: no per-parameter copy kernel (~600 launches per step)
+        if ddp and capturable and next(model.parameters()).is_cuda and \
+                torch.cuda.current_stream() == torch.cuda.default_stream():
+            # torch's recipe for capturing a DistributedDataParallel step builds the wrapper off the default stream; built
+            # on a side stream while the steps run on the default one, every gradient accumulation pays a cross-stream
+            # synchronisation in eager mode (42.3 against 39.4 ms at 2 GPUs) -- so the whole job moves to one stream
+            raise ValueError("a capturable DDP Trainer must be built, and stepped, on a non-default CUDA stream: call "
+                             "torch.cuda.set_stream(torch.cuda.Stream()) first")
         self.model = nn.parallel.DistributedDataParallel(model, device_ids=device_ids,
                                                          gradient_as_bucket_view=True) if ddp else model
         # one multi-tensor kernel per step; ``capturable``: the step counter lives on the device (GraphedTrainStep)
@@ -243,13 +263,19 @@ class GraphedTrainStep:
     and the fused AdamW update (~4 000 launches, no host synchronisation, no data-dependent control flow; the tensor
     maps of the tcgen05 kernels are kernel parameters encoded at capture time over the graph's private memory pool)
     captured once and replayed as one graph launch.  The eager training step is close to launch-bound -- its time follows
-    the host CPU from box to box -- and the replay is not.  Single-process training only (the DDP step stays eager);
-    the trainer needs ``capturable=True``.  The ``warmup`` eager steps before the capture are real training steps.
+    the host CPU from box to box -- and the replay is not.  With DistributedDataParallel the bucketed NCCL all-reduce is
+    captured with the step (see __init__ for the preconditions).  The trainer needs ``capturable=True``.  The ``warmup`` eager steps before the capture are real training steps.
     ``__call__`` copies the batch into the static inputs and returns the static loss, valid until the next call."""
 
     def __init__(self, trainer: "Trainer", images: torch.Tensor, gt: torch.Tensor, warmup: int = 3):
         if isinstance(trainer.model, nn.parallel.DistributedDataParallel):
-            raise ValueError("GraphedTrainStep captures the single-process step; the DDP step stays eager")
+            # DDP: the bucketed NCCL all-reduce is captured with the step.  torch's recipe: async error handling of the
+            # NCCL process group off before it is created, the wrapper built off the default stream (a Trainer with
+            # capturable=True insists on it), and at least 11 eager DDP iterations before the capture (bucket rebuild,
+            # reducer state).
+            if os.environ.get("TORCH_NCCL_ASYNC_ERROR_HANDLING", os.environ.get("NCCL_ASYNC_ERROR_HANDLING")) != "0":
+                raise ValueError("capturing a DDP step needs TORCH_NCCL_ASYNC_ERROR_HANDLING=0 set before init_process_group")
+            warmup = max(warmup, 11)
         if not trainer.opt.defaults.get("capturable", False):
             raise ValueError("build the Trainer with capturable=True (device-side AdamW step counter)")
         self.trainer = trainer
