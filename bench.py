@@ -43,6 +43,9 @@ def parse():
                     help="infer: BASELINE configs[1] (the headline metric); train: configs[2], fwd+SILog+bwd+AdamW at 480x640")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="e2e leg launches the forward eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--graph-ddp", action="store_true",
+                    help="--mode train at N > 1: capture the DDP step (with its NCCL all-reduce) in a CUDA graph as well; opt-in "
+                         "(verified at 2 GPUs; the default multi-GPU training bench stays eager)")
     ap.add_argument("--version", default=VERSION)
     ap.add_argument("--batch", type=int, default=BATCH)
     return ap.parse_args()
@@ -137,7 +140,7 @@ def run_ours(args, env):
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     train = args.mode == "train"
-    if train and world > 1 and not args.no_graph:
+    if train and world > 1 and args.graph_ddp and not args.no_graph:
         # the DDP step is captured in a CUDA graph (harness.GraphedTrainStep): the whole job runs on one non-default stream
         torch.cuda.set_stream(torch.cuda.Stream(dev))
     height, width, max_depth = (480, 640, 10.0) if train else (HEIGHT, WIDTH, MAX_DEPTH)
@@ -167,7 +170,7 @@ def run_ours(args, env):
     if train:
         from mde_b200.harness import Trainer, synthetic_depth
         model.train()
-        graph_step = not args.no_graph and (world == 1 or os.environ.get("TORCH_NCCL_ASYNC_ERROR_HANDLING") == "0")
+        graph_step = not args.no_graph and (world == 1 or args.graph_ddp)
         trainer = Trainer(model, ddp=world > 1, device_ids=[local] if world > 1 else None, capturable=graph_step)
         gt_host = synthetic_depth(args.batch, height, width, max_depth, seed=100 + rank).pin_memory()
         gt = gt_host.to(dev)
@@ -381,7 +384,7 @@ def main():
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
-    if args.mode == "train" and not args.no_graph:
+    if args.mode == "train" and args.graph_ddp and not args.no_graph:
         # precondition of capturing NCCL collectives in a CUDA graph (torch's DDP + whole-network-capture recipe)
         # (torchrun exports TORCH_NCCL_ASYNC_ERROR_HANDLING=1 to its workers: override, not setdefault)
         os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"

@@ -50,6 +50,11 @@ def _worker(rank, world, port, out):
     assert torch.allclose(harness.all_reduce_mean(loss), loss_ref, atol=1e-6)
     for a, b in zip(net.parameters(), ref.parameters()):
         assert torch.allclose(a, b, atol=1e-6), "DDP step differs from the full-batch step"
+    # the invariant DDP maintains, as bench.py checks it after replaying a captured DDP step
+    assert harness.replicas_in_sync(net)
+    with torch.no_grad():
+        next(net.parameters()).add_(float(rank))          # rank 1 drifts
+    assert not harness.replicas_in_sync(net)
     dist.barrier()
     dist.destroy_process_group()
     out.put(rank)
