@@ -136,6 +136,14 @@ def test_linear_forward_entry_validates_without_gpu():
     assert lib.swin_linear_forward(ptr, None, ptr, ptr, 4, 192, 768, 1, None) != 0 and b"non-null" in err()
     assert lib.swin_linear_forward(ptr, ptr, odd, ptr, 4, 192, 768, 0, None) != 0 and b"16-byte aligned" in err()
     assert lib.swin_linear_forward(ptr, ptr, ptr, ptr, 0, 192, 768, 1, None) == 0          # empty batch: no-op
+    # the residual and the training (h and GELU(h)) forms share the checks
+    assert lib.swin_linear_residual_forward(ptr, ptr, ptr, None, ptr, 4, 192, 768, None) != 0 and b"non-null" in err()
+    assert lib.swin_linear_residual_forward(ptr, ptr, ptr, odd, ptr, 4, 192, 768, None) != 0 and b"16-byte aligned" in err()
+    assert lib.swin_linear_residual_forward(ptr, ptr, ptr, ptr, ptr, 4, 192, 192, None) != 0 and b"out_features" in err()
+    assert lib.swin_linear_residual_forward(ptr, ptr, ptr, ptr, ptr, 0, 192, 768, None) == 0
+    assert lib.swin_linear_gelu_forward_train(ptr, ptr, ptr, None, ptr, 4, 192, 768, None) != 0 and b"non-null" in err()
+    assert lib.swin_linear_gelu_forward_train(ptr, ptr, ptr, ptr, ptr, 4, 100, 768, None) != 0 and b"in_features" in err()
+    assert lib.swin_linear_gelu_forward_train(ptr, ptr, ptr, ptr, ptr, 0, 192, 768, None) == 0
 
 
 def test_backward_unpadded_entry_validates_without_gpu():
@@ -186,3 +194,18 @@ def test_torch_binding_registers_ops_without_a_gpu():
     with pytest.raises(NotImplementedError):
         torch.ops.swin_attn.fwd(torch.zeros(1, 7, 7, 192), None, torch.zeros(169, 2), None, None, 7, 0, 2, 0.17, False, 0)
     assert ops._torch_lib.swin_torch_pending_timing() == 0
+    # the block-plumbing / GEMM ops of the callers either side of the path: registered, shape inference on meta tensors
+    for name in ("patch_merge_norm", "linear_act", "linear_residual", "linear_gelu", "linear_gelu_both"):
+        assert hasattr(torch.ops.swin_attn, name)
+    bf = torch.bfloat16
+    x = torch.empty(2, 11 * 38, 192, device="meta", dtype=bf)            # odd H: padded to 12 x 38 -> 6 x 19 outputs of 4C
+    y = torch.ops.swin_attn.patch_merge_norm(x, 11, 38, torch.empty(768, device="meta"), torch.empty(768, device="meta"), 1e-5)
+    assert y.shape == (2, 6 * 19, 768) and y.dtype == bf
+    t, w, b = torch.empty(3, 50, 768, device="meta", dtype=bf), torch.empty(256, 768, device="meta", dtype=bf), \
+        torch.empty(256, device="meta", dtype=bf)
+    assert torch.ops.swin_attn.linear_act(t, w, b, 1).shape == (3, 50, 256)
+    assert torch.ops.swin_attn.linear_residual(t, w, b, torch.empty(3, 50, 256, device="meta", dtype=bf)).shape == (3, 50, 256)
+    h, g = torch.ops.swin_attn.linear_gelu_both(t, w, b)
+    assert h.shape == g.shape == (3, 50, 256) and h.dtype == bf
+    with pytest.raises(NotImplementedError):
+        torch.ops.swin_attn.patch_merge_norm(torch.zeros(1, 4, 192), 2, 2, torch.ones(768), torch.zeros(768), 1e-5)
