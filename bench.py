@@ -3,19 +3,27 @@
 352x1216, bf16 autocast, batch 8 per GPU, synthetic KITTI-shape input
 (BASELINE.json configs[1]).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode infer|train]
 
 One JSON line on rank 0.  ``value`` = device-resident throughput, ``e2e`` = the
-same through ``harness.infer`` with pinned-host images copied in and the depth
-map copied out every step.  ``roofline`` is for the window-attention forward
-kernel (all its launches inside the timed region, CUDA events on the launching
-stream); ``cpu_baseline`` / ``--impl reference`` time the oracle's CPU
-restatement of the reference model (the reference is Python + missing deps
-and cannot travel to the GPU box).
+same through the serving loop ``harness.infer_host_batches`` with pinned-host
+images copied in and the depth map copied out every step.  ``roofline`` is for
+the window-attention forward kernel (all its launches inside the timed region,
+CUDA events on the launching stream).  Extra keys of the default line:
+
+* ``train``: BASELINE configs[2] -- fwd + SILog + bwd + clip + AdamW at 480x640, batch 8/GPU, DDP over NCCL at
+  N > 1 (the step, with its gradient all-reduce, replayed from a CUDA graph; the eager step beside it);
+* ``reference_gpu_eager`` (N = 1): the UNMODIFIED reference ``NewCRFDepth`` (``oracle/_ref``) on the same B200,
+  fp32 and ``torch.autocast(bf16)``, same batch, CUDA events;
+* ``cpu_baseline`` (N = 1): the same unmodified reference modules on the host cores.
+
+``--impl reference`` is the reference arm: the unmodified reference on the host cores only; it imports nothing
+from the product package (no product ``.so`` is loaded in that process).
 """
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import statistics
@@ -31,6 +39,8 @@ import torch.distributed as dist  # noqa: E402
 
 VERSION, HEIGHT, WIDTH, BATCH, MAX_DEPTH = "large07", 352, 1216, 8, 80.0
 METRIC = "NewCRFs Swin-L images/sec @352x1216 (bf16 inference, batch 8/GPU)"
+TRAIN_METRIC = "NewCRFs Swin-L training images/sec @480x640 (bf16 autocast fwd + SILog + bwd + clip + AdamW, batch 8/GPU)"
+TRAIN_LEG_TIMEOUT_S = 420.0
 
 
 def parse():
@@ -40,15 +50,25 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="infer", choices=["infer", "train"],
-                    help="infer: BASELINE configs[1] (the headline metric); train: configs[2], fwd+SILog+bwd+AdamW at 480x640")
+                    help="infer: BASELINE configs[1] (the headline metric) with configs[2] as the `train` extra key; "
+                         "train: configs[2] as the line itself (fwd+SILog+bwd+AdamW at 480x640)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-graph", action="store_true", help="e2e leg launches the forward eagerly instead of replaying a CUDA graph")
-    ap.add_argument("--graph-ddp", action="store_true",
-                    help="--mode train at N > 1: capture the DDP step (with its NCCL all-reduce) in a CUDA graph as well; opt-in "
-                         "(verified at 2 GPUs; the default multi-GPU training bench stays eager)")
+    ap.add_argument("--no-graph", action="store_true", help="launch eagerly everywhere; no CUDA graph replay")
+    ap.add_argument("--graph-ddp", action="store_true", help="(the default now; kept for compatibility)")
+    ap.add_argument("--no-graph-ddp", action="store_true",
+                    help="training at N > 1: keep the eager DDP step; do not capture it (with its NCCL all-reduce) in a CUDA graph")
+    ap.add_argument("--no-train-leg", action="store_true", help="default mode: skip the `train` extra key (BASELINE configs[2])")
+    ap.add_argument("--no-reference-gpu", action="store_true", help="skip the `reference_gpu_eager` extra key")
+    ap.add_argument("--bf16-grad-hook", action="store_true",
+                    help="training at N > 1: DDP's bf16_compress_hook on the gradient buckets (halves the all-reduce bytes)")
     ap.add_argument("--version", default=VERSION)
     ap.add_argument("--batch", type=int, default=BATCH)
     return ap.parse_args()
+
+
+def dist_env():
+    return dict(rank=int(os.environ.get("RANK", 0)), local_rank=int(os.environ.get("LOCAL_RANK", 0)),
+                world=int(os.environ.get("WORLD_SIZE", 1)))
 
 
 def peaks():
@@ -86,79 +106,178 @@ class ClockSampler(threading.Thread):
         except Exception as e:  # clocks are a report, not a dependency
             self.reasons.add(f"unavailable:{type(e).__name__}")
 
+    def stop(self):
+        self.stop_flag = True
+        if self.is_alive():
+            self.join(timeout=2)
+
     def summary(self):
         return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def cpu_model_and_sample(version):
-    from oracle.cpu_model import build_newcrfs
-    from mde_b200.harness import synthetic_images
-    model = build_newcrfs(version, seed=0, max_depth=MAX_DEPTH)
-    return model, synthetic_images(1, HEIGHT, WIDTH, seed=0)
+# ---- the reference's own code on the host cores ------------------------------------------------------------------
+
+def cpu_reference(version, steps, warmup, threads):
+    """Times the UNMODIFIED reference ``NewCRFDepth(version)`` (oracle/_ref or /root/reference through the shim), fp32,
+    ``torch.no_grad()``, one 352x1216 image per step, on ``threads`` host threads.  Falls back to the oracle port (the
+    product's module graph with the oracle attention, ``kind: "port"``) only when no reference tree is staged."""
+    from oracle import ref_model
+    torch.set_num_threads(threads)
+    if ref_model.available():
+        from oracle import reference_shim
+        model = ref_model.build_newcrfs(version, MAX_DEPTH, seed=0)
+        kind, src = "reference", f"unmodified model/NewCRFs/NewCRFDepth.py from {reference_shim.source()} (timm / mmcv: 4-symbol shim)"
+    else:
+        from oracle.cpu_model import build_newcrfs   # imports the product package: last resort, labelled as a port
+        model = build_newcrfs(version, seed=0, max_depth=MAX_DEPTH)
+        kind, src = "port", "oracle/cpu_model.py (oracle/_ref not staged: run __graft_entry__.build() where /root/reference exists)"
+    img = ref_model.images(1, HEIGHT, WIDTH, seed=0)
+    times = ref_model.time_forward(lambda: model(img), steps, warmup)
+    return {"value": steps / sum(times), "unit": "images/s", "cores": threads, "kind": kind, "source": src,
+            "sample": f"1 image (of the batch-8 workload) per step, fp32, torch CPU, {warmup} warm-up + {steps} timed forwards",
+            "median_images_per_s": 1.0 / statistics.median(times), "best_images_per_s": 1.0 / min(times),
+            "worst_images_per_s": 1.0 / max(times), "ms_per_step": sum(times) / steps * 1e3}
 
 
-def time_cpu(model, img, steps, warmup):
+def cpu_reference_configs0(threads):
+    """BASELINE configs[0]: the NeWCRF decoder block (crf3 .. crf0, window 7) of the reference ``tiny07`` model on its own
+    encoder + PSP features of one synthetic 352x704 image, fp32 on the CPU (model/NewCRFs/NewCRFDepth.py:131-137):
+    2 warm-ups, median / best of 5 on all threads, median of 3 on one thread."""
+    from oracle import ref_model
+    if not ref_model.available():
+        return None
+    model = ref_model.build_newcrfs("tiny07", MAX_DEPTH, seed=0)
+    img = ref_model.images(1, 352, 704, seed=0)
     with torch.no_grad():
-        for _ in range(warmup):
-            model(img)
-        t0 = time.perf_counter()
-        for _ in range(steps):
-            model(img)
-        dt = time.perf_counter() - t0
-    return img.shape[0] * steps / dt, dt / steps
+        feats = model.backbone(img)
+        ppm = model.decoder(feats)
+    out = {"workload": "NeWCRF decoder crf3..crf0 (window 7) on tiny07 encoder + PSP features, 1x3x352x704, fp32, CPU"}
+    for label, n_threads, steps, warmup in (("all_threads", threads, 5, 2), ("one_thread", 1, 3, 1)):
+        torch.set_num_threads(n_threads)
+        t = ref_model.time_forward(lambda: ref_model.decoder_only_forward(model, feats, ppm), steps, warmup)
+        out[label] = {"threads": n_threads, "median_ms": statistics.median(t) * 1e3, "best_ms": min(t) * 1e3, "n": steps}
+    torch.set_num_threads(threads)
+    return out
 
 
 def run_reference(args, rank):
-    """Reference arm: the reference's CPU implementation of the path (oracle port;
-    see module docstring), every host thread, one image of the workload per step."""
+    """Reference arm: the reference's own CPU implementation, every host thread, one image of the workload per step.
+    Imports nothing from the product package."""
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    model, img = cpu_model_and_sample(args.version)
-    ips, spstep = time_cpu(model, img, args.steps, args.warmup)
+    base = cpu_reference(args.version, args.steps, args.warmup, cores)
     line = {
-        "impl": "reference", "metric": METRIC, "value": ips, "unit": "images/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": spstep * 1e3, "higher_is_better": True,
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": "images/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": base["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"NewCRFs {args.version} full-model inference, 352x1216 KITTI shape",
                    "sample": "1 image per step on the host CPU"},
-        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
-                         "sample": "1 image (of the batch-8 workload) per step, fp32, torch CPU"},
-        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    try:
+        line["configs0"] = cpu_reference_configs0(cores)
+    except Exception as e:   # an extra key must never cost the line
+        line["configs0"] = {"error": f"{type(e).__name__}: {e}"}
     emit(line)
 
 
-def run_ours(args, env):
-    from mde_b200 import _lib, ops
-    from mde_b200.harness import GraphedInference, build_model, infer, infer_host_batches, prepare_inference, synthetic_images
+def reference_gpu_eager(args, dev, flush):
+    """The unmodified reference modules on the B200 (PyTorch eager: ATen / cuBLAS / cuDNN), same batch as `value`,
+    fp32 (TF32 off, torch's default) and torch.autocast(bf16) -- the "existing Blackwell implementation" (SURVEY F8)."""
+    from oracle import ref_model, reference_shim
+    if not ref_model.available():
+        return {"unavailable": "oracle/_ref not staged"}
+    model = ref_model.build_newcrfs(args.version, MAX_DEPTH, seed=0, device=dev)
+    x = ref_model.images(args.batch, HEIGHT, WIDTH, seed=0).to(dev)
+    out = {"source": reference_shim.source(), "batch": args.batch, "timing": "CUDA events per step, L2 flushed, 2 warm-ups + 5 steps"}
+    for label, bf16 in (("bf16_autocast", True), ("fp32", False)):
+        def step():
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf16):
+                model(x)
+        ms = ref_model.time_forward_cuda(step, 5, 2, flush)
+        out[label] = {"images_per_s": args.batch / (statistics.median(ms) * 1e-3), "ms_per_step": statistics.median(ms),
+                      "best_ms": min(ms)}
+    del model, x
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
 
-    rank, world, local = env["rank"], env["world"], env["local_rank"]
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    train = args.mode == "train"
-    if train and world > 1 and args.graph_ddp and not args.no_graph:
-        # the DDP step is captured in a CUDA graph (harness.GraphedTrainStep): the whole job runs on one non-default stream
-        torch.cuda.set_stream(torch.cuda.Stream(dev))
-    height, width, max_depth = (480, 640, 10.0) if train else (HEIGHT, WIDTH, MAX_DEPTH)
-    model = build_model(args.version, max_depth, seed=0, device=dev)
-    host = synthetic_images(args.batch, height, width, seed=rank, pin=True)
-    images = host.to(dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
-    def barrier():
-        if world > 1:
+# ---- helpers of the product arm -------------------------------------------------------------------------------------
+
+def roofline_of(recs, name, steps, t_res, traffic):
+    hbm, tf, which = peaks()
+    k_ms = sum(r[0] for r in recs)
+    if not recs or not k_ms:
+        return None
+    k_bytes, k_flops = sum(r[1] for r in recs), sum(r[2] for r in recs)
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    by_shape = {}
+    for r in recs:   # tag = ("fwd"|"bwd", window, shift, heads, H, W)
+        by_shape.setdefault(f"ws{r[3][1]}_nH{r[3][3]}_{r[3][4]}x{r[3][5]}", []).append(r)
+    return {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+            "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
+            "traffic": (traffic.get(name.split()[1]) or {}).get("dram_bytes_per_launch"),
+            "traffic_of": traffic.get(name.split()[1]),
+            "launches": len(recs), "kernel_ms_per_step": k_ms / steps, "share_of_step": k_ms / 1e3 / t_res,
+            "useful_tflops": k_flops / (k_ms * 1e-3) / 1e12,
+            "tensor_frac_of_sustained_bf16": k_flops / (k_ms * 1e-3) / 1e12 / tf,
+            "by_shape": {k: {"launches": len(v), "us_per_launch": sum(r[0] for r in v) / len(v) * 1e3,
+                             "frac": sum(r[1] for r in v) / (sum(r[0] for r in v) * 1e-3) / 1e9 / hbm}
+                         for k, v in sorted(by_shape.items())}}
+
+
+def roofline_linear_of(recs, steps, t_res):
+    hbm, tf, which = peaks()
+    if not recs:
+        return None
+    l_ms, l_bytes, l_flops = (sum(r[i] for r in recs) for i in range(3))
+    out = {"bound": "tensor", "kernel": "tc_linear_kernel (per-token Linears of the blocks as tcgen05 GEMMs with fused epilogues; "
+                                        "CTA pairs / cta_group::2 on the large-K shapes)",
+           "achieved": l_flops / (l_ms * 1e-3) / 1e12, "peak": tf, "unit": "TFLOP/s", "frac": l_flops / (l_ms * 1e-3) / 1e12 / tf,
+           "peak_source": f"{which} (MEASURED_PEAKS.json dense bf16)", "traffic": None,
+           "algorithmic_GBps": l_bytes / (l_ms * 1e-3) / 1e9, "hbm_frac": l_bytes / (l_ms * 1e-3) / 1e9 / hbm,
+           "launches": len(recs), "kernel_ms_per_step": l_ms / steps, "share_of_step": l_ms / 1e3 / t_res, "by_shape": {}}
+    shapes = {}
+    for r in recs:                                   # tag = ("lin", in_features, activation, out_features, rows, 0)
+        shapes.setdefault((r[3][4], r[3][1], r[3][3], r[3][2]), []).append(r)
+    for (rows, k, n, act), rs in sorted(shapes.items(), reverse=True):
+        ms = sum(r[0] for r in rs)
+        out["by_shape"][f"{rows}x{k}x{n}" + ("" if act == 1 else f"_epi{act}")] = {
+            "launches": len(rs), "us_per_launch": ms / len(rs) * 1e3, "TFLOPs": sum(r[2] for r in rs) / (ms * 1e-3) / 1e12,
+            "GBps": sum(r[1] for r in rs) / (ms * 1e-3) / 1e9}
+    return out
+
+
+def load_traffic():
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    return json.load(open(tpath)) if os.path.exists(tpath) else {}
+
+
+class Ctx:
+    """Per-process state shared by the legs."""
+
+    def __init__(self, args, env):
+        self.args, self.env = args, env
+        self.rank, self.world, self.local = env["rank"], env["world"], env["local_rank"]
+        self.dev = torch.device("cuda", self.local)
+        torch.cuda.set_device(self.dev)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)  # > 126 MB L2
+
+    def barrier(self):
+        if self.world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed_steps(step_fn, steps):
+    def timed_steps(self, step_fn, steps):
         """K steps, each bracketed by its own CUDA events with an L2 flush before it."""
         evs = []
         for _ in range(steps):
-            flush.zero_()
+            self.flush.zero_()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             step_fn()
@@ -167,69 +286,132 @@ def run_ours(args, env):
         torch.cuda.synchronize()
         return sum(a.elapsed_time(b) for a, b in evs) / 1e3
 
-    if train:
-        from mde_b200.harness import Trainer, synthetic_depth
-        model.train()
-        graph_step = not args.no_graph and (world == 1 or args.graph_ddp)
-        trainer = Trainer(model, ddp=world > 1, device_ids=[local] if world > 1 else None, capturable=graph_step)
-        gt_host = synthetic_depth(args.batch, height, width, max_depth, seed=100 + rank).pin_memory()
-        gt = gt_host.to(dev)
-        out_host = torch.empty(1).pin_memory()
+    def max_over_ranks(self, values):
+        t = torch.tensor([v or 0.0 for v in values], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.tolist()
 
-        def step_resident():
-            trainer.step(images, gt)
 
-        def step_e2e():
-            x, y = host.to(dev, non_blocking=True), gt_host.to(dev, non_blocking=True)
-            out_host.copy_(trainer.step(x, y).reshape(1), non_blocking=True)
-        h2d, d2h = host.numel() * 4 + gt_host.numel() * 4, 4
-    else:
-        prepare_inference(model)   # eval, no grads, GEMM / conv weights stored in bf16 (what autocast reads anyway)
-        out_host = torch.empty(args.batch, 1, height, width).pin_memory()
+def infer_leg(ctx):
+    """BASELINE configs[1].  Returns the pieces of the line (rank 0 uses them)."""
+    from mde_b200 import _lib, ops
+    from mde_b200.harness import GraphedInference, build_model, infer, infer_host_batches, prepare_inference, synthetic_images
+    args, dev = ctx.args, ctx.dev
+    model = build_model(args.version, MAX_DEPTH, seed=0, device=dev)
+    host = synthetic_images(args.batch, HEIGHT, WIDTH, seed=ctx.rank, pin=True)
+    images = host.to(dev)
+    prepare_inference(model)   # eval, no grads, GEMM / conv weights stored in bf16 (what autocast reads anyway)
+    out_host = torch.empty(args.batch, 1, HEIGHT, WIDTH).pin_memory()
+    out_hosts = [out_host, torch.empty_like(out_host).pin_memory()]
+    graphed = None if args.no_graph else GraphedInference(model, images)
 
-        def step_resident():
-            infer(model, images)
+    def step_resident():
+        infer(model, images)
 
-        out_hosts = [out_host, torch.empty_like(out_host).pin_memory()]
-        graphed = None if args.no_graph else GraphedInference(model, images)
-
-        def region_e2e(steps):
-            """K steps through the serving loop (harness.infer_host_batches): every step's images come from pinned host
-            memory and its depth map goes back to pinned host memory inside the timed region; the copies of neighbouring
-            steps overlap the compute on copy streams.  One event pair around the region, L2 flushed before each forward."""
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize()
-            a.record()
-            infer_host_batches(model, (host for _ in range(steps)), [out_hosts[i & 1] for i in range(steps)],
-                               before_step=flush.zero_, graphed=graphed)
-            b.record()
-            torch.cuda.synchronize()
-            return a.elapsed_time(b) / 1e3
-
-        def step_e2e():
-            region_e2e(1)
-        h2d, d2h = host.numel() * 4, out_host.numel() * 4
+    def region_e2e(steps, g):
+        """K steps through the serving loop (harness.infer_host_batches): every step's images come from pinned host
+        memory and its depth map goes back to pinned host memory inside the timed region; the copies of neighbouring
+        steps overlap the compute on copy streams.  One event pair around the region, L2 flushed before each forward."""
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        infer_host_batches(model, (host for _ in range(steps)), [out_hosts[i & 1] for i in range(steps)],
+                           before_step=ctx.flush.zero_, graphed=g)
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / 1e3
 
     for _ in range(args.warmup):
         step_resident()
-        step_e2e()
-    sampler = ClockSampler(local)
+        region_e2e(1, graphed)
+    sampler = ClockSampler(ctx.local)
     records = []
-    barrier()
+    ctx.barrier()
     if os.environ.get("BENCH_NO_CLOCK_SAMPLER") != "1":   # diagnosis only: the JSON line then carries no clock samples
         sampler.start()
     launches0 = _lib.launch_count()
     ops.set_kernel_timing(records)
-    t_res = timed_steps(step_resident, args.steps)
+    t_res = ctx.timed_steps(step_resident, args.steps)
     ops.set_kernel_timing(None)
     launches = _lib.launch_count() - launches0
-    barrier()
-    gstep = None
-    if train:
-        if graph_step:
-            # single-process training: the whole step (fwd + loss + bwd + clip + AdamW) replayed from a CUDA graph
-            # (harness.GraphedTrainStep); captured after the eager region, whose launches carry the roofline events
-            from mde_b200.harness import GraphedTrainStep
+    ctx.barrier()
+    # One event pair brackets the whole K-step serving region, so a single host hiccup (GC, the clock sampler taking
+    # the GIL, a page fault in a pinned buffer) while the ~100 ms region is being enqueued lands in the number in full.
+    # The region is therefore timed five times, each with exactly K steps and a synchronize on both sides, and the
+    # median is reported.
+    e2e_regions = sorted(region_e2e(args.steps, graphed) for _ in range(5))
+    t_e2e = e2e_regions[2]
+    t_e2e_eager = None
+    if graphed is not None:   # the same serving loop with the forward launched eagerly: comparable with `value`
+        t_e2e_eager = sorted(region_e2e(args.steps, None) for _ in range(3))[1]
+    t_graph = None
+    if graphed is not None:
+        ctx.barrier()
+        t_graph = ctx.timed_steps(lambda: graphed(images), args.steps)   # device-resident, the forward replayed as one graph
+    ctx.barrier()
+    sampler.stop()
+    t_res, t_e2e, t_graph, t_e2e_eager = ctx.max_over_ranks([t_res, t_e2e, t_graph, t_e2e_eager])
+    n_img = args.batch * ctx.world * args.steps
+    res = dict(t_res=t_res, t_e2e=t_e2e, t_graph=t_graph or None, t_e2e_eager=t_e2e_eager or None, records=records,
+               launches=int(launches), clocks=sampler.summary(), h2d=host.numel() * 4, d2h=out_host.numel() * 4,
+               e2e_regions=[n_img / t for t in e2e_regions], n_img=n_img)
+    del graphed, model, images
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
+
+
+def train_leg(ctx, steps, warmup):
+    """BASELINE configs[2]: fwd + SILog + bwd + clip + AdamW at 480x640, batch 8/GPU, stock DDP over NCCL at N > 1.
+    The eager step is timed first (its attention launches carry the roofline events), then the whole step -- with the
+    bucketed gradient all-reduce at N > 1 -- is captured as one CUDA graph (harness.GraphedTrainStep) and timed again."""
+    from mde_b200 import _lib, ops
+    from mde_b200.harness import GraphedTrainStep, Trainer, build_model, replicas_in_sync, synthetic_depth, synthetic_images
+    args, dev, world = ctx.args, ctx.dev, ctx.world
+    height, width, max_depth = 480, 640, 10.0
+    graph_step = not args.no_graph and (world == 1 or not args.no_graph_ddp)
+    if graph_step and world > 1:
+        # the DDP step is captured in a CUDA graph: torch's recipe wants the wrapper built, and the job stepped, on one
+        # non-default stream
+        torch.cuda.set_stream(torch.cuda.Stream(dev))
+    model = build_model(args.version, max_depth, seed=0, device=dev)
+    model.train()
+    host = synthetic_images(args.batch, height, width, seed=ctx.rank, pin=True)
+    images = host.to(dev)
+    trainer = Trainer(model, ddp=world > 1, device_ids=[ctx.local] if world > 1 else None, capturable=graph_step)
+    if args.bf16_grad_hook and world > 1:
+        from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+        trainer.model.register_comm_hook(None, default_hooks.bf16_compress_hook)
+    gt_host = synthetic_depth(args.batch, height, width, max_depth, seed=100 + ctx.rank).pin_memory()
+    gt = gt_host.to(dev)
+    out_host = torch.empty(1).pin_memory()
+
+    def step_resident():
+        trainer.step(images, gt)
+
+    def step_e2e_eager():
+        x, y = host.to(dev, non_blocking=True), gt_host.to(dev, non_blocking=True)
+        out_host.copy_(trainer.step(x, y).reshape(1), non_blocking=True)
+
+    for _ in range(warmup):
+        step_resident()
+        step_e2e_eager()
+    sampler = ClockSampler(ctx.local)
+    records = []
+    ctx.barrier()
+    if os.environ.get("BENCH_NO_CLOCK_SAMPLER") != "1":
+        sampler.start()
+    launches0 = _lib.launch_count()
+    ops.set_kernel_timing(records)
+    t_res = ctx.timed_steps(step_resident, steps)
+    ops.set_kernel_timing(None)
+    launches = _lib.launch_count() - launches0
+    ctx.barrier()
+    gstep, graph_error, in_sync, t_graph = None, None, None, None
+    step_e2e = step_e2e_eager
+    if graph_step:
+        try:
             gstep = GraphedTrainStep(trainer, images, gt, warmup=2)
 
             def step_e2e():   # noqa: F811  (the end-to-end step through the graph: H2D -> static inputs -> replay -> D2H)
@@ -237,129 +419,168 @@ def run_ours(args, env):
                 out_host.copy_(gstep(x, y).reshape(1), non_blocking=True)
             for _ in range(2):
                 step_e2e()
-        t_e2e = timed_steps(step_e2e, args.steps)
-    else:
-        # One event pair brackets the whole K-step serving region, so a single host hiccup (GC, the clock sampler taking
-        # the GIL, a page fault in a pinned buffer) while the ~100 ms region is being enqueued lands in the number in full
-        # (observed: 464 / 649 images/s on runs whose other regions gave 770-800; on a 2-GPU run regions of 1180 / 962 /
-        # 318 images/s beside 1540-1600 on the next four runs of the same command).  The region is therefore timed five
-        # times, each with exactly K steps and a synchronize on both sides, and the median is reported.
-        e2e_regions = sorted(region_e2e(args.steps) for _ in range(5))
-        t_e2e = e2e_regions[2]
-    t_graph = None
-    if not train and graphed is not None:
-        barrier()
-        t_graph = timed_steps(lambda: graphed(images), args.steps)   # device-resident, the forward replayed as one graph
-    in_sync = None
+        except Exception as e:   # keep the eager numbers; say why the replay is missing
+            gstep, graph_error, step_e2e = None, f"{type(e).__name__}: {e}"[:300], step_e2e_eager
+    t_e2e = ctx.timed_steps(step_e2e, steps)
     if gstep is not None:
-        t_graph = timed_steps(lambda: gstep(images, gt), args.steps)  # device-resident, the training step as one graph
+        t_graph = ctx.timed_steps(lambda: gstep(images, gt), steps)  # device-resident, the training step as one graph
         if world > 1:
             # every rank trains on its own images: the replicas stay identical only if the captured step really
             # all-reduces the gradients
-            from mde_b200.harness import replicas_in_sync
             in_sync = replicas_in_sync(model)
-    barrier()
-    sampler.stop_flag = True
-    if sampler.is_alive():
-        sampler.join(timeout=2)
+    ctx.barrier()
+    sampler.stop()
+    t_res, t_e2e, t_graph = ctx.max_over_ranks([t_res, t_e2e, t_graph])
+    res = dict(t_res=t_res, t_e2e=t_e2e, t_graph=t_graph or None, records=records, launches=int(launches),
+               clocks=sampler.summary(), h2d=host.numel() * 4 + gt_host.numel() * 4, d2h=4, in_sync=in_sync,
+               graph_error=graph_error, graphed=gstep is not None, n_img=args.batch * world * steps, steps=steps,
+               bf16_grad_hook=bool(args.bf16_grad_hook and world > 1))
+    del gstep, trainer, model
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
 
-    times = torch.tensor([t_res, t_e2e, t_graph or 0.0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    t_res, t_e2e, t_graph = times.tolist()
-    if rank != 0:
-        return
-    hbm, tf, which = peaks()
 
-    def roof(recs, name):
-        k_ms = sum(r[0] for r in recs)
-        if not recs or not k_ms:
-            return None
-        k_bytes, k_flops = sum(r[1] for r in recs), sum(r[2] for r in recs)
-        achieved = k_bytes / (k_ms * 1e-3) / 1e9
-        return {"bound": "hbm", "kernel": name, "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
-                "traffic": (traffic.get(name.split()[1]) or {}).get("dram_bytes_per_launch"),
-                "traffic_of": traffic.get(name.split()[1]),
-                "launches": len(recs), "kernel_ms_per_step": k_ms / args.steps, "share_of_step": k_ms / 1e3 / t_res,
-                "useful_tflops": k_flops / (k_ms * 1e-3) / 1e12,
-                "tensor_frac_of_sustained_bf16": k_flops / (k_ms * 1e-3) / 1e12 / tf}
-    traffic = {}
-    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-    if os.path.exists(tpath):
-        traffic = json.load(open(tpath))
-    fwd_recs = [r for r in records if r[3][0] == "fwd"]
-    bwd_recs = [r for r in records if r[3][0] == "bwd"]
-    roof_fwd = roof(fwd_recs, "swin_attn forward (all window-attention forward launches of the step)")
-    roof_bwd = roof(bwd_recs, "swin_attn backward (all window-attention backward launches of the step)")
-    n_img = args.batch * world * args.steps
-    if train:
-        metric = "NewCRFs Swin-L training images/sec @480x640 (bf16 autocast fwd + SILog + bwd + clip + AdamW, batch 8/GPU)"
-        workload = (f"NewCRFs {args.version} training step, batch {args.batch}/GPU, 3x480x640 NYU-shape synthetic images and "
-                    "depth, torch.autocast(bf16), random-init weights")
-        par = f"DDP x{world} (stock DistributedDataParallel, NCCL gradient all-reduce)" if world > 1 else "single GPU"
-    else:
-        metric = METRIC
-        workload = (f"NewCRFs {args.version} full-model inference, batch {args.batch}/GPU, 3x352x1216 "
-                    "KITTI-shape synthetic images, torch.autocast(bf16), random-init weights")
-        par = f"replicas x{world} (batch data-parallel, no data-path collective)"
-    line = {
-        "metric": metric, "value": n_img / t_res, "unit": "images/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": t_res / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": workload, "parallelism": par,
-                   "l2_flush_between_steps": True, "timing": "CUDA events per step, max over ranks",
-                   "e2e_timing": (("per step: H2D -> step -> D2H on one stream" + ("" if gstep is None else
-                                   "; the step is replayed from a CUDA graph (harness.GraphedTrainStep), while `value` is the eager "
-                                   "step so that the attention launches can be bracketed by CUDA events for the roofline"))
-                                  if train else
-                                  "median of 5 regions, each one event pair around K steps of harness.infer_host_batches (pinned host in / out, "
-                                  "copies of neighbouring steps overlapped on copy streams, L2 flush inside"
-                                  + (")" if args.no_graph else "; the forward is replayed from a CUDA graph, "
-                                     "harness.GraphedInference, while `value` is the eager forward so that the attention "
-                                     "launches can be bracketed by CUDA events for the roofline)"))},
-        "e2e": {"value": n_img / t_e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                **({} if train else {"regions_images_per_s": [n_img / t for t in e2e_regions]})},
-        "gpu_launches": int(launches),
-        "clocks": sampler.summary(),
-        "roofline": roof_bwd if train else roof_fwd,
+def train_summary(ctx, tr):
+    """The `train` extra key of the default line (and the body of the --mode train line)."""
+    world, traffic = ctx.world, load_traffic()
+    bwd = [r for r in tr["records"] if r[3][0] == "bwd"]
+    fwd = [r for r in tr["records"] if r[3][0] == "fwd"]
+    best = tr["t_graph"] or tr["t_res"]
+    return {
+        "metric": TRAIN_METRIC, "unit": "images/s", "steps": tr["steps"],
+        "value": tr["n_img"] / best, "ms_per_step": best / tr["steps"] * 1e3,
+        "value_is": "CUDA-graph replay of the whole step" if tr["t_graph"] else "eager step",
+        "eager": {"value": tr["n_img"] / tr["t_res"], "ms_per_step": tr["t_res"] / tr["steps"] * 1e3},
+        "e2e": {"value": tr["n_img"] / tr["t_e2e"], "unit": "images/s", "h2d_bytes_per_step": tr["h2d"],
+                "d2h_bytes_per_step": tr["d2h"]},
+        "graph_replay": tr["graphed"], "graph_error": tr["graph_error"], "ddp_replicas_in_sync": tr["in_sync"],
+        "bf16_grad_hook": tr["bf16_grad_hook"],
+        "parallelism": (f"DDP x{world} (stock DistributedDataParallel, bucketed NCCL gradient all-reduce"
+                        + (", captured in the step's CUDA graph)" if tr["graphed"] else ", eager)")) if world > 1 else "single GPU",
+        "workload": f"NewCRFs {ctx.args.version} training step, batch {ctx.args.batch}/GPU, 3x480x640 NYU-shape synthetic images "
+                    "and depth, torch.autocast(bf16), random-init weights",
+        "gpu_launches": tr["launches"], "clocks": tr["clocks"],
+        "roofline_backward": roofline_of(bwd, "swin_attn backward (all window-attention backward launches of the step)",
+                                         tr["steps"], tr["t_res"], traffic),
+        "roofline_forward": roofline_of(fwd, "swin_attn forward (all window-attention forward launches of the step)",
+                                        tr["steps"], tr["t_res"], traffic),
     }
-    lin_recs = [r for r in records if r[3][0] == "lin"]
-    if lin_recs:
-        l_ms, l_bytes, l_flops = (sum(r[i] for r in lin_recs) for i in range(3))
-        line["roofline_linear"] = {
-            "bound": "tensor", "kernel": "tc_linear_kernel (fc1 + bias + GELU of every block MLP, tcgen05 GEMM with fused epilogue; CTA pairs / cta_group::2 from K = 192 up)",
-            "achieved": l_flops / (l_ms * 1e-3) / 1e12, "peak": tf, "unit": "TFLOP/s", "frac": l_flops / (l_ms * 1e-3) / 1e12 / tf,
-            "peak_source": f"{which} (MEASURED_PEAKS.json dense bf16)", "traffic": None,
-            "algorithmic_GBps": l_bytes / (l_ms * 1e-3) / 1e9, "hbm_frac": l_bytes / (l_ms * 1e-3) / 1e9 / hbm,
-            "launches": len(lin_recs), "kernel_ms_per_step": l_ms / args.steps, "share_of_step": l_ms / 1e3 / t_res,
-            "by_shape": {}}
-        shapes = {}
-        for r in lin_recs:                                   # tag = ("lin", in_features, activation, out_features, rows, 0)
-            shapes.setdefault((r[3][4], r[3][1], r[3][3]), []).append(r)
-        for (rows, k, n), rs in sorted(shapes.items(), reverse=True):
-            ms = sum(r[0] for r in rs)
-            line["roofline_linear"]["by_shape"][f"{rows}x{k}x{n}"] = {
-                "launches": len(rs), "us_per_launch": ms / len(rs) * 1e3, "TFLOPs": sum(r[2] for r in rs) / (ms * 1e-3) / 1e12,
-                "GBps": sum(r[1] for r in rs) / (ms * 1e-3) / 1e9}
-    if t_graph:
-        line["graph_replay"] = {"value": n_img / t_graph, "unit": "images/s", "ms_per_step": t_graph / args.steps * 1e3,
-                                "note": ("device-resident like `value`, the whole training step replayed from a CUDA graph "
-                                         "(harness.GraphedTrainStep)" if train else
-                                         "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)")}
-    if train:
-        line["roofline_forward"] = roof_fwd
-        if in_sync is not None:
-            line["graph_replay"]["ddp_replicas_in_sync"] = in_sync
-    if world == 1 and not args.no_cpu_baseline and not train:
-        cores = os.cpu_count() or 1
-        torch.set_num_threads(cores)
-        cm, img = cpu_model_and_sample(args.version)
-        ips, _ = time_cpu(cm, img, 1, 1)
-        line["cpu_baseline"] = {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
-                                "sample": "1 image of the batch-8 workload, 1 warm-up + 1 timed forward, fp32 torch CPU "
-                                          "(oracle restatement of the reference model)"}
-    emit(line)
+
+
+def run_ours(args, env):
+    ctx = Ctx(args, env)
+    traffic = load_traffic()
+    if args.mode == "train":
+        tr = train_leg(ctx, args.steps, args.warmup)
+        if ctx.rank != 0:
+            return
+        s = train_summary(ctx, tr)
+        line = {
+            "metric": TRAIN_METRIC, "value": tr["n_img"] / tr["t_res"], "unit": "images/s", "n_gpus": ctx.world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": tr["t_res"] / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": s["workload"], "parallelism": s["parallelism"], "l2_flush_between_steps": True,
+                       "timing": "CUDA events per step, max over ranks",
+                       "e2e_timing": "per step: H2D -> step -> D2H on one stream" + (
+                           "; the step is replayed from a CUDA graph (harness.GraphedTrainStep), while `value` is the eager "
+                           "step so that the attention launches can be bracketed by CUDA events for the roofline"
+                           if tr["graphed"] else "")},
+            "e2e": s["e2e"], "gpu_launches": tr["launches"], "clocks": tr["clocks"], "roofline": s["roofline_backward"],
+            "roofline_forward": s["roofline_forward"],
+        }
+        lin = roofline_linear_of([r for r in tr["records"] if r[3][0] == "lin"], args.steps, tr["t_res"])
+        if lin:
+            line["roofline_linear"] = lin
+        if tr["t_graph"]:
+            line["graph_replay"] = {"value": tr["n_img"] / tr["t_graph"], "unit": "images/s",
+                                    "ms_per_step": tr["t_graph"] / args.steps * 1e3,
+                                    "note": "device-resident like `value`, the whole training step replayed from a CUDA graph "
+                                            "(harness.GraphedTrainStep)", "ddp_replicas_in_sync": tr["in_sync"]}
+        if tr["graph_error"]:
+            line["graph_error"] = tr["graph_error"]
+        emit(line)
+        return
+
+    inf = infer_leg(ctx)
+    line = None
+    if ctx.rank == 0:
+        fwd_recs = [r for r in inf["records"] if r[3][0] == "fwd"]
+        n_img, t_res = inf["n_img"], inf["t_res"]
+        line = {
+            "metric": METRIC, "value": n_img / t_res, "unit": "images/s", "n_gpus": ctx.world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t_res / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": (f"NewCRFs {args.version} full-model inference, batch {args.batch}/GPU, 3x352x1216 "
+                                    "KITTI-shape synthetic images, torch.autocast(bf16), random-init weights"),
+                       "parallelism": f"replicas x{ctx.world} (batch data-parallel, no data-path collective)",
+                       "l2_flush_between_steps": True, "timing": "CUDA events per step, max over ranks",
+                       "e2e_timing": "median of 5 regions, each one event pair around K steps of harness.infer_host_batches (pinned "
+                                     "host in / out, copies of neighbouring steps overlapped on copy streams, L2 flush inside"
+                                     + (")" if args.no_graph else "; the forward is replayed from a CUDA graph, "
+                                        "harness.GraphedInference, while `value` is the eager forward so that the attention "
+                                        "launches can be bracketed by CUDA events for the roofline; `e2e_eager` is the same loop "
+                                        "with eager launches)")},
+            "e2e": {"value": n_img / inf["t_e2e"], "unit": "images/s", "h2d_bytes_per_step": inf["h2d"],
+                    "d2h_bytes_per_step": inf["d2h"], "regions_images_per_s": inf["e2e_regions"]},
+            "gpu_launches": inf["launches"], "clocks": inf["clocks"],
+            "roofline": roofline_of(fwd_recs, "swin_attn forward (all window-attention forward launches of the step)",
+                                    args.steps, t_res, traffic),
+        }
+        if inf["t_e2e_eager"]:
+            line["e2e_eager"] = {"value": n_img / inf["t_e2e_eager"], "unit": "images/s",
+                                 "note": "the e2e serving loop with the forward launched eagerly (median of 3 regions)"}
+        lin = roofline_linear_of([r for r in inf["records"] if r[3][0] == "lin"], args.steps, t_res)
+        if lin:
+            line["roofline_linear"] = lin
+        if inf["t_graph"]:
+            line["graph_replay"] = {"value": n_img / inf["t_graph"], "unit": "images/s",
+                                    "ms_per_step": inf["t_graph"] / args.steps * 1e3,
+                                    "note": "device-resident like `value`, forward replayed from a CUDA graph (harness.GraphedInference)"}
+    inf = None
+
+    # From here on nothing may cost the line: every extra leg is guarded, and a watchdog emits what there is if the
+    # training leg (NCCL collectives captured in a CUDA graph at N > 1) should ever hang.
+    emitted = threading.Event()
+
+    def emit_once():
+        if not emitted.is_set():
+            emitted.set()
+            if ctx.rank == 0:
+                emit(line)
+
+    def watchdog():
+        if ctx.rank == 0 and line is not None:
+            line.setdefault("train", {"error": f"training leg did not finish within {TRAIN_LEG_TIMEOUT_S:.0f} s"})
+        emit_once()
+        os._exit(0)
+
+    if ctx.world == 1 and not args.no_reference_gpu:
+        try:
+            line["reference_gpu_eager"] = reference_gpu_eager(args, ctx.dev, ctx.flush)
+        except Exception as e:
+            line["reference_gpu_eager"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    if not args.no_train_leg:
+        timer = threading.Timer(TRAIN_LEG_TIMEOUT_S, watchdog)
+        timer.daemon = True
+        timer.start()
+        try:
+            tr = train_leg(ctx, args.steps, max(args.warmup, 3))
+            if ctx.rank == 0:
+                line["train"] = train_summary(ctx, tr)
+        except Exception as e:
+            if ctx.rank == 0:
+                line["train"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+            timer.cancel()
+            emit_once()
+            os._exit(0)   # the process group may be wedged after a failed collective: leave without the NCCL teardown
+        timer.cancel()
+    if ctx.rank == 0 and ctx.world == 1 and not args.no_cpu_baseline:
+        try:
+            line["cpu_baseline"] = cpu_reference(args.version, 5, 2, os.cpu_count() or 1)
+        except Exception as e:
+            line["cpu_baseline"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    emit_once()
 
 
 def emit(line):
@@ -377,17 +598,17 @@ def main():
     sys.stdout.flush()
     _STDOUT = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
-    from mde_b200.harness import dist_env, init_distributed
     env = dist_env()
     if args.impl == "reference":
         run_reference(args, env["rank"])
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
-    if args.mode == "train" and args.graph_ddp and not args.no_graph:
+    if env["world"] > 1 and not args.no_graph and not args.no_graph_ddp:
         # precondition of capturing NCCL collectives in a CUDA graph (torch's DDP + whole-network-capture recipe)
         # (torchrun exports TORCH_NCCL_ASYNC_ERROR_HANDLING=1 to its workers: override, not setdefault)
         os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"
+    from mde_b200.harness import init_distributed
     env = init_distributed("nccl")
     run_ours(args, env)
     if env["world"] > 1:

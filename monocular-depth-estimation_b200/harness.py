@@ -278,6 +278,10 @@ class GraphedTrainStep:
             warmup = max(warmup, 11)
         if not trainer.opt.defaults.get("capturable", False):
             raise ValueError("build the Trainer with capturable=True (device-side AdamW step counter)")
+        if any(getattr(getattr(m, "attn_drop", None), "p", 0.0) > 0.0 for m in trainer.raw.modules()):
+            # the attention-dropout seed is a host scalar drawn per call (ops.window_attention): a captured graph would
+            # replay ONE mask for ever
+            raise ValueError("GraphedTrainStep does not support attn_drop > 0 (the dropout seed would be baked into the graph)")
         self.trainer = trainer
         self.static_images, self.static_gt = images.detach().clone(), gt.detach().clone()
         side = torch.cuda.Stream(images.device)

@@ -104,7 +104,7 @@ def _relative_position_index(wh: int, ww: int) -> torch.Tensor:
 class _WindowAttentionBase(nn.Module):
     """Parameters and buffers shared by both reference flavours."""
 
-    def __init__(self, dim, window_size, num_heads, out_dim, qk_scale, attn_drop, proj_drop):
+    def __init__(self, dim, window_size, num_heads, out_dim, qk_scale, attn_drop, proj_drop, in_proj, qkv_bias):
         super().__init__()
         self.dim = dim
         self.window_size = _pair(window_size)
@@ -118,6 +118,10 @@ class _WindowAttentionBase(nn.Module):
         wh, ww = self.window_size
         self.relative_position_bias_table = nn.Parameter(torch.zeros((2 * wh - 1) * (2 * ww - 1), num_heads))
         self.register_buffer("relative_position_index", _relative_position_index(wh, ww))
+        # registered in the reference's order (table, qk | qkv, proj: newcrf_layers.py:86-105, swin_transformer.py:88-107)
+        # so that model.parameters() -- and with it an index-keyed optimizer state_dict -- lines up with the reference's
+        name, factor = in_proj
+        setattr(self, name, nn.Linear(dim, dim * factor, bias=qkv_bias))
         # applied to the softmax output inside the kernel while training (0 in every NewCRFs configuration)
         self.attn_drop = nn.Dropout(attn_drop)
         self.proj = nn.Linear(out_dim, out_dim)
@@ -144,8 +148,7 @@ class WindowAttention(_WindowAttentionBase):
     """NeWCRF decoder attention: q, k from ``x``; ``v`` external (newcrf_layers.py:62-149)."""
 
     def __init__(self, dim, window_size, num_heads, v_dim, qkv_bias=True, qk_scale=None, attn_drop=0., proj_drop=0.):
-        super().__init__(dim, window_size, num_heads, v_dim, qk_scale, attn_drop, proj_drop)
-        self.qk = nn.Linear(dim, dim * 2, bias=qkv_bias)
+        super().__init__(dim, window_size, num_heads, v_dim, qk_scale, attn_drop, proj_drop, ("qk", 2), qkv_bias)
 
     def forward(self, x, v, mask=None):
         """x, v: (num_windows*B, N, C) window-order tokens; mask: (nW, N, N) or None."""
@@ -186,8 +189,7 @@ class EncoderWindowAttention(_WindowAttentionBase):
     """Swin encoder attention with fused qkv (swin_transformer.py:64-144)."""
 
     def __init__(self, dim, window_size, num_heads, qkv_bias=True, qk_scale=None, attn_drop=0., proj_drop=0.):
-        super().__init__(dim, window_size, num_heads, dim, qk_scale, attn_drop, proj_drop)
-        self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
+        super().__init__(dim, window_size, num_heads, dim, qk_scale, attn_drop, proj_drop, ("qkv", 3), qkv_bias)
 
     def forward(self, x, mask=None):
         b_, n, c = x.shape
@@ -299,6 +301,14 @@ class BasicCRFLayer(nn.Module):
         pending = scale = None
         for blk in self.blocks:
             blk.H, blk.W = H, W
+            if self.use_checkpoint and torch.is_grad_enabled():
+                # The reference's branch (newcrf_layers.py:353-355) calls ``checkpoint(blk, x, attn_mask)`` without ``v``
+                # and raises a TypeError; NewCRF hard-codes use_checkpoint=False (:404), so it never runs there.  Here
+                # the flag does what it says: the block is recomputed in the backward (same outputs and gradients).
+                if pending is not None:
+                    x, pending = ops.residual(x, pending, scale), None
+                x = torch.utils.checkpoint.checkpoint(blk, x, v, None, use_reentrant=False)
+                continue
             if pending is None:
                 y = ops.norm_for_linear(blk.norm1, x)
             else:

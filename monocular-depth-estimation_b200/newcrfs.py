@@ -79,12 +79,40 @@ class SwinTransformer(nn.Module):
                 nn.init.ones_(m.weight)
         self.apply(init)
         if isinstance(pretrained, str):
-            state = torch.load(pretrained, map_location="cpu")
-            state = state.get("state_dict", state.get("model", state))
-            state = {k[7:] if k.startswith("module.") else k: v for k, v in state.items()}
-            self.load_state_dict(state, strict=False)
+            self.load_pretrained_state(torch.load(pretrained, map_location="cpu"))
         elif pretrained is not None:
             raise TypeError("pretrained must be a str or None")
+
+    def load_pretrained_state(self, checkpoint):
+        """What the reference's ``load_checkpoint(self, pretrained, strict=False)`` does with a checkpoint dict
+        (newcrf_utils.py:194-263): unwrap ``state_dict`` / ``model``, strip a ``module.`` prefix, keep the online
+        (``encoder.``) branch of a MoBY checkpoint, resize every ``relative_position_bias_table`` whose window size
+        differs from this model's by bicubic interpolation (a window-7 checkpoint into a window-12 model; tables whose
+        head count differs are skipped, as there), then load non-strictly.  Returns the (missing, unexpected) keys."""
+        if not isinstance(checkpoint, dict):
+            raise RuntimeError("No state_dict found in checkpoint")
+        state = checkpoint.get("state_dict", checkpoint.get("model", checkpoint))
+        if state and next(iter(state)).startswith("module."):
+            state = {k[7:]: v for k, v in state.items()}
+        if state and sorted(state)[0].startswith("encoder"):
+            state = {k.replace("encoder.", ""): v for k, v in state.items() if k.startswith("encoder.")}
+        state = dict(state)
+        state.pop("absolute_pos_embed", None)            # ape=False in every NewCRFs configuration
+        own = self.state_dict()
+        for key in [k for k in state if "relative_position_bias_table" in k]:
+            if key not in own:
+                continue
+            (l1, nh1), (l2, nh2) = state[key].shape, own[key].shape
+            if nh1 != nh2:
+                del state[key]                           # the reference logs "Error in loading ..., pass"
+            elif l1 != l2:
+                s1, s2 = int(l1 ** 0.5), int(l2 ** 0.5)
+                resized = F.interpolate(state[key].float().permute(1, 0).reshape(1, nh1, s1, s1), size=(s2, s2), mode="bicubic")
+                state[key] = resized.reshape(nh2, l2).permute(1, 0)
+        # relative_position_index depends on the window size only; a checkpoint of another window size carries a stale one
+        for key in [k for k in state if k.endswith("relative_position_index") and k in own and state[k].shape != own[k].shape]:
+            del state[key]
+        return self.load_state_dict(state, strict=False)
 
     def forward(self, x):
         x = self.patch_embed(x)

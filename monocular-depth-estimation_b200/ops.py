@@ -231,7 +231,12 @@ def window_attention(packed: Tensor, v: Optional[Tensor], bias_table: Tensor, wi
         packed.requires_grad or bias_table.requires_grad or (v is not None and v.requires_grad)
         or (packed_pad is not None and packed_pad.requires_grad) or (v_pad is not None and v_pad.requires_grad))
     if dropout_p > 0.0 and seed is None:
-        seed = int(torch.randint(0, 2 ** 62, (1,)).item())   # CPU generator: reproducible under torch.manual_seed, no sync
+        # CPU generator: reproducible under torch.manual_seed, no device sync.  The rank is folded in so that identically
+        # seeded data-parallel replicas do not share one mask.  The seed is a host scalar: a CUDA graph would bake it in
+        # (harness.GraphedTrainStep refuses models with attn_drop > 0 for that reason).
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            seed = (seed + 0x9E3779B97F4A7C15 * (torch.distributed.get_rank() + 1)) % (2 ** 63)
     o, _ = torch.ops.swin_attn.fwd(packed, v, bias_table, packed_pad, v_pad, window, shift, num_heads,
                                    float(scale), need_grad, impl, attn_mask, float(dropout_p), int(seed or 0))
     return o

@@ -18,7 +18,7 @@ import numpy as np
 import torch
 
 from . import reference_shim as rs
-from .synthetic import depth_errors, randn, synthetic_depth_gt, synthetic_state
+from .synthetic import depth_errors, randn, silog_loss, synthetic_depth_gt, synthetic_state
 from .window_attention import shift_mask
 
 OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
@@ -106,6 +106,58 @@ def full_model(name, version, b, h, w, max_depth=80.0):
                 abs_rel=float(ref_err["abs_rel"]), rmse=float(ref_err["rmse"]))
 
 
+def _metrics(depth, gt, max_depth):
+    """AbsRel / RMSE through the reference's own utils/depth_utils.py:32-54 (and the restatement agrees)."""
+    tcompute_errors = rs.module("utils.depth_utils").tcompute_errors
+    valid = (gt > 1e-3).numpy()
+    pred = depth.clamp(1e-3, max_depth).numpy()
+    ref_err = tcompute_errors(gt.numpy()[valid], pred[valid])
+    mine = depth_errors(gt.numpy()[valid], pred[valid])
+    assert abs(mine["abs_rel"] - ref_err["abs_rel"]) < 1e-12 and abs(mine["rmse"] - ref_err["rmse"]) < 1e-12
+    return float(ref_err["abs_rel"]), float(ref_err["rmse"])
+
+
+def full_model_v2(name, version, b, h, w, max_depth=80.0, keep_depth=True):
+    """The benchmarked configuration itself: reference NewCRFDepth(version) on one synthetic image at the BASELINE shape;
+    depth map + AbsRel / RMSE on the ill-conditioned GT (uniform(1e-3, max)) and on the realistic one (uniform(1, max))."""
+    D = rs.newcrf_depth()
+    m = D.NewCRFDepth(version=version, max_depth=max_depth).eval()
+    m.load_state_dict(synthetic_state(m))
+    img = randn(name + ".img", b, 3, h, w)
+    with torch.no_grad():
+        depth = m(img)
+    out = dict(kind="full_model_v2", cfg=dict(version=version, b=b, h=h, w=w, max_depth=max_depth))
+    for tag, lo in (("", 1e-3), ("_realgt", 1.0)):
+        gt = synthetic_depth_gt(name + ".gt", b, h, w, max_depth, min_depth=lo)
+        out["abs_rel" + tag], out["rmse" + tag] = _metrics(depth, gt, max_depth)
+    if keep_depth:
+        out["depth"] = depth
+    return out
+
+
+def full_model_grads(name, version, b, h, w, max_depth=10.0):
+    """A training-shape gradient fixture: reference NewCRFDepth(version) in eval mode (DropPath off, BatchNorm on its
+    running statistics: the deterministic half of SURVEY 8c "training parity"), SILog loss on a synthetic GT, backward.
+    Kept: the loss, the FULL gradient of every relative_position_bias_table and of every qkv / qk bias (the parameters
+    the fused attention path differentiates itself), and fp64 sum / L2 norm of every other parameter's gradient."""
+    D = rs.newcrf_depth()
+    m = D.NewCRFDepth(version=version, max_depth=max_depth).eval()
+    m.load_state_dict(synthetic_state(m))
+    img = randn(name + ".img", b, 3, h, w)
+    gt = synthetic_depth_gt(name + ".gt", b, h, w, max_depth, sparsity=0.3, min_depth=0.5)
+    depth = m(img)
+    loss = silog_loss(depth, gt)
+    loss.backward()
+    full, sums = {}, {}
+    for k, p in m.named_parameters():
+        g = p.grad
+        if k.endswith("relative_position_bias_table") or k.endswith("qkv.bias") or k.endswith("qk.bias"):
+            full[k] = g.detach().clone()
+        sums[k] = (float(g.double().sum()), float(g.double().norm()))
+    return dict(kind="full_model_grads", cfg=dict(version=version, b=b, h=h, w=w, max_depth=max_depth), loss=float(loss),
+                depth_mean=float(depth.mean()), grads=full, grad_sums=sums)
+
+
 CASES = {
     "crf_block_ws7_s0": lambda n: crf_block(n, 7, 0, 2, 9, 11, 64, 2),
     "crf_block_ws7_s3": lambda n: crf_block(n, 7, 3, 2, 9, 11, 64, 2),
@@ -117,13 +169,22 @@ CASES = {
     "masked_windows_ws7": lambda n: masked_windows(n, 7, 4, 2, 64, 2),
     "newcrf_level": lambda n: newcrf_level(n, 1, 10, 13, 48, 64, 32, 2),
     "newcrfdepth_tiny07": lambda n: full_model(n, "tiny07", 1, 64, 96),
+    # metrics only (same image / weights as newcrfdepth_tiny07; adds the realistic-range GT)
+    "newcrfdepth_tiny07_metrics": lambda n: full_model_v2("newcrfdepth_tiny07", "tiny07", 1, 64, 96, keep_depth=False),
+    # BASELINE configs[1]: the benchmarked model at the benchmarked shape, one image
+    "newcrfdepth_large07_kitti": lambda n: full_model_v2(n, "large07", 1, 352, 1216),
+    # BASELINE configs[2]: the training shape, loss.backward() through the reference
+    "newcrfdepth_large07_nyu_grads": lambda n: full_model_grads(n, "large07", 1, 480, 640),
 }
 
 
 def main():
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
+    only = sys.argv[1:]
     for name, fn in CASES.items():
+        if only and name not in only:
+            continue
         blob = fn(name)
         blob = {k: (v.to(torch.float32).contiguous() if torch.is_tensor(v) else v) for k, v in blob.items()}
         path = os.path.join(OUT, name + ".pt")

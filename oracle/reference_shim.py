@@ -1,9 +1,11 @@
-"""Import the reference repository (``/root/reference``) in the build container.
+"""Import the UNMODIFIED reference modules: from ``oracle/_ref`` (the copy staged by
+``oracle/stage_reference.py`` during ``__graft_entry__.build()``; it travels to the GPU box)
+or, in the build container, straight from ``/root/reference``.
 
-TEST INFRASTRUCTURE ONLY.  ``/root/reference`` does not exist on the GPU box,
-so nothing that runs there may import this module; it is used by
-``oracle/make_golden.py`` (fixture generation) and by CPU tests that skip when
-the reference is absent.
+TEST INFRASTRUCTURE ONLY.  Used by ``oracle/make_golden.py`` (fixture generation), by the
+reference arm / ``cpu_baseline`` / ``reference_gpu_eager`` legs of ``bench.py`` and by the
+tests that compare the product with the reference's own code; every user checks
+``available()`` first.  ``/root/reference`` itself is never read on the GPU box.
 
 The reference needs two packages that are not installed:
 ``timm`` (pin 0.5.4: ``DropPath``, ``to_2tuple``, ``trunc_normal_``) and
@@ -19,11 +21,29 @@ import types
 import torch
 import torch.nn as nn
 
-REFERENCE_ROOT = os.environ.get("MDE_REFERENCE_ROOT", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def _find_root() -> str:
+    env = os.environ.get("MDE_REFERENCE_ROOT")
+    if env:
+        return env
+    for root in (_STAGED, "/root/reference"):
+        if os.path.isfile(os.path.join(root, "model", "NewCRFs", "NewCRFDepth.py")):
+            return root
+    return _STAGED
+
+
+REFERENCE_ROOT = _find_root()
 
 
 def available() -> bool:
-    return os.path.isdir(os.path.join(REFERENCE_ROOT, "model", "NewCRFs"))
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "model", "NewCRFs", "NewCRFDepth.py"))
+
+
+def source() -> str:
+    """Where the reference modules come from: "oracle/_ref" (staged copy) or the upstream path."""
+    return "oracle/_ref" if os.path.abspath(REFERENCE_ROOT) == os.path.abspath(_STAGED) else REFERENCE_ROOT
 
 
 class _DropPath(nn.Module):
@@ -116,3 +136,11 @@ def newcrf_depth():
     install()
     import importlib
     return importlib.import_module("model.NewCRFs.NewCRFDepth")
+
+
+def module(name: str):
+    """Any other reference module by dotted name, e.g. ``model.ODA2.oda2_swin_transformer``,
+    ``model.Depthformer.self_attention``, ``utils.depth_utils``."""
+    install()
+    import importlib
+    return importlib.import_module(name)

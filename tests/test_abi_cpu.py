@@ -209,3 +209,31 @@ def test_torch_binding_registers_ops_without_a_gpu():
     assert h.shape == g.shape == (3, 50, 256) and h.dtype == bf
     with pytest.raises(NotImplementedError):
         torch.ops.swin_attn.patch_merge_norm(torch.zeros(1, 4, 192), 2, 2, torch.ones(768), torch.zeros(768), 1e-5)
+
+
+def test_swin_checkpoint_loading_follows_the_reference_loader():
+    """SwinTransformer.load_pretrained_state == newcrf_utils.load_checkpoint (:194-263): `module.` prefix, MoBY `encoder.`
+    branch, bicubic resize of a window-7 relative_position_bias_table into a window-12 model."""
+    import torch
+    import torch.nn.functional as F
+    from mde_b200.newcrfs import SwinTransformer
+    kw = dict(embed_dim=96, depths=(2, 2), num_heads=(3, 6), out_indices=(0, 1))
+    src = SwinTransformer(window_size=7, **kw)
+    with torch.no_grad():
+        for p in src.parameters():
+            p.normal_(0, 0.5)
+    dst = SwinTransformer(window_size=12, **kw)
+    ckpt = {"model": {"module." + k: v for k, v in src.state_dict().items()}}
+    missing, unexpected = dst.load_pretrained_state(ckpt)
+    assert not unexpected and all(k.endswith("relative_position_index") for k in missing)
+    key = "layers.1.blocks.0.attn.relative_position_bias_table"
+    want = F.interpolate(src.state_dict()[key].permute(1, 0).reshape(1, 6, 13, 13), size=(23, 23), mode="bicubic")
+    assert torch.equal(dst.state_dict()[key], want.reshape(6, 529).permute(1, 0))
+    assert torch.equal(dst.state_dict()["layers.0.blocks.1.attn.qkv.weight"], src.state_dict()["layers.0.blocks.1.attn.qkv.weight"])
+    assert dst.state_dict()["layers.0.blocks.0.attn.relative_position_index"].shape == (144, 144)
+    moby = {"encoder." + k: v for k, v in src.state_dict().items()}
+    moby.update({"encoder_k." + k: torch.zeros_like(v) for k, v in src.state_dict().items()})
+    same = SwinTransformer(window_size=7, **kw)
+    missing, unexpected = same.load_pretrained_state({"state_dict": moby})
+    assert not missing and not unexpected
+    assert all(torch.equal(a, b) for a, b in zip(same.state_dict().values(), src.state_dict().values()))
