@@ -219,10 +219,10 @@ def test_newcrf_level_vs_reference_golden(golden):
     m = m.to(DEV).eval()
     x, v = g["x"].to(DEV).requires_grad_(), g["v"].to(DEV).requires_grad_()
     out = m(x, v)
-    check(rel_err(out, g["out"]), 2e-5, "NewCRF level fp32 out (two stacked blocks + cuDNN convs)")
+    check(rel_err(out, g["out"]), TOL_F32, "NewCRF level fp32 out (two stacked blocks + cuDNN convs; measured 6.0e-7)")
     gs = torch.autograd.grad((out * g["cot"].to(DEV)).sum(), [x, v, m.crf_layer.blocks[1].attn.relative_position_bias_table])
     for got, key in zip(gs, ["dx", "dv", "dtable1"]):
-        check(rel_err(got, g[key]), 5e-5, f"NewCRF level fp32 {key}")
+        check(rel_err(got, g[key]), TOL_F32, f"NewCRF level fp32 {key} (measured <= 8.3e-7)")
 
 
 @pytest.mark.parametrize("mode", ["fp32", "bf16"])
@@ -251,7 +251,7 @@ def test_full_model_depth_metrics_vs_reference_golden(golden, mode):
         depth = m(img).float().cpu()
     err = metrics(depth)
     if mode == "fp32":
-        check(rel_err(depth, g["depth"]), 1e-4, "tiny07 full model fp32 depth (12 + 8 blocks and cuDNN/cuBLAS fp32 reductions)")
+        check(rel_err(depth, g["depth"]), TOL_F32, "tiny07 full model fp32 depth (12 + 8 blocks; measured 5.1e-7)")
         assert abs(err["abs_rel"] - g["abs_rel"]) < 1e-3 and abs(err["rmse"] - g["rmse"]) < 1e-3
         return
     ref = to_oracle(m, DEV).eval()
@@ -263,14 +263,16 @@ def test_full_model_depth_metrics_vs_reference_golden(golden, mode):
     print(f"bf16 full model: ours-vs-fp32 {ours_vs_fp32:.3e}, reference-bf16-vs-fp32 {ref_vs_fp32:.3e}, "
           f"ours-vs-reference-bf16 {ours_vs_ref:.3e}; abs_rel {err['abs_rel']:.5f}/{eref['abs_rel']:.5f}/{g['abs_rel']:.5f} "
           f"rmse {err['rmse']:.4f}/{eref['rmse']:.4f}/{g['rmse']:.4f}")
-    assert ours_vs_fp32 < 1.5 * ref_vs_fp32 + 1e-2
-    # random weights vs random GT make abs_rel O(7): the 1e-3 budget is applied relative to the metric.  abs_rel
-    # divides by gt, which reaches 1e-3 in the synthetic batch, so a handful of pixels carry the mean and bf16
-    # rounding noise does not average out: measured 2.6e-4 (reference-bf16) to 1.4e-3 (ours, whose activations
-    # are CLOSER to the fp32 golden than reference-bf16's) depending on the rounding pattern -> 2.5e-3 here,
-    # 1e-3 for the well-conditioned rmse.
-    assert abs(err["abs_rel"] - g["abs_rel"]) / g["abs_rel"] < 1.5 * abs(eref["abs_rel"] - g["abs_rel"]) / g["abs_rel"] + 2.5e-3
-    assert abs(err["rmse"] - g["rmse"]) / g["rmse"] < 1.5 * abs(eref["rmse"] - g["rmse"]) / g["rmse"] + 1e-3
+    check(ours_vs_fp32, TOL_BF16, f"tiny07 full model bf16 depth vs reference fp32 (oracle port under autocast: {ref_vs_fp32:.3e})")
+    assert ours_vs_fp32 < 1.5 * ref_vs_fp32 + 1e-3
+    # The gating metric test is on the realistic-range GT with the ABSOLUTE 1e-3 of north_star
+    # (tests/test_reference_gpu.py::test_tiny07_metrics_on_realistic_gt_hold_the_absolute_budget and the large07 one).
+    # This fixture's GT reaches down to 1e-3 (the config's validity floor), abs_rel divides by it and is O(7): a handful of
+    # pixels carry the mean, so here the deviations are REPORTED (relative) and only bounded against the oracle port's own
+    # autocast deviation.
+    check(abs(err["abs_rel"] - g["abs_rel"]) / g["abs_rel"], 1.5 * abs(eref["abs_rel"] - g["abs_rel"]) / g["abs_rel"] + 2.5e-3,
+          "tiny07 bf16 abs_rel on the ill-conditioned GT, relative (reported)")
+    check(abs(err["rmse"] - g["rmse"]) / g["rmse"], 1e-3, "tiny07 bf16 rmse on the ill-conditioned GT, relative")
 
 
 def test_host_buffer_entry_matches_device_entry():
@@ -324,7 +326,7 @@ def test_full_size_properties(shape, shift, dtype):
     qkv = torch.randn(b, h, w, 3 * c, device=DEV, generator=gen).to(dtype)
     table = 0.5 * torch.randn((2 * ws - 1) ** 2, nh, device=DEV, generator=gen)
     pad = (0.3 * torch.randn(3 * c, device=DEV, generator=gen)).to(dtype)
-    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    tol = 1e-5 if dtype == torch.float32 else TOL_BF16
 
     def run(t, p=pad):
         return torch.ops.swin_attn.fwd(t, None, table, p, None, ws, shift, nh, 32 ** -0.5, True, _lib.IMPL_AUTO, None)
@@ -349,8 +351,8 @@ def test_full_size_properties(shape, shift, dtype):
     both = qkv.clone()
     both[..., 2 * c:] = (0.5 * qkv[..., 2 * c:].float() + v2.float()).to(dtype)
     oc, _ = run(both, zpad)
-    check(rel_err(oc.float(), 0.5 * oa.float() + ob.float()), 1e-5 if dtype == torch.float32 else 3e-2,
-          f"linearity in v {dtype} (three bf16-rounded outputs compared)")
+    check(rel_err(oc.float(), 0.5 * oa.float() + ob.float()), 1e-5 if dtype == torch.float32 else TOL_BF16,
+          f"linearity in v {dtype} (three bf16-rounded outputs compared; measured 6.7e-3)")
     # (3) checksum against the oracle on one image of the batch (seconds on the CPU)
     want, want_lse = _oracle(qkv[:1].float(), None, table, ws, shift, nh, pad.float())
     assert rel_err(o[:1].float(), want) < (TOL_F32 if dtype == torch.float32 else TOL_BF16)
