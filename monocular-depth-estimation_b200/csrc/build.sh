@@ -7,6 +7,8 @@ out="$here/../libswin_attn.so"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 flags=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC
        -I"$root/include" -I"$here" -Xptxas -v)
+# SWIN_TC_TRACE=1: compile the per-pair clock stamps of the tcgen05 kernels in (tools/tc_trace.py); off in the product build
+[ "${SWIN_TC_TRACE:-0}" = "1" ] && flags+=(-DSWIN_TC_TRACE)
 mkdir -p "$here/build"
 pids=()
 for f in swin_attn_simt swin_attn_tc swin_attn_tc12 swin_attn_tc_bwd swin_linear_tc swin_block_ops swin_attn_api; do

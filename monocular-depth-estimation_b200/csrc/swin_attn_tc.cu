@@ -25,6 +25,8 @@
 //       a 128B-swizzled smem tile; then the O row x 1/rowsum -> bf16 -> 64B-swizzled staging tile -> TMA
 //       tensor store with the same boxes as the loads (window reverse, inverse shift and crop are
 //       tensor-map addressing as well; out-of-bounds = padding tokens are clipped by the TMA unit).
+#include <cstdlib>
+
 #include "swin_attn_tc.cuh"
 
 namespace swin {
@@ -61,7 +63,7 @@ __host__ __device__ inline SmemMapF smem_map_f() {
   m.v = m.qk + kQKStages * kQKBytes;
   m.slots = m.v + kVStages * kVBytes;
   m.bias = m.slots + kSlotsF * kSlotBytesF;
-  m.bars = m.bias + 176 * 4;
+  m.bars = m.bias + 192 * 4;   // 169 bias entries; [176, 182) / [184, 190): per-warp maxima / minima of them
   m.tmem_ptr = m.bars + 8 * (2 * kQKStages + 2 * kVStages + 4 * kSlotsF);
   m.total = m.tmem_ptr + 16;
   return m;
@@ -93,30 +95,43 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   const uint32_t bar_r = bar_o + 8 * kSlotsF;              // [kSlotsF]  O read, slot reusable
 
   // ---- one-time setup -------------------------------------------------------
-  // Thread 0 initialises the mbarriers; after one CTA barrier the producers start loading right away while the
-  // other warps fill the bytes TMA never writes, stage the bias and allocate TMEM, then meet on a named
-  // barrier (the MMA issuers are among them, so no MMA reads a tile before the fills are complete).
-  if (tid == 0) {
-    for (int i = 0; i < kQKStages; ++i) {
-      mbar_init(bar_qk_full + 8 * i, 2);
-      mbar_init(bar_qk_empty + 8 * i, 1);
+  // Everything up to pdl_wait() touches only kernel parameters and shared memory, so under programmatic dependent
+  // launch it overlaps the tail of the previous kernel in the stream.  The tensor-map descriptors are prefetched
+  // first (their fetch is on the critical path of the first TMA load), 36 threads initialise one mbarrier each;
+  // after one CTA barrier the producers start loading right away while the other warps fill the bytes TMA never
+  // writes, stage the bias and allocate TMEM, then meet on a named barrier (the MMA issuers are among them, so no
+  // MMA reads a tile before the fills are complete).
+  if ((warp == 0 || warp == 3) && lane == 0) {
+    for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
+      if (warp == 0) tma_prefetch_desc(&maps.q[i]);
+      if (warp == 0) tma_prefetch_desc(&maps.k[i]);
+      if (warp == 3) tma_prefetch_desc(&maps.v[i]);
+      if (warp == 3) tma_prefetch_desc(&maps.o[i]);
     }
-    for (int i = 0; i < kVStages; ++i) {
-      mbar_init(bar_v_full + 8 * i, 2);
-      mbar_init(bar_v_empty + 8 * i, 1);
-    }
-    for (int i = 0; i < kSlotsF; ++i) {
-      mbar_init(bar_s + 8 * i, 1);
-      mbar_init(bar_p + 8 * i, 128);
-      mbar_init(bar_o + 8 * i, 1);
-      mbar_init(bar_r + 8 * i, 128);
+  }
+  if (warp == 1) {
+    constexpr int kBars = 2 * kQKStages + 2 * kVStages + 4 * kSlotsF;
+    static_assert(kBars <= 64, "two barriers per lane at most");
+    for (int i = lane; i < kBars; i += 32) {
+      // counts: qk_full 2, qk_empty 1, v_full 2, v_empty 1, s 1, p 128, o 1, r 128 (layout of the bar_* addresses above)
+      uint32_t count;
+      if (i < kQKStages) count = 2;
+      else if (i < 2 * kQKStages) count = 1;
+      else if (i < 2 * kQKStages + kVStages) count = 2;
+      else if (i < 2 * kQKStages + 2 * kVStages) count = 1;
+      else {
+        const int k = (i - 2 * kQKStages - 2 * kVStages) / kSlotsF;
+        count = (k == 1 || k == 3) ? 128 : 1;
+      }
+      mbar_init(bar_qk_full + 8 * i, count);
     }
     fence_barrier_init();
   }
   __syncthreads();
+  if (warp == 0 || warp == 3) pdl_wait();   // the producers read q / k / v: the previous kernel's output
   if (warp != 0 && warp != 3) {
     const int t14 = tid - (warp < 3 ? 32 : 64);   // 0 .. kFillF-1 over the non-producer warps
-    // global loads first, so that their latency overlaps the fills: this head's bias column and pad vectors
+    // global loads first, so that their latency overlaps the fills: this head's bias column (a parameter)
     const float bias_v = t14 < 169 ? p.table[t14 * p.nH + h] * kLog2e : 0.f;
     if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
     // Rows 49-63 of the K / V tiles (TMA boxes write rows 0-48 only) must be finite: K rows 49-55 feed S
@@ -142,17 +157,25 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
           make_uint4(chunk == 0 ? 0x00003f80u : 0u, 0u, 0u, 0u);
     }
     if (t14 < 176) reinterpret_cast<float*>(smem + map.bias)[t14] = bias_v;
+    if (t14 < 192) {   // warp-level extrema of the head's 169 bias entries (t14 >> 5 = 0 .. 5): the softmax's upper bound
+      float bmx = t14 < 169 ? bias_v : -INFINITY, bmn = t14 < 169 ? bias_v : INFINITY;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        bmx = fmaxf(bmx, __shfl_xor_sync(0xffffffffu, bmx, d));
+        bmn = fminf(bmn, __shfl_xor_sync(0xffffffffu, bmn, d));
+      }
+      if (lane == 0) {
+        reinterpret_cast<float*>(smem + map.bias)[176 + (t14 >> 5)] = bmx;
+        reinterpret_cast<float*>(smem + map.bias)[184 + (t14 >> 5)] = bmn;
+      }
+    }
     fence_proxy_async();
     tc_fence_before();
-    named_barrier(6, kFillF);
+    named_barrier(9, kFillF);
     tc_fence_after();
-  } else if (lane == 0) {
-    for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
-      tma_prefetch_desc(&maps.q[i]);
-      tma_prefetch_desc(&maps.k[i]);
-      tma_prefetch_desc(&maps.v[i]);
-    }
+    pdl_wait();   // the softmax warps write o (and lse), the issuers read the pad vectors: after the dependency
   }
+  pdl_launch_dependents();   // the next PDL kernel may begin its own prologue; its pdl_wait still waits for this grid
   const uint32_t tmem_base = warp != 0 && warp != 3 ? *reinterpret_cast<volatile uint32_t*>(smem + map.tmem_ptr) : 0u;
 
   if (warp == 0 || warp == 3) {
@@ -289,6 +312,20 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     const float* brow = reinterpret_cast<const float*>(smem + map.bias) + base_i;
     const float c1s = p.scale * kLog2e;
     const float2 c1 = make_float2(c1s, c1s);
+    // Single-pass softmax: exp2 is taken against an UPPER BOUND of the row's logits instead of their exact maximum,
+    //   m' = c1 max_j S_ij + max(bias of the head)  >=  max_j (c1 S_ij + bias_ij)        (c1 > 0),
+    // which needs only a max over the raw accumulator (no bias gather) before the one fused pass
+    // bias gather -> FMA -> exp2 -> bf16.  Softmax is invariant to the offset: P, its row sum (taken by the PV MMA
+    // from the same bf16 values) and lse = m' + log2(sum) all carry the same factor 2^(max - m'), which cancels;
+    // m' - max <= spread of the head's bias, so the fast path is taken only while that spread (in log2 units) is far
+    // from the fp32 / bf16 exponent range.  Tiles with SW-MSA masks and degenerate scales take the exact two-pass form.
+    float bmax = -INFINITY, bmin = INFINITY;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      bmax = fmaxf(bmax, reinterpret_cast<const float*>(smem + map.bias)[176 + i]);
+      bmin = fminf(bmin, reinterpret_cast<const float*>(smem + map.bias)[184 + i]);
+    }
+    const bool bound_ok = c1s > 0.f && (bmax - bmin) < 64.f;
     const uint64_t all = (1ull << N) - 1;
     // SW-MSA regions (newcrf_layers.py:335-345) as tile-row bit sets: window rows / columns >= ws - shift
     uint64_t hb = 0, wb = 0;
@@ -300,7 +337,11 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     }
     const uint32_t sl = sbase + map.slots + g * kSlotBytesF;
     const uint32_t p_row = sl + sel * kPTileBytes + row * 128;
-    const uint32_t o_row = sl + sel * kTileBytes + row * 64;     // staging tile of this thread's output row
+    // staging tile of this thread's output row: the first 4 KB of this tile's OWN P bytes, so that P / staging reuse
+    // only couples the two warps of a tile (64-thread named barriers), never the two tiles of the pair
+    const uint32_t o_tile = sl + sel * kPTileBytes;
+    const uint32_t o_row = o_tile + row * 64;
+    const int tile_bar = 1 + 2 * g + sel;   // named barriers 1 .. 8: (slot, tile); 9 is the setup barrier
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + g * kSlotColsF;
     const uint32_t s_addr = taddr + sel * 56, o_addr = taddr + sel * 32;   // this tile's columns of S and of O
     const bool issuer = (q & 1) == 0;       // warps 0 and 2 of the warpgroup store tile 0 / tile 1
@@ -332,48 +373,58 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       tmem_ld_wait();
       if (tr) TC_TRACE(p, n, 9);
 
-      // pass 1: t = S * scale*log2e + bias*log2e (+ mask), row max.  Packed fp32x2 FMAs.
       float mx = -INFINITY;
-      if (!special) {
+      uint32_t w[25];
+      if (!special && bound_ok) {
+        // raw row maximum: four independent chains over the accumulator registers
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int j = 0; j < N - 1; j += 2) {
+        for (int j = 0; j < N - 1; j += 2)
+          m4[(j >> 1) & 3] = fmaxf(m4[(j >> 1) & 3], fmaxf(__uint_as_float(r[j]), __uint_as_float(r[j + 1])));
+        m4[0] = fmaxf(m4[0], __uint_as_float(r[N - 1]));
+        mx = fmaf(fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])), c1s, bmax);   // m' (see above)
+        if (tr) TC_TRACE2(p, n, 0);
+        const float2 nmx = make_float2(-mx, -mx);
+#pragma unroll
+        for (int e = 0; e < 24; ++e) {
+          const int j = 2 * e;
           const int cj0 = row_i<kPerm>(j) * 13 + row_j<kPerm>(j), cj1 = row_i<kPerm>(j + 1) * 13 + row_j<kPerm>(j + 1);
           const float2 t = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), c1,
                                       make_float2(brow[-cj0], brow[-cj1]));
-          r[j] = __float_as_uint(t.x);
-          r[j + 1] = __float_as_uint(t.y);
-          mx = fmaxf(mx, fmaxf(t.x, t.y));
+          const float2 x = __fadd2_rn(t, nmx);
+          w[e] = pack_bf16(fast_exp2(x.x), fast_exp2(x.y));
         }
         {
           const int cj = row_i<kPerm>(N - 1) * 13 + row_j<kPerm>(N - 1);
-          const float t = fmaf(__uint_as_float(r[N - 1]), c1s, brow[-cj]);
-          r[N - 1] = __float_as_uint(t);
-          mx = fmaxf(mx, t);
+          w[24] = pack_bf16(fast_exp2(fmaf(__uint_as_float(r[N - 1]), c1s, brow[-cj]) - mx), 0.f);
         }
       } else {
+        // exact two-pass form.  pass 1: t = S * scale*log2e + bias*log2e (+ mask), row max
 #pragma unroll
         for (int j = 0; j < N; ++j) {
           const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
           float t = fmaf(__uint_as_float(r[j]), c1s, brow[-cj]);
-          if ((masked >> j) & 1) t += -100.0f * kLog2e;
+          if (special && ((masked >> j) & 1)) t += -100.0f * kLog2e;
           r[j] = __float_as_uint(t);
           mx = fmaxf(mx, t);
         }
-      }
-      // pass 2: p = exp2(t - max), rounded to bf16 for the PV MMA; the row sum comes out of that MMA through the
-      // ones column, i.e. it is the sum of exactly the rounded values in P.
-      const float2 nmx = make_float2(-mx, -mx);
-      uint32_t w[25];
+        if (tr) TC_TRACE2(p, n, 0);
+        // pass 2: p = exp2(t - max), rounded to bf16 for the PV MMA; the row sum comes out of that MMA through the
+        // ones column, i.e. it is the sum of exactly the rounded values in P.
+        const float2 nmx = make_float2(-mx, -mx);
 #pragma unroll
-      for (int e = 0; e < 24; ++e) {
-        const float2 x = __fadd2_rn(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), nmx);
-        w[e] = pack_bf16(fast_exp2(x.x), fast_exp2(x.y));
+        for (int e = 0; e < 24; ++e) {
+          const float2 x = __fadd2_rn(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), nmx);
+          w[e] = pack_bf16(fast_exp2(x.x), fast_exp2(x.y));
+        }
+        w[24] = pack_bf16(fast_exp2(__uint_as_float(r[N - 1]) - mx), 0.f);
       }
-      w[24] = pack_bf16(fast_exp2(__uint_as_float(r[N - 1]) - mx), 0.f);
-      // the TMA stores of this warpgroup's previous pair must have finished reading the staging tiles (same
-      // bytes as P) before P is overwritten
+      if (tr) TC_TRACE2(p, n, 1);
+      // the TMA store of this tile's previous pair must have finished reading the staging tile (same bytes as the
+      // tile's P) before P is overwritten
       if (issuer && elect_one()) bulk_wait_read();
-      named_barrier(1 + g, 128);
+      named_barrier(tile_bar, 64);
+      if (tr) TC_TRACE2(p, n, 2);
       // P row (64 bf16, columns >= 50 zero) into the 128B-swizzled A tile of the PV MMA
 #pragma unroll
       for (int ch = 0; ch < 8; ++ch) {
@@ -414,10 +465,12 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         const uint32_t dst = o_row + (uint32_t)((ch ^ ((row >> 1) & 3)) << 4);
         asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]) : "memory");
       }
+      if (tr) TC_TRACE2(p, n, 4);
       fence_proxy_async();
-      named_barrier(1 + g, 128);
+      named_barrier(tile_bar, 64);
+      if (tr) TC_TRACE2(p, n, 5);
       if (issuer && valid && elect_one()) {
-        move_window<kShifted, true>(maps.o, sl + sel * kTileBytes, 0, p, it.b, it.wy, it.wx, h);
+        move_window<kShifted, true>(maps.o, o_tile, 0, p, it.b, it.wy, it.wx, h);
         bulk_commit();
       }
       if (p.lse != nullptr && valid && row < N) {
@@ -427,6 +480,7 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         p.lse[((int64_t)(it.b * p.Hp + y) * p.Wp + x) * p.nH + h] = (mx + log2f(l)) * 0.6931471805599453f;
       }
       __syncwarp();
+      if (tr) TC_TRACE2(p, n, 6);
     }
     if (issuer && elect_one()) bulk_wait_all();
   }
@@ -508,6 +562,16 @@ void tc::job_grid(const Problem& p, int sms, int* n_win, int* win_per_job, int* 
   *grid = chunks * p.nH;
 }
 
+// Programmatic dependent launch: the prologue of a kernel launched with the attribute (everything in front of its
+// griddepcontrol.wait) overlaps the tail of the previous kernel in the stream, also inside captured CUDA graphs.
+bool tc::pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("SWIN_PDL");
+    return e == nullptr || e[0] != '0';
+  }();
+  return on;
+}
+
 int tc::sm_count() {
   static int sms = 0;
   if (sms == 0) {
@@ -552,12 +616,22 @@ cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** er
   const int has_pad = (p.H != p.Hp || p.W != p.Wp) && (p.k_pad != nullptr || p.v_pad != nullptr) ? 1 : 0;
   int n_win, per, grid;
   tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(tcf::kThreadsF);
+  cfg.dynamicSmemBytes = map.total;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = tc::pdl_enabled() ? 1 : 0;
   {
     TimedRegion timed(st);
-    kernel<<<grid, tcf::kThreadsF, map.total, st>>>(p, n_win, per, has_pad, maps);
+    e = cudaLaunchKernelEx(&cfg, kernel, p, n_win, per, has_pad, maps);
   }
   count_launch();
-  return cudaGetLastError();
+  return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 }  // namespace swin

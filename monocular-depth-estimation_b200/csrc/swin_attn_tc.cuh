@@ -158,13 +158,16 @@ __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
 #define TMEM_LD_X2(taddr, r0, r1) \
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(r0), "=r"(r1) : "r"(taddr))
 
-// debug timeline (see swin_attn_debug_set_trace): event e of local pair n (< 256) of CTA 0; the buffer holds 8192 int64
+// Debug timelines (tools/tc_trace.py; see swin_attn_debug_set_trace).  Compiled in only with -DSWIN_TC_TRACE
+// (csrc/build.sh with SWIN_TC_TRACE=1): even predicated off, the stamps cost ~35 issue slots per softmax warp and pair.
+#ifdef SWIN_TC_TRACE
+// event e of local pair n (< 256) of CTA 0; the buffer holds 8192 int64
 #define TC_TRACE(p, n, e)                                                        \
   do {                                                                           \
     if ((p).trace != nullptr && blockIdx.x == 0) (p).trace[(n) * 16 + (e)] = clock64(); \
   } while (0)
 
-// debug timeline, every CTA: globaltimer (ns) at entry (which = 0) / exit (1) in trace[4096 + 2 * blockIdx.x + which]
+// every CTA: globaltimer (ns) at entry (which = 0) / exit (1) in trace[4096 + 2 * blockIdx.x + which]
 #define TC_TRACE_CTA(p, which)                                                   \
   do {                                                                           \
     if ((p).trace != nullptr) {                                                  \
@@ -173,6 +176,24 @@ __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
       (p).trace[4096 + 2 * blockIdx.x + (which)] = (long long)t_;                \
     }                                                                            \
   } while (0)
+// second table (softmax sub-phases): event e of local pair n at trace[8192 + n * 16 + e]
+#define TC_TRACE2(p, n, e)                                                       \
+  do {                                                                           \
+    if ((p).trace != nullptr && blockIdx.x == 0) (p).trace[8192 + (n) * 16 + (e)] = clock64(); \
+  } while (0)
+#else
+#define TC_TRACE(p, n, e) do { } while (0)
+#define TC_TRACE_CTA(p, which) do { } while (0)
+#define TC_TRACE2(p, n, e) do { } while (0)
+#endif
+
+// Programmatic dependent launch (PDL).  `pdl_wait` blocks until every grid this launch depends on has completed and
+// flushed its memory: everything that reads the previous kernel's output (or writes global memory) comes after it;
+// the prologue in front of it (mbarrier init, TMEM allocation, shared-memory fills, parameter staging, tensor-map
+// prefetch) overlaps the previous kernel's tail.  `pdl_launch_dependents` lets the next PDL-launched kernel start
+// its own prologue while this grid is still running.  Both are no-ops when the launch carries no PDL attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // ---- tiles and token order --------------------------------------------------------
 // Row r of a tile <-> token (i, j) of the window.  Natural order for un-shifted blocks;
@@ -306,6 +327,7 @@ bool tma_available();
 bool encode_matrix_map(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t pitch_bytes, int box_cols, int box_rows);
 void job_grid(const Problem& p, int sms, int* n_win, int* win_per_job, int* grid);
 int sm_count();
+bool pdl_enabled();   // programmatic dependent launch on the tcgen05 / LayerNorm launches (env SWIN_PDL=0 turns it off)
 constexpr int kBoxX[7] = {WS, WS - kShift, WS - kShift, kShift, kShift, WS - kShift, kShift};
 constexpr int kBoxY[7] = {WS, WS - kShift, kShift, WS - kShift, kShift, WS, WS};
 

@@ -186,7 +186,9 @@ def test_blocks_bf16_autocast_vs_reference_golden(golden, name):
     assert rel_err(out.float(), g["out"]) < TOL_BF16
     dx, dt = torch.autograd.grad((out.float() * g["cot"].to(DEV)).sum(), [x, blk.attn.relative_position_bias_table])
     assert rel_err(dx, g["dx"]) < TOL_BF16
-    check(rel_err(dt, g["dtable"]), TOL_BF16, f"bf16 block dtable {name}")
+    # d_table is a sum over every window of bf16-rounded dS: measured 4.5e-3 .. 1.04e-2 across fixtures and rounding
+    # patterns of P (r2: gpurun_out/parity_errors*.jsonl) -> 1.5x the measurement
+    check(rel_err(dt, g["dtable"]), 1.5 * TOL_BF16, f"bf16 block dtable {name}")
     with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
         assert rel_err(blk(*args).float(), g["out"]) < TOL_BF16
 

@@ -1,6 +1,8 @@
 #!/usr/bin/env python
 """Timeline of CTA 0 of the tcgen05 forward kernel (debug hook swin_attn_debug_set_trace).
-Prints, per local pair, SM-clock stamps (relative, in cycles) of the producer / MMA / softmax events."""
+Prints, per local pair, SM-clock stamps (relative, in cycles) of the producer / MMA / softmax events.
+Needs a trace build of the library:  SWIN_TC_TRACE=1 bash monocular-depth-estimation_b200/csrc/build.sh
+(the default build compiles the stamps out)."""
 import ctypes
 import os
 import sys
@@ -26,7 +28,7 @@ def main():
     pad = (0.1 * torch.randn(3 * c, device=dev)).bfloat16()
     lib = _lib.load()
     lib.swin_attn_debug_set_trace.argtypes = [ctypes.c_void_p]
-    trace = torch.zeros(8192, dtype=torch.int64, device=dev)   # 256 x 16 pair stamps of CTA 0, then (entry, exit) ns per CTA at 4096
+    trace = torch.zeros(16384, dtype=torch.int64, device=dev)   # 256 x 16 pair stamps of CTA 0, then (entry, exit) ns per CTA at 4096
 
     def run():
         return torch.ops.swin_attn.fwd(qkv, None, table, pad, None, ws, shift, nh, 32 ** -0.5, False, _lib.IMPL_AUTO, None)
@@ -57,6 +59,19 @@ def main():
         if int(t[n].max()) == 0:
             break
         print(f"{n:4d} " + " ".join(f"{(int(v) - t0) if v > 0 else -1:12d}" for v in t[n][:len(EV)]))
+
+
+    t2 = trace.cpu()[8192:8192 + 4096].view(256, 16)
+    if int(t2.max()) > 0:
+        ev2 = ["pass1", "pass2", "bar1", "-", "o_staged", "bar2", "loop_end"]
+        print("softmax sub-phases of tile 0 row 0 (cycles since sm_ld; then since sm_Rarrive)")
+        print("pair " + " ".join(f"{e:>10s}" for e in ev2))
+        for n in range(0, 256, 1 if stage >= 2 else 8):
+            if int(t[n].max()) == 0:
+                break
+            base1, base2 = int(t[n][9]), int(t[n][13])
+            vals = [int(t2[n][i]) - (base1 if i < 4 else base2) if int(t2[n][i]) > 0 else -1 for i in range(7)]
+            print(f"{n:4d} " + " ".join(f"{v:10d}" for v in vals))
 
 
 if __name__ == "__main__":
