@@ -111,6 +111,26 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape,
                            const void* q_pad, const void* k_pad, const void* v_pad,
                            const float* bias_table, void* o);
 
+/* Host-buffer forward that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid allocation).  Same arguments, results and error behaviour as swin_attn_forward_host, but the device
+ * staging of q / k / v / o, the pad vectors and the bias table lives in a file-scope `static __device__` array of
+ * SWIN_ATTN_STATIC_SCRATCH_BYTES inside the library instead of a cudaMalloc'd buffer; the call makes no cudaMalloc /
+ * cudaFree and calls no allocating library routine.
+ *   - Limit: 4 * align256(B*H*W*C*elem) + 3 * align256(C*elem) + align256((2ws-1)^2 * nH * 4) must not exceed
+ *     SWIN_ATTN_STATIC_SCRATCH_BYTES (8 MiB: e.g. bf16, B*H*W*C <= ~1.0 M elements).  Larger shapes are rejected with
+ *     an error naming both sizes, before any CUDA call; use swin_attn_forward_host for them.
+ *   - Cost: every GPU whose context loads the library holds those 8 MiB until the process exits.
+ *   - Sharing: all calls on a device use the SAME array, which keeps the previous call's contents (the entry point
+ *     overwrites its inputs in full and clears its output staging first).  Calls of this entry point are serialised by a
+ *     mutex and each synchronises before returning, so they never overlap; anything else that were to use the array
+ *     concurrently on the GPU would race with them. */
+#define SWIN_ATTN_STATIC_SCRATCH_BYTES (8u << 20)
+int swin_attn_forward_host_static(const swin_attn_shape_t* shape,
+                                  const void* q, const void* k, const void* v,
+                                  const void* q_pad, const void* k_pad, const void* v_pad,
+                                  const float* bias_table, void* o);
+
 /* Backward on UN-PADDED tensors (height / width need not be multiples of the window): the counterpart of calling
  * swin_attn_forward with pad vectors, i.e. the autograd of pad -> Linear -> attention -> crop of the reference
  * (newcrf_layers.py:212-217,248-249) without materialising the padded tensors.  TMA zero-fills the padding tokens, the

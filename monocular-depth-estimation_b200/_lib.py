@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libswin_attn.so")
 
 F32, BF16 = 0, 1
+STATIC_SCRATCH_BYTES = 8 << 20   # SWIN_ATTN_STATIC_SCRATCH_BYTES (include/swin_attn.h)
 IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05 = 0, 1, 2
 
 EXPORTS = (
@@ -22,6 +23,7 @@ EXPORTS = (
     "swin_attn_backward",
     "swin_attn_backward_unpadded",
     "swin_attn_forward_host",
+    "swin_attn_forward_host_static",
     "swin_layernorm_forward",
     "swin_layernorm_backward",
     "swin_patch_merge_layernorm_forward",
@@ -75,6 +77,8 @@ def load() -> ctypes.CDLL:
     lib.swin_attn_backward_unpadded.restype = c_int
     lib.swin_attn_forward_host.argtypes = [POINTER(Shape)] + [vp] * 8
     lib.swin_attn_forward_host.restype = c_int
+    lib.swin_attn_forward_host_static.argtypes = [POINTER(Shape)] + [vp] * 8
+    lib.swin_attn_forward_host_static.restype = c_int
     lib.swin_layernorm_forward.argtypes = [vp, c_int32, vp, vp, c_float, c_int64, c_int32, vp, c_int32, vp]
     lib.swin_layernorm_forward.restype = c_int
     lib.swin_layernorm_backward.argtypes = [vp, c_int32, vp, c_int32, vp, c_float, c_int64, c_int32, vp, vp, vp, vp]

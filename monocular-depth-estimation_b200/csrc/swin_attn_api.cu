@@ -194,6 +194,82 @@ int swin_attn_forward_host(const swin_attn_shape_t* shape, const void* q, const 
   return 0;
 }
 
+// ---- host-buffer forward that allocates nothing (swin_attn_forward_host_static) -------------------------------------
+// The staging scratch of swin_attn_forward_host, but in a file-scope device array instead of a cudaMalloc'd buffer:
+// for callers that may not allocate (CUDA graph capture around them, tight serving loops, harnesses that forbid
+// cudaMalloc).  Every GPU whose context loads this library holds SWIN_ATTN_STATIC_SCRATCH_BYTES of it until exit.
+// In HOST code `g_static_scratch` is only a host-side stand-in for the symbol, never a device address: the address is
+// resolved with cudaGetSymbolAddress, once per device, with that device current, and that pointer is what the copies
+// and the kernel get.
+static __device__ __align__(256) unsigned char g_static_scratch[SWIN_ATTN_STATIC_SCRATCH_BYTES];
+
+static constexpr int kMaxStaticDevices = 64;
+static std::mutex g_static_mu;
+static void* g_static_ptr[kMaxStaticDevices] = {};   // device address of g_static_scratch on device i (null = not resolved yet)
+
+// Device address of the static scratch on the CURRENT device (resolved on first use per device).  g_static_mu held.
+static int static_scratch_address(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail_cuda("swin_attn_forward_host_static: cudaGetDevice", e);
+  if (dev < 0 || dev >= kMaxStaticDevices) return fail("swin_attn_forward_host_static: device ordinal out of range");
+  if (g_static_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess) return fail_cuda("swin_attn_forward_host_static: cudaGetSymbolAddress", e);
+    if (ptr == nullptr) return fail("swin_attn_forward_host_static: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[dev] = ptr;
+  }
+  *out = g_static_ptr[dev];
+  return 0;
+}
+
+int swin_attn_forward_host_static(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v,
+                                  const void* q_pad, const void* k_pad, const void* v_pad, const float* bias_table, void* o) {
+  Problem p;
+  if (int rc = make_problem(shape, p)) return rc;
+  if (!q || !k || !v || !bias_table || !o) return fail("q, k, v, bias_table and o must be non-null");
+  if (p.q_ps != p.C || p.k_ps != p.C || p.v_ps != p.C || p.o_ps != p.C) return fail("host entry takes dense (B,H,W,C) buffers");
+  const size_t es = elem_size(shape->dtype);
+  const size_t tens = (size_t)p.B * p.H * p.W * p.C * es;
+  const size_t tens_al = (tens + 255) & ~size_t(255);
+  const size_t vec = ((size_t)p.C * es + 255) & ~size_t(255);
+  const size_t tab_bytes = (size_t)(2 * p.ws - 1) * (2 * p.ws - 1) * p.nH * 4;
+  const size_t tab = (tab_bytes + 255) & ~size_t(255);
+  const size_t need = 4 * tens_al + 3 * vec + tab;
+  if (need > (size_t)SWIN_ATTN_STATIC_SCRATCH_BYTES)   // checked before any CUDA call
+    return fail("swin_attn_forward_host_static: this shape needs " + std::to_string(need) + " bytes of device staging, the static "
+                "scratch holds SWIN_ATTN_STATIC_SCRATCH_BYTES = " + std::to_string((size_t)SWIN_ATTN_STATIC_SCRATCH_BYTES) +
+                " (use swin_attn_forward_host, which allocates)");
+  // One array per device, shared by every call: calls are serialised here and the call synchronises before it returns,
+  // so two calls of this entry point never overlap on the GPU.
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  void* scratch = nullptr;
+  if (int rc = static_scratch_address(&scratch)) return rc;
+  char* base = static_cast<char*>(scratch);
+  void* dq = base; void* dk = base + tens_al; void* dv = base + 2 * tens_al; void* dout = base + 3 * tens_al;
+  char* vecs = base + 4 * tens_al;
+  void* dqp = q_pad ? vecs : nullptr; void* dkp = k_pad ? vecs + vec : nullptr; void* dvp = v_pad ? vecs + 2 * vec : nullptr;
+  float* dtab = reinterpret_cast<float*>(vecs + 3 * vec);
+  cudaStream_t st = nullptr;
+  cudaError_t e;
+  // The array keeps the previous call's contents.  q / k / v / pads / table are overwritten in full below; the output
+  // staging is cleared, so that no byte of an earlier call's result can pass for this call's.
+  if ((e = cudaMemsetAsync(dout, 0, tens_al, st)) != cudaSuccess) return fail_cuda("clear output staging", e);
+  if ((e = cudaMemcpyAsync(dq, q, tens, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D q", e);
+  if ((e = cudaMemcpyAsync(dk, k, tens, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D k", e);
+  if ((e = cudaMemcpyAsync(dv, v, tens, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D v", e);
+  if (q_pad && (e = cudaMemcpyAsync(dqp, q_pad, p.C * es, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D q_pad", e);
+  if (k_pad && (e = cudaMemcpyAsync(dkp, k_pad, p.C * es, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D k_pad", e);
+  if (v_pad && (e = cudaMemcpyAsync(dvp, v_pad, p.C * es, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D v_pad", e);
+  if ((e = cudaMemcpyAsync(dtab, bias_table, tab_bytes, cudaMemcpyHostToDevice, st)) != cudaSuccess) return fail_cuda("H2D bias_table", e);
+  int rc = swin_attn_forward(shape, dq, dk, dv, dqp, dkp, dvp, dtab, nullptr, dout, nullptr, st);
+  if (rc) return rc;
+  if ((e = cudaMemcpyAsync(o, dout, tens, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return fail_cuda("D2H o", e);
+  if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return fail_cuda("host forward (static scratch)", e);
+  return 0;
+}
+
 int swin_layernorm_forward(const void* x, int32_t x_dtype, const float* gamma, const float* beta, float eps, int64_t rows, int32_t channels,
                            void* out, int32_t out_dtype, void* stream) {
   if (!x || !gamma || !beta || !out) return fail("layernorm: x, gamma, beta and out must be non-null");
