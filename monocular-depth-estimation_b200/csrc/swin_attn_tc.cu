@@ -9,7 +9,7 @@
 //
 //   producers (warps 0 / 3, one elected lane): window partition, cyclic shift, right/bottom zero
 //       padding are TMA tensor-map addressing over the image-order (B,H,W,channels) tensors
-//       (swin_attn_tc.cuh::move_window); two rings: 4 stages of (q0 q1 | k0 k1), 6 of (v0 v1 | ones).
+//       (swin_attn_tc.cuh::move_window); two rings: 5 stages of (q0 q1 | k0 k1), 7 of (v0 v1 | ones).
 //   pad tokens carry the Linear bias in the reference (newcrf_layers.py:212-217) while TMA zero-fills
 //       them.  All pad tokens of a head share ONE vector and the head is fixed per CTA: once a K / V
 //       tile has landed, the warp that issues its MMA overwrites the rows of the tile's pad tokens with
@@ -18,13 +18,15 @@
 //       instructions per row on half of the stage-2 tiles).
 //   MMA issuers (warps 1 / 2, one elected lane):
 //       S = [Q0;Q1] [K0;K1]^T   (M128 N112 K32)   tile t: rows 64t.., columns 56t..
-//       O = [P0;P1] [V0|V1|1]   (M128 N96  K64, V MN-major)   tile t: rows 64t.., columns 32t..;
+//       O = [P0;P1] [V0|V1|1]   (M128 N96  K64, A = P in TMEM, V MN-major)   tile t: rows 64t.., columns 32t..;
 //           column 64 multiplies a constant ones tile and holds the softmax row sums
 //   softmax warpgroups (4 x 4 warps, one accumulator slot each): scale + relative position bias (the
-//       head's 169 table entries staged in smem) + analytic SW-MSA mask, row max, exp2, P as bf16 into
-//       a 128B-swizzled smem tile; then the O row x 1/rowsum -> bf16 -> 64B-swizzled staging tile -> TMA
-//       tensor store with the same boxes as the loads (window reverse, inverse shift and crop are
-//       tensor-map addressing as well; out-of-bounds = padding tokens are clipped by the TMA unit).
+//       head's bias expanded to a [row][col] matrix in smem, read with 128-bit loads) + analytic SW-MSA
+//       mask, exact row max, exp2, P as bf16 written with tcgen05.st into the slot's spare TMEM columns
+//       (the PV MMA takes its A operand from tensor memory: P never touches shared memory); then the
+//       O row x 1/rowsum -> bf16 -> 64B-swizzled staging tile -> TMA tensor store with the same boxes as
+//       the loads (window reverse, inverse shift and crop are tensor-map addressing as well; out-of-bounds
+//       = padding tokens are clipped by the TMA unit).
 #include <cstdlib>
 
 #include "swin_attn_tc.cuh"
@@ -35,15 +37,21 @@ namespace tcf {
 using namespace tc;
 
 // Two rings: Q/K tiles live only until the S MMA has consumed them, V tiles until the PV MMA has.
-constexpr int kQKStages = 4;     // (q0 q1 | k0 k1): 4 pairs prefetched ahead of the S MMA
-constexpr int kVStages = 6;      // (v0 v1 | ones): 4 pairs inside the softmax warpgroups + 2 prefetched
+constexpr int kQKStages = 5;     // (q0 q1 | k0 k1): pairs prefetched ahead of the S MMA
+constexpr int kVStages = 7;      // (v0 v1 | ones): 4 pairs inside the softmax warpgroups + 3 prefetched
 constexpr int kSlotsF = 4;
 constexpr int kThreadsF = 128 + 128 * kSlotsF;
 constexpr int kFillF = kThreadsF - 64;         // threads of the non-producer warps
 constexpr int kQKBytes = 4 * kTileBytes;
 constexpr int kVBytes = 3 * kTileBytes;
-constexpr int kSlotBytesF = 2 * kPTileBytes;   // P0 P1 ; reused as o0 o1 staging
-constexpr int kSlotColsF = 128;                // S: 112 columns; O (65 columns) reuses them once S has been read
+// One accumulator slot = 128 TMEM columns: S in [0, 112); O (PV output, N = 96) overwrites [0, 96) once S has been
+// read; P (bf16, two per column: 64 K-values = 32 columns) lives in [96, 128) and is the A operand of the PV MMA,
+// read straight from tensor memory -- P never touches shared memory.  O goes through a 64B-swizzled staging tile per
+// (slot, tile) and a TMA tensor store (a direct store from registers was measured: every STG.128 of a warp touches 32
+// different 64-byte rows, ~2000 LSU wavefront-cycles per pair against ~500 for the staging stores).
+constexpr int kSlotColsF = 128;
+constexpr int kPColF = 96;
+constexpr int kBiasStride = 52;                // floats per row of the expanded bias matrix (49 used; 16-byte aligned rows)
 
 __device__ __forceinline__ uint32_t q_off(int t) { return t * kTileBytes; }
 __device__ __forceinline__ uint32_t k_off(int t) { return 2 * kTileBytes + t * kKTile1; }   // in a QK stage
@@ -55,15 +63,16 @@ struct TmaMapsF {
 };
 
 struct SmemMapF {
-  uint32_t qk, v, slots, bias, bars, tmem_ptr, total;
+  uint32_t qk, v, stage, bias, pads, bars, tmem_ptr, total;
 };
 __host__ __device__ inline SmemMapF smem_map_f() {
   SmemMapF m;
   m.qk = 0;
   m.v = m.qk + kQKStages * kQKBytes;
-  m.slots = m.v + kVStages * kVBytes;
-  m.bias = m.slots + kSlotsF * kSlotBytesF;
-  m.bars = m.bias + 176 * 4;
+  m.stage = m.v + kVStages * kVBytes;                       // O staging: one 64-row x 64 B tile per (slot, tile of the pair)
+  m.bias = m.stage + kSlotsF * 2 * kTileBytes;              // bias[row][col] * log2e of this CTA's head, tile order, fp32
+  m.pads = m.bias + ((N * kBiasStride * 4 + 127) & ~127);   // PadSets: y[0], y[1], x[0], x[1] (uint64 tile-row bit sets)
+  m.bars = m.pads + 32;
   m.tmem_ptr = m.bars + 8 * (2 * kQKStages + 2 * kVStages + 4 * kSlotsF);
   m.total = m.tmem_ptr + 16;
   return m;
@@ -131,8 +140,22 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   if (warp == 0 || warp == 3) pdl_wait();   // the producers read q / k / v: the previous kernel's output
   if (warp != 0 && warp != 3) {
     const int t14 = tid - (warp < 3 ? 32 : 64);   // 0 .. kFillF-1 over the non-producer warps
-    // global loads first, so that their latency overlaps the fills: this head's bias column (a parameter)
-    const float bias_v = t14 < 169 ? p.table[t14 * p.nH + h] * kLog2e : 0.f;
+    // Global loads first, so that their latency overlaps the fills: the head's relative-position bias (a parameter)
+    // expanded to bias[row][col] in TILE order (newcrf_layers.py:124-127: table[index[i, j], h]), pre-multiplied by
+    // log2(e).  Every softmax thread owns one row and reads it with 128-bit loads: 13 instead of 49 shared-memory
+    // instructions per row and pair.
+    constexpr int kBiasIters = (N * kBiasStride + kFillF - 1) / kFillF;
+    float bias_v[kBiasIters];
+#pragma unroll
+    for (int it = 0; it < kBiasIters; ++it) {
+      const int idx = t14 + it * kFillF;
+      const int r = idx / kBiasStride, c = idx - r * kBiasStride;
+      bias_v[it] = 0.f;
+      if (r < N && c < N) {
+        const int ti = (row_i<kPerm>(r) - row_i<kPerm>(c) + WS - 1) * (2 * WS - 1) + (row_j<kPerm>(r) - row_j<kPerm>(c) + WS - 1);
+        bias_v[it] = p.table[ti * p.nH + h] * kLog2e;
+      }
+    }
     if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
     // Rows 49-63 of the K / V tiles (TMA boxes write rows 0-48 only) must be finite: K rows 49-55 feed S
     // columns that are never read, V rows 49-63 are multiplied by P columns that are 0.  K tile 1 starts at row 56 of
@@ -150,18 +173,52 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
           make_uint4(0u, 0u, 0u, 0u);
     }
     // ones tile of every V stage (64B-swizzled, MN-major B of the PV MMA): element 0 of each key row is 1.0
-    // (bf16), so column 64 of O = sum_j P[i, j]
+    // (bf16), so column 64 of O = sum_j P[i, j] -- except the spare key rows 49 / 50 (see the pad vectors below)
     for (int i = t14; i < kVStages * 64 * 4; i += kFillF) {
       const int chunk = i & 3, rr = (i >> 2) & 63, st = i >> 8;
       *reinterpret_cast<uint4*>(smem + map.v + st * kVBytes + 2 * kTileBytes + rr * 64 + ((chunk ^ ((rr >> 1) & 3)) << 4)) =
-          make_uint4(chunk == 0 ? 0x00003f80u : 0u, 0u, 0u, 0u);
+          make_uint4(chunk == 0 && rr != N && rr != N + 1 ? 0x00003f80u : 0u, 0u, 0u, 0u);
     }
-    if (t14 < 176) reinterpret_cast<float*>(smem + map.bias)[t14] = bias_v;
+#pragma unroll
+    for (int it = 0; it < kBiasIters; ++it) {
+      const int idx = t14 + it * kFillF;
+      if (idx < N * kBiasStride) reinterpret_cast<float*>(smem + map.bias)[idx] = bias_v[it];
+    }
     fence_proxy_async();
     tc_fence_before();
     named_barrier(9, kFillF);
     tc_fence_after();
-    pdl_wait();   // the softmax warps write o (and lse), the issuers read the pad vectors: after the dependency
+    pdl_wait();   // the softmax warps write o (and lse); the pad vectors may come from a cast kernel: after the dependency
+    if (has_pad) {
+      // Pad tokens carry the projection bias (the reference pads before the Linear) while TMA zero-fills them.  All
+      // pad tokens of a head share ONE vector and the head is fixed per CTA, so the vectors go -- once -- into the
+      // spare row 49 of every K / V tile (rows 49+ are never written by the TMA boxes):
+      //   S column 49 = q . k_pad: the softmax substitutes it for the columns of pad tokens (whose K rows are 0);
+      //   P columns 49 / 50 = hi / lo bf16 halves of the row's summed probability over pad tokens (their V rows are 0),
+      //   times V rows 49 / 50 = v_pad -- two halves, so that the sum enters with 16 mantissa bits like the fp32
+      //   accumulation of the individual products would.
+      // The ones tile has 0 in rows 49 / 50, so the row sum is not affected.  No per-pair work is left in the MMA issuers.
+      constexpr int kKRows = kQKStages * 2 * 4, kVRows = kVStages * 2 * 2 * 4;   // x 4 chunks of 16 B; V: rows 49 and 50
+      if (t14 < kKRows + kVRows) {
+        const bool is_k = t14 < kKRows;
+        const int i = is_k ? t14 : t14 - kKRows;
+        const int chunk = i & 3, t = (i >> 2) & 1;
+        const int st = is_k ? i >> 3 : i >> 4, rowx = is_k ? N : N + ((i >> 3) & 1);
+        const void* vecp = is_k ? p.k_pad : p.v_pad;
+        const uint4 val = vecp == nullptr ? make_uint4(0u, 0u, 0u, 0u)
+                                          : reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(vecp) + h * kHeadDim)[chunk];
+        unsigned char* tile = is_k ? smem + map.qk + st * kQKBytes + k_off(t) : smem + map.v + st * kVBytes + v_off(t);
+        *reinterpret_cast<uint4*>(tile + rowx * 64 + ((chunk ^ ((rowx >> 1) & 3)) << 4)) = val;
+      }
+      if (t14 == kFillF - 1) {
+        PadSets<kPerm> pads;
+        pads.init(p);
+        uint64_t* dst = reinterpret_cast<uint64_t*>(smem + map.pads);
+        dst[0] = pads.y[0]; dst[1] = pads.y[1]; dst[2] = pads.x[0]; dst[3] = pads.x[1];
+      }
+      fence_proxy_async();
+      named_barrier(9, kFillF);
+    }
   }
   pdl_launch_dependents();   // the next PDL kernel may begin its own prologue; its pdl_wait still waits for this grid
   const uint32_t tmem_base = warp != 0 && warp != 3 ? *reinterpret_cast<volatile uint32_t*>(smem + map.tmem_ptr) : 0u;
@@ -203,32 +260,16 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   } else if (warp == 1) {
     // ===== S = Q K^T issuer (2 instructions per pair) ===========================================
     constexpr uint32_t idesc_s = instr_desc(128, 112, 0);
-    const bool fix = has_pad && p.k_pad != nullptr;
-    PadSets<kPerm> pads;
-    uint4 kvec[4] = {};
-    WinIter it;
-    it.init(p, w0);
-    if (fix) {
-      pads.init(p);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) kvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.k_pad) + h * kHeadDim)[c];
-    }
+    // The tiles of pair n + 1 are waited for right after pair n has been issued, so that nothing but the slot
+    // hand-over (bar_r) sits between a free accumulator and the S MMA.
+    auto prepare = [&](int n) {
+      const int s = n % kQKStages;
+      mbar_wait(bar_qk_full + 8 * s, (n / kQKStages) & 1);
+    };
+    if (n_pairs > 0) prepare(0);
     for (int n = 0; n < n_pairs; ++n) {
       const int s = n % kQKStages, a = n % kSlotsF;
       const uint32_t st = sbase + map.qk + s * kQKBytes;
-      mbar_wait(bar_qk_full + 8 * s, (n / kQKStages) & 1);
-      if (fix) {   // pad tokens of the two K tiles <- k_pad (generic-proxy writes after the TMA boxes have landed)
-        const uint64_t pad0 = pads.of(p, it.wy, it.wx);
-        it.advance(p, 1);
-        const uint64_t pad1 = it.w < w1 ? pads.of(p, it.wy, it.wx) : 0;
-        it.advance(p, 1);
-        if (pad0 | pad1) {
-          write_pad_rows(st + k_off(0), pad0, kvec, lane);
-          write_pad_rows(st + k_off(1), pad1, kvec, lane);
-          fence_proxy_async();
-        }
-        __syncwarp();
-      }
       mbar_wait(bar_r + 8 * a, ((n / kSlotsF) & 1) ^ 1);
       tc_fence_after();
       const uint32_t d = tmem_base + a * kSlotColsF;
@@ -243,50 +284,40 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         TC_TRACE(p, n, 4);
       }
       __syncwarp();
+      if (n + 1 < n_pairs) prepare(n + 1);
     }
   } else if (warp == 2) {
     // ===== O = P V issuer (4 instructions per pair) =============================================
     constexpr uint32_t idesc_o = instr_desc(128, 96, 1);
-    const bool fix = has_pad && p.v_pad != nullptr;
-    PadSets<kPerm> pads;
-    uint4 vvec[4] = {};
-    WinIter it;
-    it.init(p, w0);
-    if (fix) {
-      pads.init(p);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) vvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.v_pad) + h * kHeadDim)[c];
-    }
+    // As in the S issuer.  (An earlier form wrote the V rows of pad tokens here, per pair: 330-800 cycles between
+    // "P ready" and the MMA on the critical path of every pair -- the PV issuer set the pace of the whole CTA.)
+    auto prepare = [&](int m) {
+      const int s = m % kVStages;
+      if (elect_one()) TC_TRACE2(p, m, 8);
+      mbar_wait(bar_v_full + 8 * s, (m / kVStages) & 1);
+      if (elect_one()) TC_TRACE2(p, m, 9);
+    };
+    if (n_pairs > 0) prepare(0);
     for (int m = 0; m < n_pairs; ++m) {
       const int s = m % kVStages, a = m % kSlotsF;
       const uint32_t st = sbase + map.v + s * kVBytes;
-      mbar_wait(bar_v_full + 8 * s, (m / kVStages) & 1);
-      if (fix) {   // pad tokens of the two V tiles <- v_pad, while the softmax of the pair is still running
-        const uint64_t pad0 = pads.of(p, it.wy, it.wx);
-        it.advance(p, 1);
-        const uint64_t pad1 = it.w < w1 ? pads.of(p, it.wy, it.wx) : 0;
-        it.advance(p, 1);
-        if (pad0 | pad1) {
-          write_pad_rows(st + v_off(0), pad0, vvec, lane);
-          write_pad_rows(st + v_off(1), pad1, vvec, lane);
-          fence_proxy_async();
-        }
-        __syncwarp();
-      }
+      if (elect_one()) TC_TRACE2(p, m, 10);
       mbar_wait(bar_p + 8 * a, (m / kSlotsF) & 1);
       tc_fence_after();
       const uint32_t d = tmem_base + a * kSlotColsF;               // O overwrites the S columns
-      const uint64_t pd = smem_desc(sbase + map.slots + a * kSlotBytesF, 16, 1024, 2);   // 128 rows: p0 | p1
+      const uint32_t pa = d + kPColF;                              // A = P in tensor memory: 128 lanes x 64 bf16 (32 columns)
       const uint64_t vd = smem_desc(st + v_off(0), kTileBytes, 512, 4);   // N = 96: v0 | v1 | ones, one tile apart
       if (elect_one()) {
         TC_TRACE(p, m, 5);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_ss(d, pd + 2 * k, vd + 64 * k, idesc_o, k);
+        for (int k = 0; k < 4; ++k) umma_ts(d, pa + 8 * k, vd + 64 * k, idesc_o, k);   // K = 16 per step: 8 columns of A
+        TC_TRACE2(p, m, 11);
         umma_commit(bar_o + 8 * a);
         umma_commit(bar_v_empty + 8 * s);
         TC_TRACE(p, m, 6);
       }
       __syncwarp();
+      if (m + 1 < n_pairs) prepare(m + 1);
     }
   } else {
     // ===== softmax / epilogue warpgroups =======================================
@@ -296,8 +327,8 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     const int row = (q & 1) * 32 + lane;    // row of this tile's S / O held by this thread
     const int rowc = row < N ? row : N - 1;
     const int ri = row_i<kPerm>(rowc), rj = row_j<kPerm>(rowc);
-    const int base_i = ri * 13 + rj + 84;   // relative_position_index[row, col] = base_i - (ci*13 + cj)
-    const float* brow = reinterpret_cast<const float*>(smem + map.bias) + base_i;
+    // this thread's row of the expanded bias matrix (tile order, * log2e): 13 x 128-bit loads per pair
+    const float4* brow = reinterpret_cast<const float4*>(smem + map.bias + rowc * kBiasStride * 4);
     const float c1s = p.scale * kLog2e;
     const float2 c1 = make_float2(c1s, c1s);
     const uint64_t all = (1ull << N) - 1;
@@ -309,15 +340,13 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
 #pragma unroll
       for (int j = WS - kShift; j < WS; ++j) wb |= rows_of_window_col<kPerm>(j);
     }
-    const uint32_t sl = sbase + map.slots + g * kSlotBytesF;
-    const uint32_t p_row = sl + sel * kPTileBytes + row * 128;
-    // staging tile of this thread's output row: the first 4 KB of this tile's OWN P bytes, so that P / staging reuse
-    // only couples the two warps of a tile (64-thread named barriers), never the two tiles of the pair
-    const uint32_t o_tile = sl + sel * kPTileBytes;
-    const uint32_t o_row = o_tile + row * 64;
-    const int tile_bar = 1 + 2 * g + sel;   // named barriers 1 .. 8: (slot, tile); 9 is the setup barrier
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + g * kSlotColsF;
     const uint32_t s_addr = taddr + sel * 56, o_addr = taddr + sel * 32;   // this tile's columns of S and of O
+    const uint32_t p_addr = taddr + kPColF;                                // this row's 32 columns of P
+    // staging tile of this thread's output row; it couples only the two warps of a tile (64-thread named barriers)
+    const uint32_t o_tile = sbase + map.stage + (2 * g + sel) * kTileBytes;
+    const uint32_t o_row = o_tile + row * 64;
+    const int tile_bar = 1 + 2 * g + sel;   // named barriers 1 .. 8: (slot, tile); 9 is the setup barrier
     const bool issuer = (q & 1) == 0;       // warps 0 and 2 of the warpgroup store tile 0 / tile 1
     WinIter it;
     it.init(p, w0 + 2 * g + sel);
@@ -325,7 +354,13 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     int m = 0;
     for (int n = g; n < n_pairs; n += kSlotsF, ++m, it.advance(p, 2 * kSlotsF)) {
       const bool valid = it.w < w1;
-      // Padding needs nothing here: the issuer warps have put the pad vectors into the K / V rows of pad tokens.
+      // tile rows (= columns) of this window's pad tokens; they occur in the last two window rows / columns only
+      uint64_t padm = 0;
+      if (has_pad) {
+        const uint64_t* ps = reinterpret_cast<const uint64_t*>(smem + map.pads);
+        if (it.wy >= p.nWy - 2) padm |= ps[it.wy - (p.nWy - 2)];
+        if (it.wx >= p.nWx - 2) padm |= ps[2 + it.wx - (p.nWx - 2)];
+      }
       uint64_t masked = 0;
       if (kShifted) {
         const uint64_t hm = it.wy == p.nWy - 1 ? hb : 0, wm = it.wx == p.nWx - 1 ? wb : 0;
@@ -346,70 +381,81 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       TMEM_LD_X2(s_addr + 48, r[48], r[49]);   // column 49 belongs to the zero rows and is not used
       tmem_ld_wait();
       if (tr) TC_TRACE(p, n, 9);
+      if (padm != 0) {   // warp-uniform.  K rows of pad tokens are zero (TMA fill): their logit is q . k_pad = S column 49
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+          if ((padm >> j) & 1) r[j] = r[N];
+      }
 
       // pass 1: t = S * scale*log2e + bias*log2e (+ mask), exact row max.  Packed fp32x2 FMAs, four independent max
       // chains (a serial one is 25 deep).  (A single-pass form that exponentiates against an upper bound of the logits,
       // c1 max S + max bias, was measured in round 2: no faster, and it costs accuracy -- the dominant probability of a
-      // row is then no longer exactly 1.0 in bf16: large07 AbsRel deviation 7.9e-4 against 3.3e-4, mean depth bias x5.)
-      float mx = -INFINITY;
-      if (!special) {
+      // row is then no longer exactly 1.0 in bf16: profiles/r2_softmax_bound_vs_exact.md.)
+      float mx;
+      {
+        constexpr float kMasked = -100.0f * kLog2e;   // the SW-MSA mask value of the reference (-100, not -inf)
         float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int j = 0; j < N - 1; j += 2) {
-          const int cj0 = row_i<kPerm>(j) * 13 + row_j<kPerm>(j), cj1 = row_i<kPerm>(j + 1) * 13 + row_j<kPerm>(j + 1);
-          const float2 t = __ffma2_rn(make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), c1,
-                                      make_float2(brow[-cj0], brow[-cj1]));
-          r[j] = __float_as_uint(t.x);
-          r[j + 1] = __float_as_uint(t.y);
-          m4[(j >> 1) & 3] = fmaxf(m4[(j >> 1) & 3], fmaxf(t.x, t.y));
+        for (int c4 = 0; c4 < 12; ++c4) {       // columns 4 c4 .. 4 c4 + 3
+          const float4 b4 = brow[c4];
+          float2 t0 = __ffma2_rn(make_float2(__uint_as_float(r[4 * c4]), __uint_as_float(r[4 * c4 + 1])), c1, make_float2(b4.x, b4.y));
+          float2 t1 = __ffma2_rn(make_float2(__uint_as_float(r[4 * c4 + 2]), __uint_as_float(r[4 * c4 + 3])), c1, make_float2(b4.z, b4.w));
+          if (special) {   // warp-uniform: tiles of the last window row / column of a shifted block
+            if ((masked >> (4 * c4)) & 1) t0.x += kMasked;
+            if ((masked >> (4 * c4 + 1)) & 1) t0.y += kMasked;
+            if ((masked >> (4 * c4 + 2)) & 1) t1.x += kMasked;
+            if ((masked >> (4 * c4 + 3)) & 1) t1.y += kMasked;
+          }
+          r[4 * c4] = __float_as_uint(t0.x);
+          r[4 * c4 + 1] = __float_as_uint(t0.y);
+          r[4 * c4 + 2] = __float_as_uint(t1.x);
+          r[4 * c4 + 3] = __float_as_uint(t1.y);
+          m4[c4 & 3] = fmaxf(m4[c4 & 3], fmaxf(fmaxf(t0.x, t0.y), fmaxf(t1.x, t1.y)));
         }
         {
-          const int cj = row_i<kPerm>(N - 1) * 13 + row_j<kPerm>(N - 1);
-          const float t = fmaf(__uint_as_float(r[N - 1]), c1s, brow[-cj]);
+          float t = fmaf(__uint_as_float(r[N - 1]), c1s, brow[12].x);
+          if (special && ((masked >> (N - 1)) & 1)) t += kMasked;
           r[N - 1] = __float_as_uint(t);
           m4[0] = fmaxf(m4[0], t);
         }
         mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-      } else {
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-          const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
-          float t = fmaf(__uint_as_float(r[j]), c1s, brow[-cj]);
-          if ((masked >> j) & 1) t += -100.0f * kLog2e;
-          r[j] = __float_as_uint(t);
-          mx = fmaxf(mx, t);
-        }
       }
       if (tr) TC_TRACE2(p, n, 0);
       // pass 2: p = exp2(t - max), rounded to bf16 for the PV MMA; the row sum comes out of that MMA through the
       // ones column, i.e. it is the sum of exactly the rounded values in P.
       const float2 nmx = make_float2(-mx, -mx);
-      uint32_t w[25];
+      uint32_t w[32];   // P row: 64 bf16 (columns >= 49 zero), two per register = the 32 TMEM columns of this lane
 #pragma unroll
       for (int e = 0; e < 24; ++e) {
         const float2 x = __fadd2_rn(make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1])), nmx);
         w[e] = pack_bf16(fast_exp2(x.x), fast_exp2(x.y));
       }
       w[24] = pack_bf16(fast_exp2(__uint_as_float(r[N - 1]) - mx), 0.f);
-      if (tr) TC_TRACE2(p, n, 1);
-      // the TMA store of this tile's previous pair must have finished reading the staging tile (same bytes as the
-      // tile's P) before P is overwritten
-      if (issuer && elect_one()) bulk_wait_read();
-      named_barrier(tile_bar, 64);
-      if (tr) TC_TRACE2(p, n, 2);
-      // P row (64 bf16, columns >= 50 zero) into the 128B-swizzled A tile of the PV MMA
 #pragma unroll
-      for (int ch = 0; ch < 8; ++ch) {
-        const uint32_t dst = p_row + ((ch ^ (row & 7)) << 4);
-        const uint32_t w0 = 4 * ch < 25 ? w[4 * ch < 25 ? 4 * ch : 0] : 0u, w1 = 4 * ch + 1 < 25 ? w[4 * ch + 1 < 25 ? 4 * ch + 1 : 0] : 0u;
-        const uint32_t w2 = 4 * ch + 2 < 25 ? w[4 * ch + 2 < 25 ? 4 * ch + 2 : 0] : 0u, w3 = 4 * ch + 3 < 25 ? w[4 * ch + 3 < 25 ? 4 * ch + 3 : 0] : 0u;
-        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+      for (int e = 25; e < 32; ++e) w[e] = 0u;
+      if (padm != 0) {   // V rows of pad tokens are zero: their share of O is (their summed probability) x v_pad = P cols 49 / 50 x V rows 49 / 50
+        float pp = 0.f;
+#pragma unroll
+        for (int j = 0; j < N; ++j)
+          if ((padm >> j) & 1) pp += __uint_as_float((j & 1) ? (w[j >> 1] & 0xffff0000u) : (w[j >> 1] << 16));
+        const uint32_t hi = pack_bf16(0.f, pp) & 0xffff0000u;                         // column 49
+        w[24] = (w[24] & 0x0000ffffu) | hi;
+        w[25] = pack_bf16(pp - __uint_as_float(hi), 0.f);                            // column 50: what the first half lost
       }
+      if (tr) TC_TRACE2(p, n, 1);
+      // P row -> this lane's columns [96, 128) of the slot: the A operand of the PV MMA, read from tensor memory.  The
+      // S columns it overlaps ([96, 112)) are dead for this lane: its S row is in registers (tmem_ld_wait above), and
+      // every thread touches its own lane only.
+      TMEM_ST_X16(p_addr, (w + 0));
+      TMEM_ST_X16(p_addr + 16, (w + 16));
+      tmem_st_wait();
       if (tr) TC_TRACE(p, n, 10);
-      fence_proxy_async();
       tc_fence_before();
       mbar_arrive(bar_p + 8 * g);
       if (tr) TC_TRACE(p, n, 11);
+      // while the PV MMA runs: the TMA store of this tile's previous pair must have finished reading the staging tile
+      if (issuer && elect_one()) bulk_wait_read();
+      named_barrier(tile_bar, 64);
 
       mbar_wait(bar_o + 8 * g, m & 1);
       tc_fence_after();
@@ -423,7 +469,9 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       mbar_arrive(bar_r + 8 * g);
       if (tr) TC_TRACE(p, n, 13);
 
-      // O row / rowsum -> bf16 -> 64B-swizzled staging tile
+      // O row / rowsum -> bf16 -> 64B-swizzled staging tile -> TMA tensor store with the boxes of the loads: window
+      // reverse, inverse shift and the final crop (newcrf_layers.py:239-249) are tensor-map addressing; out-of-bounds
+      // elements (padding tokens) are clipped by the TMA unit.
       const float inv1 = 1.0f / l;
       const float2 inv = make_float2(inv1, inv1);
 #pragma unroll

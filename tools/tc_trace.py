@@ -64,6 +64,13 @@ def main():
     t2 = trace.cpu()[8192:8192 + 4096].view(256, 16)
     if int(t2.max()) > 0:
         ev2 = ["pass1", "pass2", "bar1", "-", "o_staged", "bar2", "loop_end"]
+        # PV issuer (absolute, relative to t0): loop top, V landed, before the P wait, MMAs issued
+        print("PV issuer: pair   loop_top   v_landed  before_P   (Pready)  mmas_out  (PV_issued)")
+        for n in range(0, 256, 1 if stage >= 2 else 8):
+            if int(t[n].max()) == 0:
+                break
+            f = lambda v: (int(v) - t0) if int(v) > 0 else -1
+            print(f"           {n:4d} {f(t2[n][8]):10d} {f(t2[n][9]):10d} {f(t2[n][10]):10d} {f(t[n][5]):10d} {f(t2[n][11]):10d} {f(t[n][6]):10d}")
         print("softmax sub-phases of tile 0 row 0 (cycles since sm_ld; then since sm_Rarrive)")
         print("pair " + " ".join(f"{e:>10s}" for e in ev2))
         for n in range(0, 256, 1 if stage >= 2 else 8):
