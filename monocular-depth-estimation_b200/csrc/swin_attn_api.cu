@@ -114,7 +114,7 @@ static int backward_impl(const swin_attn_shape_t* shape, const void* q, const vo
     return fail("backward: tensors must be aligned to 4 elements");
   p.q = q; p.k = k; p.v = v; p.o_in = o; p.d_o = d_o; p.lse = const_cast<float*>(lse);
   p.table = bias_table; p.dq = dq; p.dk = dk; p.dv = dv; p.d_table = d_bias_table;
-  p.k_pad = k_pad; p.v_pad = v_pad; p.d_kpad = d_k_pad; p.d_vpad = d_v_pad;
+  p.k_pad = k_pad; p.v_pad = v_pad; p.d_kpad = d_k_pad; p.d_vpad = d_v_pad; p.trace = g_trace;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_backward_supported(p, shape->dtype);

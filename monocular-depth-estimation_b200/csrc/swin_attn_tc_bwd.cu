@@ -25,8 +25,8 @@
 //         dQ = [dS0  ;dS1  ] [K0 |K1 ]    A = dS image read K-major  (M = query i, K = key j)
 //         T += [dS0  ;dS1  ] I            A = dS image read K-major, B = 64x64 identity
 //       T (128 lanes x 64 columns of TMEM) accumulates sum_windows dS for the job's head over the whole
-//       CTA lifetime; at the end each row is scattered once into 169 shared-memory bins and the bins
-//       are added to d_bias_table with 169 global atomics per CTA.
+//       CTA lifetime; at the end the rows go through shared memory once, one thread per relative position sums
+//       its entries, and the 169 sums are added to d_bias_table with 169 global atomics per CTA.
 //       The off-diagonal blocks of every stacked product are computed and ignored.
 //   epilogue: dQ/dK/dV rows TMEM -> registers -> bf16 -> 64B-swizzled staging tiles (they reuse the
 //       P / dS bytes of the slot) -> TMA tensor stores with the same boxes as the loads, so the
@@ -34,12 +34,24 @@
 //
 // Warps: 0 / 3 TMA producers (tile 0 / tile 1), 1 phase-1 MMA issuer, 2 phase-2 MMA issuer,
 // 4-11 two softmax warpgroups (one accumulator slot each).
+#include <utility>
+
 #include "swin_attn_tc.cuh"
 
 namespace swin {
 namespace tcb {
 
 using namespace tc;
+
+// timeline of CTA 0 (tools/tc_trace.py --bwd; trace build only): event e of local pair n at trace[12288 + n * 16 + e]
+#ifdef SWIN_TC_TRACE
+#define TCB_TRACE(p, n, e)                                                                          \
+  do {                                                                                              \
+    if ((p).trace != nullptr && blockIdx.x == 0 && (n) < 240) (p).trace[12288 + (n) * 16 + (e)] = clock64(); \
+  } while (0)
+#else
+#define TCB_TRACE(p, n, e) do { } while (0)
+#endif
 
 constexpr int kStagesB = 4;
 constexpr int kSlotsB = 2;
@@ -61,7 +73,7 @@ struct TmaMapsB {
 };
 
 struct SmemMapB {
-  uint32_t stages, slots, ident, bias, bins, padacc, bars, tmem_ptr, total;
+  uint32_t stages, slots, ident, bias, padacc, bars, tmem_ptr, total;
 };
 __host__ __device__ inline SmemMapB smem_map_b() {
   SmemMapB m;
@@ -69,8 +81,7 @@ __host__ __device__ inline SmemMapB smem_map_b() {
   m.slots = m.stages + kStagesB * kStageBytesB;
   m.ident = m.slots + kSlotsB * kSlotBytes;
   m.bias = m.ident + kPTileBytes;
-  m.bins = m.bias + 176 * 4;
-  m.padacc = (m.bins + 176 * 4 + 15) & ~15u;   // [slot][tile][dK | dV][32] fp32: sums over padding tokens (un-padded mode)
+  m.padacc = (m.bias + 176 * 4 + 15) & ~15u;   // [slot][tile][dK | dV][32] fp32: sums over padding tokens (un-padded mode)
   m.bars = m.padacc + kSlotsB * 2 * 64 * 4;
   m.tmem_ptr = m.bars + 8 * (2 * kStagesB + 4 * kSlotsB);
   m.total = m.tmem_ptr + 16;
@@ -98,6 +109,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   const uint32_t bar_o = bar_p + 8 * kSlotsB;              // [kSlotsB]  dQ, dK, dV ready
   const uint32_t bar_r = bar_o + 8 * kSlotsB;              // [kSlotsB]  outputs read, slot reusable
 
+  if (tid == 0) TCB_TRACE(p, 239, 0);                             // kernel entry
   // ---- one-time setup -------------------------------------------------------
   // As in the forward: mbarrier init, one CTA barrier, then the producers start loading while the other 10
   // warps fill what TMA never writes, stage the bias, build the identity and allocate TMEM.
@@ -115,11 +127,25 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     fence_barrier_init();
   }
   __syncthreads();
+  if (tid == 0) TCB_TRACE(p, 239, 1);                             // barriers initialised
+  // Un-padded mode (H, W not multiples of the window): TMA zero-fills the padding tokens, which carry the projection
+  // bias in the reference; their K / V rows are overwritten with k_pad / v_pad once the tiles have landed (phase-1
+  // issuer).  The vectors are read here, ahead of the fills, so that the (cold) loads overlap the set-up.
+  const bool fix = has_pad && (p.k_pad != nullptr || p.v_pad != nullptr);
+  uint4 kvec[4] = {}, vvec[4] = {};
+  if (warp == 1 && fix) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      if (p.k_pad != nullptr) kvec[c] = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.k_pad) + h * kHeadDim) + c);
+      if (p.v_pad != nullptr) vvec[c] = __ldg(reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.v_pad) + h * kHeadDim) + c);
+    }
+  }
   if (warp != 0 && warp != 3) {
     constexpr int kFill = kThreadsB - 64;
     const int t10 = tid - (warp < 3 ? 32 : 64);   // 0 .. 319 over the 10 non-producer warps
     const float bias_v = t10 < 169 ? p.table[t10 * p.nH + h] * kLog2e : 0.f;
     if (warp == 1) tmem_alloc(sbase + map.tmem_ptr, 512);
+    if (tid == 32) TCB_TRACE(p, 239, 2);                          // TMEM allocated
     // Rows 49-63 of every tile (the TMA boxes write rows 0-48) must stay finite: as the K dimension of a
     // phase-2 product they are multiplied by zero columns of P / dS.  K / V tile 1 start at row 56 of tile 0.
     for (int i = t10; i < kStagesB * 8 * 15 * 4; i += kFill) {
@@ -142,13 +168,14 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     }
     if (t10 < 176) {
       reinterpret_cast<float*>(smem + map.bias)[t10] = bias_v;
-      reinterpret_cast<float*>(smem + map.bins)[t10] = 0.f;
     }
     if (t10 < kSlotsB * 2 * 64) reinterpret_cast<float*>(smem + map.padacc)[t10] = 0.f;
     fence_proxy_async();
     tc_fence_before();
+    if (tid == 32) TCB_TRACE(p, 239, 3);                          // fills done
     named_barrier(5, kFill);
     tc_fence_after();
+    if (tid == 32) TCB_TRACE(p, 239, 4);                          // set-up barrier passed
   } else if (lane == 0) {
     for (int i = kShifted ? 1 : 0; i < (kShifted ? 7 : 1); ++i) {
       tma_prefetch_desc(&maps.q[i]); tma_prefetch_desc(&maps.k[i]); tma_prefetch_desc(&maps.v[i]);
@@ -168,6 +195,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       mbar_wait(bar_empty + 8 * s, ((n / kStagesB) & 1) ^ 1);
       if (it.w < w1) {
         if (elect_one()) {
+          if (t == 0) TCB_TRACE(p, n, 0);                       // producer: stage free, loads issued
           mbar_expect_tx(bar, kLoadBytes);
           move_window<kShifted, false>(maps.q, st + bq_off(t), bar, p, it.b, it.wy, it.wx, h);
           move_window<kShifted, false>(maps.k, st + bk_off(t), bar, p, it.b, it.wy, it.wx, h);
@@ -187,25 +215,16 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   } else if (warp == 1) {
     // ===== phase 1: S = Q K^T, dP = dO V^T ======================================================
     constexpr uint32_t idesc = instr_desc(128, 112, 0);
-    // Un-padded mode (H, W not multiples of the window): TMA zero-fills the padding tokens, which carry the projection
-    // bias in the reference; their K / V rows are overwritten with k_pad / v_pad once the tiles have landed.
-    const bool fix = has_pad && (p.k_pad != nullptr || p.v_pad != nullptr);
     PadSets<kPerm> pads;
-    uint4 kvec[4] = {}, vvec[4] = {};
     WinIter it;
     it.init(p, w0);
-    if (fix) {
-      pads.init(p);
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        if (p.k_pad != nullptr) kvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.k_pad) + h * kHeadDim)[c];
-        if (p.v_pad != nullptr) vvec[c] = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.v_pad) + h * kHeadDim)[c];
-      }
-    }
+    if (fix) pads.init(p);
     for (int n = 0; n < n_pairs; ++n) {
       const int s = n % kStagesB, a = n % kSlotsB;
       const uint32_t st = sbase + map.stages + s * kStageBytesB;
+      if (elect_one()) TCB_TRACE(p, n, 1);                      // phase 1: loop top
       mbar_wait(bar_full + 8 * s, (n / kStagesB) & 1);
+      if (elect_one()) TCB_TRACE(p, n, 2);                      // phase 1: tiles landed
       if (fix) {
         const uint64_t pad0 = pads.of(p, it.wy, it.wx);
         it.advance(p, 1);
@@ -220,6 +239,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         }
         __syncwarp();
       }
+      if (elect_one()) TCB_TRACE(p, n, 3);                      // phase 1: pads fixed, waiting for the slot
       mbar_wait(bar_r + 8 * a, ((n / kSlotsB) & 1) ^ 1);
       tc_fence_after();
       const uint32_t d = tmem_base + a * kSlotColsB;
@@ -231,6 +251,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
 #pragma unroll
         for (int k = 0; k < 2; ++k) umma_ss(d + 112, gd + 2 * k, vd + 2 * k, idesc, k);
         umma_commit(bar_s + 8 * a);
+        TCB_TRACE(p, n, 4);                                     // phase 1 issued
       }
       __syncwarp();
     }
@@ -244,6 +265,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       const int s = m % kStagesB, a = m % kSlotsB;
       mbar_wait(bar_p + 8 * a, (m / kSlotsB) & 1);
       tc_fence_after();
+      if (elect_one()) TCB_TRACE(p, m, 5);                      // phase 2: P / dS seen
       const uint32_t st = sbase + map.stages + s * kStageBytesB;
       const uint32_t sl = sbase + map.slots + a * kSlotBytes;
       const uint32_t d = tmem_base + a * kSlotColsB;
@@ -264,6 +286,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         for (int k = 0; k < 4; ++k) umma_ss(tmem_base + kDtCol, ds_k + 2 * k, id_k + 2 * k, idesc_nn, (m | k) != 0);
         umma_commit(bar_o + 8 * a);
         umma_commit(bar_empty + 8 * s);
+        TCB_TRACE(p, m, 6);                                     // phase 2 issued
       }
       __syncwarp();
     }
@@ -300,20 +323,39 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     const bool issuer = (q & 1) == 0;       // warps 0 and 2 of the warpgroup store tile 0 / tile 1
     WinIter it;
     it.init(p, w0 + 2 * g + sel);
-
-    int m = 0;
-    for (int n = g; n < n_pairs; n += kSlotsB, ++m, it.advance(p, 2 * kSlotsB)) {
-      const bool valid = it.w < w1;
-      int y = it.wy * WS + ri + p.shift, x = it.wx * WS + rj + p.shift;
+    // Per-pair state of this thread's row.  The lse read is a global load (about 1500 cycles under load): it is
+    // issued one pair AHEAD, at the top of the previous iteration, so that its latency is off the slot's critical path.
+    // padding tokens of a tile (un-padded mode): as QUERY rows they get P = 0 (lse = +inf: their output was
+    // cropped, the forward's lse there is unspecified); as KEY columns their dS / P mass is summed into column 49,
+    // so that row 49 of the dK / dV products is the gradient of k_pad / v_pad (rows 49+ of K, Q, dO tiles are zero).
+    struct RowState {
+      bool valid;
+      uint64_t padded;
+      float lse;
+    };
+    auto fetch = [&](const WinIter& w) {
+      RowState s;
+      s.valid = w.w < w1;
+      int y = w.wy * WS + ri + p.shift, x = w.wx * WS + rj + p.shift;
       if (y >= p.Hp) y -= p.Hp;
       if (x >= p.Wp) x -= p.Wp;
-      // padding tokens of this tile (un-padded mode): as QUERY rows they get P = 0 (lse = +inf: their output was
-      // cropped, the forward's lse there is unspecified); as KEY columns their dS / P mass is summed into column 49,
-      // so that row 49 of the dK / dV products is the gradient of k_pad / v_pad (rows 49+ of K, Q, dO tiles are zero).
-      const uint64_t padded = has_pad && valid ? pads.of(p, it.wy, it.wx) : 0;
-      const bool row_pad = (padded >> rowc) & 1;
-      float lse2 = 0.f;
-      if (valid && row < N) lse2 = row_pad ? INFINITY : p.lse[((int64_t)(it.b * p.Hp + y) * p.Wp + x) * p.nH + h] * kLog2e;
+      s.padded = has_pad && s.valid ? pads.of(p, w.wy, w.wx) : 0;
+      s.lse = 0.f;
+      if (s.valid && row < N) s.lse = ((s.padded >> rowc) & 1) ? INFINITY : __ldg(&p.lse[((int64_t)(w.b * p.Hp + y) * p.Wp + x) * p.nH + h]);
+      return s;
+    };
+    RowState nxt = {false, 0, 0.f};
+    if (g < n_pairs) nxt = fetch(it);
+
+    int m = 0;
+    for (int n = g; n < n_pairs; n += kSlotsB, ++m) {
+      const RowState cur = nxt;
+      WinIter itn = it;
+      itn.advance(p, 2 * kSlotsB);
+      if (n + kSlotsB < n_pairs) nxt = fetch(itn);
+      const bool valid = cur.valid;
+      const uint64_t padded = cur.padded;
+      const float lse2 = cur.lse * kLog2e;
       uint64_t masked = 0;
       if (kShifted) {
         const uint64_t hm = it.wy == p.nWy - 1 ? hb : 0, wm = it.wx == p.nWx - 1 ? wb : 0;
@@ -321,8 +363,11 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       }
       const bool special = kShifted && (it.wy == p.nWy - 1 || it.wx == p.nWx - 1);   // warp-uniform
 
+      const bool tr = q == 0 && lane == 0;
+      if (tr) TCB_TRACE(p, n, 7);                               // softmax: waiting for S / dP
       mbar_wait(bar_s + 8 * g, m & 1);
       tc_fence_after();
+      if (tr) TCB_TRACE(p, n, 8);                               // S / dP ready
       uint32_t r[N + 15], d[N + 15];
       TMEM_LD_X16(s_addr, (r + 0));
       TMEM_LD_X16(s_addr + 16, (r + 16));
@@ -333,6 +378,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       TMEM_LD_X16(dp_addr + 32, (d + 32));
       TMEM_LD_X1(dp_addr + 48, d[48]);
       tmem_ld_wait();
+      if (tr) TCB_TRACE(p, n, 9);                               // loaded
 
       // P = exp2(S * scale*log2e + bias*log2e (+ mask) - lse*log2e)
       const float2 nl = make_float2(-lse2, -lse2);
@@ -395,6 +441,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       }
       // the TMA stores of this warpgroup's previous pair must have finished reading the staging tiles
       // (same bytes as P / dS) before they are overwritten
+      if (tr) TCB_TRACE(p, n, 10);                              // math done
       if (issuer && elect_one()) bulk_wait_read();
       named_barrier(1 + g, 128);
 #pragma unroll
@@ -409,9 +456,11 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(bar_p + 8 * g);
+      if (tr) TCB_TRACE(p, n, 11);                              // P / dS handed over
 
       mbar_wait(bar_o + 8 * g, m & 1);
       tc_fence_after();
+      if (tr) TCB_TRACE(p, n, 12);                              // dQ / dK / dV ready
       // dQ (x scale), dK (x scale), dV rows -> bf16 -> 64B-swizzled staging tiles
 #pragma unroll
       for (int t3 = 0; t3 < 3; ++t3) {
@@ -447,6 +496,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       }
       tc_fence_before();
       mbar_arrive(bar_r + 8 * g);
+      if (tr) TCB_TRACE(p, n, 13);                              // outputs read, slot released
       fence_proxy_async();
       named_barrier(1 + g, 128);
       if (issuer && valid && elect_one()) {
@@ -457,14 +507,17 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         bulk_commit();
       }
       __syncwarp();
+      if (tr) TCB_TRACE(p, n, 14);                              // stores issued
+      it = itn;
     }
+    if (tid == 128) TCB_TRACE(p, 239, 5);                         // warpgroup 0: last pair stored
     if (issuer && elect_one()) bulk_wait_all();
 
     // ---- bias-table gradient: T[row i, col j] = sum over the job's windows of dS -------------------
     // The phase-2 MMAs complete in issue order, so once the warpgroup that owns the LAST pair has seen its
     // bar_o, T is final; a barrier over both warpgroups publishes that to warpgroup 0, which scatters.
     named_barrier(3, 128 * kSlotsB);
-    float* bins = reinterpret_cast<float*>(smem + map.bins);
+    if (tid == 128) TCB_TRACE(p, 239, 6);                         // both warpgroups done
     if (g == 0 && n_pairs > 0) {
       tc_fence_after();
       uint32_t tr[N + 15];
@@ -474,15 +527,26 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       TMEM_LD_X16(t_addr + 32, (tr + 32));
       TMEM_LD_X1(t_addr + 48, tr[48]);
       tmem_ld_wait();
+      // T rows -> shared memory [tile][row][49] (the stage buffers are free: every load was consumed by an MMA that has
+      // completed; lane stride 49 words, conflict-free), then one thread per bin sums the (7 - |di|)(7 - |dj|) entries
+      // of both tiles that share the relative position (di, dj).  (fp32 shared atomics are CAS loops: 49 per thread
+      // took 5 us per launch.)
+      float* ts = reinterpret_cast<float*>(smem + map.stages);
       if (row < N) {
 #pragma unroll
-        for (int j = 0; j < N; ++j) {
-          const int cj = row_i<kPerm>(j) * 13 + row_j<kPerm>(j);
-          atomicAdd(&bins[base_i - cj], __uint_as_float(tr[j]));
-        }
+        for (int j = 0; j < N; ++j) ts[(sel * N + row) * N + j] = __uint_as_float(tr[j]);
       }
       named_barrier(4, 128);
-      for (int i = tid - 128; i < 169; i += 128) atomicAdd(&p.d_table[i * p.nH + h], bins[i]);
+      for (int b = tid - 128; b < 169; b += 128) {
+        const int di = b / 13 - 6, dj = b % 13 - 6;   // bin = (ri - ci + 6) * 13 + (rj - cj + 6)
+        float sum = 0.f;
+        for (int ci = max(0, -di); ci <= min(WS - 1, WS - 1 - di); ++ci)
+          for (int cj = max(0, -dj); cj <= min(WS - 1, WS - 1 - dj); ++cj) {
+            const int e = token_row<kPerm>(ci + di, cj + dj) * N + token_row<kPerm>(ci, cj);
+            sum += ts[e] + ts[N * N + e];
+          }
+        atomicAdd(&p.d_table[b * p.nH + h], sum);
+      }
       // (the named barrier over both warpgroups above also ordered every padacc update before these reads)
       if (has_pad && tid - 128 < 64) {
         float* dst = tid - 128 < 32 ? p.d_kpad : p.d_vpad;
@@ -492,11 +556,13 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         for (int i = 0; i < kSlotsB * 2; ++i) sum += acc[i * 64];
         if (dst != nullptr) atomicAdd(&dst[h * kHeadDim + ((tid - 128) & 31)], sum);
       }
+      if (tid == 128) TCB_TRACE(p, 239, 7);                       // bias-table / pad-vector gradients added
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (tid == 0) TCB_TRACE(p, 239, 8);                             // kernel exit
   if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
@@ -539,11 +605,25 @@ cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** e
   int n_win, per, grid;
   tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
   TimedRegion timed(st);   // the memsets are device work of the op: inside the timed region
-  e = cudaMemsetAsync(p.d_table, 0, sizeof(float) * 169 * p.nH, st);
-  if (e != cudaSuccess) return e;
+  // d_bias_table, d_k_pad and d_v_pad are accumulated with atomics and start at zero.  Buffers that touch (the torch
+  // binding lays them out back to back: k_pad | v_pad | table) are cleared by ONE memset instead of three launches.
+  struct Span { char* lo; char* hi; } spans[3];
+  int n_spans = 0;
+  auto add_span = [&](float* ptr, size_t count) {
+    if (ptr != nullptr) spans[n_spans++] = Span{reinterpret_cast<char*>(ptr), reinterpret_cast<char*>(ptr + count)};
+  };
+  add_span(p.d_table, (size_t)169 * p.nH);
+  add_span(p.d_kpad, (size_t)p.C);
+  add_span(p.d_vpad, (size_t)p.C);
+  for (int i = 1; i < n_spans; ++i)
+    for (int j = i; j > 0 && spans[j].lo < spans[j - 1].lo; --j) std::swap(spans[j], spans[j - 1]);
+  for (int i = 0; i < n_spans;) {
+    int j = i + 1;
+    while (j < n_spans && spans[j].lo == spans[j - 1].hi) ++j;
+    if ((e = cudaMemsetAsync(spans[i].lo, 0, (size_t)(spans[j - 1].hi - spans[i].lo), st)) != cudaSuccess) return e;
+    i = j;
+  }
   const int has_pad = (p.H != p.Hp || p.W != p.Wp) ? 1 : 0;
-  if (p.d_kpad != nullptr && (e = cudaMemsetAsync(p.d_kpad, 0, sizeof(float) * p.C, st)) != cudaSuccess) return e;
-  if (p.d_vpad != nullptr && (e = cudaMemsetAsync(p.d_vpad, 0, sizeof(float) * p.C, st)) != cudaSuccess) return e;
   kernel<<<grid, tcb::kThreadsB, map.total, st>>>(p, n_win, per, has_pad, maps);
   count_launch();
   return cudaGetLastError();

@@ -262,16 +262,24 @@ std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor> bwd_unpadded_cuda(const Tenso
   Tensor d_packed = at::empty({b, h, w, pc}, packed.options());
   Tensor d_v = v.defined() ? at::empty({b, h, w, c}, packed.options()) : at::empty({0}, packed.options());
   const Tensor table = bias_table.detach().to(at::kFloat).contiguous();
-  Tensor d_table = at::empty_like(table);
+  // The small fp32 gradients live in ONE buffer, q_pad | k_pad | v_pad | bias table: the library clears buffers that
+  // touch with a single memset (k_pad | v_pad | table; swin_attn_tc_bwd.cu), and the q_pad part -- no gradient flows into
+  // the padding QUERIES, their output rows are cropped -- is cleared here.
   // pad vectors: k_pad = packed_pad[C:2C]; v_pad = packed_pad[2C:3C] (fused qkv) or the separate v_pad (external v)
   Tensor packed_pad, v_pad, d_packed_pad, d_v_pad;
   const char *kpad = nullptr, *vpad = nullptr;
   float *d_kpad = nullptr, *d_vpad = nullptr;
   const auto fopt = packed.options().dtype(at::kFloat);
-  if (packed_pad_in.has_value()) {
-    TORCH_CHECK(packed_pad_in->numel() == pc, "swin_attn: packed_pad must have ", pc, " elements");
+  const bool has_pp = packed_pad_in.has_value(), has_vp = v.defined() && v_pad_in.has_value();
+  if (has_pp) TORCH_CHECK(packed_pad_in->numel() == pc, "swin_attn: packed_pad must have ", pc, " elements");
+  if (has_vp) TORCH_CHECK(v_pad_in->numel() == c, "swin_attn: v_pad must have ", c, " elements");
+  const int64_t n_pp = has_pp ? pc : 0, n_vp = has_vp ? c : 0;
+  Tensor small = at::empty({n_pp + n_vp + table.numel()}, fopt);
+  Tensor d_table = small.narrow(0, n_pp + n_vp, table.numel()).view(table.sizes());
+  if (has_pp) {
     packed_pad = packed_pad_in->detach().to(dt).contiguous();
-    d_packed_pad = at::zeros({pc}, fopt);
+    d_packed_pad = small.narrow(0, 0, pc);
+    d_packed_pad.narrow(0, 0, c).zero_();
     kpad = byte_ptr(packed_pad) + c * es;
     d_kpad = d_packed_pad.data_ptr<float>() + c;
     if (!v.defined()) {
@@ -281,10 +289,9 @@ std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor> bwd_unpadded_cuda(const Tenso
   } else {
     d_packed_pad = at::empty({0}, fopt);
   }
-  if (v.defined() && v_pad_in.has_value()) {
-    TORCH_CHECK(v_pad_in->numel() == c, "swin_attn: v_pad must have ", c, " elements");
+  if (has_vp) {
     v_pad = v_pad_in->detach().to(dt).contiguous();
-    d_v_pad = at::zeros({c}, fopt);
+    d_v_pad = small.narrow(0, n_pp, c);
     vpad = byte_ptr(v_pad);
     d_vpad = d_v_pad.data_ptr<float>();
   } else {
