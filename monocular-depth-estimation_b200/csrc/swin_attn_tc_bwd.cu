@@ -33,7 +33,7 @@
 //       window reverse and the inverse cyclic shift are tensor-map addressing as well.
 //
 // Warps: 0 / 3 TMA producers (tile 0 / tile 1), 1 phase-1 MMA issuer, 2 phase-2 MMA issuer,
-// 4-11 two softmax warpgroups (one accumulator slot each).
+// 4-11 two softmax / gradient warpgroups (one accumulator slot each).  The producers also issue the TMA stores.
 #include <utility>
 
 #include "swin_attn_tc.cuh"
@@ -83,7 +83,7 @@ __host__ __device__ inline SmemMapB smem_map_b() {
   m.bias = m.ident + kPTileBytes;
   m.padacc = (m.bias + 176 * 4 + 15) & ~15u;   // [slot][tile][dK | dV][32] fp32: sums over padding tokens (un-padded mode)
   m.bars = m.padacc + kSlotsB * 2 * 64 * 4;
-  m.tmem_ptr = m.bars + 8 * (2 * kStagesB + 4 * kSlotsB);
+  m.tmem_ptr = m.bars + 8 * (2 * kStagesB + 6 * kSlotsB);
   m.total = m.tmem_ptr + 16;
   return m;
 }
@@ -108,6 +108,8 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   const uint32_t bar_p = bar_s + 8 * kSlotsB;              // [kSlotsB]  P, dS written
   const uint32_t bar_o = bar_p + 8 * kSlotsB;              // [kSlotsB]  dQ, dK, dV ready
   const uint32_t bar_r = bar_o + 8 * kSlotsB;              // [kSlotsB]  outputs read, slot reusable
+  const uint32_t bar_g = bar_r + 8 * kSlotsB;              // [kSlotsB]  dQ, dK, dV staged (softmax -> producers)
+  const uint32_t bar_f = bar_g + 8 * kSlotsB;              // [kSlotsB]  staging tiles read by the TMA stores
 
   if (tid == 0) TCB_TRACE(p, 239, 0);                             // kernel entry
   // ---- one-time setup -------------------------------------------------------
@@ -123,6 +125,8 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       mbar_init(bar_p + 8 * i, 128);
       mbar_init(bar_o + 8 * i, 1);
       mbar_init(bar_r + 8 * i, 128);
+      mbar_init(bar_g + 8 * i, 128);
+      mbar_init(bar_f + 8 * i, 2);
     }
     fence_barrier_init();
   }
@@ -187,31 +191,57 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
   if (warp == 0 || warp == 3) {
     // ===== TMA producers: warp 0 -> tile 0 of every pair, warp 3 -> tile 1 =====================
     const int t = warp == 0 ? 0 : 1;
-    WinIter it;
+    // They also issue the TMA STORES of their tile: the store of pair e is issued in iteration e + kStagesB, right
+    // after the loads that refill the stage pair e's phase 2 has just released -- its epilogue finishes a few hundred
+    // cycles later, so the wait on bar_g is short and the softmax warpgroups never issue or wait for a store.
+    WinIter it, its;
     it.init(p, w0 + t);
-    for (int n = 0; n < n_pairs; ++n, it.advance(p, 2)) {
-      const int s = n % kStagesB;
-      const uint32_t st = sbase + map.stages + s * kStageBytesB, bar = bar_full + 8 * s;
-      mbar_wait(bar_empty + 8 * s, ((n / kStagesB) & 1) ^ 1);
-      if (it.w < w1) {
-        if (elect_one()) {
-          if (t == 0) TCB_TRACE(p, n, 0);                       // producer: stage free, loads issued
-          mbar_expect_tx(bar, kLoadBytes);
-          move_window<kShifted, false>(maps.q, st + bq_off(t), bar, p, it.b, it.wy, it.wx, h);
-          move_window<kShifted, false>(maps.k, st + bk_off(t), bar, p, it.b, it.wy, it.wx, h);
-          move_window<kShifted, false>(maps.d_o, st + bdo_off(t), bar, p, it.b, it.wy, it.wx, h);
-          move_window<kShifted, false>(maps.v, st + bv_off(t), bar, p, it.b, it.wy, it.wx, h);
+    its = it;
+    for (int n = 0; n < n_pairs + kStagesB; ++n) {
+      if (n < n_pairs) {
+        const int s = n % kStagesB;
+        const uint32_t st = sbase + map.stages + s * kStageBytesB, bar = bar_full + 8 * s;
+        mbar_wait(bar_empty + 8 * s, ((n / kStagesB) & 1) ^ 1);
+        if (it.w < w1) {
+          if (elect_one()) {
+            if (t == 0) TCB_TRACE(p, n, 0);                       // producer: stage free, loads issued
+            mbar_expect_tx(bar, kLoadBytes);
+            move_window<kShifted, false>(maps.q, st + bq_off(t), bar, p, it.b, it.wy, it.wx, h);
+            move_window<kShifted, false>(maps.k, st + bk_off(t), bar, p, it.b, it.wy, it.wx, h);
+            move_window<kShifted, false>(maps.d_o, st + bdo_off(t), bar, p, it.b, it.wy, it.wx, h);
+            move_window<kShifted, false>(maps.v, st + bv_off(t), bar, p, it.b, it.wy, it.wx, h);
+          }
+        } else {
+          // Half-empty last pair of the job.  Rows 0-7 of K tile 1 are rows 56-63 of the K dimension of the dQ
+          // product of tile 0 (multiplied by zero columns of dS): they must be finite even if never loaded.
+          *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytesB + bk_off(t) + lane * 16) = make_uint4(0u, 0u, 0u, 0u);
+          fence_proxy_async();
+          __syncwarp();
+          if (elect_one()) mbar_arrive(bar);
         }
-      } else {
-        // Half-empty last pair of the job.  Rows 0-7 of K tile 1 are rows 56-63 of the K dimension of the dQ
-        // product of tile 0 (multiplied by zero columns of dS): they must be finite even if never loaded.
-        *reinterpret_cast<uint4*>(smem + map.stages + s * kStageBytesB + bk_off(t) + lane * 16) = make_uint4(0u, 0u, 0u, 0u);
-        fence_proxy_async();
         __syncwarp();
-        if (elect_one()) mbar_arrive(bar);
+        it.advance(p, 2);
       }
-      __syncwarp();
+      if (n >= kStagesB) {
+        const int e = n - kStagesB, a = e % kSlotsB;
+        mbar_wait(bar_g + 8 * a, (e / kSlotsB) & 1);            // dQ / dK / dV of pair e are in the staging tiles
+        if (elect_one()) {
+          if (its.w < w1) {
+            const uint32_t src = sbase + map.slots + a * kSlotBytes + t * kTileBytes;
+            move_window<kShifted, true>(maps.dq, src, 0, p, its.b, its.wy, its.wx, h);
+            move_window<kShifted, true>(maps.dk, src + 2 * kTileBytes, 0, p, its.b, its.wy, its.wx, h);
+            move_window<kShifted, true>(maps.dv, src + 4 * kTileBytes, 0, p, its.b, its.wy, its.wx, h);
+            bulk_commit();
+          }
+          bulk_wait_read();                  // the stores have read the staging tiles:
+          mbar_arrive(bar_f + 8 * a);        // P / dS of pair e + 2 may be written over them
+          if (t == 0) TCB_TRACE(p, e, 14);                        // stores issued and read
+        }
+        __syncwarp();
+        its.advance(p, 2);
+      }
     }
+    if (elect_one()) bulk_wait_all();
   } else if (warp == 1) {
     // ===== phase 1: S = Q K^T, dP = dO V^T ======================================================
     constexpr uint32_t idesc = instr_desc(128, 112, 0);
@@ -291,13 +321,14 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       __syncwarp();
     }
   } else {
-    // ===== softmax / gradient warpgroups ======================================================
-    const int g = (warp >> 2) - 1;          // accumulator slot owned by this warpgroup
+    // ===== softmax / gradient warpgroups: warpgroup g owns accumulator slot g, i.e. pairs g, g + 2, ... =====
+    const int g = (warp >> 2) - 1;
     const int q = warp & 3;                 // TMEM sub-partition: lanes 32q .. 32q+31
     const int sel = q >> 1;                 // tile of the pair
     const int row = (q & 1) * 32 + lane;    // row of this tile's S / dP / dQ / dK / dV held by this thread
     const int rowc = row < N ? row : N - 1;
     const int ri = row_i<kPerm>(rowc), rj = row_j<kPerm>(rowc);
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
     const int base_i = ri * 13 + rj + 84;   // relative_position_index[row, col] = base_i - (ci*13 + cj)
     const float* brow = reinterpret_cast<const float*>(smem + map.bias) + base_i;
     const float c1s = p.scale * kLog2e;
@@ -318,16 +349,17 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
     const uint32_t p_row = sl + sel * kPTileBytes + row * 128;
     const uint32_t ds_row = p_row + 2 * kPTileBytes;
     const uint32_t stage_row = sl + sel * kTileBytes + row * 64;   // + 2 * kTileBytes per output tensor
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + g * kSlotColsB;
+    const uint32_t taddr = lane_base + g * kSlotColsB;
     const uint32_t s_addr = taddr + sel * 56, dp_addr = taddr + 112 + sel * 56;
-    const bool issuer = (q & 1) == 0;       // warps 0 and 2 of the warpgroup store tile 0 / tile 1
+    const bool tr = q == 0 && lane == 0;
     WinIter it;
     it.init(p, w0 + 2 * g + sel);
-    // Per-pair state of this thread's row.  The lse read is a global load (about 1500 cycles under load): it is
-    // issued one pair AHEAD, at the top of the previous iteration, so that its latency is off the slot's critical path.
-    // padding tokens of a tile (un-padded mode): as QUERY rows they get P = 0 (lse = +inf: their output was
-    // cropped, the forward's lse there is unspecified); as KEY columns their dS / P mass is summed into column 49,
-    // so that row 49 of the dK / dV products is the gradient of k_pad / v_pad (rows 49+ of K, Q, dO tiles are zero).
+    // Per-pair state of this thread's row, fetched one pair AHEAD (in the idle window while phase 2 of the current pair
+    // runs): the lse read is a global load of about 1500 cycles under load.  Rows that must produce P = dS = 0 get
+    // lse = +inf: rows 49-63 of the tile, and the padding tokens as QUERY rows (un-padded mode; their output was
+    // cropped, the forward's lse there is unspecified).  As KEY columns the padding tokens have their dS / P mass
+    // summed into column 49, so that row 49 of the dK / dV products is the gradient of k_pad / v_pad (rows 49+ of the
+    // K, Q, dO tiles are zero).
     struct RowState {
       bool valid;
       uint64_t padded;
@@ -340,19 +372,16 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       if (y >= p.Hp) y -= p.Hp;
       if (x >= p.Wp) x -= p.Wp;
       s.padded = has_pad && s.valid ? pads.of(p, w.wy, w.wx) : 0;
-      s.lse = 0.f;
-      if (s.valid && row < N) s.lse = ((s.padded >> rowc) & 1) ? INFINITY : __ldg(&p.lse[((int64_t)(w.b * p.Hp + y) * p.Wp + x) * p.nH + h]);
+      s.lse = INFINITY;
+      if (s.valid && row < N && !((s.padded >> rowc) & 1)) s.lse = __ldg(&p.lse[((int64_t)(w.b * p.Hp + y) * p.Wp + x) * p.nH + h]);
       return s;
     };
-    RowState nxt = {false, 0, 0.f};
+    RowState nxt = {false, 0, INFINITY};
     if (g < n_pairs) nxt = fetch(it);
 
     int m = 0;
     for (int n = g; n < n_pairs; n += kSlotsB, ++m) {
       const RowState cur = nxt;
-      WinIter itn = it;
-      itn.advance(p, 2 * kSlotsB);
-      if (n + kSlotsB < n_pairs) nxt = fetch(itn);
       const bool valid = cur.valid;
       const uint64_t padded = cur.padded;
       const float lse2 = cur.lse * kLog2e;
@@ -363,7 +392,6 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       }
       const bool special = kShifted && (it.wy == p.nWy - 1 || it.wx == p.nWx - 1);   // warp-uniform
 
-      const bool tr = q == 0 && lane == 0;
       if (tr) TCB_TRACE(p, n, 7);                               // softmax: waiting for S / dP
       mbar_wait(bar_s + 8 * g, m & 1);
       tc_fence_after();
@@ -413,14 +441,13 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       }
       const float delta = fmaf(__uint_as_float(r[N - 1]), __uint_as_float(d[N - 1]), (acc.x + acc.y) + (acc_b.x + acc_b.y));
       const float2 nd = make_float2(-delta, -delta);
-      const bool live = valid && row < N;
       uint32_t wp[25], wd[25];
 #pragma unroll
       for (int e = 0; e < 24; ++e) {
         const float2 pp = make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]));
         const float2 ds = __fmul2_rn(pp, __fadd2_rn(make_float2(__uint_as_float(d[2 * e]), __uint_as_float(d[2 * e + 1])), nd));
-        wp[e] = live ? pack_bf16(pp.x, pp.y) : 0u;
-        wd[e] = live ? pack_bf16(ds.x, ds.y) : 0u;
+        wp[e] = pack_bf16(pp.x, pp.y);
+        wd[e] = pack_bf16(ds.x, ds.y);
       }
       {
         const float pl = __uint_as_float(r[N - 1]);
@@ -436,14 +463,16 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
             }
           }
         }
-        wp[24] = live ? pack_bf16(pl, u_pad) : 0u;
-        wd[24] = live ? pack_bf16(dl, s_pad) : 0u;
+        wp[24] = pack_bf16(pl, u_pad);
+        wd[24] = pack_bf16(dl, s_pad);
       }
-      // the TMA stores of this warpgroup's previous pair must have finished reading the staging tiles
-      // (same bytes as P / dS) before they are overwritten
+      if (!valid) {   // missing second tile of the job's last pair (warp-uniform): its stage bytes are not data
+#pragma unroll
+        for (int e = 0; e < 25; ++e) wp[e] = wd[e] = 0u;
+      }
       if (tr) TCB_TRACE(p, n, 10);                              // math done
-      if (issuer && elect_one()) bulk_wait_read();
-      named_barrier(1 + g, 128);
+      // the staging tiles of this slot (same bytes as P / dS) must have been read by the TMA stores of pair n - 2
+      mbar_wait(bar_f + 8 * g, (m & 1) ^ 1);
 #pragma unroll
       for (int ch = 0; ch < 8; ++ch) {
         const uint32_t off = (uint32_t)((ch ^ (row & 7)) << 4);
@@ -457,6 +486,11 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       tc_fence_before();
       mbar_arrive(bar_p + 8 * g);
       if (tr) TCB_TRACE(p, n, 11);                              // P / dS handed over
+
+      // idle window (phase 2 runs): state of this warpgroup's next pair
+      WinIter itn = it;
+      itn.advance(p, 2 * kSlotsB);
+      if (n + kSlotsB < n_pairs) nxt = fetch(itn);
 
       mbar_wait(bar_o + 8 * g, m & 1);
       tc_fence_after();
@@ -495,66 +529,66 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
         }
       }
       tc_fence_before();
-      mbar_arrive(bar_r + 8 * g);
+      mbar_arrive(bar_r + 8 * g);                               // TMEM slot free for phase 1 of pair n + 2
       if (tr) TCB_TRACE(p, n, 13);                              // outputs read, slot released
       fence_proxy_async();
-      named_barrier(1 + g, 128);
-      if (issuer && valid && elect_one()) {
-        const uint32_t src = sl + sel * kTileBytes;
-        move_window<kShifted, true>(maps.dq, src, 0, p, it.b, it.wy, it.wx, h);
-        move_window<kShifted, true>(maps.dk, src + 2 * kTileBytes, 0, p, it.b, it.wy, it.wx, h);
-        move_window<kShifted, true>(maps.dv, src + 4 * kTileBytes, 0, p, it.b, it.wy, it.wx, h);
-        bulk_commit();
-      }
-      __syncwarp();
-      if (tr) TCB_TRACE(p, n, 14);                              // stores issued
+      mbar_arrive(bar_g + 8 * g);                               // staged: the producers issue the TMA stores
       it = itn;
     }
-    if (tid == 128) TCB_TRACE(p, 239, 5);                         // warpgroup 0: last pair stored
-    if (issuer && elect_one()) bulk_wait_all();
+    if (tid == 128) TCB_TRACE(p, 239, 5);                       // warpgroup 0: last pair staged
 
     // ---- bias-table gradient: T[row i, col j] = sum over the job's windows of dS -------------------
-    // The phase-2 MMAs complete in issue order, so once the warpgroup that owns the LAST pair has seen its
-    // bar_o, T is final; a barrier over both warpgroups publishes that to warpgroup 0, which scatters.
-    named_barrier(3, 128 * kSlotsB);
+    // The phase-2 MMAs complete in issue order, so once the warpgroup that owns the LAST pair has seen its bar_o, T is
+    // final and every load has been consumed (the stage buffers are free); the barrier over both warpgroups publishes
+    // that, and every padacc update, to all 256 threads.
+    named_barrier(3, 256);
     if (tid == 128) TCB_TRACE(p, 239, 6);                         // both warpgroups done
-    if (g == 0 && n_pairs > 0) {
-      tc_fence_after();
-      uint32_t tr[N + 15];
-      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + kDtCol;
-      TMEM_LD_X16(t_addr, (tr + 0));
-      TMEM_LD_X16(t_addr + 16, (tr + 16));
-      TMEM_LD_X16(t_addr + 32, (tr + 32));
-      TMEM_LD_X1(t_addr + 48, tr[48]);
-      tmem_ld_wait();
-      // T rows -> shared memory [tile][row][49] (the stage buffers are free: every load was consumed by an MMA that has
-      // completed; lane stride 49 words, conflict-free), then one thread per bin sums the (7 - |di|)(7 - |dj|) entries
-      // of both tiles that share the relative position (di, dj).  (fp32 shared atomics are CAS loops: 49 per thread
-      // took 5 us per launch.)
+    if (n_pairs > 0) {
+      // T rows -> shared memory in WINDOW-TOKEN order [tile][query token][key token] (lane stride 49 words), then one
+      // thread per relative position (di, dj) sums the (7 - |di|)(7 - |dj|) entries of both tiles that share it:
+      // element ((ci+di)*7 + cj+dj, ci*7 + cj) = 49 (7 di + dj) + 350 ci + 50 cj.  (fp32 shared atomics are CAS loops:
+      // the 49-per-thread scatter of the first version took 5 us per launch.)
       float* ts = reinterpret_cast<float*>(smem + map.stages);
-      if (row < N) {
+      if (g == 0) {
+        tc_fence_after();
+        uint32_t tt[N + 15];
+        const uint32_t t_addr = lane_base + kDtCol;
+        TMEM_LD_X16(t_addr, (tt + 0));
+        TMEM_LD_X16(t_addr + 16, (tt + 16));
+        TMEM_LD_X16(t_addr + 32, (tt + 32));
+        TMEM_LD_X1(t_addr + 48, tt[48]);
+        tmem_ld_wait();
+        if (row < N) {
+          float* dst = ts + (sel * N + ri * WS + rj) * N;
 #pragma unroll
-        for (int j = 0; j < N; ++j) ts[(sel * N + row) * N + j] = __uint_as_float(tr[j]);
+          for (int j = 0; j < N; ++j) dst[row_i<kPerm>(j) * WS + row_j<kPerm>(j)] = __uint_as_float(tt[j]);
+        }
       }
-      named_barrier(4, 128);
-      for (int b = tid - 128; b < 169; b += 128) {
+      named_barrier(4, 256);
+      const int b = tid - 128;
+      if (b < 169) {
         const int di = b / 13 - 6, dj = b % 13 - 6;   // bin = (ri - ci + 6) * 13 + (rj - cj + 6)
-        float sum = 0.f;
-        for (int ci = max(0, -di); ci <= min(WS - 1, WS - 1 - di); ++ci)
-          for (int cj = max(0, -dj); cj <= min(WS - 1, WS - 1 - dj); ++cj) {
-            const int e = token_row<kPerm>(ci + di, cj + dj) * N + token_row<kPerm>(ci, cj);
-            sum += ts[e] + ts[N * N + e];
+        const float* src = ts + N * (WS * di + dj);
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int ci = 0; ci < WS; ++ci) {
+#pragma unroll
+          for (int cj = 0; cj < WS; ++cj) {
+            if ((unsigned)(ci + di) < (unsigned)WS && (unsigned)(cj + dj) < (unsigned)WS) {
+              s0 += src[350 * ci + 50 * cj];
+              s1 += src[N * N + 350 * ci + 50 * cj];
+            }
           }
-        atomicAdd(&p.d_table[b * p.nH + h], sum);
+        }
+        atomicAdd(&p.d_table[b * p.nH + h], s0 + s1);
       }
-      // (the named barrier over both warpgroups above also ordered every padacc update before these reads)
-      if (has_pad && tid - 128 < 64) {
-        float* dst = tid - 128 < 32 ? p.d_kpad : p.d_vpad;
-        const float* acc = reinterpret_cast<const float*>(smem + map.padacc) + (tid - 128);
+      if (has_pad && b < 64) {
+        float* dst = b < 32 ? p.d_kpad : p.d_vpad;
+        const float* acc = reinterpret_cast<const float*>(smem + map.padacc) + b;
         float sum = 0.f;
 #pragma unroll
         for (int i = 0; i < kSlotsB * 2; ++i) sum += acc[i * 64];
-        if (dst != nullptr) atomicAdd(&dst[h * kHeadDim + ((tid - 128) & 31)], sum);
+        if (dst != nullptr) atomicAdd(&dst[h * kHeadDim + (b & 31)], sum);
       }
       if (tid == 128) TCB_TRACE(p, 239, 7);                       // bias-table / pad-vector gradients added
     }

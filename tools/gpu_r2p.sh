@@ -4,7 +4,7 @@ set -x
 mkdir -p gpurun_out
 tag=${1:-r2p}
 rm -f gpurun_out/parity_errors.jsonl
-timeout 1200 python -m pytest tests -m gpu -x -q -rf -k "bwd or backward or grad or train or unpadded or no_alloc" 2>&1 | tail -12 > gpurun_out/pytest_$tag.log
+timeout 200 python -m pytest tests/test_parity_gpu.py -m gpu -x -q -k "bwd or backward" 2>&1 | tail -3; timeout 1200 python -m pytest tests -m gpu -x -q -rf -k "bwd or backward or grad or train or unpadded or no_alloc" 2>&1 | tail -12 > gpurun_out/pytest_$tag.log
 cat gpurun_out/pytest_$tag.log
 timeout 600 python tools/attn_microbench.py --impl auto --bwd > gpurun_out/micro_bwd_$tag.jsonl 2> gpurun_out/micro_bwd_$tag.err
 cut -c1-170 gpurun_out/micro_bwd_$tag.jsonl
