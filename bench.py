@@ -59,6 +59,8 @@ def parse():
                     help="training at N > 1: keep the eager DDP step; do not capture it (with its NCCL all-reduce) in a CUDA graph")
     ap.add_argument("--no-train-leg", action="store_true", help="default mode: skip the `train` extra key (BASELINE configs[2])")
     ap.add_argument("--no-reference-gpu", action="store_true", help="skip the `reference_gpu_eager` extra key")
+    ap.add_argument("--no-graph-timing", action="store_true",
+                    help="skip the instrumented CUDA-graph replays behind `roofline.graph_replay`")
     ap.add_argument("--bf16-grad-hook", action="store_true",
                     help="training at N > 1: DDP's bf16_compress_hook on the gradient buckets (halves the all-reduce bytes)")
     ap.add_argument("--version", default=VERSION)
@@ -231,6 +233,47 @@ def roofline_of(recs, name, steps, t_res, traffic):
                          for k, v in sorted(by_shape.items())}}
 
 
+def timed_graph_replays(ctx, build_graph, replay, steps):
+    """Launch times INSIDE a CUDA-graph replay: `build_graph()` captures an instrumented copy of the graph (every
+    attention / linear launch bracketed by two external event-record nodes, ops.capture_graph_timing), which is replayed
+    `steps` times with an L2 flush before each; returns (records of all replays, seconds of the replays)."""
+    from mde_b200 import ops
+    ops.capture_graph_timing(True)
+    try:
+        g = build_graph()
+    finally:
+        ops.capture_graph_timing(False)
+    recs, total = [], 0.0
+    try:
+        for i in range(steps + 1):                       # the first replay is a warm-up
+            ctx.flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            replay(g)
+            b.record()
+            torch.cuda.synchronize()
+            if i:
+                recs += [r for r in ops.read_graph_timing() if r[0] >= 0]
+                total += a.elapsed_time(b) / 1e3
+    finally:
+        del g
+        gc.collect()
+        ops.clear_graph_timing()
+    return recs, total
+
+
+def with_graph_timing(roof, recs, name, steps, t_graph, traffic):
+    """Adds the same roofline, timed inside the CUDA-graph replay, under `graph_replay` of an event-timed roofline."""
+    if roof is None or not recs:
+        return roof
+    g = roofline_of(recs, name, steps, t_graph, traffic)
+    if g:
+        roof["graph_replay"] = {k: g[k] for k in ("achieved", "frac", "launches", "kernel_ms_per_step", "share_of_step", "by_shape")}
+        roof["graph_replay"]["timed"] = ("external event-record nodes around each launch inside an instrumented copy of the step's "
+                                         "CUDA graph (no host launch gaps between the events and the kernel)")
+    return roof
+
+
 def roofline_linear_of(recs, steps, t_res):
     hbm, tf, which = peaks()
     if not recs:
@@ -351,11 +394,18 @@ def infer_leg(ctx):
         t_graph = ctx.timed_steps(lambda: graphed(images), args.steps)   # device-resident, the forward replayed as one graph
     ctx.barrier()
     sampler.stop()
+    graph_records, t_graph_timed = [], None
+    if graphed is not None and ctx.rank == 0 and not args.no_graph_timing:
+        try:
+            graph_records, t_graph_timed = timed_graph_replays(ctx, lambda: GraphedInference(model, images), lambda g: g(images), args.steps)
+        except Exception as e:
+            print(f"[bench] graph-replay launch timing skipped: {type(e).__name__}: {e}"[:300], file=sys.stderr)
+    ctx.barrier()
     t_res, t_e2e, t_graph, t_e2e_eager = ctx.max_over_ranks([t_res, t_e2e, t_graph, t_e2e_eager])
     n_img = args.batch * ctx.world * args.steps
     res = dict(t_res=t_res, t_e2e=t_e2e, t_graph=t_graph or None, t_e2e_eager=t_e2e_eager or None, records=records,
                launches=int(launches), clocks=sampler.summary(), h2d=host.numel() * 4, d2h=out_host.numel() * 4,
-               e2e_regions=[n_img / t for t in e2e_regions], n_img=n_img)
+               e2e_regions=[n_img / t for t in e2e_regions], n_img=n_img, graph_records=graph_records, t_graph_timed=t_graph_timed)
     del graphed, model, images
     gc.collect()
     torch.cuda.empty_cache()
@@ -430,11 +480,18 @@ def train_leg(ctx, steps, warmup):
             in_sync = replicas_in_sync(model)
     ctx.barrier()
     sampler.stop()
+    graph_records, t_graph_timed = [], None
+    if gstep is not None and world == 1 and not args.no_graph_timing:   # (one capture of the DDP step per process is enough risk)
+        try:
+            graph_records, t_graph_timed = timed_graph_replays(ctx, lambda: GraphedTrainStep(trainer, images, gt, warmup=2),
+                                                               lambda g: g(images, gt), steps)
+        except Exception as e:
+            print(f"[bench] graph-replay launch timing (train) skipped: {type(e).__name__}: {e}"[:300], file=sys.stderr)
     t_res, t_e2e, t_graph = ctx.max_over_ranks([t_res, t_e2e, t_graph])
     res = dict(t_res=t_res, t_e2e=t_e2e, t_graph=t_graph or None, records=records, launches=int(launches),
                clocks=sampler.summary(), h2d=host.numel() * 4 + gt_host.numel() * 4, d2h=4, in_sync=in_sync,
                graph_error=graph_error, graphed=gstep is not None, n_img=args.batch * world * steps, steps=steps,
-               bf16_grad_hook=bool(args.bf16_grad_hook and world > 1))
+               bf16_grad_hook=bool(args.bf16_grad_hook and world > 1), graph_records=graph_records, t_graph_timed=t_graph_timed)
     del gstep, trainer, model
     gc.collect()
     torch.cuda.empty_cache()
@@ -461,10 +518,14 @@ def train_summary(ctx, tr):
         "workload": f"NewCRFs {ctx.args.version} training step, batch {ctx.args.batch}/GPU, 3x480x640 NYU-shape synthetic images "
                     "and depth, torch.autocast(bf16), random-init weights",
         "gpu_launches": tr["launches"], "clocks": tr["clocks"],
-        "roofline_backward": roofline_of(bwd, "swin_attn backward (all window-attention backward launches of the step)",
-                                         tr["steps"], tr["t_res"], traffic),
-        "roofline_forward": roofline_of(fwd, "swin_attn forward (all window-attention forward launches of the step)",
-                                        tr["steps"], tr["t_res"], traffic),
+        "roofline_backward": with_graph_timing(
+            roofline_of(bwd, "swin_attn backward (all window-attention backward launches of the step)", tr["steps"], tr["t_res"], traffic),
+            [r for r in tr["graph_records"] if r[3][0] == "bwd"],
+            "swin_attn backward (all window-attention backward launches of the step)", tr["steps"], tr["t_graph_timed"], traffic),
+        "roofline_forward": with_graph_timing(
+            roofline_of(fwd, "swin_attn forward (all window-attention forward launches of the step)", tr["steps"], tr["t_res"], traffic),
+            [r for r in tr["graph_records"] if r[3][0] == "fwd"],
+            "swin_attn forward (all window-attention forward launches of the step)", tr["steps"], tr["t_graph_timed"], traffic),
     }
 
 
@@ -524,8 +585,10 @@ def run_ours(args, env):
             "e2e": {"value": n_img / inf["t_e2e"], "unit": "images/s", "h2d_bytes_per_step": inf["h2d"],
                     "d2h_bytes_per_step": inf["d2h"], "regions_images_per_s": inf["e2e_regions"]},
             "gpu_launches": inf["launches"], "clocks": inf["clocks"],
-            "roofline": roofline_of(fwd_recs, "swin_attn forward (all window-attention forward launches of the step)",
-                                    args.steps, t_res, traffic),
+            "roofline": with_graph_timing(
+                roofline_of(fwd_recs, "swin_attn forward (all window-attention forward launches of the step)", args.steps, t_res, traffic),
+                [r for r in inf["graph_records"] if r[3][0] == "fwd"],
+                "swin_attn forward (all window-attention forward launches of the step)", args.steps, inf["t_graph_timed"], traffic),
         }
         if inf["t_e2e_eager"]:
             line["e2e_eager"] = {"value": n_img / inf["t_e2e_eager"], "unit": "images/s",

@@ -174,10 +174,17 @@ struct TimedRegion {
   LaunchEvents ev;
   cudaStream_t st;
   explicit TimedRegion(cudaStream_t s) : ev(take_launch_events()), st(s) {
-    if (ev.start) cudaEventRecord(ev.start, st);
+    if (ev.start) record(ev.start);
   }
   ~TimedRegion() {
-    if (ev.stop) cudaEventRecord(ev.stop, st);
+    if (ev.stop) record(ev.stop);
+  }
+  // On a capturing stream the pair becomes two EXTERNAL event-record nodes of the graph: every replay re-records them,
+  // so the launch can be timed inside the CUDA-graph replay (cudaEventElapsedTime after the replay has finished).
+  void record(cudaEvent_t e) const {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(e, st, cudaEventRecordExternal);
+    else cudaEventRecord(e, st);
   }
   TimedRegion(const TimedRegion&) = delete;
   TimedRegion& operator=(const TimedRegion&) = delete;

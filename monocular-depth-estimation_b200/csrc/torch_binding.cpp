@@ -33,14 +33,23 @@ struct TimingRecord {
   int64_t tag[6];   // kind (0 fwd, 1 bwd), window, shift, heads, height, width
 };
 std::mutex g_timing_mutex;
-bool g_timing_on = false;
-std::vector<TimingRecord> g_records;
+// 0 off; 1 eager: every launch is bracketed, records are consumed by swin_torch_take_timing; 2 graph: only launches that
+// are being CAPTURED are bracketed (the library records the events as external event-record nodes of the graph), the
+// records persist with the graph and are read after every replay by swin_torch_read_graph_timing.
+int g_timing_on = 0;
+std::vector<TimingRecord> g_records, g_graph_records;
+
+inline bool stream_is_capturing(cudaStream_t st) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  return cudaStreamIsCapturing(st, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusActive;
+}
 
 struct TimedLaunch {
-  bool on;
+  bool on, graph;
   TimingRecord rec;
   cudaStream_t stream;
-  explicit TimedLaunch(cudaStream_t st) : on(g_timing_on), stream(st) {
+  explicit TimedLaunch(cudaStream_t st) : on(g_timing_on != 0), graph(g_timing_on == 2), stream(st) {
+    if (graph && !stream_is_capturing(st)) on = false;
     if (on) {
       cudaEventCreate(&rec.start);
       cudaEventCreate(&rec.stop);
@@ -56,7 +65,7 @@ struct TimedLaunch {
     const int64_t tag[6] = {kind, window, shift, heads, h, w};
     for (int i = 0; i < 6; ++i) rec.tag[i] = tag[i];
     std::lock_guard<std::mutex> lock(g_timing_mutex);
-    g_records.push_back(rec);
+    (graph ? g_graph_records : g_records).push_back(rec);
   }
 };
 
@@ -932,9 +941,45 @@ TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------
 extern "C" {
 
-void swin_torch_set_timing(int on) {
+void swin_torch_set_timing(int mode) {
   std::lock_guard<std::mutex> lock(g_timing_mutex);
-  g_timing_on = on != 0;
+  g_timing_on = mode;
+}
+
+// Graph mode: elapsed times of the event pairs captured into CUDA graphs, as recorded by the LAST replay (the caller
+// has synchronised).  Same layout as swin_torch_take_timing; the records stay.  Returns the number written.
+int swin_torch_read_graph_timing(double* ms, int64_t* meta, int cap) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  int n = 0;
+  for (auto& r : g_graph_records) {
+    if (n >= cap) break;
+    float t = 0.f;
+    if (cudaEventElapsedTime(&t, r.start, r.stop) != cudaSuccess) {
+      cudaGetLastError();
+      t = -1.f;
+    }
+    ms[n] = t;
+    meta[8 * n] = r.bytes;
+    meta[8 * n + 1] = r.flops;
+    for (int i = 0; i < 6; ++i) meta[8 * n + 2 + i] = r.tag[i];
+    ++n;
+  }
+  return n;
+}
+
+int swin_torch_graph_timing_count(void) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  return (int)g_graph_records.size();
+}
+
+// Forget the graph-mode records (their graphs must have been destroyed, or never be replayed again).
+void swin_torch_clear_graph_timing(void) {
+  std::lock_guard<std::mutex> lock(g_timing_mutex);
+  for (auto& r : g_graph_records) {
+    cudaEventDestroy(r.start);
+    cudaEventDestroy(r.stop);
+  }
+  g_graph_records.clear();
 }
 
 // Synchronises on the recorded events and moves up to `cap` records out: ms[i], meta[8 i .. 8 i + 7] =

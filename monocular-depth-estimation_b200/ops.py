@@ -41,6 +41,10 @@ def _load_ops():
     lib.swin_torch_take_timing.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
     lib.swin_torch_take_timing.restype = ctypes.c_int
     lib.swin_torch_pending_timing.restype = ctypes.c_int
+    lib.swin_torch_read_graph_timing.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64), ctypes.c_int]
+    lib.swin_torch_read_graph_timing.restype = ctypes.c_int
+    lib.swin_torch_graph_timing_count.restype = ctypes.c_int
+    lib.swin_torch_clear_graph_timing.restype = None
     return lib
 
 
@@ -68,6 +72,32 @@ def set_kernel_timing(records):
     else:
         _kernel_timing = records
         _torch_lib.swin_torch_set_timing(1)
+
+
+def capture_graph_timing(on: bool):
+    """Graph mode of the per-launch timing (bench.py): while on, every attention / linear launch that is being CAPTURED
+    into a CUDA graph is bracketed by two external event-record nodes of that graph (eager launches are not timed).
+    After each replay has finished, ``read_graph_timing()`` returns the launches' times inside that replay."""
+    _torch_lib.swin_torch_set_timing(2 if on else 0)
+
+
+def read_graph_timing():
+    """Records of the instrumented graphs, as timed by their LAST replay (synchronise first): same tuples as
+    ``set_kernel_timing``; a pair whose events were not recorded yet has ms = -1."""
+    n = _torch_lib.swin_torch_graph_timing_count()
+    ms = (ctypes.c_double * max(n, 1))()
+    meta = (ctypes.c_int64 * (8 * max(n, 1)))()
+    n = _torch_lib.swin_torch_read_graph_timing(ms, meta, n)
+    out = []
+    for i in range(n):
+        m = meta[8 * i:8 * i + 8]
+        out.append((ms[i], m[0], m[1], (("fwd", "bwd", "lin")[m[2]],) + tuple(m[3:8])))
+    return out
+
+
+def clear_graph_timing():
+    """Drop the graph-mode records (destroy their instrumented graphs first, or never replay them again)."""
+    _torch_lib.swin_torch_clear_graph_timing()
 
 
 def _ptr(t: Optional[Tensor]):
