@@ -23,6 +23,7 @@ from the product package (no product ``.so`` is loaded in that process).
 from __future__ import annotations
 
 import argparse
+import ctypes
 import gc
 import json
 import os
@@ -225,7 +226,7 @@ def roofline_of(recs, name, steps, t_res, traffic):
             "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
             "traffic": (traffic.get(name.split()[1]) or {}).get("dram_bytes_per_launch"),
             "traffic_of": traffic.get(name.split()[1]),
-            "launches": len(recs), "kernel_ms_per_step": k_ms / steps, "share_of_step": k_ms / 1e3 / t_res,
+            "launches": len(recs), "_steps": steps, "kernel_ms_per_step": k_ms / steps, "share_of_step": k_ms / 1e3 / t_res,
             "useful_tflops": k_flops / (k_ms * 1e-3) / 1e12,
             "tensor_frac_of_sustained_bf16": k_flops / (k_ms * 1e-3) / 1e12 / tf,
             "by_shape": {k: {"launches": len(v), "us_per_launch": sum(r[0] for r in v) / len(v) * 1e3,
@@ -262,12 +263,36 @@ def timed_graph_replays(ctx, build_graph, replay, steps):
     return recs, total
 
 
+def with_bracket_probe(roof, with_memset):
+    """Adds what the event bracket costs around an EMPTY kernel (measured now, same stream; the backward's bracket also
+    holds its memset) and the fraction net of that fixed cost.  `frac` stays the plain event-timed figure."""
+    if roof is None:
+        return roof
+    from mde_b200 import _lib
+    us = _lib.load().swin_attn_probe_empty_bracket_us(ctypes.c_void_p(torch.cuda.current_stream().cuda_stream), int(with_memset), 20)
+    if us > 0:
+        net_ms = roof["kernel_ms_per_step"] - us * 1e-3 * roof["launches"] / roof["_steps"]
+        roof["empty_kernel_bracket_us"] = us
+        roof["empty_kernel_bracket_note"] = ("median event bracket around an EMPTY 148x384 kernel" + (" preceded by the backward's memset" if with_memset else "")
+                                             + " that follows a running kernel (swin_attn_probe_empty_bracket_us, measured in this run): "
+                                             "event records, launch latency and completion -- the fixed cost inside every us_per_launch")
+        if net_ms > 0:
+            roof["frac_net_of_empty_bracket"] = roof["frac"] * roof["kernel_ms_per_step"] / net_ms
+    roof.pop("_steps", None)
+    return roof
+
+
+def with_bracket_probe_of(recs, with_memset, name, steps, t_res, traffic):
+    return with_bracket_probe(roofline_of(recs, name, steps, t_res, traffic), with_memset)
+
+
 def with_graph_timing(roof, recs, name, steps, t_graph, traffic):
     """Adds the same roofline, timed inside the CUDA-graph replay, under `graph_replay` of an event-timed roofline."""
     if roof is None or not recs:
         return roof
     g = roofline_of(recs, name, steps, t_graph, traffic)
     if g:
+        g.pop("_steps", None)
         roof["graph_replay"] = {k: g[k] for k in ("achieved", "frac", "launches", "kernel_ms_per_step", "share_of_step", "by_shape")}
         roof["graph_replay"]["timed"] = ("external event-record nodes around each launch inside an instrumented copy of the step's "
                                          "CUDA graph (no host launch gaps between the events and the kernel)")
@@ -519,11 +544,11 @@ def train_summary(ctx, tr):
                     "and depth, torch.autocast(bf16), random-init weights",
         "gpu_launches": tr["launches"], "clocks": tr["clocks"],
         "roofline_backward": with_graph_timing(
-            roofline_of(bwd, "swin_attn backward (all window-attention backward launches of the step)", tr["steps"], tr["t_res"], traffic),
+            with_bracket_probe_of(bwd, True, "swin_attn backward (all window-attention backward launches of the step)", tr["steps"], tr["t_res"], traffic),
             [r for r in tr["graph_records"] if r[3][0] == "bwd"],
             "swin_attn backward (all window-attention backward launches of the step)", tr["steps"], tr["t_graph_timed"], traffic),
         "roofline_forward": with_graph_timing(
-            roofline_of(fwd, "swin_attn forward (all window-attention forward launches of the step)", tr["steps"], tr["t_res"], traffic),
+            with_bracket_probe_of(fwd, False, "swin_attn forward (all window-attention forward launches of the step)", tr["steps"], tr["t_res"], traffic),
             [r for r in tr["graph_records"] if r[3][0] == "fwd"],
             "swin_attn forward (all window-attention forward launches of the step)", tr["steps"], tr["t_graph_timed"], traffic),
     }
@@ -586,7 +611,7 @@ def run_ours(args, env):
                     "d2h_bytes_per_step": inf["d2h"], "regions_images_per_s": inf["e2e_regions"]},
             "gpu_launches": inf["launches"], "clocks": inf["clocks"],
             "roofline": with_graph_timing(
-                roofline_of(fwd_recs, "swin_attn forward (all window-attention forward launches of the step)", args.steps, t_res, traffic),
+                with_bracket_probe_of(fwd_recs, False, "swin_attn forward (all window-attention forward launches of the step)", args.steps, t_res, traffic),
                 [r for r in inf["graph_records"] if r[3][0] == "fwd"],
                 "swin_attn forward (all window-attention forward launches of the step)", args.steps, inf["t_graph_timed"], traffic),
         }

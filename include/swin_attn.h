@@ -238,6 +238,13 @@ int swin_patch_merge_layernorm_forward(const void* x, int32_t x_dtype, const flo
  * the reference, which has no timing of its own; used by bench.py's live roofline.) */
 void swin_attn_time_next_launch(void* start_event, void* stop_event);
 
+/* Measurement probe: median, in microseconds, of `reps` event brackets (as armed by swin_attn_time_next_launch) around an
+ * EMPTY 148 x 384 kernel that follows a running kernel in `stream`, with (with_memset != 0) or without the backward's
+ * memset in front of it: the fixed cost every event-timed attention launch carries (about 5 us / 8 us on a B200).
+ * Allocates and frees a 32 MB scratch buffer; < 0 on a CUDA error.  (No counterpart in the reference; used by bench.py,
+ * which reports it next to the roofline.) */
+double swin_attn_probe_empty_bracket_us(void* stream, int32_t with_memset, int32_t reps);
+
 /* Number of kernel launches issued by this library since load (all threads). */
 uint64_t swin_attn_launch_count(void);
 

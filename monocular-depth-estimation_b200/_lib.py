@@ -37,6 +37,7 @@ EXPORTS = (
     "swin_linear_gelu_forward_train",
     "swin_linear_bias_grad",
     "swin_attn_time_next_launch",
+    "swin_attn_probe_empty_bracket_us",
     "swin_attn_launch_count",
     "swin_attn_uses_tcgen05",
     "swin_attn_last_error",
@@ -105,6 +106,8 @@ def load() -> ctypes.CDLL:
     lib.swin_patch_merge_layernorm_forward.restype = c_int
     lib.swin_attn_time_next_launch.argtypes = [vp, vp]
     lib.swin_attn_time_next_launch.restype = None
+    lib.swin_attn_probe_empty_bracket_us.argtypes = [vp, c_int32, c_int32]
+    lib.swin_attn_probe_empty_bracket_us.restype = ctypes.c_double
     lib.swin_attn_launch_count.argtypes = []
     lib.swin_attn_launch_count.restype = c_uint64
     lib.swin_attn_uses_tcgen05.argtypes = [POINTER(Shape), c_int]

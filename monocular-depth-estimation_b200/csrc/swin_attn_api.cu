@@ -1,10 +1,12 @@
 // C ABI of libswin_attn.so (see include/swin_attn.h): argument checking,
 // dispatch between the tcgen05 and the CUDA-core kernels, host-buffer entry.
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "swin_common.cuh"
 
@@ -476,6 +478,53 @@ int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int3
 void swin_linear_debug_set_pair_mode(int mode) { set_tc_linear_pair_mode(mode); }
 
 void swin_attn_debug_set_trace(void* device_buffer) { g_trace = static_cast<long long*>(device_buffer); }
+
+// Measurement probe (bench.py): what the event bracket of swin_attn_time_next_launch costs around an EMPTY kernel that
+// follows other work in the stream -- event record, launch latency of a 148 x 384 grid, completion, event record --
+// optionally with the backward's memset in front.  Median of `reps` brackets in microseconds, < 0 on a CUDA error.
+// The attention launches' event-timed durations carry this fixed cost; it is reported next to the roofline.
+namespace {
+__global__ void probe_empty_kernel(int* sink) {
+  if (sink != nullptr && threadIdx.x == 1u << 20) sink[0] = 1;
+}
+__global__ void probe_busy_kernel(float* p, size_t n) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = 1.f;
+}
+}  // namespace
+
+double swin_attn_probe_empty_bracket_us(void* stream, int with_memset, int reps) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (reps < 1) reps = 1;
+  float* busy = nullptr;
+  const size_t n_busy = (size_t)8 << 20;
+  cudaEvent_t a = nullptr, b = nullptr;
+  if (cudaMalloc(&busy, n_busy * sizeof(float)) != cudaSuccess || cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) {
+    cudaGetLastError();
+    cudaFree(busy);
+    return -1.0;
+  }
+  std::vector<float> us;
+  bool ok = true;
+  for (int i = 0; i < reps + 2 && ok; ++i) {
+    probe_busy_kernel<<<148 * 4, 256, 0, st>>>(busy, n_busy);   // the bracket follows a running kernel, as in a model step
+    cudaEventRecord(a, st);
+    if (with_memset) cudaMemsetAsync(busy, 0, 20480, st);
+    probe_empty_kernel<<<148, 384, 0, st>>>(nullptr);
+    cudaEventRecord(b, st);
+    ok = cudaStreamSynchronize(st) == cudaSuccess;
+    float ms = 0.f;
+    if (ok && cudaEventElapsedTime(&ms, a, b) == cudaSuccess && i >= 2) us.push_back(ms * 1e3f);
+  }
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  cudaFree(busy);
+  if (!ok || us.empty()) {
+    cudaGetLastError();
+    return -1.0;
+  }
+  std::sort(us.begin(), us.end());
+  return us[us.size() / 2];
+}
 
 void swin_attn_time_next_launch(void* start_event, void* stop_event) {
   g_launch_events.start = static_cast<cudaEvent_t>(start_event);
