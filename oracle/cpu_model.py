@@ -15,7 +15,7 @@ import copy
 import torch
 
 import mde_b200
-from mde_b200 import layers
+from mde_b200 import layers, siblings
 
 from .window_attention import partition, unpartition, window_attention
 
@@ -78,7 +78,33 @@ class OracleEncoderWindowAttention(layers.EncoderWindowAttention):
         return o
 
 
-_SWAP = {layers.WindowAttention: OracleWindowAttention, layers.EncoderWindowAttention: OracleEncoderWindowAttention}
+def _split3(qkv, c):
+    return qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:]
+
+
+class OracleOda2WindowAttention(siblings.Oda2WindowAttention):
+    """model/ODA2/oda2_swin_transformer.py:150-183 (windows) and :254-288 (replicate pad, roll, partition ... crop)."""
+
+    scale = property(lambda self: self.attn_scale)
+
+    def attend_windows(self, qkv_windows, mask):
+        return _windows_forward(self, *_split3(qkv_windows, self.dim), mask)
+
+    def attend_image(self, y_img, shift):
+        o, _ = window_attention(*_split3(self.qkv(y_img), self.dim), self.relative_position_bias_table, self.window_size[0], shift,
+                                self.num_heads, self.attn_scale, pad_mode="replicate")
+        return o
+
+
+class OracleOdaWindowAttention(OracleEncoderWindowAttention, siblings.OdaWindowAttention):
+    """timm WindowAttention inside model/ODA/oda_swin_transformer.py:123-160 (window-aligned grids only)."""
+
+    def attend_windows(self, qkv_windows, mask):
+        return _windows_forward(self, *_split3(qkv_windows, self.dim), mask)
+
+
+_SWAP = {layers.WindowAttention: OracleWindowAttention, layers.EncoderWindowAttention: OracleEncoderWindowAttention,
+         siblings.Oda2WindowAttention: OracleOda2WindowAttention, siblings.OdaWindowAttention: OracleOdaWindowAttention}
 
 
 def to_oracle(module: torch.nn.Module, device="cpu") -> torch.nn.Module:

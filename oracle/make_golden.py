@@ -59,6 +59,31 @@ def swin_block(name, ws, shift, b, h, w, c, nh):
                 out=out.detach(), cot=cot, dx=gs[0], dtable=gs[1], dqkv_w=gs[2], dqkv_b=gs[3])
 
 
+def oda2_stage(name, ws, b, h, w, c, nh):
+    """model/ODA2 SwinTransformerStage (depth 2: un-shifted + shifted block, replicate padding, mask built per forward)."""
+    S = rs.oda2_swin_transformer()
+    st = S.SwinTransformerStage(dim=c, depth=2, num_heads=nh, window_size=ws).eval()
+    st.load_state_dict(synthetic_state(st))
+    x = randn(name + ".x", b, h * w, c).requires_grad_()
+    out = st(x, h, w)[0]
+    a0, a1 = st.blocks[0].attn, st.blocks[1].attn
+    cot, gs = _grads(out, [x, a0.relative_position_bias_table, a1.relative_position_bias_table, a1.qkv.weight, a1.qkv.bias], name)
+    return dict(kind="oda2_stage", cfg=dict(ws=ws, b=b, h=h, w=w, c=c, nh=nh), x=x.detach(), out=out.detach(), cot=cot,
+                dx=gs[0], dtable0=gs[1], dtable1=gs[2], dqkv_w1=gs[3], dqkv_b1=gs[4])
+
+
+def oda_block(name, ws, shift, b, h, w, c, nh):
+    """model/ODA SwinTransformerBlock (timm block, fixed input_resolution, attn_mask buffer)."""
+    S = rs.oda_swin_transformer()
+    blk = S.SwinTransformerBlock(c, (h, w), nh, window_size=ws, shift_size=shift).eval()
+    blk.load_state_dict(synthetic_state(blk))
+    x = randn(name + ".x", b, h * w, c).requires_grad_()
+    out = blk(x)
+    cot, gs = _grads(out, [x, blk.attn.relative_position_bias_table, blk.attn.qkv.weight, blk.attn.qkv.bias], name)
+    return dict(kind="oda_block", cfg=dict(ws=ws, shift=shift, b=b, h=h, w=w, c=c, nh=nh), x=x.detach(), out=out.detach(),
+                cot=cot, dx=gs[0], dtable=gs[1], dqkv_w=gs[2], dqkv_b=gs[3])
+
+
 def masked_windows(name, ws, nw, groups, c, nh):
     """WindowAttention.forward(x, v, mask) on window-order tokens with an arbitrary mask."""
     L = rs.newcrf_layers()
@@ -167,6 +192,10 @@ CASES = {
     "swin_block_ws12_s6": lambda n: swin_block(n, 12, 6, 1, 13, 25, 64, 2),
     "swin_block_ws12_s0": lambda n: swin_block(n, 12, 0, 1, 24, 12, 64, 2),
     "masked_windows_ws7": lambda n: masked_windows(n, 7, 4, 2, 64, 2),
+    "oda2_stage_ws7_replicate": lambda n: oda2_stage(n, 7, 2, 16, 23, 96, 3),
+    "oda_block_ws12_s6": lambda n: oda_block(n, 12, 6, 1, 24, 36, 64, 2),
+    "oda_block_ws12_s0": lambda n: oda_block(n, 12, 0, 1, 24, 24, 64, 2),
+    "oda_block_ws7_s3": lambda n: oda_block(n, 7, 3, 2, 14, 21, 96, 3),
     "newcrf_level": lambda n: newcrf_level(n, 1, 10, 13, 48, 64, 32, 2),
     "newcrfdepth_tiny07": lambda n: full_model(n, "tiny07", 1, 64, 96),
     # metrics only (same image / weights as newcrfdepth_tiny07; adds the realistic-range GT)

@@ -108,6 +108,7 @@ def install() -> None:
         layers.DropPath, layers.to_2tuple, layers.trunc_normal_ = _DropPath, _to_2tuple, _trunc_normal_
         timm.models, models.layers = models, layers
         sys.modules.update({"timm": timm, "timm.models": models, "timm.models.layers": layers})
+        _install_timm_swin(models, layers)
     if "mmcv" not in sys.modules:
         mmcv = types.ModuleType("mmcv")
         cnn = types.ModuleType("mmcv.cnn")
@@ -118,6 +119,54 @@ def install() -> None:
         sys.modules.update({"mmcv": mmcv, "mmcv.cnn": cnn, "mmcv.utils": utils})
     if REFERENCE_ROOT not in sys.path:
         sys.path.insert(0, REFERENCE_ROOT)
+
+
+def _install_timm_swin(models, layers) -> None:
+    """What ``model/ODA/oda_swin_transformer.py:22-26`` imports from timm 0.5.4.  ``window_partition``, ``window_reverse``,
+    ``WindowAttention`` and ``Mlp`` of timm's ``swin_transformer.py`` are the published Swin algorithm (Liu et al. 2021,
+    microsoft/Swin-Transformer) that the reference ALSO carries in its own ``model/NewCRFs/swin_transformer.py:11-144``:
+    the stand-ins are those reference classes (same constructor keywords, same parameter names), resolved lazily because
+    the NewCRFs module imports ``timm.models.layers`` itself.  The other names are only touched by code paths no fixture
+    runs (model builders, checkpoint filters) and are inert placeholders."""
+    fx = types.ModuleType("timm.models.fx_features")
+    fx.register_notrace_function = lambda f: f
+    vit = types.ModuleType("timm.models.vision_transformer")
+    vit.checkpoint_filter_fn = lambda state_dict, model: state_dict
+    vit._init_vit_weights = lambda *a, **k: None
+    swin = types.ModuleType("timm.models.swin_transformer")
+
+    def _lazy(name):
+        def get(*a, **k):
+            import importlib
+            return getattr(importlib.import_module("model.NewCRFs.swin_transformer"), name)(*a, **k)
+        return get
+
+    class _LazyClass:
+        """Class stand-in whose construction is forwarded to the reference's NewCRFs Swin class of the same name."""
+
+        def __init__(self, name):
+            self._name = name
+
+        def __call__(self, *a, **k):
+            return _lazy(self._name)(*a, **k)
+
+    swin.window_partition, swin.window_reverse = _lazy("window_partition"), _lazy("window_reverse")
+    swin.WindowAttention, swin.PatchMerging = _LazyClass("WindowAttention"), _LazyClass("PatchMerging")
+    layers.Mlp, layers.PatchEmbed = _LazyClass("Mlp"), _LazyClass("PatchEmbed")
+    models.fx_features, models.vision_transformer, models.swin_transformer = fx, vit, swin
+    sys.modules.update({"timm.models.fx_features": fx, "timm.models.vision_transformer": vit, "timm.models.swin_transformer": swin})
+
+
+def oda_swin_transformer():
+    install()
+    import importlib
+    return importlib.import_module("model.ODA.oda_swin_transformer")
+
+
+def oda2_swin_transformer():
+    install()
+    import importlib
+    return importlib.import_module("model.ODA2.oda2_swin_transformer")
 
 
 def newcrf_layers():

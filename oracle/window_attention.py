@@ -69,7 +69,7 @@ def shift_mask(hp: int, wp: int, ws: int, shift: int, dtype=torch.float32, devic
     return torch.where(diff != 0, torch.full_like(diff, -100.0), torch.zeros_like(diff))
 
 
-def _pad_to_window(x: torch.Tensor, ws: int, fill: Optional[torch.Tensor]) -> torch.Tensor:
+def _pad_to_window(x: torch.Tensor, ws: int, fill: Optional[torch.Tensor], mode: str = "constant") -> torch.Tensor:
     """Right/bottom pad to a multiple of ws (newcrf_layers.py:212-217).
 
     The reference pads the *pre-Linear* tensor with zeros, so a pad token's
@@ -81,6 +81,8 @@ def _pad_to_window(x: torch.Tensor, ws: int, fill: Optional[torch.Tensor]) -> to
     pb, pr = (-h) % ws, (-w) % ws
     if pb == 0 and pr == 0:
         return x
+    if mode == "replicate":   # model/ODA2/oda2_swin_transformer.py:12,254-258: pad tokens copy the edge tokens
+        return F.pad(x, (0, 0, 0, pr, 0, pb), mode="replicate")
     out = F.pad(x, (0, 0, 0, pr, 0, pb))
     if fill is not None:
         out[:, h:, :, :] = fill
@@ -101,6 +103,7 @@ def window_attention(
     k_pad: Optional[torch.Tensor] = None,
     v_pad: Optional[torch.Tensor] = None,
     drop_scale: Optional[torch.Tensor] = None,
+    pad_mode: str = "constant",
 ) -> Tuple[torch.Tensor, torch.Tensor]:
     """Shifted-window multi-head attention on image-order tensors.
 
@@ -122,9 +125,9 @@ def window_attention(
     if scale is None:
         scale = hd ** -0.5
     n = ws * ws
-    qp = _pad_to_window(q, ws, q_pad)
-    kp = _pad_to_window(k, ws, k_pad)
-    vp = _pad_to_window(v, ws, v_pad)
+    qp = _pad_to_window(q, ws, q_pad, pad_mode)   # pad_mode="replicate": the ODA2 Swin (the pad vectors are unused)
+    kp = _pad_to_window(k, ws, k_pad, pad_mode)
+    vp = _pad_to_window(v, ws, v_pad, pad_mode)
     hp, wp = qp.shape[1], qp.shape[2]
     if shift > 0:
         qp, kp, vp = (torch.roll(t, shifts=(-shift, -shift), dims=(1, 2)) for t in (qp, kp, vp))

@@ -1,0 +1,103 @@
+"""SURVEY §8f row 3, GPU side: the ODA2 (replicate padding) and ODA (timm block, fixed attn_mask buffer, window 12) Swin
+blocks over the CUDA kernels, against fixtures generated from the reference modules.  fp32 <= 1e-5, bf16 autocast <= 1e-2
+(max-normalised); the bias-table gradient in bf16 is bounded like the NewCRFs blocks' (1.5e-2, tests/test_parity_gpu.py)."""
+import pytest
+import torch
+
+from mde_b200 import _lib, siblings
+from conftest import check, rel_err
+from test_siblings_cpu import oda2_stage_from_golden, oda_block_from_golden
+
+DEV = "cuda"
+TOL_F32, TOL_BF16 = 1e-5, 1e-2
+
+
+@pytest.mark.gpu
+def test_oda2_stage_fp32_vs_reference_golden(golden):
+    g = golden("oda2_stage_ws7_replicate")
+    cfg = g["cfg"]
+    st = oda2_stage_from_golden(g).to(DEV)
+    x = g["x"].to(DEV).requires_grad_()
+    out = st(x, cfg["h"], cfg["w"])[0]
+    check(rel_err(out, g["out"]), TOL_F32, "oda2 stage fp32 out")
+    a0, a1 = st.blocks[0].attn, st.blocks[1].attn
+    gs = torch.autograd.grad((out * g["cot"].to(DEV)).sum(), [x, a0.relative_position_bias_table, a1.relative_position_bias_table,
+                                                             a1.qkv.weight, a1.qkv.bias])
+    for got, key in zip(gs, ["dx", "dtable0", "dtable1", "dqkv_w1", "dqkv_b1"]):
+        check(rel_err(got, g[key]), TOL_F32, f"oda2 stage fp32 {key}")
+
+
+@pytest.mark.gpu
+def test_oda2_stage_bf16_autocast_vs_reference_golden(golden):
+    g = golden("oda2_stage_ws7_replicate")
+    cfg = g["cfg"]
+    st = oda2_stage_from_golden(g).to(DEV)
+    x = g["x"].to(DEV).requires_grad_()
+    launches = _lib.launch_count()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = st(x, cfg["h"], cfg["w"])[0]
+    assert _lib.launch_count() > launches                # the library's kernels ran
+    check(rel_err(out.float(), g["out"]), TOL_BF16, "oda2 stage bf16 out")
+    dx, dt0, dt1 = torch.autograd.grad((out.float() * g["cot"].to(DEV)).sum(),
+                                       [x, st.blocks[0].attn.relative_position_bias_table, st.blocks[1].attn.relative_position_bias_table])
+    check(rel_err(dx, g["dx"]), TOL_BF16, "oda2 stage bf16 dx")
+    check(rel_err(dt0, g["dtable0"]), 1.5 * TOL_BF16, "oda2 stage bf16 dtable0")
+    check(rel_err(dt1, g["dtable1"]), 1.5 * TOL_BF16, "oda2 stage bf16 dtable1")
+
+
+@pytest.mark.gpu
+def test_oda2_block_explicit_mask_path_equals_the_analytic_one(golden):
+    g = golden("oda2_stage_ws7_replicate")
+    cfg = g["cfg"]
+    st = oda2_stage_from_golden(g).to(DEV)
+    h, w, ws = cfg["h"], cfg["w"], cfg["ws"]
+    hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
+    blk = st.blocks[1]
+    blk.H, blk.W = h, w
+    x = g["x"].to(DEV)
+    std = siblings.sw_msa_mask(hp, wp, ws, ws // 2, device=DEV)
+    with torch.no_grad():
+        a = blk(x, std)
+        other = std.clone()
+        other[0, 0, 1] = -100.0
+        assert rel_err(blk(x, other), a) > 1e-7
+        other[0, 0, 1] = 0.0                             # same values again, but a tensor the block has not verified yet
+        blk._mask_check._seen.clear()
+        hit_explicit = blk._mask_check.is_standard                                  # force the explicit path once
+        blk._mask_check.is_standard = lambda *a_, **k_: False
+        d = blk(x, other)
+        blk._mask_check.is_standard = hit_explicit
+    check(rel_err(d, a), TOL_F32, "oda2 block explicit-mask path vs analytic")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["oda_block_ws12_s6", "oda_block_ws12_s0", "oda_block_ws7_s3"])
+def test_oda_block_fp32_vs_reference_golden(golden, name):
+    g = golden(name)
+    blk = oda_block_from_golden(g).to(DEV)
+    x = g["x"].to(DEV).requires_grad_()
+    out = blk(x)
+    check(rel_err(out, g["out"]), TOL_F32, f"{name} fp32 out")
+    a = blk.attn
+    gs = torch.autograd.grad((out * g["cot"].to(DEV)).sum(), [x, a.relative_position_bias_table, a.qkv.weight, a.qkv.bias])
+    for got, key in zip(gs, ["dx", "dtable", "dqkv_w", "dqkv_b"]):
+        check(rel_err(got, g[key]), TOL_F32, f"{name} fp32 {key}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["oda_block_ws12_s6", "oda_block_ws12_s0", "oda_block_ws7_s3"])
+def test_oda_block_bf16_autocast_vs_reference_golden(golden, name):
+    g = golden(name)
+    blk = oda_block_from_golden(g).to(DEV)
+    x = g["x"].to(DEV).requires_grad_()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = blk(x)
+    check(rel_err(out.float(), g["out"]), TOL_BF16, f"{name} bf16 out")
+    dx, dt = torch.autograd.grad((out.float() * g["cot"].to(DEV)).sum(), [x, blk.attn.relative_position_bias_table])
+    check(rel_err(dx, g["dx"]), TOL_BF16, f"{name} bf16 dx")
+    check(rel_err(dt, g["dtable"]), 1.5 * TOL_BF16, f"{name} bf16 dtable")
+    # a caller that overwrites the buffer gets the explicit-mask form of the op with ITS mask
+    if g["cfg"]["shift"]:
+        blk.attn_mask = torch.zeros_like(blk.attn_mask)
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            assert rel_err(blk(x).float(), out.float()) > 1e-4
