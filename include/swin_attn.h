@@ -238,6 +238,23 @@ int swin_patch_merge_layernorm_forward(const void* x, int32_t x_dtype, const flo
  * the reference, which has no timing of its own; used by bench.py's live roofline.) */
 void swin_attn_time_next_launch(void* start_event, void* stop_event);
 
+/* Global (un-windowed) multi-head attention that returns its attention map: the core of the Depthformer decoder's
+ * SelfAttentionBlock / PostNormSelfAttentionBlock (model/Depthformer/self_attention.py:70-80, :148-158):
+ *     attn = softmax(q k^T * scale) over the last axis, (batch, num_heads, seq, seq) fp32, written to attn_map when non-NULL;
+ *     o    = attn v, (batch, seq, num_heads * v_head_dim) in `dtype`.
+ * q, k: (batch, seq, num_heads * qk_head_dim), v: (batch, seq, num_heads * v_head_dim), head h at channel offset h * head_dim
+ * (what `_reshape_qkv`, :36-40, views), rows `*_row_stride` elements apart (slices of a packed projection are fine).
+ * fp32 math on the CUDA cores for both dtypes (the fp32 mode must hold 1e-5); attention dropout is not applied (the
+ * reference returns the un-dropped map; callers that train with attn_drop_prob > 0 apply it to attn_map themselves).
+ * Limits: head dims <= 64, seq <= 1664 (a 32-row block of logits lives in shared memory). */
+typedef struct {
+  int32_t batch, seq, num_heads, qk_head_dim, v_head_dim, dtype;
+  float scale;
+  int32_t reserved;
+  int64_t q_row_stride, k_row_stride, v_row_stride, o_row_stride;
+} mha_shape_t;
+int mha_attention_forward(const mha_shape_t* shape, const void* q, const void* k, const void* v, void* o, float* attn_map, void* stream);
+
 /* Measurement probe: median, in microseconds, of `reps` event brackets (as armed by swin_attn_time_next_launch) around an
  * EMPTY 148 x 384 kernel that follows a running kernel in `stream`, with (with_memset != 0) or without the backward's
  * memset in front of it: the fixed cost every event-timed attention launch carries (about 5 us / 8 us on a B200).

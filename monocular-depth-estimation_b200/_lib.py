@@ -36,6 +36,7 @@ EXPORTS = (
     "swin_linear_residual_forward",
     "swin_linear_gelu_forward_train",
     "swin_linear_bias_grad",
+    "mha_attention_forward",
     "swin_attn_time_next_launch",
     "swin_attn_probe_empty_bracket_us",
     "swin_attn_launch_count",
@@ -54,6 +55,16 @@ class Shape(Structure):
         ("scale", c_float), ("dropout_p", c_float), ("seed", c_uint64),
         ("q_pix_stride", c_int64), ("k_pix_stride", c_int64), ("v_pix_stride", c_int64), ("o_pix_stride", c_int64),
         ("mask_windows", c_int32), ("reserved", c_int32),
+    ]
+
+
+class MhaShape(Structure):
+    """Mirror of ``mha_shape_t``."""
+
+    _fields_ = [
+        ("batch", c_int32), ("seq", c_int32), ("num_heads", c_int32), ("qk_head_dim", c_int32), ("v_head_dim", c_int32),
+        ("dtype", c_int32), ("scale", c_float), ("reserved", c_int32),
+        ("q_row_stride", c_int64), ("k_row_stride", c_int64), ("v_row_stride", c_int64), ("o_row_stride", c_int64),
     ]
 
 
@@ -80,6 +91,8 @@ def load() -> ctypes.CDLL:
     lib.swin_attn_forward_host.restype = c_int
     lib.swin_attn_forward_host_static.argtypes = [POINTER(Shape)] + [vp] * 8
     lib.swin_attn_forward_host_static.restype = c_int
+    lib.mha_attention_forward.argtypes = [POINTER(MhaShape)] + [vp] * 6
+    lib.mha_attention_forward.restype = c_int
     lib.swin_layernorm_forward.argtypes = [vp, c_int32, vp, vp, c_float, c_int64, c_int32, vp, c_int32, vp]
     lib.swin_layernorm_forward.restype = c_int
     lib.swin_layernorm_backward.argtypes = [vp, c_int32, vp, c_int32, vp, c_float, c_int64, c_int32, vp, vp, vp, vp]

@@ -1,0 +1,170 @@
+// Global (un-windowed) multi-head attention that also RETURNS the attention map -- the core of the Depthformer decoder's
+// SelfAttentionBlock (model/Depthformer/self_attention.py:70-80):
+//
+//     attn = softmax(q k^T * scale)   (B, nH, S, S), returned to the caller (fp32)
+//     o    = attn v                   (B, S, nH * dv)
+//
+// S = (H/32)(W/32) tokens: 418 at 352x1216, 300 at 480x640; head dims 64.  The map has to be materialised, so the op is
+// bound by writing it (B nH S^2 4 B: 22 MB at batch 8) -- the q / k / v reads are 50x smaller.
+//
+// CUDA-core kernel, fp32 math (this is also the fp32 mode: <= 1e-5 against the reference rules out bf16 / tf32 MMAs):
+// one CTA = 32 query rows of one (image, head); its 32 x S block of logits lives in shared memory, so the softmax is
+// exact and single-pass over smem, each map row is written ONCE by a warp (coalesced 128-byte segments), and K / V
+// stream through a 64-key shared-memory tile.  Inputs are (B, S, nH * d) rows with an arbitrary row stride (slices of a
+// packed projection work); fp32 or bf16.
+#include "swin_common.cuh"
+
+namespace swin {
+namespace mha {
+
+constexpr int kRows = 32;      // query rows per CTA
+constexpr int kKeys = 64;      // keys per shared-memory tile
+constexpr int kThreads = 256;
+constexpr int kMaxHeadDim = 64;
+
+template <typename T>
+__device__ __forceinline__ float ldf(const T* p);
+template <>
+__device__ __forceinline__ float ldf<float>(const float* p) { return __ldg(p); }
+template <>
+__device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+
+template <typename T>
+__device__ __forceinline__ void stf(T* p, float v);
+template <>
+__device__ __forceinline__ void stf<float>(float* p, float v) { *p = v; }
+template <>
+__device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+
+struct Args {
+  int B, S, nH, dq, dv, s_pad;
+  int64_t q_rs, k_rs, v_rs, o_rs;   // row strides in elements
+  float scale;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T* __restrict__ q, const T* __restrict__ k,
+                                                           const T* __restrict__ v, T* __restrict__ o, float* __restrict__ attn) {
+  extern __shared__ __align__(16) float sm[];
+  float* sq = sm;                                   // [kRows][dq]
+  float* skv = sq + kRows * a.dq;                   // [kKeys][kMaxHeadDim + 1]
+  float* ss = skv + kKeys * (kMaxHeadDim + 1);      // [kRows][s_pad]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int row0 = blockIdx.x * kRows, h = blockIdx.y, b = blockIdx.z;
+  const T* qb = q + (int64_t)b * a.S * a.q_rs + h * a.dq;
+  const T* kb = k + (int64_t)b * a.S * a.k_rs + h * a.dq;
+  const T* vb = v + (int64_t)b * a.S * a.v_rs + h * a.dv;
+
+  for (int i = tid; i < kRows * a.dq; i += kThreads) {
+    const int r = i / a.dq, d = i - r * a.dq;
+    sq[i] = row0 + r < a.S ? ldf(qb + (int64_t)(row0 + r) * a.q_rs + d) : 0.f;
+  }
+
+  // ---- logits: thread (j = tid % 64, ig = tid / 64) owns S[ig + 4 r][chunk + j], r = 0..7 ----
+  const int j = tid & (kKeys - 1), ig = tid >> 6;
+  for (int c0 = 0; c0 < a.s_pad; c0 += kKeys) {
+    __syncthreads();                                // sq ready / previous tile consumed
+    for (int i = tid; i < kKeys * a.dq; i += kThreads) {
+      const int r = i / a.dq, d = i - r * a.dq;
+      skv[r * (kMaxHeadDim + 1) + d] = c0 + r < a.S ? ldf(kb + (int64_t)(c0 + r) * a.k_rs + d) : 0.f;
+    }
+    __syncthreads();
+    float acc[8] = {};
+    const float* kr = skv + j * (kMaxHeadDim + 1);
+    for (int d = 0; d < a.dq; ++d) {
+      const float kv = kr[d];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) acc[r] = fmaf(sq[(ig + 4 * r) * a.dq + d], kv, acc[r]);   // sq: warp-wide broadcast
+    }
+    const bool live = c0 + j < a.S;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) ss[(ig + 4 * r) * a.s_pad + c0 + j] = live ? acc[r] * a.scale : -INFINITY;
+  }
+  __syncthreads();
+
+  // ---- softmax: warp w owns rows w, w + 8, w + 16, w + 24; the normalised row goes to smem and to the map ----
+  for (int r = warp; r < kRows; r += kThreads / 32) {
+    float* srow = ss + r * a.s_pad;
+    float m = -INFINITY;
+    for (int c = lane; c < a.S; c += 32) m = fmaxf(m, srow[c]);
+#pragma unroll
+    for (int off = 16; off; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+    float sum = 0.f;
+    for (int c = lane; c < a.s_pad; c += 32) {
+      const float e = c < a.S ? expf(srow[c] - m) : 0.f;
+      srow[c] = e;
+      sum += e;
+    }
+#pragma unroll
+    for (int off = 16; off; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+    const float inv = 1.f / sum;
+    const bool row_live = row0 + r < a.S;
+    float* arow = attn != nullptr && row_live ? attn + (((int64_t)b * a.nH + h) * a.S + row0 + r) * a.S : nullptr;
+    for (int c = lane; c < a.s_pad; c += 32) {
+      const float p = srow[c] * inv;
+      srow[c] = p;
+      if (arow != nullptr && c < a.S) arow[c] = p;
+    }
+  }
+
+  // ---- o = P v: thread (d = tid % 64, ig) owns o[ig + 4 r][d] ----
+  float acc[8] = {};
+  for (int c0 = 0; c0 < a.s_pad; c0 += kKeys) {
+    __syncthreads();                                // P ready / previous tile consumed
+    for (int i = tid; i < kKeys * a.dv; i += kThreads) {
+      const int r = i / a.dv, d = i - r * a.dv;
+      skv[r * (kMaxHeadDim + 1) + d] = c0 + r < a.S ? ldf(vb + (int64_t)(c0 + r) * a.v_rs + d) : 0.f;
+    }
+    __syncthreads();
+    if (j < a.dv) {
+      for (int kk = 0; kk < kKeys; ++kk) {
+        const float vv = skv[kk * (kMaxHeadDim + 1) + j];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) acc[r] = fmaf(ss[(ig + 4 * r) * a.s_pad + c0 + kk], vv, acc[r]);   // broadcast
+      }
+    }
+  }
+  if (j < a.dv) {
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int row = row0 + ig + 4 * r;
+      if (row < a.S) stf(o + ((int64_t)b * a.S + row) * a.o_rs + h * a.dv + j, acc[r]);
+    }
+  }
+}
+
+}  // namespace mha
+
+size_t mha_forward_smem_bytes(int seq, int qk_head_dim) {
+  const int s_pad = (seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
+  return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + (size_t)mha::kKeys * (mha::kMaxHeadDim + 1) + (size_t)mha::kRows * s_pad);
+}
+
+cudaError_t launch_mha_forward(int dtype, int batch, int seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,
+                               int64_t o_rs, float scale, const void* q, const void* k, const void* v, void* o, float* attn,
+                               cudaStream_t st) {
+  mha::Args a;
+  a.B = batch; a.S = seq; a.nH = heads; a.dq = dq; a.dv = dv;
+  a.s_pad = (seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
+  a.q_rs = q_rs; a.k_rs = k_rs; a.v_rs = v_rs; a.o_rs = o_rs; a.scale = scale;
+  const size_t smem = mha_forward_smem_bytes(seq, dq);
+  const dim3 grid((seq + mha::kRows - 1) / mha::kRows, heads, batch);
+  cudaError_t e;
+  TimedRegion timed(st);
+  if (dtype == SWIN_ATTN_F32) {
+    e = cudaFuncSetAttribute(mha::mha_fwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    mha::mha_fwd_kernel<float><<<grid, mha::kThreads, smem, st>>>(a, static_cast<const float*>(q), static_cast<const float*>(k),
+                                                                   static_cast<const float*>(v), static_cast<float*>(o), attn);
+  } else {
+    e = cudaFuncSetAttribute(mha::mha_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    mha::mha_fwd_kernel<__nv_bfloat16><<<grid, mha::kThreads, smem, st>>>(
+        a, static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(k), static_cast<const __nv_bfloat16*>(v),
+        static_cast<__nv_bfloat16*>(o), attn);
+  }
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace swin

@@ -160,6 +160,12 @@ bool tc_linear_supported(int64_t rows, int in_features, int out_features);
 cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias, const void* residual, void* pre_act, void* y, int64_t rows,
                              int in_features, int out_features, int activation, cudaStream_t st, const char** err);
 
+// Global multi-head attention that returns its map (Depthformer SelfAttentionBlock core; mha_global.cu)
+size_t mha_forward_smem_bytes(int seq, int qk_head_dim);
+cudaError_t launch_mha_forward(int dtype, int batch, int seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,
+                               int64_t o_rs, float scale, const void* q, const void* k, const void* v, void* o, float* attn,
+                               cudaStream_t st);
+
 void set_tc_linear_pair_mode(int mode);
 void count_launch(int n = 1);
 

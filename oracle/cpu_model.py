@@ -113,10 +113,13 @@ def to_oracle(module: torch.nn.Module, device="cpu") -> torch.nn.Module:
     With ``device="cuda"`` the same restatement runs as PyTorch-eager ATen kernels on the GPU:
     that is "the reference on the B200" (used to measure the reference's own bf16-autocast
     error and the eager baseline), still never the product path."""
+    from .global_attention import SWAP as mha_swap
     clone = copy.deepcopy(module).to(device)
     for m in clone.modules():
         if type(m) in _SWAP:
             m.__class__ = _SWAP[type(m)]
+        elif type(m) in mha_swap:
+            m.__class__ = mha_swap[type(m)]
     return clone
 
 

@@ -84,6 +84,35 @@ def oda_block(name, ws, shift, b, h, w, c, nh):
                 cot=cot, dx=gs[0], dtable=gs[1], dqkv_w=gs[2], dqkv_b=gs[3])
 
 
+def depthformer_vit(name, b, s, hidden, kq, nh, repeat):
+    """model/Depthformer ViTLayer (pre-norm SelfAttentionBlock + FeedForwardBlock, shared weights over `repeat`), eval mode;
+    cotangents on BOTH outputs (hidden and the returned attention map)."""
+    V = rs.depthformer_vit_layer()
+    m = V.ViTLayer(hidden, kq, nh, num_repeat=repeat).eval()
+    m.load_state_dict(synthetic_state(m))
+    x = randn(name + ".x", b, s, hidden).requires_grad_()
+    out, attn = m(x)
+    cot_o, cot_a = randn(name + ".cot_o", *out.shape), randn(name + ".cot_a", *attn.shape)
+    sa = m.self_attn
+    gs = torch.autograd.grad((out * cot_o).sum() + (attn * cot_a).sum(),
+                             [x, sa.query_proj.weight, sa.key_proj.weight, sa.value_proj.weight, sa.out_proj.bias])
+    return dict(kind="depthformer_vit", cfg=dict(b=b, s=s, hidden=hidden, kq=kq, nh=nh, repeat=repeat), x=x.detach(),
+                out=out.detach(), attn=attn.detach(), cot_o=cot_o, cot_a=cot_a, dx=gs[0], dq_w=gs[1], dk_w=gs[2], dv_w=gs[3],
+                dout_b=gs[4])
+
+
+def depthformer_postnorm_sa(name, b, s, hidden, kq, nh):
+    S = rs.depthformer_self_attention()
+    m = S.PostNormSelfAttentionBlock(hidden, kq, nh).eval()
+    m.load_state_dict(synthetic_state(m))
+    x = randn(name + ".x", b, s, hidden).requires_grad_()
+    out, attn = m(x)
+    cot_o = randn(name + ".cot_o", *out.shape)
+    gs = torch.autograd.grad((out * cot_o).sum(), [x, m.key_proj.weight])
+    return dict(kind="depthformer_postnorm_sa", cfg=dict(b=b, s=s, hidden=hidden, kq=kq, nh=nh), x=x.detach(), out=out.detach(),
+                attn=attn.detach(), cot_o=cot_o, dx=gs[0], dk_w=gs[1])
+
+
 def masked_windows(name, ws, nw, groups, c, nh):
     """WindowAttention.forward(x, v, mask) on window-order tokens with an arbitrary mask."""
     L = rs.newcrf_layers()
@@ -196,6 +225,10 @@ CASES = {
     "oda_block_ws12_s6": lambda n: oda_block(n, 12, 6, 1, 24, 36, 64, 2),
     "oda_block_ws12_s0": lambda n: oda_block(n, 12, 0, 1, 24, 24, 64, 2),
     "oda_block_ws7_s3": lambda n: oda_block(n, 7, 3, 2, 14, 21, 96, 3),
+    # Depthformer decoder attention: S = 11 x 10 tokens, head dim 64 (the model's) / 32 with a narrower key-query width
+    "depthformer_vit_hd64": lambda n: depthformer_vit(n, 2, 110, 128, 128, 2, 2),
+    "depthformer_vit_kq32": lambda n: depthformer_vit(n, 1, 75, 128, 64, 2, 1),
+    "depthformer_postnorm_sa": lambda n: depthformer_postnorm_sa(n, 1, 97, 192, 192, 3),
     "newcrf_level": lambda n: newcrf_level(n, 1, 10, 13, 48, 64, 32, 2),
     "newcrfdepth_tiny07": lambda n: full_model(n, "tiny07", 1, 64, 96),
     # metrics only (same image / weights as newcrfdepth_tiny07; adds the realistic-range GT)

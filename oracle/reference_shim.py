@@ -169,6 +169,18 @@ def oda2_swin_transformer():
     return importlib.import_module("model.ODA2.oda2_swin_transformer")
 
 
+def depthformer_vit_layer():
+    install()
+    import importlib
+    return importlib.import_module("model.Depthformer.vit_layer")
+
+
+def depthformer_self_attention():
+    install()
+    import importlib
+    return importlib.import_module("model.Depthformer.self_attention")
+
+
 def newcrf_layers():
     install()
     import importlib

@@ -13,7 +13,7 @@ from conftest import ROOT
 def _declared():
     text = open(os.path.join(ROOT, "include", "swin_attn.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(swin_(?:attn|layernorm|add_layernorm|patch_merge_layernorm|gelu|linear)_[a-z0-9_]+)\s*\(", text)))
+    return sorted(set(re.findall(r"\b((?:swin_(?:attn|layernorm|add_layernorm|patch_merge_layernorm|gelu|linear)|mha_attention)_[a-z0-9_]+)\s*\(", text)))
 
 
 def test_library_exports_every_declared_symbol():
@@ -27,6 +27,8 @@ def test_library_exports_every_declared_symbol():
 def test_shape_struct_matches_header_layout():
     # 8 x int32, 2 x float, uint64, 4 x int64, 2 x int32
     assert ctypes.sizeof(_lib.Shape) == 8 * 4 + 2 * 4 + 8 + 4 * 8 + 2 * 4
+    # mha_shape_t: 6 x int32, float, int32, 4 x int64
+    assert ctypes.sizeof(_lib.MhaShape) == 6 * 4 + 4 + 4 + 4 * 8
 
 
 @pytest.mark.parametrize("field,value,msg", [

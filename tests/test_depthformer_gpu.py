@@ -1,0 +1,103 @@
+"""SURVEY §8f row 4, GPU side: the global attention kernel (mha_attention_forward) through the C ABI and the drop-in
+Depthformer blocks against the oracle and the reference fixtures.  fp32 <= 1e-5, bf16 autocast <= 1e-2 (max-normalised)."""
+import ctypes
+
+import pytest
+import torch
+
+from mde_b200 import _lib, depthformer
+from oracle import global_attention as oga
+from oracle.synthetic import randn
+from conftest import check, rel_err
+from test_depthformer_cpu import postnorm_from_golden, vit_from_golden
+
+DEV = "cuda"
+TOL = {torch.float32: 1e-5, torch.bfloat16: 1e-2}
+
+
+def _abi(q, k, v, nh, scale, want_map=True):
+    lib = _lib.load()
+    b, s, dqk = q.shape
+    dvv = v.shape[2]
+    o = torch.full((b, s, dvv), float("nan"), dtype=q.dtype, device=q.device)
+    attn = torch.full((b, nh, s, s), float("nan"), device=q.device) if want_map else None
+    shp = _lib.MhaShape(b, s, nh, dqk // nh, dvv // nh, _lib.F32 if q.dtype == torch.float32 else _lib.BF16, scale, 0,
+                        q.stride(1), k.stride(1), v.stride(1), o.stride(1))
+    rc = lib.mha_attention_forward(ctypes.byref(shp), ctypes.c_void_p(q.data_ptr()), ctypes.c_void_p(k.data_ptr()),
+                                   ctypes.c_void_p(v.data_ptr()), ctypes.c_void_p(o.data_ptr()),
+                                   ctypes.c_void_p(attn.data_ptr()) if want_map else None,
+                                   ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, lib.swin_attn_last_error().decode()
+    return o, attn
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("b,s,nh,dq,dv", [(2, 418, 4, 64, 64),      # Depthformer at 352 x 1216
+                                          (1, 300, 4, 64, 64),      # ... at 480 x 640
+                                          (2, 33, 2, 32, 64), (1, 1, 1, 8, 4), (1, 64, 3, 20, 12), (1, 129, 2, 64, 48)])
+def test_kernel_matches_oracle_through_the_c_abi(dtype, b, s, nh, dq, dv):
+    name = f"mha.{b}.{s}.{nh}.{dq}.{dv}"
+    packed = randn(name, b, s, nh * (2 * dq + dv)).to(DEV).to(dtype)    # q | k | v slices of one packed projection (row stride > width)
+    q, k, v = packed[..., :nh * dq], packed[..., nh * dq:2 * nh * dq], packed[..., 2 * nh * dq:]
+    scale = dq ** -0.5
+    o, attn = _abi(q, k, v, nh, scale)
+    ro, ra = oga.global_attention(q.double(), k.double(), v.double(), nh, scale)
+    check(rel_err(attn, ra), TOL[torch.float32], f"{name} {dtype} attention map vs oracle")   # fp32 math on both dtypes
+    check(rel_err(o.float(), ro), TOL[dtype], f"{name} {dtype} output vs oracle")
+    assert torch.allclose(attn.sum(-1), torch.ones_like(attn[..., 0]), atol=1e-5)
+    o2, none = _abi(q, k, v, nh, scale, want_map=False)
+    assert none is None and torch.equal(o2, o)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["depthformer_vit_hd64", "depthformer_vit_kq32"])
+def test_vit_layer_fp32_vs_reference_golden(golden, name):
+    g = golden(name)
+    m = vit_from_golden(g).to(DEV)
+    x = g["x"].to(DEV).requires_grad_()
+    launches = _lib.launch_count()
+    out, attn = m(x)
+    assert _lib.launch_count() - launches == g["cfg"]["repeat"]          # one kernel of ours per self-attention
+    check(rel_err(out, g["out"]), 1e-5, f"{name} fp32 out")
+    check(rel_err(attn, g["attn"]), 1e-5, f"{name} fp32 map")
+    sa = m.self_attn
+    gs = torch.autograd.grad((out * g["cot_o"].to(DEV)).sum() + (attn * g["cot_a"].to(DEV)).sum(),
+                             [x, sa.query_proj.weight, sa.key_proj.weight, sa.value_proj.weight, sa.out_proj.bias])
+    for got, key in zip(gs, ["dx", "dq_w", "dk_w", "dv_w", "dout_b"]):
+        check(rel_err(got, g[key]), 1e-5, f"{name} fp32 {key}")
+
+
+@pytest.mark.gpu
+def test_blocks_bf16_autocast_vs_reference_golden(golden):
+    g = golden("depthformer_vit_hd64")
+    m = vit_from_golden(g).to(DEV)
+    x = g["x"].to(DEV).requires_grad_()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out, attn = m(x)
+    assert attn.dtype == torch.float32                                   # autocast runs softmax in fp32: the map is fp32
+    check(rel_err(out.float(), g["out"]), 1e-2, "depthformer vit bf16 out")
+    check(rel_err(attn, g["attn"]), 1e-2, "depthformer vit bf16 map")
+    dx, = torch.autograd.grad((out.float() * g["cot_o"].to(DEV)).sum() + (attn * g["cot_a"].to(DEV)).sum(), [x])
+    check(rel_err(dx, g["dx"]), 1e-2, "depthformer vit bf16 dx")
+    g = golden("depthformer_postnorm_sa")
+    m = postnorm_from_golden(g).to(DEV)
+    x = g["x"].to(DEV).requires_grad_()
+    out, attn = m(x)
+    check(rel_err(out, g["out"]), 1e-5, "depthformer post-norm fp32 out")
+    check(rel_err(attn, g["attn"]), 1e-5, "depthformer post-norm fp32 map")
+    dx, dk = torch.autograd.grad((out * g["cot_o"].to(DEV)).sum(), [x, m.key_proj.weight])
+    check(rel_err(dx, g["dx"]), 1e-5, "depthformer post-norm fp32 dx")
+    check(rel_err(dk, g["dk_w"]), 1e-5, "depthformer post-norm fp32 dk_w")
+
+
+@pytest.mark.gpu
+def test_training_with_attention_dropout_returns_the_undropped_map():
+    torch.manual_seed(0)
+    m = depthformer.SelfAttentionBlock(128, 128, 2, attn_drop_prob=0.5, drop_prob=0.0).to(DEV).train()
+    x = randn("mha.drop.x", 2, 40, 128).to(DEV)
+    out, attn = m(x)
+    m.eval()
+    out_eval, attn_eval = m(x)
+    assert torch.equal(attn, attn_eval)                                  # self_attention.py:74-76: the map is returned before dropout
+    assert rel_err(out, out_eval) > 1e-3                                 # ... but the value product saw the dropped map
