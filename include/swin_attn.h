@@ -244,13 +244,14 @@ void swin_attn_time_next_launch(void* start_event, void* stop_event);
  *     o    = attn v, (batch, seq, num_heads * v_head_dim) in `dtype`.
  * q, k: (batch, seq, num_heads * qk_head_dim), v: (batch, seq, num_heads * v_head_dim), head h at channel offset h * head_dim
  * (what `_reshape_qkv`, :36-40, views), rows `*_row_stride` elements apart (slices of a packed projection are fine).
- * fp32 math on the CUDA cores for both dtypes (the fp32 mode must hold 1e-5); attention dropout is not applied (the
- * reference returns the un-dropped map; callers that train with attn_drop_prob > 0 apply it to attn_map themselves).
- * Limits: head dims <= 64, seq <= 1664 (a 32-row block of logits lives in shared memory). */
+ * Two kernels: tcgen05 (bf16, both head dims 64, 16 <= seq <= 448, 16-byte aligned pointers, row strides multiples of 8
+ * -- the Depthformer shapes; S and the bf16 P live in tensor memory, fp32 softmax) and CUDA cores (fp32 math for both
+ * dtypes -- the fp32 mode must hold 1e-5 --, head dims <= 64, seq <= 1664).  Attention dropout is not applied (the
+ * reference returns the un-dropped map; callers that train with attn_drop_prob > 0 apply it to attn_map themselves). */
 typedef struct {
   int32_t batch, seq, num_heads, qk_head_dim, v_head_dim, dtype;
   float scale;
-  int32_t reserved;
+  int32_t impl; /* SWIN_ATTN_IMPL_AUTO: tcgen05 kernel when it applies, else CUDA cores; SWIN_ATTN_IMPL_SIMT: CUDA cores */
   int64_t q_row_stride, k_row_stride, v_row_stride, o_row_stride;
 } mha_shape_t;
 int mha_attention_forward(const mha_shape_t* shape, const void* q, const void* k, const void* v, void* o, float* attn_map, void* stream);

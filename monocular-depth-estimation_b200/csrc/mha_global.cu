@@ -21,6 +21,7 @@ constexpr int kRows = 32;      // query rows per CTA
 constexpr int kKeys = 64;      // keys per shared-memory tile
 constexpr int kThreads = 256;
 constexpr int kMaxHeadDim = 64;
+constexpr int kTileStride = kMaxHeadDim + 4;   // words; 68 = 4 mod 32: 128-bit reads of consecutive rows are conflict-free
 
 template <typename T>
 __device__ __forceinline__ float ldf(const T* p);
@@ -47,8 +48,8 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
                                                            const T* __restrict__ v, T* __restrict__ o, float* __restrict__ attn) {
   extern __shared__ __align__(16) float sm[];
   float* sq = sm;                                   // [kRows][dq]
-  float* skv = sq + kRows * a.dq;                   // [kKeys][kMaxHeadDim + 1]
-  float* ss = skv + kKeys * (kMaxHeadDim + 1);      // [kRows][s_pad]
+  float* skv = sq + kRows * a.dq;                   // [kKeys][kTileStride]
+  float* ss = skv + kKeys * kTileStride;      // [kRows][s_pad]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int row0 = blockIdx.x * kRows, h = blockIdx.y, b = blockIdx.z;
   const T* qb = q + (int64_t)b * a.S * a.q_rs + h * a.dq;
@@ -66,15 +67,18 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     __syncthreads();                                // sq ready / previous tile consumed
     for (int i = tid; i < kKeys * a.dq; i += kThreads) {
       const int r = i / a.dq, d = i - r * a.dq;
-      skv[r * (kMaxHeadDim + 1) + d] = c0 + r < a.S ? ldf(kb + (int64_t)(c0 + r) * a.k_rs + d) : 0.f;
+      skv[r * kTileStride + d] = c0 + r < a.S ? ldf(kb + (int64_t)(c0 + r) * a.k_rs + d) : 0.f;
     }
     __syncthreads();
     float acc[8] = {};
-    const float* kr = skv + j * (kMaxHeadDim + 1);
-    for (int d = 0; d < a.dq; ++d) {
-      const float kv = kr[d];
+    const float4* kr = reinterpret_cast<const float4*>(skv + j * kTileStride);
+    for (int d4 = 0; d4 < a.dq / 4; ++d4) {      // qk_head_dim is a multiple of 4 (checked by the entry point)
+      const float4 kv = kr[d4];
 #pragma unroll
-      for (int r = 0; r < 8; ++r) acc[r] = fmaf(sq[(ig + 4 * r) * a.dq + d], kv, acc[r]);   // sq: warp-wide broadcast
+      for (int r = 0; r < 8; ++r) {
+        const float4 qv = reinterpret_cast<const float4*>(sq + (ig + 4 * r) * a.dq)[d4];   // warp-wide broadcast
+        acc[r] = fmaf(qv.x, kv.x, fmaf(qv.y, kv.y, fmaf(qv.z, kv.z, fmaf(qv.w, kv.w, acc[r]))));
+      }
     }
     const bool live = c0 + j < a.S;
 #pragma unroll
@@ -113,14 +117,18 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     __syncthreads();                                // P ready / previous tile consumed
     for (int i = tid; i < kKeys * a.dv; i += kThreads) {
       const int r = i / a.dv, d = i - r * a.dv;
-      skv[r * (kMaxHeadDim + 1) + d] = c0 + r < a.S ? ldf(vb + (int64_t)(c0 + r) * a.v_rs + d) : 0.f;
+      skv[r * kTileStride + d] = c0 + r < a.S ? ldf(vb + (int64_t)(c0 + r) * a.v_rs + d) : 0.f;
     }
     __syncthreads();
     if (j < a.dv) {
-      for (int kk = 0; kk < kKeys; ++kk) {
-        const float vv = skv[kk * (kMaxHeadDim + 1) + j];
+      for (int kk = 0; kk < kKeys; kk += 4) {
+        const float v0 = skv[kk * kTileStride + j], v1 = skv[(kk + 1) * kTileStride + j];
+        const float v2 = skv[(kk + 2) * kTileStride + j], v3 = skv[(kk + 3) * kTileStride + j];
 #pragma unroll
-        for (int r = 0; r < 8; ++r) acc[r] = fmaf(ss[(ig + 4 * r) * a.s_pad + c0 + kk], vv, acc[r]);   // broadcast
+        for (int r = 0; r < 8; ++r) {
+          const float4 pv = *reinterpret_cast<const float4*>(ss + (ig + 4 * r) * a.s_pad + c0 + kk);   // broadcast
+          acc[r] = fmaf(pv.w, v3, fmaf(pv.z, v2, fmaf(pv.y, v1, fmaf(pv.x, v0, acc[r]))));
+        }
       }
     }
   }
@@ -137,7 +145,7 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
 
 size_t mha_forward_smem_bytes(int seq, int qk_head_dim) {
   const int s_pad = (seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
-  return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + (size_t)mha::kKeys * (mha::kMaxHeadDim + 1) + (size_t)mha::kRows * s_pad);
+  return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + (size_t)mha::kKeys * mha::kTileStride + (size_t)mha::kRows * s_pad);
 }
 
 cudaError_t launch_mha_forward(int dtype, int batch, int seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,

@@ -485,7 +485,17 @@ int mha_attention_forward(const mha_shape_t* s, const void* q, const void* k, co
       s->v_row_stride < (int64_t)s->num_heads * s->v_head_dim || s->o_row_stride < (int64_t)s->num_heads * s->v_head_dim)
     return fail("mha forward: row strides must cover num_heads * head_dim elements");
   if (s->batch == 0 || s->seq == 0) return 0;
+  if (s->qk_head_dim % 4) return fail("mha forward: qk_head_dim must be a multiple of 4");
   if (s->batch > 65535 || s->num_heads > 65535) return fail("mha forward: batch and num_heads must be <= 65535");
+  if (s->impl != SWIN_ATTN_IMPL_AUTO && s->impl != SWIN_ATTN_IMPL_SIMT) return fail("mha forward: impl must be SWIN_ATTN_IMPL_AUTO or SWIN_ATTN_IMPL_SIMT");
+  if (s->impl == SWIN_ATTN_IMPL_AUTO && mha_tc_supported(s->dtype, s->seq, s->qk_head_dim, s->v_head_dim, s->q_row_stride, s->k_row_stride,
+                                                         s->v_row_stride, s->o_row_stride, q, k, v, o)) {
+    const char* why = nullptr;
+    cudaError_t e = launch_mha_tc_forward(s->batch, s->seq, s->num_heads, s->q_row_stride, s->k_row_stride, s->v_row_stride, s->o_row_stride,
+                                          s->scale, q, k, v, o, attn_map, static_cast<cudaStream_t>(stream), &why);
+    if (e != cudaSuccess) return fail_cuda(why ? why : "mha forward (tcgen05) launch", e);
+    return 0;
+  }
   const size_t smem = mha_forward_smem_bytes(s->seq, s->qk_head_dim);
   if (smem > 227u * 1024u)
     return fail("mha forward: seq " + std::to_string(s->seq) + " needs " + std::to_string(smem) + " B of shared memory per CTA (limit 232448; seq <= 1664)");

@@ -570,6 +570,20 @@ bool tc::encode_matrix_map(CUtensorMap* out, const void* base, int64_t rows, int
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Tensor map over (batch, rows, width) bf16 rows `row_stride` elements apart (batches rows * row_stride apart); box =
+// (box_cols, box_rows, 1), 128B swizzle for 64-column boxes.  Rows beyond `rows` load as zeros.
+bool tc::encode_rows_map(CUtensorMap* out, const void* base, int64_t batch, int64_t rows, int64_t width, int64_t row_stride, int box_cols,
+                         int box_rows) {
+  if (encode_fn() == nullptr) return false;
+  const cuuint64_t dims[4] = {(cuuint64_t)width, (cuuint64_t)rows, (cuuint64_t)batch, 1u};
+  const cuuint64_t strides[3] = {(cuuint64_t)row_stride * 2, (cuuint64_t)row_stride * 2 * rows, (cuuint64_t)row_stride * 2 * rows * batch};
+  const cuuint32_t box[4] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows, 1u, 1u};
+  const cuuint32_t estr[4] = {1u, 1u, 1u, 1u};
+  return encode_fn()(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, box_cols == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // jobs = heads x window chunks, at most one wave of CTAs; chunks hold an even number of windows
 void tc::job_grid(const Problem& p, int sms, int* n_win, int* win_per_job, int* grid) {
   *n_win = p.B * p.nWy * p.nWx;

@@ -342,6 +342,8 @@ __device__ __forceinline__ void write_pad_rows(uint32_t tile, uint64_t padded, c
 bool encode_window_map(CUtensorMap* out, const void* base, const Problem& p, int64_t pix_stride, int bx, int by);
 bool tma_available();
 bool encode_matrix_map(CUtensorMap* out, const void* base, int64_t rows, int64_t cols, int64_t pitch_bytes, int box_cols, int box_rows);
+bool encode_rows_map(CUtensorMap* out, const void* base, int64_t batch, int64_t rows, int64_t width, int64_t row_stride, int box_cols,
+                     int box_rows);
 void job_grid(const Problem& p, int sms, int* n_win, int* win_per_job, int* grid);
 int sm_count();
 bool pdl_enabled();   // programmatic dependent launch on the tcgen05 / LayerNorm launches (env SWIN_PDL=0 turns it off)

@@ -166,6 +166,11 @@ cudaError_t launch_mha_forward(int dtype, int batch, int seq, int heads, int dq,
                                int64_t o_rs, float scale, const void* q, const void* k, const void* v, void* o, float* attn,
                                cudaStream_t st);
 
+bool mha_tc_supported(int dtype, int seq, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, const void* q,
+                      const void* k, const void* v, const void* o);
+cudaError_t launch_mha_tc_forward(int batch, int seq, int heads, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, float scale,
+                                  const void* q, const void* k, const void* v, void* o, float* attn, cudaStream_t st, const char** err);
+
 void set_tc_linear_pair_mode(int mode);
 void count_launch(int n = 1);
 

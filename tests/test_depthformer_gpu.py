@@ -15,13 +15,13 @@ DEV = "cuda"
 TOL = {torch.float32: 1e-5, torch.bfloat16: 1e-2}
 
 
-def _abi(q, k, v, nh, scale, want_map=True):
+def _abi(q, k, v, nh, scale, want_map=True, impl=_lib.IMPL_AUTO):
     lib = _lib.load()
     b, s, dqk = q.shape
     dvv = v.shape[2]
     o = torch.full((b, s, dvv), float("nan"), dtype=q.dtype, device=q.device)
     attn = torch.full((b, nh, s, s), float("nan"), device=q.device) if want_map else None
-    shp = _lib.MhaShape(b, s, nh, dqk // nh, dvv // nh, _lib.F32 if q.dtype == torch.float32 else _lib.BF16, scale, 0,
+    shp = _lib.MhaShape(b, s, nh, dqk // nh, dvv // nh, _lib.F32 if q.dtype == torch.float32 else _lib.BF16, scale, impl,
                         q.stride(1), k.stride(1), v.stride(1), o.stride(1))
     rc = lib.mha_attention_forward(ctypes.byref(shp), ctypes.c_void_p(q.data_ptr()), ctypes.c_void_p(k.data_ptr()),
                                    ctypes.c_void_p(v.data_ptr()), ctypes.c_void_p(o.data_ptr()),
@@ -35,7 +35,9 @@ def _abi(q, k, v, nh, scale, want_map=True):
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("b,s,nh,dq,dv", [(2, 418, 4, 64, 64),      # Depthformer at 352 x 1216
                                           (1, 300, 4, 64, 64),      # ... at 480 x 640
-                                          (2, 33, 2, 32, 64), (1, 1, 1, 8, 4), (1, 64, 3, 20, 12), (1, 129, 2, 64, 48)])
+                                          (2, 33, 2, 32, 64), (1, 1, 1, 8, 4), (1, 64, 3, 20, 12), (1, 129, 2, 64, 48),
+                                          (1, 16, 1, 64, 64), (2, 256, 2, 64, 64), (1, 257, 1, 64, 64), (1, 448, 2, 64, 64),
+                                          (1, 449, 1, 64, 64)])
 def test_kernel_matches_oracle_through_the_c_abi(dtype, b, s, nh, dq, dv):
     name = f"mha.{b}.{s}.{nh}.{dq}.{dv}"
     packed = randn(name, b, s, nh * (2 * dq + dv)).to(DEV).to(dtype)    # q | k | v slices of one packed projection (row stride > width)
@@ -48,6 +50,12 @@ def test_kernel_matches_oracle_through_the_c_abi(dtype, b, s, nh, dq, dv):
     assert torch.allclose(attn.sum(-1), torch.ones_like(attn[..., 0]), atol=1e-5)
     o2, none = _abi(q, k, v, nh, scale, want_map=False)
     assert none is None and torch.equal(o2, o)
+    if dtype == torch.bfloat16 and dq == 64 and dv == 64 and 16 <= s <= 448:
+        # AUTO took the tcgen05 kernel (bf16 P in tensor memory); the CUDA-core kernel agrees within the bf16 bound
+        o3, attn3 = _abi(q, k, v, nh, scale, impl=_lib.IMPL_SIMT)
+        assert not torch.equal(o3, o)
+        check(rel_err(attn3, attn), 1e-5, f"{name} tcgen05 map vs CUDA-core map")
+        check(rel_err(o3.float(), o.float()), 1e-2, f"{name} tcgen05 output vs CUDA-core output")
 
 
 @pytest.mark.gpu
