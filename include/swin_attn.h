@@ -239,19 +239,23 @@ int swin_patch_merge_layernorm_forward(const void* x, int32_t x_dtype, const flo
 void swin_attn_time_next_launch(void* start_event, void* stop_event);
 
 /* Global (un-windowed) multi-head attention that returns its attention map: the core of the Depthformer decoder's
- * SelfAttentionBlock / PostNormSelfAttentionBlock (model/Depthformer/self_attention.py:70-80, :148-158):
- *     attn = softmax(q k^T * scale) over the last axis, (batch, num_heads, seq, seq) fp32, written to attn_map when non-NULL;
+ * SelfAttentionBlock / PostNormSelfAttentionBlock (model/Depthformer/self_attention.py:70-80, :148-158) and of both halves
+ * of its Luna blocks (pack: model/Depthformer/luna_layer.py:85-94, unpack: :118-127):
+ *     attn = softmax(q k^T * scale) over the last axis, (batch, num_heads, seq, kv_seq) fp32, written to attn_map when non-NULL;
  *     o    = attn v, (batch, seq, num_heads * v_head_dim) in `dtype`.
- * q, k: (batch, seq, num_heads * qk_head_dim), v: (batch, seq, num_heads * v_head_dim), head h at channel offset h * head_dim
- * (what `_reshape_qkv`, :36-40, views), rows `*_row_stride` elements apart (slices of a packed projection are fine).
- * Two kernels: tcgen05 (bf16, both head dims 64, 16 <= seq <= 448, 16-byte aligned pointers, row strides multiples of 8
+ * q: (batch, seq, num_heads * qk_head_dim), k: (batch, kv_seq, num_heads * qk_head_dim), v: (batch, kv_seq, num_heads *
+ * v_head_dim), head h at channel offset h * head_dim (what `_reshape_qkv` / `_reshape_3d` view), rows `*_row_stride` elements
+ * apart (slices of a packed projection are fine), batches seq (kv_seq) rows apart.  kv_seq = 0 means kv_seq = seq.
+ * Two kernels: tcgen05 (bf16, both head dims 64, 16 <= kv_seq <= 448, 16-byte aligned pointers, row strides multiples of 8
  * -- the Depthformer shapes; S and the bf16 P live in tensor memory, fp32 softmax) and CUDA cores (fp32 math for both
- * dtypes -- the fp32 mode must hold 1e-5 --, head dims <= 64, seq <= 1664).  Attention dropout is not applied (the
- * reference returns the un-dropped map; callers that train with attn_drop_prob > 0 apply it to attn_map themselves). */
+ * dtypes -- the fp32 mode must hold 1e-5 --, head dims <= 64 with qk_head_dim a multiple of 4, kv_seq <= 1664).  Attention
+ * dropout is not applied (the reference returns the un-dropped map; callers that train with attn_drop_prob > 0 apply it to
+ * attn_map themselves). */
 typedef struct {
-  int32_t batch, seq, num_heads, qk_head_dim, v_head_dim, dtype;
-  float scale;
+  int32_t batch, seq, kv_seq, num_heads, qk_head_dim, v_head_dim, dtype;
   int32_t impl; /* SWIN_ATTN_IMPL_AUTO: tcgen05 kernel when it applies, else CUDA cores; SWIN_ATTN_IMPL_SIMT: CUDA cores */
+  float scale;
+  int32_t reserved;
   int64_t q_row_stride, k_row_stride, v_row_stride, o_row_stride;
 } mha_shape_t;
 int mha_attention_forward(const mha_shape_t* shape, const void* q, const void* k, const void* v, void* o, float* attn_map, void* stream);

@@ -13,3 +13,4 @@ from .layers import (  # noqa: F401
     SwinTransformerBlock, WindowAttention, EncoderWindowAttention,
 )
 from .newcrfs import NewCRFDepth, SwinTransformer, PSP, DispHead  # noqa: F401
+from . import depthformer, siblings  # noqa: F401  (Depthformer attention, ODA / ODA2 Swin blocks)

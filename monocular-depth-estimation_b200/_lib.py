@@ -62,8 +62,8 @@ class MhaShape(Structure):
     """Mirror of ``mha_shape_t``."""
 
     _fields_ = [
-        ("batch", c_int32), ("seq", c_int32), ("num_heads", c_int32), ("qk_head_dim", c_int32), ("v_head_dim", c_int32),
-        ("dtype", c_int32), ("scale", c_float), ("impl", c_int32),
+        ("batch", c_int32), ("seq", c_int32), ("kv_seq", c_int32), ("num_heads", c_int32), ("qk_head_dim", c_int32),
+        ("v_head_dim", c_int32), ("dtype", c_int32), ("impl", c_int32), ("scale", c_float), ("reserved", c_int32),
         ("q_row_stride", c_int64), ("k_row_stride", c_int64), ("v_row_stride", c_int64), ("o_row_stride", c_int64),
     ]
 

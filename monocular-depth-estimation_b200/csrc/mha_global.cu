@@ -38,7 +38,7 @@ template <>
 __device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 
 struct Args {
-  int B, S, nH, dq, dv, s_pad;
+  int B, S, Sk, nH, dq, dv, s_pad;   // S query rows, Sk keys (s_pad = Sk rounded up to the key tile)
   int64_t q_rs, k_rs, v_rs, o_rs;   // row strides in elements
   float scale;
 };
@@ -53,8 +53,8 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int row0 = blockIdx.x * kRows, h = blockIdx.y, b = blockIdx.z;
   const T* qb = q + (int64_t)b * a.S * a.q_rs + h * a.dq;
-  const T* kb = k + (int64_t)b * a.S * a.k_rs + h * a.dq;
-  const T* vb = v + (int64_t)b * a.S * a.v_rs + h * a.dv;
+  const T* kb = k + (int64_t)b * a.Sk * a.k_rs + h * a.dq;
+  const T* vb = v + (int64_t)b * a.Sk * a.v_rs + h * a.dv;
 
   for (int i = tid; i < kRows * a.dq; i += kThreads) {
     const int r = i / a.dq, d = i - r * a.dq;
@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     __syncthreads();                                // sq ready / previous tile consumed
     for (int i = tid; i < kKeys * a.dq; i += kThreads) {
       const int r = i / a.dq, d = i - r * a.dq;
-      skv[r * kTileStride + d] = c0 + r < a.S ? ldf(kb + (int64_t)(c0 + r) * a.k_rs + d) : 0.f;
+      skv[r * kTileStride + d] = c0 + r < a.Sk ? ldf(kb + (int64_t)(c0 + r) * a.k_rs + d) : 0.f;
     }
     __syncthreads();
     float acc[8] = {};
@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
         acc[r] = fmaf(qv.x, kv.x, fmaf(qv.y, kv.y, fmaf(qv.z, kv.z, fmaf(qv.w, kv.w, acc[r]))));
       }
     }
-    const bool live = c0 + j < a.S;
+    const bool live = c0 + j < a.Sk;
 #pragma unroll
     for (int r = 0; r < 8; ++r) ss[(ig + 4 * r) * a.s_pad + c0 + j] = live ? acc[r] * a.scale : -INFINITY;
   }
@@ -90,12 +90,12 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
   for (int r = warp; r < kRows; r += kThreads / 32) {
     float* srow = ss + r * a.s_pad;
     float m = -INFINITY;
-    for (int c = lane; c < a.S; c += 32) m = fmaxf(m, srow[c]);
+    for (int c = lane; c < a.Sk; c += 32) m = fmaxf(m, srow[c]);
 #pragma unroll
     for (int off = 16; off; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
     float sum = 0.f;
     for (int c = lane; c < a.s_pad; c += 32) {
-      const float e = c < a.S ? expf(srow[c] - m) : 0.f;
+      const float e = c < a.Sk ? expf(srow[c] - m) : 0.f;
       srow[c] = e;
       sum += e;
     }
@@ -103,11 +103,11 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     for (int off = 16; off; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
     const float inv = 1.f / sum;
     const bool row_live = row0 + r < a.S;
-    float* arow = attn != nullptr && row_live ? attn + (((int64_t)b * a.nH + h) * a.S + row0 + r) * a.S : nullptr;
+    float* arow = attn != nullptr && row_live ? attn + (((int64_t)b * a.nH + h) * a.S + row0 + r) * a.Sk : nullptr;
     for (int c = lane; c < a.s_pad; c += 32) {
       const float p = srow[c] * inv;
       srow[c] = p;
-      if (arow != nullptr && c < a.S) arow[c] = p;
+      if (arow != nullptr && c < a.Sk) arow[c] = p;
     }
   }
 
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     __syncthreads();                                // P ready / previous tile consumed
     for (int i = tid; i < kKeys * a.dv; i += kThreads) {
       const int r = i / a.dv, d = i - r * a.dv;
-      skv[r * kTileStride + d] = c0 + r < a.S ? ldf(vb + (int64_t)(c0 + r) * a.v_rs + d) : 0.f;
+      skv[r * kTileStride + d] = c0 + r < a.Sk ? ldf(vb + (int64_t)(c0 + r) * a.v_rs + d) : 0.f;
     }
     __syncthreads();
     if (j < a.dv) {
@@ -143,19 +143,19 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
 
 }  // namespace mha
 
-size_t mha_forward_smem_bytes(int seq, int qk_head_dim) {
-  const int s_pad = (seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
+size_t mha_forward_smem_bytes(int kv_seq, int qk_head_dim) {
+  const int s_pad = (kv_seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
   return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + (size_t)mha::kKeys * mha::kTileStride + (size_t)mha::kRows * s_pad);
 }
 
-cudaError_t launch_mha_forward(int dtype, int batch, int seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,
+cudaError_t launch_mha_forward(int dtype, int batch, int seq, int kv_seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,
                                int64_t o_rs, float scale, const void* q, const void* k, const void* v, void* o, float* attn,
                                cudaStream_t st) {
   mha::Args a;
-  a.B = batch; a.S = seq; a.nH = heads; a.dq = dq; a.dv = dv;
-  a.s_pad = (seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
+  a.B = batch; a.S = seq; a.Sk = kv_seq; a.nH = heads; a.dq = dq; a.dv = dv;
+  a.s_pad = (kv_seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
   a.q_rs = q_rs; a.k_rs = k_rs; a.v_rs = v_rs; a.o_rs = o_rs; a.scale = scale;
-  const size_t smem = mha_forward_smem_bytes(seq, dq);
+  const size_t smem = mha_forward_smem_bytes(kv_seq, dq);
   const dim3 grid((seq + mha::kRows - 1) / mha::kRows, heads, batch);
   cudaError_t e;
   TimedRegion timed(st);

@@ -32,7 +32,7 @@ struct MapsM {
   CUtensorMap q, k, v;
 };
 struct ArgsM {
-  int S, s16, nH;
+  int S, Sk, s16, nH;                             // S query rows, Sk keys, s16 = Sk rounded up to 16
   float c1;                                       // scale * log2(e)
   __nv_bfloat16* o;
   int64_t o_rs;
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, con
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j)
-        if (32 * c + j < a.S) m = fmaxf(m, __uint_as_float(r[j]));
+        if (32 * c + j < a.Sk) m = fmaxf(m, __uint_as_float(r[j]));
     }
     // pass 2: e = exp2((s - max) * scale * log2 e), written back in place; row sum
     const float mc = m * a.c1;
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, con
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        const float e = 32 * c + j < a.S ? fast_exp2(fmaf(__uint_as_float(r[j]), a.c1, -mc)) : 0.f;
+        const float e = 32 * c + j < a.Sk ? fast_exp2(fmaf(__uint_as_float(r[j]), a.c1, -mc)) : 0.f;
         sum += e;
         r[j] = __float_as_uint(e);
       }
@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, con
     tmem_st_wait();
     // pass 3: p = e / sum -> the map (through the warp's staging tile: coalesced rows) and bf16 pairs back into TMEM
     const float inv = 1.f / sum;
-    float* attn_bh = a.attn != nullptr ? a.attn + ((int64_t)b * a.nH + h) * a.S * a.S : nullptr;
+    float* attn_bh = a.attn != nullptr ? a.attn + ((int64_t)b * a.nH + h) * a.S * a.Sk : nullptr;
     for (int c = 0; c < n_chunks; ++c) {
       TMEM_LD_X32(taddr + 32 * c, r);
       tmem_ld_wait();
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, con
         const int col = 32 * c + lane;
         for (int rr = 0; rr < 32; ++rr) {
           const int row = row0 + warp * 32 + rr;
-          if (row < a.S && col < a.S) attn_bh[(int64_t)row * a.S + col] = stage[rr * 33 + lane];
+          if (row < a.S && col < a.Sk) attn_bh[(int64_t)row * a.Sk + col] = stage[rr * 33 + lane];
         }
       }
       __syncwarp();
@@ -214,23 +214,23 @@ __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, con
 
 }  // namespace mhatc
 
-bool mha_tc_supported(int dtype, int seq, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, const void* q,
+bool mha_tc_supported(int dtype, int seq, int kv_seq, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, const void* q,
                       const void* k, const void* v, const void* o) {
-  if (dtype != SWIN_ATTN_BF16 || dq != mhatc::kHd || dv != mhatc::kHd || seq < 16 || seq > mhatc::kMaxSeq) return false;
+  if (dtype != SWIN_ATTN_BF16 || dq != mhatc::kHd || dv != mhatc::kHd || seq < 1 || kv_seq < 16 || kv_seq > mhatc::kMaxSeq) return false;
   if ((q_rs | k_rs | v_rs | o_rs) & 7) return false;
   auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
   if (mis(q) || mis(k) || mis(v) || mis(o)) return false;
   return tc::tma_available();
 }
 
-cudaError_t launch_mha_tc_forward(int batch, int seq, int heads, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, float scale,
+cudaError_t launch_mha_tc_forward(int batch, int seq, int kv_seq, int heads, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, float scale,
                                   const void* q, const void* k, const void* v, void* o, float* attn, cudaStream_t st, const char** err) {
   mhatc::MapsM maps;
   memset(&maps, 0, sizeof(maps));
   const int width = heads * mhatc::kHd;
   if (!tc::encode_rows_map(&maps.q, q, batch, seq, width, q_rs, mhatc::kHd, mhatc::kBoxRows) ||
-      !tc::encode_rows_map(&maps.k, k, batch, seq, width, k_rs, mhatc::kHd, mhatc::kBoxRows) ||
-      !tc::encode_rows_map(&maps.v, v, batch, seq, width, v_rs, mhatc::kHd, mhatc::kBoxRows)) {
+      !tc::encode_rows_map(&maps.k, k, batch, kv_seq, width, k_rs, mhatc::kHd, mhatc::kBoxRows) ||
+      !tc::encode_rows_map(&maps.v, v, batch, kv_seq, width, v_rs, mhatc::kHd, mhatc::kBoxRows)) {
     if (err) *err = "cuTensorMapEncodeTiled failed";
     return cudaErrorInvalidValue;
   }
@@ -241,7 +241,7 @@ cudaError_t launch_mha_tc_forward(int batch, int seq, int heads, int64_t q_rs, i
     return e;
   }
   mhatc::ArgsM a;
-  a.S = seq; a.s16 = (seq + 15) / 16 * 16; a.nH = heads;
+  a.S = seq; a.Sk = kv_seq; a.s16 = (kv_seq + 15) / 16 * 16; a.nH = heads;
   a.c1 = scale * 1.4426950408889634f;
   a.o = static_cast<__nv_bfloat16*>(o); a.o_rs = o_rs; a.attn = attn;
   const dim3 grid((seq + mhatc::kRowsM - 1) / mhatc::kRowsM, heads, batch);

@@ -478,28 +478,29 @@ int mha_attention_forward(const mha_shape_t* s, const void* q, const void* k, co
   if (s == nullptr) return fail("mha forward: shape is null");
   if (!q || !k || !v || !o) return fail("mha forward: q, k, v and o must be non-null");
   if (s->dtype != SWIN_ATTN_F32 && s->dtype != SWIN_ATTN_BF16) return fail("mha forward: dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
-  if (s->batch < 0 || s->seq < 0 || s->num_heads <= 0) return fail("mha forward: batch / seq must be >= 0 and num_heads positive");
+  if (s->batch < 0 || s->seq < 0 || s->kv_seq < 0 || s->num_heads <= 0) return fail("mha forward: batch / seq / kv_seq must be >= 0 and num_heads positive");
   if (s->qk_head_dim <= 0 || s->qk_head_dim > 64 || s->v_head_dim <= 0 || s->v_head_dim > 64)
     return fail("mha forward: head dims must be in 1..64 (got " + std::to_string(s->qk_head_dim) + ", " + std::to_string(s->v_head_dim) + ")");
   if (s->q_row_stride < (int64_t)s->num_heads * s->qk_head_dim || s->k_row_stride < (int64_t)s->num_heads * s->qk_head_dim ||
       s->v_row_stride < (int64_t)s->num_heads * s->v_head_dim || s->o_row_stride < (int64_t)s->num_heads * s->v_head_dim)
     return fail("mha forward: row strides must cover num_heads * head_dim elements");
+  const int kv_seq = s->kv_seq > 0 ? s->kv_seq : s->seq;       // 0: self-attention, keys = queries' tokens
   if (s->batch == 0 || s->seq == 0) return 0;
   if (s->qk_head_dim % 4) return fail("mha forward: qk_head_dim must be a multiple of 4");
   if (s->batch > 65535 || s->num_heads > 65535) return fail("mha forward: batch and num_heads must be <= 65535");
   if (s->impl != SWIN_ATTN_IMPL_AUTO && s->impl != SWIN_ATTN_IMPL_SIMT) return fail("mha forward: impl must be SWIN_ATTN_IMPL_AUTO or SWIN_ATTN_IMPL_SIMT");
-  if (s->impl == SWIN_ATTN_IMPL_AUTO && mha_tc_supported(s->dtype, s->seq, s->qk_head_dim, s->v_head_dim, s->q_row_stride, s->k_row_stride,
+  if (s->impl == SWIN_ATTN_IMPL_AUTO && mha_tc_supported(s->dtype, s->seq, kv_seq, s->qk_head_dim, s->v_head_dim, s->q_row_stride, s->k_row_stride,
                                                          s->v_row_stride, s->o_row_stride, q, k, v, o)) {
     const char* why = nullptr;
-    cudaError_t e = launch_mha_tc_forward(s->batch, s->seq, s->num_heads, s->q_row_stride, s->k_row_stride, s->v_row_stride, s->o_row_stride,
-                                          s->scale, q, k, v, o, attn_map, static_cast<cudaStream_t>(stream), &why);
+    cudaError_t e = launch_mha_tc_forward(s->batch, s->seq, kv_seq, s->num_heads, s->q_row_stride, s->k_row_stride, s->v_row_stride,
+                                          s->o_row_stride, s->scale, q, k, v, o, attn_map, static_cast<cudaStream_t>(stream), &why);
     if (e != cudaSuccess) return fail_cuda(why ? why : "mha forward (tcgen05) launch", e);
     return 0;
   }
-  const size_t smem = mha_forward_smem_bytes(s->seq, s->qk_head_dim);
+  const size_t smem = mha_forward_smem_bytes(kv_seq, s->qk_head_dim);
   if (smem > 227u * 1024u)
-    return fail("mha forward: seq " + std::to_string(s->seq) + " needs " + std::to_string(smem) + " B of shared memory per CTA (limit 232448; seq <= 1664)");
-  cudaError_t e = launch_mha_forward(s->dtype, s->batch, s->seq, s->num_heads, s->qk_head_dim, s->v_head_dim, s->q_row_stride,
+    return fail("mha forward: " + std::to_string(kv_seq) + " keys need " + std::to_string(smem) + " B of shared memory per CTA (limit 232448; kv_seq <= 1664)");
+  cudaError_t e = launch_mha_forward(s->dtype, s->batch, s->seq, kv_seq, s->num_heads, s->qk_head_dim, s->v_head_dim, s->q_row_stride,
                                      s->k_row_stride, s->v_row_stride, s->o_row_stride, s->scale, q, k, v, o, attn_map,
                                      static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) return fail_cuda("mha forward launch", e);

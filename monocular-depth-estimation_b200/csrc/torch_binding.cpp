@@ -943,7 +943,8 @@ TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
 // projection).  Returns o (B, S, nH * dv) in the input dtype and the fp32 map (B, nH, S, S).
 std::tuple<Tensor, Tensor> mha_fwd_cuda(const Tensor& q_in, const Tensor& k_in, const Tensor& v_in, int64_t num_heads, double scale) {
   TORCH_CHECK(q_in.dim() == 3 && k_in.dim() == 3 && v_in.dim() == 3, "mha_fwd: q, k, v must be (B, S, D)");
-  TORCH_CHECK(q_in.sizes() == k_in.sizes() && v_in.size(0) == q_in.size(0) && v_in.size(1) == q_in.size(1), "mha_fwd: q / k / v shapes disagree");
+  TORCH_CHECK(q_in.size(0) == k_in.size(0) && q_in.size(2) == k_in.size(2) && v_in.size(0) == k_in.size(0) && v_in.size(1) == k_in.size(1),
+              "mha_fwd: q (B, S, D), k (B, Sk, D), v (B, Sk, Dv) shapes disagree");
   TORCH_CHECK(num_heads > 0 && q_in.size(2) % num_heads == 0 && v_in.size(2) % num_heads == 0, "Hidden dim not multiple of num heads.");
   const auto dt = q_in.scalar_type();
   const int32_t code = dtype_code(dt);
@@ -952,12 +953,12 @@ std::tuple<Tensor, Tensor> mha_fwd_cuda(const Tensor& q_in, const Tensor& k_in, 
     return (u.stride(2) == 1 && u.stride(0) == u.size(1) * u.stride(1) && u.stride(1) >= u.size(2)) ? u : u.contiguous();
   };
   const Tensor q = rows(q_in), k = rows(k_in), v = rows(v_in);
-  const int64_t b = q.size(0), s = q.size(1);
+  const int64_t b = q.size(0), s = q.size(1), sk = k.size(1);
   Tensor o = at::empty({b, s, v.size(2)}, q.options());
-  Tensor attn = at::empty({b, num_heads, s, s}, q.options().dtype(at::kFloat));
+  Tensor attn = at::empty({b, num_heads, s, sk}, q.options().dtype(at::kFloat));
   mha_shape_t shp;
   memset(&shp, 0, sizeof(shp));
-  shp.batch = (int32_t)b; shp.seq = (int32_t)s; shp.num_heads = (int32_t)num_heads;
+  shp.batch = (int32_t)b; shp.seq = (int32_t)s; shp.kv_seq = (int32_t)sk; shp.num_heads = (int32_t)num_heads;
   shp.qk_head_dim = (int32_t)(q.size(2) / num_heads); shp.v_head_dim = (int32_t)(v.size(2) / num_heads);
   shp.dtype = code; shp.scale = (float)scale;
   shp.q_row_stride = q.stride(1); shp.k_row_stride = k.stride(1); shp.v_row_stride = v.stride(1); shp.o_row_stride = o.stride(1);
@@ -967,9 +968,9 @@ std::tuple<Tensor, Tensor> mha_fwd_cuda(const Tensor& q_in, const Tensor& k_in, 
   return {o, attn};
 }
 
-std::tuple<Tensor, Tensor> mha_fwd_meta(const Tensor& q, const Tensor&, const Tensor& v, int64_t num_heads, double) {
+std::tuple<Tensor, Tensor> mha_fwd_meta(const Tensor& q, const Tensor& k, const Tensor& v, int64_t num_heads, double) {
   return {at::empty_symint({q.sym_size(0), q.sym_size(1), v.sym_size(2)}, q.options()),
-          at::empty_symint({q.sym_size(0), c10::SymInt(num_heads), q.sym_size(1), q.sym_size(1)}, q.options().dtype(at::kFloat))};
+          at::empty_symint({q.sym_size(0), c10::SymInt(num_heads), q.sym_size(1), k.sym_size(1)}, q.options().dtype(at::kFloat))};
 }
 
 TORCH_LIBRARY_FRAGMENT(swin_attn, m) {

@@ -1,7 +1,8 @@
 """Depthformer decoder attention: drop-in ``SelfAttentionBlock`` / ``PostNormSelfAttentionBlock`` /
-``FeedForwardBlock`` / ``PostNormFeedForwardBlock`` / ``ViTLayer`` for ``model/Depthformer/{self_attention,feed_forward,
-vit_layer}.py`` -- same constructors, attribute names, ``state_dict`` keys and return values (the block returns the
-attention map, so the map is materialised).
+``FeedForwardBlock`` / ``PostNormFeedForwardBlock`` / ``ViTLayer`` / ``LunaBlock`` / ``PreNormLunaBlock`` / ``LunaLayer`` /
+``PreNormLunaLayer`` for ``model/Depthformer/{self_attention,feed_forward,vit_layer,luna_layer}.py`` -- same constructors,
+attribute names, ``state_dict`` keys and return values (the blocks return their attention maps, so the maps are
+materialised).
 
 The attention core -- ``softmax(q k^T * scale)`` returned as a (B, nH, S, S) map, times ``v`` -- runs in ONE CUDA kernel of
 ``libswin_attn.so`` (``mha_attention_forward``, csrc/mha_global.cu) instead of the reference's matmul / mul_ / softmax /
@@ -33,10 +34,10 @@ class _GlobalAttention(torch.autograd.Function):
     def backward(ctx, d_o, d_attn):
         q, k, v, attn = ctx.saved_tensors
         nh, scale = ctx.num_heads, ctx.scale
-        b, s, _ = q.shape
+        b = q.shape[0]
 
         def heads(t):
-            return t.reshape(b, s, nh, -1).transpose(1, 2).float()
+            return t.reshape(b, t.shape[1], nh, -1).transpose(1, 2).float()
 
         qh, kh, vh, doh = heads(q), heads(k), heads(v), heads(d_o)
         d_p = doh @ vh.transpose(-2, -1)
@@ -48,14 +49,15 @@ class _GlobalAttention(torch.autograd.Function):
         d_k = (d_s.transpose(-2, -1) @ qh) * scale
 
         def back(t, like):
-            return t.transpose(1, 2).reshape(b, s, -1).to(like.dtype)
+            return t.transpose(1, 2).reshape(b, like.shape[1], -1).to(like.dtype)
 
         return back(d_q, q), back(d_k, k), back(d_v, v), None, None
 
 
 def global_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, num_heads: int, scale: float) -> Tuple[torch.Tensor, torch.Tensor]:
-    """``attn = softmax(q k^T * scale)`` (B, nH, S, S) fp32 and ``o = attn v`` (B, S, D) for (B, S, D) projections whose
-    heads are consecutive channel groups (self_attention.py:36-40, :70-80)."""
+    """``attn = softmax(q k^T * scale)`` (B, nH, S, Sk) fp32 and ``o = attn v`` (B, S, Dv) for projections q (B, S, D),
+    k (B, Sk, D), v (B, Sk, Dv) whose heads are consecutive channel groups (self_attention.py:36-40, :70-80;
+    luna_layer.py:50-54, :85-94, :118-127)."""
     if not q.is_cuda:
         raise RuntimeError("global_attention needs CUDA tensors: this package has no CPU path (the oracle under oracle/ is the CPU restatement)")
     if torch.is_autocast_enabled():   # the Linears produced bf16 under autocast; the reference's matmuls run in it too
@@ -64,7 +66,27 @@ def global_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, num_head
     return _GlobalAttention.apply(q, k, v, num_heads, float(scale))
 
 
-class _SelfAttentionBase(nn.Module):
+def _attend(mod: nn.Module, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """The attention core of a block ``mod`` (``num_heads``, ``attn_scale``, ``attn_drop``): the kernel, or -- training with
+    attention dropout -- the kernel's map, ``nn.Dropout`` and the value product in torch, as the reference orders them: it
+    drops the probabilities that enter the value product and returns the un-dropped map (self_attention.py:74-80)."""
+    if mod.training and mod.attn_drop.p > 0.0:
+        _, attn = global_attention(q, k, v, mod.num_heads, mod.attn_scale)
+        b, sk, _ = v.shape
+        vh = v.view(b, sk, mod.num_heads, -1).transpose(1, 2)
+        out = torch.matmul(mod.attn_drop(attn).to(vh.dtype), vh).transpose(1, 2).reshape(b, q.shape[1], -1)
+        return out, attn
+    return global_attention(q, k, v, mod.num_heads, mod.attn_scale)
+
+
+class _AttentionCore(nn.Module):
+    """Blocks reach the attention core through this one method (the oracle's CPU copies override it)."""
+
+    def _attend(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        return _attend(self, q, k, v)
+
+
+class _SelfAttentionBase(_AttentionCore):
     def __init__(self, hidden_dim: int, key_query_dim: int, num_heads: int, attn_drop_prob: float, drop_prob: float):
         super().__init__()
         self.hidden_dim = hidden_dim
@@ -77,15 +99,7 @@ class _SelfAttentionBase(nn.Module):
             raise ValueError("the CUDA kernel serves head dims up to 64")
 
     def _core(self, hidden: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
-        q, k, v = self.query_proj(hidden), self.key_proj(hidden), self.value_proj(hidden)
-        if self.training and self.attn_drop.p > 0.0:
-            # the reference drops the probabilities that enter the value product and returns the un-dropped map (:76-80)
-            _, attn = global_attention(q, k, v, self.num_heads, self.attn_scale)
-            b, s, _ = v.shape
-            vh = v.view(b, s, self.num_heads, -1).transpose(1, 2)
-            out = torch.matmul(self.attn_drop(attn).to(vh.dtype), vh).transpose(1, 2).reshape(b, s, -1)
-            return out, attn
-        return global_attention(q, k, v, self.num_heads, self.attn_scale)
+        return self._attend(self.query_proj(hidden), self.key_proj(hidden), self.value_proj(hidden))
 
 
 class SelfAttentionBlock(_SelfAttentionBase):
@@ -190,3 +204,101 @@ class ViTLayer(nn.Module):
             hidden, attn_weight = self.self_attn(hidden)
             hidden = self.feed_forward(hidden)
         return hidden, attn_weight
+
+
+class _LunaBase(_AttentionCore):
+    """Luna: linear unified nested attention (luna_layer.py:10-131, :134-259): PACK -- K auxiliary tokens attend over the HW
+    image tokens, map (B, nH, K, HW) -- then UNPACK -- the image tokens attend over the K packed tokens, map (B, nH, HW, K).
+    Both are ``global_attention`` calls with different query and key counts."""
+
+    def __init__(self, hidden_dim: int, aux_dim: int, qk_proj_dim: int, num_heads: int, attn_drop_prob: float, drop_prob: float):
+        super().__init__()
+        self.hidden_dim, self.aux_dim, self.qk_proj_dim, self.num_heads = hidden_dim, aux_dim, qk_proj_dim, num_heads
+        if hidden_dim % num_heads != 0:
+            raise ValueError("Hidden dim not multiple of num heads.")
+        self.head_dim = hidden_dim // num_heads
+        if self.head_dim > 64 or qk_proj_dim % num_heads != 0 or qk_proj_dim // num_heads > 64:
+            raise ValueError("the CUDA kernel serves head dims up to 64 (qk_proj_dim must split over the heads)")
+
+    def _projections(self):
+        h, a, d = self.hidden_dim, self.aux_dim, self.qk_proj_dim
+        self.q1_proj, self.k1_proj, self.v1_proj, self.o1_proj = nn.Linear(a, d), nn.Linear(h, d), nn.Linear(h, h), nn.Linear(h, a)
+        self.q2_proj, self.k2_proj, self.v2_proj, self.o2_proj = nn.Linear(h, d), nn.Linear(a, d), nn.Linear(a, h), nn.Linear(h, h)
+
+    def _tail(self, attn_drop_prob, drop_prob):
+        self.attn_scale = math.sqrt(1.0 / self.head_dim)
+        self.attn_drop = nn.Dropout(attn_drop_prob, inplace=False)
+        self.drop = nn.Dropout(drop_prob, inplace=False)
+
+
+class LunaBlock(_LunaBase):
+    """Post-norm Luna sub-block (``luna_layer.py:10-131``): returns ``(out, aux_out, attn1, attn2)``."""
+
+    def __init__(self, hidden_dim: int, aux_dim: int, qk_proj_dim: int, num_heads: int, attn_drop_prob: float = 0.0, drop_prob: float = 0.1):
+        super().__init__(hidden_dim, aux_dim, qk_proj_dim, num_heads, attn_drop_prob, drop_prob)
+        self._projections()
+        self._tail(attn_drop_prob, drop_prob)
+        self.aux_norm = nn.LayerNorm(aux_dim, eps=1e-5)
+        self.norm = nn.LayerNorm(hidden_dim, eps=1e-5)
+
+    def forward(self, hidden: torch.Tensor, aux: torch.Tensor):
+        assert hidden.shape[2] == self.hidden_dim
+        out1, attn1 = self._attend(self.q1_proj(aux), self.k1_proj(hidden), self.v1_proj(hidden))
+        out1 = self.drop(self.o1_proj(out1))
+        aux_out = self.aux_norm(aux + out1)
+        out2, attn2 = self._attend(self.q2_proj(hidden), self.k2_proj(out1), self.v2_proj(out1))
+        out2 = self.drop(self.o2_proj(out2))
+        return self.norm(hidden + out2), aux_out, attn1, attn2
+
+
+class PreNormLunaBlock(_LunaBase):
+    """Pre-norm Luna sub-block (``luna_layer.py:134-259``)."""
+
+    def __init__(self, hidden_dim: int, aux_dim: int, qk_proj_dim: int, num_heads: int, attn_drop_prob: float = 0.0, drop_prob: float = 0.1):
+        super().__init__(hidden_dim, aux_dim, qk_proj_dim, num_heads, attn_drop_prob, drop_prob)
+        self.aux_norm = nn.LayerNorm(aux_dim, eps=1e-5)
+        self.inter_norm = nn.LayerNorm(aux_dim, eps=1e-5)
+        self.norm = nn.LayerNorm(hidden_dim, eps=1e-5)
+        self._projections()
+        self._tail(attn_drop_prob, drop_prob)
+
+    def forward(self, hidden: torch.Tensor, aux: torch.Tensor):
+        assert hidden.shape[2] == self.hidden_dim
+        aux_n, hidden_n = self.aux_norm(aux), self.norm(hidden)
+        out1, attn1 = self._attend(self.q1_proj(aux_n), self.k1_proj(hidden_n), self.v1_proj(hidden_n))
+        out1 = self.drop(self.o1_proj(out1))
+        aux_out = aux + out1
+        out_n = self.inter_norm(out1)
+        out2, attn2 = self._attend(self.q2_proj(hidden_n), self.k2_proj(out_n), self.v2_proj(out_n))
+        out2 = self.drop(self.o2_proj(out2))
+        return hidden + out2, aux_out, attn1, attn2
+
+
+class _LunaLayerBase(nn.Module):
+    def forward(self, hidden: torch.Tensor, aux: torch.Tensor):
+        """hidden (B, D, H, W), aux (B, K, aux_dim) -> (hidden (B, D, H, W), aux, attn1 (B, nH, K, HW), attn2 (B, nH, HW, K))."""
+        b, d, h, w = hidden.shape
+        hidden = hidden.view(b, d, h * w).transpose(1, 2).contiguous()
+        hidden, aux, attn1, attn2 = self.luna_attn(hidden, aux)
+        hidden = self.feed_forward(hidden)
+        return hidden.transpose(1, 2).reshape(b, d, h, w), aux, attn1, attn2
+
+
+class LunaLayer(_LunaLayerBase):
+    """``luna_layer.py:262-302``: post-norm Luna block + post-norm feed-forward."""
+
+    def __init__(self, hidden_dim: int, aux_dim: int, qk_proj_dim: int, num_heads: int, *, feedforward_dim: Optional[int] = None,
+                 attn_drop_prob: float = 0.0, drop_prob: float = 0.1, act_layer=nn.GELU):
+        super().__init__()
+        self.luna_attn = LunaBlock(hidden_dim, aux_dim, qk_proj_dim, num_heads, attn_drop_prob, drop_prob)
+        self.feed_forward = PostNormFeedForwardBlock(hidden_dim, feedforward_dim, drop_prob, act_layer, add_weight=1.0)
+
+
+class PreNormLunaLayer(_LunaLayerBase):
+    """``luna_layer.py:305-345``: pre-norm Luna block + pre-norm feed-forward."""
+
+    def __init__(self, hidden_dim: int, aux_dim: int, qk_proj_dim: int, num_heads: int, *, feedforward_dim: Optional[int] = None,
+                 attn_drop_prob: float = 0.0, drop_prob: float = 0.1, act_layer=nn.GELU):
+        super().__init__()
+        self.luna_attn = PreNormLunaBlock(hidden_dim, aux_dim, qk_proj_dim, num_heads, attn_drop_prob, drop_prob)
+        self.feed_forward = FeedForwardBlock(hidden_dim, feedforward_dim, drop_prob, act_layer, add_weight=1.0)

@@ -15,11 +15,12 @@ from mde_b200 import depthformer
 
 
 def global_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, num_heads: int, scale: float) -> Tuple[torch.Tensor, torch.Tensor]:
-    """q, k: (B, S, nH*dq), v: (B, S, nH*dv) -> o (B, S, nH*dv), attn (B, nH, S, S)."""
+    """q: (B, S, nH*dq), k: (B, Sk, nH*dq), v: (B, Sk, nH*dv) -> o (B, S, nH*dv), attn (B, nH, S, Sk).  Self-attention
+    (self_attention.py:70-80) has Sk = S; the two halves of a Luna block (luna_layer.py:85-94, :118-127) do not."""
     b, s, _ = q.shape
 
-    def heads(t):                                            # _reshape_qkv, self_attention.py:36-40
-        return t.view(b, s, num_heads, -1).transpose(1, 2).contiguous()
+    def heads(t):                                            # _reshape_qkv, self_attention.py:36-40; _reshape_3d, luna_layer.py:50-54
+        return t.reshape(b, t.shape[1], num_heads, -1).transpose(1, 2).contiguous()
 
     attn = torch.matmul(heads(q), heads(k).transpose(-2, -1))   # :72
     attn = attn * scale                                      # :73 (in place in the reference)
@@ -29,13 +30,12 @@ def global_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, num_head
 
 
 class _OracleCore:
-    def _core(self, hidden):
-        q, k, v = self.query_proj(hidden), self.key_proj(hidden), self.value_proj(hidden)
+    def _attend(self, q, k, v):
         out, attn = global_attention(q, k, v, self.num_heads, self.attn_scale)
         if self.training and self.attn_drop.p > 0.0:
-            b, s, _ = v.shape
-            vh = v.view(b, s, self.num_heads, -1).transpose(1, 2)
-            out = torch.matmul(self.attn_drop(attn), vh).transpose(1, 2).reshape(b, s, -1)
+            b, sk, _ = v.shape
+            vh = v.view(b, sk, self.num_heads, -1).transpose(1, 2)
+            out = torch.matmul(self.attn_drop(attn), vh).transpose(1, 2).reshape(b, q.shape[1], -1)
         return out, attn
 
 
@@ -47,5 +47,14 @@ class OraclePostNormSelfAttentionBlock(_OracleCore, depthformer.PostNormSelfAtte
     pass
 
 
+class OracleLunaBlock(_OracleCore, depthformer.LunaBlock):
+    pass
+
+
+class OraclePreNormLunaBlock(_OracleCore, depthformer.PreNormLunaBlock):
+    pass
+
+
 SWAP = {depthformer.SelfAttentionBlock: OracleSelfAttentionBlock,
-        depthformer.PostNormSelfAttentionBlock: OraclePostNormSelfAttentionBlock}
+        depthformer.PostNormSelfAttentionBlock: OraclePostNormSelfAttentionBlock,
+        depthformer.LunaBlock: OracleLunaBlock, depthformer.PreNormLunaBlock: OraclePreNormLunaBlock}

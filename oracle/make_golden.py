@@ -113,6 +113,23 @@ def depthformer_postnorm_sa(name, b, s, hidden, kq, nh):
                 attn=attn.detach(), cot_o=cot_o, dx=gs[0], dk_w=gs[1])
 
 
+def depthformer_luna(name, cls, b, h, w, hidden, aux_dim, qk, nh, k_tokens):
+    """model/Depthformer LunaLayer (post-norm) / PreNormLunaLayer: pack + unpack attention and the feed-forward, eval mode;
+    cotangents on all four outputs."""
+    Lm = rs.depthformer_luna_layer()
+    m = getattr(Lm, cls)(hidden, aux_dim, qk, nh).eval()
+    m.load_state_dict(synthetic_state(m))
+    x = randn(name + ".x", b, hidden, h, w).requires_grad_()
+    aux = randn(name + ".aux", b, k_tokens, aux_dim).requires_grad_()
+    outs = m(x, aux)
+    cots = [randn(f"{name}.cot{i}", *o.shape) for i, o in enumerate(outs)]
+    la = m.luna_attn
+    gs = torch.autograd.grad(sum((o * c).sum() for o, c in zip(outs, cots)), [x, aux, la.k1_proj.weight, la.q2_proj.weight, la.v2_proj.weight])
+    return dict(kind="depthformer_luna", cfg=dict(cls=cls, b=b, h=h, w=w, hidden=hidden, aux_dim=aux_dim, qk=qk, nh=nh, k=k_tokens),
+                x=x.detach(), aux=aux.detach(), outs=[o.detach() for o in outs], cots=cots, dx=gs[0], daux=gs[1], dk1_w=gs[2],
+                dq2_w=gs[3], dv2_w=gs[4])
+
+
 def masked_windows(name, ws, nw, groups, c, nh):
     """WindowAttention.forward(x, v, mask) on window-order tokens with an arbitrary mask."""
     L = rs.newcrf_layers()
@@ -229,6 +246,9 @@ CASES = {
     "depthformer_vit_hd64": lambda n: depthformer_vit(n, 2, 110, 128, 128, 2, 2),
     "depthformer_vit_kq32": lambda n: depthformer_vit(n, 1, 75, 128, 64, 2, 1),
     "depthformer_postnorm_sa": lambda n: depthformer_postnorm_sa(n, 1, 97, 192, 192, 3),
+    # Luna pack / unpack: K = 24 auxiliary tokens against 9 x 11 image tokens, head dim 64
+    "depthformer_luna_postnorm": lambda n: depthformer_luna(n, "LunaLayer", 2, 9, 11, 128, 96, 128, 2, 24),
+    "depthformer_luna_prenorm": lambda n: depthformer_luna(n, "PreNormLunaLayer", 1, 7, 9, 128, 128, 64, 2, 17),
     "newcrf_level": lambda n: newcrf_level(n, 1, 10, 13, 48, 64, 32, 2),
     "newcrfdepth_tiny07": lambda n: full_model(n, "tiny07", 1, 64, 96),
     # metrics only (same image / weights as newcrfdepth_tiny07; adds the realistic-range GT)

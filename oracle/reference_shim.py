@@ -175,6 +175,12 @@ def depthformer_vit_layer():
     return importlib.import_module("model.Depthformer.vit_layer")
 
 
+def depthformer_luna_layer():
+    install()
+    import importlib
+    return importlib.import_module("model.Depthformer.luna_layer")
+
+
 def depthformer_self_attention():
     install()
     import importlib

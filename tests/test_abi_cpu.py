@@ -27,8 +27,8 @@ def test_library_exports_every_declared_symbol():
 def test_shape_struct_matches_header_layout():
     # 8 x int32, 2 x float, uint64, 4 x int64, 2 x int32
     assert ctypes.sizeof(_lib.Shape) == 8 * 4 + 2 * 4 + 8 + 4 * 8 + 2 * 4
-    # mha_shape_t: 6 x int32, float, int32, 4 x int64
-    assert ctypes.sizeof(_lib.MhaShape) == 6 * 4 + 4 + 4 + 4 * 8
+    # mha_shape_t: 8 x int32, float, int32, 4 x int64
+    assert ctypes.sizeof(_lib.MhaShape) == 8 * 4 + 4 + 4 + 4 * 8
 
 
 @pytest.mark.parametrize("field,value,msg", [

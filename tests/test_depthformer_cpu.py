@@ -52,6 +52,38 @@ def test_postnorm_block_oracle_matches_reference(golden):
     assert rel_err(dx, g["dx"]) < TOL and rel_err(dk, g["dk_w"]) < TOL
 
 
+def luna_from_golden(g):
+    cfg = g["cfg"]
+    m = getattr(depthformer, cfg["cls"])(cfg["hidden"], cfg["aux_dim"], cfg["qk"], cfg["nh"])
+    m.load_state_dict(synthetic_state(m), strict=True)
+    return m.eval()
+
+
+def check_luna(m, g, x, aux, bound, check_fn):
+    outs = m(x, aux)
+    for i, (o, want) in enumerate(zip(outs, g["outs"])):
+        check_fn(rel_err(o.float(), want), bound, f"{g['cfg']['cls']} output {i}")
+    la = m.luna_attn
+    gs = torch.autograd.grad(sum((o.float() * c.to(o.device)).sum() for o, c in zip(outs, g["cots"])),
+                             [x, aux, la.k1_proj.weight, la.q2_proj.weight, la.v2_proj.weight])
+    for got, key in zip(gs, ["dx", "daux", "dk1_w", "dq2_w", "dv2_w"]):
+        check_fn(rel_err(got, g[key]), bound, f"{g['cfg']['cls']} {key}")
+    return outs
+
+
+@pytest.mark.parametrize("name", ["depthformer_luna_postnorm", "depthformer_luna_prenorm"])
+def test_luna_layer_oracle_matches_reference(golden, name):
+    g = golden(name)
+    m = to_oracle(luna_from_golden(g)).eval()
+
+    def plain(err, bound, what):
+        assert err < bound, what
+    outs = check_luna(m, g, g["x"].clone().requires_grad_(), g["aux"].clone().requires_grad_(), TOL, plain)
+    cfg = g["cfg"]
+    assert outs[2].shape == (cfg["b"], cfg["nh"], cfg["k"], cfg["h"] * cfg["w"])      # pack map (B, nH, K, HW)
+    assert outs[3].shape == (cfg["b"], cfg["nh"], cfg["h"] * cfg["w"], cfg["k"])      # unpack map (B, nH, HW, K)
+
+
 def test_reference_interface_and_errors():
     m = depthformer.ViTLayer(128, 64, 2, num_repeat=2)
     assert set(m.state_dict()) == {f"self_attn.{p}.{w}" for p in ("norm", "query_proj", "key_proj", "value_proj", "out_proj")
@@ -68,16 +100,16 @@ def test_reference_interface_and_errors():
 
 def test_c_abi_argument_checks():
     lib = _lib.load()
-    shp = _lib.MhaShape(1, 8, 2, 96, 64, _lib.F32, 0.125, 0, 192, 192, 128, 128)
+    shp = _lib.MhaShape(1, 8, 0, 2, 96, 64, _lib.F32, 0, 0.125, 0, 192, 192, 128, 128)
     dummy = ctypes.c_void_p(ctypes.addressof(ctypes.create_string_buffer(64)))
     assert lib.mha_attention_forward(ctypes.byref(shp), dummy, dummy, dummy, dummy, None, None) != 0
     assert "head dims must be in 1..64" in lib.swin_attn_last_error().decode()
-    shp = _lib.MhaShape(1, 4000, 2, 64, 64, _lib.F32, 0.125, 0, 128, 128, 128, 128)
+    shp = _lib.MhaShape(1, 8, 4000, 2, 64, 64, _lib.F32, 0, 0.125, 0, 128, 128, 128, 128)
     assert lib.mha_attention_forward(ctypes.byref(shp), dummy, dummy, dummy, dummy, None, None) != 0
     assert "shared memory" in lib.swin_attn_last_error().decode()
-    shp = _lib.MhaShape(1, 8, 2, 64, 64, _lib.F32, 0.125, 0, 100, 128, 128, 128)
+    shp = _lib.MhaShape(1, 8, 0, 2, 64, 64, _lib.F32, 0, 0.125, 0, 100, 128, 128, 128)
     assert lib.mha_attention_forward(ctypes.byref(shp), dummy, dummy, dummy, dummy, None, None) != 0
     assert "row strides" in lib.swin_attn_last_error().decode()
     assert lib.mha_attention_forward(ctypes.byref(shp), None, dummy, dummy, dummy, None, None) != 0
-    shp = _lib.MhaShape(0, 8, 2, 64, 64, _lib.F32, 0.125, 0, 128, 128, 128, 128)      # empty batch: nothing to do
+    shp = _lib.MhaShape(0, 8, 0, 2, 64, 64, _lib.F32, 0, 0.125, 0, 128, 128, 128, 128)      # empty batch: nothing to do
     assert lib.mha_attention_forward(ctypes.byref(shp), dummy, dummy, dummy, dummy, None, None) == 0

@@ -9,7 +9,7 @@ from mde_b200 import _lib, depthformer
 from oracle import global_attention as oga
 from oracle.synthetic import randn
 from conftest import check, rel_err
-from test_depthformer_cpu import postnorm_from_golden, vit_from_golden
+from test_depthformer_cpu import check_luna, luna_from_golden, postnorm_from_golden, vit_from_golden
 
 DEV = "cuda"
 TOL = {torch.float32: 1e-5, torch.bfloat16: 1e-2}
@@ -18,11 +18,11 @@ TOL = {torch.float32: 1e-5, torch.bfloat16: 1e-2}
 def _abi(q, k, v, nh, scale, want_map=True, impl=_lib.IMPL_AUTO):
     lib = _lib.load()
     b, s, dqk = q.shape
-    dvv = v.shape[2]
+    sk, dvv = v.shape[1], v.shape[2]
     o = torch.full((b, s, dvv), float("nan"), dtype=q.dtype, device=q.device)
-    attn = torch.full((b, nh, s, s), float("nan"), device=q.device) if want_map else None
-    shp = _lib.MhaShape(b, s, nh, dqk // nh, dvv // nh, _lib.F32 if q.dtype == torch.float32 else _lib.BF16, scale, impl,
-                        q.stride(1), k.stride(1), v.stride(1), o.stride(1))
+    attn = torch.full((b, nh, s, sk), float("nan"), device=q.device) if want_map else None
+    shp = _lib.MhaShape(b, s, sk if sk != s else 0, nh, dqk // nh, dvv // nh, _lib.F32 if q.dtype == torch.float32 else _lib.BF16, impl,
+                        scale, 0, q.stride(1), k.stride(1), v.stride(1), o.stride(1))
     rc = lib.mha_attention_forward(ctypes.byref(shp), ctypes.c_void_p(q.data_ptr()), ctypes.c_void_p(k.data_ptr()),
                                    ctypes.c_void_p(v.data_ptr()), ctypes.c_void_p(o.data_ptr()),
                                    ctypes.c_void_p(attn.data_ptr()) if want_map else None,
@@ -56,6 +56,38 @@ def test_kernel_matches_oracle_through_the_c_abi(dtype, b, s, nh, dq, dv):
         assert not torch.equal(o3, o)
         check(rel_err(attn3, attn), 1e-5, f"{name} tcgen05 map vs CUDA-core map")
         check(rel_err(o3.float(), o.float()), 1e-2, f"{name} tcgen05 output vs CUDA-core output")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("b,s,sk,nh,dq,dv", [(2, 32, 418, 4, 64, 64),     # Luna pack: K auxiliary tokens over the image tokens
+                                             (2, 418, 32, 4, 64, 64),     # Luna unpack
+                                             (1, 7, 300, 2, 64, 64), (1, 300, 17, 2, 64, 64), (1, 5, 9, 1, 16, 8), (1, 130, 450, 1, 64, 64)])
+def test_cross_attention_matches_oracle_through_the_c_abi(dtype, b, s, sk, nh, dq, dv):
+    name = f"mhax.{b}.{s}.{sk}.{nh}.{dq}.{dv}"
+    q = randn(name + ".q", b, s, nh * dq).to(DEV).to(dtype)
+    kv = randn(name + ".kv", b, sk, nh * (dq + dv)).to(DEV).to(dtype)
+    k, v = kv[..., :nh * dq], kv[..., nh * dq:]
+    scale = dv ** -0.5                                                   # the Luna blocks scale by the VALUE head dim (luna_layer.py:43)
+    o, attn = _abi(q, k, v, nh, scale)
+    ro, ra = oga.global_attention(q.double(), k.double(), v.double(), nh, scale)
+    assert attn.shape == (b, nh, s, sk)
+    check(rel_err(attn, ra), 1e-5, f"{name} {dtype} map vs oracle")
+    check(rel_err(o.float(), ro), TOL[dtype], f"{name} {dtype} output vs oracle")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["depthformer_luna_postnorm", "depthformer_luna_prenorm"])
+def test_luna_layer_vs_reference_golden(golden, name):
+    g = golden(name)
+    m = luna_from_golden(g).to(DEV)
+    launches = _lib.launch_count()
+    check_luna(m, g, g["x"].to(DEV).requires_grad_(), g["aux"].to(DEV).requires_grad_(), 1e-5, check)
+    assert _lib.launch_count() - launches == 2                           # pack + unpack: one kernel of ours each
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        outs = m(g["x"].to(DEV), g["aux"].to(DEV))
+    for i, (o, want) in enumerate(zip(outs, g["outs"])):
+        check(rel_err(o.float(), want), 1e-2, f"{name} bf16 output {i}")
 
 
 @pytest.mark.gpu
