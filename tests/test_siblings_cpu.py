@@ -94,3 +94,30 @@ def test_oda_block_keeps_the_reference_interface(golden):
     assert small.window_size == 6 and small.shift_size == 0 and small.attn_mask is None   # oda_swin_transformer.py:55-58
     with pytest.raises(AssertionError):
         to_oracle(blk)(torch.zeros(1, 5, cfg["c"]))
+
+
+def test_integration_recipe_names_exist_in_the_reference():
+    """INTEGRATION.md §1 'Sibling model families': every attribute the recipe assigns exists in the reference modules
+    (staged copy or /root/reference) and in the drop-in modules."""
+    from oracle import reference_shim as rs
+    if not rs.available():
+        pytest.skip("reference not staged")
+    from mde_b200 import depthformer as dfm
+    oda2, oda = rs.oda2_swin_transformer(), rs.oda_swin_transformer()
+    for name, ours in [("WindowAttention", siblings.Oda2WindowAttention), ("SwinTransformerBlock", siblings.Oda2SwinTransformerBlock),
+                       ("SwinTransformerStage", siblings.Oda2SwinTransformerStage), ("PatchMerging", siblings.Oda2PatchMerging)]:
+        assert hasattr(oda2, name) and isinstance(ours, type)
+    assert hasattr(oda, "SwinTransformerBlock")
+    sa, luna = rs.depthformer_self_attention(), rs.depthformer_luna_layer()
+    for mod, names in [(sa, ["SelfAttentionBlock", "PostNormSelfAttentionBlock"]), (luna, ["LunaBlock", "PreNormLunaBlock", "LunaLayer", "PreNormLunaLayer"]),
+                       (rs.depthformer_vit_layer(), ["ViTLayer", "SelfAttentionBlock", "FeedForwardBlock"])]:
+        for n in names:
+            assert hasattr(mod, n) and hasattr(dfm, n), n
+    # same state_dict keys as the reference modules
+    ref = luna.PreNormLunaBlock(64, 32, 64, 2)
+    assert set(ref.state_dict()) == set(dfm.PreNormLunaBlock(64, 32, 64, 2).state_dict())
+    ref = oda2.SwinTransformerStage(dim=64, depth=2, num_heads=2, window_size=7, downsample=oda2.PatchMerging)
+    ours = siblings.Oda2SwinTransformerStage(dim=64, depth=2, num_heads=2, window_size=7, downsample=siblings.Oda2PatchMerging)
+    assert set(ref.state_dict()) == set(ours.state_dict())
+    ref = oda.SwinTransformerBlock(64, (14, 14), 2, window_size=7, shift_size=3)
+    assert set(ref.state_dict()) == set(siblings.OdaSwinTransformerBlock(64, (14, 14), 2, window_size=7, shift_size=3).state_dict())
