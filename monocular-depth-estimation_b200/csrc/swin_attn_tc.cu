@@ -78,7 +78,7 @@ __host__ __device__ inline SmemMapF smem_map_f() {
   return m;
 }
 
-template <bool kShifted>
+template <bool kShifted, bool kDrop>
 __global__ void __launch_bounds__(kThreadsF, 1)
 tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __grid_constant__ TmaMapsF maps) {
   constexpr bool kPerm = kShifted;
@@ -433,6 +433,31 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       w[24] = pack_bf16(fast_exp2(__uint_as_float(r[N - 1]) - mx), 0.f);
 #pragma unroll
       for (int e = 25; e < 32; ++e) w[e] = 0u;
+      // Attention dropout (nn.Dropout on the softmax output, newcrf_layers.py:137 / swin_transformer.py:139; training
+      // only): the probabilities are dropped in registers between the two MMAs with the counter-hash mask the CUDA-core
+      // kernels and both backward kernels regenerate (swin_common.cuh), keyed by (window, head, query token, key token).
+      // The ones column would then sum the DROPPED row, so the normaliser -- the sum of the un-dropped bf16 values -- is
+      // taken here, and 1 / (1 - p) goes into the output scale.
+      float lsum = 0.f, keep_scale = 1.f;
+      if (kDrop) {
+        const Dropout drop = make_dropout(p, it.w, h, N);
+        keep_scale = drop.keep_scale;
+        const uint64_t rbase = drop.base + (uint64_t)(ri * WS + rj) * N;
+        float l4[2] = {0.f, 0.f};
+#pragma unroll
+        for (int e = 0; e < 25; ++e) {
+          const float p0 = __uint_as_float(w[e] << 16), p1 = __uint_as_float(w[e] & 0xffff0000u);
+          l4[0] += p0;
+          l4[1] += p1;
+          const int c0 = row_i<kPerm>(2 * e) * WS + row_j<kPerm>(2 * e);
+          if (dropout_hash(drop.seed, rbase + c0) < drop.threshold) w[e] &= 0xffff0000u;
+          if (2 * e + 1 < N) {
+            const int c1k = row_i<kPerm>(2 * e + 1) * WS + row_j<kPerm>(2 * e + 1);
+            if (dropout_hash(drop.seed, rbase + c1k) < drop.threshold) w[e] &= 0x0000ffffu;
+          }
+        }
+        lsum = l4[0] + l4[1];
+      }
       if (padm != 0) {   // V rows of pad tokens are zero: their share of O is (their summed probability) x v_pad = P cols 49 / 50 x V rows 49 / 50
         float pp = 0.f;
 #pragma unroll
@@ -463,7 +488,7 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       uint32_t o[32];
       TMEM_LD_X16(o_addr, (o + 0));
       TMEM_LD_X16(o_addr + 16, (o + 16));
-      const float l = __uint_as_float(tmem_ld_x1(taddr + 64));   // row sum: P x ones column
+      float l = __uint_as_float(tmem_ld_x1(taddr + 64));   // row sum: P x ones column
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(bar_r + 8 * g);
@@ -472,7 +497,8 @@ tc_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       // O row / rowsum -> bf16 -> 64B-swizzled staging tile -> TMA tensor store with the boxes of the loads: window
       // reverse, inverse shift and the final crop (newcrf_layers.py:239-249) are tensor-map addressing; out-of-bounds
       // elements (padding tokens) are clipped by the TMA unit.
-      const float inv1 = 1.0f / l;
+      if (kDrop) l = lsum;                   // the ones column summed the dropped row
+      const float inv1 = kDrop ? keep_scale / l : 1.0f / l;
       const float2 inv = make_float2(inv1, inv1);
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) {
@@ -619,7 +645,6 @@ int tc::sm_count() {
 
 bool tc_forward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
-  if (p.dropout_p > 0.0f) return false;   // attention dropout (unused by NewCRFs) is served by the CUDA-core kernels
   if (p.shift != 0 && p.shift != tc::kShift) return false;
   // TMA: 16-byte aligned base pointers and strides
   if ((p.q_ps | p.k_ps | p.v_ps | p.o_ps) & 7) return false;
@@ -641,7 +666,9 @@ cudaError_t launch_tc_forward(const Problem& p, cudaStream_t st, const char** er
     }
   }
   const tcf::SmemMapF map = tcf::smem_map_f();
-  auto kernel = shifted ? tcf::tc_fwd_kernel<true> : tcf::tc_fwd_kernel<false>;
+  const bool drop = p.dropout_p > 0.0f;
+  auto kernel = shifted ? (drop ? tcf::tc_fwd_kernel<true, true> : tcf::tc_fwd_kernel<true, false>)
+                        : (drop ? tcf::tc_fwd_kernel<false, true> : tcf::tc_fwd_kernel<false, false>);
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)map.total);
   if (e != cudaSuccess) {
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";

@@ -88,7 +88,7 @@ __host__ __device__ inline SmemMapB smem_map_b() {
   return m;
 }
 
-template <bool kShifted>
+template <bool kShifted, bool kDrop>
 __global__ void __launch_bounds__(kThreadsB, 1)
 tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __grid_constant__ TmaMapsB maps) {
   constexpr bool kPerm = kShifted;
@@ -430,6 +430,24 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
           r[j] = __float_as_uint(fast_exp2(t));
         }
       }
+      // Attention dropout (training with attn_drop > 0): the forward multiplied P by keep / (1 - p) before the value
+      // product, so dP is multiplied by the same factor here (the mask is regenerated from the counter hash,
+      // swin_common.cuh) and dV is taken with the DROPPED probabilities; delta and dS then follow unchanged.
+      uint64_t km = ~0ull;
+      float ks = 1.f;
+      if (kDrop) {
+        const Dropout drop = make_dropout(p, it.w, h, N);
+        ks = drop.keep_scale;
+        const uint64_t rbase = drop.base + (uint64_t)(ri * WS + rj) * N;
+        km = 0;
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const bool keep = dropout_hash(drop.seed, rbase + row_i<kPerm>(j) * WS + row_j<kPerm>(j)) >= drop.threshold;
+          km |= (uint64_t)keep << j;
+          d[j] = keep ? __float_as_uint(__uint_as_float(d[j]) * ks) : 0u;
+        }
+      }
+      auto kept = [&](int j) { return kDrop ? (((km >> j) & 1) ? ks : 0.f) : 1.f; };   // factor on P for the dV product
       // delta = sum_j P_ij dP_ij ; dS = P (dP - delta)
       float2 acc = make_float2(0.f, 0.f), acc_b = make_float2(0.f, 0.f);
 #pragma unroll
@@ -446,7 +464,7 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
       for (int e = 0; e < 24; ++e) {
         const float2 pp = make_float2(__uint_as_float(r[2 * e]), __uint_as_float(r[2 * e + 1]));
         const float2 ds = __fmul2_rn(pp, __fadd2_rn(make_float2(__uint_as_float(d[2 * e]), __uint_as_float(d[2 * e + 1])), nd));
-        wp[e] = pack_bf16(pp.x, pp.y);
+        wp[e] = kDrop ? pack_bf16(pp.x * kept(2 * e), pp.y * kept(2 * e + 1)) : pack_bf16(pp.x, pp.y);
         wd[e] = pack_bf16(ds.x, ds.y);
       }
       {
@@ -458,12 +476,12 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
           for (int j = 0; j < N; ++j) {
             if ((padded >> j) & 1) {
               const float pj = __uint_as_float(r[j]);
-              u_pad += pj;
+              u_pad += pj * kept(j);
               s_pad = fmaf(pj, __uint_as_float(d[j]) - delta, s_pad);
             }
           }
         }
-        wp[24] = pack_bf16(pl, u_pad);
+        wp[24] = pack_bf16(pl * kept(N - 1), u_pad);
         wd[24] = pack_bf16(dl, s_pad);
       }
       if (!valid) {   // missing second tile of the job's last pair (warp-uniform): its stage bytes are not data
@@ -605,7 +623,6 @@ tc_bwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __
 // ---- host side ------------------------------------------------------------------
 bool tc_backward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 7 || p.mask != nullptr) return false;
-  if (p.dropout_p > 0.0f) return false;   // attention dropout (unused by NewCRFs) is served by the CUDA-core kernels
   if (p.shift != 0 && p.shift != tc::kShift) return false;
   // un-padded tensors (H, W not multiples of the window) are served here and only here: TMA zero fill + pad vectors
   if ((p.q_ps | p.k_ps | p.v_ps | p.C) & 7) return false;
@@ -630,7 +647,9 @@ cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** e
     }
   }
   const tcb::SmemMapB map = tcb::smem_map_b();
-  auto kernel = shifted ? tcb::tc_bwd_kernel<true> : tcb::tc_bwd_kernel<false>;
+  const bool drop = p.dropout_p > 0.0f;
+  auto kernel = shifted ? (drop ? tcb::tc_bwd_kernel<true, true> : tcb::tc_bwd_kernel<true, false>)
+                        : (drop ? tcb::tc_bwd_kernel<false, true> : tcb::tc_bwd_kernel<false, false>);
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)map.total);
   if (e != cudaSuccess) {
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";

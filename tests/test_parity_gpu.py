@@ -526,17 +526,23 @@ def _dropout_scale(seed, n_win, nh, n, p):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("case", [(7, 3, 2, 14, 21, 2), (12, 6, 1, 24, 12, 3)])
+@pytest.mark.parametrize("case", [(7, 3, 2, 14, 21, 2), (7, 0, 1, 21, 14, 3), (7, 3, 1, 16, 23, 2), (12, 6, 1, 24, 12, 3)])
 def test_attention_dropout_matches_oracle_with_the_same_mask(case, dtype):
     """p > 0 (unused by NewCRFs, but part of the module signature): forward and backward against the oracle fed
-    with the numpy restatement of the kernel's counter-based mask; plus keep-rate statistics."""
+    with the numpy restatement of the kernel's counter-based mask; plus keep-rate statistics.  bf16 / window 7 runs on
+    the tcgen05 kernels (the probabilities are dropped in registers between the two MMAs, forward and backward), every
+    other case on the CUDA cores -- all with the same mask."""
     ws, shift, b, h, w, nh = case
+    if dtype == torch.bfloat16 and ws == 7:
+        shp = _lib.Shape(b, h, w, nh, ws, shift, _lib.BF16, _lib.IMPL_AUTO, 32 ** -0.5, 0.25, 123456789, 3 * nh * 32, 3 * nh * 32,
+                         3 * nh * 32, nh * 32, 0, 0)
+        assert _lib.load().swin_attn_uses_tcgen05(ctypes.byref(shp), 0) == 1 and _lib.load().swin_attn_uses_tcgen05(ctypes.byref(shp), 1) == 1
     c, n, p, seed = nh * 32, ws * ws, 0.25, 123456789
     name = f"drop{case}"
     packed = randn(name + ".p", b, h, w, 3 * c).to(dtype)
     table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
     cot = randn(name + ".c", b, h, w, c).to(dtype)
-    n_win = b * (h // ws) * (w // ws)
+    n_win = b * -(-h // ws) * -(-w // ws)
     scale = _dropout_scale(seed, n_win, nh, n, p)
     assert abs(float((scale > 0).float().mean()) - (1 - p)) < 0.01
     pr, tr = packed.double().requires_grad_(), table.double().requires_grad_()
