@@ -122,7 +122,7 @@ static int backward_impl(const swin_attn_shape_t* shape, const void* q, const vo
   bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_backward_supported(p, shape->dtype);
   if (shape->impl == SWIN_ATTN_IMPL_TCGEN05 && !want_tc) return fail("tcgen05 backward does not support this shape/dtype");
   if (ragged && !want_tc)
-    return fail("backward on un-padded tensors needs the tcgen05 kernel (bf16, window 7, shift 0 or 3, no mask, no dropout, 16-byte "
+    return fail("backward on un-padded tensors needs the tcgen05 kernel (bf16, window 7, shift 0 or 3, no mask, 16-byte "
                 "aligned tensors); pad explicitly otherwise");
   if (want_tc) {
     const char* why = nullptr;

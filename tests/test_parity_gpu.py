@@ -548,10 +548,17 @@ def test_attention_dropout_matches_oracle_with_the_same_mask(case, dtype):
     pr, tr = packed.double().requires_grad_(), table.double().requires_grad_()
     o_ref, _ = wa.window_attention(pr[..., :c], pr[..., c:2 * c], pr[..., 2 * c:], tr, ws, shift, nh, drop_scale=scale.double())
     g_ref = torch.autograd.grad((o_ref * cot.double()).sum(), [pr, tr])
+    tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
+    if h % ws or w % ws:
+        # un-padded tensors (the kernels zero-fill the padding tokens): forward only -- the op differentiates window-aligned
+        # tensors, the layers pad explicitly when they train with attention dropout (layers.py::_fused_pad_backward)
+        with torch.no_grad():
+            o = ops.window_attention(packed.to(DEV), None, table.to(DEV), ws, shift, nh, dropout_p=p, seed=seed)
+        check(rel_err(o.float(), o_ref.detach()), tol, f"dropout forward on un-padded tensors {case} {dtype}")
+        return
     pg, tg = packed.to(DEV).requires_grad_(), table.to(DEV).requires_grad_()
     o = ops.window_attention(pg, None, tg, ws, shift, nh, dropout_p=p, seed=seed)
     g = torch.autograd.grad((o.float() * cot.to(DEV).float()).sum(), [pg, tg])
-    tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
     assert rel_err(o.float(), o_ref) < tol
     assert rel_err(g[0].float(), g_ref[0]) < tol and rel_err(g[1], g_ref[1]) < tol
     # a different seed gives a different mask; p = 0 ignores the seed
