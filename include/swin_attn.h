@@ -248,7 +248,7 @@ void swin_attn_time_next_launch(void* start_event, void* stop_event);
  * apart (slices of a packed projection are fine), batches seq (kv_seq) rows apart.  kv_seq = 0 means kv_seq = seq.
  * Two kernels: tcgen05 (bf16, both head dims 64, 16 <= kv_seq <= 448, 16-byte aligned pointers, row strides multiples of 8
  * -- the Depthformer shapes; S and the bf16 P live in tensor memory, fp32 softmax) and CUDA cores (fp32 math for both
- * dtypes -- the fp32 mode must hold 1e-5 --, head dims <= 64 with qk_head_dim a multiple of 4, kv_seq <= 1664).  Attention
+ * dtypes -- the fp32 mode must hold 1e-5 --, head dims <= 64 with qk_head_dim a multiple of 4, kv_seq <= 1472).  Attention
  * dropout is not applied (the reference returns the un-dropped map; callers that train with attn_drop_prob > 0 apply it to
  * attn_map themselves). */
 typedef struct {

@@ -48,8 +48,8 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
                                                            const T* __restrict__ v, T* __restrict__ o, float* __restrict__ attn) {
   extern __shared__ __align__(16) float sm[];
   float* sq = sm;                                   // [kRows][dq]
-  float* skv = sq + kRows * a.dq;                   // [kKeys][kTileStride]
-  float* ss = skv + kKeys * kTileStride;      // [kRows][s_pad]
+  float* skv0 = sq + kRows * a.dq;                  // 2 x [kKeys][kTileStride]: tile t in buffer t & 1
+  float* ss = skv0 + 2 * kKeys * kTileStride;       // [kRows][s_pad]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int row0 = blockIdx.x * kRows, h = blockIdx.y, b = blockIdx.z;
   const T* qb = q + (int64_t)b * a.S * a.q_rs + h * a.dq;
@@ -61,15 +61,35 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     sq[i] = row0 + r < a.S ? ldf(qb + (int64_t)(row0 + r) * a.q_rs + d) : 0.f;
   }
 
+  // K / V tiles: the global loads of tile t + 1 are issued into registers BEFORE tile t is consumed and stored to the other
+  // buffer after it, so their latency hides behind the FMAs (a tile is 64 x d <= 4096 values: <= 16 per thread).
+  constexpr int kStage = kKeys * kMaxHeadDim / kThreads;
+  float stage[kStage];
+  auto tile_load = [&](const T* base, int64_t rs, int d_head, int c0) {
+#pragma unroll
+    for (int u = 0; u < kStage; ++u) {
+      const int i = tid + u * kThreads, r = i / d_head, d = i - r * d_head;
+      stage[u] = (i < kKeys * d_head && c0 + r < a.Sk) ? ldf(base + (int64_t)(c0 + r) * rs + d) : 0.f;
+    }
+  };
+  auto tile_store = [&](float* buf, int d_head) {
+#pragma unroll
+    for (int u = 0; u < kStage; ++u) {
+      const int i = tid + u * kThreads, r = i / d_head, d = i - r * d_head;
+      if (i < kKeys * d_head) buf[r * kTileStride + d] = stage[u];
+    }
+  };
+  const int n_tiles = a.s_pad / kKeys;
+
   // ---- logits: thread (j = tid % 64, ig = tid / 64) owns S[ig + 4 r][chunk + j], r = 0..7 ----
   const int j = tid & (kKeys - 1), ig = tid >> 6;
-  for (int c0 = 0; c0 < a.s_pad; c0 += kKeys) {
-    __syncthreads();                                // sq ready / previous tile consumed
-    for (int i = tid; i < kKeys * a.dq; i += kThreads) {
-      const int r = i / a.dq, d = i - r * a.dq;
-      skv[r * kTileStride + d] = c0 + r < a.Sk ? ldf(kb + (int64_t)(c0 + r) * a.k_rs + d) : 0.f;
-    }
-    __syncthreads();
+  tile_load(kb, a.k_rs, a.dq, 0);
+  tile_store(skv0, a.dq);
+  __syncthreads();                                  // sq and tile 0 ready
+  for (int t = 0; t < n_tiles; ++t) {
+    const int c0 = t * kKeys;
+    const float* skv = skv0 + (t & 1) * kKeys * kTileStride;
+    if (t + 1 < n_tiles) tile_load(kb, a.k_rs, a.dq, c0 + kKeys);
     float acc[8] = {};
     const float4* kr = reinterpret_cast<const float4*>(skv + j * kTileStride);
     for (int d4 = 0; d4 < a.dq / 4; ++d4) {      // qk_head_dim is a multiple of 4 (checked by the entry point)
@@ -83,8 +103,10 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     const bool live = c0 + j < a.Sk;
 #pragma unroll
     for (int r = 0; r < 8; ++r) ss[(ig + 4 * r) * a.s_pad + c0 + j] = live ? acc[r] * a.scale : -INFINITY;
+    if (t + 1 < n_tiles) tile_store(skv0 + ((t + 1) & 1) * kKeys * kTileStride, a.dq);
+    __syncthreads();                                // next tile stored, this one consumed, logits visible
   }
-  __syncthreads();
+  tile_load(vb, a.v_rs, a.dv, 0);                   // first V tile: in flight during the softmax
 
   // ---- softmax: warp w owns rows w, w + 8, w + 16, w + 24; the normalised row goes to smem and to the map ----
   for (int r = warp; r < kRows; r += kThreads / 32) {
@@ -113,13 +135,12 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
 
   // ---- o = P v: thread (d = tid % 64, ig) owns o[ig + 4 r][d] ----
   float acc[8] = {};
-  for (int c0 = 0; c0 < a.s_pad; c0 += kKeys) {
-    __syncthreads();                                // P ready / previous tile consumed
-    for (int i = tid; i < kKeys * a.dv; i += kThreads) {
-      const int r = i / a.dv, d = i - r * a.dv;
-      skv[r * kTileStride + d] = c0 + r < a.Sk ? ldf(vb + (int64_t)(c0 + r) * a.v_rs + d) : 0.f;
-    }
-    __syncthreads();
+  tile_store(skv0, a.dv);
+  __syncthreads();                                  // P rows and V tile 0 ready
+  for (int t = 0; t < n_tiles; ++t) {
+    const int c0 = t * kKeys;
+    const float* skv = skv0 + (t & 1) * kKeys * kTileStride;
+    if (t + 1 < n_tiles) tile_load(vb, a.v_rs, a.dv, c0 + kKeys);
     if (j < a.dv) {
       for (int kk = 0; kk < kKeys; kk += 4) {
         const float v0 = skv[kk * kTileStride + j], v1 = skv[(kk + 1) * kTileStride + j];
@@ -131,6 +152,8 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
         }
       }
     }
+    if (t + 1 < n_tiles) tile_store(skv0 + ((t + 1) & 1) * kKeys * kTileStride, a.dv);
+    __syncthreads();
   }
   if (j < a.dv) {
 #pragma unroll
@@ -145,7 +168,7 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
 
 size_t mha_forward_smem_bytes(int kv_seq, int qk_head_dim) {
   const int s_pad = (kv_seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
-  return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + (size_t)mha::kKeys * mha::kTileStride + (size_t)mha::kRows * s_pad);
+  return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + 2 * (size_t)mha::kKeys * mha::kTileStride + (size_t)mha::kRows * s_pad);
 }
 
 cudaError_t launch_mha_forward(int dtype, int batch, int seq, int kv_seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,

@@ -499,7 +499,7 @@ int mha_attention_forward(const mha_shape_t* s, const void* q, const void* k, co
   }
   const size_t smem = mha_forward_smem_bytes(kv_seq, s->qk_head_dim);
   if (smem > 227u * 1024u)
-    return fail("mha forward: " + std::to_string(kv_seq) + " keys need " + std::to_string(smem) + " B of shared memory per CTA (limit 232448; kv_seq <= 1664)");
+    return fail("mha forward: " + std::to_string(kv_seq) + " keys need " + std::to_string(smem) + " B of shared memory per CTA (limit 232448; kv_seq <= 1472)");
   cudaError_t e = launch_mha_forward(s->dtype, s->batch, s->seq, kv_seq, s->num_heads, s->qk_head_dim, s->v_head_dim, s->q_row_stride,
                                      s->k_row_stride, s->v_row_stride, s->o_row_stride, s->scale, q, k, v, o, attn_map,
                                      static_cast<cudaStream_t>(stream));
