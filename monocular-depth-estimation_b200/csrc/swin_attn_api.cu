@@ -130,6 +130,11 @@ static int backward_impl(const swin_attn_shape_t* shape, const void* q, const vo
     if (e != cudaSuccess) return why ? fail(std::string("tcgen05 backward: ") + why) : fail_cuda("tcgen05 backward launch", e);
     return 0;
   }
+  if (shape->impl == SWIN_ATTN_IMPL_AUTO && mma12_backward_supported(p, shape->dtype)) {   // window 12: warp-MMA kernel
+    cudaError_t e = launch_mma12_backward(p, st);
+    if (e != cudaSuccess) return fail_cuda("window-12 backward launch", e);
+    return 0;
+  }
   cudaError_t e = launch_simt_backward(p, shape->dtype, st);
   if (e != cudaSuccess) return fail_cuda("backward launch", e);
   return 0;
