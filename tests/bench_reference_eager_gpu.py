@@ -9,9 +9,11 @@ reference modules) -- next to the fused kernel, on the stage grids of NewCRFs Sw
     python tests/bench_reference_eager_gpu.py [--iters 10] [--only NAME] [--bwd]
     python tests/bench_reference_eager_gpu.py --model     # whole NewCRFs Swin-L forward, reference op sequence on the GPU
 
-``--model`` is the "stronger bar" of SURVEY.md 8d / BASELINE.md 4: the reference's own eager op sequence (oracle/cpu_model.py,
-the restatement pinned against the reference modules) on the same B200 in fp32 and under torch.autocast(bf16), batch 8 at
-352x1216, beside this repo's model (harness.infer on a prepare_inference'd model).
+``--model`` is the "stronger bar" of SURVEY.md 8d / BASELINE.md 4: the UNMODIFIED reference ``NewCRFDepth("large07")`` (staged
+copy ``oracle/_ref``, built by ``oracle/ref_model.py``; no product module or kernel in it) on the same B200 in fp32 and under
+torch.autocast(bf16), batch 8 at 352x1216, beside this repo's model (harness.infer on a prepare_inference'd model).  The same
+numbers are the ``reference_gpu_eager`` key of the default ``bench.py`` line.  (The per-op mode above times the oracle's
+restatement of the scoped path, i.e. the reference's eager OP SEQUENCE, not its modules.)
 """
 import argparse
 import json
@@ -48,11 +50,13 @@ def timed(fn, iters, flush):
 def model_mode(iters):
     import mde_b200
     from mde_b200.harness import build_model, infer, prepare_inference, synthetic_images
-    from oracle.cpu_model import to_oracle
+    from oracle import ref_model
+    if not ref_model.available():
+        raise SystemExit("the staged reference (oracle/_ref) is missing: run __graft_entry__.build() where /root/reference exists")
     dev = torch.device("cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     model = build_model("large07", 80.0, seed=0, device=dev).eval()
-    ref = to_oracle(model, dev).eval()
+    ref = ref_model.build_newcrfs("large07", 80.0, seed=0, synthetic=True, device=dev).eval()   # the reference's own modules
     images = synthetic_images(8, 352, 1216, seed=0).to(dev)
     out = {}
     with torch.no_grad():
