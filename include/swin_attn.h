@@ -260,6 +260,18 @@ typedef struct {
 } mha_shape_t;
 int mha_attention_forward(const mha_shape_t* shape, const void* q, const void* k, const void* v, void* o, float* attn_map, void* stream);
 
+/* The same attention with an ORDERED bias -- the "pluggable bias source" of the ODA2 depth-order decoder windows
+ * (`PreNormOrderedSwinSA.forward`, model/ODA2/oda2_red_order_swin2_decoder.py:88-93, :112-117): every
+ * token carries an integer index (its depth bin), and
+ *     logit(i, j) = q_i . k_j * scale + index_bias[token_index[i] - token_index[j] + num_emb - 1, head]
+ * (the `F.embedding` gather of `depth_embedding` by the pairwise index difference, added after the scaling, before the
+ * softmax; no shift mask).  A window of the reference is one batch element here: q, k, v are the projections of the
+ * window-partitioned tokens, (num_windows * B, r * r, C).  token_index: (batch, seq) int32 in [0, num_emb); index_bias:
+ * (2 * num_emb - 1, num_heads) fp32.  Self-attention only (kv_seq == seq).  The tcgen05 kernel needs num_emb <= 256 on top of
+ * its other conditions; otherwise the CUDA-core kernel runs. */
+int mha_attention_forward_ordered(const mha_shape_t* shape, const void* q, const void* k, const void* v, const int32_t* token_index,
+                                  const float* index_bias, int32_t num_emb, void* o, float* attn_map, void* stream);
+
 /* Measurement probe: median, in microseconds, of `reps` event brackets (as armed by swin_attn_time_next_launch) around an
  * EMPTY 148 x 384 kernel that follows a running kernel in `stream`, with (with_memset != 0) or without the backward's
  * memset in front of it: the fixed cost every event-timed attention launch carries (about 5 us / 8 us on a B200).

@@ -37,6 +37,7 @@ EXPORTS = (
     "swin_linear_gelu_forward_train",
     "swin_linear_bias_grad",
     "mha_attention_forward",
+    "mha_attention_forward_ordered",
     "swin_attn_time_next_launch",
     "swin_attn_probe_empty_bracket_us",
     "swin_attn_launch_count",
@@ -93,6 +94,8 @@ def load() -> ctypes.CDLL:
     lib.swin_attn_forward_host_static.restype = c_int
     lib.mha_attention_forward.argtypes = [POINTER(MhaShape)] + [vp] * 6
     lib.mha_attention_forward.restype = c_int
+    lib.mha_attention_forward_ordered.argtypes = [POINTER(MhaShape), vp, vp, vp, vp, vp, c_int32, vp, vp, vp]
+    lib.mha_attention_forward_ordered.restype = c_int
     lib.swin_layernorm_forward.argtypes = [vp, c_int32, vp, vp, c_float, c_int64, c_int32, vp, c_int32, vp]
     lib.swin_layernorm_forward.restype = c_int
     lib.swin_layernorm_backward.argtypes = [vp, c_int32, vp, c_int32, vp, c_float, c_int64, c_int32, vp, vp, vp, vp]

@@ -41,6 +41,11 @@ struct Args {
   int B, S, Sk, nH, dq, dv, s_pad;   // S query rows, Sk keys (s_pad = Sk rounded up to the key tile)
   int64_t q_rs, k_rs, v_rs, o_rs;   // row strides in elements
   float scale;
+  // optional ordered bias (model/ODA2/oda2_red_order_swin2_decoder.py:88-93): logit(i, j) += idx_bias[tok_idx[i] -
+  // tok_idx[j] + n_emb - 1, head]; self-attention only (S == Sk); null = none
+  const int* tok_idx;     // (B, S)
+  const float* idx_bias;  // (2 n_emb - 1, nH)
+  int n_emb;
 };
 
 template <typename T>
@@ -50,8 +55,15 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
   float* sq = sm;                                   // [kRows][dq]
   float* skv0 = sq + kRows * a.dq;                  // 2 x [kKeys][kTileStride]: tile t in buffer t & 1
   float* ss = skv0 + 2 * kKeys * kTileStride;       // [kRows][s_pad]
+  int* sidx = reinterpret_cast<int*>(ss + kRows * a.s_pad);   // [s_pad] token indices of this image (ordered bias only)
+  float* sbias = reinterpret_cast<float*>(sidx + a.s_pad);    // [2 n_emb - 1] this head's bias column
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int row0 = blockIdx.x * kRows, h = blockIdx.y, b = blockIdx.z;
+  const bool biased = a.tok_idx != nullptr;
+  if (biased) {
+    for (int i = tid; i < a.s_pad; i += kThreads) sidx[i] = i < a.Sk ? a.tok_idx[(int64_t)b * a.Sk + i] : 0;
+    for (int i = tid; i < 2 * a.n_emb - 1; i += kThreads) sbias[i] = a.idx_bias[(int64_t)i * a.nH + h];
+  }
   const T* qb = q + (int64_t)b * a.S * a.q_rs + h * a.dq;
   const T* kb = k + (int64_t)b * a.Sk * a.k_rs + h * a.dq;
   const T* vb = v + (int64_t)b * a.Sk * a.v_rs + h * a.dv;
@@ -102,7 +114,11 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
     }
     const bool live = c0 + j < a.Sk;
 #pragma unroll
-    for (int r = 0; r < 8; ++r) ss[(ig + 4 * r) * a.s_pad + c0 + j] = live ? acc[r] * a.scale : -INFINITY;
+    for (int r = 0; r < 8; ++r) {
+      float t = acc[r] * a.scale;
+      if (biased) t += sbias[sidx[min(row0 + ig + 4 * r, a.S - 1)] - sidx[c0 + j] + a.n_emb - 1];
+      ss[(ig + 4 * r) * a.s_pad + c0 + j] = live ? t : -INFINITY;
+    }
     if (t + 1 < n_tiles) tile_store(skv0 + ((t + 1) & 1) * kKeys * kTileStride, a.dq);
     __syncthreads();                                // next tile stored, this one consumed, logits visible
   }
@@ -166,19 +182,21 @@ __global__ void __launch_bounds__(kThreads) mha_fwd_kernel(const Args a, const T
 
 }  // namespace mha
 
-size_t mha_forward_smem_bytes(int kv_seq, int qk_head_dim) {
+size_t mha_forward_smem_bytes(int kv_seq, int qk_head_dim, int n_emb) {
   const int s_pad = (kv_seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
-  return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + 2 * (size_t)mha::kKeys * mha::kTileStride + (size_t)mha::kRows * s_pad);
+  return sizeof(float) * ((size_t)mha::kRows * qk_head_dim + 2 * (size_t)mha::kKeys * mha::kTileStride + (size_t)mha::kRows * s_pad +
+                          (n_emb > 0 ? (size_t)s_pad + 2 * (size_t)n_emb : 0));
 }
 
 cudaError_t launch_mha_forward(int dtype, int batch, int seq, int kv_seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,
                                int64_t o_rs, float scale, const void* q, const void* k, const void* v, void* o, float* attn,
-                               cudaStream_t st) {
+                               const int* tok_idx, const float* idx_bias, int n_emb, cudaStream_t st) {
   mha::Args a;
+  a.tok_idx = tok_idx; a.idx_bias = idx_bias; a.n_emb = tok_idx != nullptr ? n_emb : 0;
   a.B = batch; a.S = seq; a.Sk = kv_seq; a.nH = heads; a.dq = dq; a.dv = dv;
   a.s_pad = (kv_seq + mha::kKeys - 1) / mha::kKeys * mha::kKeys;
   a.q_rs = q_rs; a.k_rs = k_rs; a.v_rs = v_rs; a.o_rs = o_rs; a.scale = scale;
-  const size_t smem = mha_forward_smem_bytes(kv_seq, dq);
+  const size_t smem = mha_forward_smem_bytes(kv_seq, dq, a.n_emb);
   const dim3 grid((seq + mha::kRows - 1) / mha::kRows, heads, batch);
   cudaError_t e;
   TimedRegion timed(st);

@@ -37,9 +37,14 @@ struct ArgsM {
   __nv_bfloat16* o;
   int64_t o_rs;
   float* attn;
+  // optional ordered bias (see mha_global.cu): logit(i, j) += idx_bias[tok_idx[i] - tok_idx[j] + n_emb - 1, head]
+  const int* tok_idx;
+  const float* idx_bias;
+  int n_emb;
 };
+constexpr int kMaxEmb = 256;                      // 2 n_emb - 1 <= 511 bias entries per head in shared memory
 struct SmemM {
-  uint32_t q, k, v, stage, bars, tmem_ptr, total;
+  uint32_t q, k, v, stage, idx, bias, bars, tmem_ptr, total;
 };
 __host__ __device__ inline SmemM smem_m() {
   SmemM m;
@@ -47,7 +52,9 @@ __host__ __device__ inline SmemM smem_m() {
   m.k = m.q + 2 * kBoxBytesM;
   m.v = m.k + 7 * kBoxBytesM;
   m.stage = m.v + 7 * kBoxBytesM;                 // [4 warps][32 rows][33] fp32
-  m.bars = m.stage + 4 * 32 * 33 * 4;
+  m.idx = m.stage + 4 * 32 * 33 * 4;              // [kMaxSeq] token indices of the image
+  m.bias = m.idx + kMaxSeq * 4;                   // [2 kMaxEmb] bias column of the head, * log2(e)
+  m.bars = m.bias + 2 * kMaxEmb * 4;
   m.tmem_ptr = m.bars + 8 * 8;
   m.total = m.tmem_ptr + 16;
   return m;
@@ -59,6 +66,7 @@ __host__ __device__ inline SmemM smem_m() {
     TMEM_LD_X16((taddr) + 16, ((r) + 16)); \
   } while (0)
 
+template <bool kBias>
 __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, const __grid_constant__ MapsM maps) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const SmemM map = smem_m();
@@ -78,6 +86,12 @@ __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, con
     fence_barrier_init();
   }
   if (warp == 5) tmem_alloc(sbase + map.tmem_ptr, 512);
+  if (kBias && warp < 4) {
+    int* sidx = reinterpret_cast<int*>(smem + map.idx);
+    float* sbias = reinterpret_cast<float*>(smem + map.bias);
+    for (int i = tid; i < kMaxSeq; i += 128) sidx[i] = i < a.Sk ? a.tok_idx[(int64_t)b * a.Sk + i] : 0;
+    for (int i = tid; i < 2 * a.n_emb - 1; i += 128) sbias[i] = a.idx_bias[(int64_t)i * a.nH + h] * 1.4426950408889634f;
+  }
   if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&maps.q);
     tma_prefetch_desc(&maps.k);
@@ -133,24 +147,29 @@ __global__ void __launch_bounds__(kThreadsM, 1) mha_tc_kernel(const ArgsM a, con
     mbar_wait(bar_s, 0);
     tc_fence_after();
     uint32_t r[32];
-    // pass 1: row maximum of the raw scores
+    // ordered bias of this thread's row: t(j) = s c1 + brow[-idx[j]] (already in the log2 domain)
+    const int* sidx = reinterpret_cast<const int*>(smem + map.idx);
+    const float* brow = reinterpret_cast<const float*>(smem + map.bias) +
+                        (kBias ? sidx[min(row0 + warp * 32 + lane, a.S - 1)] + a.n_emb - 1 : 0);
+    // pass 1: row maximum of the logits (log2 domain)
     float m = -INFINITY;
     for (int c = 0; c < n_chunks; ++c) {
       TMEM_LD_X32(taddr + 32 * c, r);
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j)
-        if (32 * c + j < a.Sk) m = fmaxf(m, __uint_as_float(r[j]));
+        if (32 * c + j < a.Sk) m = fmaxf(m, kBias ? fmaf(__uint_as_float(r[j]), a.c1, brow[-sidx[32 * c + j]]) : __uint_as_float(r[j]) * a.c1);
     }
-    // pass 2: e = exp2((s - max) * scale * log2 e), written back in place; row sum
-    const float mc = m * a.c1;
+    // pass 2: e = exp2(t - max), written back in place; row sum
+    const float mc = m;
     float sum = 0.f;
     for (int c = 0; c < n_chunks; ++c) {
       TMEM_LD_X32(taddr + 32 * c, r);
       tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
-        const float e = 32 * c + j < a.Sk ? fast_exp2(fmaf(__uint_as_float(r[j]), a.c1, -mc)) : 0.f;
+        const float bj = kBias && 32 * c + j < a.Sk ? brow[-sidx[32 * c + j]] : 0.f;
+        const float e = 32 * c + j < a.Sk ? fast_exp2(fmaf(__uint_as_float(r[j]), a.c1, bj - mc)) : 0.f;
         sum += e;
         r[j] = __float_as_uint(e);
       }
@@ -224,7 +243,8 @@ bool mha_tc_supported(int dtype, int seq, int kv_seq, int dq, int dv, int64_t q_
 }
 
 cudaError_t launch_mha_tc_forward(int batch, int seq, int kv_seq, int heads, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, float scale,
-                                  const void* q, const void* k, const void* v, void* o, float* attn, cudaStream_t st, const char** err) {
+                                  const void* q, const void* k, const void* v, void* o, float* attn, const int* tok_idx,
+                                  const float* idx_bias, int n_emb, cudaStream_t st, const char** err) {
   mhatc::MapsM maps;
   memset(&maps, 0, sizeof(maps));
   const int width = heads * mhatc::kHd;
@@ -235,7 +255,9 @@ cudaError_t launch_mha_tc_forward(int batch, int seq, int kv_seq, int heads, int
     return cudaErrorInvalidValue;
   }
   const mhatc::SmemM map = mhatc::smem_m();
-  cudaError_t e = cudaFuncSetAttribute(mhatc::mha_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)map.total);
+  const bool biased = tok_idx != nullptr;
+  auto kernel = biased ? mhatc::mha_tc_kernel<true> : mhatc::mha_tc_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)map.total);
   if (e != cudaSuccess) {
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
     return e;
@@ -244,9 +266,10 @@ cudaError_t launch_mha_tc_forward(int batch, int seq, int kv_seq, int heads, int
   a.S = seq; a.Sk = kv_seq; a.s16 = (kv_seq + 15) / 16 * 16; a.nH = heads;
   a.c1 = scale * 1.4426950408889634f;
   a.o = static_cast<__nv_bfloat16*>(o); a.o_rs = o_rs; a.attn = attn;
+  a.tok_idx = tok_idx; a.idx_bias = idx_bias; a.n_emb = biased ? n_emb : 0;
   const dim3 grid((seq + mhatc::kRowsM - 1) / mhatc::kRowsM, heads, batch);
   TimedRegion timed(st);
-  mhatc::mha_tc_kernel<<<grid, mhatc::kThreadsM, map.total, st>>>(a, maps);
+  kernel<<<grid, mhatc::kThreadsM, map.total, st>>>(a, maps);
   count_launch();
   return cudaGetLastError();
 }

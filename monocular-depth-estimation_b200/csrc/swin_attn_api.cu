@@ -479,7 +479,8 @@ int swin_layernorm_backward(const void* x, int32_t x_dtype, const void* dy, int3
 
 // Debug hook (not part of the public header): device buffer of >= 16 * pairs-per-CTA int64 that receives
 // clock64 stamps of CTA 0 of the tcgen05 kernel; pass NULL to switch tracing off.
-int mha_attention_forward(const mha_shape_t* s, const void* q, const void* k, const void* v, void* o, float* attn_map, void* stream) {
+static int mha_impl(const mha_shape_t* s, const void* q, const void* k, const void* v, void* o, float* attn_map, const int32_t* tok_idx,
+                    const float* idx_bias, int n_emb, void* stream) {
   if (s == nullptr) return fail("mha forward: shape is null");
   if (!q || !k || !v || !o) return fail("mha forward: q, k, v and o must be non-null");
   if (s->dtype != SWIN_ATTN_F32 && s->dtype != SWIN_ATTN_BF16) return fail("mha forward: dtype must be SWIN_ATTN_F32 or SWIN_ATTN_BF16");
@@ -494,22 +495,38 @@ int mha_attention_forward(const mha_shape_t* s, const void* q, const void* k, co
   if (s->qk_head_dim % 4) return fail("mha forward: qk_head_dim must be a multiple of 4");
   if (s->batch > 65535 || s->num_heads > 65535) return fail("mha forward: batch and num_heads must be <= 65535");
   if (s->impl != SWIN_ATTN_IMPL_AUTO && s->impl != SWIN_ATTN_IMPL_SIMT) return fail("mha forward: impl must be SWIN_ATTN_IMPL_AUTO or SWIN_ATTN_IMPL_SIMT");
-  if (s->impl == SWIN_ATTN_IMPL_AUTO && mha_tc_supported(s->dtype, s->seq, kv_seq, s->qk_head_dim, s->v_head_dim, s->q_row_stride, s->k_row_stride,
-                                                         s->v_row_stride, s->o_row_stride, q, k, v, o)) {
+  if (tok_idx != nullptr) {
+    if (idx_bias == nullptr || n_emb < 1) return fail("mha forward (ordered bias): index_bias must be non-null and num_emb positive");
+    if (kv_seq != s->seq) return fail("mha forward (ordered bias): self-attention only (kv_seq must equal seq)");
+  }
+  if (s->impl == SWIN_ATTN_IMPL_AUTO && (tok_idx == nullptr || n_emb <= 256) &&
+      mha_tc_supported(s->dtype, s->seq, kv_seq, s->qk_head_dim, s->v_head_dim, s->q_row_stride, s->k_row_stride, s->v_row_stride,
+                       s->o_row_stride, q, k, v, o)) {
     const char* why = nullptr;
     cudaError_t e = launch_mha_tc_forward(s->batch, s->seq, kv_seq, s->num_heads, s->q_row_stride, s->k_row_stride, s->v_row_stride,
-                                          s->o_row_stride, s->scale, q, k, v, o, attn_map, static_cast<cudaStream_t>(stream), &why);
+                                          s->o_row_stride, s->scale, q, k, v, o, attn_map, tok_idx, idx_bias, n_emb,
+                                          static_cast<cudaStream_t>(stream), &why);
     if (e != cudaSuccess) return fail_cuda(why ? why : "mha forward (tcgen05) launch", e);
     return 0;
   }
-  const size_t smem = mha_forward_smem_bytes(kv_seq, s->qk_head_dim);
+  const size_t smem = mha_forward_smem_bytes(kv_seq, s->qk_head_dim, tok_idx != nullptr ? n_emb : 0);
   if (smem > 227u * 1024u)
     return fail("mha forward: " + std::to_string(kv_seq) + " keys need " + std::to_string(smem) + " B of shared memory per CTA (limit 232448; kv_seq <= 1472)");
   cudaError_t e = launch_mha_forward(s->dtype, s->batch, s->seq, kv_seq, s->num_heads, s->qk_head_dim, s->v_head_dim, s->q_row_stride,
-                                     s->k_row_stride, s->v_row_stride, s->o_row_stride, s->scale, q, k, v, o, attn_map,
-                                     static_cast<cudaStream_t>(stream));
+                                     s->k_row_stride, s->v_row_stride, s->o_row_stride, s->scale, q, k, v, o, attn_map, tok_idx, idx_bias,
+                                     n_emb, static_cast<cudaStream_t>(stream));
   if (e != cudaSuccess) return fail_cuda("mha forward launch", e);
   return 0;
+}
+
+int mha_attention_forward(const mha_shape_t* s, const void* q, const void* k, const void* v, void* o, float* attn_map, void* stream) {
+  return mha_impl(s, q, k, v, o, attn_map, nullptr, nullptr, 0, stream);
+}
+
+int mha_attention_forward_ordered(const mha_shape_t* s, const void* q, const void* k, const void* v, const int32_t* token_index,
+                                  const float* index_bias, int32_t num_emb, void* o, float* attn_map, void* stream) {
+  if (token_index == nullptr) return fail("mha forward (ordered bias): token_index must be non-null");
+  return mha_impl(s, q, k, v, o, attn_map, token_index, index_bias, num_emb, stream);
 }
 
 // Debug hook (not part of the public header): CTA-pair mode of the tcgen05 linear kernel, -1 automatic, 0 off, 1 on.

@@ -163,15 +163,16 @@ cudaError_t launch_tc_linear(const void* x, const void* weight, const void* bias
                              int in_features, int out_features, int activation, cudaStream_t st, const char** err);
 
 // Global multi-head attention that returns its map (Depthformer SelfAttentionBlock core; mha_global.cu)
-size_t mha_forward_smem_bytes(int kv_seq, int qk_head_dim);
+size_t mha_forward_smem_bytes(int kv_seq, int qk_head_dim, int n_emb);
 cudaError_t launch_mha_forward(int dtype, int batch, int seq, int kv_seq, int heads, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs,
                                int64_t o_rs, float scale, const void* q, const void* k, const void* v, void* o, float* attn,
-                               cudaStream_t st);
+                               const int* tok_idx, const float* idx_bias, int n_emb, cudaStream_t st);
 
 bool mha_tc_supported(int dtype, int seq, int kv_seq, int dq, int dv, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, const void* q,
                       const void* k, const void* v, const void* o);
 cudaError_t launch_mha_tc_forward(int batch, int seq, int kv_seq, int heads, int64_t q_rs, int64_t k_rs, int64_t v_rs, int64_t o_rs, float scale,
-                                  const void* q, const void* k, const void* v, void* o, float* attn, cudaStream_t st, const char** err);
+                                  const void* q, const void* k, const void* v, void* o, float* attn, const int* tok_idx,
+                                  const float* idx_bias, int n_emb, cudaStream_t st, const char** err);
 
 void set_tc_linear_pair_mode(int mode);
 void count_launch(int n = 1);

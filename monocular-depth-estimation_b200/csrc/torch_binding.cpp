@@ -941,7 +941,8 @@ TORCH_LIBRARY_IMPL(swin_attn, Autograd, m) {
 // ---- swin_attn::mha_fwd: global multi-head attention that returns its map (Depthformer SelfAttentionBlock core) -------
 // q, k: (B, S, nH * dq), v: (B, S, nH * dv), unit channel stride (row strides may exceed the width: slices of a packed
 // projection).  Returns o (B, S, nH * dv) in the input dtype and the fp32 map (B, nH, S, S).
-std::tuple<Tensor, Tensor> mha_fwd_cuda(const Tensor& q_in, const Tensor& k_in, const Tensor& v_in, int64_t num_heads, double scale) {
+std::tuple<Tensor, Tensor> mha_fwd_impl(const Tensor& q_in, const Tensor& k_in, const Tensor& v_in, const optional<Tensor>& token_index,
+                                        const optional<Tensor>& index_bias, int64_t num_heads, double scale) {
   TORCH_CHECK(q_in.dim() == 3 && k_in.dim() == 3 && v_in.dim() == 3, "mha_fwd: q, k, v must be (B, S, D)");
   TORCH_CHECK(q_in.size(0) == k_in.size(0) && q_in.size(2) == k_in.size(2) && v_in.size(0) == k_in.size(0) && v_in.size(1) == k_in.size(1),
               "mha_fwd: q (B, S, D), k (B, Sk, D), v (B, Sk, Dv) shapes disagree");
@@ -964,8 +965,34 @@ std::tuple<Tensor, Tensor> mha_fwd_cuda(const Tensor& q_in, const Tensor& k_in, 
   shp.q_row_stride = q.stride(1); shp.k_row_stride = k.stride(1); shp.v_row_stride = v.stride(1); shp.o_row_stride = o.stride(1);
   c10::cuda::CUDAGuard guard(q.device());
   cudaStream_t stream = at::cuda::getCurrentCUDAStream();
-  check_rc(mha_attention_forward(&shp, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), attn.data_ptr<float>(), stream));
+  if (token_index.has_value()) {
+    TORCH_CHECK(index_bias.has_value() && index_bias->dim() == 2 && index_bias->size(1) == num_heads && index_bias->size(0) % 2 == 1,
+                "mha_fwd_ordered: index_bias must be (2 * num_emb - 1, num_heads)");
+    TORCH_CHECK(token_index->dim() == 2 && token_index->size(0) == b && token_index->size(1) == s && s == sk,
+                "mha_fwd_ordered: token_index must be (B, S) and the attention self-attention");
+    const Tensor idx = token_index->to(at::kInt).contiguous();
+    const Tensor bias = index_bias->detach().to(at::kFloat).contiguous();
+    check_rc(mha_attention_forward_ordered(&shp, q.data_ptr(), k.data_ptr(), v.data_ptr(), idx.data_ptr<int32_t>(), bias.data_ptr<float>(),
+                                           (int32_t)((bias.size(0) + 1) / 2), o.data_ptr(), attn.data_ptr<float>(), stream));
+  } else {
+    check_rc(mha_attention_forward(&shp, q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), attn.data_ptr<float>(), stream));
+  }
   return {o, attn};
+}
+
+std::tuple<Tensor, Tensor> mha_fwd_cuda(const Tensor& q, const Tensor& k, const Tensor& v, int64_t num_heads, double scale) {
+  return mha_fwd_impl(q, k, v, c10::nullopt, c10::nullopt, num_heads, scale);
+}
+
+std::tuple<Tensor, Tensor> mha_fwd_ordered_cuda(const Tensor& q, const Tensor& k, const Tensor& v, const Tensor& token_index,
+                                                const Tensor& index_bias, int64_t num_heads, double scale) {
+  return mha_fwd_impl(q, k, v, token_index, index_bias, num_heads, scale);
+}
+
+std::tuple<Tensor, Tensor> mha_fwd_ordered_meta(const Tensor& q, const Tensor& k, const Tensor& v, const Tensor&, const Tensor&,
+                                                int64_t num_heads, double) {
+  return {at::empty_symint({q.sym_size(0), q.sym_size(1), v.sym_size(2)}, q.options()),
+          at::empty_symint({q.sym_size(0), c10::SymInt(num_heads), q.sym_size(1), k.sym_size(1)}, q.options().dtype(at::kFloat))};
 }
 
 std::tuple<Tensor, Tensor> mha_fwd_meta(const Tensor& q, const Tensor& k, const Tensor& v, int64_t num_heads, double) {
@@ -975,9 +1002,16 @@ std::tuple<Tensor, Tensor> mha_fwd_meta(const Tensor& q, const Tensor& k, const 
 
 TORCH_LIBRARY_FRAGMENT(swin_attn, m) {
   m.def("mha_fwd(Tensor q, Tensor k, Tensor v, int num_heads, float scale) -> (Tensor, Tensor)");
+  m.def("mha_fwd_ordered(Tensor q, Tensor k, Tensor v, Tensor token_index, Tensor index_bias, int num_heads, float scale) -> (Tensor, Tensor)");
 }
-TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) { m.impl("mha_fwd", mha_fwd_cuda); }
-TORCH_LIBRARY_IMPL(swin_attn, Meta, m) { m.impl("mha_fwd", mha_fwd_meta); }
+TORCH_LIBRARY_IMPL(swin_attn, CUDA, m) {
+  m.impl("mha_fwd", mha_fwd_cuda);
+  m.impl("mha_fwd_ordered", mha_fwd_ordered_cuda);
+}
+TORCH_LIBRARY_IMPL(swin_attn, Meta, m) {
+  m.impl("mha_fwd", mha_fwd_meta);
+  m.impl("mha_fwd_ordered", mha_fwd_ordered_meta);
+}
 
 // ---- timing control (ctypes; not tensor ops) -------------------------------------------------------------------
 extern "C" {

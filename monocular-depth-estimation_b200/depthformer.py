@@ -24,10 +24,14 @@ from . import ops  # noqa: F401  (loads libswin_attn_torch.so and registers swin
 
 class _GlobalAttention(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, num_heads, scale):
-        o, attn = torch.ops.swin_attn.mha_fwd(q, k, v, num_heads, scale)
+    def forward(ctx, q, k, v, num_heads, scale, token_index=None, index_bias=None):
+        if token_index is None:
+            o, attn = torch.ops.swin_attn.mha_fwd(q, k, v, num_heads, scale)
+        else:
+            o, attn = torch.ops.swin_attn.mha_fwd_ordered(q, k, v, token_index, index_bias, num_heads, scale)
         ctx.save_for_backward(q, k, v, attn)
         ctx.num_heads, ctx.scale = num_heads, scale
+        ctx.token_index, ctx.bias_shape = token_index, None if index_bias is None else (index_bias.shape, index_bias.dtype)
         return o, attn
 
     @staticmethod
@@ -51,19 +55,29 @@ class _GlobalAttention(torch.autograd.Function):
         def back(t, like):
             return t.transpose(1, 2).reshape(b, like.shape[1], -1).to(like.dtype)
 
-        return back(d_q, q), back(d_k, k), back(d_v, v), None, None
+        d_bias = None
+        if ctx.token_index is not None and ctx.needs_input_grad[6]:
+            # the bias enters the logits as index_bias[idx_i - idx_j + n - 1, head]: scatter dS back by that index
+            shape, dtype = ctx.bias_shape
+            idx = ctx.token_index.long()
+            rel = (idx[:, :, None] - idx[:, None, :] + (shape[0] + 1) // 2 - 1).reshape(-1)
+            d_bias = torch.zeros(shape, dtype=torch.float32, device=q.device).index_add_(0, rel, d_s.permute(0, 2, 3, 1).reshape(-1, nh))
+            d_bias = d_bias.to(dtype)
+        return back(d_q, q), back(d_k, k), back(d_v, v), None, None, None, d_bias
 
 
-def global_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, num_heads: int, scale: float) -> Tuple[torch.Tensor, torch.Tensor]:
+def global_attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, num_heads: int, scale: float,
+                     token_index: Optional[torch.Tensor] = None, index_bias: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """``attn = softmax(q k^T * scale)`` (B, nH, S, Sk) fp32 and ``o = attn v`` (B, S, Dv) for projections q (B, S, D),
     k (B, Sk, D), v (B, Sk, Dv) whose heads are consecutive channel groups (self_attention.py:36-40, :70-80;
-    luna_layer.py:50-54, :85-94, :118-127)."""
+    luna_layer.py:50-54, :85-94, :118-127).  ``token_index`` (B, S) integers with ``index_bias`` (2 n - 1, nH) add the ordered
+    bias ``index_bias[idx_i - idx_j + n - 1, head]`` to the scaled logits (oda2_red_order_swin2_decoder.py:88-93, :112-117)."""
     if not q.is_cuda:
         raise RuntimeError("global_attention needs CUDA tensors: this package has no CPU path (the oracle under oracle/ is the CPU restatement)")
     if torch.is_autocast_enabled():   # the Linears produced bf16 under autocast; the reference's matmuls run in it too
         dt = torch.get_autocast_dtype("cuda")
         q, k, v = q.to(dt), k.to(dt), v.to(dt)
-    return _GlobalAttention.apply(q, k, v, num_heads, float(scale))
+    return _GlobalAttention.apply(q, k, v, num_heads, float(scale), token_index, index_bias)
 
 
 def _attend(mod: nn.Module, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:

@@ -347,3 +347,94 @@ class OdaSwinTransformerBlock(nn.Module):
             o = ow.view(b, h // ws, w // ws, ws, ws, c).permute(0, 1, 3, 2, 4, 5).reshape(b, h, w, c)
             o = torch.roll(o, shifts=(shift, shift), dims=(1, 2))
         return _finish(self, x, o.reshape(b, h * w, c))
+
+
+class PreNormOrderedSwinSA(nn.Module):
+    """``model/ODA2/oda2_red_order_swin2_decoder.py:13-132``: pre-norm window self-attention of the ODA2 depth-order decoder --
+    windows of 4 / 8 / 16, NO shift mask, and a data-dependent bias: every pixel carries an integer depth index and the logit
+    of (query i, key j) gets ``depth_embedding[idx_i - idx_j + num_emb - 1, head]``.  Returns ``(x + attention, attn)`` with
+    the attention map (num_windows * B, heads, r*r, r*r).
+
+    The windows are the batch of the global-attention kernels (``mha_attention_forward_ordered``: one launch computes the
+    scaled dot product, the index-difference bias gather, the softmax, the returned map and the value product); roll,
+    window partition / reverse and the projections stay torch ops, as in the reference.  ``attn_drop_prob > 0`` in
+    training (the reference drops the scaled LOGITS, before the bias and the softmax, :110) takes the reference's op sequence
+    in torch."""
+
+    def __init__(self, in_dims: int, num_heads: int, num_emb: int, window_size: int = 8, shift_size: int = 0,
+                 attn_drop_prob: float = 0.0, drop_prob: float = 0.0, bias_type: str = "depth", bias_init: str = "linear"):
+        super().__init__()
+        self.in_dims, self.num_heads = in_dims, num_heads
+        if in_dims % num_heads != 0:
+            raise ValueError(f"Input dim {in_dims} is not divisible by num_heads {num_heads}.")
+        self.head_dim = in_dims // num_heads
+        if self.head_dim > 64 or self.head_dim % 4:
+            raise ValueError("the CUDA kernels serve head dims up to 64 (multiples of 4)")
+        self.norm = nn.LayerNorm(in_dims)
+        self.q_proj, self.k_proj = nn.Linear(in_dims, in_dims), nn.Linear(in_dims, in_dims)
+        self.v_proj, self.o_proj = nn.Linear(in_dims, in_dims), nn.Linear(in_dims, in_dims)
+        self.attn_scale = math.sqrt(1 / self.head_dim)
+        self.drop = nn.Dropout(drop_prob)
+        self.attn_drop = nn.Dropout(attn_drop_prob)
+        self.window_size, self.shift_size = window_size, shift_size
+        self.windowing = SwinWindowing(window_size=window_size)
+        assert (self.window_size == 16) or (self.window_size == 8) or (self.window_size == 4)
+        self.num_emb, self.bias_type = num_emb, bias_type
+        if bias_type == "depth":
+            if bias_init == "linear":      # :50-59
+                with torch.no_grad():
+                    de = torch.linspace(1, 2 * num_emb - 1, 2 * num_emb - 1) - num_emb
+                    de = de.unsqueeze(-1).expand(2 * num_emb - 1, num_heads).contiguous()
+                    init = torch.ones(num_heads, dtype=torch.float32).uniform_(0.01, 0.04)
+                    de[:num_emb] *= init
+                    de[-num_emb:] *= (-init)
+            elif bias_init == "random":
+                de = torch.zeros(2 * num_emb - 1, num_heads).uniform_(-0.05, 0.05)
+            else:
+                raise ValueError(f"Unsupported bias init {bias_init}.")
+            self.depth_embedding = nn.Parameter(de, requires_grad=True)
+        elif bias_type == "none":
+            pass
+        elif bias_type == "pos":
+            raise NotImplementedError
+        else:
+            raise ValueError(f"Unsupported bias type {bias_type}.")
+
+    def forward(self, x: torch.Tensor, indices: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+        from .depthformer import global_attention
+        b, h, w, d = x.shape
+        assert d == self.in_dims
+        r, s = self.window_size, self.shift_size
+        identity = x
+        if s > 0:
+            x = torch.roll(x, shifts=(-s, -s), dims=(1, 2))
+            indices = torch.roll(indices, shifts=(-s, -s), dims=(1, 2))
+        xw = self.windowing.window_partition(x).reshape(-1, r * r, d)          # (nW*B, rr, d)
+        x_norm = self.norm(xw)
+        q, k, v = self.q_proj(x_norm), self.k_proj(x_norm), self.v_proj(x_norm)
+        depth = self.bias_type == "depth"
+        idx = self.windowing.window_partition(indices.unsqueeze(-1)).reshape(-1, r * r) if depth else None
+        if self.training and self.attn_drop.p > 0.0:
+            out, attn = self._reference_core(q, k, v, idx)
+        else:
+            out, attn = global_attention(q, k, v, self.num_heads, self.attn_scale, idx, self.depth_embedding if depth else None)
+        out = self.drop(self.o_proj(out)).reshape(-1, r, r, d)
+        out = self.windowing.window_reverse(out, h, w)
+        if s > 0:
+            out = torch.roll(out, shifts=(s, s), dims=(1, 2))
+        return out + identity, attn
+
+    def _reference_core(self, q, k, v, idx):
+        """:104-122 as written (training with dropout on the scaled logits)."""
+        n, rr, d = q.shape
+
+        def heads(t):
+            return t.view(n, rr, self.num_heads, d // self.num_heads).transpose(1, 2).contiguous()
+
+        attn = torch.matmul(heads(q), heads(k).transpose(-1, -2)) * self.attn_scale
+        attn = self.attn_drop(attn)
+        if idx is not None:
+            rel = idx.view(-1, rr, 1) - idx.view(-1, 1, rr) + (self.num_emb - 1)
+            attn = attn + F.embedding(rel, weight=self.depth_embedding).permute(0, 3, 1, 2)
+        attn = torch.softmax(attn, dim=-1)
+        return torch.matmul(attn.to(v.dtype), heads(v)).transpose(1, 2).reshape(n, rr, d), attn

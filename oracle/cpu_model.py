@@ -114,6 +114,8 @@ def to_oracle(module: torch.nn.Module, device="cpu") -> torch.nn.Module:
     that is "the reference on the B200" (used to measure the reference's own bf16-autocast
     error and the eager baseline), still never the product path."""
     from .global_attention import SWAP as mha_swap
+    from .ordered_window_attention import SWAP as ordered_swap
+    mha_swap = {**mha_swap, **ordered_swap}
     clone = copy.deepcopy(module).to(device)
     for m in clone.modules():
         if type(m) in _SWAP:

@@ -130,6 +130,24 @@ def depthformer_luna(name, cls, b, h, w, hidden, aux_dim, qk, nh, k_tokens):
                 dq2_w=gs[3], dv2_w=gs[4])
 
 
+def oda2_ordered_sa(name, b, h, w, dims, nh, n_emb, r, shift):
+    """model/ODA2 PreNormOrderedSwinSA: depth-order bias from per-pixel integer indices, window r, no shift mask; eval mode;
+    cotangents on both outputs; the bias table is perturbed so that its gradient is not symmetric by construction."""
+    D = rs.oda2_ordered_swin_decoder()
+    torch.manual_seed(0)
+    m = D.PreNormOrderedSwinSA(dims, nh, n_emb, window_size=r, shift_size=shift).eval()
+    m.load_state_dict(synthetic_state(m))
+    x = randn(name + ".x", b, h, w, dims).requires_grad_()
+    g = torch.Generator().manual_seed(1234)
+    indices = torch.randint(0, n_emb, (b, h, w), generator=g)
+    out, attn = m(x, indices)
+    cot_o, cot_a = randn(name + ".cot_o", *out.shape), randn(name + ".cot_a", *attn.shape)
+    gs = torch.autograd.grad((out * cot_o).sum() + (attn * cot_a).sum(), [x, m.depth_embedding, m.k_proj.weight, m.v_proj.bias])
+    return dict(kind="oda2_ordered_sa", cfg=dict(b=b, h=h, w=w, dims=dims, nh=nh, n_emb=n_emb, r=r, shift=shift), x=x.detach(),
+                indices=indices, out=out.detach(), attn=attn.detach(), cot_o=cot_o, cot_a=cot_a, dx=gs[0], dbias=gs[1], dk_w=gs[2],
+                dv_b=gs[3])
+
+
 def masked_windows(name, ws, nw, groups, c, nh):
     """WindowAttention.forward(x, v, mask) on window-order tokens with an arbitrary mask."""
     L = rs.newcrf_layers()
@@ -242,6 +260,9 @@ CASES = {
     "oda_block_ws12_s6": lambda n: oda_block(n, 12, 6, 1, 24, 36, 64, 2),
     "oda_block_ws12_s0": lambda n: oda_block(n, 12, 0, 1, 24, 24, 64, 2),
     "oda_block_ws7_s3": lambda n: oda_block(n, 7, 3, 2, 14, 21, 96, 3),
+    # ODA2 depth-order decoder windows: window 8 shifted by 4 with head dim 64, window 4 un-shifted with head dim 32
+    "oda2_ordered_sa_r8_s4": lambda n: oda2_ordered_sa(n, 1, 16, 24, 128, 2, 16, 8, 4),
+    "oda2_ordered_sa_r4_s0": lambda n: oda2_ordered_sa(n, 2, 8, 12, 64, 2, 9, 4, 0),
     # Depthformer decoder attention: S = 11 x 10 tokens, head dim 64 (the model's) / 32 with a narrower key-query width
     "depthformer_vit_hd64": lambda n: depthformer_vit(n, 2, 110, 128, 128, 2, 2),
     "depthformer_vit_kq32": lambda n: depthformer_vit(n, 1, 75, 128, 64, 2, 1),

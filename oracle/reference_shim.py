@@ -175,6 +175,12 @@ def depthformer_vit_layer():
     return importlib.import_module("model.Depthformer.vit_layer")
 
 
+def oda2_ordered_swin_decoder():
+    install()
+    import importlib
+    return importlib.import_module("model.ODA2.oda2_red_order_swin2_decoder")
+
+
 def depthformer_luna_layer():
     install()
     import importlib

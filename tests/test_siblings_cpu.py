@@ -121,3 +121,30 @@ def test_integration_recipe_names_exist_in_the_reference():
     assert set(ref.state_dict()) == set(ours.state_dict())
     ref = oda.SwinTransformerBlock(64, (14, 14), 2, window_size=7, shift_size=3)
     assert set(ref.state_dict()) == set(siblings.OdaSwinTransformerBlock(64, (14, 14), 2, window_size=7, shift_size=3).state_dict())
+
+
+def ordered_sa_from_golden(g):
+    cfg = g["cfg"]
+    torch.manual_seed(0)
+    m = siblings.PreNormOrderedSwinSA(cfg["dims"], cfg["nh"], cfg["n_emb"], window_size=cfg["r"], shift_size=cfg["shift"])
+    m.load_state_dict(synthetic_state(m), strict=True)
+    return m.eval()
+
+
+@pytest.mark.parametrize("name", ["oda2_ordered_sa_r8_s4", "oda2_ordered_sa_r4_s0"])
+def test_oda2_ordered_window_attention_oracle_matches_reference(golden, name):
+    """model/ODA2/oda2_red_order_swin2_decoder.py PreNormOrderedSwinSA: depth-order bias, windows of 8 / 4, no shift mask."""
+    g = golden(name)
+    m = to_oracle(ordered_sa_from_golden(g)).eval()
+    x = g["x"].clone().requires_grad_()
+    out, attn = m(x, g["indices"])
+    assert rel_err(out, g["out"]) < TOL and rel_err(attn, g["attn"]) < TOL
+    gs = torch.autograd.grad((out * g["cot_o"]).sum() + (attn * g["cot_a"]).sum(), [x, m.depth_embedding, m.k_proj.weight, m.v_proj.bias])
+    for got, key in zip(gs, ["dx", "dbias", "dk_w", "dv_b"]):
+        assert rel_err(got, g[key]) < TOL, key
+    cfg = g["cfg"]
+    n_win = cfg["b"] * (cfg["h"] // cfg["r"]) * (cfg["w"] // cfg["r"])
+    assert attn.shape == (n_win, cfg["nh"], cfg["r"] ** 2, cfg["r"] ** 2)
+    assert set(m.state_dict()) == {"depth_embedding"} | {f"{p}.{w}" for p in ("norm", "q_proj", "k_proj", "v_proj", "o_proj") for w in ("weight", "bias")}
+    with pytest.raises(AssertionError):
+        siblings.PreNormOrderedSwinSA(64, 2, 8, window_size=7)      # the reference accepts windows of 4, 8, 16 only (:45)
