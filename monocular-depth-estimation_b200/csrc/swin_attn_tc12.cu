@@ -20,8 +20,15 @@
 //   epilogue: O row / rowsum -> bf16 -> staging -> TMA tensor store of the half window (12 x 6, or 6 x 12 /
 //           two 6 x 6 boxes for shifted blocks).
 //
-// Not covered here (served by the CUDA-core kernels): padding (H or W not a multiple of 12; every ODA
-// stage of a 384 x 384 input is a multiple), explicit masks, fp32, the backward.
+// Padding (H or W not a multiple of 12: every ODA stage of a 352 x 1216 or 480 x 640 input): TMA zero-fills the
+// out-of-image part of a load box and clips it from a store box.  The reference pads BEFORE the qkv Linear
+// (oda_swin_transformer.py:249-253), so pad tokens carry the Linear bias: k_pad goes -- once per CTA -- into the
+// spare row 144 of every K tile and v_pad into the spare rows 144 / 145 of every V tile (tiles are 160 rows; the
+// boxes write 144).  With padding S is N = 160 wide (column 144 = q . k_pad, which the softmax substitutes for the
+// columns of pad tokens) and the PV product takes a tenth K-step whose P columns 144 / 145 hold the hi / lo bf16
+// halves of the row's summed probability over pad tokens.  Window-aligned launches run the 144 / 9-step shapes.
+//
+// Not covered here (served by the CUDA-core kernels): explicit masks, fp32; the backward is swin_attn_mma12_bwd.cu.
 #include "swin_attn_tc.cuh"
 
 namespace swin {
@@ -33,15 +40,17 @@ constexpr int WS12 = 12;
 constexpr int N12 = 144;
 constexpr int kHalf = 72;            // query rows per unit
 constexpr int kSplit = 6;            // shift = 6: a shifted window splits 6 | 6 along each axis
-constexpr int kTile12 = N12 * 64;    // 9216 B: one tensor of one tile
-constexpr int kStage12 = 3 * kTile12;
+constexpr int kTile12 = N12 * 64;    // 9216 B: one tensor of one tile (what the TMA boxes write)
+constexpr int kRowsKV = 160;         // rows of a K / V tile: 144 tokens + the pad-vector rows (144, 145) + zero rows
+constexpr int kTileKV = kRowsKV * 64;
+constexpr int kStage12 = kTile12 + 2 * kTileKV;
 constexpr int kStages12 = 4;
 constexpr int kSlots12 = 3;
 constexpr int kThreads12 = 128 + 128 * kSlots12;
 constexpr int kFill12 = kThreads12 - 64;
 constexpr int kPBlock = kHalf * 128;             // 72 rows x 64 bf16 columns
 constexpr int kPSlot = 3 * kPBlock;              // column blocks [0,64) [64,128) [128,144)
-constexpr int kSlotCols12 = 144;
+constexpr int kSlotCols12 = 160;          // S accumulator of a unit: 144 keys (+ 16 with padding); O in [0, 32)
 constexpr int kTable12 = 23 * 23;                // (2 ws - 1)^2
 
 // tensor maps per tensor: [0] 12x12 (x,y), [1] 6x6, [2] 6x12 (6 wide, 12 tall), [3] 12x6 (12 wide, 6 tall)
@@ -80,6 +89,13 @@ template <bool kPerm>
 __host__ __device__ constexpr int row_j12(int r) {
   if (!kPerm) return r % WS12;
   return r < 72 ? r % 6 : 6 + r % 6;
+}
+
+// bits [lo, hi) clipped to the 12 rows / columns of a window
+__device__ __forceinline__ int span_bits(int lo, int hi) {
+  lo = min(max(lo, 0), WS12);
+  hi = min(max(hi, 0), WS12);
+  return ((1 << hi) - 1) & ~((1 << lo) - 1);
 }
 
 // One window of one tensor, global -> shared: 1 box (un-shifted) or the 2 / 4 parts of a shifted window.
@@ -125,7 +141,7 @@ __device__ __forceinline__ void store_half12(const CUtensorMap* maps, uint32_t s
 
 template <bool kShifted>
 __global__ void __launch_bounds__(kThreads12, 1)
-tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_constant__ TmaMaps12 maps) {
+tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, int has_pad, const __grid_constant__ TmaMaps12 maps) {
   constexpr bool kPerm = kShifted;
   extern __shared__ __align__(1024) unsigned char smem[];
   const SmemMap12 map = smem_map_12();
@@ -173,6 +189,20 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) bmax = fmaxf(bmax, __shfl_xor_sync(0xffffffffu, bmax, o));
     if (lane == 0) bias[kTable12 + (t14 >> 5)] = bmax;
+    if (has_pad) {
+      // spare rows 144 .. 159 of every K / V tile (64B-swizzled rows, never written by the TMA boxes): row 144 = the
+      // head's pad vector (K and V), row 145 = the pad vector again (V: the lo half of the pad probability), rest zero
+      for (int i = t14; i < kStages12 * 2 * 16 * 4; i += kFill12) {
+        const int chunk = i & 3, rr = (i >> 2) & 15, is_v = (i >> 6) & 1, st = i >> 7;
+        const int rowx = N12 + rr;
+        const void* vecp = is_v ? p.v_pad : p.k_pad;
+        const bool vec_row = rr == 0 || (is_v && rr == 1);
+        const uint4 val = vec_row && vecp != nullptr ? reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(vecp) + h * kHeadDim)[chunk]
+                                                     : make_uint4(0u, 0u, 0u, 0u);
+        unsigned char* tile = smem + map.stages + st * kStage12 + kTile12 + is_v * kTileKV;
+        *reinterpret_cast<uint4*>(tile + rowx * 64 + ((chunk ^ ((rowx >> 1) & 3)) << 4)) = val;
+      }
+    }
     fence_proxy_async();
     tc_fence_before();
     named_barrier(6, kFill12);
@@ -198,13 +228,13 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
         mbar_expect_tx(bar, 3 * kTile12);
         load_window12<kShifted>(maps.q, st, bar, p, it.b, it.wy, it.wx, h);
         load_window12<kShifted>(maps.k, st + kTile12, bar, p, it.b, it.wy, it.wx, h);
-        load_window12<kShifted>(maps.v, st + 2 * kTile12, bar, p, it.b, it.wy, it.wx, h);
+        load_window12<kShifted>(maps.v, st + kTile12 + kTileKV, bar, p, it.b, it.wy, it.wx, h);
       }
       __syncwarp();
     }
   } else if (warp == 1) {
     // ===== S = Q_half K^T issuer ================================================================
-    constexpr uint32_t idesc_s = instr_desc(128, N12, 0);
+    const uint32_t idesc_s = has_pad ? instr_desc(128, kRowsKV, 0) : instr_desc(128, N12, 0);
     for (int u = 0; u < n_units; ++u) {
       const int n = u >> 1, half = u & 1, s = n % kStages12, a = u % kSlots12;
       if (half == 0) mbar_wait(bar_full + 8 * s, (n / kStages12) & 1);
@@ -221,19 +251,20 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
       __syncwarp();
     }
   } else if (warp == 2) {
-    // ===== O = P V issuer (9 K-steps over the three column blocks of P) =========================
+    // ===== O = P V issuer (9 K-steps over the three column blocks of P; a tenth for the pad columns) ==
     constexpr uint32_t idesc_o = instr_desc(128, 32, 1);
+    const int ksteps = has_pad ? 10 : 9;
     for (int u = 0; u < n_units; ++u) {
       const int n = u >> 1, half = u & 1, s = n % kStages12, a = u % kSlots12;
       mbar_wait(bar_p + 8 * a, (u / kSlots12) & 1);
       tc_fence_after();
-      const uint32_t vt = sbase + map.stages + s * kStage12 + 2 * kTile12;
+      const uint32_t vt = sbase + map.stages + s * kStage12 + kTile12 + kTileKV;
       const uint32_t pb = sbase + map.slots + a * kPSlot;
       const uint64_t vd = smem_desc(vt, 16, 512, 4);
       if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 9; ++k)
-          umma_ss(tmem_base + a * kSlotCols12, smem_desc(pb + (k >> 2) * kPBlock, 16, 1024, 2) + 2 * (k & 3), vd + 64 * k, idesc_o, k);
+        for (int k = 0; k < 10; ++k)
+          if (k < ksteps) umma_ss(tmem_base + a * kSlotCols12, smem_desc(pb + (k >> 2) * kPBlock, 16, 1024, 2) + 2 * (k & 3), vd + 64 * k, idesc_o, k);
         umma_commit(bar_o + 8 * a);
         if (half == 1) umma_commit(bar_empty + 8 * s);
       }
@@ -272,6 +303,14 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
       // with (ci >= 6) == a, (cj >= 6) == b.
       const bool hm = kShifted && it.wy == p.nWy - 1, wm = kShifted && it.wx == p.nWx - 1;
       const bool my_h = ri >= kSplit, my_w = rj >= kSplit;
+      // window rows / columns of this window that are pad tokens (bit i of pi: window row i): the pad rows [H, Hp) of
+      // the image are rows [H - shift, Hp - shift) of the rolled image
+      int pi = 0, pj = 0;
+      if (has_pad) {
+        pi = span_bits(p.H - p.shift - it.wy * WS12, p.Hp - p.shift - it.wy * WS12);
+        pj = span_bits(p.W - p.shift - it.wx * WS12, p.Wp - p.shift - it.wx * WS12);
+      }
+      const bool wpad = (pi | pj) != 0;   // warp-uniform
 
       mbar_wait(bar_s + 8 * g, m & 1);
       tc_fence_after();
@@ -296,7 +335,16 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
           for (int e = 0; e < 64; e += 2)
             if (e < cols) mx4[(e >> 1) & 3] = fmaxf(mx4[(e >> 1) & 3], fmaxf(__uint_as_float(r[e]), __uint_as_float(r[e + 1])));
         }
-        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        // K rows of pad tokens are zero (TMA fill): their raw score is q . k_pad = S column 144.  (The zeros those
+        // columns held in the maximum above only loosen the bound.)
+        uint32_t s_pad = 0u;
+        if (wpad) {
+          TMEM_LD_X1(taddr + N12, s_pad);
+          tmem_ld_wait();
+          mx = fmaxf(mx, __uint_as_float(s_pad));
+        }
+        float pp_pad = 0.f;
         m_ub = fmaf(mx, c1s, bmax);
         float nm[2][2];
 #pragma unroll
@@ -315,6 +363,11 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
           for (int c = 0; c < kMaxCols / 16; ++c)
             if (16 * c < cols) TMEM_LD_X16(taddr + 64 * blk + 16 * c, (r + 16 * c));
           tmem_ld_wait();
+          if (wpad) {
+#pragma unroll
+            for (int e = 0; e < kMaxCols; ++e)
+              if (e < cols && (((pi >> row_i12<kPerm>(64 * blk + e)) | (pj >> row_j12<kPerm>(64 * blk + e))) & 1)) r[e] = s_pad;
+          }
           uint32_t w[kMaxCols / 2];
 #pragma unroll
           for (int e = 0; e < kMaxCols / 2; ++e) {
@@ -329,6 +382,12 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
               w[e] = pack_bf16(pp.x, pp.y);
             }
           }
+          if (wpad) {   // V rows of pad tokens are zero: their share of O is (their summed probability) x v_pad, below
+#pragma unroll
+            for (int e = 0; e < kMaxCols; ++e)
+              if (e < cols && (((pi >> row_i12<kPerm>(64 * blk + e)) | (pj >> row_j12<kPerm>(64 * blk + e))) & 1))
+                pp_pad += __uint_as_float((e & 1) ? (w[e >> 1] & 0xffff0000u) : (w[e >> 1] << 16));
+          }
           if (row_ok) {
             const uint32_t p_row = sl + blk * kPBlock + row * 128;
 #pragma unroll
@@ -342,6 +401,15 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
           }
         }
         l = l2.x + l2.y;
+        if (has_pad && row_ok) {
+          // P columns 144 / 145 = hi / lo bf16 halves of the pad probability (x V rows 144 / 145 = v_pad: the sum enters
+          // with 16 mantissa bits), columns 146 .. 159 zero: chunks 2 and 3 of the row in column block 2
+          const float hi = __uint_as_float(pack_bf16(pp_pad, 0.f) << 16);
+          const uint32_t p_row = sl + 2 * kPBlock + row * 128;
+          const uint32_t w8 = pack_bf16(hi, pp_pad - hi), z = 0u;
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%2,%2};" ::"r"(p_row + ((2 ^ (row & 7)) << 4)), "r"(w8), "r"(z) : "memory");
+          asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(p_row + ((3 ^ (row & 7)) << 4)), "r"(z) : "memory");
+        }
       }
       fence_proxy_async();
       tc_fence_before();
@@ -402,10 +470,10 @@ tc12_fwd_kernel(const Problem p, int n_win, int win_per_job, const __grid_consta
 bool tc12_forward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 12 || p.mask != nullptr || p.dropout_p > 0.0f) return false;
   if (p.shift != 0 && p.shift != tc12::kSplit) return false;
-  if (p.H != p.Hp || p.W != p.Wp) return false;   // padding: CUDA-core kernels
+  if (p.H < p.shift || p.W < p.shift) return false;   // the pad rows would wrap around the rolled image
   if ((p.q_ps | p.k_ps | p.v_ps | p.o_ps) & 7) return false;
   auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
-  if (mis(p.q) || mis(p.k) || mis(p.v) || mis(p.o)) return false;
+  if (mis(p.q) || mis(p.k) || mis(p.v) || mis(p.o) || mis(p.k_pad) || mis(p.v_pad)) return false;
   return tc::tma_available();
 }
 
@@ -431,11 +499,12 @@ cudaError_t launch_tc12_forward(const Problem& p, cudaStream_t st, const char** 
     if (err) *err = "cudaFuncSetAttribute(max dynamic smem) failed";
     return e;
   }
+  const int has_pad = (p.H != p.Hp || p.W != p.Wp) && (p.k_pad != nullptr || p.v_pad != nullptr) ? 1 : 0;
   int n_win, per, grid;
   tc::job_grid(p, tc::sm_count(), &n_win, &per, &grid);
   {
     TimedRegion timed(st);
-    kernel<<<grid, tc12::kThreads12, map.total, st>>>(p, n_win, per, maps);
+    kernel<<<grid, tc12::kThreads12, map.total, st>>>(p, n_win, per, has_pad, maps);
   }
   count_launch();
   return cudaGetLastError();

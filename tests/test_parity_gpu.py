@@ -91,6 +91,42 @@ def test_forward_ws12_tcgen05_matches_oracle(case):
     assert rel_err(got.float(), ref.float()) < TOL_BF16
 
 
+# un-aligned window-12 shapes (TMA zero-fill + pad vectors in the spare rows of the K / V tiles): the four ODA stage grids
+# of a 352 x 1216 image (88x304 .. 11x38, scaled down in batch / heads), one padded row or column only, pads that span
+# the last TWO window rows of a shifted block, a single window with every wrap, and no pad vectors at all (zero pads)
+TC12_PAD_CASES = [(12, 0, 1, 13, 25, 2, False, True), (12, 6, 1, 13, 25, 2, False, True), (12, 6, 1, 11, 38, 3, True, True),
+                  (12, 0, 2, 22, 76, 2, False, True), (12, 6, 1, 44, 152, 2, False, True), (12, 6, 1, 88, 304, 1, False, True),
+                  (12, 6, 2, 7, 9, 1, False, True), (12, 6, 1, 24, 31, 2, True, True), (12, 0, 1, 35, 24, 2, False, True),
+                  (12, 6, 1, 20, 30, 2, False, False), (12, 6, 1, 30, 18, 26, False, True)]
+
+
+@pytest.mark.parametrize("case", TC12_PAD_CASES)
+def test_forward_ws12_tcgen05_on_unaligned_tensors_matches_oracle(case):
+    ws, shift, b, h, w, nh, ext, with_pads = case
+    c = nh * 32
+    name = f"fwd12pad{case}"
+    packed = randn(name + ".p", b, h, w, (2 if ext else 3) * c).bfloat16()
+    v = randn(name + ".v", b, h, w, c).bfloat16() if ext else None
+    table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
+    # pad vectors of the size of the activations, so that a wrong or missing substitution is far outside the tolerance
+    pads = randn(name + ".pad", (2 if ext else 3) * c).bfloat16() if with_pads else None
+    v_pad = randn(name + ".vpad", c).bfloat16() if ext and with_pads else None
+    want, want_lse = _oracle(packed.float(), None if v is None else v.float(), table, ws, shift, nh,
+                             None if pads is None else pads.float(), None if v_pad is None else v_pad.float())
+    ps = (2 if ext else 3) * c
+    shp = _lib.Shape(b, h, w, nh, ws, shift, _lib.BF16, _lib.IMPL_TCGEN05, 32 ** -0.5, 0.0, 0, ps, ps, c if ext else ps, c, 0, 0)
+    assert _lib.load().swin_attn_uses_tcgen05(ctypes.byref(shp), 0) == 1
+    dev = lambda t: None if t is None else t.to(DEV)
+    got, lse = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, True,
+                                       _lib.IMPL_TCGEN05, None)
+    assert got.shape == (b, h, w, c)
+    check(rel_err(got.float(), want), TOL_BF16, "ws12 tcgen05, un-aligned")
+    check(rel_err(lse[:, :h, :w], want_lse[:, :h, :w]), TOL_BF16, "lse ws12 tcgen05, un-aligned")
+    ref, _ = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, False,
+                                     _lib.IMPL_SIMT, None)
+    check(rel_err(got.float(), ref.float()), TOL_BF16, "ws12 tcgen05 vs CUDA-core kernel, un-aligned")
+
+
 # window-aligned shapes for the backward: odd window counts (a job's last pair is half empty), several
 # window chunks per head, external v, shifted wrap rows / columns
 BWD_CASES = [c for c in CASES if c[3] % c[0] == 0 and c[4] % c[0] == 0] + [
