@@ -2,46 +2,76 @@
 // Swin-L/384 sibling of SURVEY.md §8f row 3 and the window-12 rows of the microbench sweep.  Round 1 served this shape on
 // the CUDA cores at 0.013 of the HBM roofline (2.4 ms per stage-0 launch).
 //
-// N = 144 tokens = 9 x 16: the window fits the warp-level m16n16k16 bf16 MMA (`mma.sync`, nvcuda::wmma) without any
-// padding, which the 128-lane tcgen05 accumulator does not (144 = 128 + 16 or 72 + 72: 44 % of the tile wasted, and the
-// S + dP + dQ/dK/dV accumulators of one unit already fill tensor memory).  This is therefore a
-// warp-MMA kernel on purpose; it is not the tcgen05 path and is labelled as such in DESIGN.md.
+// N = 144 tokens = 9 x 16: the window fits the warp-level m16n8k16 bf16 MMA (`mma.sync`) without any padding, which the
+// 128-lane tcgen05 accumulator does not (144 = 128 + 16 or 72 + 72: 44 % of the tile wasted, and the S + dP + dQ/dK/dV
+// accumulators of one unit already fill tensor memory).  This is therefore a warp-MMA kernel on
+// purpose; it is not the tcgen05 path and is labelled as such in DESIGN.md.
 //
-// One CTA = one job = (head, contiguous range of windows), 9 warps; warp w owns the 16-row strip w of every product:
-//   S strip  = Q_w K^T              (9 tiles x 2 k-steps)  -> fp32 strip in shared memory (warp-private)
-//   P        = exp2(S c + bias (+ mask) - lse)              -> bf16 rows of the P image
-//   dP strip = dO_w V^T                                     -> the same fp32 strip
-//   delta    = sum_j P dP (warp shuffles), dS = P (dP - delta) -> bf16 rows of the dS image
+// One CTA = one job = (head, contiguous range of windows), 9 warps; warp w owns the 16-row strip w of every product and
+// keeps its strips in REGISTERS (v2; v1 went through fp32 strips in shared memory with wmma load / store, 47 k warp
+// instructions per window):
+//   dP strip = dO_w V^T              18 n-tiles x 2 k-steps, 72 accumulator registers per thread
+//   S tile   = Q_w K^T (one n-tile at a time) -> P = exp2(S c + bias (+ mask) - lse) -> bf16 pairs (kept in registers and
+//              written to the P image), delta += P dP
+//   delta    = row sum over the quad;  dS = P (dP - delta) -> bf16 pairs: the dS image AND, as they are, the A fragments
+//              of dQ_w = scale dS_w K (the accumulator layout of two adjacent n-tiles is the A layout of one k-step)
 //   -- CTA barrier: the products below read every strip --
-//   dV_w = (P^T)_w dO     dK_w = scale (dS^T)_w Q     dQ_w = scale dS_w K      (9 k-steps x 2 tiles each)
+//   dV_w = (P^T)_w dO     dK_w = scale (dS^T)_w Q     (A fragments by ldmatrix.trans from the images)
 //   d_table bins += dS by relative position: one thread per bin gathers its diagonal (no atomics; the bins live in
 //   shared memory for the whole job and are added to global memory once per CTA)
-// q, k, v, dO rows are gathered from / dq, dk, dv rows scattered to the image-order tensors with the cyclic shift folded
-// into the token coordinates (newcrf_layers.py:220-227 / swin_transformer.py:212-219 and their inverses).
-#include <mma.h>
-
+// q, k, v, dO rows are gathered (cp.async, one window ahead, two tile buffers) from / dq, dk, dv rows scattered to the
+// image-order tensors with the cyclic shift folded into the token coordinates (newcrf_layers.py:220-227 /
+// swin_transformer.py:212-219 and their inverses).
 #include "swin_common.cuh"
 
 namespace swin {
 namespace mma12 {
 
-using namespace nvcuda;
-
 constexpr int N = 144, WS = 12, HD = 32, NT = 23 * 23;
 constexpr int kWarps = 9, kThreads = kWarps * 32;
 constexpr int kTileLd = 40;            // bf16 elements per row of the q / k / v / dO tiles (80 B: conflict-free ldmatrix rows)
-constexpr int kImgLd = 152;            // bf16 elements per row of the P / dS images
-constexpr int kStripLd = 148;          // fp32 elements per row of a warp's S / dP strip
+constexpr int kImgLd = 152;            // bf16 elements per row of the P / dS images (304 B: conflict-free ldmatrix rows)
+constexpr int kTile = N * kTileLd;
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct Smem {
-  __nv_bfloat16 q[N * kTileLd], k[N * kTileLd], v[N * kTileLd], d_o[N * kTileLd];
+  __nv_bfloat16 tile[2][4][kTile];     // q, k, v, dO of the current and the next window
   __nv_bfloat16 p[N * kImgLd], ds[N * kImgLd];
-  float strip[kWarps][16 * kStripLd];
-  float bias[NT + 3], bins[NT + 3];
-  float lse2[N];
-  unsigned char region[N];
+  float2 bias2[NT + 1];                // {b[NT-1-k], b[NT-2-k]} log2e: the biases of an (even, odd) key pair in one 8-byte load
+  float bins[NT + 3];
+  float lse[2][N];
 };
+
+__device__ __forceinline__ uint32_t s_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+// D (16 x 8, fp32) += A (16 x 16, row) B (16 x 8, col), bf16 operands
+__device__ __forceinline__ void mma_bf16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&v);
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 // token t of window (wy, wx) -> pixel of the (window-aligned) image, cyclic shift folded in (compile-time window size)
 __device__ __forceinline__ int64_t token_pixel(const Problem& p, int b, int wy, int wx, int t) {
@@ -56,188 +86,184 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t4 = lane & 3;                      // accumulator rows g / g + 8, columns 2 t4, 2 t4 + 1 of an n-tile
   const int h = (int)blockIdx.x % p.nH;
   const int w0 = ((int)blockIdx.x / p.nH) * win_per_job, w1 = min(w0 + win_per_job, n_win);
   const float c1 = p.scale * kLog2e;
 
   for (int i = tid; i < NT; i += kThreads) {
-    sm.bias[i] = p.table[i * p.nH + h] * kLog2e;
+    const float b0 = p.table[(NT - 1 - i) * p.nH + h] * kLog2e;
+    const float b1 = i + 1 < NT ? p.table[(NT - 2 - i) * p.nH + h] * kLog2e : 0.f;
+    sm.bias2[i] = make_float2(b0, b1);
     sm.bins[i] = 0.f;
   }
-  float* strip = sm.strip[warp];
   const int r0 = warp * 16;
+  // ldmatrix lane addressing.  "A pattern": matrices (rows 0-7, cols 0-7) (rows 8-15, cols 0-7) (rows 0-7, cols 8-15)
+  // (rows 8-15, cols 8-15); "T pattern" swaps the middle two.
+  const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8, la_col = ((lane >> 4) & 1) * 8;
+  const int lt_row = (lane & 7) + ((lane >> 4) & 1) * 8, lt_col = ((lane >> 3) & 1) * 8;
+  const int lb_row = lane & 7, lb_col = (lane >> 3) * 8;      // B of S / dP: 8 keys x 32 channels = four k-blocks of one n-tile
+  // this thread's rows: window coordinates and the row part of the reversed bias index, k = rb + (23 jy + jx)
+  const int i0 = r0 + g, i1 = i0 + 8;
+  const int iy0 = i0 / WS, ix0 = i0 - iy0 * WS, iy1 = i1 / WS, ix1 = i1 - iy1 * WS;
+  const int rb0 = 264 - 23 * iy0 - ix0, rb1 = 264 - 23 * iy1 - ix1;
 
   // The four tiles of a window (144 rows x 64 B each = 2304 16-byte chunks = 8 per thread) and its lse row are fetched
-  // into REGISTERS one window ahead, so that the global-load latency hides behind the previous window's math.
-  uint4 pre[8];
-  float lse_pre = 0.f;
-  auto fetch = [&](int w) {
+  // with cp.async one window ahead, into the other tile buffer.
+  auto fetch = [&](int w, int buf) {
     const int wx = w % p.nWx, wy = (w / p.nWx) % p.nWy, b = w / (p.nWx * p.nWy);
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
-      const int i = tid + u * kThreads, ch = i & 3, t = (i >> 2) % N, which = i / (4 * N);
-      const int64_t pix = token_pixel(p, b, wy, wx, t);
+      const int i = tid + u * kThreads, ch = i & 3, tk = (i >> 2) % N, which = i / (4 * N);
+      const int64_t pix = token_pixel(p, b, wy, wx, tk);
       const __nv_bfloat16* src = which == 0   ? static_cast<const __nv_bfloat16*>(p.q) + pix * p.q_ps
                                  : which == 1 ? static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps
                                  : which == 2 ? static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps
                                               : static_cast<const __nv_bfloat16*>(p.d_o) + pix * p.C;
-      pre[u] = __ldg(reinterpret_cast<const uint4*>(src + h * HD + ch * 8));
+      cp_async16(s_u32(&sm.tile[buf][which][tk * kTileLd + ch * 8]), src + h * HD + ch * 8);
     }
-    if (tid < N) lse_pre = __ldg(&p.lse[token_pixel(p, b, wy, wx, tid) * p.nH + h]);
+    if (tid < N) cp_async4(s_u32(&sm.lse[buf][tid]), &p.lse[token_pixel(p, b, wy, wx, tid) * p.nH + h]);
+    cp_async_commit();
   };
-  if (w0 < w1) fetch(w0);
+  if (w0 < w1) fetch(w0, 0);
 
   for (int w = w0; w < w1; ++w) {
+    const int buf = (w - w0) & 1;
     const int wx = w % p.nWx, wy = (w / p.nWx) % p.nWy, b = w / (p.nWx * p.nWy);
-    const bool masked = p.shift > 0 && (wy == p.nWy - 1 || wx == p.nWx - 1);
-    __syncthreads();   // the previous window's images, tiles and bins gather are done
-    // ---- the prefetched tiles, lse and the SW-MSA region ids -> shared memory; then the next window's fetch is issued ----
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int i = tid + u * kThreads, ch = i & 3, t = (i >> 2) % N, which = i / (4 * N);
-      __nv_bfloat16* dst = (which == 0 ? sm.q : which == 1 ? sm.k : which == 2 ? sm.v : sm.d_o) + t * kTileLd + ch * 8;
-      *reinterpret_cast<uint4*>(dst) = pre[u];
-    }
-    if (tid < N) {
-      sm.lse2[tid] = lse_pre * kLog2e;
-      sm.region[tid] = masked ? (unsigned char)region_id(p, wy, wx, tid) : 0;
-    }
-    __syncthreads();
-    if (w + 1 < w1) fetch(w + 1);
+    // SW-MSA mask (swin_transformer.py:361-380): regions split at window row / column 6 in the last window row / column
+    const bool hm = p.shift > 0 && wy == p.nWy - 1, wm = p.shift > 0 && wx == p.nWx - 1;
+    const bool masked = hm || wm;
+    cp_async_wait_all();
+    __syncthreads();   // this window's tiles have landed; the previous window's images, tiles and bins gather are done
+    if (w + 1 < w1) fetch(w + 1, buf ^ 1);
+    const __nv_bfloat16 *tq = sm.tile[buf][0], *tk_ = sm.tile[buf][1], *tv = sm.tile[buf][2], *td = sm.tile[buf][3];
+    const float nl0 = -sm.lse[buf][i0] * kLog2e, nl1 = -sm.lse[buf][i1] * kLog2e;
 
-    // ---- S strip = Q_w K^T ----
+    // ---- dP strip = dO_w V^T (registers) ----
+    float dp[18][4];
     {
-      wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::row_major> a[2];
-      wmma::load_matrix_sync(a[0], sm.q + r0 * kTileLd, kTileLd);
-      wmma::load_matrix_sync(a[1], sm.q + r0 * kTileLd + 16, kTileLd);
+      uint32_t a[2][4];
+      ldsm_x4(a[0], s_u32(td + (r0 + la_row) * kTileLd + la_col));
+      ldsm_x4(a[1], s_u32(td + (r0 + la_row) * kTileLd + la_col + 16));
 #pragma unroll
-      for (int jt = 0; jt < 9; ++jt) {
-        wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc;
-        wmma::fill_fragment(acc, 0.f);
-#pragma unroll
-        for (int kk = 0; kk < 2; ++kk) {
-          wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::col_major> bk;   // B[d][j] = K[j][d]
-          wmma::load_matrix_sync(bk, sm.k + jt * 16 * kTileLd + kk * 16, kTileLd);
-          wmma::mma_sync(acc, a[kk], bk, acc);
-        }
-        wmma::store_matrix_sync(strip + jt * 16, acc, kStripLd, wmma::mem_row_major);
+      for (int nt = 0; nt < 18; ++nt) {
+        uint32_t bv[4];
+        ldsm_x4(bv, s_u32(tv + (nt * 8 + lb_row) * kTileLd + lb_col));
+        dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
+        mma_bf16(dp[nt], a[0][0], a[0][1], a[0][2], a[0][3], bv[0], bv[1]);
+        mma_bf16(dp[nt], a[1][0], a[1][1], a[1][2], a[1][3], bv[2], bv[3]);
       }
     }
-    __syncwarp();
-    // ---- P = exp2(S c + bias (+ mask) - lse) -> bf16 P rows; kept in the strip as fp32 for dS ----
-    int cj[5], rg[5];   // this lane's columns j = lane + 32 u: relative-index offset jy * 23 + jx and SW-MSA region
-#pragma unroll
-    for (int u = 0; u < 5; ++u) {
-      const int j = min(lane + 32 * u, N - 1), jy = j / WS;
-      cj[u] = jy * (2 * WS - 1) + (j - jy * WS);
-      rg[u] = sm.region[j];
-    }
-    for (int rr = 0; rr < 16; ++rr) {
-      const int i = r0 + rr, iy = i / WS;
-      const float* brow = sm.bias + iy * (2 * WS - 1) + (i - iy * WS) + (WS - 1) * 2 * WS;   // index = brow_off - cj
-      const float nl = -sm.lse2[i];
-      const int ri = sm.region[i];
-#pragma unroll
-      for (int u = 0; u < 5; ++u) {
-        const int j = lane + 32 * u;
-        if (j < N) {
-          float t = fmaf(strip[rr * kStripLd + j], c1, brow[-cj[u]] + nl);
-          if (masked && rg[u] != ri) t += -100.0f * kLog2e;
-          float pr;
-          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(pr) : "f"(t));
-          sm.p[i * kImgLd + j] = __float2bfloat16_rn(pr);
-        }
-      }
-    }
-    __syncwarp();
-    // ---- dP strip = dO_w V^T ----
+    // ---- S = Q_w K^T one n-tile at a time; P = exp2(S c + bias (+ mask) - lse) -> bf16 pairs; delta += P dP ----
+    uint32_t pk[18][2];   // [n-tile][row g / g + 8]: first P, then dS
+    float d0 = 0.f, d1 = 0.f;
     {
-      wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::row_major> a[2];
-      wmma::load_matrix_sync(a[0], sm.d_o + r0 * kTileLd, kTileLd);
-      wmma::load_matrix_sync(a[1], sm.d_o + r0 * kTileLd + 16, kTileLd);
+      uint32_t a[2][4];
+      ldsm_x4(a[0], s_u32(tq + (r0 + la_row) * kTileLd + la_col));
+      ldsm_x4(a[1], s_u32(tq + (r0 + la_row) * kTileLd + la_col + 16));
+      const bool my_h0 = iy0 >= 6, my_w0 = ix0 >= 6, my_h1 = iy1 >= 6, my_w1 = ix1 >= 6;
 #pragma unroll
-      for (int jt = 0; jt < 9; ++jt) {
-        wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc;
-        wmma::fill_fragment(acc, 0.f);
-#pragma unroll
-        for (int kk = 0; kk < 2; ++kk) {
-          wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::col_major> bv;
-          wmma::load_matrix_sync(bv, sm.v + jt * 16 * kTileLd + kk * 16, kTileLd);
-          wmma::mma_sync(acc, a[kk], bv, acc);
+      for (int nt = 0; nt < 18; ++nt) {
+        uint32_t bk[4];
+        ldsm_x4(bk, s_u32(tk_ + (nt * 8 + lb_row) * kTileLd + lb_col));
+        float sc[4] = {0.f, 0.f, 0.f, 0.f};
+        mma_bf16(sc, a[0][0], a[0][1], a[0][2], a[0][3], bk[0], bk[1]);
+        mma_bf16(sc, a[1][0], a[1][1], a[1][2], a[1][3], bk[2], bk[3]);
+        const int j = nt * 8 + 2 * t4;                 // keys j, j + 1: same window row, neighbouring columns
+        const int jy = (j * 171) >> 11, jx = j - jy * WS;   // j / 12 for j < 144
+        const int cj = j + 11 * jy;                    // 23 jy + jx
+        const float2 bb0 = sm.bias2[rb0 + cj], bb1 = sm.bias2[rb1 + cj];
+        float m0 = nl0, m1 = nl1;
+        if (masked) {   // warp-uniform; both keys of the pair lie in the same region
+          const bool kh = jy >= 6, kw = jx >= 6;
+          if ((hm && kh != my_h0) || (wm && kw != my_w0)) m0 += -100.0f * kLog2e;
+          if ((hm && kh != my_h1) || (wm && kw != my_w1)) m1 += -100.0f * kLog2e;
         }
-        wmma::store_matrix_sync(strip + jt * 16, acc, kStripLd, wmma::mem_row_major);
+        const uint32_t p0 = pack2(ex2(fmaf(sc[0], c1, bb0.x + m0)), ex2(fmaf(sc[1], c1, bb0.y + m0)));
+        const uint32_t p1 = pack2(ex2(fmaf(sc[2], c1, bb1.x + m1)), ex2(fmaf(sc[3], c1, bb1.y + m1)));
+        pk[nt][0] = p0;
+        pk[nt][1] = p1;
+        *reinterpret_cast<uint32_t*>(&sm.p[i0 * kImgLd + j]) = p0;
+        *reinterpret_cast<uint32_t*>(&sm.p[i1 * kImgLd + j]) = p1;
+        // the bf16-rounded probabilities, as the products below see them
+        d0 = fmaf(__uint_as_float(p0 << 16), dp[nt][0], fmaf(__uint_as_float(p0 & 0xffff0000u), dp[nt][1], d0));
+        d1 = fmaf(__uint_as_float(p1 << 16), dp[nt][2], fmaf(__uint_as_float(p1 & 0xffff0000u), dp[nt][3], d1));
       }
     }
-    __syncwarp();
-    // ---- delta = sum_j P dP ; dS = P (dP - delta) -> bf16 dS rows ----
-    for (int rr = 0; rr < 16; ++rr) {
-      const int i = r0 + rr;
-      float pv[5], dv[5], acc = 0.f;
+    d0 += __shfl_xor_sync(0xffffffffu, d0, 1);
+    d0 += __shfl_xor_sync(0xffffffffu, d0, 2);
+    d1 += __shfl_xor_sync(0xffffffffu, d1, 1);
+    d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
+    // ---- dS = P (dP - delta) -> bf16 pairs: the dS image and the A fragments of dQ ----
 #pragma unroll
-      for (int u = 0; u < 5; ++u) {
-        const int j = lane + 32 * u;
-        pv[u] = j < N ? __bfloat162float(sm.p[i * kImgLd + j]) : 0.f;
-        dv[u] = j < N ? strip[rr * kStripLd + j] : 0.f;
-        acc = fmaf(pv[u], dv[u], acc);
+    for (int nt = 0; nt < 18; ++nt) {
+      const int j = nt * 8 + 2 * t4;
+      const uint32_t p0 = pk[nt][0], p1 = pk[nt][1];
+      const uint32_t s0 = pack2(__uint_as_float(p0 << 16) * (dp[nt][0] - d0), __uint_as_float(p0 & 0xffff0000u) * (dp[nt][1] - d0));
+      const uint32_t s1 = pack2(__uint_as_float(p1 << 16) * (dp[nt][2] - d1), __uint_as_float(p1 & 0xffff0000u) * (dp[nt][3] - d1));
+      pk[nt][0] = s0;
+      pk[nt][1] = s1;
+      *reinterpret_cast<uint32_t*>(&sm.ds[i0 * kImgLd + j]) = s0;
+      *reinterpret_cast<uint32_t*>(&sm.ds[i1 * kImgLd + j]) = s1;
+    }
+    const int64_t pix0 = token_pixel(p, b, wy, wx, i0), pix1 = token_pixel(p, b, wy, wx, i1);
+    // 16 x 32 fp32 accumulator (four n-tiles) -> bf16 -> rows i0 / i1 of an image-order tensor
+    auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl) {
+      __nv_bfloat16* d0p = static_cast<__nv_bfloat16*>(base) + pix0 * ps + h * HD + 2 * t4;
+      __nv_bfloat16* d1p = static_cast<__nv_bfloat16*>(base) + pix1 * ps + h * HD + 2 * t4;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        *reinterpret_cast<uint32_t*>(d0p + nt * 8) = pack2(acc[nt][0] * scl, acc[nt][1] * scl);
+        *reinterpret_cast<uint32_t*>(d1p + nt * 8) = pack2(acc[nt][2] * scl, acc[nt][3] * scl);
       }
+    };
+    // ---- dQ_w = scale dS_w K: A from the registers, B = K (keys x channels) by transposing loads ----
+    {
+      float acc[4][4];
 #pragma unroll
-      for (int off = 16; off; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+      for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
 #pragma unroll
-      for (int u = 0; u < 5; ++u) {
-        const int j = lane + 32 * u;
-        if (j < N) sm.ds[i * kImgLd + j] = __float2bfloat16_rn(pv[u] * (dv[u] - acc));
+      for (int kt = 0; kt < 9; ++kt) {
+        uint32_t b0[4], b1[4];
+        ldsm_x4_t(b0, s_u32(tk_ + (kt * 16 + la_row) * kTileLd + la_col));
+        ldsm_x4_t(b1, s_u32(tk_ + (kt * 16 + la_row) * kTileLd + la_col + 16));
+        const uint32_t a0 = pk[2 * kt][0], a1 = pk[2 * kt][1], a2 = pk[2 * kt + 1][0], a3 = pk[2 * kt + 1][1];
+        mma_bf16(acc[0], a0, a1, a2, a3, b0[0], b0[1]);
+        mma_bf16(acc[1], a0, a1, a2, a3, b0[2], b0[3]);
+        mma_bf16(acc[2], a0, a1, a2, a3, b1[0], b1[1]);
+        mma_bf16(acc[3], a0, a1, a2, a3, b1[2], b1[3]);
       }
+      put(acc, p.dq, p.q_ps, p.scale);
     }
     __syncthreads();   // every strip of P and dS is written
 
-    // ---- dV_w = (P^T)_w dO, dK_w = (dS^T)_w Q, dQ_w = dS_w K: 16 x 32 each, staged in the warp's strip ----
+    // ---- dV_w = (P^T)_w dO, dK_w = scale (dS^T)_w Q: A = the image, transposed on load; rows = this warp's 16 keys ----
 #pragma unroll
-    for (int which = 0; which < 3; ++which) {
+    for (int which = 0; which < 2; ++which) {
       const __nv_bfloat16* img = which == 0 ? sm.p : sm.ds;
-      const __nv_bfloat16* rhs = which == 0 ? sm.d_o : which == 1 ? sm.q : sm.k;
-      wmma::fragment<wmma::accumulator, 16, 16, 16, float> acc[2];
-      wmma::fill_fragment(acc[0], 0.f);
-      wmma::fill_fragment(acc[1], 0.f);
+      const __nv_bfloat16* rhs = which == 0 ? td : tq;
+      float acc[4][4];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
 #pragma unroll
       for (int kt = 0; kt < 9; ++kt) {
-        wmma::fragment<wmma::matrix_b, 16, 16, 16, __nv_bfloat16, wmma::row_major> b0, b1;
-        wmma::load_matrix_sync(b0, rhs + kt * 16 * kTileLd, kTileLd);
-        wmma::load_matrix_sync(b1, rhs + kt * 16 * kTileLd + 16, kTileLd);
-        if (which < 2) {   // A[j][i] = img[i][j]: column-major view of the image, rows = this warp's 16 keys
-          wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::col_major> a;
-          wmma::load_matrix_sync(a, img + kt * 16 * kImgLd + r0, kImgLd);
-          wmma::mma_sync(acc[0], a, b0, acc[0]);
-          wmma::mma_sync(acc[1], a, b1, acc[1]);
-        } else {
-          wmma::fragment<wmma::matrix_a, 16, 16, 16, __nv_bfloat16, wmma::row_major> a;
-          wmma::load_matrix_sync(a, img + r0 * kImgLd + kt * 16, kImgLd);
-          wmma::mma_sync(acc[0], a, b0, acc[0]);
-          wmma::mma_sync(acc[1], a, b1, acc[1]);
-        }
+        uint32_t a[4], b0[4], b1[4];
+        ldsm_x4_t(a, s_u32(img + (kt * 16 + lt_row) * kImgLd + r0 + lt_col));
+        ldsm_x4_t(b0, s_u32(rhs + (kt * 16 + la_row) * kTileLd + la_col));
+        ldsm_x4_t(b1, s_u32(rhs + (kt * 16 + la_row) * kTileLd + la_col + 16));
+        mma_bf16(acc[0], a[0], a[1], a[2], a[3], b0[0], b0[1]);
+        mma_bf16(acc[1], a[0], a[1], a[2], a[3], b0[2], b0[3]);
+        mma_bf16(acc[2], a[0], a[1], a[2], a[3], b1[0], b1[1]);
+        mma_bf16(acc[3], a[0], a[1], a[2], a[3], b1[2], b1[3]);
       }
-      wmma::store_matrix_sync(strip + which * 32, acc[0], kStripLd, wmma::mem_row_major);
-      wmma::store_matrix_sync(strip + which * 32 + 16, acc[1], kStripLd, wmma::mem_row_major);
-    }
-    __syncwarp();
-    // rows of dV | dK | dQ (fp32, columns [0,32) [32,64) [64,96) of the strip) -> bf16 -> the tokens' pixels
-    for (int i = lane; i < 16 * 3 * 4; i += 32) {
-      const int ch = i & 3, which = (i >> 2) % 3, rr = i / 12;
-      const int64_t pix = token_pixel(p, b, wy, wx, r0 + rr);
-      const float sc = which == 0 ? 1.0f : p.scale;
-      const float* src = strip + rr * kStripLd + which * 32 + ch * 8;
-      __align__(16) __nv_bfloat16 out[8];
-#pragma unroll
-      for (int e = 0; e < 8; ++e) out[e] = __float2bfloat16_rn(src[e] * sc);
-      __nv_bfloat16* dst = which == 0   ? static_cast<__nv_bfloat16*>(p.dv) + pix * p.v_ps
-                           : which == 1 ? static_cast<__nv_bfloat16*>(p.dk) + pix * p.k_ps
-                                        : static_cast<__nv_bfloat16*>(p.dq) + pix * p.q_ps;
-      *reinterpret_cast<uint4*>(dst + h * HD + ch * 8) = *reinterpret_cast<const uint4*>(out);
+      if (which == 0) put(acc, p.dv, p.v_ps, 1.0f);
+      else put(acc, p.dk, p.k_ps, p.scale);
     }
     // ---- bias-table gradient: bin (di, dj) += sum over keys (cy, cx) of dS[(cy + di, cx + dj)][(cy, cx)], in two steps.
     // (1) Two threads per (query row qy, key row ky): each takes 6 of the 12 query columns of that 12 x 12 block of dS and
     //     sums it along its 23 x-diagonals in registers (fully unrolled: no divergence, no atomics).
-    __syncthreads();   // every warp has written its output rows: the strips are free and become the diagonal sums,
-    float* diag = &sm.strip[0][0];   // [half][query row qy][key row ky][24]: dS summed over the x diagonals of a 12 x 12 block
+    __syncthreads();   // every warp is done with the P image: it becomes the diagonal sums
+    float* diag = reinterpret_cast<float*>(sm.p);   // [half][query row qy][key row ky][24]: dS summed over the x diagonals of a 12 x 12 block
     {
       const int pair = tid >> 1, half = tid & 1, qy = pair / WS, ky = pair - qy * WS;
       float dg[17];   // local diagonals e = qx6 - kx in [-11, 5], stored at e + 11

@@ -132,6 +132,8 @@ def test_forward_ws12_tcgen05_on_unaligned_tensors_matches_oracle(case):
 BWD_CASES = [c for c in CASES if c[3] % c[0] == 0 and c[4] % c[0] == 0] + [
     (7, 0, 1, 7, 21, 3, False), (7, 3, 1, 21, 35, 4, True), (7, 3, 3, 28, 49, 6, False), (7, 0, 5, 35, 63, 2, True),
     (7, 3, 1, 7, 7, 2, False), (7, 3, 2, 14, 7, 48, False),
+    # window 12 (warp-MMA backward): single window with every wrap, odd window counts per job, several chunks, many heads
+    (12, 6, 2, 12, 12, 1, False), (12, 0, 1, 36, 60, 3, False), (12, 6, 3, 48, 24, 6, True), (12, 6, 1, 12, 24, 24, False),
 ]
 
 
