@@ -7,39 +7,42 @@
 // accumulators of one unit already fill tensor memory).  This is therefore a warp-MMA kernel on
 // purpose; it is not the tcgen05 path and is labelled as such in DESIGN.md.
 //
-// One CTA = one job = (head, contiguous range of windows), 9 warps; warp w owns the 16-row strip w of every product and
-// keeps its strips in REGISTERS (v2; v1 went through fp32 strips in shared memory with wmma load / store, 47 k warp
-// instructions per window):
-//   dP strip = dO_w V^T              18 n-tiles x 2 k-steps, 72 accumulator registers per thread
-//   S tile   = Q_w K^T (one n-tile at a time) -> P = exp2(S c + bias (+ mask) - lse) -> bf16 pairs (kept in registers and
-//              written to the P image), delta += P dP
-//   delta    = row sum over the quad;  dS = P (dP - delta) -> bf16 pairs: the dS image AND, as they are, the A fragments
-//              of dQ_w = scale dS_w K (the accumulator layout of two adjacent n-tiles is the A layout of one k-step)
+// One CTA = one job = (head, contiguous range of windows), 18 warps.  Two warps share the 16-row strip s = warp / 2 of
+// the query-side products and split its key columns (n-tiles 0-9 / 10-17); everything a strip needs stays in REGISTERS
+// (v1 went through fp32 strips in shared memory with wmma load / store: 47 k warp instructions per window, 459 us on
+// the ODA stage-0 grid; v2, 9 warps with whole strips in registers: 21 k, 214 us, latency-bound at 2.25 warps per
+// scheduler; v3 is this one):
+//   delta    = rowsum(dO . O) of the strip's rows, from the dO / O tiles (so no row sum over the other warp's columns)
+//   per n-tile (8 keys): S = Q_s K^T and dP = dO_s V^T (two k-steps each) -> P = exp2(S c + bias (+ mask) - lse),
+//              dS = P (dP - delta) -> bf16 pairs into the P / dS images; the dS pairs stay in registers: the
+//              accumulator layout of two adjacent n-tiles is the A-fragment layout of one k-step of dQ_s = scale dS_s K
+//   dQ       = the two warps' partial products, summed through shared memory (lane-major, conflict-free)
 //   -- CTA barrier: the products below read every strip --
-//   dV_w = (P^T)_w dO     dK_w = scale (dS^T)_w Q     (A fragments by ldmatrix.trans from the images)
+//   warp 2s: dV_s = (P^T)_s dO     warp 2s+1: dK_s = scale (dS^T)_s Q     (A fragments by ldmatrix.trans from the images)
 //   d_table bins += dS by relative position: one thread per bin gathers its diagonal (no atomics; the bins live in
 //   shared memory for the whole job and are added to global memory once per CTA)
-// q, k, v, dO rows are gathered (cp.async, one window ahead, two tile buffers) from / dq, dk, dv rows scattered to the
-// image-order tensors with the cyclic shift folded into the token coordinates (newcrf_layers.py:220-227 /
-// swin_transformer.py:212-219 and their inverses).
+// q, k, v, dO, o rows are gathered (cp.async, one window ahead, two tile buffers; one token per thread) from / dq, dk, dv
+// rows scattered to the image-order tensors with the cyclic shift folded into the token coordinates
+// (newcrf_layers.py:220-227 / swin_transformer.py:212-219 and their inverses).
 #include "swin_common.cuh"
 
 namespace swin {
 namespace mma12 {
 
 constexpr int N = 144, WS = 12, HD = 32, NT = 23 * 23;
-constexpr int kWarps = 9, kThreads = kWarps * 32;
-constexpr int kTileLd = 40;            // bf16 elements per row of the q / k / v / dO tiles (80 B: conflict-free ldmatrix rows)
+constexpr int kWarps = 18, kThreads = kWarps * 32;
+constexpr int kTileLd = 40;            // bf16 elements per row of the q / k / v / dO / o tiles (80 B: conflict-free ldmatrix rows)
 constexpr int kImgLd = 152;            // bf16 elements per row of the P / dS images (304 B: conflict-free ldmatrix rows)
 constexpr int kTile = N * kTileLd;
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct Smem {
-  __nv_bfloat16 tile[2][4][kTile];     // q, k, v, dO of the current and the next window
+  __nv_bfloat16 tile[2][5][kTile];     // q, k, v, dO, o of the current and the next window
   __nv_bfloat16 p[N * kImgLd], ds[N * kImgLd];
   float2 bias2[NT + 1];                // {b[NT-1-k], b[NT-2-k]} log2e: the biases of an (even, odd) key pair in one 8-byte load
   float bins[NT + 3];
   float lse[2][N];
+  float dqx[9][16][32];                // dQ partial of the odd warp of a strip: [accumulator register][lane]
 };
 
 __device__ __forceinline__ uint32_t s_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
@@ -73,19 +76,32 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
-// token t of window (wy, wx) -> pixel of the (window-aligned) image, cyclic shift folded in (compile-time window size)
-__device__ __forceinline__ int64_t token_pixel(const Problem& p, int b, int wy, int wx, int t) {
-  const int i = t / WS, j = t - i * WS;
-  int y = wy * WS + i + p.shift, x = wx * WS + j + p.shift;
+// Token (ty, tx) of window (wy, wx) of image b -> pixel of the (window-aligned) image, cyclic shift folded in.
+__device__ __forceinline__ int64_t token_pixel(const Problem& p, int b, int wy, int wx, int ty, int tx) {
+  int y = wy * WS + ty + p.shift, x = wx * WS + tx + p.shift;
   if (y >= p.H) y -= p.H;
   if (x >= p.W) x -= p.W;
   return ((int64_t)b * p.H + y) * p.W + x;
 }
+struct Win {
+  int b, wy, wx;
+  __device__ __forceinline__ void next(const Problem& p) {
+    if (++wx == p.nWx) {
+      wx = 0;
+      if (++wy == p.nWy) {
+        wy = 0;
+        ++b;
+      }
+    }
+  }
+};
+__device__ __forceinline__ void pair_barrier(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
 
 __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p, int n_win, int win_per_job) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int strip = warp >> 1, kh = warp & 1;                  // kh: which part of the strip's key columns / which of dV, dK
   const int g = lane >> 2, t4 = lane & 3;                      // accumulator rows g / g + 8, columns 2 t4, 2 t4 + 1 of an n-tile
   const int h = (int)blockIdx.x % p.nH;
   const int w0 = ((int)blockIdx.x / p.nH) * win_per_job, w1 = min(w0 + win_per_job, n_win);
@@ -97,7 +113,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     sm.bias2[i] = make_float2(b0, b1);
     sm.bins[i] = 0.f;
   }
-  const int r0 = warp * 16;
+  const int r0 = strip * 16;
+  const int n0 = kh ? 10 : 0, n_cnt = kh ? 8 : 10;             // this warp's n-tiles (8 keys each) = 5 / 4 k-steps of dQ
   // ldmatrix lane addressing.  "A pattern": matrices (rows 0-7, cols 0-7) (rows 8-15, cols 0-7) (rows 0-7, cols 8-15)
   // (rows 8-15, cols 8-15); "T pattern" swaps the middle two.
   const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8, la_col = ((lane >> 4) & 1) * 8;
@@ -107,106 +124,108 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   const int i0 = r0 + g, i1 = i0 + 8;
   const int iy0 = i0 / WS, ix0 = i0 - iy0 * WS, iy1 = i1 / WS, ix1 = i1 - iy1 * WS;
   const int rb0 = 264 - 23 * iy0 - ix0, rb1 = 264 - 23 * iy1 - ix1;
+  const bool my_h0 = iy0 >= 6, my_w0 = ix0 >= 6, my_h1 = iy1 >= 6, my_w1 = ix1 >= 6;
 
-  // The four tiles of a window (144 rows x 64 B each = 2304 16-byte chunks = 8 per thread) and its lse row are fetched
-  // with cp.async one window ahead, into the other tile buffer.
-  auto fetch = [&](int w, int buf) {
-    const int wx = w % p.nWx, wy = (w / p.nWx) % p.nWy, b = w / (p.nWx * p.nWy);
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int i = tid + u * kThreads, ch = i & 3, tk = (i >> 2) % N, which = i / (4 * N);
-      const int64_t pix = token_pixel(p, b, wy, wx, tk);
-      const __nv_bfloat16* src = which == 0   ? static_cast<const __nv_bfloat16*>(p.q) + pix * p.q_ps
-                                 : which == 1 ? static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps
-                                 : which == 2 ? static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps
-                                              : static_cast<const __nv_bfloat16*>(p.d_o) + pix * p.C;
-      cp_async16(s_u32(&sm.tile[buf][which][tk * kTileLd + ch * 8]), src + h * HD + ch * 8);
-    }
-    if (tid < N) cp_async4(s_u32(&sm.lse[buf][tid]), &p.lse[token_pixel(p, b, wy, wx, tid) * p.nH + h]);
+  // The five tiles of a window (144 rows x 64 B each: one token per four threads, one 16-byte chunk of each tensor per
+  // thread) and its lse row are fetched with cp.async one window ahead, into the other tile buffer.
+  const int ft = tid >> 2, fch = tid & 3, fty = ft / WS, ftx = ft - fty * WS;
+  auto fetch = [&](const Win& wn, int buf) {
+    const int64_t pix = token_pixel(p, wn.b, wn.wy, wn.wx, fty, ftx);
+    const int off = h * HD + fch * 8;
+    const uint32_t dst = s_u32(&sm.tile[buf][0][ft * kTileLd + fch * 8]);
+    cp_async16(dst, static_cast<const __nv_bfloat16*>(p.q) + pix * p.q_ps + off);
+    cp_async16(dst + 2 * kTile, static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps + off);
+    cp_async16(dst + 4 * kTile, static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps + off);
+    cp_async16(dst + 6 * kTile, static_cast<const __nv_bfloat16*>(p.d_o) + pix * p.C + off);
+    cp_async16(dst + 8 * kTile, static_cast<const __nv_bfloat16*>(p.o_in) + pix * p.C + off);
+    if (fch == 0) cp_async4(s_u32(&sm.lse[buf][ft]), &p.lse[pix * p.nH + h]);
     cp_async_commit();
   };
-  if (w0 < w1) fetch(w0, 0);
+  Win cur, nxt;
+  cur.wx = w0 % p.nWx;
+  cur.wy = (w0 / p.nWx) % p.nWy;
+  cur.b = w0 / (p.nWx * p.nWy);
+  nxt = cur;
+  if (w0 < w1) fetch(cur, 0);
 
-  for (int w = w0; w < w1; ++w) {
+  for (int w = w0; w < w1; ++w, cur = nxt) {
     const int buf = (w - w0) & 1;
-    const int wx = w % p.nWx, wy = (w / p.nWx) % p.nWy, b = w / (p.nWx * p.nWy);
     // SW-MSA mask (swin_transformer.py:361-380): regions split at window row / column 6 in the last window row / column
-    const bool hm = p.shift > 0 && wy == p.nWy - 1, wm = p.shift > 0 && wx == p.nWx - 1;
+    const bool hm = p.shift > 0 && cur.wy == p.nWy - 1, wm = p.shift > 0 && cur.wx == p.nWx - 1;
     const bool masked = hm || wm;
     cp_async_wait_all();
     __syncthreads();   // this window's tiles have landed; the previous window's images, tiles and bins gather are done
-    if (w + 1 < w1) fetch(w + 1, buf ^ 1);
-    const __nv_bfloat16 *tq = sm.tile[buf][0], *tk_ = sm.tile[buf][1], *tv = sm.tile[buf][2], *td = sm.tile[buf][3];
+    nxt.next(p);
+    if (w + 1 < w1) fetch(nxt, buf ^ 1);
+    const __nv_bfloat16 *tq = sm.tile[buf][0], *tk_ = sm.tile[buf][1], *tv = sm.tile[buf][2], *td = sm.tile[buf][3], *to = sm.tile[buf][4];
     const float nl0 = -sm.lse[buf][i0] * kLog2e, nl1 = -sm.lse[buf][i1] * kLog2e;
+    const int64_t pix0 = token_pixel(p, cur.b, cur.wy, cur.wx, iy0, ix0), pix1 = token_pixel(p, cur.b, cur.wy, cur.wx, iy1, ix1);
 
-    // ---- dP strip = dO_w V^T (registers) ----
-    float dp[18][4];
+    // ---- delta = rowsum(dO . O) of rows i0, i1: 8 channels per lane of the quad ----
+    float d0, d1;
     {
-      uint32_t a[2][4];
-      ldsm_x4(a[0], s_u32(td + (r0 + la_row) * kTileLd + la_col));
-      ldsm_x4(a[1], s_u32(td + (r0 + la_row) * kTileLd + la_col + 16));
+      auto dot8 = [](uint4 x, uint4 y) {
+        const __nv_bfloat162* xa = reinterpret_cast<const __nv_bfloat162*>(&x);
+        const __nv_bfloat162* ya = reinterpret_cast<const __nv_bfloat162*>(&y);
+        float acc = 0.f;
 #pragma unroll
-      for (int nt = 0; nt < 18; ++nt) {
-        uint32_t bv[4];
-        ldsm_x4(bv, s_u32(tv + (nt * 8 + lb_row) * kTileLd + lb_col));
-        dp[nt][0] = dp[nt][1] = dp[nt][2] = dp[nt][3] = 0.f;
-        mma_bf16(dp[nt], a[0][0], a[0][1], a[0][2], a[0][3], bv[0], bv[1]);
-        mma_bf16(dp[nt], a[1][0], a[1][1], a[1][2], a[1][3], bv[2], bv[3]);
-      }
-    }
-    // ---- S = Q_w K^T one n-tile at a time; P = exp2(S c + bias (+ mask) - lse) -> bf16 pairs; delta += P dP ----
-    uint32_t pk[18][2];   // [n-tile][row g / g + 8]: first P, then dS
-    float d0 = 0.f, d1 = 0.f;
-    {
-      uint32_t a[2][4];
-      ldsm_x4(a[0], s_u32(tq + (r0 + la_row) * kTileLd + la_col));
-      ldsm_x4(a[1], s_u32(tq + (r0 + la_row) * kTileLd + la_col + 16));
-      const bool my_h0 = iy0 >= 6, my_w0 = ix0 >= 6, my_h1 = iy1 >= 6, my_w1 = ix1 >= 6;
-#pragma unroll
-      for (int nt = 0; nt < 18; ++nt) {
-        uint32_t bk[4];
-        ldsm_x4(bk, s_u32(tk_ + (nt * 8 + lb_row) * kTileLd + lb_col));
-        float sc[4] = {0.f, 0.f, 0.f, 0.f};
-        mma_bf16(sc, a[0][0], a[0][1], a[0][2], a[0][3], bk[0], bk[1]);
-        mma_bf16(sc, a[1][0], a[1][1], a[1][2], a[1][3], bk[2], bk[3]);
-        const int j = nt * 8 + 2 * t4;                 // keys j, j + 1: same window row, neighbouring columns
-        const int jy = (j * 171) >> 11, jx = j - jy * WS;   // j / 12 for j < 144
-        const int cj = j + 11 * jy;                    // 23 jy + jx
-        const float2 bb0 = sm.bias2[rb0 + cj], bb1 = sm.bias2[rb1 + cj];
-        float m0 = nl0, m1 = nl1;
-        if (masked) {   // warp-uniform; both keys of the pair lie in the same region
-          const bool kh = jy >= 6, kw = jx >= 6;
-          if ((hm && kh != my_h0) || (wm && kw != my_w0)) m0 += -100.0f * kLog2e;
-          if ((hm && kh != my_h1) || (wm && kw != my_w1)) m1 += -100.0f * kLog2e;
+        for (int e = 0; e < 4; ++e) {
+          const float2 xf = __bfloat1622float2(xa[e]), yf = __bfloat1622float2(ya[e]);
+          acc = fmaf(xf.x, yf.x, fmaf(xf.y, yf.y, acc));
         }
-        const uint32_t p0 = pack2(ex2(fmaf(sc[0], c1, bb0.x + m0)), ex2(fmaf(sc[1], c1, bb0.y + m0)));
-        const uint32_t p1 = pack2(ex2(fmaf(sc[2], c1, bb1.x + m1)), ex2(fmaf(sc[3], c1, bb1.y + m1)));
-        pk[nt][0] = p0;
-        pk[nt][1] = p1;
-        *reinterpret_cast<uint32_t*>(&sm.p[i0 * kImgLd + j]) = p0;
-        *reinterpret_cast<uint32_t*>(&sm.p[i1 * kImgLd + j]) = p1;
-        // the bf16-rounded probabilities, as the products below see them
-        d0 = fmaf(__uint_as_float(p0 << 16), dp[nt][0], fmaf(__uint_as_float(p0 & 0xffff0000u), dp[nt][1], d0));
-        d1 = fmaf(__uint_as_float(p1 << 16), dp[nt][2], fmaf(__uint_as_float(p1 & 0xffff0000u), dp[nt][3], d1));
+        return acc;
+      };
+      d0 = dot8(*reinterpret_cast<const uint4*>(td + i0 * kTileLd + 8 * t4), *reinterpret_cast<const uint4*>(to + i0 * kTileLd + 8 * t4));
+      d1 = dot8(*reinterpret_cast<const uint4*>(td + i1 * kTileLd + 8 * t4), *reinterpret_cast<const uint4*>(to + i1 * kTileLd + 8 * t4));
+      d0 += __shfl_xor_sync(0xffffffffu, d0, 1);
+      d0 += __shfl_xor_sync(0xffffffffu, d0, 2);
+      d1 += __shfl_xor_sync(0xffffffffu, d1, 1);
+      d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
+    }
+    // ---- per n-tile: S, dP -> P, dS (bf16 pairs) ----
+    uint32_t pk[10][2];   // dS pairs [n-tile][row g / g + 8]: the A fragments of dQ
+    {
+      uint32_t aq[2][4], ad[2][4];
+      ldsm_x4(aq[0], s_u32(tq + (r0 + la_row) * kTileLd + la_col));
+      ldsm_x4(aq[1], s_u32(tq + (r0 + la_row) * kTileLd + la_col + 16));
+      ldsm_x4(ad[0], s_u32(td + (r0 + la_row) * kTileLd + la_col));
+      ldsm_x4(ad[1], s_u32(td + (r0 + la_row) * kTileLd + la_col + 16));
+#pragma unroll
+      for (int nn = 0; nn < 10; ++nn) {
+        if (nn < n_cnt) {
+          const int nt = n0 + nn;
+          uint32_t bk[4], bv[4];
+          ldsm_x4(bk, s_u32(tk_ + (nt * 8 + lb_row) * kTileLd + lb_col));
+          ldsm_x4(bv, s_u32(tv + (nt * 8 + lb_row) * kTileLd + lb_col));
+          float sc[4] = {0.f, 0.f, 0.f, 0.f}, dp[4] = {0.f, 0.f, 0.f, 0.f};
+          mma_bf16(sc, aq[0][0], aq[0][1], aq[0][2], aq[0][3], bk[0], bk[1]);
+          mma_bf16(dp, ad[0][0], ad[0][1], ad[0][2], ad[0][3], bv[0], bv[1]);
+          mma_bf16(sc, aq[1][0], aq[1][1], aq[1][2], aq[1][3], bk[2], bk[3]);
+          mma_bf16(dp, ad[1][0], ad[1][1], ad[1][2], ad[1][3], bv[2], bv[3]);
+          const int j = nt * 8 + 2 * t4;                 // keys j, j + 1: same window row, neighbouring columns
+          const int jy = (j * 171) >> 11, jx = j - jy * WS;   // j / 12 for j < 144
+          const int cj = j + 11 * jy;                    // 23 jy + jx
+          const float2 bb0 = sm.bias2[rb0 + cj], bb1 = sm.bias2[rb1 + cj];
+          float m0 = nl0, m1 = nl1;
+          if (masked) {   // warp-uniform; both keys of the pair lie in the same region
+            const bool kh_ = jy >= 6, kw_ = jx >= 6;
+            if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) m0 += -100.0f * kLog2e;
+            if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) m1 += -100.0f * kLog2e;
+          }
+          const uint32_t p0 = pack2(ex2(fmaf(sc[0], c1, bb0.x + m0)), ex2(fmaf(sc[1], c1, bb0.y + m0)));
+          const uint32_t p1 = pack2(ex2(fmaf(sc[2], c1, bb1.x + m1)), ex2(fmaf(sc[3], c1, bb1.y + m1)));
+          // dS from the bf16-rounded probabilities, as the products below see them
+          const uint32_t s0 = pack2(__uint_as_float(p0 << 16) * (dp[0] - d0), __uint_as_float(p0 & 0xffff0000u) * (dp[1] - d0));
+          const uint32_t s1 = pack2(__uint_as_float(p1 << 16) * (dp[2] - d1), __uint_as_float(p1 & 0xffff0000u) * (dp[3] - d1));
+          *reinterpret_cast<uint32_t*>(&sm.p[i0 * kImgLd + j]) = p0;
+          *reinterpret_cast<uint32_t*>(&sm.p[i1 * kImgLd + j]) = p1;
+          *reinterpret_cast<uint32_t*>(&sm.ds[i0 * kImgLd + j]) = s0;
+          *reinterpret_cast<uint32_t*>(&sm.ds[i1 * kImgLd + j]) = s1;
+          pk[nn][0] = s0;
+          pk[nn][1] = s1;
+        }
       }
     }
-    d0 += __shfl_xor_sync(0xffffffffu, d0, 1);
-    d0 += __shfl_xor_sync(0xffffffffu, d0, 2);
-    d1 += __shfl_xor_sync(0xffffffffu, d1, 1);
-    d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
-    // ---- dS = P (dP - delta) -> bf16 pairs: the dS image and the A fragments of dQ ----
-#pragma unroll
-    for (int nt = 0; nt < 18; ++nt) {
-      const int j = nt * 8 + 2 * t4;
-      const uint32_t p0 = pk[nt][0], p1 = pk[nt][1];
-      const uint32_t s0 = pack2(__uint_as_float(p0 << 16) * (dp[nt][0] - d0), __uint_as_float(p0 & 0xffff0000u) * (dp[nt][1] - d0));
-      const uint32_t s1 = pack2(__uint_as_float(p1 << 16) * (dp[nt][2] - d1), __uint_as_float(p1 & 0xffff0000u) * (dp[nt][3] - d1));
-      pk[nt][0] = s0;
-      pk[nt][1] = s1;
-      *reinterpret_cast<uint32_t*>(&sm.ds[i0 * kImgLd + j]) = s0;
-      *reinterpret_cast<uint32_t*>(&sm.ds[i1 * kImgLd + j]) = s1;
-    }
-    const int64_t pix0 = token_pixel(p, b, wy, wx, i0), pix1 = token_pixel(p, b, wy, wx, i1);
     // 16 x 32 fp32 accumulator (four n-tiles) -> bf16 -> rows i0 / i1 of an image-order tensor
     auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl) {
       __nv_bfloat16* d0p = static_cast<__nv_bfloat16*>(base) + pix0 * ps + h * HD + 2 * t4;
@@ -217,31 +236,43 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         *reinterpret_cast<uint32_t*>(d1p + nt * 8) = pack2(acc[nt][2] * scl, acc[nt][3] * scl);
       }
     };
-    // ---- dQ_w = scale dS_w K: A from the registers, B = K (keys x channels) by transposing loads ----
+    // ---- dQ_s = scale dS_s K over this warp's keys: A from the registers, B = K (keys x channels) by transposing loads ----
     {
       float acc[4][4];
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
 #pragma unroll
-      for (int kt = 0; kt < 9; ++kt) {
-        uint32_t b0[4], b1[4];
-        ldsm_x4_t(b0, s_u32(tk_ + (kt * 16 + la_row) * kTileLd + la_col));
-        ldsm_x4_t(b1, s_u32(tk_ + (kt * 16 + la_row) * kTileLd + la_col + 16));
-        const uint32_t a0 = pk[2 * kt][0], a1 = pk[2 * kt][1], a2 = pk[2 * kt + 1][0], a3 = pk[2 * kt + 1][1];
-        mma_bf16(acc[0], a0, a1, a2, a3, b0[0], b0[1]);
-        mma_bf16(acc[1], a0, a1, a2, a3, b0[2], b0[3]);
-        mma_bf16(acc[2], a0, a1, a2, a3, b1[0], b1[1]);
-        mma_bf16(acc[3], a0, a1, a2, a3, b1[2], b1[3]);
+      for (int kk = 0; kk < 5; ++kk) {
+        if (2 * kk < n_cnt) {
+          const int krow = (n0 + 2 * kk) * 8;
+          uint32_t b0[4], b1[4];
+          ldsm_x4_t(b0, s_u32(tk_ + (krow + la_row) * kTileLd + la_col));
+          ldsm_x4_t(b1, s_u32(tk_ + (krow + la_row) * kTileLd + la_col + 16));
+          const uint32_t a0 = pk[2 * kk][0], a1 = pk[2 * kk][1], a2 = pk[2 * kk + 1][0], a3 = pk[2 * kk + 1][1];
+          mma_bf16(acc[0], a0, a1, a2, a3, b0[0], b0[1]);
+          mma_bf16(acc[1], a0, a1, a2, a3, b0[2], b0[3]);
+          mma_bf16(acc[2], a0, a1, a2, a3, b1[0], b1[1]);
+          mma_bf16(acc[3], a0, a1, a2, a3, b1[2], b1[3]);
+        }
       }
-      put(acc, p.dq, p.q_ps, p.scale);
+      // the odd warp hands its partial sum to the even warp of the strip
+      if (kh) {
+#pragma unroll
+        for (int e = 0; e < 16; ++e) sm.dqx[strip][e][lane] = acc[e >> 2][e & 3];
+      }
+      pair_barrier(1 + strip);
+      if (!kh) {
+#pragma unroll
+        for (int e = 0; e < 16; ++e) acc[e >> 2][e & 3] += sm.dqx[strip][e][lane];
+        put(acc, p.dq, p.q_ps, p.scale);
+      }
     }
     __syncthreads();   // every strip of P and dS is written
 
-    // ---- dV_w = (P^T)_w dO, dK_w = scale (dS^T)_w Q: A = the image, transposed on load; rows = this warp's 16 keys ----
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      const __nv_bfloat16* img = which == 0 ? sm.p : sm.ds;
-      const __nv_bfloat16* rhs = which == 0 ? td : tq;
+    // ---- even warp: dV_s = (P^T)_s dO; odd warp: dK_s = scale (dS^T)_s Q.  A = the image, transposed on load ----
+    {
+      const __nv_bfloat16* img = kh == 0 ? sm.p : sm.ds;
+      const __nv_bfloat16* rhs = kh == 0 ? td : tq;
       float acc[4][4];
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
@@ -256,7 +287,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         mma_bf16(acc[2], a[0], a[1], a[2], a[3], b1[0], b1[1]);
         mma_bf16(acc[3], a[0], a[1], a[2], a[3], b1[2], b1[3]);
       }
-      if (which == 0) put(acc, p.dv, p.v_ps, 1.0f);
+      if (kh == 0) put(acc, p.dv, p.v_ps, 1.0f);
       else put(acc, p.dk, p.k_ps, p.scale);
     }
     // ---- bias-table gradient: bin (di, dj) += sum over keys (cy, cx) of dS[(cy + di, cx + dj)][(cy, cx)], in two steps.
@@ -264,7 +295,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     //     sums it along its 23 x-diagonals in registers (fully unrolled: no divergence, no atomics).
     __syncthreads();   // every warp is done with the P image: it becomes the diagonal sums
     float* diag = reinterpret_cast<float*>(sm.p);   // [half][query row qy][key row ky][24]: dS summed over the x diagonals of a 12 x 12 block
-    {
+    if (tid < 2 * N) {
       const int pair = tid >> 1, half = tid & 1, qy = pair / WS, ky = pair - qy * WS;
       float dg[17];   // local diagonals e = qx6 - kx in [-11, 5], stored at e + 11
 #pragma unroll
@@ -286,7 +317,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     }
     __syncthreads();
     // (2) one thread per bin: <= 12 key rows x the two halves
-    for (int bin = tid; bin < NT; bin += kThreads) {
+    if (tid < NT) {
+      const int bin = tid;
       const int di = bin / (2 * WS - 1) - (WS - 1), dj = bin % (2 * WS - 1) - (WS - 1);
       float sacc = 0.f;
       for (int ky = max(0, -di); ky < min(WS, WS - di); ++ky) {
@@ -311,7 +343,7 @@ bool mma12_backward_supported(const Problem& p, int dtype) {
   if (p.H != p.Hp || p.W != p.Wp) return false;           // window-aligned tensors (what the op differentiates)
   if ((p.q_ps | p.k_ps | p.v_ps | p.C) & 7) return false;
   auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
-  return !(mis(p.q) || mis(p.k) || mis(p.v) || mis(p.d_o) || mis(p.dq) || mis(p.dk) || mis(p.dv));
+  return p.o_in != nullptr && !(mis(p.q) || mis(p.k) || mis(p.v) || mis(p.d_o) || mis(p.o_in) || mis(p.dq) || mis(p.dk) || mis(p.dv));
 }
 
 cudaError_t launch_mma12_backward(const Problem& p, cudaStream_t st) {
