@@ -21,6 +21,7 @@
 //   warp 2s: dV_s = (P^T)_s dO     warp 2s+1: dK_s = scale (dS^T)_s Q     (A fragments by ldmatrix.trans from the images)
 //   d_table bins += dS by relative position: one thread per bin gathers its diagonal (no atomics; the bins live in
 //   shared memory for the whole job and are added to global memory once per CTA)
+// Three CTA barriers per window (tiles landed / images written / diagonal sums written) and one 64-thread barrier per strip.
 // q, k, v, dO, o rows are gathered (cp.async, one window ahead, two tile buffers; one token per thread) from / dq, dk, dv
 // rows scattered to the image-order tensors with the cyclic shift folded into the token coordinates
 // (newcrf_layers.py:220-227 / swin_transformer.py:212-219 and their inverses).
@@ -31,19 +32,23 @@ namespace mma12 {
 
 constexpr int N = 144, WS = 12, HD = 32, NT = 23 * 23;
 constexpr int kWarps = 18, kThreads = kWarps * 32;
-constexpr int kTileLd = 40;            // bf16 elements per row of the q / k / v / dO / o tiles (80 B: conflict-free ldmatrix rows)
 constexpr int kImgLd = 152;            // bf16 elements per row of the P / dS images (304 B: conflict-free ldmatrix rows)
-constexpr int kTile = N * kTileLd;
+constexpr int kTile = N * HD;          // q / k / v / dO / o tiles: 64-byte rows, 16-byte chunks XOR-swizzled by the row pair
+constexpr int kDiagLd = 2 * N + 1;     // diagonal sums [17][2 N + 1]: conflict-free for the writers (thread-major) and the bins
 constexpr float kLog2e = 1.4426950408889634f;
 
 struct Smem {
-  __nv_bfloat16 tile[2][5][kTile];     // q, k, v, dO, o of the current and the next window
+  __nv_bfloat16 tile[2][5][kTile];     // q, dO, k, v, o of the current and the next window
   __nv_bfloat16 p[N * kImgLd], ds[N * kImgLd];
   float2 bias2[NT + 1];                // {b[NT-1-k], b[NT-2-k]} log2e: the biases of an (even, odd) key pair in one 8-byte load
   float bins[NT + 3];
   float lse[2][N];
   float dqx[9][16][32];                // dQ partial of the odd warp of a strip: [accumulator register][lane]
+  float diag[17 * kDiagLd];            // dS summed over the x diagonals of each (query row, key row) block, per half
 };
+// byte offset of 16-byte chunk c of row r in a tile: 8 consecutive rows at one logical chunk (ldmatrix) and 2 rows x 4
+// chunks (cp.async by 8 threads) both cover all 32 banks
+__device__ __forceinline__ int toff(int r, int c) { return r * 64 + ((c ^ ((r >> 1) & 3)) << 4); }
 
 __device__ __forceinline__ uint32_t s_u32(const void* ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
@@ -117,9 +122,12 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   const int n0 = kh ? 10 : 0, n_cnt = kh ? 8 : 10;             // this warp's n-tiles (8 keys each) = 5 / 4 k-steps of dQ
   // ldmatrix lane addressing.  "A pattern": matrices (rows 0-7, cols 0-7) (rows 8-15, cols 0-7) (rows 0-7, cols 8-15)
   // (rows 8-15, cols 8-15); "T pattern" swaps the middle two.
-  const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8, la_col = ((lane >> 4) & 1) * 8;
+  const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8;
   const int lt_row = (lane & 7) + ((lane >> 4) & 1) * 8, lt_col = ((lane >> 3) & 1) * 8;
-  const int lb_row = lane & 7, lb_col = (lane >> 3) * 8;      // B of S / dP: 8 keys x 32 channels = four k-blocks of one n-tile
+  // tile offsets (bytes) of this lane's ldmatrix row: A pattern at channels [0,16) / [16,32); B of S / dP (8 keys x 32
+  // channels = the four k-blocks of one n-tile).  Row bases are multiples of 8 rows, which the swizzle does not see.
+  const int offa0 = toff(la_row, (lane >> 4) & 1), offa1 = toff(la_row, 2 + ((lane >> 4) & 1));
+  const int offb = toff(lane & 7, lane >> 3);
   // this thread's rows: window coordinates and the row part of the reversed bias index, k = rb + (23 jy + jx)
   const int i0 = r0 + g, i1 = i0 + 8;
   const int iy0 = i0 / WS, ix0 = i0 - iy0 * WS, iy1 = i1 / WS, ix1 = i1 - iy1 * WS;
@@ -132,11 +140,11 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   auto fetch = [&](const Win& wn, int buf) {
     const int64_t pix = token_pixel(p, wn.b, wn.wy, wn.wx, fty, ftx);
     const int off = h * HD + fch * 8;
-    const uint32_t dst = s_u32(&sm.tile[buf][0][ft * kTileLd + fch * 8]);
+    const uint32_t dst = s_u32(sm.tile[buf][0]) + toff(ft, fch);
     cp_async16(dst, static_cast<const __nv_bfloat16*>(p.q) + pix * p.q_ps + off);
-    cp_async16(dst + 2 * kTile, static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps + off);
-    cp_async16(dst + 4 * kTile, static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps + off);
-    cp_async16(dst + 6 * kTile, static_cast<const __nv_bfloat16*>(p.d_o) + pix * p.C + off);
+    cp_async16(dst + 2 * kTile, static_cast<const __nv_bfloat16*>(p.d_o) + pix * p.C + off);
+    cp_async16(dst + 4 * kTile, static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps + off);
+    cp_async16(dst + 6 * kTile, static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps + off);
     cp_async16(dst + 8 * kTile, static_cast<const __nv_bfloat16*>(p.o_in) + pix * p.C + off);
     if (fch == 0) cp_async4(s_u32(&sm.lse[buf][ft]), &p.lse[pix * p.nH + h]);
     cp_async_commit();
@@ -157,7 +165,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     __syncthreads();   // this window's tiles have landed; the previous window's images, tiles and bins gather are done
     nxt.next(p);
     if (w + 1 < w1) fetch(nxt, buf ^ 1);
-    const __nv_bfloat16 *tq = sm.tile[buf][0], *tk_ = sm.tile[buf][1], *tv = sm.tile[buf][2], *td = sm.tile[buf][3], *to = sm.tile[buf][4];
+    const uint32_t tq = s_u32(sm.tile[buf][0]), td = s_u32(sm.tile[buf][1]), tk_ = s_u32(sm.tile[buf][2]), tv = s_u32(sm.tile[buf][3]);
+    const unsigned char *tdp = reinterpret_cast<const unsigned char*>(sm.tile[buf][1]), *top = reinterpret_cast<const unsigned char*>(sm.tile[buf][4]);
     const float nl0 = -sm.lse[buf][i0] * kLog2e, nl1 = -sm.lse[buf][i1] * kLog2e;
     const int64_t pix0 = token_pixel(p, cur.b, cur.wy, cur.wx, iy0, ix0), pix1 = token_pixel(p, cur.b, cur.wy, cur.wx, iy1, ix1);
 
@@ -175,8 +184,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         }
         return acc;
       };
-      d0 = dot8(*reinterpret_cast<const uint4*>(td + i0 * kTileLd + 8 * t4), *reinterpret_cast<const uint4*>(to + i0 * kTileLd + 8 * t4));
-      d1 = dot8(*reinterpret_cast<const uint4*>(td + i1 * kTileLd + 8 * t4), *reinterpret_cast<const uint4*>(to + i1 * kTileLd + 8 * t4));
+      d0 = dot8(*reinterpret_cast<const uint4*>(tdp + toff(i0, t4)), *reinterpret_cast<const uint4*>(top + toff(i0, t4)));
+      d1 = dot8(*reinterpret_cast<const uint4*>(tdp + toff(i1, t4)), *reinterpret_cast<const uint4*>(top + toff(i1, t4)));
       d0 += __shfl_xor_sync(0xffffffffu, d0, 1);
       d0 += __shfl_xor_sync(0xffffffffu, d0, 2);
       d1 += __shfl_xor_sync(0xffffffffu, d1, 1);
@@ -186,17 +195,17 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     uint32_t pk[10][2];   // dS pairs [n-tile][row g / g + 8]: the A fragments of dQ
     {
       uint32_t aq[2][4], ad[2][4];
-      ldsm_x4(aq[0], s_u32(tq + (r0 + la_row) * kTileLd + la_col));
-      ldsm_x4(aq[1], s_u32(tq + (r0 + la_row) * kTileLd + la_col + 16));
-      ldsm_x4(ad[0], s_u32(td + (r0 + la_row) * kTileLd + la_col));
-      ldsm_x4(ad[1], s_u32(td + (r0 + la_row) * kTileLd + la_col + 16));
+      ldsm_x4(aq[0], tq + r0 * 64 + offa0);
+      ldsm_x4(aq[1], tq + r0 * 64 + offa1);
+      ldsm_x4(ad[0], td + r0 * 64 + offa0);
+      ldsm_x4(ad[1], td + r0 * 64 + offa1);
 #pragma unroll
       for (int nn = 0; nn < 10; ++nn) {
         if (nn < n_cnt) {
           const int nt = n0 + nn;
           uint32_t bk[4], bv[4];
-          ldsm_x4(bk, s_u32(tk_ + (nt * 8 + lb_row) * kTileLd + lb_col));
-          ldsm_x4(bv, s_u32(tv + (nt * 8 + lb_row) * kTileLd + lb_col));
+          ldsm_x4(bk, tk_ + nt * 512 + offb);
+          ldsm_x4(bv, tv + nt * 512 + offb);
           float sc[4] = {0.f, 0.f, 0.f, 0.f}, dp[4] = {0.f, 0.f, 0.f, 0.f};
           mma_bf16(sc, aq[0][0], aq[0][1], aq[0][2], aq[0][3], bk[0], bk[1]);
           mma_bf16(dp, ad[0][0], ad[0][1], ad[0][2], ad[0][3], bv[0], bv[1]);
@@ -246,8 +255,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         if (2 * kk < n_cnt) {
           const int krow = (n0 + 2 * kk) * 8;
           uint32_t b0[4], b1[4];
-          ldsm_x4_t(b0, s_u32(tk_ + (krow + la_row) * kTileLd + la_col));
-          ldsm_x4_t(b1, s_u32(tk_ + (krow + la_row) * kTileLd + la_col + 16));
+          ldsm_x4_t(b0, tk_ + krow * 64 + offa0);
+          ldsm_x4_t(b1, tk_ + krow * 64 + offa1);
           const uint32_t a0 = pk[2 * kk][0], a1 = pk[2 * kk][1], a2 = pk[2 * kk + 1][0], a3 = pk[2 * kk + 1][1];
           mma_bf16(acc[0], a0, a1, a2, a3, b0[0], b0[1]);
           mma_bf16(acc[1], a0, a1, a2, a3, b0[2], b0[3]);
@@ -272,7 +281,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     // ---- even warp: dV_s = (P^T)_s dO; odd warp: dK_s = scale (dS^T)_s Q.  A = the image, transposed on load ----
     {
       const __nv_bfloat16* img = kh == 0 ? sm.p : sm.ds;
-      const __nv_bfloat16* rhs = kh == 0 ? td : tq;
+      const uint32_t rhs = kh == 0 ? td : tq;
       float acc[4][4];
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
@@ -280,8 +289,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
       for (int kt = 0; kt < 9; ++kt) {
         uint32_t a[4], b0[4], b1[4];
         ldsm_x4_t(a, s_u32(img + (kt * 16 + lt_row) * kImgLd + r0 + lt_col));
-        ldsm_x4_t(b0, s_u32(rhs + (kt * 16 + la_row) * kTileLd + la_col));
-        ldsm_x4_t(b1, s_u32(rhs + (kt * 16 + la_row) * kTileLd + la_col + 16));
+        ldsm_x4_t(b0, rhs + kt * 1024 + offa0);
+        ldsm_x4_t(b1, rhs + kt * 1024 + offa1);
         mma_bf16(acc[0], a[0], a[1], a[2], a[3], b0[0], b0[1]);
         mma_bf16(acc[1], a[0], a[1], a[2], a[3], b0[2], b0[3]);
         mma_bf16(acc[2], a[0], a[1], a[2], a[3], b1[0], b1[1]);
@@ -293,8 +302,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     // ---- bias-table gradient: bin (di, dj) += sum over keys (cy, cx) of dS[(cy + di, cx + dj)][(cy, cx)], in two steps.
     // (1) Two threads per (query row qy, key row ky): each takes 6 of the 12 query columns of that 12 x 12 block of dS and
     //     sums it along its 23 x-diagonals in registers (fully unrolled: no divergence, no atomics).
-    __syncthreads();   // every warp is done with the P image: it becomes the diagonal sums
-    float* diag = reinterpret_cast<float*>(sm.p);   // [half][query row qy][key row ky][24]: dS summed over the x diagonals of a 12 x 12 block
+    //     The sums have their own buffer, so no barrier separates this from dV / dK.
+    float* diag = sm.diag;   // [local diagonal][2 (query row qy, key row ky) + half]
     if (tid < 2 * N) {
       const int pair = tid >> 1, half = tid & 1, qy = pair / WS, ky = pair - qy * WS;
       float dg[17];   // local diagonals e = qx6 - kx in [-11, 5], stored at e + 11
@@ -311,9 +320,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         }
       }
       // this thread's query columns are qx = half * 6 + qx6, so the true diagonal is dj = e + 6 half
-      float* out = diag + ((half * N + pair) * 24);
 #pragma unroll
-      for (int d = 0; d < 17; ++d) out[d] = dg[d];
+      for (int d = 0; d < 17; ++d) diag[d * kDiagLd + tid] = dg[d];
     }
     __syncthreads();
     // (2) one thread per bin: <= 12 key rows x the two halves
@@ -326,7 +334,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           const int d = dj - half * 6 + 11;           // index into that half's 17 local diagonals
-          if (d >= 0 && d < 17) sacc += diag[(half * N + pair) * 24 + d];
+          if (d >= 0 && d < 17) sacc += diag[d * kDiagLd + 2 * pair + half];
         }
       }
       sm.bins[bin] += sacc;
