@@ -54,8 +54,11 @@ extern "C" {
 enum { SWIN_ATTN_F32 = 0, SWIN_ATTN_BF16 = 1 };
 
 /* Which kernel family serves the bf16 forward/backward.  AUTO picks the
- * tcgen05/TMEM kernel whenever the shape allows it. */
-enum { SWIN_ATTN_IMPL_AUTO = 0, SWIN_ATTN_IMPL_SIMT = 1, SWIN_ATTN_IMPL_TCGEN05 = 2 };
+ * tcgen05/TMEM kernel whenever the shape allows it (window 12: the warp-MMA
+ * kernels for the backward and for the forward of un-aligned grids, where they
+ * are the faster ones).  WARP_MMA forces the warp-level tensor-core kernels
+ * (window 12 only; an error elsewhere). */
+enum { SWIN_ATTN_IMPL_AUTO = 0, SWIN_ATTN_IMPL_SIMT = 1, SWIN_ATTN_IMPL_TCGEN05 = 2, SWIN_ATTN_IMPL_WARP_MMA = 3 };
 
 typedef struct {
   int32_t batch;       /* B */

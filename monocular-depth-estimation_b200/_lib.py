@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libswin_attn.so")
 
 F32, BF16 = 0, 1
 STATIC_SCRATCH_BYTES = 8 << 20   # SWIN_ATTN_STATIC_SCRATCH_BYTES (include/swin_attn.h)
-IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05 = 0, 1, 2
+IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05, IMPL_WARP_MMA = 0, 1, 2, 3
 
 EXPORTS = (
     "swin_attn_forward",

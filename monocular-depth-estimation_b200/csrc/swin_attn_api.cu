@@ -86,6 +86,16 @@ int swin_attn_forward(const swin_attn_shape_t* shape, const void* q, const void*
   p.table = bias_table; p.o = o; p.lse = lse; p.trace = g_trace;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // window 12, impl AUTO: un-aligned grids (every ODA stage of a 352 x 1216 or 480 x 640 image) go to the warp-MMA forward
+  // -- every lane carries a row, two CTAs per SM, padding is free -- which beats the tcgen05 window-12 kernel there by
+  // 1.1-1.4x; aligned grids stay on tcgen05 (profiles/r2_micro_fwd_ws12_mma.jsonl).  impl = TCGEN05 forces tcgen05.
+  const bool mma_ok = attn_mask == nullptr && mma12_forward_supported(p, shape->dtype);
+  if (shape->impl == SWIN_ATTN_IMPL_WARP_MMA && !mma_ok) return fail("warp-MMA forward does not support this shape/dtype (window 12, bf16, no explicit mask)");
+  if (mma_ok && (shape->impl == SWIN_ATTN_IMPL_WARP_MMA || (shape->impl == SWIN_ATTN_IMPL_AUTO && (p.H != p.Hp || p.W != p.Wp)))) {
+    cudaError_t e = launch_mma12_forward(p, st);
+    if (e != cudaSuccess) return fail_cuda("window-12 warp-MMA forward launch", e);
+    return 0;
+  }
   const bool want_tc12 = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc12_forward_supported(p, shape->dtype);
   bool want_tc = want_tc12 || (shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_forward_supported(p, shape->dtype));
   if (shape->impl == SWIN_ATTN_IMPL_TCGEN05 && !want_tc) return fail("tcgen05 forward does not support this shape/dtype");
@@ -130,7 +140,9 @@ static int backward_impl(const swin_attn_shape_t* shape, const void* q, const vo
     if (e != cudaSuccess) return why ? fail(std::string("tcgen05 backward: ") + why) : fail_cuda("tcgen05 backward launch", e);
     return 0;
   }
-  if (shape->impl == SWIN_ATTN_IMPL_AUTO && mma12_backward_supported(p, shape->dtype)) {   // window 12: warp-MMA kernel
+  if (shape->impl == SWIN_ATTN_IMPL_WARP_MMA && !mma12_backward_supported(p, shape->dtype))
+    return fail("warp-MMA backward does not support this shape/dtype (window 12, bf16, window-aligned, no explicit mask / dropout)");
+  if ((shape->impl == SWIN_ATTN_IMPL_AUTO || shape->impl == SWIN_ATTN_IMPL_WARP_MMA) && mma12_backward_supported(p, shape->dtype)) {   // window 12: warp-MMA kernel
     cudaError_t e = launch_mma12_backward(p, st);
     if (e != cudaSuccess) return fail_cuda("window-12 backward launch", e);
     return 0;

@@ -346,6 +346,230 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
 
 }  // namespace mma12
 
+// =====================================================================================================================
+// Forward for window 12 on the same warp-MMA building blocks (FlashAttention-2 form).  The tcgen05 forward of
+// swin_attn_tc12.cu is bound by its softmax threads (72 of 128 accumulator lanes carry rows, one sub-partition idles, two
+// passes over tensor memory); here every lane of every warp carries work, P goes from the S accumulators straight into
+// the A fragments of P V, and a CTA needs 60 KB of shared memory, so two CTAs (18 warps) share an SM.
+//   warp w = query strip w (16 rows); keys in three chunks of 48 with the running maximum / sum of the online softmax
+//   (exp2 domain; the SW-MSA mask is -100, never -inf, so no row is empty);  O is rescaled per chunk and divided by the
+//   sum of the bf16-rounded probabilities at the end.
+// Padding (H or W not a multiple of 12) costs nothing in the math: the gather writes k_pad / v_pad into the K / V rows of
+// pad tokens (the reference pads before the qkv Linear, oda_swin_transformer.py:249-253), zero-fills their Q rows and the
+// epilogue skips their output rows.
+namespace mma12 {
+
+constexpr int kFwdWarps = 9, kFwdThreads = kFwdWarps * 32;
+struct SmemF {
+  __nv_bfloat16 tile[2][3][kTile];     // q, k, v of the current and the next window
+  float2 bias2[NT + 1];
+};
+
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, int bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem p, int n_win, int win_per_job) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SmemF& sm = *reinterpret_cast<SmemF*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int h = (int)blockIdx.x % p.nH;
+  const int w0 = ((int)blockIdx.x / p.nH) * win_per_job, w1 = min(w0 + win_per_job, n_win);
+  const float c1 = p.scale * kLog2e;
+  for (int i = tid; i < NT; i += kFwdThreads) {
+    const float b0 = p.table[(NT - 1 - i) * p.nH + h] * kLog2e;
+    const float b1 = i + 1 < NT ? p.table[(NT - 2 - i) * p.nH + h] * kLog2e : 0.f;
+    sm.bias2[i] = make_float2(b0, b1);
+  }
+  const int r0 = warp * 16;
+  const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8;
+  const int offa0 = toff(la_row, (lane >> 4) & 1), offa1 = toff(la_row, 2 + ((lane >> 4) & 1));
+  const int offb = toff(lane & 7, lane >> 3);
+  const int i0 = r0 + g, i1 = i0 + 8;
+  const int iy0 = i0 / WS, ix0 = i0 - iy0 * WS, iy1 = i1 / WS, ix1 = i1 - iy1 * WS;
+  const int rb0 = 264 - 23 * iy0 - ix0, rb1 = 264 - 23 * iy1 - ix1;
+  const bool my_h0 = iy0 >= 6, my_w0 = ix0 >= 6, my_h1 = iy1 >= 6, my_w1 = ix1 >= 6;
+  // Keys j = 8 nt + 2 t4 (+ 1) of n-tile nt: their window row is jy = (8 nt) / 12 + (nt % 3 == 1 && t4 >= 2), so the bias
+  // index rb + 23 jy + jx = rb + j + 11 jy is a per-thread base (two variants) plus a compile-time constant.
+  const int hi = t4 >> 1;
+  const float2 *pb0a = sm.bias2 + rb0 + 2 * t4, *pb0b = pb0a + 11 * hi, *pb1a = sm.bias2 + rb1 + 2 * t4, *pb1b = pb1a + 11 * hi;
+  const bool padded = p.H != p.Hp || p.W != p.Wp;
+
+  // token (ty, tx) of a window -> un-rolled coordinates in the PADDED image
+  auto coords = [&](const Win& wn, int ty, int tx, int& y, int& x) {
+    y = wn.wy * WS + ty + p.shift;
+    x = wn.wx * WS + tx + p.shift;
+    if (y >= p.Hp) y -= p.Hp;
+    if (x >= p.Wp) x -= p.Wp;
+  };
+  // gather: two tokens per thread (ft, ft + 72), one 16-byte chunk of q, k, v each
+  const int ft = tid >> 2, fch = tid & 3;
+  const int fty0 = ft / WS, ftx0 = ft - fty0 * WS, fty1 = (ft + 72) / WS, ftx1 = (ft + 72) - fty1 * WS;
+  const int off = h * HD + fch * 8;
+  const __nv_bfloat16* kpad = static_cast<const __nv_bfloat16*>(p.k_pad);
+  const __nv_bfloat16* vpad = static_cast<const __nv_bfloat16*>(p.v_pad);
+  auto fetch = [&](const Win& wn, int buf) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int tk = ft + 72 * u;
+      int y, x;
+      coords(wn, u ? fty1 : fty0, u ? ftx1 : ftx0, y, x);
+      const uint32_t dst = s_u32(sm.tile[buf][0]) + toff(tk, fch);
+      if (!padded || (y < p.H && x < p.W)) {
+        const int64_t pix = ((int64_t)wn.b * p.H + y) * p.W + x;
+        cp_async16(dst, static_cast<const __nv_bfloat16*>(p.q) + pix * p.q_ps + off);
+        cp_async16(dst + 2 * kTile, static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps + off);
+        cp_async16(dst + 4 * kTile, static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps + off);
+      } else {   // pad token: q = 0 (its output row is cropped), k / v = the pad vectors (or 0 without them)
+        cp_async16_zfill(dst, p.q, 0);
+        cp_async16_zfill(dst + 2 * kTile, kpad ? static_cast<const void*>(kpad + off) : p.k, kpad ? 16 : 0);
+        cp_async16_zfill(dst + 4 * kTile, vpad ? static_cast<const void*>(vpad + off) : p.v, vpad ? 16 : 0);
+      }
+    }
+    cp_async_commit();
+  };
+  Win cur, nxt;
+  cur.wx = w0 % p.nWx;
+  cur.wy = (w0 / p.nWx) % p.nWy;
+  cur.b = w0 / (p.nWx * p.nWy);
+  nxt = cur;
+  if (w0 < w1) fetch(cur, 0);
+
+  for (int w = w0; w < w1; ++w, cur = nxt) {
+    const int buf = (w - w0) & 1;
+    const bool hm = p.shift > 0 && cur.wy == p.nWy - 1, wm = p.shift > 0 && cur.wx == p.nWx - 1;
+    const bool masked = hm || wm;
+    cp_async_wait_all();
+    __syncthreads();   // this window's tiles have landed; every warp is done with the other buffer
+    nxt.next(p);
+    if (w + 1 < w1) fetch(nxt, buf ^ 1);
+    const uint32_t tq = s_u32(sm.tile[buf][0]), tk_ = s_u32(sm.tile[buf][1]), tv = s_u32(sm.tile[buf][2]);
+
+    uint32_t aq[2][4];
+    ldsm_x4(aq[0], tq + r0 * 64 + offa0);
+    ldsm_x4(aq[1], tq + r0 * 64 + offa1);
+    float o[5][4];   // four n-tiles of O and a ones tile: its columns are the row sum of the bf16 probabilities
+#pragma unroll
+    for (int nt = 0; nt < 5; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float t[6][4];
+      float cm0 = -INFINITY, cm1 = -INFINITY;
+#pragma unroll
+      for (int nn = 0; nn < 6; ++nn) {
+        const int nt = c * 6 + nn;
+        uint32_t bk[4];
+        ldsm_x4(bk, tk_ + nt * 512 + offb);
+        float sc[4] = {0.f, 0.f, 0.f, 0.f};
+        mma_bf16(sc, aq[0][0], aq[0][1], aq[0][2], aq[0][3], bk[0], bk[1]);
+        mma_bf16(sc, aq[1][0], aq[1][1], aq[1][2], aq[1][3], bk[2], bk[3]);
+        const int cc = 8 * nt + 11 * ((8 * nt) / WS);   // compile-time after unrolling
+        const float2 bb0 = (nt % 3 == 1 ? pb0b : pb0a)[cc], bb1 = (nt % 3 == 1 ? pb1b : pb1a)[cc];
+        float m0 = 0.f, m1 = 0.f;
+        if (masked) {
+          const int jy = (8 * nt) / WS + (nt % 3 == 1 ? hi : 0), jx = 8 * nt + 2 * t4 - jy * WS;
+          const bool kh_ = jy >= 6, kw_ = jx >= 6;
+          if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) m0 = -100.0f * kLog2e;
+          if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) m1 = -100.0f * kLog2e;
+        }
+        t[nn][0] = fmaf(sc[0], c1, bb0.x + m0);
+        t[nn][1] = fmaf(sc[1], c1, bb0.y + m0);
+        t[nn][2] = fmaf(sc[2], c1, bb1.x + m1);
+        t[nn][3] = fmaf(sc[3], c1, bb1.y + m1);
+        cm0 = fmaxf(cm0, fmaxf(t[nn][0], t[nn][1]));
+        cm1 = fmaxf(cm1, fmaxf(t[nn][2], t[nn][3]));
+      }
+      cm0 = fmaxf(cm0, __shfl_xor_sync(0xffffffffu, cm0, 1));
+      cm0 = fmaxf(cm0, __shfl_xor_sync(0xffffffffu, cm0, 2));
+      cm1 = fmaxf(cm1, __shfl_xor_sync(0xffffffffu, cm1, 1));
+      cm1 = fmaxf(cm1, __shfl_xor_sync(0xffffffffu, cm1, 2));
+      const float n0 = fmaxf(mx0, cm0), n1 = fmaxf(mx1, cm1);
+      const float al0 = ex2(mx0 - n0), al1 = ex2(mx1 - n1);   // exp2(-inf) = 0 for the first chunk
+      mx0 = n0;
+      mx1 = n1;
+#pragma unroll
+      for (int nt = 0; nt < 5; ++nt) {
+        o[nt][0] *= al0;
+        o[nt][1] *= al0;
+        o[nt][2] *= al1;
+        o[nt][3] *= al1;
+      }
+      uint32_t pa[6][2];
+#pragma unroll
+      for (int nn = 0; nn < 6; ++nn) {
+        const uint32_t p0 = pack2(ex2(t[nn][0] - n0), ex2(t[nn][1] - n0));
+        const uint32_t p1 = pack2(ex2(t[nn][2] - n1), ex2(t[nn][3] - n1));
+        pa[nn][0] = p0;
+        pa[nn][1] = p1;
+      }
+#pragma unroll
+      for (int kk = 0; kk < 3; ++kk) {
+        const int krow = (c * 6 + 2 * kk) * 8;
+        uint32_t b0[4], b1[4];
+        ldsm_x4_t(b0, tv + krow * 64 + offa0);
+        ldsm_x4_t(b1, tv + krow * 64 + offa1);
+        const uint32_t a0 = pa[2 * kk][0], a1 = pa[2 * kk][1], a2 = pa[2 * kk + 1][0], a3 = pa[2 * kk + 1][1];
+        mma_bf16(o[0], a0, a1, a2, a3, b0[0], b0[1]);
+        mma_bf16(o[1], a0, a1, a2, a3, b0[2], b0[3]);
+        mma_bf16(o[2], a0, a1, a2, a3, b1[0], b1[1]);
+        mma_bf16(o[3], a0, a1, a2, a3, b1[2], b1[3]);
+        mma_bf16(o[4], a0, a1, a2, a3, 0x3f803f80u, 0x3f803f80u);   // B = ones (bf16 pairs): the normaliser, from the MMA
+      }
+    }
+    const float l0 = o[4][0], l1 = o[4][2];
+    // ---- epilogue: rows i0 / i1 -> their pixels (cropped when they are pad tokens); lse on the padded grid ----
+    int y0, x0, y1, x1;
+    coords(cur, iy0, ix0, y0, x0);
+    coords(cur, iy1, ix1, y1, x1);
+    const float inv0 = 1.0f / l0, inv1 = 1.0f / l1;
+    if (y0 < p.H && x0 < p.W) {
+      __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.o) + (((int64_t)cur.b * p.H + y0) * p.W + x0) * p.o_ps + h * HD + 2 * t4;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) *reinterpret_cast<uint32_t*>(dst + nt * 8) = pack2(o[nt][0] * inv0, o[nt][1] * inv0);
+    }
+    if (y1 < p.H && x1 < p.W) {
+      __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.o) + (((int64_t)cur.b * p.H + y1) * p.W + x1) * p.o_ps + h * HD + 2 * t4;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) *reinterpret_cast<uint32_t*>(dst + nt * 8) = pack2(o[nt][2] * inv1, o[nt][3] * inv1);
+    }
+    if (p.lse != nullptr && t4 == 0) {
+      p.lse[(((int64_t)cur.b * p.Hp + y0) * p.Wp + x0) * p.nH + h] = (mx0 + log2f(l0)) * 0.6931471805599453f;
+      p.lse[(((int64_t)cur.b * p.Hp + y1) * p.Wp + x1) * p.nH + h] = (mx1 + log2f(l1)) * 0.6931471805599453f;
+    }
+  }
+}
+
+}  // namespace mma12
+
+bool mma12_forward_supported(const Problem& p, int dtype) {
+  if (dtype != SWIN_ATTN_BF16 || p.ws != 12 || p.mask != nullptr || p.dropout_p > 0.0f) return false;
+  if (p.shift != 0 && p.shift != 6) return false;
+  if (p.H < p.shift || p.W < p.shift) return false;   // the pad rows would wrap around the rolled image
+  if ((p.q_ps | p.k_ps | p.v_ps | p.o_ps) & 7) return false;
+  auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
+  return !(mis(p.q) || mis(p.k) || mis(p.v) || mis(p.o) || mis(p.k_pad) || mis(p.v_pad));
+}
+
+cudaError_t launch_mma12_forward(const Problem& p, cudaStream_t st) {
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int smem = (int)sizeof(mma12::SmemF);
+  cudaError_t e = cudaFuncSetAttribute(mma12::mma12_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return e;
+  const int n_win = p.B * p.nWy * p.nWx;
+  int chunks = 2 * sms / p.nH;   // two CTAs per SM
+  if (chunks < 1) chunks = 1;
+  if (chunks > n_win) chunks = n_win;
+  const int per = (n_win + chunks - 1) / chunks;
+  chunks = (n_win + per - 1) / per;
+  TimedRegion timed(st);
+  mma12::mma12_fwd_kernel<<<chunks * p.nH, mma12::kFwdThreads, smem, st>>>(p, n_win, per);
+  count_launch();
+  return cudaGetLastError();
+}
+
 bool mma12_backward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 12 || p.mask != nullptr || p.dropout_p > 0.0f) return false;
   if (p.H != p.Hp || p.W != p.Wp) return false;           // window-aligned tensors (what the op differentiates)

@@ -140,6 +140,8 @@ cudaError_t launch_tc12_forward(const Problem& p, cudaStream_t st, const char** 
 bool tc_backward_supported(const Problem& p, int dtype);
 bool mma12_backward_supported(const Problem& p, int dtype);                 // window 12, bf16, aligned: warp-MMA kernel
 cudaError_t launch_mma12_backward(const Problem& p, cudaStream_t st);
+bool mma12_forward_supported(const Problem& p, int dtype);                  // window 12, bf16, padded or not: warp-MMA kernel
+cudaError_t launch_mma12_forward(const Problem& p, cudaStream_t st);
 cudaError_t launch_tc_backward(const Problem& p, cudaStream_t st, const char** err);
 
 cudaError_t launch_layernorm(const void* x, int x_dtype, const float* gamma, const float* beta, float eps, int64_t rows, int channels,

@@ -127,6 +127,38 @@ def test_forward_ws12_tcgen05_on_unaligned_tensors_matches_oracle(case):
     check(rel_err(got.float(), ref.float()), TOL_BF16, "ws12 tcgen05 vs CUDA-core kernel, un-aligned")
 
 
+# The warp-MMA forward of swin_attn_mma12_bwd.cu (online softmax over three key chunks, pad vectors written into the K / V
+# rows of pad tokens by the gather): what impl AUTO runs on un-aligned window-12 grids; forced here on aligned ones too
+@pytest.mark.parametrize("case", [c + (True,) for c in TC12_CASES] + TC12_PAD_CASES)
+def test_forward_ws12_warp_mma_matches_oracle(case):
+    ws, shift, b, h, w, nh, ext, with_pads = case
+    c = nh * 32
+    name = f"fwd12mma{case}"
+    packed = randn(name + ".p", b, h, w, (2 if ext else 3) * c).bfloat16()
+    v = randn(name + ".v", b, h, w, c).bfloat16() if ext else None
+    table = 0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh)
+    pads = randn(name + ".pad", (2 if ext else 3) * c).bfloat16() if with_pads else None
+    v_pad = randn(name + ".vpad", c).bfloat16() if ext and with_pads else None
+    want, want_lse = _oracle(packed.float(), None if v is None else v.float(), table, ws, shift, nh,
+                             None if pads is None else pads.float(), None if v_pad is None else v_pad.float())
+    dev = lambda t: None if t is None else t.to(DEV)
+    before = _lib.load().swin_attn_launch_count()
+    got, lse = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, True,
+                                       _lib.IMPL_WARP_MMA, None)
+    assert _lib.load().swin_attn_launch_count() == before + 1
+    assert got.shape == (b, h, w, c)
+    check(rel_err(got.float(), want), TOL_BF16, "ws12 warp-MMA forward")
+    if h % ws or w % ws:   # un-aligned: impl AUTO is this kernel
+        auto, _ = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, False,
+                                          _lib.IMPL_AUTO, None)
+        assert torch.equal(auto, got)
+    check(rel_err(lse[:, :h, :w], want_lse[:, :h, :w]), TOL_BF16, "lse ws12 warp-MMA forward")
+    # the two tensor-core forwards agree on the same bf16 inputs
+    tc, _ = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, False,
+                                    _lib.IMPL_TCGEN05, None)
+    check(rel_err(got.float(), tc.float()), TOL_BF16, "ws12 warp-MMA vs tcgen05 forward")
+
+
 # window-aligned shapes for the backward: odd window counts (a job's last pair is half empty), several
 # window chunks per head, external v, shifted wrap rows / columns
 BWD_CASES = [c for c in CASES if c[3] % c[0] == 0 and c[4] % c[0] == 0] + [

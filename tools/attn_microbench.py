@@ -35,7 +35,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--bwd", action="store_true")
     ap.add_argument("--only", default=None)
-    ap.add_argument("--impl", default="both", choices=["both", "auto", "simt"])
+    ap.add_argument("--impl", default="both", choices=["both", "auto", "simt", "tc", "mma"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--flush", action="store_true", default=True)
     args = ap.parse_args()
@@ -46,7 +46,7 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     impls = {"auto": _lib.IMPL_AUTO, "simt": _lib.IMPL_SIMT}
     if args.impl != "both":
-        impls = {args.impl: impls[args.impl]}
+        impls = {args.impl: {"auto": _lib.IMPL_AUTO, "simt": _lib.IMPL_SIMT, "tc": _lib.IMPL_TCGEN05, "mma": _lib.IMPL_WARP_MMA}[args.impl]}
     for name, (b, h, w, nh, ws, ext) in SHAPES.items():
         if args.only and args.only not in name:
             continue
