@@ -86,7 +86,7 @@ int swin_attn_forward(const swin_attn_shape_t* shape, const void* q, const void*
   p.table = bias_table; p.o = o; p.lse = lse; p.trace = g_trace;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // window 12, impl AUTO: un-aligned grids (every ODA stage of a 352 x 1216 or 480 x 640 image) go to the warp-MMA forward
+  // window 12, impl AUTO: un-aligned grids (every stage of the window-12 encoder on a 352 x 1216 or 480 x 640 image) go to the warp-MMA forward
   // -- every lane carries a row, two CTAs per SM, padding is free -- which beats the tcgen05 window-12 kernel there by
   // 1.1-1.4x; aligned grids stay on tcgen05 (profiles/r2_micro_fwd_ws12_mma.jsonl).  impl = TCGEN05 forces tcgen05.
   const bool mma_ok = attn_mask == nullptr && mma12_forward_supported(p, shape->dtype);

@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
 //   (exp2 domain; the SW-MSA mask is -100, never -inf, so no row is empty);  O is rescaled per chunk and divided by the
 //   sum of the bf16-rounded probabilities at the end.
 // Padding (H or W not a multiple of 12) costs nothing in the math: the gather writes k_pad / v_pad into the K / V rows of
-// pad tokens (the reference pads before the qkv Linear, oda_swin_transformer.py:249-253), zero-fills their Q rows and the
+// pad tokens (the reference pads before the qkv Linear, model/NewCRFs/swin_transformer.py:204-209; window 12 = NewCRFDepth version "large12", NewCRFDepth.py:26), zero-fills their Q rows and the
 // epilogue skips their output rows.
 namespace mma12 {
 

@@ -20,9 +20,9 @@
 //   epilogue: O row / rowsum -> bf16 -> staging -> TMA tensor store of the half window (12 x 6, or 6 x 12 /
 //           two 6 x 6 boxes for shifted blocks).
 //
-// Padding (H or W not a multiple of 12: every ODA stage of a 352 x 1216 or 480 x 640 input): TMA zero-fills the
+// Padding (H or W not a multiple of 12: every stage of the window-12 encoder, NewCRFDepth "large12", on a 352 x 1216 or 480 x 640 input): TMA zero-fills the
 // out-of-image part of a load box and clips it from a store box.  The reference pads BEFORE the qkv Linear
-// (oda_swin_transformer.py:249-253), so pad tokens carry the Linear bias: k_pad goes -- once per CTA -- into the
+// (model/NewCRFs/swin_transformer.py:204-209; window 12 = NewCRFDepth version "large12", NewCRFDepth.py:26), so pad tokens carry the Linear bias: k_pad goes -- once per CTA -- into the
 // spare row 144 of every K tile and v_pad into the spare rows 144 / 145 of every V tile (tiles are 160 rows; the
 // boxes write 144).  With padding S is N = 160 wide (column 144 = q . k_pad, which the softmax substitutes for the
 // columns of pad tokens) and the PV product takes a tenth K-step whose P columns 144 / 145 hold the hi / lo bf16

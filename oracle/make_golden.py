@@ -272,6 +272,9 @@ CASES = {
     "depthformer_luna_prenorm": lambda n: depthformer_luna(n, "PreNormLunaLayer", 1, 7, 9, 128, 128, 64, 2, 17),
     "newcrf_level": lambda n: newcrf_level(n, 1, 10, 13, 48, 64, 32, 2),
     "newcrfdepth_tiny07": lambda n: full_model(n, "tiny07", 1, 64, 96),
+    # the window-12 encoder (version "..12", NewCRFDepth.py:26) on a 96 x 160 image: stage grids 24x40, 12x20, 6x10, 3x5 --
+    # padding along W at every stage, along H from stage 2 on, and a last stage smaller than the shift
+    "newcrfdepth_tiny12": lambda n: full_model(n, "tiny12", 1, 96, 160),
     # metrics only (same image / weights as newcrfdepth_tiny07; adds the realistic-range GT)
     "newcrfdepth_tiny07_metrics": lambda n: full_model_v2("newcrfdepth_tiny07", "tiny07", 1, 64, 96, keep_depth=False),
     # BASELINE configs[1]: the benchmarked model at the benchmarked shape, one image

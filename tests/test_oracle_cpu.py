@@ -77,8 +77,9 @@ def test_newcrf_level_matches_reference(golden):
         assert rel_err(got, g[key]) < TOL, key
 
 
-def test_full_model_matches_reference(golden):
-    g = golden("newcrfdepth_tiny07")
+@pytest.mark.parametrize("fixture", ["newcrfdepth_tiny07", "newcrfdepth_tiny12"])
+def test_full_model_matches_reference(golden, fixture):
+    g = golden(fixture)
     cfg = g["cfg"]
     m = mde_b200.NewCRFDepth(version=cfg["version"], max_depth=cfg["max_depth"])
     m.load_state_dict(synthetic_state(m), strict=True)
@@ -86,7 +87,7 @@ def test_full_model_matches_reference(golden):
     with torch.no_grad():
         depth = m(g["img"])
     assert rel_err(depth, g["depth"]) < TOL
-    gt = synthetic_depth_gt("newcrfdepth_tiny07.gt", cfg["b"], cfg["h"], cfg["w"], cfg["max_depth"])
+    gt = synthetic_depth_gt(fixture + ".gt", cfg["b"], cfg["h"], cfg["w"], cfg["max_depth"])
     valid = (gt > 1e-3).numpy()
     err = depth_errors(gt.numpy()[valid], depth.clamp(1e-3, cfg["max_depth"]).numpy()[valid])
     assert abs(err["abs_rel"] - g["abs_rel"]) < 1e-3 and abs(err["rmse"] - g["rmse"]) < 1e-3

@@ -91,7 +91,7 @@ def test_forward_ws12_tcgen05_matches_oracle(case):
     assert rel_err(got.float(), ref.float()) < TOL_BF16
 
 
-# un-aligned window-12 shapes (TMA zero-fill + pad vectors in the spare rows of the K / V tiles): the four ODA stage grids
+# un-aligned window-12 shapes (TMA zero-fill + pad vectors in the spare rows of the K / V tiles): the four window-12 stage grids
 # of a 352 x 1216 image (88x304 .. 11x38, scaled down in batch / heads), one padded row or column only, pads that span
 # the last TWO window rows of a shifted block, a single window with every wrap, and no pad vectors at all (zero pads)
 TC12_PAD_CASES = [(12, 0, 1, 13, 25, 2, False, True), (12, 6, 1, 13, 25, 2, False, True), (12, 6, 1, 11, 38, 3, True, True),
@@ -347,6 +347,45 @@ def test_full_model_depth_metrics_vs_reference_golden(golden, mode):
     # rmse is O(29 m) here: measured 1.02e-3 relative for the product, 6.5e-4 for the oracle port's own autocast run
     check(abs(err["rmse"] - g["rmse"]) / g["rmse"], 1.5 * abs(eref["rmse"] - g["rmse"]) / g["rmse"] + 1e-3,
           "tiny07 bf16 rmse on the ill-conditioned GT, relative (reported)")
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16", "bf16_train"])
+def test_window12_full_model_vs_reference_golden(golden, mode):
+    """NewCRFDepth("tiny12") -- the window-12 encoder, NewCRFDepth.py:26 -- on a 96 x 160 image against the reference's CPU
+    output: stage grids 24x40, 12x20, 6x10 (un-aligned: the warp-MMA forward under bf16 inference) and 3x5 (smaller than
+    the shift: CUDA cores).  bf16_train: the same forward with gradients enabled, where the layers pad explicitly and the
+    aligned kernels run (tcgen05 window-12 forward, warp-MMA backward); its depth must agree and every gradient be finite."""
+    from oracle.cpu_model import to_oracle
+    g = golden("newcrfdepth_tiny12")
+    cfg = g["cfg"]
+    m = mde_b200.NewCRFDepth(version=cfg["version"], max_depth=cfg["max_depth"])
+    m.load_state_dict(synthetic_state(m), strict=True)
+    m = m.to(DEV).eval()
+    img = g["img"].to(DEV)
+    before = _lib.load().swin_attn_launch_count()
+    if mode == "fp32":
+        with torch.no_grad():
+            depth = m(img).float().cpu()
+        check(rel_err(depth, g["depth"]), TOL_F32, "tiny12 full model fp32 depth")
+        return
+    if mode == "bf16":
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            depth = m(img).float().cpu()
+    else:
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = m(img)
+        out.float().square().mean().backward()
+        depth = out.detach().float().cpu()
+        tables = [p for n, p in m.named_parameters() if n.endswith("relative_position_bias_table")]
+        assert tables and all(p.grad is not None and torch.isfinite(p.grad).all() and float(p.grad.abs().max()) > 0 for p in tables)
+        assert all(torch.isfinite(p.grad).all() for p in m.parameters() if p.grad is not None)
+    assert _lib.load().swin_attn_launch_count() - before >= 12 + 8    # every block went through the library
+    ref = to_oracle(m, DEV).eval()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        depth_ref = ref(img).float().cpu()
+    ours_vs_fp32, ref_vs_fp32 = rel_err(depth, g["depth"]), rel_err(depth_ref, g["depth"])
+    check(ours_vs_fp32, TOL_BF16, f"tiny12 full model {mode} depth vs reference fp32 (oracle port under autocast: {ref_vs_fp32:.3e})")
+    assert ours_vs_fp32 < 1.5 * ref_vs_fp32 + 1e-3
 
 
 def test_host_buffer_entry_matches_device_entry():

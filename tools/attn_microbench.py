@@ -24,7 +24,7 @@ SHAPES = {
     "crf2_352x1216": (8, 22, 76, 16, 7, True), "crf3_352x1216": (8, 11, 38, 32, 7, True),
     "enc_s0_480x640": (8, 120, 160, 6, 7, False), "enc_s2_480x640": (8, 30, 40, 24, 7, False),
     "oda_ws12_s0": (8, 96, 96, 6, 12, False), "oda_ws12_s2": (8, 24, 24, 24, 12, False),
-    # the ODA (window 12) encoder on the 352 x 1216 input: no stage grid is a multiple of 12
+    # the window-12 encoder (NewCRFDepth "large12") on the 352 x 1216 input: no stage grid is a multiple of 12
     "oda_ws12_s0_352x1216": (8, 88, 304, 6, 12, False), "oda_ws12_s1_352x1216": (8, 44, 152, 12, 12, False),
     "oda_ws12_s2_352x1216": (8, 22, 76, 24, 12, False), "oda_ws12_s3_352x1216": (8, 11, 38, 48, 12, False),
 }
