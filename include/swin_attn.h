@@ -54,9 +54,8 @@ extern "C" {
 enum { SWIN_ATTN_F32 = 0, SWIN_ATTN_BF16 = 1 };
 
 /* Which kernel family serves the bf16 forward/backward.  AUTO picks the
- * tcgen05/TMEM kernel whenever the shape allows it (window 12: the warp-MMA
- * kernels for the backward and for the forward of un-aligned grids, where they
- * are the faster ones).  WARP_MMA forces the warp-level tensor-core kernels
+ * tcgen05/TMEM kernel whenever the shape allows it, except for window 12,
+ * where the warp-MMA kernels are the faster ones (forward and backward).  WARP_MMA forces the warp-level tensor-core kernels
  * (window 12 only; an error elsewhere). */
 enum { SWIN_ATTN_IMPL_AUTO = 0, SWIN_ATTN_IMPL_SIMT = 1, SWIN_ATTN_IMPL_TCGEN05 = 2, SWIN_ATTN_IMPL_WARP_MMA = 3 };
 
@@ -285,7 +284,7 @@ double swin_attn_probe_empty_bracket_us(void* stream, int32_t with_memset, int32
 /* Number of kernel launches issued by this library since load (all threads). */
 uint64_t swin_attn_launch_count(void);
 
-/* 1 if the tcgen05 kernel serves this shape under IMPL_AUTO, else 0. */
+/* 1 if a tcgen05 kernel serves this shape under shape->impl (AUTO or TCGEN05), else 0 (CUDA cores or warp-level MMAs). */
 int swin_attn_uses_tcgen05(const swin_attn_shape_t* shape, int backward);
 
 const char* swin_attn_last_error(void);

@@ -86,12 +86,12 @@ int swin_attn_forward(const swin_attn_shape_t* shape, const void* q, const void*
   p.table = bias_table; p.o = o; p.lse = lse; p.trace = g_trace;
   if (int rc = set_mask(shape, attn_mask, p)) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // window 12, impl AUTO: un-aligned grids (every stage of the window-12 encoder on a 352 x 1216 or 480 x 640 image) go to the warp-MMA forward
-  // -- every lane carries a row, two CTAs per SM, padding is free -- which beats the tcgen05 window-12 kernel there by
-  // 1.1-1.4x; aligned grids stay on tcgen05 (profiles/r2_micro_fwd_ws12_mma.jsonl).  impl = TCGEN05 forces tcgen05.
+  // window 12, impl AUTO: the warp-MMA forward -- every lane carries a row, two CTAs per SM, padding is free -- beats the
+  // tcgen05 window-12 kernel by 1.03x (aligned 96 x 96 grids) to 1.5x (the un-aligned stage grids of the window-12
+  // encoder on a 352 x 1216 image): profiles/r2_micro_fwd_ws12_mma.jsonl.  impl = TCGEN05 forces the tcgen05 kernel.
   const bool mma_ok = attn_mask == nullptr && mma12_forward_supported(p, shape->dtype);
   if (shape->impl == SWIN_ATTN_IMPL_WARP_MMA && !mma_ok) return fail("warp-MMA forward does not support this shape/dtype (window 12, bf16, no explicit mask)");
-  if (mma_ok && (shape->impl == SWIN_ATTN_IMPL_WARP_MMA || (shape->impl == SWIN_ATTN_IMPL_AUTO && (p.H != p.Hp || p.W != p.Wp)))) {
+  if (mma_ok && (shape->impl == SWIN_ATTN_IMPL_WARP_MMA || shape->impl == SWIN_ATTN_IMPL_AUTO)) {
     cudaError_t e = launch_mma12_forward(p, st);
     if (e != cudaSuccess) return fail_cuda("window-12 warp-MMA forward launch", e);
     return 0;
@@ -603,8 +603,10 @@ uint64_t swin_attn_launch_count(void) { return g_launches.load(std::memory_order
 int swin_attn_uses_tcgen05(const swin_attn_shape_t* shape, int backward) {
   Problem p;
   if (make_problem(shape, p)) return 0;
-  if (backward) return shape->impl != SWIN_ATTN_IMPL_SIMT && tc_backward_supported(p, shape->dtype) ? 1 : 0;
-  return shape->impl != SWIN_ATTN_IMPL_SIMT && (tc_forward_supported(p, shape->dtype) || tc12_forward_supported(p, shape->dtype)) ? 1 : 0;
+  if (shape->impl == SWIN_ATTN_IMPL_SIMT || shape->impl == SWIN_ATTN_IMPL_WARP_MMA) return 0;
+  if (backward) return tc_backward_supported(p, shape->dtype) ? 1 : 0;
+  if (shape->impl == SWIN_ATTN_IMPL_AUTO && mma12_forward_supported(p, shape->dtype)) return 0;   // window 12: warp-MMA forward
+  return tc_forward_supported(p, shape->dtype) || tc12_forward_supported(p, shape->dtype) ? 1 : 0;
 }
 
 const char* swin_attn_last_error(void) { return g_error.c_str(); }

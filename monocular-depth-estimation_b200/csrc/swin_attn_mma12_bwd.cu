@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   const int h = (int)blockIdx.x % p.nH;
   const int w0 = ((int)blockIdx.x / p.nH) * win_per_job, w1 = min(w0 + win_per_job, n_win);
   const float c1 = p.scale * kLog2e;
+  const float2 c1c1 = make_float2(c1, c1);
 
   for (int i = tid; i < NT; i += kThreads) {
     const float b0 = p.table[(NT - 1 - i) * p.nH + h] * kLog2e;
@@ -192,6 +193,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
       d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
     }
     // ---- per n-tile: S, dP -> P, dS (bf16 pairs) ----
+    const float2 nd0 = make_float2(-d0, -d0), nd1 = make_float2(-d1, -d1);
     uint32_t pk[10][2];   // dS pairs [n-tile][row g / g + 8]: the A fragments of dQ
     {
       uint32_t aq[2][4], ad[2][4];
@@ -221,11 +223,18 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
             if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) m0 += -100.0f * kLog2e;
             if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) m1 += -100.0f * kLog2e;
           }
-          const uint32_t p0 = pack2(ex2(fmaf(sc[0], c1, bb0.x + m0)), ex2(fmaf(sc[1], c1, bb0.y + m0)));
-          const uint32_t p1 = pack2(ex2(fmaf(sc[2], c1, bb1.x + m1)), ex2(fmaf(sc[3], c1, bb1.y + m1)));
+          // packed fp32x2 arithmetic: the two keys of a pair share every operand layout
+          const float2 e0 = __ffma2_rn(make_float2(sc[0], sc[1]), c1c1, __fadd2_rn(bb0, make_float2(m0, m0)));
+          const float2 e1 = __ffma2_rn(make_float2(sc[2], sc[3]), c1c1, __fadd2_rn(bb1, make_float2(m1, m1)));
+          const uint32_t p0 = pack2(ex2(e0.x), ex2(e0.y));
+          const uint32_t p1 = pack2(ex2(e1.x), ex2(e1.y));
           // dS from the bf16-rounded probabilities, as the products below see them
-          const uint32_t s0 = pack2(__uint_as_float(p0 << 16) * (dp[0] - d0), __uint_as_float(p0 & 0xffff0000u) * (dp[1] - d0));
-          const uint32_t s1 = pack2(__uint_as_float(p1 << 16) * (dp[2] - d1), __uint_as_float(p1 & 0xffff0000u) * (dp[3] - d1));
+          const float2 g0 = __fmul2_rn(make_float2(__uint_as_float(p0 << 16), __uint_as_float(p0 & 0xffff0000u)),
+                                       __fadd2_rn(make_float2(dp[0], dp[1]), nd0));
+          const float2 g1 = __fmul2_rn(make_float2(__uint_as_float(p1 << 16), __uint_as_float(p1 & 0xffff0000u)),
+                                       __fadd2_rn(make_float2(dp[2], dp[3]), nd1));
+          const uint32_t s0 = pack2(g0.x, g0.y);
+          const uint32_t s1 = pack2(g1.x, g1.y);
           *reinterpret_cast<uint32_t*>(&sm.p[i0 * kImgLd + j]) = p0;
           *reinterpret_cast<uint32_t*>(&sm.p[i1 * kImgLd + j]) = p1;
           *reinterpret_cast<uint32_t*>(&sm.ds[i0 * kImgLd + j]) = s0;
@@ -377,6 +386,7 @@ __global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem
   const int h = (int)blockIdx.x % p.nH;
   const int w0 = ((int)blockIdx.x / p.nH) * win_per_job, w1 = min(w0 + win_per_job, n_win);
   const float c1 = p.scale * kLog2e;
+  const float2 c1c1 = make_float2(c1, c1);
   for (int i = tid; i < NT; i += kFwdThreads) {
     const float b0 = p.table[(NT - 1 - i) * p.nH + h] * kLog2e;
     const float b1 = i + 1 < NT ? p.table[(NT - 2 - i) * p.nH + h] * kLog2e : 0.f;
@@ -455,7 +465,7 @@ __global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem
     float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      float t[6][4];
+      float2 t[6][2];   // [n-tile][row g / g + 8]: the logits of a key pair
       float cm0 = -INFINITY, cm1 = -INFINITY;
 #pragma unroll
       for (int nn = 0; nn < 6; ++nn) {
@@ -467,19 +477,18 @@ __global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem
         mma_bf16(sc, aq[1][0], aq[1][1], aq[1][2], aq[1][3], bk[2], bk[3]);
         const int cc = 8 * nt + 11 * ((8 * nt) / WS);   // compile-time after unrolling
         const float2 bb0 = (nt % 3 == 1 ? pb0b : pb0a)[cc], bb1 = (nt % 3 == 1 ? pb1b : pb1a)[cc];
-        float m0 = 0.f, m1 = 0.f;
+        float2 b0 = bb0, b1 = bb1;
         if (masked) {
           const int jy = (8 * nt) / WS + (nt % 3 == 1 ? hi : 0), jx = 8 * nt + 2 * t4 - jy * WS;
           const bool kh_ = jy >= 6, kw_ = jx >= 6;
-          if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) m0 = -100.0f * kLog2e;
-          if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) m1 = -100.0f * kLog2e;
+          if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) b0 = __fadd2_rn(b0, make_float2(-100.0f * kLog2e, -100.0f * kLog2e));
+          if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) b1 = __fadd2_rn(b1, make_float2(-100.0f * kLog2e, -100.0f * kLog2e));
         }
-        t[nn][0] = fmaf(sc[0], c1, bb0.x + m0);
-        t[nn][1] = fmaf(sc[1], c1, bb0.y + m0);
-        t[nn][2] = fmaf(sc[2], c1, bb1.x + m1);
-        t[nn][3] = fmaf(sc[3], c1, bb1.y + m1);
-        cm0 = fmaxf(cm0, fmaxf(t[nn][0], t[nn][1]));
-        cm1 = fmaxf(cm1, fmaxf(t[nn][2], t[nn][3]));
+        // packed fp32x2 arithmetic: the two keys of a pair share every operand layout
+        t[nn][0] = __ffma2_rn(make_float2(sc[0], sc[1]), c1c1, b0);
+        t[nn][1] = __ffma2_rn(make_float2(sc[2], sc[3]), c1c1, b1);
+        cm0 = fmaxf(cm0, fmaxf(t[nn][0].x, t[nn][0].y));
+        cm1 = fmaxf(cm1, fmaxf(t[nn][1].x, t[nn][1].y));
       }
       cm0 = fmaxf(cm0, __shfl_xor_sync(0xffffffffu, cm0, 1));
       cm0 = fmaxf(cm0, __shfl_xor_sync(0xffffffffu, cm0, 2));
@@ -489,20 +498,22 @@ __global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem
       const float al0 = ex2(mx0 - n0), al1 = ex2(mx1 - n1);   // exp2(-inf) = 0 for the first chunk
       mx0 = n0;
       mx1 = n1;
+      const float2 a00 = make_float2(al0, al0), a11 = make_float2(al1, al1);
 #pragma unroll
       for (int nt = 0; nt < 5; ++nt) {
-        o[nt][0] *= al0;
-        o[nt][1] *= al0;
-        o[nt][2] *= al1;
-        o[nt][3] *= al1;
+        const float2 u0 = __fmul2_rn(make_float2(o[nt][0], o[nt][1]), a00), u1 = __fmul2_rn(make_float2(o[nt][2], o[nt][3]), a11);
+        o[nt][0] = u0.x;
+        o[nt][1] = u0.y;
+        o[nt][2] = u1.x;
+        o[nt][3] = u1.y;
       }
+      const float2 nn0 = make_float2(-n0, -n0), nn1 = make_float2(-n1, -n1);
       uint32_t pa[6][2];
 #pragma unroll
       for (int nn = 0; nn < 6; ++nn) {
-        const uint32_t p0 = pack2(ex2(t[nn][0] - n0), ex2(t[nn][1] - n0));
-        const uint32_t p1 = pack2(ex2(t[nn][2] - n1), ex2(t[nn][3] - n1));
-        pa[nn][0] = p0;
-        pa[nn][1] = p1;
+        const float2 e0 = __fadd2_rn(t[nn][0], nn0), e1 = __fadd2_rn(t[nn][1], nn1);
+        pa[nn][0] = pack2(ex2(e0.x), ex2(e0.y));
+        pa[nn][1] = pack2(ex2(e1.x), ex2(e1.y));
       }
 #pragma unroll
       for (int kk = 0; kk < 3; ++kk) {

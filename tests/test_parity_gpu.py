@@ -128,7 +128,7 @@ def test_forward_ws12_tcgen05_on_unaligned_tensors_matches_oracle(case):
 
 
 # The warp-MMA forward of swin_attn_mma12_bwd.cu (online softmax over three key chunks, pad vectors written into the K / V
-# rows of pad tokens by the gather): what impl AUTO runs on un-aligned window-12 grids; forced here on aligned ones too
+# rows of pad tokens by the gather): what impl AUTO runs on window-12 grids, aligned or not
 @pytest.mark.parametrize("case", [c + (True,) for c in TC12_CASES] + TC12_PAD_CASES)
 def test_forward_ws12_warp_mma_matches_oracle(case):
     ws, shift, b, h, w, nh, ext, with_pads = case
@@ -148,10 +148,10 @@ def test_forward_ws12_warp_mma_matches_oracle(case):
     assert _lib.load().swin_attn_launch_count() == before + 1
     assert got.shape == (b, h, w, c)
     check(rel_err(got.float(), want), TOL_BF16, "ws12 warp-MMA forward")
-    if h % ws or w % ws:   # un-aligned: impl AUTO is this kernel
-        auto, _ = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, False,
-                                          _lib.IMPL_AUTO, None)
-        assert torch.equal(auto, got)
+    # impl AUTO is this kernel
+    auto, _ = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, False,
+                                      _lib.IMPL_AUTO, None)
+    assert torch.equal(auto, got)
     check(rel_err(lse[:, :h, :w], want_lse[:, :h, :w]), TOL_BF16, "lse ws12 warp-MMA forward")
     # the two tensor-core forwards agree on the same bf16 inputs
     tc, _ = torch.ops.swin_attn.fwd(dev(packed), dev(v), dev(table), dev(pads), dev(v_pad), ws, shift, nh, 32 ** -0.5, False,
