@@ -290,7 +290,14 @@ class Trainer:
         loss = self.loss_fn(pred, gt)
         loss.backward()
         if self.grad_norm:
-            torch.nn.utils.clip_grad_norm_(self.raw.parameters(), self.grad_norm)
+            if self.opt.defaults.get("fused"):
+                # clip_grad_norm_ without its pass over the gradients: the fused AdamW kernel divides every gradient by
+                # `grad_scale` on the fly (the hook torch's GradScaler uses), so the clip coefficient goes there
+                grads = [p.grad for p in self.raw.parameters() if p.grad is not None]
+                total = torch.linalg.vector_norm(torch.stack(torch._foreach_norm(grads)))
+                self.opt.grad_scale = ((total + 1e-6) / self.grad_norm).clamp(min=1.0).float()   # 1 / clip coefficient
+            else:
+                torch.nn.utils.clip_grad_norm_(self.raw.parameters(), self.grad_norm)
         self.opt.step()
         return loss.detach()
 

@@ -41,19 +41,46 @@ class DropPath(nn.Module):
     def __init__(self, drop_prob: float = 0.0):
         super().__init__()
         self.drop_prob = float(drop_prob)
+        self._banked = None   # this forward's gate, drawn with every other DropPath's in one go (draw_drop_path_gates)
 
     def forward(self, x):
         if self.drop_prob == 0.0 or not self.training:
             return x
-        return x * self.gate(x)   # one pass over x (timm: x.div(keep) * gate)
+        return x * self.gate(x).to(x.dtype)   # one pass over x (timm: x.div(keep) * gate)
 
     def gate(self, x):
         """Per-sample scale 0 | 1/keep of shape (B, 1, ..), or None when the path is never dropped (eval, rate 0):
-        lets the caller fold the scaling into the residual add (``ops.residual``)."""
+        lets the caller fold the scaling into the residual add (``ops.residual``).  fp32 when it comes from the
+        model-wide draw (what the fused add + LayerNorm kernels take), else the dtype of ``x``; the value 1/keep is
+        rounded to the dtype of ``x`` either way."""
         if self.drop_prob == 0.0 or not self.training:
             return None
+        g, self._banked = self._banked, None
+        if g is not None and g.shape[0] == x.shape[0] and g.device == x.device:
+            return g.view((x.shape[0],) + (1,) * (x.ndim - 1))
         keep = 1.0 - self.drop_prob
         return x.new_empty((x.shape[0],) + (1,) * (x.ndim - 1)).bernoulli_(keep) / keep
+
+
+def draw_drop_path_gates(root: nn.Module, batch: int, device, dtype) -> None:
+    """The stochastic-depth gates of EVERY DropPath under ``root`` for one training forward, drawn by three kernels
+    (uniform numbers, compare, scale) instead of two or three per module and two more per module for the fp32 copies the
+    fused add + LayerNorm nodes take -- ~250 launches of a Swin-L training step.  Each module's ``gate`` then returns its
+    row; the per-sample statistics are those of ``bernoulli_(keep) / keep`` per module (timm 0.5.4 ``drop_path``), the
+    value 1/keep rounded to ``dtype`` as the per-module draw on a ``dtype`` tensor rounds it."""
+    cache = root.__dict__.get("_drop_path_cache")
+    if cache is None or cache[1].device != torch.device(device) or cache[3] != dtype:
+        mods = [m for m in root.modules() if isinstance(m, DropPath) and m.drop_prob > 0.0]
+        keep = torch.tensor([1.0 - m.drop_prob for m in mods], dtype=torch.float32)
+        inv = (1.0 / keep).to(dtype).float()
+        cache = (mods, keep.to(device).unsqueeze(1), inv.to(device).unsqueeze(1), dtype)
+        root.__dict__["_drop_path_cache"] = cache
+    mods, keep, inv, _ = cache
+    if not mods:
+        return
+    bank = (torch.rand(len(mods), batch, device=keep.device) < keep).float() * inv
+    for i, m in enumerate(mods):
+        m._banked = bank[i]
 
 
 def _gate(drop_path, x):

@@ -16,7 +16,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from . import ops
-from .layers import BasicLayer, NewCRF, PatchEmbed, PatchMerging
+from .layers import BasicLayer, NewCRF, PatchEmbed, PatchMerging, draw_drop_path_gates
 
 _VARIANTS = {
     "tiny": dict(embed_dim=96, depths=[2, 2, 6, 2], num_heads=[3, 6, 12, 24]),
@@ -264,6 +264,9 @@ class NewCRFDepth(nn.Module):
         self.decoder.init_weights()
 
     def forward(self, imgs):
+        if self.training and torch.is_grad_enabled():   # every stochastic-depth gate of this forward in one draw
+            bf16 = torch.is_autocast_enabled() and torch.get_autocast_dtype(imgs.device.type) == torch.bfloat16
+            draw_drop_path_gates(self, imgs.shape[0], imgs.device, torch.bfloat16 if bf16 else imgs.dtype)
         feats = self.backbone(imgs)
         e = self.decoder(feats)
         e = F.pixel_shuffle(self.crf3(feats[3], e), 2)

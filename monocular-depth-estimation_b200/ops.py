@@ -220,7 +220,11 @@ def gelu(act: torch.nn.Module, x: Tensor) -> Tensor:
 
 def residual(x: Tensor, delta: Tensor, scale: Optional[Tensor] = None) -> Tensor:
     """``x + delta`` or, with a stochastic-depth gate, ``x + delta * scale`` in one kernel (DropPath.gate)."""
-    return x + delta if scale is None else torch.addcmul(x, delta, scale)
+    if scale is None:
+        return x + delta
+    if scale.dtype != delta.dtype:   # the model-wide draw is fp32 (layers.draw_drop_path_gates); keep the stream's dtype
+        scale = scale.to(delta.dtype)
+    return torch.addcmul(x, delta, scale)
 
 
 def add_norm(norm: torch.nn.Module, x: Tensor, delta: Tensor, scale: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:

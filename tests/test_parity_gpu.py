@@ -1209,6 +1209,68 @@ def test_add_norm_training_node_matches_unfused_autograd(channels, gated, stream
         assert float(got[3][0].float().abs().max()) == 0.0       # dropped sample: no gradient into the branch
 
 
+def test_trainer_clip_through_the_fused_adamw_equals_clip_grad_norm_then_step():
+    """Trainer.step hands the clip coefficient to the fused AdamW kernel as `grad_scale` (no pass over the gradients):
+    same parameters as torch.nn.utils.clip_grad_norm_ followed by the same optimizer step, on a net whose backward is
+    deterministic, with a gradient norm far above the threshold (clipping active) and below it (inactive)."""
+    from mde_b200 import harness
+
+    def make():
+        torch.manual_seed(11)
+        return torch.nn.Sequential(torch.nn.Conv2d(3, 8, 1), torch.nn.Tanh(), torch.nn.Conv2d(8, 1, 1), torch.nn.Softplus()).to(DEV)
+
+    gen = torch.Generator(device=DEV).manual_seed(7)
+    x = torch.randn(2, 3, 12, 16, device=DEV, generator=gen)
+    gt = torch.rand(2, 1, 12, 16, device=DEV, generator=gen) * 9 + 0.5
+    for grad_norm in (1e-3, 1e3):
+        a, b = make(), make()
+        tr = harness.Trainer(a, lr=1e-2, grad_norm=grad_norm, bf16=False)
+        opt = torch.optim.AdamW(b.parameters(), lr=1e-2, weight_decay=0.0, fused=True)
+        loss_fn = harness.SILogLoss()
+        for _ in range(3):
+            la = tr.step(x, gt)
+            opt.zero_grad(set_to_none=True)
+            lb = loss_fn(b(x), gt)
+            lb.backward()
+            torch.nn.utils.clip_grad_norm_(b.parameters(), grad_norm)
+            opt.step()
+            assert abs(float(la) - float(lb)) <= 1e-5 * abs(float(lb))
+        for p, q in zip(a.parameters(), b.parameters()):
+            assert torch.allclose(p, q, rtol=1e-4, atol=1e-6), (grad_norm, float((p - q).abs().max()))
+
+
+def test_drop_path_gates_of_a_training_forward_come_from_one_draw():
+    """layers.draw_drop_path_gates: NewCRFDepth.forward draws every stochastic-depth gate of the step at once; each
+    DropPath consumes its row (fp32, 0 or bf16(1/keep) under autocast), none is left behind, gradients are finite, and a
+    module outside a model still draws for itself."""
+    m = mde_b200.NewCRFDepth(version="tiny07", max_depth=10.0)
+    m.load_state_dict(synthetic_state(m), strict=True)
+    m = m.to(DEV).train()
+    dps = [d for d in m.modules() if isinstance(d, layers.DropPath) and d.drop_prob > 0.0]
+    assert len(dps) >= 10
+    layers.draw_drop_path_gates(m, 4, DEV, torch.bfloat16)
+    for d in dps:
+        g = d._banked
+        want = float(torch.tensor(1.0 / (1.0 - d.drop_prob)).bfloat16())
+        assert g.dtype == torch.float32 and g.shape == (4,) and all(v in (0.0, want) for v in g.tolist())
+    x = randn("dpbank.img", 4, 3, 64, 96).to(DEV)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = m(x)
+    out.float().mean().backward()
+    assert all(d._banked is None for d in dps)
+    assert all(torch.isfinite(p.grad).all() for p in m.parameters() if p.grad is not None)
+    # keep rate of the model-wide draw
+    layers.draw_drop_path_gates(m, 4096, DEV, torch.bfloat16)
+    d = dps[-1]
+    rate = float((d._banked > 0).float().mean())
+    assert abs(rate - (1.0 - d.drop_prob)) < 0.03
+    for q in dps:
+        q._banked = None
+    lone = layers.DropPath(0.25).to(DEV).train()
+    y = lone(torch.ones(4096, 3, device=DEV))
+    assert y.dtype == torch.float32 and abs(float((y[:, 0] > 0).float().mean()) - 0.75) < 0.03
+
+
 def test_graphed_train_step_follows_the_eager_training_steps():
     """harness.GraphedTrainStep (forward + SILog + backward + clip + AdamW captured as one CUDA graph) against the eager
     Trainer.step on the same batches from the same initial state: same losses step by step (up to the order of the
