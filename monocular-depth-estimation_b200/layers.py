@@ -41,7 +41,7 @@ class DropPath(nn.Module):
     def __init__(self, drop_prob: float = 0.0):
         super().__init__()
         self.drop_prob = float(drop_prob)
-        self._banked = None   # this forward's gate, drawn with every other DropPath's in one go (draw_drop_path_gates)
+        self._banked = None   # this forward's gates (a block uses its DropPath twice), drawn with every other DropPath's in one go
 
     def forward(self, x):
         if self.drop_prob == 0.0 or not self.training:
@@ -55,9 +55,10 @@ class DropPath(nn.Module):
         rounded to the dtype of ``x`` either way."""
         if self.drop_prob == 0.0 or not self.training:
             return None
-        g, self._banked = self._banked, None
-        if g is not None and g.shape[0] == x.shape[0] and g.device == x.device:
-            return g.view((x.shape[0],) + (1,) * (x.ndim - 1))
+        if self._banked:
+            g = self._banked.pop()
+            if g.shape[0] == x.shape[0] and g.device == x.device:
+                return g.view((x.shape[0],) + (1,) * (x.ndim - 1))
         keep = 1.0 - self.drop_prob
         return x.new_empty((x.shape[0],) + (1,) * (x.ndim - 1)).bernoulli_(keep) / keep
 
@@ -66,7 +67,7 @@ def draw_drop_path_gates(root: nn.Module, batch: int, device, dtype) -> None:
     """The stochastic-depth gates of EVERY DropPath under ``root`` for one training forward, drawn by three kernels
     (uniform numbers, compare, scale) instead of two or three per module and two more per module for the fp32 copies the
     fused add + LayerNorm nodes take -- ~250 launches of a Swin-L training step.  Each module's ``gate`` then returns its
-    row; the per-sample statistics are those of ``bernoulli_(keep) / keep`` per module (timm 0.5.4 ``drop_path``), the
+    rows (two per module and forward); the per-sample statistics are those of ``bernoulli_(keep) / keep`` per module (timm 0.5.4 ``drop_path``), the
     value 1/keep rounded to ``dtype`` as the per-module draw on a ``dtype`` tensor rounds it."""
     cache = root.__dict__.get("_drop_path_cache")
     if cache is None or cache[1].device != torch.device(device) or cache[3] != dtype:
@@ -78,9 +79,10 @@ def draw_drop_path_gates(root: nn.Module, batch: int, device, dtype) -> None:
     mods, keep, inv, _ = cache
     if not mods:
         return
-    bank = (torch.rand(len(mods), batch, device=keep.device) < keep).float() * inv
+    # two independent gates per module: a block calls its DropPath on the attention branch and on the MLP branch
+    bank = (torch.rand(2, len(mods), batch, device=keep.device) < keep).float() * inv
     for i, m in enumerate(mods):
-        m._banked = bank[i]
+        m._banked = [bank[1, i], bank[0, i]]
 
 
 def _gate(drop_path, x):

@@ -1250,19 +1250,20 @@ def test_drop_path_gates_of_a_training_forward_come_from_one_draw():
     assert len(dps) >= 10
     layers.draw_drop_path_gates(m, 4, DEV, torch.bfloat16)
     for d in dps:
-        g = d._banked
         want = float(torch.tensor(1.0 / (1.0 - d.drop_prob)).bfloat16())
-        assert g.dtype == torch.float32 and g.shape == (4,) and all(v in (0.0, want) for v in g.tolist())
+        assert len(d._banked) == 2   # a block gates its attention branch and its MLP branch
+        for g in d._banked:
+            assert g.dtype == torch.float32 and g.shape == (4,) and all(v in (0.0, want) for v in g.tolist())
     x = randn("dpbank.img", 4, 3, 64, 96).to(DEV)
     with torch.autocast("cuda", dtype=torch.bfloat16):
         out = m(x)
     out.float().mean().backward()
-    assert all(d._banked is None for d in dps)
+    assert all(not d._banked for d in dps)
     assert all(torch.isfinite(p.grad).all() for p in m.parameters() if p.grad is not None)
     # keep rate of the model-wide draw
     layers.draw_drop_path_gates(m, 4096, DEV, torch.bfloat16)
     d = dps[-1]
-    rate = float((d._banked > 0).float().mean())
+    rate = float((torch.stack(d._banked) > 0).float().mean())
     assert abs(rate - (1.0 - d.drop_prob)) < 0.03
     for q in dps:
         q._banked = None
