@@ -1309,6 +1309,11 @@ def test_graphed_train_step_follows_the_eager_training_steps():
     for a, b in zip(loss_e[3:], loss_g[3:]):
         assert abs(a - b) <= 2e-3 * abs(a), (loss_e, loss_g)
     for (n, p), (_, q) in zip(net_e.named_parameters(), net_g.named_parameters()):
+        if n.endswith("attn.qk.bias"):
+            # The gradient of the KEY bias is zero in exact arithmetic (a constant added to every key shifts all logits of
+            # a row alike and the softmax ignores it): what reaches AdamW is rounding noise whose sign depends on the order
+            # of the atomic sums, and AdamW normalises it to steps of +-lr.  Compare the query half only.
+            p, q = p[:p.numel() // 2], q[:q.numel() // 2]
         assert float(((p - q).abs() > 5e-4).float().mean()) < 1e-2, n
     with pytest.raises(ValueError):
         harness.GraphedTrainStep(harness.Trainer(Net().to(DEV)), *batches[0])     # needs capturable=True
