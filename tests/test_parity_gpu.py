@@ -433,6 +433,17 @@ FULL = [  # large07 stage-0 grids of the three BASELINE shapes, batch 8 / 2; the
 @pytest.mark.parametrize("shape", FULL)
 @pytest.mark.parametrize("shift", [0, 3])
 def test_full_size_properties(shape, shift, dtype):
+    _full_size_forward_properties(shape, shift, dtype)
+
+
+# the window-12 encoder (NewCRFDepth "large12") at 352 x 1216, batch 8: stage 0, stage 2 and stage 3 grids, none a multiple of 12
+@pytest.mark.parametrize("shape", [(8, 88, 304, 6, 12), (8, 22, 76, 24, 12), (8, 11, 38, 48, 12)])
+@pytest.mark.parametrize("shift", [0, 6])
+def test_full_size_properties_window12(shape, shift):
+    _full_size_forward_properties(shape, shift, torch.bfloat16)
+
+
+def _full_size_forward_properties(shape, shift, dtype):
     b, h, w, nh, ws = shape
     c = nh * 32
     gen = torch.Generator(device=DEV).manual_seed(1234)
@@ -477,6 +488,17 @@ def test_full_size_properties(shape, shift, dtype):
 @pytest.mark.parametrize("shift", [0, 3])
 @pytest.mark.parametrize("shape", [(8, 91, 308, 6, 7), (8, 28, 77, 24, 7)])   # large07 stage-0 / stage-2 padded grids, batch 8
 def test_full_size_backward_properties(shape, shift):
+    _full_size_backward_properties(shape, shift, _lib.IMPL_TCGEN05)
+
+
+# large12 training grids (480 x 640, padded to multiples of 12 by the layers): stage 0 and stage 2, batch 8: the warp-MMA backward
+@pytest.mark.parametrize("shift", [0, 6])
+@pytest.mark.parametrize("shape", [(8, 120, 168, 6, 12), (8, 36, 48, 24, 12)])
+def test_full_size_backward_properties_window12(shape, shift):
+    _full_size_backward_properties(shape, shift, _lib.IMPL_WARP_MMA)
+
+
+def _full_size_backward_properties(shape, shift, impl):
     b, h, w, nh, ws = shape
     c = nh * 32
     gen = torch.Generator(device=DEV).manual_seed(4321)
@@ -484,16 +506,16 @@ def test_full_size_backward_properties(shape, shift):
     table = 0.5 * torch.randn((2 * ws - 1) ** 2, nh, device=DEV, generator=gen)
     d_o = torch.randn(b, h, w, c, device=DEV, generator=gen).bfloat16()
     o, lse = torch.ops.swin_attn.fwd(qkv, None, table, None, None, ws, shift, nh, 32 ** -0.5, True, _lib.IMPL_AUTO, None)
-    g_tc = torch.ops.swin_attn.bwd(d_o, qkv, None, o, lse, table, ws, shift, nh, 32 ** -0.5, None, _lib.IMPL_TCGEN05)
+    g_tc = torch.ops.swin_attn.bwd(d_o, qkv, None, o, lse, table, ws, shift, nh, 32 ** -0.5, None, impl)
     g_simt = torch.ops.swin_attn.bwd(d_o, qkv, None, o, lse, table, ws, shift, nh, 32 ** -0.5, None, _lib.IMPL_SIMT)
-    # (1) the tcgen05 and the CUDA-core backward agree (both bf16 storage, fp32 accumulation)
+    # (1) the tensor-core and the CUDA-core backward agree (both bf16 storage, fp32 accumulation)
     assert rel_err(g_tc[0].float(), g_simt[0].float()) < 2e-2
     assert rel_err(g_tc[2], g_simt[2]) < 2e-2
     # (2) every row of dS sums to zero, hence so does every head's column of the bias-table gradient
     assert float(g_tc[2].sum(0).abs().max() / g_tc[2].abs().max()) < 2e-2
     # (3) dV is linear in dO:  bwd(2 dO).dv == 2 bwd(dO).dv exactly in bf16 (power of two)
     g2 = torch.ops.swin_attn.bwd((2 * d_o.float()).bfloat16(), qkv, None, o, lse, table, ws, shift, nh, 32 ** -0.5, None,
-                                 _lib.IMPL_TCGEN05)
+                                 impl)
     assert rel_err(g2[0][..., 2 * c:].float(), 2 * g_tc[0][..., 2 * c:].float()) < 1e-6
     # (4) one image against the fp64 oracle's autograd
     pr = qkv[:1].double().cpu().requires_grad_()
