@@ -25,6 +25,8 @@
 // q, k, v, dO, o rows are gathered (cp.async, one window ahead, two tile buffers; one token per thread) from / dq, dk, dv
 // rows scattered to the image-order tensors with the cyclic shift folded into the token coordinates
 // (newcrf_layers.py:220-227 / swin_transformer.py:212-219 and their inverses).
+#include <type_traits>
+
 #include "swin_common.cuh"
 
 namespace swin {
@@ -120,7 +122,6 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     sm.bins[i] = 0.f;
   }
   const int r0 = strip * 16;
-  const int n0 = kh ? 10 : 0, n_cnt = kh ? 8 : 10;             // this warp's n-tiles (8 keys each) = 5 / 4 k-steps of dQ
   // ldmatrix lane addressing.  "A pattern": matrices (rows 0-7, cols 0-7) (rows 8-15, cols 0-7) (rows 0-7, cols 8-15)
   // (rows 8-15, cols 8-15); "T pattern" swaps the middle two.
   const int la_row = (lane & 7) + ((lane >> 3) & 1) * 8;
@@ -134,6 +135,12 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   const int iy0 = i0 / WS, ix0 = i0 - iy0 * WS, iy1 = i1 / WS, ix1 = i1 - iy1 * WS;
   const int rb0 = 264 - 23 * iy0 - ix0, rb1 = 264 - 23 * iy1 - ix1;
   const bool my_h0 = iy0 >= 6, my_w0 = ix0 >= 6, my_h1 = iy1 >= 6, my_w1 = ix1 >= 6;
+  // keys j = 8 nt + 2 t4 (+ 1) of n-tile nt lie in window row (8 nt) / 12 + (nt % 3 == 1 && t4 >= 2): the bias index
+  // rb + 23 jy + jx = rb + j + 11 jy is a per-thread base (two variants) plus a compile-time constant; same for the images
+  const int hi = t4 >> 1;
+  const float2 *pb0a = sm.bias2 + rb0 + 2 * t4, *pb0b = pb0a + 11 * hi, *pb1a = sm.bias2 + rb1 + 2 * t4, *pb1b = pb1a + 11 * hi;
+  __nv_bfloat16 *pimg0 = sm.p + i0 * kImgLd + 2 * t4, *pimg1 = sm.p + i1 * kImgLd + 2 * t4;
+  __nv_bfloat16 *simg0 = sm.ds + i0 * kImgLd + 2 * t4, *simg1 = sm.ds + i1 * kImgLd + 2 * t4;
 
   // The five tiles of a window (144 rows x 64 B each: one token per four threads, one 16-byte chunk of each tensor per
   // thread) and its lse row are fetched with cp.async one window ahead, into the other tile buffer.
@@ -192,19 +199,32 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
       d1 += __shfl_xor_sync(0xffffffffu, d1, 1);
       d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
     }
-    // ---- per n-tile: S, dP -> P, dS (bf16 pairs) ----
-    const float2 nd0 = make_float2(-d0, -d0), nd1 = make_float2(-d1, -d1);
-    uint32_t pk[10][2];   // dS pairs [n-tile][row g / g + 8]: the A fragments of dQ
-    {
-      uint32_t aq[2][4], ad[2][4];
-      ldsm_x4(aq[0], tq + r0 * 64 + offa0);
-      ldsm_x4(aq[1], tq + r0 * 64 + offa1);
-      ldsm_x4(ad[0], td + r0 * 64 + offa0);
-      ldsm_x4(ad[1], td + r0 * 64 + offa1);
+    // 16 x 32 fp32 accumulator (four n-tiles) -> bf16 -> rows i0 / i1 of an image-order tensor
+    auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl) {
+      __nv_bfloat16* d0p = static_cast<__nv_bfloat16*>(base) + pix0 * ps + h * HD + 2 * t4;
+      __nv_bfloat16* d1p = static_cast<__nv_bfloat16*>(base) + pix1 * ps + h * HD + 2 * t4;
 #pragma unroll
-      for (int nn = 0; nn < 10; ++nn) {
-        if (nn < n_cnt) {
-          const int nt = n0 + nn;
+      for (int nt = 0; nt < 4; ++nt) {
+        *reinterpret_cast<uint32_t*>(d0p + nt * 8) = pack2(acc[nt][0] * scl, acc[nt][1] * scl);
+        *reinterpret_cast<uint32_t*>(d1p + nt * 8) = pack2(acc[nt][2] * scl, acc[nt][3] * scl);
+      }
+    };
+    // The query side of the strip, specialised on which half of the key columns this warp takes: every n-tile index is
+    // then a compile-time constant (bias offsets, image addresses, tile addresses fold into immediates).
+    const float2 nd0 = make_float2(-d0, -d0), nd1 = make_float2(-d1, -d1);
+    auto query_side = [&](auto KH) {
+      constexpr int kN0 = decltype(KH)::value ? 10 : 0, kCnt = decltype(KH)::value ? 8 : 10;
+      // ---- per n-tile: S, dP -> P, dS (bf16 pairs) ----
+      uint32_t pk[kCnt][2];   // dS pairs [n-tile][row g / g + 8]: the A fragments of dQ
+      {
+        uint32_t aq[2][4], ad[2][4];
+        ldsm_x4(aq[0], tq + r0 * 64 + offa0);
+        ldsm_x4(aq[1], tq + r0 * 64 + offa1);
+        ldsm_x4(ad[0], td + r0 * 64 + offa0);
+        ldsm_x4(ad[1], td + r0 * 64 + offa1);
+#pragma unroll
+        for (int nn = 0; nn < kCnt; ++nn) {
+          const int nt = kN0 + nn;
           uint32_t bk[4], bv[4];
           ldsm_x4(bk, tk_ + nt * 512 + offb);
           ldsm_x4(bv, tv + nt * 512 + offb);
@@ -213,12 +233,12 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
           mma_bf16(dp, ad[0][0], ad[0][1], ad[0][2], ad[0][3], bv[0], bv[1]);
           mma_bf16(sc, aq[1][0], aq[1][1], aq[1][2], aq[1][3], bk[2], bk[3]);
           mma_bf16(dp, ad[1][0], ad[1][1], ad[1][2], ad[1][3], bv[2], bv[3]);
-          const int j = nt * 8 + 2 * t4;                 // keys j, j + 1: same window row, neighbouring columns
-          const int jy = (j * 171) >> 11, jx = j - jy * WS;   // j / 12 for j < 144
-          const int cj = j + 11 * jy;                    // 23 jy + jx
-          const float2 bb0 = sm.bias2[rb0 + cj], bb1 = sm.bias2[rb1 + cj];
+          // keys j = 8 nt + 2 t4, j + 1 (same window row): bias index = per-thread base + compile-time constant
+          const int cc = 8 * nt + 11 * ((8 * nt) / WS);
+          const float2 bb0 = (nt % 3 == 1 ? pb0b : pb0a)[cc], bb1 = (nt % 3 == 1 ? pb1b : pb1a)[cc];
           float m0 = nl0, m1 = nl1;
           if (masked) {   // warp-uniform; both keys of the pair lie in the same region
+            const int jy = (8 * nt) / WS + (nt % 3 == 1 ? hi : 0), jx = 8 * nt + 2 * t4 - jy * WS;
             const bool kh_ = jy >= 6, kw_ = jx >= 6;
             if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) m0 += -100.0f * kLog2e;
             if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) m1 += -100.0f * kLog2e;
@@ -235,56 +255,44 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
                                        __fadd2_rn(make_float2(dp[2], dp[3]), nd1));
           const uint32_t s0 = pack2(g0.x, g0.y);
           const uint32_t s1 = pack2(g1.x, g1.y);
-          *reinterpret_cast<uint32_t*>(&sm.p[i0 * kImgLd + j]) = p0;
-          *reinterpret_cast<uint32_t*>(&sm.p[i1 * kImgLd + j]) = p1;
-          *reinterpret_cast<uint32_t*>(&sm.ds[i0 * kImgLd + j]) = s0;
-          *reinterpret_cast<uint32_t*>(&sm.ds[i1 * kImgLd + j]) = s1;
+          *reinterpret_cast<uint32_t*>(pimg0 + nt * 8) = p0;
+          *reinterpret_cast<uint32_t*>(pimg1 + nt * 8) = p1;
+          *reinterpret_cast<uint32_t*>(simg0 + nt * 8) = s0;
+          *reinterpret_cast<uint32_t*>(simg1 + nt * 8) = s1;
           pk[nn][0] = s0;
           pk[nn][1] = s1;
         }
       }
-    }
-    // 16 x 32 fp32 accumulator (four n-tiles) -> bf16 -> rows i0 / i1 of an image-order tensor
-    auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl) {
-      __nv_bfloat16* d0p = static_cast<__nv_bfloat16*>(base) + pix0 * ps + h * HD + 2 * t4;
-      __nv_bfloat16* d1p = static_cast<__nv_bfloat16*>(base) + pix1 * ps + h * HD + 2 * t4;
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt) {
-        *reinterpret_cast<uint32_t*>(d0p + nt * 8) = pack2(acc[nt][0] * scl, acc[nt][1] * scl);
-        *reinterpret_cast<uint32_t*>(d1p + nt * 8) = pack2(acc[nt][2] * scl, acc[nt][3] * scl);
-      }
-    };
-    // ---- dQ_s = scale dS_s K over this warp's keys: A from the registers, B = K (keys x channels) by transposing loads ----
-    {
+      // ---- dQ_s = scale dS_s K over this warp's keys: A from the registers, B = K (keys x channels) by transposing loads ----
       float acc[4][4];
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
 #pragma unroll
-      for (int kk = 0; kk < 5; ++kk) {
-        if (2 * kk < n_cnt) {
-          const int krow = (n0 + 2 * kk) * 8;
-          uint32_t b0[4], b1[4];
-          ldsm_x4_t(b0, tk_ + krow * 64 + offa0);
-          ldsm_x4_t(b1, tk_ + krow * 64 + offa1);
-          const uint32_t a0 = pk[2 * kk][0], a1 = pk[2 * kk][1], a2 = pk[2 * kk + 1][0], a3 = pk[2 * kk + 1][1];
-          mma_bf16(acc[0], a0, a1, a2, a3, b0[0], b0[1]);
-          mma_bf16(acc[1], a0, a1, a2, a3, b0[2], b0[3]);
-          mma_bf16(acc[2], a0, a1, a2, a3, b1[0], b1[1]);
-          mma_bf16(acc[3], a0, a1, a2, a3, b1[2], b1[3]);
-        }
+      for (int kk = 0; kk < kCnt / 2; ++kk) {
+        const int krow = (kN0 + 2 * kk) * 8;
+        uint32_t b0[4], b1[4];
+        ldsm_x4_t(b0, tk_ + krow * 64 + offa0);
+        ldsm_x4_t(b1, tk_ + krow * 64 + offa1);
+        const uint32_t a0 = pk[2 * kk][0], a1 = pk[2 * kk][1], a2 = pk[2 * kk + 1][0], a3 = pk[2 * kk + 1][1];
+        mma_bf16(acc[0], a0, a1, a2, a3, b0[0], b0[1]);
+        mma_bf16(acc[1], a0, a1, a2, a3, b0[2], b0[3]);
+        mma_bf16(acc[2], a0, a1, a2, a3, b1[0], b1[1]);
+        mma_bf16(acc[3], a0, a1, a2, a3, b1[2], b1[3]);
       }
       // the odd warp hands its partial sum to the even warp of the strip
-      if (kh) {
+      if (decltype(KH)::value) {
 #pragma unroll
         for (int e = 0; e < 16; ++e) sm.dqx[strip][e][lane] = acc[e >> 2][e & 3];
       }
       pair_barrier(1 + strip);
-      if (!kh) {
+      if (!decltype(KH)::value) {
 #pragma unroll
         for (int e = 0; e < 16; ++e) acc[e >> 2][e & 3] += sm.dqx[strip][e][lane];
         put(acc, p.dq, p.q_ps, p.scale);
       }
-    }
+    };
+    if (kh) query_side(std::integral_constant<int, 1>{});
+    else query_side(std::integral_constant<int, 0>{});
     __syncthreads();   // every strip of P and dS is written
 
     // ---- even warp: dV_s = (P^T)_s dO; odd warp: dK_s = scale (dS^T)_s Q.  A = the image, transposed on load ----
