@@ -83,6 +83,22 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
+// SW-MSA mask of one query row against the key pairs of a thread, as six bits: bit 3 kh + c3 is set when keys with
+// (window row >= 6) == kh in the n-tile class c3 = nt % 3 lie in another region than the row.  Keys j = 8 nt + 2 t4 (+ 1):
+// their window row (8 nt) / 12 (+ 1 for nt % 3 == 1, t4 >= 2, which never crosses row 6) is >= 6 iff (8 nt) / 12 >= 6, a
+// compile-time fact of nt; their window column is >= 6 iff t4 == 3 (c3 = 0), t4 < 2 (c3 = 1), t4 >= 1 (c3 = 2).
+__device__ __forceinline__ int mask_bits(bool hm, bool wm, bool my_h, bool my_w, int t4) {
+  const bool kw[3] = {t4 == 3, t4 < 2, t4 >= 1};
+  int bits = 0;
+#pragma unroll
+  for (int kh = 0; kh < 2; ++kh)
+#pragma unroll
+    for (int c3 = 0; c3 < 3; ++c3)
+      if ((hm && (kh != 0) != my_h) || (wm && kw[c3] != my_w)) bits |= 1 << (3 * kh + c3);
+  return bits;
+}
+__host__ __device__ constexpr int mask_bit_of(int nt) { return 3 * ((8 * nt) / 12 >= 6 ? 1 : 0) + nt % 3; }
+
 // Token (ty, tx) of window (wy, wx) of image b -> pixel of the (window-aligned) image, cyclic shift folded in.
 __device__ __forceinline__ int64_t token_pixel(const Problem& p, int b, int wy, int wx, int ty, int tx) {
   int y = wy * WS + ty + p.shift, x = wx * WS + tx + p.shift;
@@ -212,6 +228,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     // The query side of the strip, specialised on which half of the key columns this warp takes: every n-tile index is
     // then a compile-time constant (bias offsets, image addresses, tile addresses fold into immediates).
     const float2 nd0 = make_float2(-d0, -d0), nd1 = make_float2(-d1, -d1);
+    const int mb0 = masked ? mask_bits(hm, wm, my_h0, my_w0, t4) : 0, mb1 = masked ? mask_bits(hm, wm, my_h1, my_w1, t4) : 0;
     auto query_side = [&](auto KH) {
       constexpr int kN0 = decltype(KH)::value ? 10 : 0, kCnt = decltype(KH)::value ? 8 : 10;
       // ---- per n-tile: S, dP -> P, dS (bf16 pairs) ----
@@ -238,10 +255,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
           const float2 bb0 = (nt % 3 == 1 ? pb0b : pb0a)[cc], bb1 = (nt % 3 == 1 ? pb1b : pb1a)[cc];
           float m0 = nl0, m1 = nl1;
           if (masked) {   // warp-uniform; both keys of the pair lie in the same region
-            const int jy = (8 * nt) / WS + (nt % 3 == 1 ? hi : 0), jx = 8 * nt + 2 * t4 - jy * WS;
-            const bool kh_ = jy >= 6, kw_ = jx >= 6;
-            if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) m0 += -100.0f * kLog2e;
-            if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) m1 += -100.0f * kLog2e;
+            if (mb0 & (1 << mask_bit_of(nt))) m0 += -100.0f * kLog2e;
+            if (mb1 & (1 << mask_bit_of(nt))) m1 += -100.0f * kLog2e;
           }
           // packed fp32x2 arithmetic: the two keys of a pair share every operand layout
           const float2 e0 = __ffma2_rn(make_float2(sc[0], sc[1]), c1c1, __fadd2_rn(bb0, make_float2(m0, m0)));
@@ -464,6 +479,7 @@ __global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem
     if (w + 1 < w1) fetch(nxt, buf ^ 1);
     const uint32_t tq = s_u32(sm.tile[buf][0]), tk_ = s_u32(sm.tile[buf][1]), tv = s_u32(sm.tile[buf][2]);
 
+    const int mb0 = masked ? mask_bits(hm, wm, my_h0, my_w0, t4) : 0, mb1 = masked ? mask_bits(hm, wm, my_h1, my_w1, t4) : 0;
     uint32_t aq[2][4];
     ldsm_x4(aq[0], tq + r0 * 64 + offa0);
     ldsm_x4(aq[1], tq + r0 * 64 + offa1);
@@ -486,11 +502,9 @@ __global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem
         const int cc = 8 * nt + 11 * ((8 * nt) / WS);   // compile-time after unrolling
         const float2 bb0 = (nt % 3 == 1 ? pb0b : pb0a)[cc], bb1 = (nt % 3 == 1 ? pb1b : pb1a)[cc];
         float2 b0 = bb0, b1 = bb1;
-        if (masked) {
-          const int jy = (8 * nt) / WS + (nt % 3 == 1 ? hi : 0), jx = 8 * nt + 2 * t4 - jy * WS;
-          const bool kh_ = jy >= 6, kw_ = jx >= 6;
-          if ((hm && kh_ != my_h0) || (wm && kw_ != my_w0)) b0 = __fadd2_rn(b0, make_float2(-100.0f * kLog2e, -100.0f * kLog2e));
-          if ((hm && kh_ != my_h1) || (wm && kw_ != my_w1)) b1 = __fadd2_rn(b1, make_float2(-100.0f * kLog2e, -100.0f * kLog2e));
+        if (masked) {   // warp-uniform
+          if (mb0 & (1 << mask_bit_of(nt))) b0 = __fadd2_rn(b0, make_float2(-100.0f * kLog2e, -100.0f * kLog2e));
+          if (mb1 & (1 << mask_bit_of(nt))) b1 = __fadd2_rn(b1, make_float2(-100.0f * kLog2e, -100.0f * kLog2e));
         }
         // packed fp32x2 arithmetic: the two keys of a pair share every operand layout
         t[nn][0] = __ffma2_rn(make_float2(sc[0], sc[1]), c1c1, b0);
