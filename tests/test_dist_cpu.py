@@ -81,3 +81,31 @@ def test_dist_env_defaults_single_process(monkeypatch):
     assert harness.dist_env() == dict(rank=0, local_rank=0, world=1)
     x = torch.ones(3)
     assert harness.all_reduce_mean(x) is x
+
+
+def test_drop_path_gates_are_drawn_once_per_forward_host_logic():
+    """layers.draw_drop_path_gates on CPU tensors: two rows per module and forward (a block gates its attention branch and its
+    MLP branch), values 0 or 1/keep rounded to the requested dtype, modules with rate 0 untouched, a module left without
+    rows draws for itself, eval mode never gates."""
+    sys.path.insert(0, ROOT)
+    from mde_b200 import layers
+    root = torch.nn.Sequential(layers.DropPath(0.1), layers.DropPath(0.3), layers.DropPath(0.0)).train()
+    torch.manual_seed(0)
+    layers.draw_drop_path_gates(root, 4096, "cpu", torch.bfloat16)
+    x = torch.ones(4096, 3, 2)
+    assert root[2]._banked is None and root[2].gate(x) is None
+    for m in (root[0], root[1]):
+        want = float(torch.tensor(1.0 / (1.0 - m.drop_prob)).bfloat16())
+        assert len(m._banked) == 2
+        a, b = m.gate(x), m.gate(x)
+        assert not m._banked and a.shape == b.shape == (4096, 1, 1) and a.dtype == torch.float32
+        assert set(a.unique().tolist()) == {0.0, want} and not torch.equal(a, b)
+        assert abs(float((a > 0).float().mean()) - (1.0 - m.drop_prob)) < 0.03
+        c = m.gate(x)                                    # a third use in the same forward: the module's own draw
+        assert c.shape == (4096, 1, 1) and abs(float((c > 0).float().mean()) - (1.0 - m.drop_prob)) < 0.03
+        y = m(x)                                         # forward keeps the dtype of x
+        assert y.dtype == x.dtype and set(y.unique().tolist()) <= {0.0, float(torch.tensor(1.0 / (1.0 - m.drop_prob)))}
+    layers.draw_drop_path_gates(root, 8, "cpu", torch.float32)
+    assert root[0]._banked[0].shape == (8,) and root[0].gate(torch.ones(4, 2)).shape == (4, 1)   # wrong batch: own draw
+    root.eval()
+    assert root[0].gate(x) is None and torch.equal(root[0](x), x)
