@@ -140,7 +140,8 @@ int swin_attn_forward_host_static(const swin_attn_shape_t* shape,
  * gradient is zero), drops their dq / dk / dv rows and returns instead d_k_pad / d_v_pad (C fp32 each, OVERWRITTEN): the
  * sums of dK / dV over all padding tokens, which the caller adds to the gradient of the projection bias.  k_pad / v_pad may
  * be NULL (zero padding; then the matching d_*_pad must be NULL).  lse: (B, Hp, Wp, nH) as written by the forward.
- * tcgen05 kernel only: bf16, window 7, shift 0 or 3, no mask; returns an error otherwise. */
+ * bf16, no mask; window 7 with shift 0 or 3 (tcgen05 kernel) or window 12 with shift 0 or 6 on a grid at least `shift` tall
+ * and wide (warp-MMA kernel); returns an error otherwise. */
 int swin_attn_backward_unpadded(const swin_attn_shape_t* shape, const void* q, const void* k, const void* v, const void* k_pad,
                                 const void* v_pad, const void* o, const void* d_o, const float* lse, const float* bias_table,
                                 void* dq, void* dk, void* dv, float* d_bias_table, float* d_k_pad, float* d_v_pad, void* stream);

@@ -131,9 +131,11 @@ static int backward_impl(const swin_attn_shape_t* shape, const void* q, const vo
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   bool want_tc = shape->impl != SWIN_ATTN_IMPL_SIMT && attn_mask == nullptr && tc_backward_supported(p, shape->dtype);
   if (shape->impl == SWIN_ATTN_IMPL_TCGEN05 && !want_tc) return fail("tcgen05 backward does not support this shape/dtype");
-  if (ragged && !want_tc)
-    return fail("backward on un-padded tensors needs the tcgen05 kernel (bf16, window 7, shift 0 or 3, no mask, 16-byte "
-                "aligned tensors); pad explicitly otherwise");
+  const bool want_mma12 = !want_tc && (shape->impl == SWIN_ATTN_IMPL_AUTO || shape->impl == SWIN_ATTN_IMPL_WARP_MMA) && attn_mask == nullptr &&
+                          mma12_backward_supported(p, shape->dtype);
+  if (ragged && !want_tc && !want_mma12)
+    return fail("backward on un-padded tensors needs the tcgen05 kernel (bf16, window 7, shift 0 or 3) or the warp-MMA kernel (bf16, "
+                "window 12, shift 0 or 6, height and width >= shift), no mask, 16-byte aligned tensors; pad explicitly otherwise");
   if (want_tc) {
     const char* why = nullptr;
     cudaError_t e = launch_tc_backward(p, st, &why);
@@ -142,7 +144,7 @@ static int backward_impl(const swin_attn_shape_t* shape, const void* q, const vo
   }
   if (shape->impl == SWIN_ATTN_IMPL_WARP_MMA && !mma12_backward_supported(p, shape->dtype))
     return fail("warp-MMA backward does not support this shape/dtype (window 12, bf16, window-aligned, no explicit mask / dropout)");
-  if ((shape->impl == SWIN_ATTN_IMPL_AUTO || shape->impl == SWIN_ATTN_IMPL_WARP_MMA) && mma12_backward_supported(p, shape->dtype)) {   // window 12: warp-MMA kernel
+  if (want_mma12) {   // window 12: warp-MMA kernel
     cudaError_t e = launch_mma12_backward(p, st);
     if (e != cudaSuccess) return fail_cuda("window-12 backward launch", e);
     return 0;

@@ -47,6 +47,7 @@ struct Smem {
   float lse[2][N];
   float dqx[9][16][32];                // dQ partial of the odd warp of a strip: [accumulator register][lane]
   float diag[17 * kDiagLd];            // dS summed over the x diagonals of each (query row, key row) block, per half
+  float padacc[2][HD];                 // un-padded tensors: dV / dK summed over the pad tokens of this head (-> d_vpad / d_kpad)
 };
 // byte offset of 16-byte chunk c of row r in a tile: 8 consecutive rows at one logical chunk (ldmatrix) and 2 rows x 4
 // chunks (cp.async by 8 threads) both cover all 32 banks
@@ -67,6 +68,9 @@ __device__ __forceinline__ void mma_bf16(float (&c)[4], uint32_t a0, uint32_t a1
 }
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, int bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
@@ -99,12 +103,15 @@ __device__ __forceinline__ int mask_bits(bool hm, bool wm, bool my_h, bool my_w,
 }
 __host__ __device__ constexpr int mask_bit_of(int nt) { return 3 * ((8 * nt) / 12 >= 6 ? 1 : 0) + nt % 3; }
 
-// Token (ty, tx) of window (wy, wx) of image b -> pixel of the (window-aligned) image, cyclic shift folded in.
-__device__ __forceinline__ int64_t token_pixel(const Problem& p, int b, int wy, int wx, int ty, int tx) {
+// Token (ty, tx) of window (wy, wx) of image b -> its pixel, cyclic shift folded in; the image is H x W, the windows tile
+// the padded Hp x Wp grid: false for a pad token; `lpix` is the pixel in the padded grid, which is how lse is laid out.
+__device__ __forceinline__ bool token_pixel_padded(const Problem& p, int b, int wy, int wx, int ty, int tx, int64_t& pix, int64_t& lpix) {
   int y = wy * WS + ty + p.shift, x = wx * WS + tx + p.shift;
-  if (y >= p.H) y -= p.H;
-  if (x >= p.W) x -= p.W;
-  return ((int64_t)b * p.H + y) * p.W + x;
+  if (y >= p.Hp) y -= p.Hp;
+  if (x >= p.Wp) x -= p.Wp;
+  pix = ((int64_t)b * p.H + y) * p.W + x;
+  lpix = ((int64_t)b * p.Hp + y) * p.Wp + x;
+  return y < p.H && x < p.W;
 }
 struct Win {
   int b, wy, wx;
@@ -137,6 +144,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     sm.bias2[i] = make_float2(b0, b1);
     sm.bins[i] = 0.f;
   }
+  if (tid < 2 * HD) (&sm.padacc[0][0])[tid] = 0.f;
   const int r0 = strip * 16;
   // ldmatrix lane addressing.  "A pattern": matrices (rows 0-7, cols 0-7) (rows 8-15, cols 0-7) (rows 0-7, cols 8-15)
   // (rows 8-15, cols 8-15); "T pattern" swaps the middle two.
@@ -161,16 +169,35 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   // The five tiles of a window (144 rows x 64 B each: one token per four threads, one 16-byte chunk of each tensor per
   // thread) and its lse row are fetched with cp.async one window ahead, into the other tile buffer.
   const int ft = tid >> 2, fch = tid & 3, fty = ft / WS, ftx = ft - fty * WS;
+  // Un-padded tensors (swin_attn_backward_unpadded): a pad token has no pixel.  Its q, dO, o rows are zero (its output row
+  // was cropped, so no gradient arrives and it sends none: dS = 0), its k / v rows are the pad vectors; lse is laid out
+  // on the padded grid by the forward.
+  const bool padded = p.H != p.Hp || p.W != p.Wp;
+  const __nv_bfloat16* kpad = static_cast<const __nv_bfloat16*>(p.k_pad);
+  const __nv_bfloat16* vpad = static_cast<const __nv_bfloat16*>(p.v_pad);
   auto fetch = [&](const Win& wn, int buf) {
-    const int64_t pix = token_pixel(p, wn.b, wn.wy, wn.wx, fty, ftx);
+    int64_t pix, lpix;
+    const bool ok = token_pixel_padded(p, wn.b, wn.wy, wn.wx, fty, ftx, pix, lpix);
     const int off = h * HD + fch * 8;
     const uint32_t dst = s_u32(sm.tile[buf][0]) + toff(ft, fch);
-    cp_async16(dst, static_cast<const __nv_bfloat16*>(p.q) + pix * p.q_ps + off);
-    cp_async16(dst + 2 * kTile, static_cast<const __nv_bfloat16*>(p.d_o) + pix * p.C + off);
-    cp_async16(dst + 4 * kTile, static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps + off);
-    cp_async16(dst + 6 * kTile, static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps + off);
-    cp_async16(dst + 8 * kTile, static_cast<const __nv_bfloat16*>(p.o_in) + pix * p.C + off);
-    if (fch == 0) cp_async4(s_u32(&sm.lse[buf][ft]), &p.lse[pix * p.nH + h]);
+    if (ok) {
+      cp_async16(dst, static_cast<const __nv_bfloat16*>(p.q) + pix * p.q_ps + off);
+      cp_async16(dst + 2 * kTile, static_cast<const __nv_bfloat16*>(p.d_o) + pix * p.C + off);
+      cp_async16(dst + 4 * kTile, static_cast<const __nv_bfloat16*>(p.k) + pix * p.k_ps + off);
+      cp_async16(dst + 6 * kTile, static_cast<const __nv_bfloat16*>(p.v) + pix * p.v_ps + off);
+      cp_async16(dst + 8 * kTile, static_cast<const __nv_bfloat16*>(p.o_in) + pix * p.C + off);
+    } else {
+      cp_async16_zfill(dst, p.q, 0);
+      cp_async16_zfill(dst + 2 * kTile, p.q, 0);
+      cp_async16_zfill(dst + 4 * kTile, kpad ? static_cast<const void*>(kpad + off) : p.q, kpad ? 16 : 0);
+      cp_async16_zfill(dst + 6 * kTile, vpad ? static_cast<const void*>(vpad + off) : p.q, vpad ? 16 : 0);
+      cp_async16_zfill(dst + 8 * kTile, p.q, 0);
+    }
+    // lse of a pad query row: +inf, so that its probabilities are exactly 0 whatever the forward left there
+    if (fch == 0) {
+      if (ok) cp_async4(s_u32(&sm.lse[buf][ft]), &p.lse[lpix * p.nH + h]);
+      else sm.lse[buf][ft] = INFINITY;
+    }
     cp_async_commit();
   };
   Win cur, nxt;
@@ -192,7 +219,9 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
     const uint32_t tq = s_u32(sm.tile[buf][0]), td = s_u32(sm.tile[buf][1]), tk_ = s_u32(sm.tile[buf][2]), tv = s_u32(sm.tile[buf][3]);
     const unsigned char *tdp = reinterpret_cast<const unsigned char*>(sm.tile[buf][1]), *top = reinterpret_cast<const unsigned char*>(sm.tile[buf][4]);
     const float nl0 = -sm.lse[buf][i0] * kLog2e, nl1 = -sm.lse[buf][i1] * kLog2e;
-    const int64_t pix0 = token_pixel(p, cur.b, cur.wy, cur.wx, iy0, ix0), pix1 = token_pixel(p, cur.b, cur.wy, cur.wx, iy1, ix1);
+    int64_t pix0, pix1, lp_unused;
+    const bool ok0 = token_pixel_padded(p, cur.b, cur.wy, cur.wx, iy0, ix0, pix0, lp_unused);
+    const bool ok1 = token_pixel_padded(p, cur.b, cur.wy, cur.wx, iy1, ix1, pix1, lp_unused);
 
     // ---- delta = rowsum(dO . O) of rows i0, i1: 8 channels per lane of the quad ----
     float d0, d1;
@@ -216,13 +245,27 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
       d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
     }
     // 16 x 32 fp32 accumulator (four n-tiles) -> bf16 -> rows i0 / i1 of an image-order tensor
-    auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl) {
+    // Rows of pad tokens are not stored; `pad_sum` (dV, dK only) adds them up instead: the gradient of the pad vector.
+    auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl, float* pad_sum) {
       __nv_bfloat16* d0p = static_cast<__nv_bfloat16*>(base) + pix0 * ps + h * HD + 2 * t4;
       __nv_bfloat16* d1p = static_cast<__nv_bfloat16*>(base) + pix1 * ps + h * HD + 2 * t4;
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) {
-        *reinterpret_cast<uint32_t*>(d0p + nt * 8) = pack2(acc[nt][0] * scl, acc[nt][1] * scl);
-        *reinterpret_cast<uint32_t*>(d1p + nt * 8) = pack2(acc[nt][2] * scl, acc[nt][3] * scl);
+        if (ok0) *reinterpret_cast<uint32_t*>(d0p + nt * 8) = pack2(acc[nt][0] * scl, acc[nt][1] * scl);
+        if (ok1) *reinterpret_cast<uint32_t*>(d1p + nt * 8) = pack2(acc[nt][2] * scl, acc[nt][3] * scl);
+      }
+      if (pad_sum != nullptr && __any_sync(0xffffffffu, !ok0 || !ok1)) {   // warp-uniform: this strip holds pad tokens
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            float v = (ok0 ? 0.f : acc[nt][e]) + (ok1 ? 0.f : acc[nt][2 + e]);
+            v += __shfl_xor_sync(0xffffffffu, v, 4);     // over the eight row groups g of the strip
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (g == 0) atomicAdd(&pad_sum[nt * 8 + 2 * t4 + e], v * scl);
+          }
+        }
       }
     };
     // The query side of the strip, specialised on which half of the key columns this warp takes: every n-tile index is
@@ -303,7 +346,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
       if (!decltype(KH)::value) {
 #pragma unroll
         for (int e = 0; e < 16; ++e) acc[e >> 2][e & 3] += sm.dqx[strip][e][lane];
-        put(acc, p.dq, p.q_ps, p.scale);
+        put(acc, p.dq, p.q_ps, p.scale, nullptr);
       }
     };
     if (kh) query_side(std::integral_constant<int, 1>{});
@@ -328,8 +371,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         mma_bf16(acc[2], a[0], a[1], a[2], a[3], b1[0], b1[1]);
         mma_bf16(acc[3], a[0], a[1], a[2], a[3], b1[2], b1[3]);
       }
-      if (kh == 0) put(acc, p.dv, p.v_ps, 1.0f);
-      else put(acc, p.dk, p.k_ps, p.scale);
+      if (kh == 0) put(acc, p.dv, p.v_ps, 1.0f, padded ? sm.padacc[0] : nullptr);
+      else put(acc, p.dk, p.k_ps, p.scale, padded ? sm.padacc[1] : nullptr);
     }
     // ---- bias-table gradient: bin (di, dj) += sum over keys (cy, cx) of dS[(cy + di, cx + dj)][(cy, cx)], in two steps.
     // (1) Two threads per (query row qy, key row ky): each takes 6 of the 12 query columns of that 12 x 12 block of dS and
@@ -374,6 +417,10 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   }
   __syncthreads();
   for (int i = tid; i < NT; i += kThreads) atomicAdd(&p.d_table[i * p.nH + h], sm.bins[i]);
+  if (padded && tid < 2 * HD) {
+    float* dst = tid < HD ? p.d_vpad : p.d_kpad;
+    if (dst != nullptr) atomicAdd(&dst[h * HD + (tid & (HD - 1))], (&sm.padacc[0][0])[tid]);
+  }
 }
 
 }  // namespace mma12
@@ -396,10 +443,6 @@ struct SmemF {
   __nv_bfloat16 tile[2][3][kTile];     // q, k, v of the current and the next window
   float2 bias2[NT + 1];
 };
-
-__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, int bytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
-}
 
 __global__ void __launch_bounds__(kFwdThreads, 2) mma12_fwd_kernel(const Problem p, int n_win, int win_per_job) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -605,10 +648,12 @@ cudaError_t launch_mma12_forward(const Problem& p, cudaStream_t st) {
 
 bool mma12_backward_supported(const Problem& p, int dtype) {
   if (dtype != SWIN_ATTN_BF16 || p.ws != 12 || p.mask != nullptr || p.dropout_p > 0.0f) return false;
-  if (p.H != p.Hp || p.W != p.Wp) return false;           // window-aligned tensors (what the op differentiates)
+  if (p.shift != 0 && p.shift != 6) return false;
+  if (p.H < p.shift || p.W < p.shift) return false;        // un-padded tensors: the pad rows would wrap around the rolled image
   if ((p.q_ps | p.k_ps | p.v_ps | p.C) & 7) return false;
   auto mis = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) != 0; };
-  return p.o_in != nullptr && !(mis(p.q) || mis(p.k) || mis(p.v) || mis(p.d_o) || mis(p.o_in) || mis(p.dq) || mis(p.dk) || mis(p.dv));
+  return p.o_in != nullptr && !(mis(p.q) || mis(p.k) || mis(p.v) || mis(p.d_o) || mis(p.o_in) || mis(p.dq) || mis(p.dk) || mis(p.dv) ||
+                                mis(p.k_pad) || mis(p.v_pad));
 }
 
 cudaError_t launch_mma12_backward(const Problem& p, cudaStream_t st) {
@@ -625,6 +670,8 @@ cudaError_t launch_mma12_backward(const Problem& p, cudaStream_t st) {
   chunks = (n_win + per - 1) / per;
   TimedRegion timed(st);
   e = cudaMemsetAsync(p.d_table, 0, sizeof(float) * mma12::NT * p.nH, st);
+  if (e == cudaSuccess && p.d_kpad != nullptr) e = cudaMemsetAsync(p.d_kpad, 0, sizeof(float) * p.C, st);
+  if (e == cudaSuccess && p.d_vpad != nullptr) e = cudaMemsetAsync(p.d_vpad, 0, sizeof(float) * p.C, st);
   if (e != cudaSuccess) return e;
   mma12::mma12_bwd_kernel<<<chunks * p.nH, mma12::kThreads, smem, st>>>(p, n_win, per);
   count_launch();

@@ -651,7 +651,10 @@ struct AttnFunction : public torch::autograd::Function<AttnFunction> {
     ctx->saved_data["seed"] = seed;
     const bool aligned = packed.size(1) % window == 0 && packed.size(2) % window == 0;
     // un-padded tensors: the tcgen05 backward takes them with the pad vectors (swin_attn_backward_unpadded)
-    const bool unpadded_ok = !aligned && packed.scalar_type() == at::kBFloat16 && window == 7 && (shift == 0 || shift == 3) &&
+    // (window 7: tcgen05 kernel; window 12: warp-MMA kernel, which needs the pad rows not to wrap around the rolled image)
+    const bool unpadded_ok = !aligned && packed.scalar_type() == at::kBFloat16 &&
+                             ((window == 7 && (shift == 0 || shift == 3)) ||
+                              (window == 12 && (shift == 0 || shift == 6) && packed.size(1) >= shift && packed.size(2) >= shift)) &&
                              !attn_mask.has_value() && dropout_p == 0.0;
     ctx->saved_data["ok"] = need_lse && (aligned || unpadded_ok);
     ctx->saved_data["unpadded"] = !aligned;

@@ -158,11 +158,14 @@ class _WindowAttentionBase(nn.Module):
         nn.init.trunc_normal_(self.relative_position_bias_table, std=0.02)
         self.softmax = nn.Softmax(dim=-1)  # kept for module-tree parity; the kernel does the softmax
 
-    def _fused_pad_backward(self, shift):
-        """True when the tcgen05 backward takes un-padded tensors (bf16 autocast, window 7, shift 0 / 3, no attention
-        dropout): training then runs the same call as inference -- no F.pad before the Linear, no crop after the
-        attention -- and the gradient of the pad tokens reaches the Linear bias through the op's ``packed_pad`` input."""
-        return (self.window_size[0] == 7 and shift in (0, 3) and self._drop_p() == 0.0 and torch.is_autocast_enabled()
+    def _fused_pad_backward(self, shift, height, width):
+        """True when the backward kernel takes un-padded tensors (bf16 autocast, no attention dropout; window 7, shift
+        0 / 3: tcgen05 kernel; window 12, shift 0 / 6 on a grid at least ``shift`` tall and wide: warp-MMA kernel): training
+        then runs the same call as inference -- no F.pad before the Linear, no crop after the attention -- and the
+        gradient of the pad tokens reaches the Linear bias through the op's ``packed_pad`` input."""
+        ws = self.window_size[0]
+        shape_ok = (ws == 7 and shift in (0, 3)) or (ws == 12 and shift in (0, 6) and height >= shift and width >= shift)
+        return (shape_ok and self._drop_p() == 0.0 and torch.is_autocast_enabled()
                 and torch.get_autocast_dtype("cuda") == torch.bfloat16)
 
     def _drop_p(self):
@@ -197,7 +200,7 @@ class WindowAttention(_WindowAttentionBase):
         tokens take the Linear bias for q/k and zero for v, as in the reference
         where ``F.pad`` precedes the Linear (newcrf_layers.py:212-216)."""
         ws = self.window_size[0]
-        if torch.is_grad_enabled() and not self._fused_pad_backward(shift) and (
+        if torch.is_grad_enabled() and not self._fused_pad_backward(shift, x_img.shape[1], x_img.shape[2]) and (
                 x_img.requires_grad or v_img.requires_grad or self.relative_position_bias_table.requires_grad):
             h, w = x_img.shape[1:3]
             pb, pr = (-h) % ws, (-w) % ws
@@ -233,7 +236,7 @@ class EncoderWindowAttention(_WindowAttentionBase):
     def attend_image(self, x_img, shift):
         """(B, H, W, C) normalised image-order tokens -> attention output before ``proj``."""
         ws = self.window_size[0]
-        if torch.is_grad_enabled() and not self._fused_pad_backward(shift) and (
+        if torch.is_grad_enabled() and not self._fused_pad_backward(shift, x_img.shape[1], x_img.shape[2]) and (
                 x_img.requires_grad or self.relative_position_bias_table.requires_grad):
             h, w = x_img.shape[1:3]
             pb, pr = (-h) % ws, (-w) % ws

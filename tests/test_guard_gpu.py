@@ -123,6 +123,44 @@ def test_backward_writes_nothing_outside_its_outputs(case):
     assert torch.allclose(d_table, want[2], rtol=1e-4, atol=1e-5 * float(want[2].abs().max()))
 
 
+@pytest.mark.parametrize("case", [(7, 3, 2, 15, 23, 3), (12, 6, 1, 13, 25, 2), (12, 0, 2, 22, 31, 3), (12, 6, 1, 29, 17, 5)])
+def test_unpadded_backward_writes_nothing_outside_its_outputs(case):
+    """swin_attn_backward_unpadded (tcgen05 window 7, warp-MMA window 12): guard bands around dq | dk | dv, d_table and the
+    pad-vector gradients; finite results."""
+    ws, shift, b, h, w, nh = case
+    c = nh * 32
+    name = f"guardu{case}"
+    hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
+    packed, _pf = _guarded_in(randn(name + ".p", b, h, w, 3 * c).bfloat16())
+    table, _t = _guarded_in(0.5 * randn(name + ".t", (2 * ws - 1) ** 2, nh))
+    pads, _p = _guarded_in(randn(name + ".pad", 3 * c).bfloat16())
+    o_t, lse_t = torch.ops.swin_attn.fwd(packed.clone(), None, table.clone(), pads.clone(), None, ws, shift, nh, 32 ** -0.5, True,
+                                         _lib.IMPL_AUTO, None)
+    assert lse_t.shape == (b, hp, wp, nh)
+    o, _o = _guarded_in(o_t)
+    lse, _l = _guarded_in(lse_t)
+    d_o, _d = _guarded_in(randn(name + ".c", b, h, w, c).bfloat16())
+    d_packed, dp_full = _guarded_out((b, h, w, 3 * c), torch.bfloat16)
+    d_table, dt_full = _guarded_out(((2 * ws - 1) ** 2, nh), torch.float32)
+    d_kv_pad, dkv_full = _guarded_out((2 * c,), torch.float32)
+    es = 2
+    base, dbase = packed.data_ptr(), d_packed.data_ptr()
+    shp = _lib.Shape(b, h, w, nh, ws, shift, _lib.BF16, _lib.IMPL_AUTO, 32 ** -0.5, 0.0, 0, 3 * c, 3 * c, 3 * c, c, 0, 0)
+    lib = _lib.load()
+    vp = ctypes.c_void_p
+    rc = lib.swin_attn_backward_unpadded(ctypes.byref(shp), vp(base), vp(base + c * es), vp(base + 2 * c * es),
+                                         vp(pads.data_ptr() + c * es), vp(pads.data_ptr() + 2 * c * es), _ptr(o), _ptr(d_o), _ptr(lse),
+                                         _ptr(table), vp(dbase), vp(dbase + c * es), vp(dbase + 2 * c * es), _ptr(d_table),
+                                         vp(d_kv_pad.data_ptr()), vp(d_kv_pad.data_ptr() + c * 4), None)
+    assert rc == 0, lib.swin_attn_last_error().decode()
+    torch.cuda.synchronize()
+    assert _bands_intact(dp_full, d_packed.numel()), "write outside dq / dk / dv"
+    assert _bands_intact(dt_full, d_table.numel()), "write outside d_table"
+    assert _bands_intact(dkv_full, d_kv_pad.numel()), "write outside d_k_pad / d_v_pad"
+    assert torch.isfinite(d_packed.float()).all() and torch.isfinite(d_table).all() and torch.isfinite(d_kv_pad).all()
+    assert float(d_kv_pad.abs().max()) > 0.0
+
+
 @pytest.mark.parametrize("case", [(2, 418, 4, 64, torch.bfloat16), (1, 300, 2, 64, torch.bfloat16), (2, 77, 3, 32, torch.float32),
                                   (1, 449, 2, 64, torch.bfloat16)])
 def test_global_attention_writes_nothing_outside_its_outputs(case):

@@ -1069,6 +1069,11 @@ UNPADDED_BWD_CASES = [  # ws, shift, B, H, W, nH, external_v : H or W not a mult
     # full size: large07 stage 3 (48 heads) and decoder level crf3 (32 heads, external v) at batch 8, both BASELINE shapes
     (7, 3, 8, 11, 38, 48, False), (7, 0, 8, 11, 38, 32, True), (7, 3, 8, 15, 20, 32, True), (7, 0, 8, 15, 20, 48, False),
     (7, 3, 8, 22, 76, 24, False),
+    # window 12 (warp-MMA backward): pads along both axes, along one, spanning two window rows of a shifted block, a single
+    # window, external v; then the large12 training grids of a 480 x 640 image (120x160, 30x40, 15x20) at batch 2
+    (12, 6, 1, 13, 25, 2, False), (12, 0, 2, 13, 25, 2, True), (12, 6, 2, 24, 31, 3, False), (12, 0, 1, 35, 24, 2, False),
+    (12, 6, 2, 7, 9, 1, True), (12, 6, 1, 30, 18, 26, False),
+    (12, 6, 2, 120, 160, 6, False), (12, 0, 2, 30, 40, 24, False), (12, 6, 2, 15, 20, 48, False),
 ]
 
 
