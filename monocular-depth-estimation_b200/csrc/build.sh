@@ -11,12 +11,12 @@ flags=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompil
 [ "${SWIN_TC_TRACE:-0}" = "1" ] && flags+=(-DSWIN_TC_TRACE)
 mkdir -p "$here/build"
 pids=()
-for f in swin_attn_simt swin_attn_tc swin_attn_tc12 swin_attn_mma12_bwd swin_attn_tc_bwd swin_linear_tc swin_block_ops mha_global mha_tc swin_attn_api; do
+for f in swin_attn_simt swin_attn_tc swin_attn_tc12 swin_attn_mma12 swin_attn_tc_bwd swin_linear_tc swin_block_ops mha_global mha_tc swin_attn_api; do
   "$NVCC" "${flags[@]}" -c "$here/$f.cu" -o "$here/build/$f.o" > "$here/build/$f.log" 2>&1 &
   pids+=($!)
 done
 for p in "${pids[@]}"; do wait "$p" || { cat "$here"/build/*.log; exit 1; }; done
-"$NVCC" -shared -o "$out" "$here"/build/swin_attn_simt.o "$here"/build/swin_attn_tc.o "$here"/build/swin_attn_tc12.o "$here"/build/swin_attn_mma12_bwd.o "$here"/build/swin_attn_tc_bwd.o "$here"/build/swin_linear_tc.o "$here"/build/swin_block_ops.o "$here"/build/mha_global.o "$here"/build/mha_tc.o "$here"/build/swin_attn_api.o -lcudart
+"$NVCC" -shared -o "$out" "$here"/build/swin_attn_simt.o "$here"/build/swin_attn_tc.o "$here"/build/swin_attn_tc12.o "$here"/build/swin_attn_mma12.o "$here"/build/swin_attn_tc_bwd.o "$here"/build/swin_linear_tc.o "$here"/build/swin_block_ops.o "$here"/build/mha_global.o "$here"/build/mha_tc.o "$here"/build/swin_attn_api.o -lcudart
 echo "built $out"
 
 # torch.library binding (C++ dispatcher ops over the C ABI): host-only code, g++, links libswin_attn.so by $ORIGIN

@@ -1,6 +1,7 @@
-// Tensor-core backward of the window-12 attention (bf16, window-aligned tensors, analytic SW-MSA mask): the ODA / timm
-// Swin-L/384 sibling of SURVEY.md §8f row 3 and the window-12 rows of the microbench sweep.  Round 1 served this shape on
-// the CUDA cores at 0.013 of the HBM roofline (2.4 ms per stage-0 launch).
+// Warp-level tensor-core kernels of the window-12 attention (bf16, analytic SW-MSA mask, window-aligned or un-padded tensors):
+// the backward (first) and the forward (second half of this file) of the ODA / timm Swin-L/384 sibling of SURVEY.md §8f row 3,
+// of the window-12 NewCRFs variants (NewCRFDepth "large12", NewCRFDepth.py:26) and of the window-12 rows of the microbench
+// sweep.  Round 1 served the backward on the CUDA cores at 0.013 of the HBM roofline (2.4 ms per stage-0 launch).
 //
 // N = 144 tokens = 9 x 16: the window fits the warp-level m16n8k16 bf16 MMA (`mma.sync`) without any padding, which the
 // 128-lane tcgen05 accumulator does not (144 = 128 + 16 or 72 + 72: 44 % of the tile wasted, and the S + dP + dQ/dK/dV

@@ -28,7 +28,7 @@
 // columns of pad tokens) and the PV product takes a tenth K-step whose P columns 144 / 145 hold the hi / lo bf16
 // halves of the row's summed probability over pad tokens.  Window-aligned launches run the 144 / 9-step shapes.
 //
-// Not covered here (served by the CUDA-core kernels): explicit masks, fp32; the backward is swin_attn_mma12_bwd.cu.
+// Not covered here (served by the CUDA-core kernels): explicit masks, fp32; the backward is swin_attn_mma12.cu.
 #include "swin_attn_tc.cuh"
 
 namespace swin {

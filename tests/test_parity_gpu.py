@@ -127,7 +127,7 @@ def test_forward_ws12_tcgen05_on_unaligned_tensors_matches_oracle(case):
     check(rel_err(got.float(), ref.float()), TOL_BF16, "ws12 tcgen05 vs CUDA-core kernel, un-aligned")
 
 
-# The warp-MMA forward of swin_attn_mma12_bwd.cu (online softmax over three key chunks, pad vectors written into the K / V
+# The warp-MMA forward of swin_attn_mma12.cu (online softmax over three key chunks, pad vectors written into the K / V
 # rows of pad tokens by the gather): what impl AUTO runs on window-12 grids, aligned or not
 @pytest.mark.parametrize("case", [c + (True,) for c in TC12_CASES] + TC12_PAD_CASES)
 def test_forward_ws12_warp_mma_matches_oracle(case):
