@@ -207,6 +207,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   cur.b = w0 / (p.nWx * p.nWy);
   nxt = cur;
   if (w0 < w1) fetch(cur, 0);
+  float padreg[4][2] = {};   // un-padded tensors: this thread's share of dV (even warps) / dK (odd warps) summed over pad tokens
 
   for (int w = w0; w < w1; ++w, cur = nxt) {
     const int buf = (w - w0) & 1;
@@ -246,8 +247,9 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
       d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
     }
     // 16 x 32 fp32 accumulator (four n-tiles) -> bf16 -> rows i0 / i1 of an image-order tensor
-    // Rows of pad tokens are not stored; `pad_sum` (dV, dK only) adds them up instead: the gradient of the pad vector.
-    auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl, float* pad_sum) {
+    // Rows of pad tokens are not stored; with `pad_sum` (dV, dK only) they are added up instead, per thread over all the
+    // windows of the job: the gradient of the pad vector.
+    auto put = [&](float (&acc)[4][4], void* base, int64_t ps, float scl, bool pad_sum) {
       __nv_bfloat16* d0p = static_cast<__nv_bfloat16*>(base) + pix0 * ps + h * HD + 2 * t4;
       __nv_bfloat16* d1p = static_cast<__nv_bfloat16*>(base) + pix1 * ps + h * HD + 2 * t4;
 #pragma unroll
@@ -255,16 +257,16 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         if (ok0) *reinterpret_cast<uint32_t*>(d0p + nt * 8) = pack2(acc[nt][0] * scl, acc[nt][1] * scl);
         if (ok1) *reinterpret_cast<uint32_t*>(d1p + nt * 8) = pack2(acc[nt][2] * scl, acc[nt][3] * scl);
       }
-      if (pad_sum != nullptr && __any_sync(0xffffffffu, !ok0 || !ok1)) {   // warp-uniform: this strip holds pad tokens
+      if (pad_sum) {
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            float v = (ok0 ? 0.f : acc[nt][e]) + (ok1 ? 0.f : acc[nt][2 + e]);
-            v += __shfl_xor_sync(0xffffffffu, v, 4);     // over the eight row groups g of the strip
-            v += __shfl_xor_sync(0xffffffffu, v, 8);
-            v += __shfl_xor_sync(0xffffffffu, v, 16);
-            if (g == 0) atomicAdd(&pad_sum[nt * 8 + 2 * t4 + e], v * scl);
+          if (!ok0) {
+            padreg[nt][0] += acc[nt][0];
+            padreg[nt][1] += acc[nt][1];
+          }
+          if (!ok1) {
+            padreg[nt][0] += acc[nt][2];
+            padreg[nt][1] += acc[nt][3];
           }
         }
       }
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
       if (!decltype(KH)::value) {
 #pragma unroll
         for (int e = 0; e < 16; ++e) acc[e >> 2][e & 3] += sm.dqx[strip][e][lane];
-        put(acc, p.dq, p.q_ps, p.scale, nullptr);
+        put(acc, p.dq, p.q_ps, p.scale, false);
       }
     };
     if (kh) query_side(std::integral_constant<int, 1>{});
@@ -372,8 +374,8 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
         mma_bf16(acc[2], a[0], a[1], a[2], a[3], b1[0], b1[1]);
         mma_bf16(acc[3], a[0], a[1], a[2], a[3], b1[2], b1[3]);
       }
-      if (kh == 0) put(acc, p.dv, p.v_ps, 1.0f, padded ? sm.padacc[0] : nullptr);
-      else put(acc, p.dk, p.k_ps, p.scale, padded ? sm.padacc[1] : nullptr);
+      if (kh == 0) put(acc, p.dv, p.v_ps, 1.0f, padded);
+      else put(acc, p.dk, p.k_ps, p.scale, padded);
     }
     // ---- bias-table gradient: bin (di, dj) += sum over keys (cy, cx) of dS[(cy + di, cx + dj)][(cy, cx)], in two steps.
     // (1) Two threads per (query row qy, key row ky): each takes 6 of the 12 query columns of that 12 x 12 block of dS and
@@ -418,9 +420,24 @@ __global__ void __launch_bounds__(kThreads, 1) mma12_bwd_kernel(const Problem p,
   }
   __syncthreads();
   for (int i = tid; i < NT; i += kThreads) atomicAdd(&p.d_table[i * p.nH + h], sm.bins[i]);
-  if (padded && tid < 2 * HD) {
-    float* dst = tid < HD ? p.d_vpad : p.d_kpad;
-    if (dst != nullptr) atomicAdd(&dst[h * HD + (tid & (HD - 1))], (&sm.padacc[0][0])[tid]);
+  if (padded) {
+    // over the eight row groups of the warp, then the nine warps of a kind through shared memory, then one atomic per channel
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        float v = padreg[nt][e];
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        if (g == 0) atomicAdd(&sm.padacc[kh][nt * 8 + 2 * t4 + e], v * (kh ? p.scale : 1.0f));
+      }
+    }
+    __syncthreads();
+    if (tid < 2 * HD) {
+      float* dst = tid < HD ? p.d_vpad : p.d_kpad;
+      if (dst != nullptr) atomicAdd(&dst[h * HD + (tid & (HD - 1))], (&sm.padacc[0][0])[tid]);
+    }
   }
 }
 

@@ -38,6 +38,9 @@ def main():
     ap.add_argument("--impl", default="both", choices=["both", "auto", "simt", "tc", "mma"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--flush", action="store_true", default=True)
+    ap.add_argument("--unpadded", action="store_true",
+                    help="--bwd on un-aligned grids: time swin_attn_backward_unpadded on the un-padded tensors (what the layers "
+                         "call in bf16 training) instead of the window-aligned backward on explicitly padded ones")
     args = ap.parse_args()
     dev = torch.device("cuda")
     dt = torch.bfloat16 if args.dtype == "bf16" else torch.float32
@@ -56,14 +59,23 @@ def main():
         v = torch.randn(b, h, w, c, device=dev, generator=g).to(dt) if ext else None
         table = 0.02 * torch.randn((2 * ws - 1) ** 2, nh, device=dev, generator=g)
         pad = (0.1 * torch.randn(packed.shape[-1], device=dev, generator=g)).to(dt)
-        if args.bwd and (h % ws or w % ws):   # the backward takes window-aligned tensors (the layers pad explicitly)
+        unpadded = args.bwd and args.unpadded and (h % ws or w % ws) and dt == torch.bfloat16
+        if args.bwd and (h % ws or w % ws) and not unpadded:   # the window-aligned backward: pad explicitly
             hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
             packed = torch.nn.functional.pad(packed, (0, 0, 0, wp - w, 0, hp - h)).contiguous()
             v = None if v is None else torch.nn.functional.pad(v, (0, 0, 0, wp - w, 0, hp - h)).contiguous()
             h, w = hp, wp
         for shift in (0, ws // 2):
             for iname, impl in impls.items():
-                if args.bwd:
+                if unpadded:
+                    if iname != "auto":
+                        continue
+                    o, lse = torch.ops.swin_attn.fwd(packed, v, table, pad, None, ws, shift, nh, 32 ** -0.5, True, impl, None)
+                    d_o = torch.randn(b, h, w, c, device=dev, generator=g).to(dt)
+
+                    def run():
+                        return torch.ops.swin_attn.bwd_unpadded(d_o, packed, v, o, lse, table, pad, None, ws, shift, nh, 32 ** -0.5)
+                elif args.bwd:
                     o, lse = torch.ops.swin_attn.fwd(packed, v, table, None, None, ws, shift, nh, 32 ** -0.5, True, impl, None)
                     d_o = torch.randn(b, h, w, c, device=dev, generator=g).to(dt)
 
@@ -92,7 +104,7 @@ def main():
                 nbytes = (7 if args.bwd else 4) * b * h * w * c * packed.element_size() + (b * h * w * nh * 4 if args.bwd else 0)
                 hp, wp = -(-h // ws) * ws, -(-w // ws) * ws
                 flops = (10 if args.bwd else 4) * b * hp * wp * ws * ws * c
-                print(json.dumps({"case": name, "pass": "bwd" if args.bwd else "fwd", "shift": shift, "impl": iname, "dtype": args.dtype, "us": round(ms * 1e3, 2),
+                print(json.dumps({"case": name, "pass": "bwd" if args.bwd else "fwd", "shift": shift, "impl": iname + ("-unpadded" if unpadded else ""), "dtype": args.dtype, "us": round(ms * 1e3, 2),
                                   "GBps": round(nbytes / ms / 1e6, 1), "hbm_frac": round(nbytes / ms / 1e6 / hbm, 4),
                                   "TFLOPs": round(flops / ms / 1e9, 2), "MB": round(nbytes / 1e6, 1)}), flush=True)
 
