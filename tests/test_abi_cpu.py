@@ -239,3 +239,36 @@ def test_swin_checkpoint_loading_follows_the_reference_loader():
     missing, unexpected = same.load_pretrained_state({"state_dict": moby})
     assert not missing and not unexpected
     assert all(torch.equal(a, b) for a, b in zip(same.state_dict().values(), src.state_dict().values()))
+
+
+def test_impl_selectors_match_the_header_and_are_validated_without_gpu():
+    """SWIN_ATTN_IMPL_*: the ctypes mirror carries the header's values; impl = WARP_MMA on a shape that has no warp-MMA kernel
+    (window 7) is an error, not a silent downgrade; swin_attn_uses_tcgen05 says which family serves a shape (host logic)."""
+    import re
+    hdr = open(os.path.join(ROOT, "include", "swin_attn.h")).read()
+    enum = dict((k, int(v)) for k, v in re.findall(r"SWIN_ATTN_(IMPL_[A-Z0-9_]+) = (\d+)", hdr))
+    assert enum == {"IMPL_AUTO": _lib.IMPL_AUTO, "IMPL_SIMT": _lib.IMPL_SIMT, "IMPL_TCGEN05": _lib.IMPL_TCGEN05,
+                    "IMPL_WARP_MMA": _lib.IMPL_WARP_MMA}
+    lib = _lib.load()
+    buf = (ctypes.c_float * 4096)()
+    base = ctypes.addressof(buf)
+    base += (-base) % 16
+    ptr = ctypes.c_void_p(base)
+    c = 64
+    shp7 = _lib.Shape(1, 14, 14, 2, 7, 3, _lib.BF16, _lib.IMPL_WARP_MMA, 32 ** -0.5, 0.0, 0, 3 * c, 3 * c, 3 * c, c, 0, 0)
+    assert lib.swin_attn_forward(ctypes.byref(shp7), ptr, ptr, ptr, None, None, None, ptr, None, ptr, None, None) != 0
+    assert b"warp-MMA forward does not support" in lib.swin_attn_last_error()
+    assert lib.swin_attn_backward(ctypes.byref(shp7), ptr, ptr, ptr, ptr, ptr, ptr, ptr, None, ptr, ptr, ptr, ptr, None) != 0
+    assert b"warp-MMA backward does not support" in lib.swin_attn_last_error()
+
+    def uses_tc(ws, shift, h, w, impl, backward):
+        s = _lib.Shape(1, h, w, 2, ws, shift, _lib.BF16, impl, 32 ** -0.5, 0.0, 0, 3 * c, 3 * c, 3 * c, c, 0, 0)
+        return lib.swin_attn_uses_tcgen05(ctypes.byref(s), backward)
+
+    if lib.swin_attn_uses_tcgen05(ctypes.byref(_lib.Shape(1, 14, 14, 2, 7, 3, _lib.BF16, _lib.IMPL_AUTO, 32 ** -0.5, 0.0, 0, 3 * c,
+                                                          3 * c, 3 * c, c, 0, 0)), 0) == 1:   # the driver API is present (TMA encode)
+        assert uses_tc(7, 3, 15, 23, _lib.IMPL_AUTO, 0) == 1 and uses_tc(7, 0, 14, 14, _lib.IMPL_AUTO, 1) == 1
+        assert uses_tc(12, 6, 24, 36, _lib.IMPL_TCGEN05, 0) == 1          # the tcgen05 window-12 forward, on request
+    assert uses_tc(12, 6, 24, 36, _lib.IMPL_AUTO, 0) == 0                 # window 12: warp-MMA kernels by default
+    assert uses_tc(12, 6, 13, 25, _lib.IMPL_AUTO, 0) == 0 and uses_tc(12, 0, 24, 36, _lib.IMPL_AUTO, 1) == 0
+    assert uses_tc(7, 3, 14, 14, _lib.IMPL_SIMT, 0) == 0 and uses_tc(7, 3, 14, 14, _lib.IMPL_WARP_MMA, 0) == 0
